@@ -1,0 +1,118 @@
+"""ctypes binding of libfcnod_b200.so (the C ABI declared in include/fcnod_b200.h).
+
+There is no CPU fallback anywhere in this package: if the shared library is
+missing, or a compute entry point fails (e.g. no CUDA device), an exception is
+raised.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libfcnod_b200.so')
+
+FCNOD_PRECISION_FP32 = 0
+FCNOD_PRECISION_BF16 = 1
+FCNOD_MAX_DET = 64
+
+
+class FcnodError(RuntimeError):
+    pass
+
+
+class PostnetParams(C.Structure):
+    _fields_ = [('prob_thresh', C.c_float), ('min_boxes', C.c_int), ('eps', C.c_double),
+                ('net_w', C.c_int), ('net_h', C.c_int), ('stride', C.c_int),
+                ('skip_background', C.c_int), ('min_height', C.c_int)]
+
+
+class AugDraw(C.Structure):
+    _fields_ = [('flip', C.c_int32), ('shift_x', C.c_int32), ('shift_y', C.c_int32),
+                ('sign_x', C.c_int32), ('sign_y', C.c_int32), ('_pad', C.c_int32),
+                ('f1', C.c_double), ('f2', C.c_double)]
+
+
+_P = C.c_void_p
+_I = C.c_int
+_SZ = C.c_size_t
+_STR = C.c_char_p
+
+# name -> (restype, argtypes); every symbol include/fcnod_b200.h declares
+SIGNATURES = {
+    'fcnod_version': (_I, []),
+    'fcnod_last_error': (_STR, []),
+    'fcnod_device_count': (_I, [C.POINTER(_I)]),
+    'fcnod_net_create': (_I, [_STR, _STR, _I, _I, C.POINTER(_P)]),
+    'fcnod_net_destroy': (_I, [_P]),
+    'fcnod_net_reshape': (_I, [_P, _I]),
+    'fcnod_net_input_dims': (_I, [_P, C.POINTER(_I * 4)]),
+    'fcnod_net_blob_dims': (_I, [_P, _STR, C.POINTER(_I * 4)]),
+    'fcnod_net_num_blobs': (_I, [_P]),
+    'fcnod_net_blob_name': (_STR, [_P, _I]),
+    'fcnod_net_describe': (_I, [_P, _P, _SZ]),
+    'fcnod_net_launches_per_forward': (_I, [_P]),
+    'fcnod_net_forward': (_I, [_P, _P]),
+    'fcnod_net_forward_device': (_I, [_P, _P, _P]),
+    'fcnod_net_blob_read': (_I, [_P, _STR, _P, _SZ]),
+    'fcnod_net_output_device': (_I, [_P, _STR, C.POINTER(_P)]),
+    'fcnod_net_run_step': (_I, [_P, _I, _I, _P]),
+    'fcnod_postnet_default_params': (None, [C.POINTER(PostnetParams)]),
+    'fcnod_postnet_scratch_bytes': (_SZ, [_I, _I]),
+    'fcnod_postnet_device': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P, _P, _P]),
+    'fcnod_postnet': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P]),
+    'fcnod_preprocess': (_I, [_P, _I, _I, _I, _I, _I, _P]),
+    'fcnod_preprocess_device': (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
+    'fcnod_detect': (_I, [_P, _P, _I, _I, _I, C.POINTER(PostnetParams), _P, _P, _P, _P]),
+    'fcnod_detect_from_data': (_I, [_P, _P, _I, C.POINTER(PostnetParams), _P, _P, _P, _P]),
+    'fcnod_detect_device': (_I, [_P, _P, _I, C.POINTER(PostnetParams), C.POINTER(_P), C.POINTER(_P),
+                                 C.POINTER(_P), C.POINTER(_P), _P]),
+    'fcnod_detect_graph_build': (_I, [_P, _P, _I, C.POINTER(PostnetParams), _P]),
+    'fcnod_detect_graph_launch': (_I, [_P, _P]),
+    'fcnod_label_raster_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P]),
+    'fcnod_label_raster': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
+    'fcnod_aug_scratch_bytes': (_SZ, [_I]),
+    'fcnod_aug_forward_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_aug_forward': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises if it has not been built (python -m fcn_object_detector_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FcnodError('%s is missing: build it with `python -m fcn_object_detector_b200.build` '
+                             '(there is no CPU fallback)' % LIB_PATH)
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().fcnod_last_error()
+        raise FcnodError(msg.decode() if msg else 'fcnod call failed')
+
+
+def ptr(a):
+    """Data pointer of a C-contiguous numpy array (or None)."""
+    if a is None:
+        return None
+    if not a.flags['C_CONTIGUOUS']:
+        raise ValueError('array must be C-contiguous')
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def default_postnet_params(**kw):
+    p = PostnetParams()
+    lib().fcnod_postnet_default_params(C.byref(p))
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise AttributeError(k)
+        setattr(p, k, v)
+    return p

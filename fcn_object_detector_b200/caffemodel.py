@@ -1,0 +1,72 @@
+"""Writer for Caffe `.caffemodel` files (binary protobuf `NetParameter`).
+
+The upstream launch file points at `models/snapshot_iter_1000.caffemodel`
+(/root/reference/launch/fcn_object_detector.launch:8) which is not shipped
+(/root/reference/.MISSING_LARGE_BLOBS:1).  The product reads such files in C++
+(csrc/caffemodel.cpp); this module only *writes* them, so that tests, smoke and
+bench can synthesise weights with the fillers the prototxt declares (xavier
+weights, constant bias -- /root/reference/models/deploy.prototxt:38-45).
+
+Wire layout used (caffe.proto): NetParameter{name=1, layer=100};
+LayerParameter{name=1, type=2, blobs=7}; BlobProto{data=5 packed float,
+shape=7}; BlobShape{dim=1 packed int64}.
+"""
+import struct
+import numpy as np
+
+
+def _varint(n):
+    out = bytearray()
+    while True:
+        b = n & 0x7F
+        n >>= 7
+        if n:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _ld(field, payload):
+    return _varint((field << 3) | 2) + _varint(len(payload)) + payload
+
+
+def _blob(arr, legacy=False):
+    arr = np.ascontiguousarray(arr, dtype='<f4')
+    if legacy:
+        dims = list(arr.shape)
+        dims = [1] * (4 - len(dims)) + dims
+        head = b''.join(_varint((f << 3) | 0) + _varint(d) for f, d in zip((1, 2, 3, 4), dims))
+        return head + _ld(5, arr.tobytes())
+    shape = _ld(1, b''.join(_varint(d) for d in arr.shape))
+    return _ld(7, shape) + _ld(5, arr.tobytes())
+
+
+def write_caffemodel(path, layers, net_name='fcn_detector', legacy_shape=False):
+    """layers: iterable of (name, type, [ndarray blobs])."""
+    body = _ld(1, net_name.encode())
+    for name, typ, blobs in layers:
+        lp = _ld(1, name.encode()) + _ld(2, typ.encode())
+        for b in blobs:
+            lp += _ld(7, _blob(b, legacy_shape))
+        body += _ld(100, lp)
+    with open(path, 'wb') as f:
+        f.write(body)
+    return path
+
+
+def xavier_weights(conv_shapes, seed=0):
+    """Caffe 'xavier' filler: U(-s, s), s = sqrt(3 / fan_in); constant bias."""
+    rng = np.random.RandomState(seed)
+    out = []
+    for name, cout, cin, k, bias in conv_shapes:
+        s = np.sqrt(3.0 / (cin * k * k))
+        w = rng.uniform(-s, s, size=(cout, cin, k, k)).astype(np.float32)
+        b = np.full((cout,), bias, dtype=np.float32)
+        out.append((name, 'Convolution', [w, b]))
+    return out
+
+
+def write_synthetic_caffemodel(path, seed=0, **kw):
+    from .netspec import conv_shapes
+    return write_caffemodel(path, xavier_weights(conv_shapes(**kw), seed))

@@ -1,0 +1,50 @@
+// Host-side network definition readers: Caffe prototxt (text) + caffemodel (binary protobuf).
+//
+// Replaces what `caffe.Net(proto, weights, caffe.TEST)` does at
+// /root/reference/scripts/fcn_object_detector.py:317 for the layer types that
+// /root/reference/models/deploy.prototxt:1-2178 uses.  No protoc / libprotobuf:
+// the text format is parsed by a small recursive-descent reader and the binary
+// format by a wire-format walker (field numbers from caffe.proto, listed in
+// caffemodel.cpp).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+namespace fcnod {
+
+enum LayerType { L_CONV, L_RELU, L_POOL, L_LRN, L_CONCAT, L_POWER, L_DROPOUT, L_SIGMOID, L_UNKNOWN };
+
+struct LayerDef {
+    std::string name, type_name;
+    LayerType type = L_UNKNOWN;
+    std::vector<std::string> bottom, top;
+    // Convolution / Pooling
+    int num_output = 0, kernel = 1, stride = 1, pad = 0;
+    bool bias_term = true;
+    bool pool_max = true;
+    // LRN
+    int local_size = 5;
+    float alpha = 1.f, beta = 0.75f, lrn_k = 1.f;
+    // Power
+    float power = 1.f, scale = 1.f, shift = 0.f;
+};
+
+struct NetDef {
+    std::string input_name;
+    int input_dims[4] = {0, 0, 0, 0};
+    std::vector<LayerDef> layers;
+};
+
+struct HostBlob {
+    std::vector<int> shape;
+    std::vector<float> data;
+};
+typedef std::map<std::string, std::vector<HostBlob> > WeightMap;
+
+// Both throw std::runtime_error with a message on malformed input.
+NetDef parse_prototxt_file(const std::string& path);
+NetDef parse_prototxt_text(const std::string& text);
+WeightMap read_caffemodel(const std::string& path);
+
+}  // namespace fcnod

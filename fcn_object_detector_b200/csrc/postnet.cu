@@ -1,0 +1,331 @@
+// Post-net stage on the device: coverage threshold -> grid-box decode -> cv::groupRectangles
+// clustering -> height filter / confidence -> rescale to source pixels.
+//
+// Restates, for B frames at once, the per-frame Python of
+// /root/reference/scripts/fcn_object_detector.py:
+//   per-class loop            :89-90,104-118      (skip coverage channel 0, bbox channels 4*index..)
+//   gridbox_to_boxes          :357-394            (row-major candidate order, float32 + int -> float64)
+//   vote_boxes                :337-351            (cv.groupRectangles on [x1,y1,x2,y2] "as if" x,y,w,h)
+//   resize_detection          :396-405            (double scale, truncation toward zero)
+// and OpenCV's groupRectangles (objdetect/cascadedetect.cpp: SimilarRects + partition +
+// fp32 mean with round-half-even + containment filter).  Integer / double arithmetic only:
+// results are bit-exact against the oracle (tests/test_postnet_gpu.py).
+//
+// Kernel 1 (decode_group_kernel): one CTA per (frame, foreground class).  Coverage is read
+//   with coalesced loads, candidates are compacted IN ROW-MAJOR ORDER with warp ballots +
+//   a cross-warp scan, kept in shared memory, clustered there (min-label propagation with
+//   pointer jumping = connected components, class order = smallest member index, exactly
+//   what cv::partition yields), reduced with shared-memory atomics and filtered.
+// Kernel 2 (assemble_kernel): one warp per frame concatenates the per-class lists in
+//   class order and rescales.
+#include <cmath>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace fcnod {
+namespace {
+
+constexpr int kMaxCand = 1024;     // grid cells per (frame, class) handled in shared memory
+constexpr int kThreads = 256;
+
+struct PostParams {
+    float prob_thresh;
+    int group_threshold;
+    double eps;
+    int cell_w, cell_h;
+    int rows_used;
+    int skip_bg;
+    int min_height;
+    int net_w, net_h;
+};
+
+// exclusive, order-preserving block scan of a 0/1 flag; returns this thread's offset and the block total
+__device__ __forceinline__ int block_scan_flag(bool flag, int* warp_tot /*[8]*/, int* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned m = __ballot_sync(0xffffffffu, flag);
+    int pre = __popc(m & ((1u << lane) - 1u));
+    if (lane == 0) warp_tot[warp] = __popc(m);
+    __syncthreads();
+    int base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) {
+        int t = warp_tot[w];
+        if (w < warp) base += t;
+        tot += t;
+    }
+    __syncthreads();
+    *total = tot;
+    return base + pre;
+}
+
+__global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __restrict__ coverage,
+                                                               const float* __restrict__ bboxes, int c_cvg, int c_bbox,
+                                                               int gh, int gw, PostParams P,
+                                                               int32_t* __restrict__ cls_det /*[B][ncls][MAX_DET][6]*/,
+                                                               int32_t* __restrict__ cls_cnt /*[B][ncls]*/) {
+    __shared__ int rx[kMaxCand], ry[kMaxCand], rw[kMaxCand], rh[kMaxCand];
+    __shared__ int lab[kMaxCand];
+    __shared__ int sx[kMaxCand], sy[kMaxCand], sw[kMaxCand], sh[kMaxCand], cnt[kMaxCand];
+    __shared__ int warp_tot[kThreads / 32];
+    __shared__ int s_any;
+
+    const int cls = blockIdx.x, b = blockIdx.y, ncls = gridDim.x;
+    const int cch = cls + (P.skip_bg ? 1 : 0);
+    const float* cv = coverage + ((size_t)b * c_cvg + cch) * gh * gw;
+    const float* bb = bboxes + ((size_t)b * c_bbox + 4 * cls) * gh * gw;
+    const int plane = gh * gw;
+    const int ncell = P.rows_used * gw;
+    int32_t* out = cls_det + ((size_t)b * ncls + cls) * FCNOD_MAX_DET * 6;
+
+    if (threadIdx.x == 0) s_any = 0;
+    __syncthreads();
+
+    // ---- 1. threshold + ordered compaction + decode (float64) + round-half-even to int
+    int n = 0;
+    for (int base = 0; base < ncell; base += kThreads) {
+        const int i = base + threadIdx.x;
+        bool f = false;
+        if (i < ncell) f = cv[i] >= P.prob_thresh;
+        int tot;
+        const int off = block_scan_flag(f, warp_tot, &tot);
+        if (f) {
+            const int y = i / gw, x = i - y * gw;
+            const double mx = (double)(x * P.cell_w), my = (double)(y * P.cell_h);
+            const double x1 = (double)bb[i] + mx, y1 = (double)bb[plane + i] + my;
+            const double x2 = (double)bb[2 * plane + i] + mx, y2 = (double)bb[3 * plane + i] + my;
+            if (x1 != 0.0 || y1 != 0.0 || x2 != 0.0 || y2 != 0.0) s_any = 1;   // `propose_boxes.any()` (:339)
+            const int k = n + off;
+            rx[k] = __double2int_rn(x1); ry[k] = __double2int_rn(y1);
+            rw[k] = __double2int_rn(x2); rh[k] = __double2int_rn(y2);
+        }
+        n += tot;
+    }
+    __syncthreads();
+    if (n == 0 || !s_any) {
+        if (threadIdx.x == 0) cls_cnt[b * ncls + cls] = 0;
+        return;
+    }
+
+    // ---- 2. cv::partition with SimilarRects(eps): connected components, label = smallest member index
+    for (int i = threadIdx.x; i < n; i += kThreads) { lab[i] = i; sx[i] = sy[i] = sw[i] = sh[i] = cnt[i] = 0; }
+    __syncthreads();
+    if (P.group_threshold > 0) {
+        volatile int* vlab = lab;
+        for (;;) {
+            int changed = 0;
+            for (int i = threadIdx.x; i < n; i += kThreads) {
+                const int xi = rx[i], yi = ry[i], wi = rw[i], hi = rh[i];
+                int m = vlab[i];
+                for (int j = 0; j < n; ++j) {
+                    const int wj = rw[j], hj = rh[j];
+                    const double delta = P.eps * (double)(min(wi, wj) + min(hi, hj)) * 0.5;
+                    const int xj = rx[j], yj = ry[j];
+                    if ((double)abs(xi - xj) <= delta && (double)abs(yi - yj) <= delta &&
+                        (double)abs(xi + wi - xj - wj) <= delta && (double)abs(yi + hi - yj - hj) <= delta) {
+                        const int lj = vlab[j];
+                        if (lj < m) m = lj;
+                    }
+                }
+                if (m < vlab[i]) { vlab[i] = m; changed = 1; }
+            }
+            __syncthreads();
+            for (int i = threadIdx.x; i < n; i += kThreads) {   // pointer jumping
+                int l = vlab[i];
+                while (vlab[l] < l) l = vlab[l];
+                if (l < vlab[i]) { vlab[i] = l; changed = 1; }
+            }
+            if (!__syncthreads_or(changed)) break;
+        }
+    }
+    // ---- 3. per-class integer sums
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+        const int r = lab[i];
+        atomicAdd(&sx[r], rx[i]); atomicAdd(&sy[r], ry[i]);
+        atomicAdd(&sw[r], rw[i]); atomicAdd(&sh[r], rh[i]);
+        atomicAdd(&cnt[r], 1);
+    }
+    __syncthreads();
+    // ---- 4. mean rect: saturate_cast<int>(sum * (1.f / n))  (fp32, round half even)
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+        if (lab[i] != i) continue;
+        if (P.group_threshold > 0) {
+            const float s = __fdiv_rn(1.f, (float)cnt[i]);
+            sx[i] = __float2int_rn(__fmul_rn((float)sx[i], s)); sy[i] = __float2int_rn(__fmul_rn((float)sy[i], s));
+            sw[i] = __float2int_rn(__fmul_rn((float)sw[i], s)); sh[i] = __float2int_rn(__fmul_rn((float)sh[i], s));
+        }
+    }
+    __syncthreads();
+    // ---- 5. threshold on member count + containment filter, then vote_boxes' height filter; ordered output
+    int nout = 0;
+    for (int base = 0; base < n; base += kThreads) {
+        const int i = base + threadIdx.x;
+        bool keep = false;
+        int n1 = 0;
+        if (i < n && lab[i] == i) {
+            n1 = cnt[i];
+            if (P.group_threshold <= 0) keep = true;
+            else if (n1 > P.group_threshold) {
+                keep = true;
+                const int x1 = sx[i], y1 = sy[i], w1 = sw[i], h1 = sh[i];
+                for (int j = 0; j < n; ++j) {
+                    if (j == i || lab[j] != j) continue;
+                    const int n2 = cnt[j];
+                    if (n2 <= P.group_threshold) continue;
+                    const int x2 = sx[j], y2 = sy[j], w2 = sw[j], h2 = sh[j];
+                    const int dx = __double2int_rn((double)w2 * P.eps), dy = __double2int_rn((double)h2 * P.eps);
+                    if (x1 >= x2 - dx && y1 >= y2 - dy && x1 + w1 <= x2 + w2 + dx && y1 + h1 <= y2 + h2 + dy &&
+                        (n2 > max(3, n1) || n1 < 3)) { keep = false; break; }
+                }
+            }
+            if (keep && (sh[i] - sy[i]) < P.min_height) keep = false;    // rect[3]-rect[1] >= 20 (:346)
+        }
+        int tot;
+        const int off = block_scan_flag(keep, warp_tot, &tot);
+        if (keep) {
+            const int k = nout + off;
+            if (k < FCNOD_MAX_DET) {
+                int32_t* o = out + k * 6;
+                o[0] = sx[i]; o[1] = sy[i]; o[2] = sw[i]; o[3] = sh[i];
+                o[4] = (int)log((double)n1);                               // int(math.log(weight)) (:347,:123)
+                o[5] = n1;
+            }
+        }
+        nout += tot;
+    }
+    if (threadIdx.x == 0) cls_cnt[b * ncls + cls] = min(nout, FCNOD_MAX_DET);
+}
+
+__global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32_t* __restrict__ cls_cnt, int B, int ncls,
+                                const int32_t* __restrict__ src_hw, int net_w, int net_h, int32_t* __restrict__ out_det,
+                                int32_t* __restrict__ out_label, int32_t* __restrict__ out_weight,
+                                int32_t* __restrict__ out_count) {
+    const int b = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= B) return;
+    double diffx = 1.0, diffy = 1.0;
+    if (src_hw) {
+        diffx = (double)src_hw[2 * b + 1] / (double)net_w;
+        diffy = (double)src_hw[2 * b] / (double)net_h;
+    }
+    int total = 0;
+    for (int c = 0; c < ncls; ++c) {
+        const int k = cls_cnt[b * ncls + c];
+        const int32_t* src = cls_det + ((size_t)b * ncls + c) * FCNOD_MAX_DET * 6;
+        for (int i = lane; i < k; i += 32) {
+            const int d = total + i;
+            if (d >= FCNOD_MAX_DET) break;
+            int32_t* o = out_det + ((size_t)b * FCNOD_MAX_DET + d) * 5;
+            o[0] = (int)((double)src[i * 6 + 0] * diffx);
+            o[1] = (int)((double)src[i * 6 + 1] * diffy);
+            o[2] = (int)((double)src[i * 6 + 2] * diffx);
+            o[3] = (int)((double)src[i * 6 + 3] * diffy);
+            o[4] = src[i * 6 + 4];
+            out_label[b * FCNOD_MAX_DET + d] = c;
+            out_weight[b * FCNOD_MAX_DET + d] = src[i * 6 + 5];
+        }
+        total += k;
+    }
+    if (lane == 0) out_count[b] = min(total, FCNOD_MAX_DET);
+}
+
+}  // namespace
+
+size_t postnet_scratch_bytes(int B, int c_cvg) {
+    return (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1) * sizeof(int32_t);
+}
+int postnet_num_launches() { return 2; }
+
+void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                    const int32_t* src_hw, const fcnod_postnet_params& p, void* scratch, int32_t* out_det,
+                    int32_t* out_label, int32_t* out_weight, int32_t* out_count, cudaStream_t stream) {
+    FCNOD_CHECK(B > 0 && c_cvg > 0 && gh > 0 && gw > 0, "postnet: bad dimensions");
+    FCNOD_CHECK(p.stride > 0 && p.net_w >= p.stride && p.net_h >= p.stride, "postnet: bad stride / net size");
+    const int ncls = c_cvg - (p.skip_background ? 1 : 0);
+    FCNOD_CHECK(ncls > 0, "postnet: no foreground coverage channel");
+    FCNOD_CHECK(c_bbox >= 4 * ncls, "postnet: bboxes has fewer than 4 channels per foreground class");
+    FCNOD_CHECK(gh * gw <= kMaxCand, "postnet: grid larger than 1024 cells is not supported");
+    PostParams P;
+    P.prob_thresh = p.prob_thresh;
+    P.group_threshold = p.min_boxes;
+    P.eps = p.eps;
+    const int grid_sz_x = p.net_w / p.stride, grid_sz_y = p.net_h / p.stride;   // int(im_sz / stride)   (:362-363)
+    P.cell_w = p.net_w / grid_sz_x;                                              // Py2 int division     (:368-369)
+    P.cell_h = p.net_h / grid_sz_y;
+    P.rows_used = std::min(gh, std::min(grid_sz_y, grid_sz_x));                  // net_cvg[0:gy][0:gx]  (:371)
+    P.skip_bg = p.skip_background ? 1 : 0;
+    P.min_height = p.min_height;
+    P.net_w = p.net_w; P.net_h = p.net_h;
+    int32_t* cls_det = static_cast<int32_t*>(scratch);
+    int32_t* cls_cnt = cls_det + (size_t)B * ncls * FCNOD_MAX_DET * 6;
+    decode_group_kernel<<<dim3(ncls, B), kThreads, 0, stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, cls_det, cls_cnt);
+    FCNOD_CUDA(cudaGetLastError());
+    assemble_kernel<<<ceil_div(B, 4), 128, 0, stream>>>(cls_det, cls_cnt, B, ncls, src_hw, p.net_w, p.net_h, out_det,
+                                                        out_label, out_weight, out_count);
+    FCNOD_CUDA(cudaGetLastError());
+}
+
+}  // namespace fcnod
+
+using namespace fcnod;
+
+extern "C" {
+
+void fcnod_postnet_default_params(fcnod_postnet_params* p) {
+    if (!p) return;
+    p->prob_thresh = 0.5f; p->min_boxes = 3; p->eps = 0.2;
+    p->net_w = 448; p->net_h = 448; p->stride = 16; p->skip_background = 1; p->min_height = 20;
+}
+
+size_t fcnod_postnet_scratch_bytes(int B, int c_cvg) { return postnet_scratch_bytes(B, c_cvg); }
+
+int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                         const int32_t* src_hw, const fcnod_postnet_params* p, void* scratch, int32_t* out_det,
+                         int32_t* out_label, int32_t* out_weight, int32_t* out_count, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(coverage && bboxes && p && scratch && out_det && out_label && out_weight && out_count, "null argument");
+    postnet_launch(coverage, bboxes, B, c_cvg, c_bbox, gh, gw, src_hw, *p, scratch, out_det, out_label, out_weight,
+                   out_count, (cudaStream_t)stream);
+    FCNOD_API_END
+}
+
+int fcnod_postnet(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                  const int32_t* src_hw, const fcnod_postnet_params* p, int32_t* out_det, int32_t* out_label,
+                  int32_t* out_weight, int32_t* out_count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(coverage && bboxes && p && out_det && out_label && out_weight && out_count, "null argument");
+    FCNOD_CHECK(B > 0 && c_cvg > 0 && c_bbox > 0 && gh > 0 && gw > 0, "postnet: bad dimensions");
+    const size_t ncv = (size_t)B * c_cvg * gh * gw, nbb = (size_t)B * c_bbox * gh * gw;
+    float *d_cv = 0, *d_bb = 0;
+    int32_t *d_hw = 0, *d_det = 0, *d_lab = 0, *d_w = 0, *d_cnt = 0;
+    void* d_scr = 0;
+    struct Guard {
+        void** p[8]; int n;
+        ~Guard() { for (int i = 0; i < n; ++i) if (*p[i]) cudaFree(*p[i]); }
+    } g = {{(void**)&d_cv, (void**)&d_bb, (void**)&d_hw, (void**)&d_det, (void**)&d_lab, (void**)&d_w, (void**)&d_cnt, &d_scr}, 8};
+    FCNOD_CUDA(cudaMalloc(&d_cv, ncv * 4));
+    FCNOD_CUDA(cudaMalloc(&d_bb, nbb * 4));
+    FCNOD_CUDA(cudaMalloc(&d_det, (size_t)B * FCNOD_MAX_DET * 5 * 4));
+    FCNOD_CUDA(cudaMalloc(&d_lab, (size_t)B * FCNOD_MAX_DET * 4));
+    FCNOD_CUDA(cudaMalloc(&d_w, (size_t)B * FCNOD_MAX_DET * 4));
+    FCNOD_CUDA(cudaMalloc(&d_cnt, (size_t)B * 4));
+    FCNOD_CUDA(cudaMalloc(&d_scr, postnet_scratch_bytes(B, c_cvg)));
+    FCNOD_CUDA(cudaMemcpy(d_cv, coverage, ncv * 4, cudaMemcpyHostToDevice));
+    FCNOD_CUDA(cudaMemcpy(d_bb, bboxes, nbb * 4, cudaMemcpyHostToDevice));
+    if (src_hw) {
+        FCNOD_CUDA(cudaMalloc(&d_hw, (size_t)B * 2 * 4));
+        FCNOD_CUDA(cudaMemcpy(d_hw, src_hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice));
+    }
+    FCNOD_CUDA(cudaMemset(d_det, 0, (size_t)B * FCNOD_MAX_DET * 5 * 4));
+    FCNOD_CUDA(cudaMemset(d_lab, 0, (size_t)B * FCNOD_MAX_DET * 4));
+    FCNOD_CUDA(cudaMemset(d_w, 0, (size_t)B * FCNOD_MAX_DET * 4));
+    postnet_launch(d_cv, d_bb, B, c_cvg, c_bbox, gh, gw, d_hw, *p, d_scr, d_det, d_lab, d_w, d_cnt, 0);
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    FCNOD_CUDA(cudaMemcpy(out_det, d_det, (size_t)B * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost));
+    FCNOD_CUDA(cudaMemcpy(out_label, d_lab, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost));
+    FCNOD_CUDA(cudaMemcpy(out_weight, d_w, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost));
+    FCNOD_CUDA(cudaMemcpy(out_count, d_cnt, (size_t)B * 4, cudaMemcpyDeviceToHost));
+    FCNOD_API_END
+}
+
+}  // extern "C"

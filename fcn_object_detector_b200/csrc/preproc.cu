@@ -1,0 +1,164 @@
+// Detector prelude on the device: BGR uint8 HxWx3 frame -> blob `data` (3 x net_h x net_w fp32).
+//
+// Restates /root/reference/scripts/fcn_object_detector.py:
+//   demean_rgb_image   :407-413  float64; per-channel mean subtraction (BGR order), global min-max to [0,1]
+//   cv.resize          :80       default INTER_LINEAR (half-pixel centres, edge clamp); identity at 448x448
+//   transpose + write  :81-82    HWC -> CHW, cast to the blob's float32
+// Pass 1: per-frame, per-channel uint8 min / max (integer atomics; min/max commute with the
+//   monotone `- mean_c`, so the float64 global min / max are recovered exactly from them).
+// Pass 2: normalise in float64 and resample; one thread per 4 output pixels, float4 stores.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace fcnod {
+namespace {
+
+__device__ __forceinline__ double mean64(int c) {
+    return c == 0 ? 104.0069879317889 : (c == 1 ? 116.66876761696767 : 122.6789143406786);
+}
+
+__global__ void pre_init_kernel(int* mm, int B) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B * 6) mm[i] = (i % 6) < 3 ? 255 : 0;     // [b][0..2] = min per channel, [b][3..5] = max
+}
+
+__global__ void __launch_bounds__(256) pre_minmax_kernel(const uint8_t* __restrict__ img, long npix, int* __restrict__ mm) {
+    const int b = blockIdx.y;
+    const uint8_t* p = img + (size_t)b * npix * 3;
+    int mn[3] = {255, 255, 255}, mx[3] = {0, 0, 0};
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < npix; i += (long)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { int v = p[i * 3 + c]; mn[c] = min(mn[c], v); mx[c] = max(mx[c], v); }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[c] = min(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+            mx[c] = max(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { atomicMin(&mm[b * 6 + c], mn[c]); atomicMax(&mm[b * 6 + 3 + c], mx[c]); }
+    }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __restrict__ img, int B, int src_h, int src_w,
+                                                           int net_h, int net_w, const int* __restrict__ mm,
+                                                           float* __restrict__ data) {
+    const int wv = net_w / VEC;
+    const long total = (long)B * net_h * wv;
+    const bool same = (src_h == net_h && src_w == net_w);
+    const double sy = (double)src_h / (double)net_h, sx = (double)src_w / (double)net_w;
+    for (long t = blockIdx.x * (long)blockDim.x + threadIdx.x; t < total; t += (long)gridDim.x * blockDim.x) {
+        const int xv = (int)(t % wv);
+        const long r = t / wv;
+        const int oy = (int)(r % net_h), b = (int)(r / net_h);
+        const int* m = mm + b * 6;
+        double mn = fmin(fmin((double)m[0] - mean64(0), (double)m[1] - mean64(1)), (double)m[2] - mean64(2));
+        double mx = fmax(fmax((double)m[3] - mean64(0), (double)m[4] - mean64(1)), (double)m[5] - mean64(2));
+        const double range = mx - mn;
+        const uint8_t* p = img + (size_t)b * src_h * src_w * 3;
+        double fyd = ((double)oy + 0.5) * sy - 0.5;
+        int y0 = (int)floor(fyd);
+        double ay = fyd - (double)y0;
+        if (y0 < 0) { y0 = 0; ay = 0.0; }
+        if (y0 >= src_h - 1) { y0 = src_h - 1; ay = 0.0; }
+        const int y1 = min(y0 + 1, src_h - 1);
+        float res[3][VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            const int ox = xv * VEC + v;
+            double fxd = ((double)ox + 0.5) * sx - 0.5;
+            int x0 = (int)floor(fxd);
+            double ax = fxd - (double)x0;
+            if (x0 < 0) { x0 = 0; ax = 0.0; }
+            if (x0 >= src_w - 1) { x0 = src_w - 1; ax = 0.0; }
+            const int x1 = min(x0 + 1, src_w - 1);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const double mc = mean64(c);
+                const double p00 = (((double)p[((size_t)y0 * src_w + x0) * 3 + c] - mc) - mn) / range;
+                if (same) { res[c][v] = (float)p00; continue; }
+                const double p01 = (((double)p[((size_t)y0 * src_w + x1) * 3 + c] - mc) - mn) / range;
+                const double p10 = (((double)p[((size_t)y1 * src_w + x0) * 3 + c] - mc) - mn) / range;
+                const double p11 = (((double)p[((size_t)y1 * src_w + x1) * 3 + c] - mc) - mn) / range;
+                const double tp = p00 * (1.0 - ax) + p01 * ax, bt = p10 * (1.0 - ax) + p11 * ax;
+                res[c][v] = (float)(tp * (1.0 - ay) + bt * ay);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float* o = data + (((size_t)b * 3 + c) * net_h + oy) * net_w + xv * VEC;
+            if (VEC == 4) *reinterpret_cast<float4*>(o) = make_float4(res[c][0], res[c][1], res[c][2], res[c][3]);
+            else
+#pragma unroll
+                for (int v = 0; v < VEC; ++v) o[v] = res[c][v];
+        }
+    }
+}
+
+int grid_1d(long items, int threads) {
+    long b = (items + threads - 1) / threads;
+    long cap = 148L * 16;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+}  // namespace
+
+int preprocess_num_launches() { return 3; }
+
+void preprocess_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, float* data_dev,
+                       void* scratch, cudaStream_t s) {
+    FCNOD_CHECK(B > 0 && src_h > 0 && src_w > 0 && net_h > 0 && net_w > 0, "preprocess: bad dimensions");
+    int* mm = static_cast<int*>(scratch);
+    pre_init_kernel<<<ceil_div(B * 6, 128), 128, 0, s>>>(mm, B);
+    FCNOD_CUDA(cudaGetLastError());
+    pre_minmax_kernel<<<dim3(32, B), 256, 0, s>>>(images_dev, (long)src_h * src_w, mm);
+    FCNOD_CUDA(cudaGetLastError());
+    if (net_w % 4 == 0)
+        pre_resample_kernel<4><<<grid_1d((long)B * net_h * (net_w / 4), 256), 256, 0, s>>>(images_dev, B, src_h, src_w, net_h, net_w, mm, data_dev);
+    else
+        pre_resample_kernel<1><<<grid_1d((long)B * net_h * net_w, 256), 256, 0, s>>>(images_dev, B, src_h, src_w, net_h, net_w, mm, data_dev);
+    FCNOD_CUDA(cudaGetLastError());
+}
+
+}  // namespace fcnod
+
+using namespace fcnod;
+
+extern "C" {
+
+int fcnod_preprocess_device(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, float* data_dev,
+                            void* scratch, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(images_dev && data_dev && scratch, "null argument");
+    preprocess_launch(images_dev, B, src_h, src_w, net_h, net_w, data_dev, scratch, (cudaStream_t)stream);
+    FCNOD_API_END
+}
+
+int fcnod_preprocess(const uint8_t* images, int B, int src_h, int src_w, int net_h, int net_w, float* data_out) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(images && data_out, "null argument");
+    FCNOD_CHECK(B > 0 && src_h > 0 && src_w > 0 && net_h > 0 && net_w > 0, "preprocess: bad dimensions");
+    uint8_t* d_img = 0;
+    float* d_out = 0;
+    void* d_scr = 0;
+    struct Guard { void** p[3]; ~Guard() { for (int i = 0; i < 3; ++i) if (*p[i]) cudaFree(*p[i]); } }
+        g = {{(void**)&d_img, (void**)&d_out, &d_scr}};
+    const size_t nin = (size_t)B * src_h * src_w * 3, nout = (size_t)B * 3 * net_h * net_w;
+    FCNOD_CUDA(cudaMalloc(&d_img, nin));
+    FCNOD_CUDA(cudaMalloc(&d_out, nout * 4));
+    FCNOD_CUDA(cudaMalloc(&d_scr, (size_t)B * 6 * 4));
+    FCNOD_CUDA(cudaMemcpy(d_img, images, nin, cudaMemcpyHostToDevice));
+    preprocess_launch(d_img, B, src_h, src_w, net_h, net_w, d_out, d_scr, 0);
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    FCNOD_CUDA(cudaMemcpy(data_out, d_out, nout * 4, cudaMemcpyDeviceToHost));
+    FCNOD_API_END
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+"""Predict-on-image entry point of the detector node, on the B200 path.
+
+Mirrors `FCNObjectDetector` of /root/reference/scripts/fcn_object_detector.py:25-461
+without ROS: the rosparams of :33-38 are constructor arguments with the same
+names and defaults, `run_detector(cv_img)` is the body of :54-132 (everything
+after :132 is drawing / HighGUI and is dropped), `callback` forwards to it as
+in :307-308.  All arithmetic runs in libfcnod_b200 (prelude, network, decode,
+groupRectangles clustering, rescale); this class only marshals buffers.
+"""
+import ctypes as C
+import logging
+import os
+
+import numpy as np
+
+from . import _lib
+from . import caffe_shim as caffe
+
+log = logging.getLogger('fcn_object_detector')
+
+
+class FCNObjectDetector(object):
+    def __init__(self, pretrained_weights=None, deployment_prototxt=None, detection_threshold=0.5, min_boxes=3,
+                 nms_eps=0.2, device_id=0, manifest=None, stride=16, precision='bf16'):
+        self.__net = None
+        self.__im_width = None
+        self.__im_height = None
+        self.__prob_thresh = detection_threshold
+        self.__min_bbox_thresh = min_boxes
+        self.__group_eps_thresh = nms_eps
+        self.__weights = pretrained_weights
+        self.__model_proto = deployment_prototxt
+        self.__device_id = device_id
+        self.__stride = stride            # upstream literal is 16/2 (:360); the deploy net is stride 16 (A2)
+        self.__precision = precision
+        if self.is_file_valid():
+            self.load_caffe_model()
+            log.info('DETECTOR SETUP SUCCESSFUL')
+        self.__label_manifest = manifest
+        self.load_label_manifest()
+
+    # ------------------------------------------------------------------ :315-328
+    def load_caffe_model(self):
+        log.info('LOADING CAFFE MODEL..')
+        caffe.set_device(self.__device_id)
+        caffe.set_mode_gpu()
+        self.__net = caffe.Net(self.__model_proto, self.__weights, caffe.TEST, precision=self.__precision)
+        shape = self.__net.blobs['data'].data.shape
+        self.__im_height = shape[2]
+        self.__im_width = shape[3]
+        self.__net.blobs['data'].reshape(1, 3, self.__im_height, self.__im_width)
+
+    @property
+    def net(self):
+        return self.__net
+
+    def _params(self):
+        return _lib.default_postnet_params(prob_thresh=float(self.__prob_thresh), min_boxes=int(self.__min_bbox_thresh),
+                                           eps=float(self.__group_eps_thresh), net_w=int(self.__im_width),
+                                           net_h=int(self.__im_height), stride=int(self.__stride))
+
+    # ------------------------------------------------------------------ :54-132
+    def run_detector(self, cv_img):
+        """cv_img: HxWx3 uint8 BGR (what CvBridge.imgmsg_to_cv2(msg, 'bgr8') returns, :57).
+        Returns (object_boxes int (K,5) [x1,y1,x2,y2,int(conf)] in source pixels, object_labels int (K,))
+        or None when nothing is detected (the reference logs and returns, :128-130)."""
+        if cv_img is None:
+            return None
+        boxes, labels = self.predict_batch(np.asarray(cv_img)[None])[0]
+        if not len(boxes):
+            log.warning('not detection')
+            return None
+        return boxes, labels
+
+    def predict(self, cv_img):
+        """Like run_detector but always returns (boxes, labels) (possibly empty)."""
+        return self.predict_batch(np.asarray(cv_img)[None])[0]
+
+    def predict_batch(self, images):
+        """images: (B,H,W,3) uint8 BGR.  One fcnod_detect call: H2D, prelude, net, post-net, D2H."""
+        images = np.ascontiguousarray(images, dtype=np.uint8)
+        if images.ndim != 4 or images.shape[3] != 3:
+            raise ValueError('images must be (B,H,W,3) uint8 BGR')
+        B, H, W, _ = images.shape
+        M = _lib.FCNOD_MAX_DET
+        det = np.zeros((B, M, 5), np.int32)
+        lab = np.zeros((B, M), np.int32)
+        wgt = np.zeros((B, M), np.int32)
+        cnt = np.zeros((B,), np.int32)
+        p = self._params()
+        _lib.check(_lib.lib().fcnod_detect(self.__net.handle, _lib.ptr(images), B, H, W, C.byref(p), _lib.ptr(det),
+                                           _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
+        self.__net._sync_after_device_run(B)
+        return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64)) for b in range(B)]
+
+    def predict_data(self, data):
+        """data: (B,3,H,W) float32 blob contents (post-prelude).  Returns per-frame (boxes, labels, weights)."""
+        data = np.ascontiguousarray(data, dtype=np.float32)
+        B = data.shape[0]
+        M = _lib.FCNOD_MAX_DET
+        det = np.zeros((B, M, 5), np.int32)
+        lab = np.zeros((B, M), np.int32)
+        wgt = np.zeros((B, M), np.int32)
+        cnt = np.zeros((B,), np.int32)
+        p = self._params()
+        _lib.check(_lib.lib().fcnod_detect_from_data(self.__net.handle, _lib.ptr(data), B, C.byref(p), _lib.ptr(det),
+                                                     _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
+        self.__net._sync_after_device_run(B)
+        return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64), wgt[b, :cnt[b]].astype(np.int64))
+                for b in range(B)]
+
+    def callback(self, cv_img):
+        return self.run_detector(cv_img)
+
+    # ------------------------------------------------------------------ :428-461
+    def is_file_valid(self):
+        if self.__model_proto is None or self.__weights is None:
+            log.critical('PROVIDE PRETRAINED MODEL! KILLING NODE...')
+            return False
+        if not os.path.isfile(str(self.__model_proto)) or not os.path.isfile(str(self.__weights)):
+            log.critical('NOT SUCH FILES')
+            return False
+        return True
+
+    def load_label_manifest(self):
+        self.labels = []
+        if self.__label_manifest is None or not os.path.isfile(self.__label_manifest):
+            log.warning('Object Label Names not Provided!')
+            if self.__net is not None:
+                out_size = self.__net.blobs['score'].data.shape[1]
+                self.labels = ['object_' + str(i - 1) for i in range(out_size)]
+            return
+        for line in open(self.__label_manifest):
+            idx, _, oname = line.rstrip('\n').split(' ')
+            self.labels.append(str(oname))
+
+
+def postnet(coverage, bboxes, src_hw=None, **params):
+    """Post-net stage alone on host arrays: coverage (B,Cc,G,G), bboxes (B,Cb,G,G) float32.
+    Returns per-frame (boxes (K,5) int, labels (K,), weights (K,))."""
+    coverage = np.ascontiguousarray(coverage, dtype=np.float32)
+    bboxes = np.ascontiguousarray(bboxes, dtype=np.float32)
+    B, Cc, gh, gw = coverage.shape
+    Cb = bboxes.shape[1]
+    M = _lib.FCNOD_MAX_DET
+    det = np.zeros((B, M, 5), np.int32); lab = np.zeros((B, M), np.int32)
+    wgt = np.zeros((B, M), np.int32); cnt = np.zeros((B,), np.int32)
+    hw = None if src_hw is None else np.ascontiguousarray(src_hw, dtype=np.int32).reshape(B, 2)
+    p = _lib.default_postnet_params(**params)
+    _lib.check(_lib.lib().fcnod_postnet(_lib.ptr(coverage), _lib.ptr(bboxes), B, Cc, Cb, gh, gw, _lib.ptr(hw), C.byref(p),
+                                        _lib.ptr(det), _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
+    return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64), wgt[b, :cnt[b]].astype(np.int64))
+            for b in range(B)]
+
+
+def preprocess(images, net_h=448, net_w=448):
+    """Prelude alone: (B,H,W,3) uint8 BGR -> (B,3,net_h,net_w) float32."""
+    images = np.ascontiguousarray(images, dtype=np.uint8)
+    B, H, W, _ = images.shape
+    out = np.zeros((B, 3, net_h, net_w), np.float32)
+    _lib.check(_lib.lib().fcnod_preprocess(_lib.ptr(images), B, H, W, net_h, net_w, _lib.ptr(out)))
+    return out

@@ -1,0 +1,162 @@
+/* fcnod_b200 -- C ABI of the B200 (sm_100a) detection hot path.
+ *
+ * Drop-in boundary for the two places where iKrishneel/fcn_object_detector
+ * hands work to an engine (citations relative to /root/reference):
+ *
+ *   B2  detector node -> pycaffe      scripts/fcn_object_detector.py
+ *         caffe.Net(proto, weights, caffe.TEST)              :317   fcnod_net_create
+ *         net.blobs['data'].reshape(B,3,H,W)                 :199,:328  fcnod_net_reshape
+ *         net.blobs['data'].data[...] = x ; net.forward()    :82,:87    fcnod_net_forward{,_device}
+ *         net.blobs[name].data                               :89-90     fcnod_net_blob_read
+ *         demean_rgb_image + cv.resize + transpose           :79-82,:407-413  fcnod_preprocess
+ *         gridbox_to_boxes + vote_boxes(cv.groupRectangles)
+ *           + resize_detection, per class                    :104-132,:337-405  fcnod_postnet{,_device}
+ *         whole run_detector body                            :54-132    fcnod_detect
+ *
+ *   B1  Caffe Python layer -> numpy   scripts/data_argumentation_layer/
+ *         ArgumentationEngine.bounding_box_parameterized_labels   argumentation_engine.py:69-109   fcnod_label_raster
+ *         random_argumentation + resize_image_and_labels + labels argumentation_engine.py:114-303  fcnod_aug_forward
+ *         (layer contract README.md:60-76; data_argumentation_layer.py:16-124)
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure
+ * (fcnod_last_error() gives a message for the calling thread).  "_device"
+ * entry points take DEVICE pointers and a cudaStream_t (passed as void*), do
+ * not synchronise, and are CUDA-graph capturable; the others take HOST
+ * buffers, copy in/out and synchronise.  Blob layout at this boundary is
+ * Caffe's: NCHW float32.  Handles are not thread-safe.  There is no CPU
+ * fallback: without a usable CUDA device every compute call fails.
+ */
+#ifndef FCNOD_B200_H
+#define FCNOD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FCNOD_PRECISION_FP32 0 /* SIMT fp32 everywhere (parity mode, 1e-5) */
+#define FCNOD_PRECISION_BF16 1 /* bf16 activations/weights, fp32 accumulate, tcgen05 convolutions */
+
+#define FCNOD_MAX_DET 64 /* detections kept per frame */
+
+typedef struct fcnod_net fcnod_net;
+
+int fcnod_version(void);
+const char* fcnod_last_error(void);
+int fcnod_device_count(int* count);
+
+/* ---- B2: network ------------------------------------------------------- */
+/* device >= 0: CUDA device ordinal.  device < 0: PLAN-ONLY handle (parses + plans on the host, no
+ * CUDA call is made; fcnod_net_describe / dims work, every compute entry point fails). */
+int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int device, int precision,
+                     fcnod_net** out);
+int fcnod_net_destroy(fcnod_net* net);
+int fcnod_net_reshape(fcnod_net* net, int batch);
+int fcnod_net_input_dims(const fcnod_net* net, int dims[4]);            /* N,C,H,W of blob `data` */
+int fcnod_net_blob_dims(const fcnod_net* net, const char* blob, int dims[4]);
+int fcnod_net_num_blobs(const fcnod_net* net);
+const char* fcnod_net_blob_name(const fcnod_net* net, int index);
+/* Plan introspection (host only, no CUDA work): one line per planned kernel launch. */
+int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen);
+/* Number of kernel launches one forward issues. */
+int fcnod_net_launches_per_forward(const fcnod_net* net);
+/* Host NCHW float32 in (N*3*H*W), runs the whole net, synchronises. */
+int fcnod_net_forward(fcnod_net* net, const float* data_host);
+/* Device NCHW float32 in; async on `stream`. */
+int fcnod_net_forward_device(fcnod_net* net, const float* data_dev, void* stream);
+/* Copy any blob out as NCHW float32 (count must equal N*C*H*W). */
+int fcnod_net_blob_read(fcnod_net* net, const char* blob, float* host_out, size_t count);
+/* Device address of an OUTPUT blob (NCHW float32), valid until reshape/destroy. */
+int fcnod_net_output_device(fcnod_net* net, const char* blob, const float** dev_ptr);
+/* Run only the n-th planned launch `reps` times (profiling aid). */
+int fcnod_net_run_step(fcnod_net* net, int step, int reps, void* stream);
+
+/* ---- B2: post-net (threshold -> decode -> groupRectangles -> filter -> rescale) */
+typedef struct fcnod_postnet_params {
+    float prob_thresh;      /* ~detection_threshold (0.5)   fcn_object_detector.py:33 */
+    int min_boxes;          /* ~min_boxes (3)                                     :34 */
+    double eps;             /* ~nms_eps (0.2)                                     :35 */
+    int net_w, net_h;       /* 448, 448                                           :324-326 */
+    int stride;             /* 16 for the deploy net; the literal upstream value is 8 (:360) */
+    int skip_background;    /* 1: drop coverage channel 0                         :89 */
+    int min_height;         /* 20                                                 :346 */
+} fcnod_postnet_params;
+
+void fcnod_postnet_default_params(fcnod_postnet_params* p);
+
+/* coverage [B][c_cvg][gh][gw], bboxes [B][c_bbox][gh][gw] float32 (device).
+ * src_hw [B][2] int32 = source image (height,width) per frame, or NULL for net size.
+ * out_det [B][FCNOD_MAX_DET][5] int32 = x1,y1,x2,y2,int(log(weight)) in source pixels,
+ * out_label [B][FCNOD_MAX_DET] int32, out_weight [B][FCNOD_MAX_DET] int32 (cluster size),
+ * out_count [B] int32.  scratch: fcnod_postnet_scratch_bytes(B, c_cvg) bytes of device memory. */
+size_t fcnod_postnet_scratch_bytes(int B, int c_cvg);
+int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                         const int32_t* src_hw, const fcnod_postnet_params* p, void* scratch,
+                         int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count,
+                         void* stream);
+/* Same with HOST buffers (allocates, copies, synchronises). */
+int fcnod_postnet(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                  const int32_t* src_hw, const fcnod_postnet_params* p,
+                  int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);
+
+/* ---- B2: prelude: BGR uint8 HxWx3 -> blob `data` (1x3xnet_hxnet_w float32) --------------- */
+/* images: B frames of identical size src_h x src_w x 3 (host, uint8, BGR). data_out host NCHW float32. */
+int fcnod_preprocess(const uint8_t* images, int B, int src_h, int src_w, int net_h, int net_w, float* data_out);
+int fcnod_preprocess_device(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w,
+                            float* data_dev, void* scratch /* 6*B int32 */, void* stream);
+
+/* ---- B2: whole run_detector body on B frames (host buffers) ---------------------------------
+ * images as for fcnod_preprocess; outputs as for fcnod_postnet (boxes in source pixels).
+ * Uses blobs `coverage` / `bboxes`. */
+int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int src_w, const fcnod_postnet_params* p,
+                 int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);
+/* Same, starting from blob `data` already in HOST memory (B*3*H*W float32). */
+int fcnod_detect_from_data(fcnod_net* net, const float* data_host, int B, const fcnod_postnet_params* p,
+                           int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);
+/* Same with `data` resident on the DEVICE; results stay on the device in the net's own
+ * buffers (pointers returned); async on `stream`; CUDA-graph capturable. */
+int fcnod_detect_device(fcnod_net* net, const float* data_dev, int B, const fcnod_postnet_params* p,
+                        const int32_t** det_dev, const int32_t** label_dev, const int32_t** weight_dev,
+                        const int32_t** count_dev, void* stream);
+/* Capture fcnod_detect_device for the current batch into a CUDA graph and replay it. */
+int fcnod_detect_graph_build(fcnod_net* net, const float* data_dev, int B, const fcnod_postnet_params* p, void* stream);
+int fcnod_detect_graph_launch(fcnod_net* net, void* stream);
+
+/* ---- B1: training-side layer ------------------------------------------------------------- */
+/* Label rasteriser.  rects [N][R][4] int32 (x,y,w,h at net resolution), labels [N][R] int32,
+ * nrect [N] int32 (<= R).  Outputs NCHW float32: fg [N][C][gh][gw]; bbox,size,obj,cvg [N][4C][gh][gw]. */
+int fcnod_label_raster_device(const int32_t* rects, const int32_t* labels, const int32_t* nrect, int N, int R,
+                              int net_h, int net_w, int stride, int num_classes, float* fg, float* bbox,
+                              float* size, float* obj, float* cvg, void* stream);
+int fcnod_label_raster(const int32_t* rects, const int32_t* labels, const int32_t* nrect, int N, int R,
+                       int net_h, int net_w, int stride, int num_classes, float* fg, float* bbox,
+                       float* size, float* obj, float* cvg);
+
+typedef struct fcnod_aug_draw {   /* host-made random draws for one image (argumentation_engine.py:146,165-166,200-202) */
+    int32_t flip;                 /* randint(-1,2): -1/0/1 flip, 2 none */
+    int32_t shift_x, shift_y;     /* randint(0,int(w/2)), randint(0,int(h/2)) */
+    int32_t sign_x, sign_y;       /* randint(0,1) x2 */
+    int32_t _pad;
+    double f1, f2;                /* uniform(1, scale_x), uniform(1, scale_y) */
+} fcnod_aug_draw;
+
+/* Whole layer forward (README.md:60-76 contract).  data_in [N][3][src_h][src_w] float32 (pixel values),
+ * label [N][5] float32 = x,y,w,h,class.  tops: data [N][3][net_h][net_w]; fg [N][C][gh][gw];
+ * bbox/size/obj/cvg [N][4C][gh][gw].  rects_out [N][4] int32 (augmented rect, may be NULL).
+ * scratch >= fcnod_aug_scratch_bytes(N). */
+size_t fcnod_aug_scratch_bytes(int N);
+int fcnod_aug_forward_device(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N,
+                             int src_h, int src_w, int net_h, int net_w, int stride, int num_classes,
+                             float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                             int32_t* rects_out, void* scratch, void* stream);
+int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N,
+                      int src_h, int src_w, int net_h, int net_w, int stride, int num_classes,
+                      float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                      int32_t* rects_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCNOD_B200_H */

@@ -1,0 +1,169 @@
+"""CPU: the C-ABI library loads and exports every declared symbol; host-side logic
+(prototxt/caffemodel readers, planning, Python shims) -- no compute calls."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from tests.util import ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, 'include', 'fcnod_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(fcnod_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    from fcn_object_detector_b200 import _lib
+    lib = C.CDLL(built_lib)
+    names = declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), n
+    assert sorted(_lib.SIGNATURES) == names          # the ctypes table binds exactly the header
+    assert _lib.lib().fcnod_version() == 100
+
+
+def test_plan_only_handle(built_lib, model_files):
+    from fcn_object_detector_b200 import _lib
+    L = _lib.lib()
+    proto, cm = model_files
+    for prec, n_tc in ((_lib.FCNOD_PRECISION_FP32, 0), (_lib.FCNOD_PRECISION_BF16, 58)):
+        h = C.c_void_p()
+        _lib.check(L.fcnod_net_create(proto.encode(), cm.encode(), -1, prec, C.byref(h)))
+        buf = C.create_string_buffer(1 << 16)
+        _lib.check(L.fcnod_net_describe(h, buf, len(buf)))
+        plan = buf.value.decode().splitlines()
+        assert len(plan) == L.fcnod_net_launches_per_forward(h) == 77
+        assert sum('conv_tc' in l for l in plan) == n_tc
+        assert sum('conv_' in l for l in plan) == 59 and sum(l.split()[1] == 'pool' for l in plan) == 12
+        assert not any('relu' == l.split()[1] for l in plan)          # all 57 ReLUs fused into conv epilogues
+        assert not any('concat-copy' in l for l in plan)              # all 9 Concats eliminated
+        d = (C.c_int * 4)()
+        _lib.check(L.fcnod_net_blob_dims(h, b'coverage', C.byref(d))); assert tuple(d) == (1, 4, 28, 28)
+        _lib.check(L.fcnod_net_blob_dims(h, b'bboxes', C.byref(d))); assert tuple(d) == (1, 16, 28, 28)
+        _lib.check(L.fcnod_net_blob_dims(h, b'inception_5b/output', C.byref(d))); assert tuple(d) == (1, 1024, 28, 28)
+        # compute on a plan-only handle must fail loudly -- there is no CPU fallback
+        x = np.zeros((1, 3, 448, 448), np.float32)
+        assert L.fcnod_net_forward(h, _lib.ptr(x)) != 0
+        assert b'no CPU fallback' in L.fcnod_last_error()
+        _lib.check(L.fcnod_net_destroy(h))
+
+
+def test_create_errors(built_lib, model_files, tmp_path):
+    from fcn_object_detector_b200 import _lib
+    L = _lib.lib()
+    proto, cm = model_files
+    h = C.c_void_p()
+    assert L.fcnod_net_create(b'/nonexistent.prototxt', cm.encode(), -1, 1, C.byref(h)) != 0
+    assert b'cannot open prototxt' in L.fcnod_last_error()
+    assert L.fcnod_net_create(proto.encode(), b'/nonexistent.caffemodel', -1, 1, C.byref(h)) != 0
+    bad = tmp_path / 'bad.prototxt'
+    bad.write_text('input: "data"\ninput_shape { dim: 1 dim: 3 dim: 8 dim: 8 }\nlayer { name: "x" type: "Softmax" bottom: "data" top: "y" }\n')
+    assert L.fcnod_net_create(str(bad).encode(), cm.encode(), -1, 1, C.byref(h)) != 0
+    assert b'unsupported type' in L.fcnod_last_error()
+    trunc = tmp_path / 'trunc.caffemodel'
+    trunc.write_bytes(open(cm, 'rb').read()[:1000])
+    assert L.fcnod_net_create(proto.encode(), str(trunc).encode(), -1, 1, C.byref(h)) != 0
+    # weights with a wrong shape
+    from fcn_object_detector_b200.caffemodel import write_caffemodel
+    wrong = write_caffemodel(str(tmp_path / 'wrong.caffemodel'), [('conv1/7x7_s2', 'Convolution', [np.zeros((64, 3, 5, 5), np.float32), np.zeros(64, np.float32)])])
+    assert L.fcnod_net_create(proto.encode(), wrong.encode(), -1, 1, C.byref(h)) != 0
+    assert b'wrong size' in L.fcnod_last_error()
+    assert L.fcnod_net_create(proto.encode(), cm.encode(), -1, 7, C.byref(h)) != 0
+
+
+def test_cpp_caffemodel_reader_accepts_legacy_shape(built_lib, model_files, tmp_path):
+    """V2 layer + legacy num/channels/height/width blob header (SURVEY.md hard part 7)."""
+    from fcn_object_detector_b200 import _lib
+    from fcn_object_detector_b200.caffemodel import write_caffemodel, xavier_weights
+    from fcn_object_detector_b200.netspec import conv_shapes
+    proto, _ = model_files
+    p = write_caffemodel(str(tmp_path / 'legacy.caffemodel'), xavier_weights(conv_shapes(), 0), legacy_shape=True)
+    h = C.c_void_p()
+    _lib.check(_lib.lib().fcnod_net_create(proto.encode(), p.encode(), -1, 1, C.byref(h)))
+    _lib.lib().fcnod_net_destroy(h)
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    from fcn_object_detector_b200 import _lib
+    monkeypatch.setattr(_lib, '_lib', None)
+    monkeypatch.setattr(_lib, 'LIB_PATH', '/nonexistent/libfcnod_b200.so')
+    with pytest.raises(_lib.FcnodError):
+        _lib.lib()
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, 'fcn_object_detector_b200')
+    for dp, dn, fn in os.walk(pkg):
+        for f in fn:
+            if f.endswith(('.py', '.cu', '.cuh', '.cpp', '.h')):
+                text = open(os.path.join(dp, f)).read()
+                assert not re.search(r'^\s*(from|import)\s+oracle\b', text, flags=re.M), f
+                assert 'oracle/' not in text or f == 'build.py', f
+
+
+def test_shim_net_blobs_and_aliases(built_lib, model_files):
+    import fcn_object_detector_b200.caffe_shim as caffe
+    proto, cm = model_files
+    net = caffe.Net(proto, cm, caffe.TEST, device=-1)
+    assert net.blobs['data'].data.shape == (1, 3, 448, 448)
+    assert net.blobs['pool_score'] is net.blobs['coverage']
+    assert net.blobs['upscore_pool5_bbox'] is net.blobs['bboxes'] and net.blobs['score'].data.shape[1] == 4
+    with pytest.raises(KeyError):
+        net.blobs['nope']
+    with pytest.raises(Exception):
+        net.blobs['data'].reshape(1, 3, 224, 224)
+    with pytest.raises(Exception):
+        caffe.set_mode_cpu()
+
+
+class _B(object):
+    def __init__(self, arr):
+        self.data = arr
+    num = property(lambda s: s.data.shape[0])
+
+    def reshape(self, *d):
+        self.data = np.zeros(d, np.float32)
+
+
+def test_layer_setup_reshape_contract():
+    from fcn_object_detector_b200.data_argumentation_layer import DataArgumentationLayer
+    L = DataArgumentationLayer()
+    L.param_str = '448, 448,16, 1'
+    bottom = [_B(np.zeros((32, 3, 480, 640), np.float32)), _B(np.zeros((32, 1, 1, 5), np.float32))]
+    top = [_B(np.zeros((1,), np.float32)) for _ in range(6)]
+    L.setup(bottom, top)
+    assert (L.image_size_x, L.image_size_y, L.stride, L.num_classes) == (448, 448, 16, 1)
+    L.reshape(bottom, top)
+    assert top[0].data.shape == (32, 3, 448, 448) and top[1].data.shape == (32, 1, 28, 28)
+    assert all(t.data.shape == (32, 4, 28, 28) for t in top[2:])
+    with pytest.raises(Exception, match='6 top blobs'):
+        L.setup(bottom, top[:5])
+    L.param_str = '448, x'
+    with pytest.raises(ValueError, match='Parameter string missing or data type is wrong!'):
+        L.setup(bottom, top)
+    L.backward(top, None, bottom)
+
+
+def test_host_draws_match_oracle_draws():
+    import random
+    from fcn_object_detector_b200.data_argumentation_layer import draw_augmentation
+    from oracle.layer_ref import draw_params
+    a, b = random.Random(7), random.Random(7)
+    rs = np.random.RandomState(0)
+    for i in range(200):
+        w, h = int(rs.randint(32, 257)), int(rs.randint(32, 257))
+        rect = [int(rs.randint(0, 640 - w)), int(rs.randint(0, 480 - h)), w, h]
+        d, o = draw_augmentation(a, 640, 480, rect), draw_params(b, 640, 480, rect)
+        assert (d.flip, d.f1, d.f2, d.shift_x, d.shift_y, d.sign_x, d.sign_y) == \
+            (o['flip'], o['f1'], o['f2'], o['shift_x'], o['shift_y'], o['sign_x'], o['sign_y'])
+
+
+def test_detector_without_files_is_inert():
+    from fcn_object_detector_b200.detector import FCNObjectDetector
+    d = FCNObjectDetector(pretrained_weights=None, deployment_prototxt=None)
+    assert d.net is None and d.labels == []

@@ -1,0 +1,100 @@
+"""GPU: network forward through the C ABI against the oracle.
+fp32 mode (SIMT): 1e-5 relative.  bf16 mode (tcgen05): 1e-2 relative on coverage / bboxes
+(metric max|a-b| / max|b| per blob)."""
+import os
+
+import numpy as np
+import pytest
+
+from tests.golden import make_golden as G
+from tests.util import GOLDEN, bf16_round, gpu_forward, oracle_forward, rel_err, write_mini_net
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-5
+TOL_BF16 = 1e-2
+
+
+def test_fp32_full_net_matches_oracle(model_files):
+    proto, cm = model_files
+    x = np.random.RandomState(2).uniform(0, 1, (2, 3, 448, 448)).astype(np.float32)
+    want = ['conv1/7x7_s2', 'pool1/3x3_s2', 'pool1/norm1', 'conv2/3x3', 'conv2/norm2', 'pool2/3x3_s2',
+            'inception_3a/output', 'inception_3b/output', 'pool3/3x3_s2', 'inception_4a/output',
+            'inception_4e/output', 'inception_5b/output', 'cvg/classifier', 'coverage', 'bboxes']
+    exp = oracle_forward(proto, cm, x, want=want)
+    got, plan = gpu_forward(proto, cm, x, 'fp32', want)
+    assert 'conv_tc' not in plan
+    for k in want:
+        assert got[k].shape == exp[k].shape, k
+        assert rel_err(got[k], exp[k]) < TOL_FP32, (k, rel_err(got[k], exp[k]))
+
+
+def test_fp32_golden_fixture(model_files):
+    proto, cm = model_files
+    g = np.load(os.path.join(GOLDEN, 'net_seed2.npz'))
+    got, _ = gpu_forward(proto, cm, G.net_inputs(), 'fp32', ['coverage', 'bboxes', 'pool1/norm1', 'inception_3a/output'])
+    assert rel_err(got['coverage'], g['coverage']) < TOL_FP32 and rel_err(got['bboxes'], g['bboxes']) < TOL_FP32
+    assert rel_err(got['pool1/norm1'][:, ::8, ::16, ::16], g['norm1_probe']) < TOL_FP32
+    assert rel_err(got['inception_3a/output'][:, ::16, ::8, ::8], g['i3a_probe']) < TOL_FP32
+
+
+TC_CASES = [
+    # tag, H, W, cin, branches [(cout, k)], batch
+    ('k1_c64', 28, 28, 64, [(64, 1)], 2),
+    ('k3_c64', 28, 28, 64, [(128, 3)], 2),
+    ('k5_c16', 28, 28, 16, [(32, 5)], 2),
+    ('k3_c96_sw64', 56, 56, 96, [(128, 3)], 1),
+    ('k5_c24', 28, 28, 24, [(64, 5)], 1),
+    ('k1_c480', 28, 28, 480, [(192, 1), (96, 1)], 1),
+    ('k3_c160_n320', 28, 28, 160, [(320, 3), (24, 1)], 1),
+    ('k3_w112', 112, 112, 64, [(192, 3)], 1),
+    ('mix_3a', 56, 56, 192, [(64, 1), (128, 3), (32, 5), (32, 1)], 2),
+    ('odd_hw', 20, 36, 32, [(48, 3), (16, 5)], 3),
+    ('cin48_k5', 28, 28, 48, [(128, 5)], 1),
+    ('big_w', 12, 160, 64, [(64, 3)], 1),
+]
+
+
+@pytest.mark.parametrize('case', TC_CASES, ids=[c[0] for c in TC_CASES])
+def test_conv_tc_mini_nets(case, tmp_path):
+    """Every tcgen05 tiling the deploy net uses (CK 16/32/64, BN 16..128, 1x1/3x3/5x5, concat slices),
+    against the oracle with the same bf16 operand rounding: only fp32 accumulation order differs."""
+    tag, H, W, cin, branches, batch = case
+    proto, cm = write_mini_net(str(tmp_path), tag, H, W, cin, branches, batch=batch, seed=len(tag))
+    x = np.random.RandomState(1).uniform(0, 1, (batch, 3, H, W)).astype(np.float32)
+    names = ['br%d' % i for i in range(len(branches))]
+    tc_layers = set(names + ['final'])
+    want = names + ['out']
+    exp = oracle_forward(proto, cm, x, bf16=True, want=want, tc_layers=tc_layers)
+    got, plan = gpu_forward(proto, cm, x, 'bf16', want)
+    assert plan.count('conv_tc') == len(branches) + 1, plan
+    for k in names:
+        # stored bf16: allow one bf16 ulp of the blob's magnitude
+        assert rel_err(got[k], exp[k]) < 1.0 / 128, (k, rel_err(got[k], exp[k]))
+    assert rel_err(got['out'], exp['out']) < 5e-3, rel_err(got['out'], exp['out'])
+    # and against the true fp32 oracle at the bf16 tolerance
+    ref = oracle_forward(proto, cm, x, want=['out'])
+    assert rel_err(got['out'], ref['out']) < TOL_BF16
+
+
+def test_bf16_full_net_within_tolerance(model_files):
+    proto, cm = model_files
+    x = np.random.RandomState(2).uniform(0, 1, (2, 3, 448, 448)).astype(np.float32)
+    want = ['conv2/3x3', 'inception_3a/output', 'inception_4e/output', 'inception_5b/output', 'coverage', 'bboxes']
+    exp = oracle_forward(proto, cm, x, want=want)
+    got, plan = gpu_forward(proto, cm, x, 'bf16', want)
+    assert plan.count('conv_tc') == 58
+    errs = {k: rel_err(got[k], exp[k]) for k in want}
+    print(errs)
+    assert errs['coverage'] < TOL_BF16 and errs['bboxes'] < TOL_BF16, errs
+    for k in want[:-2]:
+        assert errs[k] < 3e-2, errs
+
+
+def test_batch_independence_bf16(model_files):
+    """Size-independent property at a larger batch: frame i of a batch equals frame i run alone."""
+    proto, cm = model_files
+    x = np.random.RandomState(7).uniform(0, 1, (8, 3, 448, 448)).astype(np.float32)
+    full, _ = gpu_forward(proto, cm, x, 'bf16', ['coverage', 'bboxes'])
+    one, _ = gpu_forward(proto, cm, x[5:6], 'bf16', ['coverage', 'bboxes'])
+    assert np.array_equal(full['coverage'][5], one['coverage'][0]) and np.array_equal(full['bboxes'][5], one['bboxes'][0])
