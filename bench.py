@@ -169,7 +169,11 @@ def run_ours(args):
     g = torch.Generator(device='cpu').manual_seed(2 + rank)
     data_host = torch.rand((B, 3, 448, 448), generator=g, dtype=torch.float32).pin_memory()
     data = data_host.cuda()
-    stream = torch.cuda.current_stream().cuda_stream
+    # a non-default stream (the legacy default stream cannot be captured into a graph); made torch's current
+    # stream so that torch.cuda.Event timings and the kernels share it
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
     p = _lib.default_postnet_params()
     _lib.check(L.fcnod_detect_graph_build(h, data.data_ptr(), B, C.byref(p), stream))
     launches_per_step = L.fcnod_net_launches_per_forward(h) + 2
