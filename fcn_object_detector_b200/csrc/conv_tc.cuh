@@ -31,7 +31,8 @@ struct ConvTcParams {
     const float* bias;    // [>= n_tiles*BN] (zero padded)
     int H, W;             // spatial size (in == out)
     int Cout, ldo;
-    int kh, kw, pad;
+    int kh, kw;
+    int pad_h, pad_w;     // TMA box origin = (ow0 + s - pad_w, oh0 + r - pad_h)
     int n_cchunks;        // ceil(Cin / CK)
     int CK;               // 16 / 32 / 64 channels per K-block
     int BW, BH;           // pixel box
@@ -41,7 +42,18 @@ struct ConvTcParams {
     int relu;
     int out_fp32;
     uint32_t tmem_cols;   // power of two >= BN, >= 32
+    // Optional border-aware bias (first convolution with the input Power shift folded in, see net.cu):
+    // bias = bias_tab[(row_class(oh) * (bt_lo_w + bt_hi_w + 1) + col_class(ow)) * bt_ld + channel]
+    const float* bias_tab;
+    int bt_lo_h, bt_hi_h, bt_lo_w, bt_hi_w, bt_ld;
 };
+
+// class of an output coordinate: 0..lo-1 = the first `lo` positions, lo = interior, lo+1.. = the last `hi`
+__host__ __device__ __forceinline__ int border_class(int o, int n, int lo, int hi) {
+    if (o < lo) return o;
+    if (o >= n - hi) return lo + 1 + (o - (n - hi));
+    return lo;
+}
 
 namespace tc {
 
@@ -228,7 +240,7 @@ __global__ void __launch_bounds__(kConvTcThreads) conv_tc_kernel(const __grid_co
                         const uint32_t fb = full0 + 8u * stage;
                         mbar_expect_tx(fb, tx_bytes);
                         const uint32_t sa = smem_base + stage * stage_bytes;
-                        tma_load_4d(sa, &tmap_a, fb, cc * p.CK, ow0 + s - p.pad, oh0 + r - p.pad, n_img);
+                        tma_load_4d(sa, &tmap_a, fb, cc * p.CK, ow0 + s - p.pad_w, oh0 + r - p.pad_h, n_img);
                         tma_load_2d(sa + a_bytes, &tmap_b, fb, kb * p.CK, n0);
                         if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1u; }
                     }
@@ -262,6 +274,12 @@ __global__ void __launch_bounds__(kConvTcThreads) conv_tc_kernel(const __grid_co
         const size_t pix = ((size_t)n_img * p.H + (valid ? oh : 0)) * p.W + (valid ? ow : 0);
         void* out_pix = p.out_fp32 ? (void*)(static_cast<float*>(p.out) + pix * p.ldo)
                                    : (void*)(static_cast<bf16*>(p.out) + pix * p.ldo);
+        const float* bias = p.bias + n0;
+        if (p.bias_tab) {
+            const int cls = border_class(valid ? oh : 0, p.H, p.bt_lo_h, p.bt_hi_h) * (p.bt_lo_w + p.bt_hi_w + 1) +
+                            border_class(valid ? ow : 0, p.W, p.bt_lo_w, p.bt_hi_w);
+            bias = p.bias_tab + (size_t)cls * p.bt_ld + n0;
+        }
         mbar_wait(tfull, 0);
         fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -271,13 +289,13 @@ __global__ void __launch_bounds__(kConvTcThreads) conv_tc_kernel(const __grid_co
             uint32_t r[32];
             tmem_ld32(trow + (uint32_t)c, r);
             tmem_ld_wait();
-            if (valid && c < nvalid) store_chunk<32>(r, p.bias + n0, c, nvalid - c, (char*)out_pix + (size_t)n0 * (p.out_fp32 ? 4 : 2) , p.relu, p.out_fp32);
+            if (valid && c < nvalid) store_chunk<32>(r, bias, c, nvalid - c, (char*)out_pix + (size_t)n0 * (p.out_fp32 ? 4 : 2) , p.relu, p.out_fp32);
         }
         if (c < p.BN) {
             uint32_t r[16];
             tmem_ld16(trow + (uint32_t)c, r);
             tmem_ld_wait();
-            if (valid && c < nvalid) store_chunk<16>(r, p.bias + n0, c, nvalid - c, (char*)out_pix + (size_t)n0 * (p.out_fp32 ? 4 : 2), p.relu, p.out_fp32);
+            if (valid && c < nvalid) store_chunk<16>(r, bias, c, nvalid - c, (char*)out_pix + (size_t)n0 * (p.out_fp32 ? 4 : 2), p.relu, p.out_fp32);
         }
         fence_before();
     }

@@ -11,6 +11,12 @@
 //                                                  straight into channel slices
 //   * Dropout (TEST)                            -> alias
 //   * Power on the input + NCHW->NHWC           -> one transform launch
+// bf16 ("deploy") precision only -- the fp32 precision is the layer-by-layer parity mode and keeps
+// every blob materialised (set FCNOD_NO_FUSION=1 to get that plan in bf16 too):
+//   * Power + first stride-2 convolution        -> 2x2 space-to-depth transform + ONE stride-1 tcgen05
+//                                                  convolution; scale folded into the weights, shift into a
+//                                                  border-aware bias table (zero padding happens AFTER the shift)
+//   * Pooling -> LRN, LRN -> Pooling            -> one launch each (fused_pool.cuh)
 #include <cuda.h>
 
 #include <algorithm>
@@ -25,6 +31,7 @@
 #include "conv_simt.cuh"
 #include "conv_tc.cuh"
 #include "elementwise.cuh"
+#include "fused_pool.cuh"
 #include "kernels.h"
 #include "netdef.h"
 
@@ -60,7 +67,7 @@ struct Blob {
     std::string name;
     int C = 0, H = 0, W = 0;
     int dtype = DT_F32;
-    int buf = -1;     // buffer index
+    int buf = -1;     // buffer index; -1 = the NCHW input; -2 = fused away (never materialised)
     int c_off = 0;    // channel offset inside the buffer
     int ldc = 0;      // channels of the buffer
     bool is_output = false;
@@ -72,7 +79,7 @@ struct Buffer {
     void* ptr = 0;
 };
 
-enum StepKind { S_TRANSFORM, S_CONV_SIMT, S_CONV_TC, S_POOL, S_LRN, S_UNARY, S_COPY, S_EXPORT };
+enum StepKind { S_TRANSFORM, S_S2D, S_CONV_SIMT, S_CONV_TC, S_POOL, S_LRN, S_POOL_LRN, S_LRN_POOL, S_UNARY, S_COPY, S_EXPORT };
 
 struct ConvWeights {
     int Cout = 0, Cin = 0, k = 0;
@@ -84,14 +91,28 @@ struct ConvWeights {
     bf16* d_w_tc = 0;
     float* d_bias = 0;         // padded
     int CK = 0, n_cchunks = 0, BN = 0, n_tiles = 0;
+    // space-to-depth form of a stride-2 convolution on the (Power-transformed) network input
+    bool s2d = false;
+    int ka = 0;                // taps per axis after space-to-depth (padded to 1/2/4)
+    int q = 0;                 // even padding: ih = 2*(oh - q/2 + a) + dy
+    int stride = 1, pad = 0;
+    float in_scale = 1.f, in_shift = 0.f;   // the folded Power layer: y = in_shift + in_scale * x
+    float* d_bias_tab = 0;
+    int bt_lo_h = 0, bt_hi_h = 0, bt_lo_w = 0, bt_hi_w = 0;
 };
+
+const int kS2dCpad = 16;       // channels per space-to-depth pixel (4*Cin padded)
 
 struct Step {
     StepKind kind;
     std::string desc;
     int in = -1, out = -1;     // blob indices
     int layer = -1;
+    int layer2 = -1;           // second layer of a fused pair (Pool->LRN, LRN->Pool)
     int conv = -1;             // index into convs
+    int s2d_buf = -1;          // S_S2D / s2d convolution: buffer index of the space-to-depth image
+    int s2d_wp = 0, s2d_padl = 0;
+    bool s2d_overlap = false;  // one K-block per kernel row (overlapping-window tensor map) vs one per tap
     bool relu = false;
     int unary_op = 0;
     // TC state (rebuilt on reshape)
@@ -178,6 +199,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
     std::map<std::string, Shape> shp;
     std::map<std::string, int> producer;        // blob -> first layer writing it (not in-place)
     std::map<std::string, std::vector<int> > consumers;
+    std::map<std::string, int> inplace_ops;     // blob -> number of in-place layers rewriting it
     shp[def.input_name] = Shape{def.input_dims[1], def.input_dims[2], def.input_dims[3]};
     for (size_t i = 0; i < def.layers.size(); ++i) {
         const LayerDef& L = def.layers[i];
@@ -211,9 +233,49 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
         if (shp.count(L.top[0])) {
             Shape e = shp[L.top[0]];
             FCNOD_CHECK(e.C == o.C && e.H == o.H && e.W == o.W, "in-place layer '" + L.name + "' changes shape");
+            inplace_ops[L.top[0]]++;
         } else {
             shp[L.top[0]] = o;
             producer[L.top[0]] = (int)i;
+        }
+    }
+
+    // ---- network outputs = blobs nobody consumes
+    std::set<std::string> outputs;
+    for (std::map<std::string, Shape>::iterator it = shp.begin(); it != shp.end(); ++it)
+        if (!consumers.count(it->first) && it->first != def.input_name) outputs.insert(it->first);
+
+    // ---- pass 1b: fusions of the bf16 plan (see the header comment)
+    const bool fuse = bf && !getenv("FCNOD_NO_FUSION");
+    std::set<std::string> virt;            // blobs that are never materialised
+    std::map<int, int> s2d_conv;           // conv layer -> Power layer folded into it
+    std::map<int, int> s2d_power;          // Power layer -> its conv
+    std::map<int, int> fuse_first;         // first layer of a fused pair -> second
+    std::map<int, int> fuse_second;        // second -> first
+    if (fuse) {
+        for (size_t i = 0; i < def.layers.size(); ++i) {
+            const LayerDef& L = def.layers[i];
+            const std::string& top = L.top[0];
+            if (L.bottom[0] == top || inplace_ops.count(top) || outputs.count(top)) continue;
+            if (!consumers.count(top) || consumers[top].size() != 1) continue;
+            const int ci = consumers[top][0];
+            const LayerDef& Cn = def.layers[ci];
+            if (Cn.bottom.size() != 1 || Cn.top[0] == top) continue;
+            const Shape si = shp[L.bottom[0]], so = shp[Cn.top[0]];
+            if (L.type == L_POWER && L.bottom[0] == def.input_name && L.power == 1.f && Cn.type == L_CONV && Cn.stride == 2 &&
+                4 * si.C <= kS2dCpad && si.H % 2 == 0 && si.W % 2 == 0 && so.H == si.H / 2 && so.W == si.W / 2 &&
+                so.W >= 8) {
+                const int q = Cn.pad + (Cn.pad & 1);
+                const int ka = (q - Cn.pad + Cn.kernel + 1) / 2;
+                if (ka <= 4) { s2d_conv[ci] = (int)i; s2d_power[(int)i] = ci; virt.insert(top); }
+            } else if (L.type == L_POOL && Cn.type == L_LRN && L.pool_max && L.kernel == 3 && L.stride == 2 &&
+                       Cn.local_size == 5 && si.C % 8 == 0 && si.C / 8 <= 256 && !fuse_second.count((int)i)) {
+                fuse_first[(int)i] = ci; fuse_second[ci] = (int)i; virt.insert(top);
+            } else if (L.type == L_LRN && Cn.type == L_POOL && Cn.pool_max && Cn.kernel == 3 && Cn.stride == 2 &&
+                       L.local_size == 5 && si.C % 8 == 0 && (size_t)9 * 17 * si.C * 2 <= 200 * 1024 &&
+                       !fuse_second.count((int)i)) {
+                fuse_first[(int)i] = ci; fuse_second[ci] = (int)i; virt.insert(top);
+            }
         }
     }
 
@@ -240,11 +302,6 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
     }
     // Dropout: the top aliases the bottom (processed when creating blobs, in order)
 
-    // ---- network outputs = blobs nobody consumes
-    std::set<std::string> outputs;
-    for (std::map<std::string, Shape>::iterator it = shp.begin(); it != shp.end(); ++it)
-        if (!consumers.count(it->first) && it->first != def.input_name) outputs.insert(it->first);
-
     // ---- dtype per blob
     std::map<std::string, int> dt;
     for (std::map<std::string, Shape>::iterator it = shp.begin(); it != shp.end(); ++it) {
@@ -269,11 +326,13 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
     net->blobs.clear(); net->blob_index.clear(); net->buffers.clear();
     struct Maker {
         fcnod_net* net; std::map<std::string, Shape>& shp; std::map<std::string, int>& dt;
-        std::map<std::string, Alias>& alias; std::set<std::string>& outputs;
+        std::map<std::string, Alias>& alias; std::set<std::string>& outputs; std::set<std::string>& virt;
         int make(const std::string& nm) {
             if (net->blob_index.count(nm)) return net->blob_index[nm];
             Blob b; b.name = nm; Shape s = shp[nm]; b.C = s.C; b.H = s.H; b.W = s.W; b.dtype = dt[nm];
-            if (alias.count(nm)) {
+            if (virt.count(nm)) {
+                b.buf = -2; b.c_off = 0; b.ldc = s.C;
+            } else if (alias.count(nm)) {
                 int r = make(alias[nm].root);
                 const Blob& rb = net->blobs[r];
                 FCNOD_CHECK(rb.dtype == b.dtype, "concat slice dtype mismatch for '" + nm + "'");
@@ -288,7 +347,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             net->blob_index[nm] = (int)net->blobs.size() - 1;
             return net->blob_index[nm];
         }
-    } mk = {net, shp, dt, alias, outputs};
+    } mk = {net, shp, dt, alias, outputs, virt};
 
     // the input blob has no NHWC buffer of its own (it arrives NCHW); give it a descriptor only
     {
@@ -315,6 +374,22 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
         switch (L.type) {
             case L_POWER: {
                 FCNOD_CHECK(L.bottom[0] == def.input_name, "Power is only supported directly on the network input ('" + L.name + "')");
+                if (s2d_power.count((int)i)) {
+                    // folded into the following stride-2 convolution: emit the space-to-depth transform only
+                    const LayerDef& Cn = def.layers[s2d_power[(int)i]];
+                    const Shape si = shp[def.input_name];
+                    const int q = Cn.pad + (Cn.pad & 1);
+                    int ka = (q - Cn.pad + Cn.kernel + 1) / 2;
+                    ka = ka <= 1 ? 1 : (ka <= 2 ? 2 : 4);
+                    mk.make(top);   // virtual
+                    Buffer bu; bu.C = kS2dCpad; bu.H = si.H / 2; bu.W = si.W / 2 + ka - 1 + (q / 2); bu.dtype = DT_BF16;
+                    net->buffers.push_back(bu);
+                    st.kind = S_S2D; st.in = 0; st.out = -1;
+                    st.s2d_buf = (int)net->buffers.size() - 1; st.s2d_wp = bu.W; st.s2d_padl = q / 2;
+                    st.desc = "s2d " + L.name + " (Power folded into " + Cn.name + ")";
+                    net->steps.push_back(st);
+                    break;
+                }
                 st.kind = S_TRANSFORM; st.in = 0; st.out = mk.make(top);
                 st.desc = "transform " + L.name;
                 net->steps.push_back(st);
@@ -322,7 +397,8 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             }
             case L_CONV: {
                 st.in = blob_id(net, L.bottom[0]);
-                FCNOD_CHECK(net->blobs[st.in].buf >= 0, "Convolution directly on the NCHW input is not supported; insert a Power layer ('" + L.name + "')");
+                const bool is_s2d = s2d_conv.count((int)i) > 0;
+                FCNOD_CHECK(is_s2d || net->blobs[st.in].buf >= 0, "Convolution directly on the NCHW input is not supported; insert a Power layer ('" + L.name + "')");
                 st.out = mk.make(top);
                 // fuse a directly following in-place ReLU
                 if (i + 1 < def.layers.size() && def.layers[i + 1].type == L_RELU && def.layers[i + 1].bottom[0] == top &&
@@ -344,13 +420,30 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 bool tc_ok = bf && L.stride == 1 && 2 * L.pad == L.kernel - 1 && ib.dtype == DT_BF16 && ib.C % 8 == 0 &&
                              ib.ldc % 8 == 0 && ib.c_off % 8 == 0 &&
                              (ob.dtype == DT_F32 || (ob.ldc % 8 == 0 && ob.c_off % 8 == 0));
+                cw.stride = L.stride; cw.pad = L.pad;
+                if (is_s2d) {
+                    const LayerDef& P = def.layers[s2d_conv[(int)i]];
+                    tc_ok = ob.dtype == DT_F32 || (ob.ldc % 8 == 0 && ob.c_off % 8 == 0);
+                    FCNOD_CHECK(tc_ok, "space-to-depth convolution '" + L.name + "': output slice is not 16-byte aligned");
+                    cw.s2d = true; cw.in_scale = P.scale; cw.in_shift = P.shift;
+                    cw.q = L.pad + (L.pad & 1);
+                    int ka = (cw.q - L.pad + L.kernel + 1) / 2;
+                    cw.ka = ka <= 1 ? 1 : (ka <= 2 ? 2 : 4);
+                    for (size_t sj = 0; sj < net->steps.size(); ++sj)
+                        if (net->steps[sj].kind == S_S2D && net->steps[sj].layer == s2d_conv[(int)i]) {
+                            st.s2d_buf = net->steps[sj].s2d_buf; st.s2d_wp = net->steps[sj].s2d_wp;
+                            st.s2d_padl = net->steps[sj].s2d_padl;
+                        }
+                    FCNOD_CHECK(st.s2d_buf >= 0, "internal: no space-to-depth buffer for '" + L.name + "'");
+                    st.s2d_overlap = true;
+                }
                 st.kind = tc_ok ? S_CONV_TC : S_CONV_SIMT;
                 if (tc_ok) choose_tc_tiling(cw);
                 net->convs.push_back(cw);
                 st.conv = (int)net->convs.size() - 1;
                 std::ostringstream d;
                 d << (tc_ok ? "conv_tc " : "conv_simt ") << L.name << " " << L.kernel << "x" << L.kernel << "/" << L.stride
-                  << " Cin=" << cw.Cin << " Cout=" << cw.Cout << (st.relu ? " +relu" : "");
+                  << " Cin=" << cw.Cin << " Cout=" << cw.Cout << (st.relu ? " +relu" : "") << (is_s2d ? " +s2d+power" : "");
                 st.desc = d.str();
                 net->steps.push_back(st);
                 break;
@@ -370,6 +463,15 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_POOL: {
+                if (fuse_first.count((int)i)) { mk.make(top); break; }      // Pool -> LRN: emitted at the LRN
+                if (fuse_second.count((int)i)) {                            // LRN -> Pool
+                    const LayerDef& F = def.layers[fuse_second[(int)i]];
+                    st.kind = S_LRN_POOL; st.layer = fuse_second[(int)i]; st.layer2 = (int)i;
+                    st.in = blob_id(net, F.bottom[0]); st.out = mk.make(top);
+                    st.desc = "lrn+pool " + F.name + " + " + L.name;
+                    net->steps.push_back(st);
+                    break;
+                }
                 st.kind = S_POOL; st.in = blob_id(net, L.bottom[0]); st.out = mk.make(top);
                 FCNOD_CHECK(net->blobs[st.in].C % 8 == 0, "Pooling '" + L.name + "' needs channels % 8 == 0");
                 st.desc = "pool " + L.name;
@@ -377,6 +479,15 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_LRN: {
+                if (fuse_first.count((int)i)) { mk.make(top); break; }      // LRN -> Pool: emitted at the Pool
+                if (fuse_second.count((int)i)) {                            // Pool -> LRN
+                    const LayerDef& F = def.layers[fuse_second[(int)i]];
+                    st.kind = S_POOL_LRN; st.layer = fuse_second[(int)i]; st.layer2 = (int)i;
+                    st.in = blob_id(net, F.bottom[0]); st.out = mk.make(top);
+                    st.desc = "pool+lrn " + F.name + " + " + L.name;
+                    net->steps.push_back(st);
+                    break;
+                }
                 st.kind = S_LRN; st.in = blob_id(net, L.bottom[0]); st.out = mk.make(top);
                 FCNOD_CHECK(net->blobs[st.in].C % 8 == 0, "LRN '" + L.name + "' needs channels % 8 == 0");
                 FCNOD_CHECK(L.local_size == 3 || L.local_size == 5 || L.local_size == 7 || L.local_size == 9,
@@ -415,6 +526,13 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
 
 // ------------------------------------------------------------------------------------ tcgen05 tiling (host only)
 void choose_tc_tiling(ConvWeights& cw) {
+    cw.n_tiles = (cw.Cout + 127) / 128;
+    cw.BN = ((cw.Cout + cw.n_tiles - 1) / cw.n_tiles + 15) / 16 * 16;
+    if (cw.s2d) {   // K-block = one kernel row of ka taps x 16 channels (or one tap, see setup_tc_step)
+        cw.CK = cw.ka * kS2dCpad;
+        cw.n_cchunks = 1;
+        return;
+    }
     // K-block width: minimise padded K with a small per-block cost
     int best = 64; long best_cost = -1;
     const int cand[3] = {64, 32, 16};
@@ -425,8 +543,6 @@ void choose_tc_tiling(ConvWeights& cw) {
     }
     cw.CK = best;
     cw.n_cchunks = (cw.Cin + cw.CK - 1) / cw.CK;
-    cw.n_tiles = (cw.Cout + 127) / 128;
-    cw.BN = ((cw.Cout + cw.n_tiles - 1) / cw.n_tiles + 15) / 16 * 16;
 }
 
 void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
@@ -435,24 +551,34 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
     ConvTcParams& p = st.tc;
-    p.out = 0; p.bias = 0;
-    p.H = ib.H; p.W = ib.W;
+    memset(&p, 0, sizeof(p));
+    p.H = ob.H; p.W = ob.W;     // == input size for the stride-1 "same" convolutions; == s2d image size for s2d
     p.Cout = cw.Cout; p.ldo = ob.ldc;
-    p.kh = p.kw = cw.k; p.pad = L.pad;
+    p.kh = p.kw = cw.k; p.pad_h = p.pad_w = L.pad;
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
-    p.BW = std::min(ib.W, 128);
-    p.BH = std::max(1, std::min(ib.H, 128 / p.BW));
-    p.tiles_x = ceil_div(ib.W, p.BW);
-    p.tiles_y = ceil_div(ib.H, p.BH);
+    int ck = cw.CK;
+    if (cw.s2d) {
+        if (st.s2d_overlap) { p.kh = cw.ka; p.kw = 1; ck = cw.ka * kS2dCpad; }
+        else { p.kh = p.kw = cw.ka; ck = kS2dCpad; }
+        p.CK = ck; p.n_cchunks = 1;
+        p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
+        p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
+        p.bt_ld = cw.n_tiles * cw.BN;
+    }
+    // pixel box: the fewest boxes per row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
+    p.BW = ceil_div(ob.W, ceil_div(ob.W, 128));
+    p.BH = std::max(1, std::min(ob.H, 128 / p.BW));
+    p.tiles_x = ceil_div(ob.W, p.BW);
+    p.tiles_y = ceil_div(ob.H, p.BH);
     p.BN = cw.BN;
     p.relu = st.relu ? 1 : 0;
     p.out_fp32 = ob.dtype == DT_F32;
     uint32_t cols = 32;
     while ((int)cols < p.BN) cols <<= 1;
     p.tmem_cols = cols;
-    const uint32_t span = cw.CK * 2;
+    const uint32_t span = ck * 2;
     const size_t stage_bytes = 128 * span + align_up((size_t)p.BN * span, 1024);
-    const int KB = cw.k * cw.k * cw.n_cchunks;
+    const int KB = p.kh * p.kw * p.n_cchunks;
     int stages = (int)(96 * 1024 / stage_bytes);
     stages = std::max(2, std::min(stages, 8));
     stages = std::min(stages, std::max(2, KB));
@@ -483,6 +609,66 @@ void upload_weights(fcnod_net* net) {
             std::vector<float> b(cw.ldw, 0.f);
             std::copy(cw.b.begin(), cw.b.end(), b.begin());
             FCNOD_CUDA(cudaMemcpy(cw.d_bias, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
+        } else if (cw.s2d) {
+            // stride-2 convolution on the Power-transformed input as a stride-1 ka x ka convolution on the
+            // 2x2 space-to-depth image:  ih = 2*oh - pad + r,  r = 2*a + dy - (q - pad),  q = pad rounded up to even.
+            // GEMM weights = in_scale * w (bf16); the Power shift goes into the border-aware bias table
+            // bias[class(oh)][class(ow)][o] = b[o] + in_shift * sum over the taps that fall INSIDE the image.
+            const int ka = cw.ka, off = cw.q - cw.pad, Kp = ka * ka * kS2dCpad, Np = cw.n_tiles * cw.BN;
+            std::vector<bf16> w((size_t)Np * Kp, __float2bfloat16(0.f));
+            for (int o = 0; o < Cout; ++o)
+                for (int ah = 0; ah < ka; ++ah)
+                    for (int aw = 0; aw < ka; ++aw)
+                        for (int dy = 0; dy < 2; ++dy)
+                            for (int dx = 0; dx < 2; ++dx) {
+                                const int r = 2 * ah + dy - off, sx = 2 * aw + dx - off;
+                                if (r < 0 || r >= k || sx < 0 || sx >= k) continue;
+                                for (int c = 0; c < Cin; ++c)
+                                    w[(size_t)o * Kp + (size_t)(ah * ka + aw) * kS2dCpad + (dy * 2 + dx) * Cin + c] =
+                                        __float2bfloat16(cw.in_scale * cw.w[(((size_t)o * Cin + c) * k + r) * k + sx]);
+                            }
+            FCNOD_CUDA(cudaMalloc(&cw.d_w_tc, w.size() * 2));
+            FCNOD_CUDA(cudaMemcpy(cw.d_w_tc, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
+            std::vector<float> b(Np, 0.f);
+            std::copy(cw.b.begin(), cw.b.end(), b.begin());
+            FCNOD_CUDA(cudaMalloc(&cw.d_bias, b.size() * 4));
+            FCNOD_CUDA(cudaMemcpy(cw.d_bias, b.data(), b.size() * 4, cudaMemcpyHostToDevice));
+            const Blob& ibv = net->blobs[st.in];
+            const Blob& obv = net->blobs[st.out];
+            struct Cls { int lo, hi; };
+            Cls ch, cwd;
+            const int dimsI[2] = {ibv.H, ibv.W}, dimsO[2] = {obv.H, obv.W};
+            Cls* cl[2] = {&ch, &cwd};
+            for (int d = 0; d < 2; ++d) {
+                cl[d]->lo = (cw.pad + 1) / 2;
+                const int first_bad = (dimsI[d] + cw.pad - k + 1 + 1) / 2;     // first o with 2o - pad + k - 1 >= size
+                cl[d]->hi = std::max(0, dimsO[d] - first_bad);
+                FCNOD_CHECK(cl[d]->lo + cl[d]->hi < dimsO[d], "space-to-depth convolution: image too small for the border classes");
+            }
+            cw.bt_lo_h = ch.lo; cw.bt_hi_h = ch.hi; cw.bt_lo_w = cwd.lo; cw.bt_hi_w = cwd.hi;
+            const int nrc = ch.lo + ch.hi + 1, ncc = cwd.lo + cwd.hi + 1;
+            std::vector<float> tab((size_t)nrc * ncc * Np, 0.f);
+            for (int rc = 0; rc < nrc; ++rc) {
+                const int oh = rc < ch.lo ? rc : (rc == ch.lo ? ch.lo : obv.H - ch.hi + (rc - ch.lo - 1));
+                for (int cc = 0; cc < ncc; ++cc) {
+                    const int ow = cc < cwd.lo ? cc : (cc == cwd.lo ? cwd.lo : obv.W - cwd.hi + (cc - cwd.lo - 1));
+                    for (int o = 0; o < Cout; ++o) {
+                        double sum = 0.0;
+                        for (int r = 0; r < k; ++r) {
+                            const int ih = 2 * oh - cw.pad + r;
+                            if (ih < 0 || ih >= ibv.H) continue;
+                            for (int sx = 0; sx < k; ++sx) {
+                                const int iw = 2 * ow - cw.pad + sx;
+                                if (iw < 0 || iw >= ibv.W) continue;
+                                for (int c = 0; c < Cin; ++c) sum += (double)cw.w[(((size_t)o * Cin + c) * k + r) * k + sx];
+                            }
+                        }
+                        tab[((size_t)rc * ncc + cc) * Np + o] = (float)((double)cw.b[o] + (double)cw.in_shift * sum);
+                    }
+                }
+            }
+            FCNOD_CUDA(cudaMalloc(&cw.d_bias_tab, tab.size() * 4));
+            FCNOD_CUDA(cudaMemcpy(cw.d_bias_tab, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
         } else {
             const int Kp = k * k * cw.n_cchunks * cw.CK, Np = cw.n_tiles * cw.BN;
             std::vector<bf16> w((size_t)Np * Kp, __float2bfloat16(0.f));
@@ -524,29 +710,64 @@ void free_activations(fcnod_net* net) {
     if (net->pinned_out) { cudaFreeHost(net->pinned_out); net->pinned_out = 0; }
 }
 
+CUresult encode_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides,
+                    const cuuint32_t* box, uint32_t span, CUtensorMapL2promotion l2) {
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    const CUtensorMapSwizzle sw = span == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                              : (span == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+    return get_encode_tiled()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, base, dims, strides, box, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+
 void setup_tc_step(fcnod_net* net, Step& st) {
     const LayerDef& L = net->def.layers[st.layer];
     ConvWeights& cw = net->convs[st.conv];
     const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
     const int B = net->batch;
+    if (cw.s2d) {
+        // A = the W-padded space-to-depth image [B][H2][Wp][16] bf16.  Preferred: ONE K-block per kernel row,
+        // its A rows being the 128-byte windows of ka consecutive pixels (an overlapping-stride tensor map:
+        // dim0 = ka*16 contiguous elements, dim1 = window start, one pixel = 32 bytes apart).  If the driver
+        // refuses that map, one K-block per tap over the plain map (same weights buffer, same results).
+        const int H2 = ob.H, W2 = ob.W, Wp = st.s2d_wp;
+        void* base = net->buffers[st.s2d_buf].ptr;
+        const cuuint64_t pix = kS2dCpad * 2;
+        const char* force = getenv("FCNOD_S2D_TAPS");
+        st.s2d_overlap = !(force && force[0] == '1');
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            fill_tc_geometry(net, st, B);
+            ConvTcParams& p = st.tc;
+            const uint32_t span = p.CK * 2;
+            cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)(st.s2d_overlap ? W2 : Wp), (cuuint64_t)H2, (cuuint64_t)B};
+            cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
+            cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
+            CUresult r = encode_map(&st.tmap_a, base, 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+            if (r != CUDA_SUCCESS && st.s2d_overlap) { st.s2d_overlap = false; continue; }
+            FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
+            const cuuint64_t Kp = (cuuint64_t)cw.ka * cw.ka * kS2dCpad;
+            cuuint64_t bd[2] = {Kp, (cuuint64_t)cw.n_tiles * cw.BN};
+            cuuint64_t bs[1] = {Kp * 2};
+            cuuint32_t bb[2] = {(cuuint32_t)p.CK, (cuuint32_t)cw.BN};
+            r = encode_map(&st.tmap_b, cw.d_w_tc, 2, bd, bs, bb, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+            FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
+            p.out = view_ptr(net, ob);
+            p.bias = cw.d_bias;
+            p.bias_tab = cw.d_bias_tab;
+            break;
+        }
+        return;
+    }
     fill_tc_geometry(net, st, B);
     ConvTcParams& p = st.tc;
     p.out = view_ptr(net, ob);
     p.bias = cw.d_bias;
     const uint32_t span = cw.CK * 2;
-
-    EncodeTiledFn enc = get_encode_tiled();
-    const CUtensorMapSwizzle sw = span == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
-                                              : (span == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
     {
         cuuint64_t dims[4] = {(cuuint64_t)ib.C, (cuuint64_t)ib.W, (cuuint64_t)ib.H, (cuuint64_t)B};
         cuuint64_t strides[3] = {(cuuint64_t)ib.ldc * 2, (cuuint64_t)ib.W * ib.ldc * 2, (cuuint64_t)ib.H * ib.W * ib.ldc * 2};
         cuuint32_t box[4] = {(cuuint32_t)cw.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
-        cuuint32_t es[4] = {1, 1, 1, 1};
-        CUresult r = enc(&st.tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, view_ptr(net, ib), dims, strides, box, es,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        CUresult r = encode_map(&st.tmap_a, view_ptr(net, ib), 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
     {
@@ -554,10 +775,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         cuuint64_t dims[2] = {Kp, (cuuint64_t)cw.n_tiles * cw.BN};
         cuuint64_t strides[1] = {Kp * 2};
         cuuint32_t box[2] = {(cuuint32_t)cw.CK, (cuuint32_t)cw.BN};
-        cuuint32_t es[2] = {1, 1};
-        CUresult r = enc(&st.tmap_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, cw.d_w_tc, dims, strides, box, es,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        CUresult r = encode_map(&st.tmap_b, cw.d_w_tc, 2, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
 }
@@ -593,6 +811,18 @@ void launch_pool(const fcnod_net* net, const Step& st, const LayerDef& L, cudaSt
     const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
     long items = (long)net->batch * ob.H * ob.W * (ib.C / 8);
+    if (L.kernel == 3 && (L.stride == 1 || L.stride == 2) && items < (1L << 31)) {
+        // 2x2 output pixels per thread from one shared input window
+        long blocks2 = (long)net->batch * ((ob.H + 1) / 2) * ((ob.W + 1) / 2) * (ib.C / 8);
+        int g = grid_for(blocks2, 256);
+        if (L.stride == 1)
+            pool_tile_kernel<T, 3, 1><<<g, 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), net->batch, ib.C,
+                                                         ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, L.pad);
+        else
+            pool_tile_kernel<T, 3, 2><<<g, 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), net->batch, ib.C,
+                                                         ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, L.pad);
+        return;
+    }
     pool_max_kernel<T><<<grid_for(items, 256), 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), net->batch,
                                                              ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, L.kernel,
                                                              L.stride, L.pad);
@@ -660,6 +890,40 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             long npix = (long)net->batch * ob.H * ob.W;
             input_transform_kernel<<<grid_for(npix, 256), 256, 0, s>>>(data_dev, (float*)view_ptr(net, ob), net->batch, ob.C,
                                                                         ob.H * ob.W, L->shift, L->scale, L->power);
+            break;
+        }
+        case S_S2D: {
+            const Blob& ib = net->blobs[0];
+            long items = (long)net->batch * (ib.H / 2) * (ib.W / 2);
+            input_s2d_kernel<<<grid_for(items, 256), 256, 0, s>>>(data_dev, (bf16*)net->buffers[st.s2d_buf].ptr, net->batch, ib.C,
+                                                                   ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+            break;
+        }
+        case S_POOL_LRN: {   // layer = Pooling, layer2 = LRN
+            const LayerDef& R = net->def.layers[st.layer2];
+            const Blob& ib = net->blobs[st.in];
+            const Blob& ob = net->blobs[st.out];
+            FCNOD_CHECK(ib.dtype == DT_BF16 && ob.dtype == DT_BF16, "pool+lrn: bf16 only");
+            const int CG = ib.C / 8, npix_cta = 256 / CG;
+            long npix = (long)net->batch * ob.H * ob.W;
+            int g = (int)std::min<long>((npix + npix_cta - 1) / npix_cta, (long)kNumSMs * 8);
+            size_t smem = (size_t)npix_cta * (ib.C + 16) * 4;
+            pool_lrn_kernel<bf16, 3, 2, 2, true><<<g, 256, smem, s>>>((const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob),
+                                                                      net->batch, ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc,
+                                                                      L->pad, R.alpha / R.local_size, R.beta, R.lrn_k);
+            break;
+        }
+        case S_LRN_POOL: {   // layer = LRN, layer2 = Pooling
+            const LayerDef& P = net->def.layers[st.layer2];
+            const Blob& ib = net->blobs[st.in];
+            const Blob& ob = net->blobs[st.out];
+            FCNOD_CHECK(ib.dtype == DT_BF16 && ob.dtype == DT_BF16, "lrn+pool: bf16 only");
+            constexpr int TH = 4, TW = 8;
+            const int tx = ceil_div(ob.W, TW), ty = ceil_div(ob.H, TH);
+            size_t smem = (size_t)(2 * (TH - 1) + 3) * (2 * (TW - 1) + 3) * ib.C * 2;
+            lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW><<<tx * ty * net->batch, 256, smem, s>>>(
+                (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad, tx,
+                ty, L->alpha / L->local_size, L->beta, L->lrn_k);
             break;
         }
         case S_CONV_SIMT: launch_conv_simt(net, st, *L, s); break;
@@ -793,6 +1057,8 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     FCNOD_CHECK(prop.major == 10, "fcnod_b200 is built for sm_100a (Blackwell B200) only; found sm_" +
                                       std::to_string(prop.major) + std::to_string(prop.minor));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
     upload_weights(net.get());
     reshape(net.get(), net->def.input_dims[0] > 0 ? net->def.input_dims[0] : 1);
@@ -811,6 +1077,7 @@ int fcnod_net_destroy(fcnod_net* net) {
             if (net->convs[i].d_w_simt) cudaFree(net->convs[i].d_w_simt);
             if (net->convs[i].d_w_tc) cudaFree(net->convs[i].d_w_tc);
             if (net->convs[i].d_bias) cudaFree(net->convs[i].d_bias);
+            if (net->convs[i].d_bias_tab) cudaFree(net->convs[i].d_bias_tab);
         }
         if (net->stream) cudaStreamDestroy(net->stream);
         delete net;
@@ -865,6 +1132,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
             const Blob& b = net->blobs[st.out];
             o << " -> " << b.name << " (" << b.C << "," << b.H << "," << b.W << ") " << (b.dtype == DT_F32 ? "f32" : "bf16")
               << " buf" << b.buf << "+" << b.c_off << "/" << b.ldc;
+            if (st.kind == S_CONV_TC && net->convs[st.conv].s2d) o << (st.s2d_overlap ? " [row K-blocks]" : " [tap K-blocks]");
         }
         o << "\n";
     }
@@ -901,6 +1169,8 @@ int fcnod_net_blob_read(fcnod_net* net, const char* blob, float* host_out, size_
     const Blob& b = net->blobs[blob_id(net, blob)];
     size_t n = (size_t)net->batch * b.C * b.H * b.W;
     FCNOD_CHECK(count == n, "blob_read: count mismatch (blob has " + std::to_string(n) + " elements)");
+    FCNOD_CHECK(b.buf != -2, std::string("blob '") + blob + "' is fused away in the bf16 plan and never materialised; "
+                "create the net with FCNOD_PRECISION_FP32, or set FCNOD_NO_FUSION=1, to inspect it");
     if (b.buf < 0) {
         FCNOD_CUDA(cudaMemcpy(host_out, net->data_dev, n * 4, cudaMemcpyDeviceToHost));
     } else if (b.is_output) {

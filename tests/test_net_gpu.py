@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from tests.golden import make_golden as G
-from tests.util import GOLDEN, bf16_round, gpu_forward, oracle_forward, rel_err, write_mini_net
+from tests.util import GOLDEN, bf16_round, gpu_forward, oracle_forward, rel_err, write_mini_net, write_stem_net
 
 pytestmark = pytest.mark.gpu
 
@@ -77,13 +77,62 @@ def test_conv_tc_mini_nets(case, tmp_path):
     assert rel_err(got['out'], ref['out']) < TOL_BF16
 
 
+STEM_CASES = [
+    # tag, H, W, batch, k, pad, cout, shift, scale, c2
+    ('deploy_like', 64, 96, 2, 7, 3, 64, -127.0, 1.0, 192),
+    ('two_boxes', 40, 300, 1, 7, 3, 64, -127.0, 1.0, 64),      # W/2 = 150 -> two 75-pixel boxes per row
+    ('k3_p1', 36, 52, 2, 3, 1, 32, -0.5, 2.0, 64),               # ka = 2 taps
+    ('k5_p2', 48, 48, 1, 5, 2, 48, 0.25, 0.5, 64),               # ka = 3 -> padded to 4
+    ('full_rows', 448, 64, 1, 7, 3, 64, -127.0, 1.0, 64),        # all 224 output rows, every border class
+]
+
+
+@pytest.mark.parametrize('case', STEM_CASES, ids=[c[0] for c in STEM_CASES])
+def test_s2d_conv_and_fused_pool_lrn(case, tmp_path, monkeypatch):
+    """bf16 plan of the stem: Power folded into the stride-2 convolution (space-to-depth, tcgen05), fused
+    Pool->LRN and LRN->Pool, against the fp32 oracle and against the unfused bf16 plan."""
+    tag, H, W, batch, k, pad, cout, shift, scale, c2 = case
+    proto, cm = write_stem_net(str(tmp_path), tag, H, W, batch=batch, seed=len(tag), k=k, pad=pad, cout=cout, shift=shift,
+                               scale=scale, c2=c2)
+    x = np.random.RandomState(4).uniform(0, 1, (batch, 3, H, W)).astype(np.float32)
+    want = ['c1', 'n1', 'c2', 'p2', 'out']
+    ref = oracle_forward(proto, cm, x, want=want)
+    got, plan = gpu_forward(proto, cm, x, 'bf16', want)
+    assert '+s2d+power' in plan and 'pool+lrn' in plan and 'lrn+pool' in plan and 'conv_simt' not in plan, plan
+    errs = {n: rel_err(got[n], ref[n]) for n in want}
+    # c1 is stored in bf16 (1 ulp = 2^-8 of the value); later blobs accumulate a few such roundings
+    assert errs['c1'] < 1.0 / 128, errs
+    assert all(e < 2e-2 for e in errs.values()), errs
+    # the fused-away blobs answer with a clear error, the unfused plan materialises them and agrees
+    import fcn_object_detector_b200.caffe_shim as caffe
+    from fcn_object_detector_b200._lib import FcnodError
+    net = caffe.Net(proto, cm, caffe.TEST, device=0, precision='bf16')
+    net.blobs['data'].reshape(*x.shape); net.blobs['data'].data[...] = x; net.forward()
+    with pytest.raises(FcnodError):
+        net.blobs['p1'].data
+    net.close()
+    monkeypatch.setenv('FCNOD_NO_FUSION', '1')
+    unf, plan2 = gpu_forward(proto, cm, x, 'bf16', want + ['p1', 'n2'])
+    assert 'pool+lrn' not in plan2 and 'conv_simt' in plan2
+    for n in ('n1', 'p2', 'out'):
+        assert rel_err(got[n], unf[n]) < 2e-2, (n, rel_err(got[n], unf[n]))
+    # the tap-per-K-block variant of the s2d convolution gives the same bits as the row-per-K-block one
+    monkeypatch.delenv('FCNOD_NO_FUSION')
+    monkeypatch.setenv('FCNOD_S2D_TAPS', '1')
+    taps, plan3 = gpu_forward(proto, cm, x, 'bf16', ['c1'])
+    assert '[tap K-blocks]' in plan3
+    if '[row K-blocks]' in plan:
+        assert rel_err(taps['c1'], got['c1']) < 1.0 / 128
+
+
 def test_bf16_full_net_within_tolerance(model_files):
     proto, cm = model_files
     x = np.random.RandomState(2).uniform(0, 1, (2, 3, 448, 448)).astype(np.float32)
-    want = ['conv2/3x3', 'inception_3a/output', 'inception_4e/output', 'inception_5b/output', 'coverage', 'bboxes']
+    want = ['conv1/7x7_s2', 'pool1/norm1', 'conv2/3x3', 'pool2/3x3_s2', 'inception_3a/output', 'inception_4e/output',
+            'inception_5b/output', 'coverage', 'bboxes']
     exp = oracle_forward(proto, cm, x, want=want)
     got, plan = gpu_forward(proto, cm, x, 'bf16', want)
-    assert plan.count('conv_tc') == 58
+    assert 'conv_simt' not in plan and '+s2d+power' in plan
     errs = {k: rel_err(got[k], exp[k]) for k in want}
     print(errs)
     assert errs['coverage'] < TOL_BF16 and errs['bboxes'] < TOL_BF16, errs

@@ -62,6 +62,35 @@ def write_mini_net(dirpath, tag, H, W, cin, branches, batch=1, seed=0, final=8):
     return proto, cm
 
 
+def write_stem_net(dirpath, tag, H, W, batch=1, seed=0, k=7, pad=3, cout=64, shift=-127.0, scale=1.0, mid=64, c2=64):
+    """The deploy net's stem in miniature (deploy.prototxt:8-162): data -> Power(shift) -> conv kxk/2 relu -> pool 3/2
+    -> LRN -> 1x1 (mid) relu -> 3x3 (c2) relu -> LRN -> pool 3/2 -> 1x1 out.  Exercises the bf16 plan's
+    space-to-depth convolution (Power folded, border-aware bias) and the fused Pool->LRN / LRN->Pool kernels."""
+    from fcn_object_detector_b200.caffemodel import write_caffemodel
+    rs = np.random.RandomState(seed)
+    txt = 'input: "data"\ninput_shape { dim: %d dim: 3 dim: %d dim: %d }\n' % (batch, H, W)
+    txt += 'layer { name: "xf" type: "Power" bottom: "data" top: "x" power_param { shift: %r scale: %r } }\n' % (shift, scale)
+    txt += _conv_txt('c1', 'x', 'c1', cout, k, pad=pad, stride=2)
+    txt += 'layer { name: "p1" type: "Pooling" bottom: "c1" top: "p1" pooling_param { pool: MAX kernel_size: 3 stride: 2 } }\n'
+    txt += 'layer { name: "n1" type: "LRN" bottom: "p1" top: "n1" lrn_param { local_size: 5 alpha: 0.0001 beta: 0.75 } }\n'
+    txt += _conv_txt('r2', 'n1', 'r2', mid, 1)
+    txt += _conv_txt('c2', 'r2', 'c2', c2, 3, pad=1)
+    txt += 'layer { name: "n2" type: "LRN" bottom: "c2" top: "n2" lrn_param { local_size: 5 alpha: 0.0001 beta: 0.75 } }\n'
+    txt += 'layer { name: "p2" type: "Pooling" bottom: "n2" top: "p2" pooling_param { pool: MAX kernel_size: 3 stride: 2 } }\n'
+    txt += _conv_txt('final', 'p2', 'out', 8, 1, relu=False)
+
+    def wb(co, ci, kk, bias_lo=-0.2, bias_hi=0.2):
+        s_ = np.sqrt(3.0 / (ci * kk * kk))
+        return [rs.uniform(-s_, s_, (co, ci, kk, kk)).astype(np.float32), rs.uniform(bias_lo, bias_hi, co).astype(np.float32)]
+    layers = [('c1', 'Convolution', wb(cout, 3, k)), ('r2', 'Convolution', wb(mid, cout, 1)),
+              ('c2', 'Convolution', wb(c2, mid, 3)), ('final', 'Convolution', wb(8, c2, 1))]
+    proto = os.path.join(dirpath, tag + '.prototxt')
+    with open(proto, 'w') as f:
+        f.write(txt)
+    cm = write_caffemodel(os.path.join(dirpath, tag + '.caffemodel'), layers)
+    return proto, cm
+
+
 def bf16_round(a):
     import torch
     return torch.as_tensor(np.asarray(a, np.float32)).to(torch.bfloat16).to(torch.float32).numpy()
