@@ -240,18 +240,18 @@ def run_ours(args):
             torch.cuda.synchronize()
             per.append(a.elapsed_time(b) / reps)
         from fcn_object_detector_b200.netspec import conv_shapes
-        macs = {}
-        hw = {}
-        for d in plan:
-            if '->' in d and '(' in d:
-                name = d.split()[2]
-                dims = d.split('(')[1].split(')')[0].split(',')
-                hw[name] = int(dims[1]) * int(dims[2])
-        for n, co, ci, k, _b in conv_shapes():
-            out_hw = hw.get(n, 28 * 28) if n not in ('bbox/regressor',) else 28 * 28
-            macs[n] = co * ci * k * k * out_hw
+        import re
+        shapes = {n: (co, ci, k) for n, co, ci, k, _b in conv_shapes()}
+
+        def step_macs(d):
+            """algorithmic MACs per frame of one conv_tc launch (a launch may hold several fused convolutions)"""
+            names = re.match(r'\d+: conv_tc (.+?) \d+x\d+/\d+ ', d).group(1).split(' + ')
+            dims = d.split(' -> ')[1].split('(')[1].split(')')[0].split(',')
+            out_hw = int(dims[1]) * int(dims[2])
+            return sum(shapes[n][0] * shapes[n][1] * shapes[n][2] ** 2 * out_hw for n in names)
+        macs = {d: step_macs(d) for d in plan if 'conv_tc' in d}
         tc_ms = sum(t for t, d in zip(per, plan) if 'conv_tc' in d)
-        tc_flop = sum(2.0 * macs[d.split()[2]] * B for d in plan if 'conv_tc' in d)
+        tc_flop = sum(2.0 * macs[d] * B for d in plan if 'conv_tc' in d)
         n_tc = sum('conv_tc' in d for d in plan)
         tot_ms = sum(per)
         ach = tc_flop / (tc_ms * 1e-3) / 1e12

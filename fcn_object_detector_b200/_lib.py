@@ -55,6 +55,7 @@ SIGNATURES = {
     'fcnod_net_blob_read': (_I, [_P, _STR, _P, _SZ]),
     'fcnod_net_output_device': (_I, [_P, _STR, C.POINTER(_P)]),
     'fcnod_net_run_step': (_I, [_P, _I, _I, _P]),
+    'fcnod_net_profile_conv_step': (_I, [_P, _I, _P, _SZ]),
     'fcnod_postnet_default_params': (None, [C.POINTER(PostnetParams)]),
     'fcnod_postnet_scratch_bytes': (_SZ, [_I, _I]),
     'fcnod_postnet_device': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P, _P, _P]),

@@ -1,0 +1,400 @@
+// Persistent bf16 implicit-GEMM convolution on the 5th-generation tensor cores (sm_100a); second generation of
+// conv_tc.cuh (which stays as the simple one-tile-per-CTA form, selectable with FCNOD_CONV_V1=1).
+//
+// GEMM view  D[M = pixels][N = Cout] = A[M][K] * B[N][K]^T,  K = kh*kw*Cin_pad, as in conv_tc.cuh.  What changes:
+//
+//   * ONE CTA per SM looping over (pixel tile, N tile) pairs: TMEM allocation, barrier initialisation and
+//     tensor-map prefetch are paid once per launch instead of once per 112-pixel tile.
+//   * TWO accumulators in TMEM: the MMA warp starts the next tile while the four epilogue warps drain the
+//     previous one (tmem_full / tmem_empty mbarriers).  N tiles up to 256 columns (2 x 256 = all 512 TMEM columns).
+//   * Separate shared-memory rings for A (activations) and B (weights), each with full / empty mbarriers.
+//   * HALO mode for k x k convolutions (3x3 pad 1, 5x5 pad 2 of /root/reference/models/deploy.prototxt): per 64-channel
+//     chunk ONE TMA box brings the (BH+k-1) x (BW+k-1) input patch of the tile; it lands densely as
+//     [patch pixel][64 ch] = 128-byte swizzled rows.  Tap (r, s) is then the SAME shared-memory tile read through a
+//     UMMA descriptor whose start address is shifted by r*(BW+k-1) + s rows: accumulator row i = py*(BW+k-1) + px
+//     reads patch pixel (py+r, px+s).  The 9 (25) taps re-use one load instead of 9 (25) shifted loads; rows with
+//     px >= BW are computed and discarded.  TAP mode (1x1, the space-to-depth first convolution) = one A box per K-block.
+//   * Epilogue through shared memory, 8 warps: two per TMEM lane quadrant, each draining half of the columns of its
+//     32 accumulator rows: bias (staged in smem per tile) + ReLU, pack to bf16 into a private swizzled staging area,
+//     read back so that consecutive lanes store consecutive 16-byte pieces of one pixel (full lines instead of 32
+//     scattered sectors per store).  No cross-warp synchronisation in the epilogue.
+//   * Horizontal fusion: N may be the concatenation of several convolutions reading the same input (the 1x1 /
+//     3x3_reduce / 5x5_reduce branches of an inception module, deploy.prototxt:163-377): up to four output SEGMENTS
+//     with their own destination views; boundaries are multiples of 8 channels.
+//   * "Direct" segments (the fp32 heads, deploy.prototxt:2118-2175) are written straight from registers as NCHW
+//     float32 (lanes = consecutive pixels), with an optional sigmoid (coverage/sig :2144-2149).
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+#include "conv_tc.cuh"
+
+namespace fcnod {
+
+enum { SEG_RELU = 1, SEG_DIRECT = 2, SEG_SIGMOID = 4 };
+
+struct ConvSeg {
+    void* out;     // bf16 NHWC view base (already offset to the slice), or float NCHW blob base for SEG_DIRECT
+    int ldo;       // NHWC: channels of the destination buffer; DIRECT: channels of the NCHW blob
+    int col0;      // first fused-N column of this segment (multiple of 8)
+    int ncols;     // valid channels (NHWC: multiple of 8)
+    int flags;
+};
+
+struct ConvTc2Params {
+    const float* bias;       // [n_tiles * BN] over the fused N (zero padded)
+    const float* bias_tab;   // optional border-aware bias (see conv_tc.cuh)
+    int bt_lo_h, bt_hi_h, bt_lo_w, bt_hi_w, bt_ld;
+    int H, W;
+    int kh, kw, pad_h, pad_w, n_cchunks, CK;
+    int BW, BH, tiles_x, tiles_y;
+    int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
+    int halo;                // 1 = HALO mode
+    int m_tiles, n_tiles, BN;
+    int a_stages, b_stages;
+    uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
+    uint32_t tmem_cols;      // whole allocation (2 accumulators), power of two
+    uint32_t acc_stride;     // columns between the two accumulators
+    uint32_t row_bytes;      // staging row pitch of one epilogue warp: its columns * 2, rounded up to 128
+    int cols_half0;          // columns drained by the first warp of each quadrant pair (multiple of 16); rest = BN - cols_half0
+    int flags;               // SEG_RELU / SEG_DIRECT: uniform over the segments of one launch
+    int bt_interior;         // bias_tab: class index of interior pixels (== the row `bias` points at)
+    int nseg;
+    ConvSeg seg[4];
+    // optional timeline of CTA 0 (fcnod_net_profile_conv_step): clock64 stamps [4 roles][8 tiles][64 events]
+    unsigned long long* prof;
+};
+
+#define FCNOD_PROF(role, tile, ev)                                                                      \
+    do {                                                                                                \
+        if (p.prof && blockIdx.x == 0 && (tile) < 8 && (ev) < 64)                                       \
+            p.prof[((role) * 8 + (tile)) * 64 + (ev)] = (unsigned long long)clock64();                  \
+    } while (0)
+
+constexpr int kTcProducerWarps = 4;
+constexpr int kTcMmaWarp = 4;
+constexpr int kConvTc2Threads = 32 * (kTcProducerWarps + 1 + 8);   // 4 TMA warps + MMA warp + 8 epilogue warps
+
+namespace tc {
+// K-major SWIZZLE_128B descriptor for a start address that is only 128-byte (one row) aligned: the matrix base
+// offset field carries the row phase (start >> 7) & 7 of the 1024-byte swizzle pattern.
+__device__ __forceinline__ uint64_t umma_desc_sw128_rows(uint32_t saddr) {
+    return umma_desc(saddr, 128) | ((uint64_t)((saddr >> 7) & 7u) << 49);
+}
+// tcgen05.mma with both operand descriptors given as {lo, hi} 32-bit halves (hi is shared by A and B)
+__device__ __forceinline__ void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                               uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accum)
+        : "memory");
+}
+// wait with back-off, for the warps that wait long (keeps their spinning out of the issue slots of the TMA / MMA threads)
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+    for (uint32_t it = 0; it < (1u << 22); ++it) {
+        if (mbar_try_wait(bar, parity)) return;
+        __nanosleep(40);
+    }
+    __trap();
+}
+}  // namespace tc
+
+// KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0
+template <int KSTEPS, bool HALO, bool PROF>
+__global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                                                                      const __grid_constant__ CUtensorMap tmap_b,
+                                                                      const __grid_constant__ ConvTc2Params p) {
+    using namespace tc;
+    extern __shared__ __align__(1024) uint8_t smem_raw2[];
+    const uint32_t smem_base = (smem_u32(smem_raw2) + 1023u) & ~1023u;
+    const uint32_t span = (uint32_t)p.CK * 2u;
+    const uint32_t a_base = smem_base;
+    const uint32_t b_base = a_base + (uint32_t)p.a_stages * p.a_stage_bytes;
+    const uint32_t stage_base = b_base + (uint32_t)p.b_stages * p.b_stage_bytes;   // epilogue staging: 8 warps x 32 rows
+    const uint32_t bias_base = stage_base + 8u * 32u * p.row_bytes;                // 8 warps x 128 floats
+    const uint32_t bar_base = bias_base + 8u * 512u;
+    const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * p.a_stages;
+    const uint32_t bfull0 = aempty0 + 8u * p.a_stages, bempty0 = bfull0 + 8u * p.b_stages;
+    const uint32_t tfull0 = bempty0 + 8u * p.b_stages, tempty0 = tfull0 + 16u;
+    const uint32_t tmem_slot = tempty0 + 16u;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total_tiles = p.m_tiles * p.n_tiles;
+    const int tpi = p.tiles_x * p.tiles_y;
+    const int taps = p.kh * p.kw;
+    const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
+        for (int s = 0; s < p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == kTcMmaWarp) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp < kTcProducerWarps) {
+        // ================= TMA producers: warps 0,1 feed the A ring (even / odd loads), warps 2,3 the B ring ============
+        // One thread per warp.  A single thread needs ~300 cycles per (wait, expect_tx, TMA) round, so the loads of a
+        // ring are dealt round-robin to two warps; every stage has its own barriers, arrival order does not matter.
+        if (lane == 0) {
+            const bool ringB = warp >= 2;
+            const uint32_t par = (uint32_t)warp & 1u;
+            asm volatile("prefetch.tensormap [%0];" ::"l"(ringB ? &tmap_b : &tmap_a) : "memory");
+            const uint32_t b_tx = (uint32_t)p.BN * span;
+            const int kb_stride = p.n_cchunks * p.CK;          // K columns between two taps of the packed weights
+            const uint32_t nst = ringB ? (uint32_t)p.b_stages : (uint32_t)p.a_stages;
+            const uint32_t st_bytes = ringB ? p.b_stage_bytes : p.a_stage_bytes;
+            const uint32_t ring_base = ringB ? b_base : a_base;
+            const uint32_t full0 = ringB ? bfull0 : afull0, empty0 = ringB ? bempty0 : aempty0;
+            uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
+            int tile_i = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tile_i) {
+                const int nt = t % p.n_tiles, mt = t / p.n_tiles;
+                const int n_img = mt / tpi, trem = mt - n_img * tpi;
+                const int ty = trem / p.tiles_x, tx = trem - ty * p.tiles_x;
+                const int oh0 = ty * p.BH - p.pad_h, ow0 = tx * p.BW - p.pad_w, n0 = nt * p.BN;
+                if (!ringB) {
+                    // ---- A: one box per channel chunk (HALO) or per (tap, chunk) (TAP)
+                    for (int r = 0; r < (HALO ? 1 : p.kh); ++r)
+                        for (int s = 0; s < (HALO ? 1 : p.kw); ++s)
+                            for (int cc = 0; cc < p.n_cchunks; ++cc, ++idx) {
+                                if ((idx & 1u) == par) {
+                                    mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                    mbar_expect_tx(full0 + 8u * sg, p.a_tx_bytes);
+                                    tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
+                                }
+                                dst += st_bytes;
+                                if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
+                            }
+                } else {
+                    // ---- B: one box per K-block; K column = tap * kb_stride + cc * CK
+                    const int n_outer = HALO ? p.n_cchunks : taps, n_inner = HALO ? taps : p.n_cchunks;
+                    const int outer_step = HALO ? p.CK : kb_stride, inner_step = HALO ? kb_stride : p.CK;
+                    int ev = 0;
+                    for (int o = 0, kcol_o = 0; o < n_outer; ++o, kcol_o += outer_step)
+                        for (int i = 0, kcol = kcol_o; i < n_inner; ++i, kcol += inner_step, ++idx, ++ev) {
+                            if ((idx & 1u) == par) {
+                                mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                if (PROF) FCNOD_PROF(0, tile_i, ev);
+                                mbar_expect_tx(full0 + 8u * sg, b_tx);
+                                tma_load_2d(dst, &tmap_b, full0 + 8u * sg, kcol, n0);
+                            }
+                            dst += st_bytes;
+                            if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
+                        }
+                }
+            }
+        }
+    } else if (warp == kTcMmaWarp) {
+        // ================= MMA issuer (one thread; descriptors advanced with 32-bit adds, K steps unrolled) ============
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | (8u << 24);
+            // descriptor = {lo: start address >> 4 | LBO 1 << 16, hi: SBO (8 rows) >> 4 | version 1 << 14 | swizzle << 29}
+            const uint32_t desc_hi = ((8u * span) >> 4) | (1u << 14) | ((span == 128 ? 2u : (span == 64 ? 4u : 6u)) << 29);
+            const uint32_t a_lo_base = ((a_base & 0x3FFFFu) >> 4) | (1u << 16), a_lo_step = p.a_stage_bytes >> 4;
+            const uint32_t b_lo_base = ((b_base & 0x3FFFFu) >> 4) | (1u << 16), b_lo_step = p.b_stage_bytes >> 4;
+            const uint32_t row_step = (uint32_t)p.PW * 8u;      // HALO: one patch row = PW rows of 128 bytes, in 16-byte units
+            uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
+            uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
+            int it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+                const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
+                if (PROF) FCNOD_PROF(1, it, 61);
+                mbar_wait(tempty0 + 8u * acc, aphase ^ 1u);          // the epilogue has drained this accumulator
+                fence_after();
+                if (PROF) FCNOD_PROF(1, it, 62);
+                const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
+                uint32_t accum = 0;
+                int ev = 0;
+                for (int ai = 0; ai < a_iters; ++ai) {
+                    mbar_wait(afull0 + 8u * sa, pa);
+                    uint32_t a_row = a_lo;
+                    for (int r = 0; r < (HALO ? p.kh : 1); ++r, a_row += row_step) {
+                        for (int s = 0; s < (HALO ? p.kw : 1); ++s, ++ev) {
+                            mbar_wait(bfull0 + 8u * sb, pb);
+                            fence_after();
+                            if (PROF) FCNOD_PROF(1, it, ev);
+                            const uint32_t a_tap = a_row + (uint32_t)s * 8u;
+#pragma unroll
+                            for (int k = 0; k < KSTEPS; ++k) {
+                                umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_lo + 2u * k, desc_hi, idesc, accum);
+                                accum = 1;
+                            }
+                            umma_commit(bempty0 + 8u * sb);
+                            if (PROF) FCNOD_PROF(3, it, ev);
+                            b_lo += b_lo_step;
+                            if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
+                        }
+                    }
+                    umma_commit(aempty0 + 8u * sa);
+                    a_lo += a_lo_step;
+                    if (++sa == (uint32_t)p.a_stages) { sa = 0; pa ^= 1u; a_lo = a_lo_base; }
+                }
+                umma_commit(tfull0 + 8u * acc);
+                if (PROF) FCNOD_PROF(1, it, 63);
+            }
+        }
+    } else {
+        // ================= epilogue: 8 warps; warp w drains TMEM lane quadrant w % 4, column half (w - 5) / 4 ===========
+        const int ew = warp - (kTcMmaWarp + 1);
+        const int q = warp & 3, half = ew >> 2;
+        const int HW = p.H * p.W;
+        // this warp's columns inside the N tile: [wc0, wc0 + wcols), 16-column granular
+        const int wc0 = half ? p.cols_half0 : 0;
+        const int wcols = half ? p.BN - p.cols_half0 : p.cols_half0;
+        const uint32_t my_stage = stage_base + (uint32_t)ew * 32u * p.row_bytes;
+        const uint32_t my_row = my_stage + (uint32_t)lane * p.row_bytes;
+        const uint32_t my_bias = bias_base + (uint32_t)ew * 512u;                  // 128 floats
+        const bool relu = (p.flags & SEG_RELU) != 0;
+        // read-back mapping: PL lanes cover the 16-byte pieces of one row, 32 / PL rows per instruction
+        const int cpr = wcols >> 3;
+        int PL = 1;
+        while (PL < cpr) PL <<= 1;
+        const int rb_piece = lane & (PL - 1), rb_sub = lane / PL, rb_rows = 32 / PL;
+        int it = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
+            const int nt = t % p.n_tiles, mt = t / p.n_tiles;
+            const int n_img = mt / tpi, trem = mt - n_img * tpi;
+            const int ty = trem / p.tiles_x, tx = trem - ty * p.tiles_x;
+            const int n0 = nt * p.BN + wc0;             // first fused-N column of this warp
+            const int m = q * 32 + lane;                // accumulator row
+            const int py = m / p.PW, px = m - py * p.PW;
+            const int oh = ty * p.BH + py, ow = tx * p.BW + px;
+            const bool valid = (py < p.BH) && (px < p.BW) && (oh < p.H) && (ow < p.W);
+            const int pix_in_img = valid ? oh * p.W + ow : -1;
+            // bias of this warp's columns -> shared memory (overlaps the wait for the accumulator)
+            if (wcols > 0) {
+                for (int j = lane; j < wcols; j += 32)
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(my_bias + 4u * j), "f"(__ldg(p.bias + n0 + j)) : "memory");
+            }
+            const float* gbias = nullptr;               // border pixels of the first convolution: per-class bias
+            if (p.bias_tab && valid) {
+                const int cls = border_class(oh, p.H, p.bt_lo_h, p.bt_hi_h) * (p.bt_lo_w + p.bt_hi_w + 1) +
+                                border_class(ow, p.W, p.bt_lo_w, p.bt_hi_w);
+                if (cls != p.bt_interior) gbias = p.bias_tab + (size_t)cls * p.bt_ld + n0;
+            }
+            // destination of this lane's read-back piece (loop invariant over the rows)
+            bf16* rb_out = nullptr;
+            size_t rb_ld = 0;
+            if (!(p.flags & SEG_DIRECT) && rb_piece < cpr) {
+                const int col = n0 + rb_piece * 8;
+                int si = 0;
+#pragma unroll
+                for (int s = 1; s < 4; ++s)
+                    if (s < p.nseg && col >= p.seg[s].col0) si = s;
+                const int cl = col - p.seg[si].col0;
+                if (cl < p.seg[si].ncols) {
+                    rb_ld = (size_t)p.seg[si].ldo;
+                    rb_out = static_cast<bf16*>(p.seg[si].out) + (size_t)n_img * HW * rb_ld + cl;
+                }
+            }
+            __syncwarp();
+            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 0);
+            mbar_wait_sleep(tfull0 + 8u * acc, aphase);
+            fence_after();
+            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 1);
+            const uint32_t trow = tmem_base + acc * p.acc_stride + ((uint32_t)(q * 32) << 16) + (uint32_t)wc0;
+            for (int c = 0; c < wcols; c += 32) {
+                uint32_t r[32];
+                const bool two = c + 32 <= wcols;
+                if (two) tmem_ld32(trow + (uint32_t)c, r);
+                else tmem_ld16(trow + (uint32_t)c, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    if (g >= 2 && !two) break;
+                    float v[8];
+#pragma unroll
+                    for (int j4 = 0; j4 < 2; ++j4) {
+                        float4 b;
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                                     : "r"(my_bias + 4u * (uint32_t)(c + 8 * g + 4 * j4)));
+                        if (gbias) {
+                            const float* gb = gbias + c + 8 * g + 4 * j4;
+                            b.x = __ldg(gb); b.y = __ldg(gb + 1); b.z = __ldg(gb + 2); b.w = __ldg(gb + 3);
+                        }
+                        v[4 * j4 + 0] = __uint_as_float(r[8 * g + 4 * j4 + 0]) + b.x;
+                        v[4 * j4 + 1] = __uint_as_float(r[8 * g + 4 * j4 + 1]) + b.y;
+                        v[4 * j4 + 2] = __uint_as_float(r[8 * g + 4 * j4 + 2]) + b.z;
+                        v[4 * j4 + 3] = __uint_as_float(r[8 * g + 4 * j4 + 3]) + b.w;
+                    }
+                    if (relu) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+                    }
+                    if (p.flags & SEG_DIRECT) {
+                        // fp32 heads: NCHW float32 straight from registers (lanes = consecutive pixels)
+                        const int colh = n0 + c + 8 * g;
+                        int si = 0;
+#pragma unroll
+                        for (int s = 1; s < 4; ++s)
+                            if (s < p.nseg && colh >= p.seg[s].col0) si = s;
+                        if (valid) {
+                            const bool sig = (p.seg[si].flags & SEG_SIGMOID) != 0;
+                            float* o = static_cast<float*>(p.seg[si].out) + (size_t)n_img * p.seg[si].ldo * HW + pix_in_img;
+                            const int cl = colh - p.seg[si].col0, nc = p.seg[si].ncols;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (cl + j < nc) o[(size_t)(cl + j) * HW] = sig ? 1.f / (1.f + expf(-v[j])) : v[j];
+                        }
+                    } else {
+                        uint4 pk;
+                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                        const uint32_t piece = (uint32_t)((c >> 3) + g);
+                        const uint32_t phys = (piece & ~7u) | ((piece ^ (uint32_t)lane) & 7u);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + phys * 16u), "r"(pk.x), "r"(pk.y),
+                                     "r"(pk.z), "r"(pk.w)
+                                     : "memory");
+                    }
+                }
+            }
+            // the accumulator has left TMEM: hand the buffer back to the MMA warp
+            fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 2);
+            // coalesced read-back: PL consecutive lanes = consecutive 16-byte pieces of one pixel
+            if (!(p.flags & SEG_DIRECT)) {
+                for (int i = 0; i < PL; ++i) {
+                    const int row = i * rb_rows + rb_sub;
+                    const int rv = __shfl_sync(0xffffffffu, pix_in_img, row);
+                    if (rb_out != nullptr && rv >= 0) {
+                        const uint32_t phys = ((uint32_t)rb_piece & ~7u) | (((uint32_t)rb_piece ^ (uint32_t)row) & 7u);
+                        uint4 pk;
+                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(pk.x), "=r"(pk.y), "=r"(pk.z), "=r"(pk.w)
+                                     : "r"(my_stage + (uint32_t)row * p.row_bytes + phys * 16u));
+                        *reinterpret_cast<uint4*>(rb_out + (size_t)rv * rb_ld) = pk;
+                    }
+                }
+            }
+            __syncwarp();
+            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 3);
+        }
+    }
+    __syncthreads();
+    if (warp == kTcMmaWarp) {
+        fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+    }
+}
+
+}  // namespace fcnod

@@ -30,6 +30,7 @@
 #include "common.cuh"
 #include "conv_simt.cuh"
 #include "conv_tc.cuh"
+#include "conv_tc2.cuh"
 #include "elementwise.cuh"
 #include "fused_pool.cuh"
 #include "kernels.h"
@@ -91,6 +92,7 @@ struct ConvWeights {
     bf16* d_w_tc = 0;
     float* d_bias = 0;         // padded
     int CK = 0, n_cchunks = 0, BN = 0, n_tiles = 0;
+    bool halo = false;         // k x k taps served from one shared-memory patch per channel chunk (conv_tc2.cuh)
     // space-to-depth form of a stride-2 convolution on the (Power-transformed) network input
     bool s2d = false;
     int ka = 0;                // taps per axis after space-to-depth (padded to 1/2/4)
@@ -115,11 +117,13 @@ struct Step {
     bool s2d_overlap = false;  // one K-block per kernel row (overlapping-window tensor map) vs one per tap
     bool relu = false;
     int unary_op = 0;
-    // TC state (rebuilt on reshape)
+    // tensor-core convolution: output segments (one per fused convolution) + launch state (rebuilt on reshape)
+    struct Seg { int blob; int direct_blob; int col0, ncols, flags; std::string name; };
+    std::vector<Seg> segs;
     CUtensorMap tmap_a, tmap_b;
-    ConvTcParams tc;
+    ConvTc2Params tc;
     size_t tc_smem = 0;
-    dim3 tc_grid;
+    int tc_grid = 0;
 };
 
 }  // namespace
@@ -264,7 +268,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             const Shape si = shp[L.bottom[0]], so = shp[Cn.top[0]];
             if (L.type == L_POWER && L.bottom[0] == def.input_name && L.power == 1.f && Cn.type == L_CONV && Cn.stride == 2 &&
                 4 * si.C <= kS2dCpad && si.H % 2 == 0 && si.W % 2 == 0 && so.H == si.H / 2 && so.W == si.W / 2 &&
-                so.W >= 8) {
+                so.W >= 8 && Cn.num_output % 8 == 0) {
                 const int q = Cn.pad + (Cn.pad & 1);
                 const int ka = (q - Cn.pad + Cn.kernel + 1) / 2;
                 if (ka <= 4) { s2d_conv[ci] = (int)i; s2d_power[(int)i] = ci; virt.insert(top); }
@@ -320,6 +324,93 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             if (all) d = DT_F32;
         }
         dt[nm] = d;
+    }
+
+    // ---- pass 2b: tensor-core eligibility, horizontal groups, directly written heads (bf16 plan)
+    std::map<std::string, std::string> drop_alias;
+    for (size_t i = 0; i < def.layers.size(); ++i)
+        if (def.layers[i].type == L_DROPOUT && def.layers[i].bottom[0] != def.layers[i].top[0])
+            drop_alias[def.layers[i].top[0]] = def.layers[i].bottom[0];
+    struct SliceOf {
+        std::map<std::string, Alias>& alias; std::map<std::string, std::string>& drop; std::map<std::string, Shape>& shp;
+        void operator()(std::string nm, int& off, int& ldc, std::string& root) const {
+            off = 0;
+            for (;;) {
+                if (drop.count(nm)) nm = drop[nm];
+                else if (alias.count(nm)) { off += alias[nm].off; nm = alias[nm].root; }
+                else break;
+            }
+            ldc = shp[nm].C; root = nm;
+        }
+    } slice_of = {alias, drop_alias, shp};
+    std::map<int, int> sig_of;                   // conv layer -> Sigmoid layer folded into its epilogue
+    std::map<int, std::string> direct_blob;      // conv layer -> network output it writes as NCHW float32
+    std::set<int> sig_fused;                     // Sigmoid layers folded away
+    std::set<std::string> direct_outputs;        // outputs that need no export step
+    std::map<int, std::vector<int> > group;      // leader conv layer -> all members (leader first)
+    std::map<int, int> group_leader;             // non-leader member -> leader
+    std::set<int> tc_layers;                     // conv layers that run on tcgen05
+    if (bf) {
+        for (size_t i = 0; i < def.layers.size(); ++i) {
+            const LayerDef& L = def.layers[i];
+            if (L.type != L_CONV) continue;
+            const std::string& top = L.top[0];
+            if (s2d_conv.count((int)i)) { tc_layers.insert((int)i); continue; }
+            if (L.stride != 1 || 2 * L.pad != L.kernel - 1) continue;
+            if (L.bottom[0] == def.input_name || virt.count(L.bottom[0]) || dt[L.bottom[0]] != DT_BF16) continue;
+            int off, ldc; std::string root;
+            slice_of(L.bottom[0], off, ldc, root);
+            if (shp[L.bottom[0]].C % 8 || off % 8 || ldc % 8) continue;
+            // heads: a convolution that is a network output, or feeds only a Sigmoid that is one
+            const bool relu_only = !inplace_ops.count(top) ||
+                                   (inplace_ops[top] == 1 && i + 1 < def.layers.size() && def.layers[i + 1].type == L_RELU &&
+                                    def.layers[i + 1].top[0] == top);
+            if (fuse && relu_only && outputs.count(top)) {
+                direct_blob[(int)i] = top;
+            } else if (fuse && !inplace_ops.count(top) && consumers.count(top) && consumers[top].size() == 1) {
+                const LayerDef& S = def.layers[consumers[top][0]];
+                if (S.type == L_SIGMOID && S.top[0] != top && outputs.count(S.top[0]) && !inplace_ops.count(S.top[0])) {
+                    sig_of[(int)i] = consumers[top][0];
+                    direct_blob[(int)i] = S.top[0];
+                }
+            }
+            if (!direct_blob.count((int)i)) {
+                if (dt[top] != DT_BF16) continue;            // fp32 NHWC outputs stay on the SIMT kernel (unfused plan only)
+                slice_of(top, off, ldc, root);
+                if (shp[top].C % 8 || off % 8 || ldc % 8) continue;
+            }
+            tc_layers.insert((int)i);
+        }
+        for (std::map<int, int>::iterator it = sig_of.begin(); it != sig_of.end(); ++it) {
+            sig_fused.insert(it->second);
+            virt.insert(def.layers[it->first].top[0]);
+        }
+        for (std::map<int, std::string>::iterator it = direct_blob.begin(); it != direct_blob.end(); ++it)
+            direct_outputs.insert(it->second);
+        if (fuse) {
+            for (std::set<int>::iterator it = tc_layers.begin(); it != tc_layers.end(); ++it) {
+                const int i = *it;
+                if (group_leader.count(i) || s2d_conv.count(i)) continue;
+                const LayerDef& L = def.layers[i];
+                std::vector<int> mem(1, i);
+                for (std::set<int>::iterator jt = tc_layers.upper_bound(i); jt != tc_layers.end() && mem.size() < 4; ++jt) {
+                    const LayerDef& M = def.layers[*jt];
+                    if (group_leader.count(*jt) || group.count(*jt) || s2d_conv.count(*jt)) continue;
+                    if (M.bottom[0] != L.bottom[0] || M.kernel != L.kernel || M.pad != L.pad) continue;
+                    if (direct_blob.count(*jt) != direct_blob.count(i)) continue;
+                    {   // the epilogue applies one ReLU flag to the whole launch
+                        const bool ri = (size_t)i + 1 < def.layers.size() && def.layers[i + 1].type == L_RELU && def.layers[i + 1].top[0] == L.top[0];
+                        const bool rj = (size_t)*jt + 1 < def.layers.size() && def.layers[*jt + 1].type == L_RELU && def.layers[*jt + 1].top[0] == M.top[0];
+                        if (ri != rj) continue;
+                    }
+                    mem.push_back(*jt);
+                }
+                if (mem.size() > 1) {
+                    group[i] = mem;
+                    for (size_t m = 1; m < mem.size(); ++m) group_leader[mem[m]] = i;
+                }
+            }
+        }
     }
 
     // ---- create blobs + buffers in definition order
@@ -396,35 +487,54 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_CONV: {
+                if (group_leader.count((int)i)) break;      // emitted with its group leader
                 st.in = blob_id(net, L.bottom[0]);
                 const bool is_s2d = s2d_conv.count((int)i) > 0;
+                const bool tc_ok = tc_layers.count((int)i) > 0;
                 FCNOD_CHECK(is_s2d || net->blobs[st.in].buf >= 0, "Convolution directly on the NCHW input is not supported; insert a Power layer ('" + L.name + "')");
-                st.out = mk.make(top);
-                // fuse a directly following in-place ReLU
-                if (i + 1 < def.layers.size() && def.layers[i + 1].type == L_RELU && def.layers[i + 1].bottom[0] == top &&
-                    def.layers[i + 1].top[0] == top)
-                    st.relu = true;
-                WeightMap::const_iterator wi = weights.find(L.name);
-                FCNOD_CHECK(wi != weights.end(), "caffemodel has no blobs for layer '" + L.name + "'");
-                const std::vector<HostBlob>& wb = wi->second;
-                const Blob& ib = net->blobs[st.in];
-                ConvWeights cw; cw.Cout = L.num_output; cw.Cin = ib.C; cw.k = L.kernel;
-                size_t wn = (size_t)cw.Cout * cw.Cin * cw.k * cw.k;
-                FCNOD_CHECK(wb.size() >= 1 && wb[0].data.size() == wn, "weight blob of '" + L.name + "' has the wrong size");
-                cw.w = wb[0].data;
-                if (L.bias_term) {
-                    FCNOD_CHECK(wb.size() >= 2 && wb[1].data.size() == (size_t)cw.Cout, "bias blob of '" + L.name + "' has the wrong size");
-                    cw.b = wb[1].data;
-                } else cw.b.assign(cw.Cout, 0.f);
-                const Blob& ob = net->blobs[st.out];
-                bool tc_ok = bf && L.stride == 1 && 2 * L.pad == L.kernel - 1 && ib.dtype == DT_BF16 && ib.C % 8 == 0 &&
-                             ib.ldc % 8 == 0 && ib.c_off % 8 == 0 &&
-                             (ob.dtype == DT_F32 || (ob.ldc % 8 == 0 && ob.c_off % 8 == 0));
-                cw.stride = L.stride; cw.pad = L.pad;
+                std::vector<int> members(1, (int)i);
+                if (group.count((int)i)) members = group[(int)i];
+                const int Cin = net->blobs[st.in].C;
+                ConvWeights cw; cw.Cin = Cin; cw.k = L.kernel; cw.stride = L.stride; cw.pad = L.pad; cw.Cout = 0;
+                std::string names;
+                for (size_t m = 0; m < members.size(); ++m) {
+                    const int li = members[m];
+                    const LayerDef& M = def.layers[li];
+                    const std::string& mtop = M.top[0];
+                    const bool relu = (size_t)li + 1 < def.layers.size() && def.layers[li + 1].type == L_RELU &&
+                                      def.layers[li + 1].bottom[0] == mtop && def.layers[li + 1].top[0] == mtop;
+                    WeightMap::const_iterator wi = weights.find(M.name);
+                    FCNOD_CHECK(wi != weights.end(), "caffemodel has no blobs for layer '" + M.name + "'");
+                    const std::vector<HostBlob>& wb = wi->second;
+                    const size_t per = (size_t)Cin * cw.k * cw.k, wn = (size_t)M.num_output * per;
+                    FCNOD_CHECK(wb.size() >= 1 && wb[0].data.size() == wn, "weight blob of '" + M.name + "' has the wrong size");
+                    if (M.bias_term)
+                        FCNOD_CHECK(wb.size() >= 2 && wb[1].data.size() == (size_t)M.num_output, "bias blob of '" + M.name + "' has the wrong size");
+                    Step::Seg sg;
+                    sg.name = M.name;
+                    sg.blob = mk.make(mtop);
+                    sg.direct_blob = -1;
+                    sg.col0 = (cw.Cout + 7) / 8 * 8;
+                    sg.ncols = M.num_output;
+                    sg.flags = relu ? SEG_RELU : 0;
+                    if (direct_blob.count(li)) {
+                        sg.direct_blob = mk.make(direct_blob[li]);
+                        sg.flags |= SEG_DIRECT;
+                        if (sig_of.count(li)) sg.flags |= SEG_SIGMOID;
+                    }
+                    cw.w.resize((size_t)sg.col0 * per, 0.f);
+                    cw.b.resize(sg.col0, 0.f);
+                    cw.w.insert(cw.w.end(), wb[0].data.begin(), wb[0].data.end());
+                    if (M.bias_term) cw.b.insert(cw.b.end(), wb[1].data.begin(), wb[1].data.end());
+                    else cw.b.resize(sg.col0 + M.num_output, 0.f);
+                    cw.Cout = sg.col0 + M.num_output;
+                    st.segs.push_back(sg);
+                    names += (m ? " + " : "") + M.name;
+                }
+                st.out = st.segs[0].blob;
+                st.relu = (st.segs[0].flags & SEG_RELU) != 0;
                 if (is_s2d) {
                     const LayerDef& P = def.layers[s2d_conv[(int)i]];
-                    tc_ok = ob.dtype == DT_F32 || (ob.ldc % 8 == 0 && ob.c_off % 8 == 0);
-                    FCNOD_CHECK(tc_ok, "space-to-depth convolution '" + L.name + "': output slice is not 16-byte aligned");
                     cw.s2d = true; cw.in_scale = P.scale; cw.in_shift = P.shift;
                     cw.q = L.pad + (L.pad & 1);
                     int ka = (cw.q - L.pad + L.kernel + 1) / 2;
@@ -438,12 +548,22 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                     st.s2d_overlap = true;
                 }
                 st.kind = tc_ok ? S_CONV_TC : S_CONV_SIMT;
-                if (tc_ok) choose_tc_tiling(cw);
+                if (tc_ok) {
+                    choose_tc_tiling(cw);
+                    for (size_t m = 0; m < st.segs.size(); ++m) {
+                        if (st.segs[m].flags & SEG_DIRECT) continue;
+                        const Blob& sb = net->blobs[st.segs[m].blob];
+                        FCNOD_CHECK(sb.dtype == DT_BF16 && sb.C % 8 == 0 && sb.ldc % 8 == 0 && sb.c_off % 8 == 0,
+                                    "tensor-core convolution '" + st.segs[m].name + "': output slice is not bf16 / 16-byte aligned");
+                    }
+                }
                 net->convs.push_back(cw);
                 st.conv = (int)net->convs.size() - 1;
                 std::ostringstream d;
-                d << (tc_ok ? "conv_tc " : "conv_simt ") << L.name << " " << L.kernel << "x" << L.kernel << "/" << L.stride
+                d << (tc_ok ? "conv_tc " : "conv_simt ") << names << " " << L.kernel << "x" << L.kernel << "/" << L.stride
                   << " Cin=" << cw.Cin << " Cout=" << cw.Cout << (st.relu ? " +relu" : "") << (is_s2d ? " +s2d+power" : "");
+                for (size_t m = 0; m < st.segs.size(); ++m)
+                    if (st.segs[m].flags & SEG_DIRECT) d << ((st.segs[m].flags & SEG_SIGMOID) ? " +sigmoid" : "") << " +nchw";
                 st.desc = d.str();
                 net->steps.push_back(st);
                 break;
@@ -457,6 +577,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_SIGMOID: {
+                if (sig_fused.count((int)i)) { mk.make(top); break; }     // folded into the producing convolution
                 st.kind = S_UNARY; st.unary_op = 1; st.in = blob_id(net, L.bottom[0]); st.out = mk.make(top);
                 st.desc = "sigmoid " + L.name;
                 net->steps.push_back(st);
@@ -519,72 +640,129 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
         if (net->blobs[i].is_output) {
             net->blobs[i].out_index = (int)net->outputs.size();
             net->outputs.push_back((int)i);
+            if (direct_outputs.count(net->blobs[i].name)) continue;   // written as NCHW float32 by its convolution
             Step st; st.kind = S_EXPORT; st.in = (int)i; st.desc = "export " + net->blobs[i].name;
             net->steps.push_back(st);
         }
 }
 
 // ------------------------------------------------------------------------------------ tcgen05 tiling (host only)
+const size_t kTcSmemBudget = 225 * 1024;
+
+// K layout of the packed weights (independent of the batch): channel-chunk width, HALO mode.
 void choose_tc_tiling(ConvWeights& cw) {
-    cw.n_tiles = (cw.Cout + 127) / 128;
-    cw.BN = ((cw.Cout + cw.n_tiles - 1) / cw.n_tiles + 15) / 16 * 16;
     if (cw.s2d) {   // K-block = one kernel row of ka taps x 16 channels (or one tap, see setup_tc_step)
         cw.CK = cw.ka * kS2dCpad;
         cw.n_cchunks = 1;
+        cw.halo = false;
         return;
     }
-    // K-block width: minimise padded K with a small per-block cost
-    int best = 64; long best_cost = -1;
-    const int cand[3] = {64, 32, 16};
-    for (int i = 0; i < 3; ++i) {
-        int ck = cand[i];
-        long cost = (long)((cw.Cin + ck - 1) / ck) * (ck + 8);
-        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = ck; }
+    const char* nh = getenv("FCNOD_NO_HALO");
+    cw.halo = cw.k > 1 && !(nh && nh[0] == '1');
+    if (cw.halo) {
+        cw.CK = 64;     // HALO mode shifts the A descriptor by whole 128-byte rows: SWIZZLE_128B only
+    } else {
+        // K-block width: minimise padded K with a small per-block cost
+        int best = 64; long best_cost = -1;
+        const int cand[3] = {64, 32, 16};
+        for (int i = 0; i < 3; ++i) {
+            int ck = cand[i];
+            long cost = (long)((cw.Cin + ck - 1) / ck) * (ck + 8);
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = ck; }
+        }
+        cw.CK = best;
     }
-    cw.CK = best;
     cw.n_cchunks = (cw.Cin + cw.CK - 1) / cw.CK;
 }
 
+// Everything of ConvTc2Params that does not need device pointers: pixel box, N tiling, pipeline depth.
 void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
-    const LayerDef& L = net->def.layers[st.layer];
     const ConvWeights& cw = net->convs[st.conv];
-    const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
-    ConvTcParams& p = st.tc;
+    ConvTc2Params& p = st.tc;
     memset(&p, 0, sizeof(p));
     p.H = ob.H; p.W = ob.W;     // == input size for the stride-1 "same" convolutions; == s2d image size for s2d
-    p.Cout = cw.Cout; p.ldo = ob.ldc;
-    p.kh = p.kw = cw.k; p.pad_h = p.pad_w = L.pad;
+    p.kh = p.kw = cw.k; p.pad_h = p.pad_w = cw.pad;
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
-    int ck = cw.CK;
+    p.halo = cw.halo ? 1 : 0;
     if (cw.s2d) {
-        if (st.s2d_overlap) { p.kh = cw.ka; p.kw = 1; ck = cw.ka * kS2dCpad; }
-        else { p.kh = p.kw = cw.ka; ck = kS2dCpad; }
-        p.CK = ck; p.n_cchunks = 1;
+        if (st.s2d_overlap) { p.kh = cw.ka; p.kw = 1; p.CK = cw.ka * kS2dCpad; }
+        else { p.kh = p.kw = cw.ka; p.CK = kS2dCpad; }
+        p.n_cchunks = 1;
         p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
         p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
-        p.bt_ld = cw.n_tiles * cw.BN;
     }
-    // pixel box: the fewest boxes per row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
-    p.BW = ceil_div(ob.W, ceil_div(ob.W, 128));
-    p.BH = std::max(1, std::min(ob.H, 128 / p.BW));
+    const uint32_t span = p.CK * 2;
+    // pixel box: the fewest boxes per image row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
+    const int halo_w = p.halo ? p.kw - 1 : 0, halo_h = p.halo ? p.kh - 1 : 0;
+    const int bw_max = 128 - halo_w;
+    p.BW = ceil_div(ob.W, ceil_div(ob.W, bw_max));
+    p.PW = p.BW + halo_w;
+    p.BH = std::max(1, std::min(ob.H, 128 / p.PW));
     p.tiles_x = ceil_div(ob.W, p.BW);
     p.tiles_y = ceil_div(ob.H, p.BH);
-    p.BN = cw.BN;
-    p.relu = st.relu ? 1 : 0;
-    p.out_fp32 = ob.dtype == DT_F32;
-    uint32_t cols = 32;
-    while ((int)cols < p.BN) cols <<= 1;
-    p.tmem_cols = cols;
-    const uint32_t span = ck * 2;
-    const size_t stage_bytes = 128 * span + align_up((size_t)p.BN * span, 1024);
-    const int KB = p.kh * p.kw * p.n_cchunks;
-    int stages = (int)(96 * 1024 / stage_bytes);
-    stages = std::max(2, std::min(stages, 8));
-    stages = std::min(stages, std::max(2, KB));
-    p.stages = stages;
-    st.tc_smem = stages * stage_bytes + 16 * stages + 16 + 1024;
-    st.tc_grid = dim3(p.tiles_x * p.tiles_y * batch, cw.n_tiles, 1);
+    p.m_tiles = p.tiles_x * p.tiles_y * batch;
+    const int taps = p.kh * p.kw;
+    const int Kp = taps * p.n_cchunks * p.CK;
+    if (p.halo) {
+        p.a_tx_bytes = (uint32_t)(p.PW * (p.BH + halo_h)) * span;
+        const int rows = std::max(128 + halo_h * p.PW + halo_w, p.PW * (p.BH + halo_h));
+        p.a_stage_bytes = (uint32_t)align_up((size_t)rows * span, 1024);
+    } else {
+        p.a_tx_bytes = (uint32_t)(p.BW * p.BH) * span;
+        p.a_stage_bytes = 128 * span;
+    }
+    // N tiling: the candidate with the smallest modelled time that fits in shared memory.
+    //   tile time = max(MMA issue, L2->smem bytes, epilogue) + fixed;  total = rounds over 148 persistent CTAs
+    const int N8 = (cw.Cout + 7) / 8 * 8;
+    double best_cost = -1;
+    for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
+        const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
+        if (BN > 256 || nt * BN - N8 >= BN) continue;
+        const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024);
+        const int half0 = ceil_div(BN, 32) * 16;
+        const uint32_t row_bytes = (uint32_t)align_up((size_t)half0 * 2, 128);
+        const size_t fixed = 8 * 32 * (size_t)row_bytes + 8 * 512 + 512 + 1024;
+        int a_st, b_st;
+        if (p.halo) {
+            a_st = 2;      // the next tile's patch loads while this one is multiplied
+            if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
+            if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
+            b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
+        } else {
+            const size_t pair = (size_t)p.a_stage_bytes + b_stage;
+            if (fixed + 2 * pair > kTcSmemBudget) continue;
+            a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
+        }
+        const double mma = (Kp / 16.0) * std::max(BN / 2.0, 32.0);
+        const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
+        const double load = (a_bytes + (double)BN * Kp * 2) / 48.0;
+        const double epi = 10.0 * BN;
+        const double tile = std::max(mma, std::max(load, epi)) + 500.0;
+        const long rounds = ((long)p.m_tiles * nt + kNumSMs - 1) / kNumSMs;
+        const double cost = rounds * tile;
+        if (best_cost < 0 || cost < best_cost) {
+            best_cost = cost;
+            p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st;
+            p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
+        }
+    }
+    FCNOD_CHECK(best_cost >= 0, "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
+    uint32_t acc = 32;
+    while ((int)acc < p.BN) acc <<= 1;
+    p.acc_stride = acc;
+    p.tmem_cols = std::max<uint32_t>(2 * acc, 32);
+    p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
+    st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 8 * 32 * (size_t)p.row_bytes +
+                 8 * 512 + 512 + 1024;
+    st.tc_grid = std::min(p.m_tiles * p.n_tiles, kNumSMs);
+    p.nseg = (int)st.segs.size();
+    p.flags = st.segs[0].flags & (SEG_RELU | SEG_DIRECT);
+    p.bt_interior = cw.bt_lo_h * (cw.bt_lo_w + cw.bt_hi_w + 1) + cw.bt_lo_w;
+    for (int i = 0; i < p.nseg; ++i) {
+        FCNOD_CHECK((st.segs[i].flags & (SEG_RELU | SEG_DIRECT)) == p.flags, "internal: fused convolutions disagree on ReLU / direct output");
+        p.seg[i].col0 = st.segs[i].col0; p.seg[i].ncols = st.segs[i].ncols; p.seg[i].flags = st.segs[i].flags;
+    }
 }
 
 // ------------------------------------------------------------------------------------ weights
@@ -595,6 +773,7 @@ void upload_weights(fcnod_net* net) {
         ConvWeights& cw = net->convs[st.conv];
         const int k = cw.k, Cin = cw.Cin, Cout = cw.Cout;
         if (st.kind == S_CONV_SIMT) {
+            FCNOD_CHECK(st.segs.size() == 1, "internal: grouped convolution on the SIMT path");
             cw.ldw = (Cout + 63) / 64 * 64;
             const int K = k * k * Cin;
             std::vector<float> w((size_t)K * cw.ldw, 0.f);
@@ -614,8 +793,9 @@ void upload_weights(fcnod_net* net) {
             // 2x2 space-to-depth image:  ih = 2*oh - pad + r,  r = 2*a + dy - (q - pad),  q = pad rounded up to even.
             // GEMM weights = in_scale * w (bf16); the Power shift goes into the border-aware bias table
             // bias[class(oh)][class(ow)][o] = b[o] + in_shift * sum over the taps that fall INSIDE the image.
-            const int ka = cw.ka, off = cw.q - cw.pad, Kp = ka * ka * kS2dCpad, Np = cw.n_tiles * cw.BN;
-            std::vector<bf16> w((size_t)Np * Kp, __float2bfloat16(0.f));
+            const int ka = cw.ka, off = cw.q - cw.pad, Kp = ka * ka * kS2dCpad;
+            const int Nrows = (Cout + 15) / 16 * 16, Np = (int)align_up((size_t)(Cout + 7) / 8 * 8, 256) + 256;
+            std::vector<bf16> w((size_t)Nrows * Kp, __float2bfloat16(0.f));
             for (int o = 0; o < Cout; ++o)
                 for (int ah = 0; ah < ka; ++ah)
                     for (int aw = 0; aw < ka; ++aw)
@@ -670,8 +850,9 @@ void upload_weights(fcnod_net* net) {
             FCNOD_CUDA(cudaMalloc(&cw.d_bias_tab, tab.size() * 4));
             FCNOD_CUDA(cudaMemcpy(cw.d_bias_tab, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
         } else {
-            const int Kp = k * k * cw.n_cchunks * cw.CK, Np = cw.n_tiles * cw.BN;
-            std::vector<bf16> w((size_t)Np * Kp, __float2bfloat16(0.f));
+            const int Kp = k * k * cw.n_cchunks * cw.CK;
+            const int Nrows = (Cout + 15) / 16 * 16, Np = (int)align_up((size_t)(Cout + 7) / 8 * 8, 256) + 256;
+            std::vector<bf16> w((size_t)Nrows * Kp, __float2bfloat16(0.f));
             for (int o = 0; o < Cout; ++o)
                 for (int c = 0; c < Cin; ++c)
                     for (int r = 0; r < k; ++r)
@@ -719,12 +900,33 @@ CUresult encode_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims
                               CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 
+void bind_tc_pointers(fcnod_net* net, Step& st) {
+    ConvWeights& cw = net->convs[st.conv];
+    ConvTc2Params& p = st.tc;
+    p.bias = cw.d_bias_tab ? cw.d_bias_tab + (size_t)p.bt_interior * p.bt_ld : cw.d_bias;
+    p.bias_tab = cw.d_bias_tab;
+    for (size_t i = 0; i < st.segs.size(); ++i) {
+        const Step::Seg& sg = st.segs[i];
+        if (sg.flags & SEG_DIRECT) {
+            const Blob& ob = net->blobs[sg.direct_blob];
+            FCNOD_CHECK(ob.out_index >= 0, "internal: direct segment without an output slot");
+            p.seg[i].out = net->out_dev[ob.out_index];
+            p.seg[i].ldo = ob.C;
+        } else {
+            const Blob& ob = net->blobs[sg.blob];
+            p.seg[i].out = view_ptr(net, ob);
+            p.seg[i].ldo = ob.ldc;
+        }
+    }
+}
+
 void setup_tc_step(fcnod_net* net, Step& st) {
     const LayerDef& L = net->def.layers[st.layer];
     ConvWeights& cw = net->convs[st.conv];
     const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
     const int B = net->batch;
+    const int Nrows = (cw.Cout + 15) / 16 * 16;
     if (cw.s2d) {
         // A = the W-padded space-to-depth image [B][H2][Wp][16] bf16.  Preferred: ONE K-block per kernel row,
         // its A rows being the 128-byte windows of ka consecutive pixels (an overlapping-stride tensor map:
@@ -737,7 +939,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         st.s2d_overlap = !(force && force[0] == '1');
         for (int attempt = 0; attempt < 2; ++attempt) {
             fill_tc_geometry(net, st, B);
-            ConvTcParams& p = st.tc;
+            ConvTc2Params& p = st.tc;
             const uint32_t span = p.CK * 2;
             cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)(st.s2d_overlap ? W2 : Wp), (cuuint64_t)H2, (cuuint64_t)B};
             cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
@@ -746,43 +948,45 @@ void setup_tc_step(fcnod_net* net, Step& st) {
             if (r != CUDA_SUCCESS && st.s2d_overlap) { st.s2d_overlap = false; continue; }
             FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
             const cuuint64_t Kp = (cuuint64_t)cw.ka * cw.ka * kS2dCpad;
-            cuuint64_t bd[2] = {Kp, (cuuint64_t)cw.n_tiles * cw.BN};
+            cuuint64_t bd[2] = {Kp, (cuuint64_t)Nrows};
             cuuint64_t bs[1] = {Kp * 2};
-            cuuint32_t bb[2] = {(cuuint32_t)p.CK, (cuuint32_t)cw.BN};
+            cuuint32_t bb[2] = {(cuuint32_t)p.CK, (cuuint32_t)p.BN};
             r = encode_map(&st.tmap_b, cw.d_w_tc, 2, bd, bs, bb, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
             FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
-            p.out = view_ptr(net, ob);
-            p.bias = cw.d_bias;
-            p.bias_tab = cw.d_bias_tab;
             break;
         }
+        bind_tc_pointers(net, st);
         return;
     }
     fill_tc_geometry(net, st, B);
-    ConvTcParams& p = st.tc;
-    p.out = view_ptr(net, ob);
-    p.bias = cw.d_bias;
+    ConvTc2Params& p = st.tc;
     const uint32_t span = cw.CK * 2;
     {
         cuuint64_t dims[4] = {(cuuint64_t)ib.C, (cuuint64_t)ib.W, (cuuint64_t)ib.H, (cuuint64_t)B};
         cuuint64_t strides[3] = {(cuuint64_t)ib.ldc * 2, (cuuint64_t)ib.W * ib.ldc * 2, (cuuint64_t)ib.H * ib.W * ib.ldc * 2};
-        cuuint32_t box[4] = {(cuuint32_t)cw.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
+        cuuint32_t box[4] = {(cuuint32_t)cw.CK, (cuuint32_t)p.PW, (cuuint32_t)(p.halo ? p.BH + p.kh - 1 : p.BH), 1};
         CUresult r = encode_map(&st.tmap_a, view_ptr(net, ib), 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
     {
         const cuuint64_t Kp = (cuuint64_t)cw.k * cw.k * cw.n_cchunks * cw.CK;
-        cuuint64_t dims[2] = {Kp, (cuuint64_t)cw.n_tiles * cw.BN};
+        cuuint64_t dims[2] = {Kp, (cuuint64_t)Nrows};
         cuuint64_t strides[1] = {Kp * 2};
-        cuuint32_t box[2] = {(cuuint32_t)cw.CK, (cuuint32_t)cw.BN};
+        cuuint32_t box[2] = {(cuuint32_t)cw.CK, (cuuint32_t)p.BN};
         CUresult r = encode_map(&st.tmap_b, cw.d_w_tc, 2, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
+    bind_tc_pointers(net, st);
 }
 
 void reshape(fcnod_net* net, int batch) {
     FCNOD_CHECK(batch > 0, "batch must be positive");
-    FCNOD_CHECK(net->device >= 0, "plan-only handle (device < 0): no compute is possible; there is no CPU fallback");
+    if (net->device < 0) {   // plan-only handle: re-plan the tilings for the new batch (host only)
+        net->batch = batch;
+        for (size_t i = 0; i < net->steps.size(); ++i)
+            if (net->steps[i].kind == S_CONV_TC) fill_tc_geometry(net, net->steps[i], batch);
+        return;
+    }
     require_device(net);
     if (batch == net->batch && !net->buffers.empty() && net->buffers[0].ptr) return;
     FCNOD_CUDA(cudaDeviceSynchronize());
@@ -875,6 +1079,32 @@ void launch_conv_simt(const fcnod_net* net, const Step& st, const LayerDef& L, c
     else conv_simt_kernel<bf16, float><<<grid, 256, 0, s>>>(p);
 }
 
+// the instantiations of the tensor-core convolution: K steps per block (CK / 16) x HALO, + the profiled twins
+template <bool PROF>
+void launch_conv_tc2_p(const Step& st, cudaStream_t s) {
+    const int ks = st.tc.CK / 16;
+    const dim3 g(st.tc_grid), b(kConvTc2Threads);
+    if (st.tc.halo) { FCNOD_CHECK(ks == 4, "HALO mode needs CK = 64"); conv_tc2_kernel<4, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc); }
+    else if (ks == 4) conv_tc2_kernel<4, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    else if (ks == 2) conv_tc2_kernel<2, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    else conv_tc2_kernel<1, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+}
+void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof) {
+    if (prof) launch_conv_tc2_p<true>(st, s);
+    else launch_conv_tc2_p<false>(st, s);
+}
+void conv_tc2_set_smem_limit() {
+    const int lim = 227 * 1024;
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+}
+
 void launch_export(const fcnod_net* net, const Blob& b, float* dst, cudaStream_t s) {
     long total = (long)net->batch * b.C * b.H * b.W;
     int g = grid_for(total, 256);
@@ -928,7 +1158,7 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
         }
         case S_CONV_SIMT: launch_conv_simt(net, st, *L, s); break;
         case S_CONV_TC:
-            conv_tc_kernel<<<st.tc_grid, kConvTcThreads, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+            launch_conv_tc2(st, s, false);
             break;
         case S_POOL:
             if (net->blobs[st.in].dtype == DT_F32) launch_pool<float>(net, st, *L, s);
@@ -1056,7 +1286,7 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     FCNOD_CUDA(cudaGetDeviceProperties(&prop, device));
     FCNOD_CHECK(prop.major == 10, "fcnod_b200 is built for sm_100a (Blackwell B200) only; found sm_" +
                                       std::to_string(prop.major) + std::to_string(prop.minor));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    conv_tc2_set_smem_limit();
     FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
@@ -1125,8 +1355,9 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         o << i << ": " << st.desc;
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
-            o << " [CK=" << cw.CK << " BN=" << cw.BN << "x" << cw.n_tiles << " stages=" << st.tc.stages << " grid=" << st.tc_grid.x
-              << "x" << st.tc_grid.y << " smem=" << st.tc_smem << "]";
+            o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {
             const Blob& b = net->blobs[st.out];
@@ -1204,6 +1435,25 @@ int fcnod_net_run_step(fcnod_net* net, int step, int reps, void* stream) {
     FCNOD_CHECK(net && step >= 0 && step < (int)net->steps.size(), "bad step index");
     require_device(net);
     for (int i = 0; i < reps; ++i) run_step(net, net->steps[step], net->data_dev, (cudaStream_t)stream);
+    FCNOD_API_END
+}
+
+int fcnod_net_profile_conv_step(fcnod_net* net, int step, unsigned long long* out, size_t count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && out && step >= 0 && step < (int)net->steps.size(), "bad step index");
+    FCNOD_CHECK(net->steps[step].kind == S_CONV_TC, "step is not a tensor-core convolution");
+    FCNOD_CHECK(count == 4 * 8 * 64, "profile buffer must hold 4*8*64 values");
+    require_device(net);
+    unsigned long long* d = 0;
+    FCNOD_CUDA(cudaMalloc(&d, count * 8));
+    FCNOD_CUDA(cudaMemset(d, 0, count * 8));
+    Step st = net->steps[step];
+    st.tc.prof = d;
+    launch_conv_tc2(st, net->stream, true);
+    cudaError_t e = cudaStreamSynchronize(net->stream);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d, count * 8, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    FCNOD_CUDA(e);
     FCNOD_API_END
 }
 

@@ -72,6 +72,10 @@ int fcnod_net_blob_read(fcnod_net* net, const char* blob, float* host_out, size_
 int fcnod_net_output_device(fcnod_net* net, const char* blob, const float** dev_ptr);
 /* Run only the n-th planned launch `reps` times (profiling aid). */
 int fcnod_net_run_step(fcnod_net* net, int step, int reps, void* stream);
+/* Profiling aid: run a tensor-core convolution step once and return the clock64 timeline of its CTA 0:
+ * out[4 roles (TMA producer: B-load issue; MMA issuer: B-load landed; first epilogue warp; MMA issuer: tap issued)]
+ * [8 tiles][64 events] (count must be 2048). */
+int fcnod_net_profile_conv_step(fcnod_net* net, int step, unsigned long long* out, size_t count);
 
 /* ---- B2: post-net (threshold -> decode -> groupRectangles -> filter -> rescale) */
 typedef struct fcnod_postnet_params {

@@ -17,6 +17,7 @@ run detect_fp32 300 tests/test_detect_gpu.py -k config1
 for c in k1_c64 k3_c64 k5_c16 k3_c96_sw64 k5_c24 k1_c480 k3_c160_n320 k3_w112 mix_3a odd_hw cin48_k5 big_w; do
   run tc_$c 120 "tests/test_net_gpu.py::test_conv_tc_mini_nets[$c]"
 done
+run stem 300 tests/test_net_gpu.py -k "s2d"
 run net_bf16 600 tests/test_net_gpu.py -k "bf16"
 run detect_bf16 300 tests/test_detect_gpu.py -k bf16
 cat gpurun_out/summary.txt
