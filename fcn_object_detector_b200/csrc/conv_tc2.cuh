@@ -47,6 +47,7 @@ struct ConvTc2Params {
     int bt_lo_h, bt_hi_h, bt_lo_w, bt_hi_w, bt_ld;
     int H, W;
     int kh, kw, pad_h, pad_w, n_cchunks, CK;
+    int ksteps_last;         // 16-wide K steps that hold real channels in the LAST channel chunk (the rest is zero fill)
     int BW, BH, tiles_x, tiles_y;
     int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
     int halo;                // 1 = HALO mode
@@ -92,6 +93,12 @@ __device__ __forceinline__ void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, u
         "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
         ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accum)
         : "memory");
+}
+// tcgen05.wait::ld that also ties the 32 destination registers to the wait, so that no read of them can be
+// scheduled above it
+__device__ __forceinline__ void tmem_ld_wait_dep32(uint32_t* r) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
+    asm volatile("" : "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]) :: "memory");
 }
 // wait with back-off, for the warps that wait long (keeps their spinning out of the issue slots of the TMA / MMA threads)
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
@@ -220,8 +227,11 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
                 uint32_t accum = 0;
                 int ev = 0;
+                int cc = 0;
                 for (int ai = 0; ai < a_iters; ++ai) {
                     mbar_wait(afull0 + 8u * sa, pa);
+                    const int ks = (cc == p.n_cchunks - 1) ? p.ksteps_last : KSTEPS;   // skip all-zero K steps
+                    if (++cc == p.n_cchunks) cc = 0;
                     uint32_t a_row = a_lo;
                     for (int r = 0; r < (HALO ? p.kh : 1); ++r, a_row += row_step) {
                         for (int s = 0; s < (HALO ? p.kw : 1); ++s, ++ev) {
@@ -231,8 +241,10 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             const uint32_t a_tap = a_row + (uint32_t)s * 8u;
 #pragma unroll
                             for (int k = 0; k < KSTEPS; ++k) {
-                                umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_lo + 2u * k, desc_hi, idesc, accum);
-                                accum = 1;
+                                if (k < ks) {
+                                    umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_lo + 2u * k, desc_hi, idesc, accum);
+                                    accum = 1;
+                                }
                             }
                             umma_commit(bempty0 + 8u * sb);
                             if (PROF) FCNOD_PROF(3, it, ev);
@@ -259,6 +271,10 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         const uint32_t my_stage = stage_base + (uint32_t)ew * 32u * p.row_bytes;
         const uint32_t my_row = my_stage + (uint32_t)lane * p.row_bytes;
         const uint32_t my_bias = bias_base + (uint32_t)ew * 512u;                  // 128 floats
+        uint8_t* const smem_gen = smem_raw2 + (smem_base - smem_u32(smem_raw2));    // generic view of smem_base
+        uint8_t* const stage_warp = smem_gen + (my_stage - smem_base);
+        uint8_t* const stage_row = smem_gen + (my_row - smem_base);
+        float* const bias_s = reinterpret_cast<float*>(smem_gen + (my_bias - smem_base));
         const bool relu = (p.flags & SEG_RELU) != 0;
         // read-back mapping: PL lanes cover the 16-byte pieces of one row, 32 / PL rows per instruction
         const int cpr = wcols >> 3;
@@ -279,8 +295,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             const int pix_in_img = valid ? oh * p.W + ow : -1;
             // bias of this warp's columns -> shared memory (overlaps the wait for the accumulator)
             if (wcols > 0) {
-                for (int j = lane; j < wcols; j += 32)
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(my_bias + 4u * j), "f"(__ldg(p.bias + n0 + j)) : "memory");
+                for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);
             }
             const float* gbias = nullptr;               // border pixels of the first convolution: per-class bias
             if (p.bias_tab && valid) {
@@ -309,37 +324,14 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             fence_after();
             if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 1);
             const uint32_t trow = tmem_base + acc * p.acc_stride + ((uint32_t)(q * 32) << 16) + (uint32_t)wc0;
-            for (int c = 0; c < wcols; c += 32) {
-                uint32_t r[32];
-                const bool two = c + 32 <= wcols;
-                if (two) tmem_ld32(trow + (uint32_t)c, r);
-                else tmem_ld16(trow + (uint32_t)c, r);
-                tmem_ld_wait();
+            if (p.flags & SEG_DIRECT) {
+                // ---- fp32 heads: NCHW float32 straight from registers (lanes = consecutive pixels); tiny, kept simple
+                for (int c = 0; c < wcols; c += 16) {
+                    uint32_t r[16];
+                    tmem_ld16(trow + (uint32_t)c, r);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    if (g >= 2 && !two) break;
-                    float v[8];
-#pragma unroll
-                    for (int j4 = 0; j4 < 2; ++j4) {
-                        float4 b;
-                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                     : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-                                     : "r"(my_bias + 4u * (uint32_t)(c + 8 * g + 4 * j4)));
-                        if (gbias) {
-                            const float* gb = gbias + c + 8 * g + 4 * j4;
-                            b.x = __ldg(gb); b.y = __ldg(gb + 1); b.z = __ldg(gb + 2); b.w = __ldg(gb + 3);
-                        }
-                        v[4 * j4 + 0] = __uint_as_float(r[8 * g + 4 * j4 + 0]) + b.x;
-                        v[4 * j4 + 1] = __uint_as_float(r[8 * g + 4 * j4 + 1]) + b.y;
-                        v[4 * j4 + 2] = __uint_as_float(r[8 * g + 4 * j4 + 2]) + b.z;
-                        v[4 * j4 + 3] = __uint_as_float(r[8 * g + 4 * j4 + 3]) + b.w;
-                    }
-                    if (relu) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-                    }
-                    if (p.flags & SEG_DIRECT) {
-                        // fp32 heads: NCHW float32 straight from registers (lanes = consecutive pixels)
+                    for (int g = 0; g < 2; ++g) {
                         const int colh = n0 + c + 8 * g;
                         int si = 0;
 #pragma unroll
@@ -350,38 +342,80 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             float* o = static_cast<float*>(p.seg[si].out) + (size_t)n_img * p.seg[si].ldo * HW + pix_in_img;
                             const int cl = colh - p.seg[si].col0, nc = p.seg[si].ncols;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                if (cl + j < nc) o[(size_t)(cl + j) * HW] = sig ? 1.f / (1.f + expf(-v[j])) : v[j];
+                            for (int j = 0; j < 8; ++j) {
+                                float x = __uint_as_float(r[8 * g + j]) + bias_s[c + 8 * g + j];
+                                if (relu) x = fmaxf(x, 0.f);
+                                if (cl + j < nc) o[(size_t)(cl + j) * HW] = sig ? 1.f / (1.f + expf(-x)) : x;
+                            }
                         }
-                    } else {
-                        uint4 pk;
-                        __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                        const uint32_t piece = (uint32_t)((c >> 3) + g);
-                        const uint32_t phys = (piece & ~7u) | ((piece ^ (uint32_t)lane) & 7u);
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + phys * 16u), "r"(pk.x), "r"(pk.y),
-                                     "r"(pk.z), "r"(pk.w)
-                                     : "memory");
                     }
                 }
-            }
-            // the accumulator has left TMEM: hand the buffer back to the MMA warp
-            fence_before();
-            __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
-            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 2);
-            // coalesced read-back: PL consecutive lanes = consecutive 16-byte pieces of one pixel
-            if (!(p.flags & SEG_DIRECT)) {
+                fence_before();
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+            } else {
+                // ---- bf16 NHWC: drain 32 columns at a time; the TMEM load of the next chunk is in flight while this
+                //      one is biased / packed / staged.  Plain (non-volatile) shared-memory accesses: ptxas schedules them.
+                const bool any_g = __any_sync(0xffffffffu, gbias != nullptr);
+                uint32_t ra[32];
+                if (wcols > 0) {
+                    if (wcols >= 32) tmem_ld32(trow, ra);
+                    else tmem_ld16(trow, ra);
+                }
+                for (int c = 0; c < wcols; c += 32) {
+                    const int ncol = min(32, wcols - c);      // 32 or 16
+                    float bb[32];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 t4 = *reinterpret_cast<const float4*>(bias_s + c + 4 * j);
+                        bb[4 * j] = t4.x; bb[4 * j + 1] = t4.y; bb[4 * j + 2] = t4.z; bb[4 * j + 3] = t4.w;
+                    }
+                    if (any_g && gbias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < ncol) bb[j] = __ldg(gbias + c + j);
+                    }
+                    tmem_ld_wait_dep32(ra);
+                    uint32_t rc[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) rc[j] = ra[j];
+                    const int cn = c + 32;
+                    if (cn < wcols) {
+                        if (cn + 32 <= wcols) tmem_ld32(trow + (uint32_t)cn, ra);
+                        else tmem_ld16(trow + (uint32_t)cn, ra);
+                    }
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        if (8 * g < ncol) {
+                            float v[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                v[j] = __uint_as_float(rc[8 * g + j]) + bb[8 * g + j];
+                                if (relu) v[j] = fmaxf(v[j], 0.f);
+                            }
+                            uint4 pk;
+                            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            const uint32_t piece = (uint32_t)((c >> 3) + g);
+                            const uint32_t phys = (piece & ~7u) | ((piece ^ (uint32_t)lane) & 7u);
+                            *reinterpret_cast<uint4*>(stage_row + phys * 16u) = pk;
+                        }
+                    }
+                }
+                // the accumulator has left TMEM: hand the buffer back to the MMA warp
+                fence_before();
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+                if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 2);
+                // coalesced read-back: PL consecutive lanes = consecutive 16-byte pieces of one pixel
+#pragma unroll 4
                 for (int i = 0; i < PL; ++i) {
                     const int row = i * rb_rows + rb_sub;
                     const int rv = __shfl_sync(0xffffffffu, pix_in_img, row);
                     if (rb_out != nullptr && rv >= 0) {
                         const uint32_t phys = ((uint32_t)rb_piece & ~7u) | (((uint32_t)rb_piece ^ (uint32_t)row) & 7u);
-                        uint4 pk;
-                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                                     : "=r"(pk.x), "=r"(pk.y), "=r"(pk.z), "=r"(pk.w)
-                                     : "r"(my_stage + (uint32_t)row * p.row_bytes + phys * 16u));
+                        const uint4 pk = *reinterpret_cast<const uint4*>(stage_warp + (uint32_t)row * p.row_bytes + phys * 16u);
                         *reinterpret_cast<uint4*>(rb_out + (size_t)rv * rb_ld) = pk;
                     }
                 }

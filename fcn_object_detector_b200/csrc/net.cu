@@ -692,6 +692,8 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
         p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
         p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
     }
+    p.ksteps_last = p.CK / 16;
+    if (!cw.s2d) p.ksteps_last = std::min(p.CK / 16, ceil_div(cw.Cin - (p.n_cchunks - 1) * p.CK, 16));
     const uint32_t span = p.CK * 2;
     // pixel box: the fewest boxes per image row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
     const int halo_w = p.halo ? p.kw - 1 : 0, halo_h = p.halo ? p.kh - 1 : 0;

@@ -13,9 +13,10 @@
 //
 // Kernel 1 (decode_group_kernel): one CTA per (frame, foreground class).  Coverage is read
 //   with coalesced loads, candidates are compacted IN ROW-MAJOR ORDER with warp ballots +
-//   a cross-warp scan, kept in shared memory, clustered there (min-label propagation with
+//   a cross-warp scan, kept in shared memory, clustered there: every SimilarRects pair is tested
+//   once into a shared-memory bit matrix, then min-label propagation over its set bits with
 //   pointer jumping = connected components, class order = smallest member index, exactly
-//   what cv::partition yields), reduced with shared-memory atomics and filtered.
+//   what cv::partition yields; reduced with shared-memory atomics and filtered.
 // Kernel 2 (assemble_kernel): one warp per frame concatenates the per-class lists in
 //   class order and rescales.
 #include <cmath>
@@ -59,16 +60,35 @@ __device__ __forceinline__ int block_scan_flag(bool flag, int* warp_tot /*[8]*/,
     return base + pre;
 }
 
+constexpr int kDeltaTable = 8192;   // T(m) for 0 <= m < 8192 (sum of two box sides); larger m take the FP64 path
+
+// T(m) = floor(eps * m * 0.5), evaluated in double exactly as cv::SimilarRects does
+__global__ void delta_table_kernel(double eps, int* __restrict__ tab) {
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < kDeltaTable) tab[m] = (int)floor(eps * (double)m * 0.5);
+}
+
 __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __restrict__ coverage,
                                                                const float* __restrict__ bboxes, int c_cvg, int c_bbox,
                                                                int gh, int gw, PostParams P,
+                                                               const int* __restrict__ delta_tab,
                                                                int32_t* __restrict__ cls_det /*[B][ncls][MAX_DET][6]*/,
                                                                int32_t* __restrict__ cls_cnt /*[B][ncls]*/) {
     __shared__ int rx[kMaxCand], ry[kMaxCand], rw[kMaxCand], rh[kMaxCand];
     __shared__ int lab[kMaxCand];
-    __shared__ int sx[kMaxCand], sy[kMaxCand], sw[kMaxCand], sh[kMaxCand], cnt[kMaxCand];
     __shared__ int warp_tot[kThreads / 32];
     __shared__ int s_any;
+    // dynamic shared memory, used twice: first the similarity bit matrix [n][words] (words = ceil(gh*gw / 32)),
+    // then (after the partition) the per-class sums / counts / containment margins, 7 arrays of gh*gw ints
+    extern __shared__ unsigned adj[];
+    const int ncell_all = gh * gw;
+    int* const sx = reinterpret_cast<int*>(adj);
+    int* const sy = sx + ncell_all;
+    int* const sw = sy + ncell_all;
+    int* const sh = sw + ncell_all;
+    int* const cnt = sh + ncell_all;
+    int* const dxr = cnt + ncell_all;
+    int* const dyr = dxr + ncell_all;
 
     const int cls = blockIdx.x, b = blockIdx.y, ncls = gridDim.x;
     const int cch = cls + (P.skip_bg ? 1 : 0);
@@ -108,21 +128,79 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
     }
 
     // ---- 2. cv::partition with SimilarRects(eps): connected components, label = smallest member index
-    for (int i = threadIdx.x; i < n; i += kThreads) { lab[i] = i; sx[i] = sy[i] = sw[i] = sh[i] = cnt[i] = 0; }
+    for (int i = threadIdx.x; i < n; i += kThreads) lab[i] = i;
     __syncthreads();
     if (P.group_threshold > 0) {
+        // 2a. every SimilarRects pair test once per direction, into a bit matrix (no atomics: a task owns its word).
+        // OpenCV: delta = eps * (min(w) + min(h)) * 0.5 in double; similar iff all four |d| <= delta.  The |d| are
+        // integers, so the test is |d| <= floor(delta) =: T(m), m = min(w) + min(h); T comes from a table built with that
+        // very double expression (delta_table_kernel), FP64 only outside the table (FP64 issue is scarce on this part).
+        // Rows of ceil(n / 32) words, pitch made odd; consecutive lanes = consecutive i for one word w, so the candidate
+        // j they all test against is a shared-memory broadcast and the matrix accesses are conflict-free.
+        const int wn = (n + 31) >> 5, words = wn | 1;
+        if (threadIdx.x == 0) s_any = 1;     // re-used: 1 = every coordinate is small enough for 32-bit arithmetic
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += kThreads) {
+            const int lim = 1 << 28;
+            if (abs(rx[i]) >= lim || abs(ry[i]) >= lim || abs(rw[i]) >= lim || abs(rh[i]) >= lim) s_any = 0;
+        }
+        __syncthreads();
+        const bool small = s_any != 0;
+        for (int idx = threadIdx.x; idx < n * wn; idx += kThreads) {
+            const int w = idx / n, i = idx - w * n;
+            const int j0 = w << 5, j1 = min(n, j0 + 32);
+            const int xi = rx[i], yi = ry[i], wi = rw[i], hi = rh[i];
+            unsigned bits = 0;
+            if (small) {
+                // T is monotone in m and m <= wi + hi: |xi - xj| > T(wi + hi) rejects most pairs after one load
+                const int mi = wi + hi;
+                const int Tmax = mi < 0 ? -1 : (mi < kDeltaTable ? __ldg(delta_tab + mi) : (int)floor(P.eps * (double)mi * 0.5));
+                const bool pre = P.eps > 0.0;
+                for (int j = (pre && Tmax < 0) ? j1 : j0; j < j1; ++j) {
+                    const int xj = rx[j];
+                    const int d0 = abs(xi - xj);
+                    if (pre && d0 > Tmax) continue;
+                    const int yj = ry[j];
+                    const int d1 = abs(yi - yj);
+                    if (pre && d1 > Tmax) continue;
+                    const int wj = rw[j], hj = rh[j];
+                    const int m = min(wi, wj) + min(hi, hj);
+                    int T;
+                    if (m < 0) T = -1;
+                    else if (m < kDeltaTable) T = __ldg(delta_tab + m);
+                    else T = (int)floor(P.eps * (double)m * 0.5);
+                    const int d2 = abs(xi + wi - xj - wj), d3 = abs(yi + hi - yj - hj);
+                    if (d0 <= T && d1 <= T && d2 <= T && d3 <= T) bits |= 1u << (j & 31);
+                }
+            } else {
+                for (int j = j0; j < j1; ++j) {
+                    const int wj = rw[j], hj = rh[j];
+                    const long long m = (long long)min(wi, wj) + (long long)min(hi, hj);
+                    long long T;
+                    if (m < 0) T = -1;
+                    else if (m < kDeltaTable) T = __ldg(delta_tab + (int)m);
+                    else T = (long long)floor(P.eps * (double)m * 0.5);
+                    const int xj = rx[j], yj = ry[j];
+                    const long long d0 = llabs((long long)xi - xj), d1 = llabs((long long)yi - yj);
+                    const long long d2 = llabs((long long)xi + wi - xj - wj), d3 = llabs((long long)yi + hi - yj - hj);
+                    if (d0 <= T && d1 <= T && d2 <= T && d3 <= T) bits |= 1u << (j & 31);
+                }
+            }
+            adj[i * words + w] = bits;
+        }
+        __syncthreads();
+        // 2b. min-label propagation over the bit matrix + pointer jumping until nothing changes
         volatile int* vlab = lab;
         for (;;) {
             int changed = 0;
             for (int i = threadIdx.x; i < n; i += kThreads) {
-                const int xi = rx[i], yi = ry[i], wi = rw[i], hi = rh[i];
                 int m = vlab[i];
-                for (int j = 0; j < n; ++j) {
-                    const int wj = rw[j], hj = rh[j];
-                    const double delta = P.eps * (double)(min(wi, wj) + min(hi, hj)) * 0.5;
-                    const int xj = rx[j], yj = ry[j];
-                    if ((double)abs(xi - xj) <= delta && (double)abs(yi - yj) <= delta &&
-                        (double)abs(xi + wi - xj - wj) <= delta && (double)abs(yi + hi - yj - hj) <= delta) {
+                const unsigned* row = adj + (size_t)i * words;
+                for (int w = 0; w < wn; ++w) {
+                    unsigned bits = row[w];
+                    while (bits) {
+                        const int j = (w << 5) + __ffs(bits) - 1;
+                        bits &= bits - 1;
                         const int lj = vlab[j];
                         if (lj < m) m = lj;
                     }
@@ -138,7 +216,10 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
             if (!__syncthreads_or(changed)) break;
         }
     }
-    // ---- 3. per-class integer sums
+    // ---- 3. per-class integer sums (the bit matrix is dead: its memory becomes the sums)
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += kThreads) sx[i] = sy[i] = sw[i] = sh[i] = cnt[i] = 0;
+    __syncthreads();
     for (int i = threadIdx.x; i < n; i += kThreads) {
         const int r = lab[i];
         atomicAdd(&sx[r], rx[i]); atomicAdd(&sy[r], ry[i]);
@@ -154,6 +235,9 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
             sx[i] = __float2int_rn(__fmul_rn((float)sx[i], s)); sy[i] = __float2int_rn(__fmul_rn((float)sy[i], s));
             sw[i] = __float2int_rn(__fmul_rn((float)sw[i], s)); sh[i] = __float2int_rn(__fmul_rn((float)sh[i], s));
         }
+        // containment margins of this class, once per class instead of once per pair (FP64 is scarce)
+        dxr[i] = __double2int_rn((double)sw[i] * P.eps);
+        dyr[i] = __double2int_rn((double)sh[i] * P.eps);
     }
     __syncthreads();
     // ---- 5. threshold on member count + containment filter, then vote_boxes' height filter; ordered output
@@ -173,7 +257,7 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
                     const int n2 = cnt[j];
                     if (n2 <= P.group_threshold) continue;
                     const int x2 = sx[j], y2 = sy[j], w2 = sw[j], h2 = sh[j];
-                    const int dx = __double2int_rn((double)w2 * P.eps), dy = __double2int_rn((double)h2 * P.eps);
+                    const int dx = dxr[j], dy = dyr[j];
                     if (x1 >= x2 - dx && y1 >= y2 - dy && x1 + w1 <= x2 + w2 + dx && y1 + h1 <= y2 + h2 + dy &&
                         (n2 > max(3, n1) || n1 < 3)) { keep = false; break; }
                 }
@@ -232,9 +316,9 @@ __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32
 }  // namespace
 
 size_t postnet_scratch_bytes(int B, int c_cvg) {
-    return (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1) * sizeof(int32_t);
+    return (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1) * sizeof(int32_t) + kDeltaTable * sizeof(int32_t);
 }
-int postnet_num_launches() { return 2; }
+int postnet_num_launches() { return 3; }
 
 void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                     const int32_t* src_hw, const fcnod_postnet_params& p, void* scratch, int32_t* out_det,
@@ -258,7 +342,18 @@ void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg
     P.net_w = p.net_w; P.net_h = p.net_h;
     int32_t* cls_det = static_cast<int32_t*>(scratch);
     int32_t* cls_cnt = cls_det + (size_t)B * ncls * FCNOD_MAX_DET * 6;
-    decode_group_kernel<<<dim3(ncls, B), kThreads, 0, stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, cls_det, cls_cnt);
+    int* delta_tab = static_cast<int*>(scratch) + (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1);
+    delta_table_kernel<<<kDeltaTable / 256, 256, 0, stream>>>(p.eps, delta_tab);
+    FCNOD_CUDA(cudaGetLastError());
+    const size_t adj_bytes = std::max((size_t)gh * gw * ((gh * gw + 31) / 32), (size_t)7 * gh * gw) * sizeof(unsigned);
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    FCNOD_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {     // first call on a device happens outside any graph capture
+        FCNOD_CUDA(cudaFuncSetAttribute(decode_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        attr_set[dev] = true;
+    }
+    decode_group_kernel<<<dim3(ncls, B), kThreads, adj_bytes, stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, delta_tab, cls_det, cls_cnt);
     FCNOD_CUDA(cudaGetLastError());
     assemble_kernel<<<ceil_div(B, 4), 128, 0, stream>>>(cls_det, cls_cnt, B, ncls, src_hw, p.net_w, p.net_h, out_det,
                                                         out_label, out_weight, out_count);
