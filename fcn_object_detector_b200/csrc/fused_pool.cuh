@@ -178,6 +178,147 @@ __global__ void __launch_bounds__(256) pool_lrn_kernel(const T* __restrict__ in,
     }
 }
 
+// ---- Pooling (3x3 stride 2) -> LRN(5), register marching ---------------------------------------------------------
+// One thread = 8 channels of one output column, marching down RS output rows: the horizontal 3-max of the input row it
+// shares with the next output row is carried in registers, so an output costs 6 new 128-bit loads instead of 9.  The CG
+// (= C / 8, a power of two <= 32) lanes that hold one pixel exchange the two edge channels with their neighbours by
+// shuffle for the LRN window.  No shared memory, no block barriers.
+template <int CG, int RS, bool FAST>
+__global__ void __launch_bounds__(256) pool3s2_lrn5_march_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int H,
+                                                                 int W, int ldi, int Ho, int Wo, int ldo, int p,
+                                                                 float alpha_over_n, float beta, float kk) {
+    constexpr int C = CG * 8;
+    const int strips = (Ho + RS - 1) / RS;
+    const unsigned total = (unsigned)N * strips * Wo * CG;           // multiple of CG: lanes of a pixel stay together
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < total;
+    const unsigned ii = live ? i : 0;
+    const int cg = ii % CG;
+    unsigned t = ii / CG;
+    const int ow = t % Wo; t /= Wo;
+    const int strip = t % strips;
+    const int n = t / strips;
+    const int oh_begin = strip * RS, oh_end = min(Ho, oh_begin + RS);
+    const int iw0 = ow * 2 - p;
+    const bf16* img = in + (size_t)n * H * W * ldi + cg * 8;
+    auto hmax_row = [&](int ih, Pack8<bf16>& m) {      // max over the 3 columns of input row ih (-inf outside the image)
+        m.fill_neg_inf();
+        if (ih < 0 || ih >= H) return;
+        const bf16* row = img + (size_t)ih * W * ldi;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int iw = iw0 + c;
+            if (iw >= 0 && iw < W) { Pack8<bf16> x; x.load(row + (size_t)iw * ldi); m.max_with(x); }
+        }
+    };
+    Pack8<bf16> carry;
+    hmax_row(oh_begin * 2 - p, carry);
+    for (int oh = oh_begin; oh < oh_end; ++oh) {
+        Pack8<bf16> m = carry, a, b;
+        hmax_row(oh * 2 - p + 1, a);
+        hmax_row(oh * 2 - p + 2, b);
+        m.max_with(a); m.max_with(b);
+        carry = b;
+        float x[12];                                       // channels cg*8-2 .. cg*8+9
+        m.to_f32(x + 2);
+        // edge channels from the neighbouring lanes of the same pixel (zero beyond the first / last channel)
+        const float l0 = __shfl_up_sync(0xffffffffu, x[8], 1), l1 = __shfl_up_sync(0xffffffffu, x[9], 1);
+        const float r0 = __shfl_down_sync(0xffffffffu, x[2], 1), r1 = __shfl_down_sync(0xffffffffu, x[3], 1);
+        x[0] = cg > 0 ? l0 : 0.f; x[1] = cg > 0 ? l1 : 0.f;
+        x[10] = cg < CG - 1 ? r0 : 0.f; x[11] = cg < CG - 1 ? r1 : 0.f;
+        Vec8<bf16> o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float ss = x[j] * x[j] + x[j + 1] * x[j + 1] + x[j + 2] * x[j + 2] + x[j + 3] * x[j + 3] + x[j + 4] * x[j + 4];
+            o.v[j] = x[j + 2] * lrn_scale<FAST>(kk + alpha_over_n * ss, beta);
+        }
+        if (live) o.store(out + ((size_t)(n * Ho + oh) * Wo + ow) * ldo + cg * 8);
+    }
+    (void)C;
+}
+
+// ---- Pooling -> LRN, shared-memory tiled ----------------------------------------------------------------------
+// One CTA per (image, TH x TW output tile): the (S*(TH-1)+K) x (S*(TW-1)+K) input region is read ONCE with coalesced
+// 128-bit loads into shared memory (bf16), pooled from there into an fp32 tile [TH*TW][C + 16] (8 zeros either side of
+// the channels), then normalised across channels.  Input bytes leave L2 once instead of ~2.25 times.
+template <typename T, int K, int S, int HALF, bool FAST, int TH, int TW>
+__global__ void __launch_bounds__(256) pool_lrn_tile_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W,
+                                                            int ldi, int Ho, int Wo, int ldo, int p, int tiles_x, int tiles_y,
+                                                            float alpha_over_n, float beta, float kk) {
+    extern __shared__ __align__(16) unsigned char plt_smem[];
+    constexpr int RH = S * (TH - 1) + K, RW = S * (TW - 1) + K;
+    T* region = reinterpret_cast<T*>(plt_smem);
+    const int CG = C >> 3;
+    const int rowf = C + 16;
+    float* pooled = reinterpret_cast<float*>(plt_smem + (((size_t)RH * RW * C * sizeof(T) + 15) & ~(size_t)15));
+    int b = blockIdx.x;
+    const int tx = b % tiles_x; b /= tiles_x;
+    const int ty = b % tiles_y;
+    const int n = b / tiles_y;
+    const int oh0 = ty * TH, ow0 = tx * TW;
+    const int ih0 = oh0 * S - p, iw0 = ow0 * S - p;
+    const T* img = in + (size_t)n * H * W * ldi;
+    // stage 1: region -> smem (-inf outside the image); zero the pads of the pooled tile
+    for (int i = threadIdx.x; i < RH * RW * CG; i += 256) {
+        const int cg = i % CG;
+        const int rp = i / CG;
+        const int rr = rp / RW, rc = rp - rr * RW;
+        const int ih = ih0 + rr, iw = iw0 + rc;
+        Pack8<T> x;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) x.load(img + ((size_t)ih * W + iw) * ldi + cg * 8);
+        else x.fill_neg_inf();
+        x.store(region + (size_t)rp * C + cg * 8);
+    }
+    for (int i = threadIdx.x; i < TH * TW * 16; i += 256) {
+        const int r = i >> 4, j = i & 15;
+        pooled[r * rowf + (j < 8 ? j : C + j)] = 0.f;
+    }
+    __syncthreads();
+    // stage 2: pool from smem into the fp32 tile
+    for (int i = threadIdx.x; i < TH * TW * CG; i += 256) {
+        const int cg = i % CG;
+        const int op = i / CG;
+        const int a = op / TW, bc = op - a * TW;
+        Pack8<T> m;
+        m.fill_neg_inf();
+#pragma unroll
+        for (int r = 0; r < K; ++r)
+#pragma unroll
+            for (int c = 0; c < K; ++c) {
+                Pack8<T> x;
+                x.load(region + (size_t)((a * S + r) * RW + bc * S + c) * C + cg * 8);
+                m.max_with(x);
+            }
+        float v[8];
+        m.to_f32(v);
+        float* d = pooled + op * rowf + 8 + cg * 8;
+        *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(d + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    __syncthreads();
+    // stage 3: LRN across channels, store
+    for (int i = threadIdx.x; i < TH * TW * CG; i += 256) {
+        const int cg = i % CG;
+        const int op = i / CG;
+        const int a = op / TW, bc = op - a * TW;
+        const int oh = oh0 + a, ow = ow0 + bc;
+        if (oh >= Ho || ow >= Wo) continue;
+        const float* sp = pooled + op * rowf + 8 + cg * 8;
+        float x[8 + 2 * HALF];
+#pragma unroll
+        for (int j = 0; j < 8 + 2 * HALF; ++j) x[j] = sp[j - HALF];
+        Vec8<T> o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d <= 2 * HALF; ++d) acc += x[j + d] * x[j + d];
+            o.v[j] = x[j + HALF] * lrn_scale<FAST>(kk + alpha_over_n * acc, beta);
+        }
+        o.store(out + ((size_t)(n * Ho + oh) * Wo + ow) * ldo + cg * 8);
+    }
+}
+
 // ---- LRN -> Pooling -------------------------------------------------------------------------------------------
 // One CTA per (image, TH x TW output tile).  smem: T [(S*(TH-1)+K) * (S*(TW-1)+K)][C].
 template <typename T, int K, int S, int HALF, bool FAST, int TH, int TW>
@@ -256,8 +397,11 @@ __global__ void __launch_bounds__(256) lrn_pool_kernel(const T* __restrict__ in,
 // out[n][h2][PADL + w2][(dy*2+dx)*C + c] = bf16(in[n][c][2*h2+dy][2*w2+dx]);  channels >= 4*C and the pad
 // columns stay zero (written once at allocation).  Feeds the first convolution (stride 2) as a stride-1
 // tensor-core convolution (see net.cu: plan_conv_s2d).
-__global__ void __launch_bounds__(256) input_s2d_kernel(const float* __restrict__ in, bf16* __restrict__ out, int N, int C,
+template <int CT>   // CT = channel count known at compile time (1..4, 16 output channels per pixel), or 0 = generic
+__global__ void __launch_bounds__(256) input_s2d_kernel(const float* __restrict__ in, bf16* __restrict__ out, int N, int C_rt,
                                                         int H, int W, int Wp, int padl, int ldc) {
+    const int C = CT > 0 ? CT : C_rt;
+    // one thread per space-to-depth pixel: 2 rows x float2 per channel in (coalesced over w2), ldc bf16 out as 16-byte stores
     const int H2 = H >> 1, W2 = W >> 1;
     const unsigned total = (unsigned)N * H2 * W2;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -265,15 +409,34 @@ __global__ void __launch_bounds__(256) input_s2d_kernel(const float* __restrict_
         unsigned t = i / W2;
         const int h2 = t % H2;
         const int n = t / H2;
-        bf16* o = out + ((size_t)(n * H2 + h2) * Wp + padl + w2) * ldc;
-        for (int c = 0; c < C; ++c) {
-            const float* src = in + ((size_t)(n * C + c) * H + 2 * h2) * W + 2 * w2;
-            const float2 r0 = *reinterpret_cast<const float2*>(src);
-            const float2 r1 = *reinterpret_cast<const float2*>(src + W);
-            o[0 * C + c] = __float2bfloat16_rn(r0.x);
-            o[1 * C + c] = __float2bfloat16_rn(r0.y);
-            o[2 * C + c] = __float2bfloat16_rn(r1.x);
-            o[3 * C + c] = __float2bfloat16_rn(r1.y);
+        __align__(16) bf16 v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = __float2bfloat16_rn(0.f);
+        if (CT > 0) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (c < CT) {
+                    const float* src = in + ((size_t)(n * C + c) * H + 2 * h2) * W + 2 * w2;
+                    const float2 r0 = __ldg(reinterpret_cast<const float2*>(src));
+                    const float2 r1 = __ldg(reinterpret_cast<const float2*>(src + W));
+                    v[0 * CT + c] = __float2bfloat16_rn(r0.x);
+                    v[1 * CT + c] = __float2bfloat16_rn(r0.y);
+                    v[2 * CT + c] = __float2bfloat16_rn(r1.x);
+                    v[3 * CT + c] = __float2bfloat16_rn(r1.y);
+                }
+            }
+            uint4* o = reinterpret_cast<uint4*>(out + ((size_t)(n * H2 + h2) * Wp + padl + w2) * 16);
+            o[0] = *reinterpret_cast<const uint4*>(v);
+            o[1] = *reinterpret_cast<const uint4*>(v + 8);
+        } else {
+            bf16* o = out + ((size_t)(n * H2 + h2) * Wp + padl + w2) * ldc;
+            for (int c = 0; c < C; ++c) {
+                const float* src = in + ((size_t)(n * C + c) * H + 2 * h2) * W + 2 * w2;
+                o[0 * C + c] = __float2bfloat16_rn(src[0]);
+                o[1 * C + c] = __float2bfloat16_rn(src[1]);
+                o[2 * C + c] = __float2bfloat16_rn(src[W]);
+                o[3 * C + c] = __float2bfloat16_rn(src[W + 1]);
+            }
         }
     }
 }

@@ -1127,8 +1127,14 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
         case S_S2D: {
             const Blob& ib = net->blobs[0];
             long items = (long)net->batch * (ib.H / 2) * (ib.W / 2);
-            input_s2d_kernel<<<grid_for(items, 256), 256, 0, s>>>(data_dev, (bf16*)net->buffers[st.s2d_buf].ptr, net->batch, ib.C,
-                                                                   ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+            bf16* dst = (bf16*)net->buffers[st.s2d_buf].ptr;
+            const int g = grid_for(items, 256);
+            if (ib.C == 3)
+                input_s2d_kernel<3><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+            else if (ib.C == 1)
+                input_s2d_kernel<1><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+            else
+                input_s2d_kernel<0><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
             break;
         }
         case S_POOL_LRN: {   // layer = Pooling, layer2 = LRN
@@ -1136,6 +1142,26 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             const Blob& ib = net->blobs[st.in];
             const Blob& ob = net->blobs[st.out];
             FCNOD_CHECK(ib.dtype == DT_BF16 && ob.dtype == DT_BF16, "pool+lrn: bf16 only");
+            if (ib.C == 64) {   // register-marching form (deploy net: pool1 + norm1 on 64 channels)
+                constexpr int RS = 8;
+                const long threads = (long)net->batch * ceil_div(ob.H, RS) * ob.W * 8;
+                pool3s2_lrn5_march_kernel<8, RS, true><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(
+                    (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), net->batch, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc,
+                    L->pad, R.alpha / R.local_size, R.beta, R.lrn_k);
+                break;
+            }
+            {   // shared-memory tiled form when the tile fits
+                constexpr int TH = 4, TW = 16;
+                const size_t region = align_up((size_t)(2 * (TH - 1) + 3) * (2 * (TW - 1) + 3) * ib.C * 2, 16);
+                const size_t smem_t = region + (size_t)TH * TW * (ib.C + 16) * 4;
+                if (smem_t <= 100 * 1024) {
+                    const int tx = ceil_div(ob.W, TW), ty = ceil_div(ob.H, TH);
+                    pool_lrn_tile_kernel<bf16, 3, 2, 2, true, TH, TW><<<tx * ty * net->batch, 256, smem_t, s>>>(
+                        (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc,
+                        L->pad, tx, ty, R.alpha / R.local_size, R.beta, R.lrn_k);
+                    break;
+                }
+            }
             const int CG = ib.C / 8, npix_cta = 256 / CG;
             long npix = (long)net->batch * ob.H * ob.W;
             int g = (int)std::min<long>((npix + npix_cta - 1) / npix_cta, (long)kNumSMs * 8);
@@ -1291,6 +1317,7 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     conv_tc2_set_smem_limit();
     FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_tile_kernel<bf16, 3, 2, 2, true, 4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
     upload_weights(net.get());
     reshape(net.get(), net->def.input_dims[0] > 0 ? net->def.input_dims[0] : 1);
