@@ -53,6 +53,7 @@ struct ConvTc2Params {
     int halo;                // 1 = HALO mode
     int m_tiles, n_tiles, BN;
     int a_stages, b_stages;
+    int b_taps;              // K-blocks per B stage: 1, or kw in HALO mode (one kernel row of taps per TMA / barrier round)
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
     uint32_t tmem_cols;      // whole allocation (2 accumulators), power of two
     uint32_t acc_stride;     // columns between the two accumulators
@@ -99,6 +100,12 @@ __device__ __forceinline__ void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, u
 __device__ __forceinline__ void tmem_ld_wait_dep32(uint32_t* r) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
     asm volatile("" : "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]) :: "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
 }
 // wait with back-off, for the warps that wait long (keeps their spinning out of the issue slots of the TMA / MMA threads)
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
@@ -159,14 +166,17 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         // ring are dealt round-robin to two warps; every stage has its own barriers, arrival order does not matter.
         if (lane == 0) {
             const bool ringB = warp >= 2;
-            const uint32_t par = (uint32_t)warp & 1u;
+            uint32_t par = (uint32_t)warp & 1u;
             asm volatile("prefetch.tensormap [%0];" ::"l"(ringB ? &tmap_b : &tmap_a) : "memory");
-            const uint32_t b_tx = (uint32_t)p.BN * span;
-            const int kb_stride = p.n_cchunks * p.CK;          // K columns between two taps of the packed weights
+            const uint32_t b_tx = (uint32_t)p.BN * span * (uint32_t)p.b_taps;
             const uint32_t nst = ringB ? (uint32_t)p.b_stages : (uint32_t)p.a_stages;
             const uint32_t st_bytes = ringB ? p.b_stage_bytes : p.a_stage_bytes;
             const uint32_t ring_base = ringB ? b_base : a_base;
             const uint32_t full0 = ringB ? bfull0 : afull0, empty0 = ringB ? bempty0 : aempty0;
+            // a one-stage ring is fed by ONE warp: with two, a warp's consecutive visits to the stage would be two
+            // barrier phases apart, which a parity wait cannot tell from zero
+            uint32_t idx_mask = 1u;
+            if (nst < 2) { idx_mask = 0u; if (par) par = 2u; }      // par 2 never matches: the odd warp idles
             uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
             int tile_i = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tile_i) {
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                     for (int r = 0; r < (HALO ? 1 : p.kh); ++r)
                         for (int s = 0; s < (HALO ? 1 : p.kw); ++s)
                             for (int cc = 0; cc < p.n_cchunks; ++cc, ++idx) {
-                                if ((idx & 1u) == par) {
+                                if ((idx & idx_mask) == par) {
                                     mbar_wait(empty0 + 8u * sg, ph ^ 1u);
                                     mbar_expect_tx(full0 + 8u * sg, p.a_tx_bytes);
                                     tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
@@ -188,21 +198,36 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                                 if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
                             }
                 } else {
-                    // ---- B: one box per K-block; K column = tap * kb_stride + cc * CK
-                    const int n_outer = HALO ? p.n_cchunks : taps, n_inner = HALO ? taps : p.n_cchunks;
-                    const int outer_step = HALO ? p.CK : kb_stride, inner_step = HALO ? kb_stride : p.CK;
+                    // ---- B: weights are packed [K-block][N][CK]; one box = b_taps consecutive K-blocks x BN rows.
+                    //      K-block order = consumption order of the MMA warp: TAP (r, s, cc); HALO (cc: r: s) -> block
+                    //      (r * n_cchunks + cc) * kw + s, so the kw taps of one kernel row are adjacent.
                     int ev = 0;
-                    for (int o = 0, kcol_o = 0; o < n_outer; ++o, kcol_o += outer_step)
-                        for (int i = 0, kcol = kcol_o; i < n_inner; ++i, kcol += inner_step, ++idx, ++ev) {
-                            if ((idx & 1u) == par) {
+                    if (HALO) {
+                        for (int cc = 0; cc < p.n_cchunks; ++cc)
+                            for (int r = 0; r < p.kh; ++r)
+                                for (int s = 0; s < p.kw; s += p.b_taps, ++idx, ++ev) {
+                                    if ((idx & idx_mask) == par) {
+                                        mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                        if (PROF) FCNOD_PROF(0, tile_i, ev);
+                                        mbar_expect_tx(full0 + 8u * sg, b_tx);
+                                        tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, (r * p.n_cchunks + cc) * p.kw + s);
+                                    }
+                                    dst += st_bytes;
+                                    if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
+                                }
+                    } else {
+                        const int nkb = taps * p.n_cchunks;
+                        for (int kb = 0; kb < nkb; ++kb, ++idx, ++ev) {
+                            if ((idx & idx_mask) == par) {
                                 mbar_wait(empty0 + 8u * sg, ph ^ 1u);
                                 if (PROF) FCNOD_PROF(0, tile_i, ev);
                                 mbar_expect_tx(full0 + 8u * sg, b_tx);
-                                tma_load_2d(dst, &tmap_b, full0 + 8u * sg, kcol, n0);
+                                tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, kb);
                             }
                             dst += st_bytes;
                             if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
                         }
+                    }
                 }
             }
         }
@@ -214,6 +239,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             const uint32_t desc_hi = ((8u * span) >> 4) | (1u << 14) | ((span == 128 ? 2u : (span == 64 ? 4u : 6u)) << 29);
             const uint32_t a_lo_base = ((a_base & 0x3FFFFu) >> 4) | (1u << 16), a_lo_step = p.a_stage_bytes >> 4;
             const uint32_t b_lo_base = ((b_base & 0x3FFFFu) >> 4) | (1u << 16), b_lo_step = p.b_stage_bytes >> 4;
+            const uint32_t b_tap_step = ((uint32_t)p.BN * span) >> 4;      // one tap tile inside a multi-tap B stage
             const uint32_t row_step = (uint32_t)p.PW * 8u;      // HALO: one patch row = PW rows of 128 bytes, in 16-byte units
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
@@ -234,22 +260,30 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                     if (++cc == p.n_cchunks) cc = 0;
                     uint32_t a_row = a_lo;
                     for (int r = 0; r < (HALO ? p.kh : 1); ++r, a_row += row_step) {
-                        for (int s = 0; s < (HALO ? p.kw : 1); ++s, ++ev) {
-                            mbar_wait(bfull0 + 8u * sb, pb);
-                            fence_after();
-                            if (PROF) FCNOD_PROF(1, it, ev);
+                        int in_stage = 0;                  // taps already consumed from the current B stage
+                        for (int s = 0; s < (HALO ? p.kw : 1); ++s) {
+                            if (in_stage == 0) {
+                                mbar_wait(bfull0 + 8u * sb, pb);
+                                fence_after();
+                                if (PROF) FCNOD_PROF(1, it, ev);
+                            }
                             const uint32_t a_tap = a_row + (uint32_t)s * 8u;
+                            const uint32_t b_tap = b_lo + (uint32_t)in_stage * b_tap_step;
 #pragma unroll
                             for (int k = 0; k < KSTEPS; ++k) {
                                 if (k < ks) {
-                                    umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_lo + 2u * k, desc_hi, idesc, accum);
+                                    umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_tap + 2u * k, desc_hi, idesc, accum);
                                     accum = 1;
                                 }
                             }
-                            umma_commit(bempty0 + 8u * sb);
-                            if (PROF) FCNOD_PROF(3, it, ev);
-                            b_lo += b_lo_step;
-                            if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
+                            if (++in_stage == p.b_taps) {
+                                in_stage = 0;
+                                umma_commit(bempty0 + 8u * sb);
+                                if (PROF) FCNOD_PROF(3, it, ev);
+                                ++ev;
+                                b_lo += b_lo_step;
+                                if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
+                            }
                         }
                     }
                     umma_commit(aempty0 + 8u * sa);

@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(256) pool_lrn_tile_kernel(const T* __restrict_
 // ---- LRN -> Pooling -------------------------------------------------------------------------------------------
 // One CTA per (image, TH x TW output tile).  smem: T [(S*(TH-1)+K) * (S*(TW-1)+K)][C].
 template <typename T, int K, int S, int HALF, bool FAST, int TH, int TW>
-__global__ void __launch_bounds__(256) lrn_pool_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W,
+__global__ void __launch_bounds__(512) lrn_pool_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W,
                                                        int ldi, int Ho, int Wo, int ldo, int p, int tiles_x, int tiles_y,
                                                        float alpha_over_n, float beta, float kk) {
     extern __shared__ __align__(16) unsigned char lp_smem_raw[];
@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(256) lrn_pool_kernel(const T* __restrict__ in,
     const T* img = in + (size_t)n * H * W * ldi;
     // stage 1: normalise the input region into shared memory (-inf outside the image: max ignores it)
     const int items = RH * RW * CG;
-    for (int i = threadIdx.x; i < items; i += 256) {
+    for (int i = threadIdx.x; i < items; i += blockDim.x) {
         const int cg = i % CG;
         const int rp = i / CG;
         const int rr = rp / RW, rc = rp - rr * RW;
@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(256) lrn_pool_kernel(const T* __restrict__ in,
     __syncthreads();
     // stage 2: pool from shared memory
     const int oitems = TH * TW * CG;
-    for (int i = threadIdx.x; i < oitems; i += 256) {
+    for (int i = threadIdx.x; i < oitems; i += blockDim.x) {
         const int cg = i % CG;
         const int op = i / CG;
         const int a = op / TW, bcol = op - a * TW;

@@ -686,8 +686,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
     p.halo = cw.halo ? 1 : 0;
     if (cw.s2d) {
-        if (st.s2d_overlap) { p.kh = cw.ka; p.kw = 1; p.CK = cw.ka * kS2dCpad; }
-        else { p.kh = p.kw = cw.ka; p.CK = kS2dCpad; }
+        p.kh = cw.ka; p.kw = 1; p.CK = cw.ka * kS2dCpad;     // one K-block per kernel row (overlapping-window tensor map)
         p.n_cchunks = 1;
         p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
         p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
@@ -718,35 +717,43 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     //   tile time = max(MMA issue, L2->smem bytes, epilogue) + fixed;  total = rounds over 148 persistent CTAs
     const int N8 = (cw.Cout + 7) / 8 * 8;
     double best_cost = -1;
+    // real 16-wide K steps per tap (the last chunk may be partly zero fill)
+    const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);
     for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > 256 || nt * BN - N8 >= BN) continue;
-        const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024);
         const int half0 = ceil_div(BN, 32) * 16;
         const uint32_t row_bytes = (uint32_t)align_up((size_t)half0 * 2, 128);
         const size_t fixed = 8 * 32 * (size_t)row_bytes + 8 * 512 + 512 + 1024;
-        int a_st, b_st;
-        if (p.halo) {
-            a_st = 2;      // the next tile's patch loads while this one is multiplied
-            if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
-            if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
-            b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
-        } else {
-            const size_t pair = (size_t)p.a_stage_bytes + b_stage;
-            if (fixed + 2 * pair > kTcSmemBudget) continue;
-            a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
-        }
-        const double mma = (Kp / 16.0) * std::max(BN / 2.0, 32.0);
-        const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
-        const double load = (a_bytes + (double)BN * Kp * 2) / 48.0;
-        const double epi = 10.0 * BN;
-        const double tile = std::max(mma, std::max(load, epi)) + 500.0;
-        const long rounds = ((long)p.m_tiles * nt + kNumSMs - 1) / kNumSMs;
-        const double cost = rounds * tile;
-        if (best_cost < 0 || cost < best_cost) {
-            best_cost = cost;
-            p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st;
-            p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
+        for (int bt = (p.halo ? p.kw : 1); bt >= 1; bt = (bt > 1 ? 1 : 0)) {       // B stage = kw taps (HALO) or 1
+            const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024) * bt;
+            int a_st, b_st;
+            if (p.halo) {
+                a_st = 2;      // the next tile's patch loads while this one is multiplied
+                if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
+                if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
+                b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
+            } else {
+                const size_t pair = (size_t)p.a_stage_bytes + b_stage;
+                if (fixed + 2 * pair > kTcSmemBudget) continue;
+                a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
+            }
+            // tensor pipe: BN/2 cycles per K step, at least 32 (the 128 x 16 A slice streams from smem at 128 B/clk);
+            // the one issuing thread: ~300 cycles per barrier round (wait + commit) + ~25 per MMA
+            const double mma = ksteps_tile * std::max(BN / 2.0, 32.0);
+            const double rounds_b = (double)taps * p.n_cchunks / bt;
+            const double issue = rounds_b * 300.0 + ksteps_tile * 25.0;
+            const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
+            const double load = (a_bytes + (double)BN * Kp * 2) / 30.0;                 // ~30 B/clk/SM seen from L2
+            const double epi = 12.0 * BN;
+            const double tile = std::max(std::max(mma, issue), std::max(load, epi)) + 500.0;
+            const long rounds = ((long)p.m_tiles * nt + kNumSMs - 1) / kNumSMs;
+            const double cost = rounds * tile;
+            if (best_cost < 0 || cost < best_cost) {
+                best_cost = cost;
+                p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st; p.b_taps = bt;
+                p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
+            }
         }
     }
     FCNOD_CHECK(best_cost >= 0, "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
@@ -797,7 +804,9 @@ void upload_weights(fcnod_net* net) {
             // bias[class(oh)][class(ow)][o] = b[o] + in_shift * sum over the taps that fall INSIDE the image.
             const int ka = cw.ka, off = cw.q - cw.pad, Kp = ka * ka * kS2dCpad;
             const int Nrows = (Cout + 15) / 16 * 16, Np = (int)align_up((size_t)(Cout + 7) / 8 * 8, 256) + 256;
+            // packed [K-block = kernel row ah][N][aw * 16 + (dy*2+dx)*Cin + c]
             std::vector<bf16> w((size_t)Nrows * Kp, __float2bfloat16(0.f));
+            const size_t kbs = (size_t)Nrows * ka * kS2dCpad;
             for (int o = 0; o < Cout; ++o)
                 for (int ah = 0; ah < ka; ++ah)
                     for (int aw = 0; aw < ka; ++aw)
@@ -806,7 +815,7 @@ void upload_weights(fcnod_net* net) {
                                 const int r = 2 * ah + dy - off, sx = 2 * aw + dx - off;
                                 if (r < 0 || r >= k || sx < 0 || sx >= k) continue;
                                 for (int c = 0; c < Cin; ++c)
-                                    w[(size_t)o * Kp + (size_t)(ah * ka + aw) * kS2dCpad + (dy * 2 + dx) * Cin + c] =
+                                    w[ah * kbs + (size_t)o * ka * kS2dCpad + (size_t)aw * kS2dCpad + (dy * 2 + dx) * Cin + c] =
                                         __float2bfloat16(cw.in_scale * cw.w[(((size_t)o * Cin + c) * k + r) * k + sx]);
                             }
             FCNOD_CUDA(cudaMalloc(&cw.d_w_tc, w.size() * 2));
@@ -854,13 +863,16 @@ void upload_weights(fcnod_net* net) {
         } else {
             const int Kp = k * k * cw.n_cchunks * cw.CK;
             const int Nrows = (Cout + 15) / 16 * 16, Np = (int)align_up((size_t)(Cout + 7) / 8 * 8, 256) + 256;
+            // packed [K-block][N][CK]; K-block order = the kernel's consumption order:
+            //   TAP  (r * k + s) * n_cchunks + cc        HALO  (r * n_cchunks + cc) * k + s   (taps of a kernel row adjacent)
             std::vector<bf16> w((size_t)Nrows * Kp, __float2bfloat16(0.f));
             for (int o = 0; o < Cout; ++o)
                 for (int c = 0; c < Cin; ++c)
                     for (int r = 0; r < k; ++r)
                         for (int s = 0; s < k; ++s) {
-                            size_t kk = ((size_t)(r * k + s) * cw.n_cchunks + c / cw.CK) * cw.CK + c % cw.CK;
-                            w[(size_t)o * Kp + kk] = __float2bfloat16(cw.w[(((size_t)o * Cin + c) * k + r) * k + s]);
+                            const int cc = c / cw.CK;
+                            const size_t kb = cw.halo ? (size_t)(r * cw.n_cchunks + cc) * k + s : (size_t)(r * k + s) * cw.n_cchunks + cc;
+                            w[(kb * Nrows + o) * cw.CK + c % cw.CK] = __float2bfloat16(cw.w[(((size_t)o * Cin + c) * k + r) * k + s]);
                         }
             FCNOD_CUDA(cudaMalloc(&cw.d_w_tc, w.size() * 2));
             FCNOD_CUDA(cudaMemcpy(cw.d_w_tc, w.data(), w.size() * 2, cudaMemcpyHostToDevice));
@@ -922,6 +934,17 @@ void bind_tc_pointers(fcnod_net* net, Step& st) {
     }
 }
 
+// B = packed weights [K-block][Nrows][CK]; box = b_taps consecutive K-blocks x BN rows x CK
+void encode_weight_map(Step& st, const ConvWeights& cw, int Nrows, int n_kblocks, const std::string& name) {
+    const ConvTc2Params& p = st.tc;
+    const uint32_t span = p.CK * 2;
+    cuuint64_t dims[3] = {(cuuint64_t)p.CK, (cuuint64_t)Nrows, (cuuint64_t)n_kblocks};
+    cuuint64_t strides[2] = {(cuuint64_t)span, (cuuint64_t)Nrows * span};
+    cuuint32_t box[3] = {(cuuint32_t)p.CK, (cuuint32_t)p.BN, (cuuint32_t)p.b_taps};
+    CUresult r = encode_map(&st.tmap_b, cw.d_w_tc, 3, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+    FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B) failed for '" + name + "' (" + std::to_string((int)r) + ")");
+}
+
 void setup_tc_step(fcnod_net* net, Step& st) {
     const LayerDef& L = net->def.layers[st.layer];
     ConvWeights& cw = net->convs[st.conv];
@@ -930,33 +953,21 @@ void setup_tc_step(fcnod_net* net, Step& st) {
     const int B = net->batch;
     const int Nrows = (cw.Cout + 15) / 16 * 16;
     if (cw.s2d) {
-        // A = the W-padded space-to-depth image [B][H2][Wp][16] bf16.  Preferred: ONE K-block per kernel row,
-        // its A rows being the 128-byte windows of ka consecutive pixels (an overlapping-stride tensor map:
-        // dim0 = ka*16 contiguous elements, dim1 = window start, one pixel = 32 bytes apart).  If the driver
-        // refuses that map, one K-block per tap over the plain map (same weights buffer, same results).
+        // A = the W-padded space-to-depth image [B][H2][Wp][16] bf16.  ONE K-block per kernel row: its A rows are the
+        // 128-byte windows of ka consecutive pixels, fetched through an overlapping-stride tensor map
+        // (dim0 = ka*16 contiguous elements, dim1 = window start, one pixel = 32 bytes apart).
         const int H2 = ob.H, W2 = ob.W, Wp = st.s2d_wp;
         void* base = net->buffers[st.s2d_buf].ptr;
         const cuuint64_t pix = kS2dCpad * 2;
-        const char* force = getenv("FCNOD_S2D_TAPS");
-        st.s2d_overlap = !(force && force[0] == '1');
-        for (int attempt = 0; attempt < 2; ++attempt) {
-            fill_tc_geometry(net, st, B);
-            ConvTc2Params& p = st.tc;
-            const uint32_t span = p.CK * 2;
-            cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)(st.s2d_overlap ? W2 : Wp), (cuuint64_t)H2, (cuuint64_t)B};
-            cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
-            cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
-            CUresult r = encode_map(&st.tmap_a, base, 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
-            if (r != CUDA_SUCCESS && st.s2d_overlap) { st.s2d_overlap = false; continue; }
-            FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
-            const cuuint64_t Kp = (cuuint64_t)cw.ka * cw.ka * kS2dCpad;
-            cuuint64_t bd[2] = {Kp, (cuuint64_t)Nrows};
-            cuuint64_t bs[1] = {Kp * 2};
-            cuuint32_t bb[2] = {(cuuint32_t)p.CK, (cuuint32_t)p.BN};
-            r = encode_map(&st.tmap_b, cw.d_w_tc, 2, bd, bs, bb, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
-            FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
-            break;
-        }
+        fill_tc_geometry(net, st, B);
+        ConvTc2Params& p = st.tc;
+        const uint32_t span = p.CK * 2;
+        cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)W2, (cuuint64_t)H2, (cuuint64_t)B};
+        cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
+        cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
+        CUresult r = encode_map(&st.tmap_a, base, 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+        FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
+        encode_weight_map(st, cw, Nrows, cw.ka, L.name);
         bind_tc_pointers(net, st);
         return;
     }
@@ -970,14 +981,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         CUresult r = encode_map(&st.tmap_a, view_ptr(net, ib), 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
-    {
-        const cuuint64_t Kp = (cuuint64_t)cw.k * cw.k * cw.n_cchunks * cw.CK;
-        cuuint64_t dims[2] = {Kp, (cuuint64_t)Nrows};
-        cuuint64_t strides[1] = {Kp * 2};
-        cuuint32_t box[2] = {(cuuint32_t)cw.CK, (cuuint32_t)p.BN};
-        CUresult r = encode_map(&st.tmap_b, cw.d_w_tc, 2, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
-        FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(B) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
-    }
+    encode_weight_map(st, cw, Nrows, cw.k * cw.k * cw.n_cchunks, L.name);
     bind_tc_pointers(net, st);
 }
 
@@ -1179,7 +1183,7 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             constexpr int TH = 4, TW = 8;
             const int tx = ceil_div(ob.W, TW), ty = ceil_div(ob.H, TH);
             size_t smem = (size_t)(2 * (TH - 1) + 3) * (2 * (TW - 1) + 3) * ib.C * 2;
-            lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW><<<tx * ty * net->batch, 256, smem, s>>>(
+            lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW><<<tx * ty * net->batch, 512, smem, s>>>(
                 (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad, tx,
                 ty, L->alpha / L->local_size, L->beta, L->lrn_k);
             break;
@@ -1385,14 +1389,14 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
             o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {
             const Blob& b = net->blobs[st.out];
             o << " -> " << b.name << " (" << b.C << "," << b.H << "," << b.W << ") " << (b.dtype == DT_F32 ? "f32" : "bf16")
               << " buf" << b.buf << "+" << b.c_off << "/" << b.ldc;
-            if (st.kind == S_CONV_TC && net->convs[st.conv].s2d) o << (st.s2d_overlap ? " [row K-blocks]" : " [tap K-blocks]");
+            if (st.kind == S_CONV_TC && net->convs[st.conv].s2d) o << " [row K-blocks]";
         }
         o << "\n";
     }

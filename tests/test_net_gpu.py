@@ -117,13 +117,6 @@ def test_s2d_conv_and_fused_pool_lrn(case, tmp_path, monkeypatch):
     assert 'pool+lrn' not in plan2 and 'conv_simt' in plan2
     for n in ('n1', 'p2', 'out'):
         assert rel_err(got[n], unf[n]) < 2e-2, (n, rel_err(got[n], unf[n]))
-    # the tap-per-K-block variant of the s2d convolution gives the same bits as the row-per-K-block one
-    monkeypatch.delenv('FCNOD_NO_FUSION')
-    monkeypatch.setenv('FCNOD_S2D_TAPS', '1')
-    taps, plan3 = gpu_forward(proto, cm, x, 'bf16', ['c1'])
-    assert '[tap K-blocks]' in plan3
-    if '[row K-blocks]' in plan:
-        assert rel_err(taps['c1'], got['c1']) < 1.0 / 128
 
 
 def test_bf16_full_net_within_tolerance(model_files):
