@@ -13,10 +13,10 @@
 //
 // Kernel 1 (decode_group_kernel): one CTA per (frame, foreground class).  Coverage is read
 //   with coalesced loads, candidates are compacted IN ROW-MAJOR ORDER with warp ballots +
-//   a cross-warp scan, kept in shared memory, clustered there: every SimilarRects pair is tested
-//   once into a shared-memory bit matrix, then min-label propagation over its set bits with
-//   pointer jumping = connected components, class order = smallest member index, exactly
-//   what cv::partition yields; reduced with shared-memory atomics and filtered.
+//   a cross-warp scan, kept in shared memory, clustered there: every unordered SimilarRects pair
+//   is tested once and similar pairs are merged at once in a lock-free union-find (larger root
+//   hooked under the smaller) = connected components, class order = smallest member index,
+//   exactly what cv::partition yields; reduced with shared-memory atomics and filtered.
 // Kernel 2 (assemble_kernel): one warp per frame concatenates the per-class lists in
 //   class order and rescales.
 #include <cmath>
@@ -28,7 +28,7 @@ namespace fcnod {
 namespace {
 
 constexpr int kMaxCand = 1024;     // grid cells per (frame, class) handled in shared memory
-constexpr int kThreads = 256;
+constexpr int kThreads = 1024;
 
 struct PostParams {
     float prob_thresh;
@@ -60,6 +60,18 @@ __device__ __forceinline__ int block_scan_flag(bool flag, int* warp_tot /*[8]*/,
     return base + pre;
 }
 
+// Lock-free union-find over shared memory.  Invariant: lab[x] <= x, and only roots (lab[x] == x) are ever hooked, so
+// the structure is a forest whose roots are the smallest members of their trees.
+__device__ __forceinline__ int uf_find(volatile int* lab, int x) {
+    const int x0 = x;
+    int p = lab[x];
+    if (p == x) return x;
+    do { x = p; p = lab[x]; } while (p != x);
+    // compress the starting node with a plain store: x is an ancestor of x0 whatever else happened meanwhile, so a lost
+    // race only leaves a longer (still valid) path
+    lab[x0] = x;
+    return x;
+}
 constexpr int kDeltaTable = 8192;   // T(m) for 0 <= m < 8192 (sum of two box sides); larger m take the FP64 path
 
 // T(m) = floor(eps * m * 0.5), evaluated in double exactly as cv::SimilarRects does
@@ -78,8 +90,7 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
     __shared__ int lab[kMaxCand];
     __shared__ int warp_tot[kThreads / 32];
     __shared__ int s_any;
-    // dynamic shared memory, used twice: first the similarity bit matrix [n][words] (words = ceil(gh*gw / 32)),
-    // then (after the partition) the per-class sums / counts / containment margins, 7 arrays of gh*gw ints
+    // dynamic shared memory: per-class sums / counts / containment margins / surviving-class list, 8 arrays of gh*gw ints
     extern __shared__ unsigned adj[];
     const int ncell_all = gh * gw;
     int* const sx = reinterpret_cast<int*>(adj);
@@ -89,6 +100,7 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
     int* const cnt = sh + ncell_all;
     int* const dxr = cnt + ncell_all;
     int* const dyr = dxr + ncell_all;
+    int* const strong = dyr + ncell_all;
 
     const int cls = blockIdx.x, b = blockIdx.y, ncls = gridDim.x;
     const int cch = cls + (P.skip_bg ? 1 : 0);
@@ -129,94 +141,95 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
 
     // ---- 2. cv::partition with SimilarRects(eps): connected components, label = smallest member index
     for (int i = threadIdx.x; i < n; i += kThreads) lab[i] = i;
+    if (threadIdx.x == 0) s_any = 1;     // re-used: 1 = every coordinate is small enough for 32-bit arithmetic
     __syncthreads();
     if (P.group_threshold > 0) {
-        // 2a. every SimilarRects pair test once per direction, into a bit matrix (no atomics: a task owns its word).
+        // Every unordered pair (i, j < i) is tested ONCE and, when similar, merged straight
+        // away in a lock-free union-find over `lab` (hook the larger root under the smaller one with atomicCAS): no
+        // similarity matrix, no propagation sweeps.  Links always point to a smaller index, so the root of a component
+        // is its smallest member -- the class order cv::partition produces -- whatever order the merges happen in.
         // OpenCV: delta = eps * (min(w) + min(h)) * 0.5 in double; similar iff all four |d| <= delta.  The |d| are
         // integers, so the test is |d| <= floor(delta) =: T(m), m = min(w) + min(h); T comes from a table built with that
         // very double expression (delta_table_kernel), FP64 only outside the table (FP64 issue is scarce on this part).
-        // Rows of ceil(n / 32) words, pitch made odd; consecutive lanes = consecutive i for one word w, so the candidate
-        // j they all test against is a shared-memory broadcast and the matrix accesses are conflict-free.
-        const int wn = (n + 31) >> 5, words = wn | 1;
-        if (threadIdx.x == 0) s_any = 1;     // re-used: 1 = every coordinate is small enough for 32-bit arithmetic
-        __syncthreads();
+        // A WARP takes rows r and n-1-r (r + (n-1-r) partners: balanced) and walks each row 32 partners at a time: lane = j,
+        // control flow is warp-uniform, the similar lanes are found with one ballot and merged together.
         for (int i = threadIdx.x; i < n; i += kThreads) {
             const int lim = 1 << 28;
             if (abs(rx[i]) >= lim || abs(ry[i]) >= lim || abs(rw[i]) >= lim || abs(rh[i]) >= lim) s_any = 0;
         }
         __syncthreads();
         const bool small = s_any != 0;
-        for (int idx = threadIdx.x; idx < n * wn; idx += kThreads) {
-            const int w = idx / n, i = idx - w * n;
-            const int j0 = w << 5, j1 = min(n, j0 + 32);
-            const int xi = rx[i], yi = ry[i], wi = rw[i], hi = rh[i];
-            unsigned bits = 0;
-            if (small) {
-                // T is monotone in m and m <= wi + hi: |xi - xj| > T(wi + hi) rejects most pairs after one load
-                const int mi = wi + hi;
-                const int Tmax = mi < 0 ? -1 : (mi < kDeltaTable ? __ldg(delta_tab + mi) : (int)floor(P.eps * (double)mi * 0.5));
-                const bool pre = P.eps > 0.0;
-                for (int j = (pre && Tmax < 0) ? j1 : j0; j < j1; ++j) {
-                    const int xj = rx[j];
-                    const int d0 = abs(xi - xj);
-                    if (pre && d0 > Tmax) continue;
-                    const int yj = ry[j];
-                    const int d1 = abs(yi - yj);
-                    if (pre && d1 > Tmax) continue;
-                    const int wj = rw[j], hj = rh[j];
-                    const int m = min(wi, wj) + min(hi, hj);
-                    int T;
-                    if (m < 0) T = -1;
-                    else if (m < kDeltaTable) T = __ldg(delta_tab + m);
-                    else T = (int)floor(P.eps * (double)m * 0.5);
-                    const int d2 = abs(xi + wi - xj - wj), d3 = abs(yi + hi - yj - hj);
-                    if (d0 <= T && d1 <= T && d2 <= T && d3 <= T) bits |= 1u << (j & 31);
-                }
-            } else {
-                for (int j = j0; j < j1; ++j) {
-                    const int wj = rw[j], hj = rh[j];
-                    const long long m = (long long)min(wi, wj) + (long long)min(hi, hj);
-                    long long T;
-                    if (m < 0) T = -1;
-                    else if (m < kDeltaTable) T = __ldg(delta_tab + (int)m);
-                    else T = (long long)floor(P.eps * (double)m * 0.5);
-                    const int xj = rx[j], yj = ry[j];
-                    const long long d0 = llabs((long long)xi - xj), d1 = llabs((long long)yi - yj);
-                    const long long d2 = llabs((long long)xi + wi - xj - wj), d3 = llabs((long long)yi + hi - yj - hj);
-                    if (d0 <= T && d1 <= T && d2 <= T && d3 <= T) bits |= 1u << (j & 31);
-                }
-            }
-            adj[i * words + w] = bits;
-        }
-        __syncthreads();
-        // 2b. min-label propagation over the bit matrix + pointer jumping until nothing changes
+        const bool pre = P.eps > 0.0;
         volatile int* vlab = lab;
-        for (;;) {
-            int changed = 0;
-            for (int i = threadIdx.x; i < n; i += kThreads) {
-                int m = vlab[i];
-                const unsigned* row = adj + (size_t)i * words;
-                for (int w = 0; w < wn; ++w) {
-                    unsigned bits = row[w];
-                    while (bits) {
-                        const int j = (w << 5) + __ffs(bits) - 1;
-                        bits &= bits - 1;
-                        const int lj = vlab[j];
-                        if (lj < m) m = lj;
+        const int lane = threadIdx.x & 31;
+        for (int r = threadIdx.x >> 5; 2 * r < n; r += kThreads / 32) {      // warp-uniform
+            for (int pass = 0; pass < 2; ++pass) {
+                const int i = pass ? n - 1 - r : r;
+                if (pass && i == r) break;
+                const int xi = rx[i], yi = ry[i], wi = rw[i], hi = rh[i];
+                // T is monotone in m and m <= wi + hi: |d| > T(wi + hi) rejects most pairs before the table look-up
+                const int mi = wi + hi;
+                int Tmax = 0;
+                if (small) {
+                    Tmax = mi < 0 ? -1 : (mi < kDeltaTable ? __ldg(delta_tab + mi) : (int)floor(P.eps * (double)mi * 0.5));
+                    if (pre && Tmax < 0) continue;
+                }
+                for (int j0 = 0; j0 < i; j0 += 32) {
+                    const int j = j0 + lane;
+                    const bool valid = j < i;
+                    bool sim = false;
+                    if (small) {
+                        int xj = 0, yj = 0, d0 = 0, d1 = 0;
+                        bool cand = false;
+                        if (valid) {
+                            xj = rx[j]; yj = ry[j];
+                            d0 = abs(xi - xj); d1 = abs(yi - yj);
+                            cand = !pre || (d0 <= Tmax && d1 <= Tmax);
+                        }
+                        if (!__any_sync(0xffffffffu, cand)) continue;
+                        if (cand) {
+                            const int wj = rw[j], hj = rh[j];
+                            const int m = min(wi, wj) + min(hi, hj);
+                            int T;
+                            if (m < 0) T = -1;
+                            else if (m < kDeltaTable) T = __ldg(delta_tab + m);
+                            else T = (int)floor(P.eps * (double)m * 0.5);
+                            const int d2 = abs(xi + wi - xj - wj), d3 = abs(yi + hi - yj - hj);
+                            sim = d0 <= T && d1 <= T && d2 <= T && d3 <= T;
+                        }
+                    } else if (valid) {
+                        const int xj = rx[j], yj = ry[j], wj = rw[j], hj = rh[j];
+                        const long long m = (long long)min(wi, wj) + (long long)min(hi, hj);
+                        long long T;
+                        if (m < 0) T = -1;
+                        else if (m < kDeltaTable) T = __ldg(delta_tab + (int)m);
+                        else T = (long long)floor(P.eps * (double)m * 0.5);
+                        const long long d0 = llabs((long long)xi - xj), d1 = llabs((long long)yi - yj);
+                        const long long d2 = llabs((long long)xi + wi - xj - wj), d3 = llabs((long long)yi + hi - yj - hj);
+                        sim = d0 <= T && d1 <= T && d2 <= T && d3 <= T;
+                    }
+                    if (!__any_sync(0xffffffffu, sim)) continue;
+                    // merge i with all its similar j of this chunk: every tree involved is hooked under the smallest root
+                    // seen; a failed hook (the root was taken by another warp meanwhile) is found again in the next round
+                    for (;;) {
+                        const int ri = __shfl_sync(0xffffffffu, uf_find(vlab, i), 0);
+                        const int rj = sim ? uf_find(vlab, j) : ri;
+                        const int tt = min(__reduce_min_sync(0xffffffffu, rj), ri);
+                        bool again = false;
+                        if (rj != tt) { atomicCAS(lab + rj, rj, tt); again = true; }
+                        if (ri != tt) { if (lane == 0) atomicCAS(lab + ri, ri, tt); again = true; }
+                        if (!__any_sync(0xffffffffu, again)) break;
                     }
                 }
-                if (m < vlab[i]) { vlab[i] = m; changed = 1; }
             }
-            __syncthreads();
-            for (int i = threadIdx.x; i < n; i += kThreads) {   // pointer jumping
-                int l = vlab[i];
-                while (vlab[l] < l) l = vlab[l];
-                if (l < vlab[i]) { vlab[i] = l; changed = 1; }
-            }
-            if (!__syncthreads_or(changed)) break;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += kThreads) {   // flatten: every member points at its root
+            const int root = uf_find(vlab, i);
+            vlab[i] = root;
         }
     }
-    // ---- 3. per-class integer sums (the bit matrix is dead: its memory becomes the sums)
+    // ---- 3. per-class integer sums
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += kThreads) sx[i] = sy[i] = sw[i] = sh[i] = cnt[i] = 0;
     __syncthreads();
@@ -240,22 +253,33 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
         dyr[i] = __double2int_rn((double)sh[i] * P.eps);
     }
     __syncthreads();
-    // ---- 5. threshold on member count + containment filter, then vote_boxes' height filter; ordered output
-    int nout = 0;
+    // ---- 5. threshold on member count: the surviving classes, compacted in index (= cv::partition class) order ...
+    int ns = 0;
     for (int base = 0; base < n; base += kThreads) {
         const int i = base + threadIdx.x;
+        const bool f = i < n && lab[i] == i && (P.group_threshold <= 0 || cnt[i] > P.group_threshold);
+        int tot;
+        const int off = block_scan_flag(f, warp_tot, &tot);
+        if (f) strong[ns + off] = i;
+        ns += tot;
+    }
+    __syncthreads();
+    // ... then the containment filter among them and vote_boxes' height filter; ordered output
+    int nout = 0;
+    for (int base = 0; base < ns; base += kThreads) {
+        const int k = base + threadIdx.x;
         bool keep = false;
-        int n1 = 0;
-        if (i < n && lab[i] == i) {
+        int i = 0, n1 = 0;
+        if (k < ns) {
+            i = strong[k];
             n1 = cnt[i];
-            if (P.group_threshold <= 0) keep = true;
-            else if (n1 > P.group_threshold) {
-                keep = true;
+            keep = true;
+            if (P.group_threshold > 0) {
                 const int x1 = sx[i], y1 = sy[i], w1 = sw[i], h1 = sh[i];
-                for (int j = 0; j < n; ++j) {
-                    if (j == i || lab[j] != j) continue;
+                for (int q = 0; q < ns; ++q) {
+                    const int j = strong[q];
+                    if (j == i) continue;
                     const int n2 = cnt[j];
-                    if (n2 <= P.group_threshold) continue;
                     const int x2 = sx[j], y2 = sy[j], w2 = sw[j], h2 = sh[j];
                     const int dx = dxr[j], dy = dyr[j];
                     if (x1 >= x2 - dx && y1 >= y2 - dy && x1 + w1 <= x2 + w2 + dx && y1 + h1 <= y2 + h2 + dy &&
@@ -267,9 +291,9 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
         int tot;
         const int off = block_scan_flag(keep, warp_tot, &tot);
         if (keep) {
-            const int k = nout + off;
-            if (k < FCNOD_MAX_DET) {
-                int32_t* o = out + k * 6;
+            const int o_k = nout + off;
+            if (o_k < FCNOD_MAX_DET) {
+                int32_t* o = out + o_k * 6;
                 o[0] = sx[i]; o[1] = sy[i]; o[2] = sw[i]; o[3] = sh[i];
                 o[4] = (int)log((double)n1);                               // int(math.log(weight)) (:347,:123)
                 o[5] = n1;
@@ -345,12 +369,12 @@ void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg
     int* delta_tab = static_cast<int*>(scratch) + (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1);
     delta_table_kernel<<<kDeltaTable / 256, 256, 0, stream>>>(p.eps, delta_tab);
     FCNOD_CUDA(cudaGetLastError());
-    const size_t adj_bytes = std::max((size_t)gh * gw * ((gh * gw + 31) / 32), (size_t)7 * gh * gw) * sizeof(unsigned);
+    const size_t adj_bytes = (size_t)8 * gh * gw * sizeof(unsigned);
     static bool attr_set[64] = {false};
     int dev = 0;
     FCNOD_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {     // first call on a device happens outside any graph capture
-        FCNOD_CUDA(cudaFuncSetAttribute(decode_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        FCNOD_CUDA(cudaFuncSetAttribute(decode_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
         attr_set[dev] = true;
     }
     decode_group_kernel<<<dim3(ncls, B), kThreads, adj_bytes, stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, delta_tab, cls_det, cls_cnt);
