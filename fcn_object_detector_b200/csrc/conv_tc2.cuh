@@ -52,6 +52,7 @@ struct ConvTc2Params {
     int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
     int halo;                // 1 = HALO mode
     int m_tiles, n_tiles, BN;
+    int step_nt, step_tx, step_ty, step_img;   // the grid size written in the mixed radix (img, ty, tx, nt): tile t -> t + grid
     int a_stages, b_stages;
     int b_taps;              // K-blocks per B stage: 1, or kw in HALO mode (one kernel row of taps per TMA / barrier round)
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
@@ -107,6 +108,22 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// mbarrier wait whose try_wait carries a suspend-time hint: the thread sleeps in hardware until the phase completes
+// (or the hint expires) instead of burning issue slots that the epilogue warps need
+__device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity) {
+    for (uint32_t it = 0; it < (1u << 22); ++it) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(20000u)
+            : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
 // wait with back-off, for the warps that wait long (keeps their spinning out of the issue slots of the TMA / MMA threads)
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
     for (uint32_t it = 0; it < (1u << 22); ++it) {
@@ -116,6 +133,26 @@ __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
     __trap();
 }
 }  // namespace tc
+
+// Tile t = ((img * tiles_y + ty) * tiles_x + tx) * n_tiles + nt, walked with stride gridDim.x: one division chain at the
+// start, then carries (the stride's digits come precomputed in the parameters).
+struct TileIter {
+    int nt, tx, ty, img;
+    __device__ __forceinline__ void init(int t, const ConvTc2Params& p) {
+        nt = t % p.n_tiles;
+        const int mt = t / p.n_tiles, tpi = p.tiles_x * p.tiles_y;
+        img = mt / tpi;
+        const int trem = mt - img * tpi;
+        ty = trem / p.tiles_x;
+        tx = trem - ty * p.tiles_x;
+    }
+    __device__ __forceinline__ void next(const ConvTc2Params& p) {
+        nt += p.step_nt; if (nt >= p.n_tiles) { nt -= p.n_tiles; ++tx; }
+        tx += p.step_tx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
+        ty += p.step_ty; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++img; }
+        img += p.step_img;
+    }
+};
 
 // KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0
 template <int KSTEPS, bool HALO, bool PROF>
@@ -138,7 +175,6 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total_tiles = p.m_tiles * p.n_tiles;
-    const int tpi = p.tiles_x * p.tiles_y;
     const int taps = p.kh * p.kw;
     const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
 
@@ -179,18 +215,18 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             if (nst < 2) { idx_mask = 0u; if (par) par = 2u; }      // par 2 never matches: the odd warp idles
             uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
             int tile_i = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tile_i) {
-                const int nt = t % p.n_tiles, mt = t / p.n_tiles;
-                const int n_img = mt / tpi, trem = mt - n_img * tpi;
-                const int ty = trem / p.tiles_x, tx = trem - ty * p.tiles_x;
-                const int oh0 = ty * p.BH - p.pad_h, ow0 = tx * p.BW - p.pad_w, n0 = nt * p.BN;
+            TileIter ti;
+            ti.init(blockIdx.x, p);
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tile_i, ti.next(p)) {
+                const int n_img = ti.img;
+                const int oh0 = ti.ty * p.BH - p.pad_h, ow0 = ti.tx * p.BW - p.pad_w, n0 = ti.nt * p.BN;
                 if (!ringB) {
                     // ---- A: one box per channel chunk (HALO) or per (tap, chunk) (TAP)
                     for (int r = 0; r < (HALO ? 1 : p.kh); ++r)
                         for (int s = 0; s < (HALO ? 1 : p.kw); ++s)
                             for (int cc = 0; cc < p.n_cchunks; ++cc, ++idx) {
                                 if ((idx & idx_mask) == par) {
-                                    mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                    mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
                                     mbar_expect_tx(full0 + 8u * sg, p.a_tx_bytes);
                                     tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
                                 }
@@ -207,7 +243,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             for (int r = 0; r < p.kh; ++r)
                                 for (int s = 0; s < p.kw; s += p.b_taps, ++idx, ++ev) {
                                     if ((idx & idx_mask) == par) {
-                                        mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                        mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
                                         if (PROF) FCNOD_PROF(0, tile_i, ev);
                                         mbar_expect_tx(full0 + 8u * sg, b_tx);
                                         tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, (r * p.n_cchunks + cc) * p.kw + s);
@@ -219,7 +255,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                         const int nkb = taps * p.n_cchunks;
                         for (int kb = 0; kb < nkb; ++kb, ++idx, ++ev) {
                             if ((idx & idx_mask) == par) {
-                                mbar_wait(empty0 + 8u * sg, ph ^ 1u);
+                                mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
                                 if (PROF) FCNOD_PROF(0, tile_i, ev);
                                 mbar_expect_tx(full0 + 8u * sg, b_tx);
                                 tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, kb);
@@ -247,7 +283,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
                 const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
                 if (PROF) FCNOD_PROF(1, it, 61);
-                mbar_wait(tempty0 + 8u * acc, aphase ^ 1u);          // the epilogue has drained this accumulator
+                mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);          // the epilogue has drained this accumulator
                 fence_after();
                 if (PROF) FCNOD_PROF(1, it, 62);
                 const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
@@ -255,7 +291,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 int ev = 0;
                 int cc = 0;
                 for (int ai = 0; ai < a_iters; ++ai) {
-                    mbar_wait(afull0 + 8u * sa, pa);
+                    mbar_wait_hint(afull0 + 8u * sa, pa);
                     const int ks = (cc == p.n_cchunks - 1) ? p.ksteps_last : KSTEPS;   // skip all-zero K steps
                     if (++cc == p.n_cchunks) cc = 0;
                     uint32_t a_row = a_lo;
@@ -263,7 +299,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                         int in_stage = 0;                  // taps already consumed from the current B stage
                         for (int s = 0; s < (HALO ? p.kw : 1); ++s) {
                             if (in_stage == 0) {
-                                mbar_wait(bfull0 + 8u * sb, pb);
+                                mbar_wait_hint(bfull0 + 8u * sb, pb);
                                 fence_after();
                                 if (PROF) FCNOD_PROF(1, it, ev);
                             }
@@ -296,6 +332,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         }
     } else {
         // ================= epilogue: 8 warps; warp w drains TMEM lane quadrant w % 4, column half (w - 5) / 4 ===========
+        // Everything that does not change from tile to tile is computed once: the lane's position inside the pixel box,
+        // the read-back mapping, and (per N tile) the bias staging and the destination segment of the lane's piece.
         const int ew = warp - (kTcMmaWarp + 1);
         const int q = warp & 3, half = ew >> 2;
         const int HW = p.H * p.W;
@@ -315,44 +353,48 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         int PL = 1;
         while (PL < cpr) PL <<= 1;
         const int rb_piece = lane & (PL - 1), rb_sub = lane / PL, rb_rows = 32 / PL;
+        const int m = q * 32 + lane;                // accumulator row
+        const int py = m / p.PW, px = m - py * p.PW;
+        const bool vpos = (py < p.BH) && (px < p.BW);
+        const int ncc = p.bt_lo_w + p.bt_hi_w + 1;
+        int cur_nt = -1, n0 = 0;
+        bf16* rb_seg = nullptr;                     // destination of this lane's read-back piece, image 0
+        size_t rb_ld = 0;
         int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        TileIter ti;
+        ti.init(blockIdx.x, p);
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it, ti.next(p)) {
             const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
-            const int nt = t % p.n_tiles, mt = t / p.n_tiles;
-            const int n_img = mt / tpi, trem = mt - n_img * tpi;
-            const int ty = trem / p.tiles_x, tx = trem - ty * p.tiles_x;
-            const int n0 = nt * p.BN + wc0;             // first fused-N column of this warp
-            const int m = q * 32 + lane;                // accumulator row
-            const int py = m / p.PW, px = m - py * p.PW;
-            const int oh = ty * p.BH + py, ow = tx * p.BW + px;
-            const bool valid = (py < p.BH) && (px < p.BW) && (oh < p.H) && (ow < p.W);
-            const int pix_in_img = valid ? oh * p.W + ow : -1;
-            // bias of this warp's columns -> shared memory (overlaps the wait for the accumulator)
-            if (wcols > 0) {
+            const int n_img = ti.img;
+            if (ti.nt != cur_nt) {
+                cur_nt = ti.nt;
+                n0 = cur_nt * p.BN + wc0;               // first fused-N column of this warp
+                __syncwarp();
                 for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);
+                rb_seg = nullptr;
+                if (!(p.flags & SEG_DIRECT) && rb_piece < cpr) {
+                    const int col = n0 + rb_piece * 8;
+                    int si = 0;
+#pragma unroll
+                    for (int s = 1; s < 4; ++s)
+                        if (s < p.nseg && col >= p.seg[s].col0) si = s;
+                    const int cl = col - p.seg[si].col0;
+                    if (cl < p.seg[si].ncols) {
+                        rb_ld = (size_t)p.seg[si].ldo;
+                        rb_seg = static_cast<bf16*>(p.seg[si].out) + cl;
+                    }
+                }
+                __syncwarp();
             }
+            const int oh = ti.ty * p.BH + py, ow = ti.tx * p.BW + px;
+            const bool valid = vpos && (oh < p.H) && (ow < p.W);
+            const int pix_in_img = valid ? oh * p.W + ow : -1;
             const float* gbias = nullptr;               // border pixels of the first convolution: per-class bias
             if (p.bias_tab && valid) {
-                const int cls = border_class(oh, p.H, p.bt_lo_h, p.bt_hi_h) * (p.bt_lo_w + p.bt_hi_w + 1) +
-                                border_class(ow, p.W, p.bt_lo_w, p.bt_hi_w);
+                const int cls = border_class(oh, p.H, p.bt_lo_h, p.bt_hi_h) * ncc + border_class(ow, p.W, p.bt_lo_w, p.bt_hi_w);
                 if (cls != p.bt_interior) gbias = p.bias_tab + (size_t)cls * p.bt_ld + n0;
             }
-            // destination of this lane's read-back piece (loop invariant over the rows)
-            bf16* rb_out = nullptr;
-            size_t rb_ld = 0;
-            if (!(p.flags & SEG_DIRECT) && rb_piece < cpr) {
-                const int col = n0 + rb_piece * 8;
-                int si = 0;
-#pragma unroll
-                for (int s = 1; s < 4; ++s)
-                    if (s < p.nseg && col >= p.seg[s].col0) si = s;
-                const int cl = col - p.seg[si].col0;
-                if (cl < p.seg[si].ncols) {
-                    rb_ld = (size_t)p.seg[si].ldo;
-                    rb_out = static_cast<bf16*>(p.seg[si].out) + (size_t)n_img * HW * rb_ld + cl;
-                }
-            }
-            __syncwarp();
+            bf16* const rb_out = rb_seg ? rb_seg + (size_t)n_img * HW * rb_ld : nullptr;
             if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 0);
             mbar_wait_sleep(tfull0 + 8u * acc, aphase);
             fence_after();

@@ -765,6 +765,13 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 8 * 32 * (size_t)p.row_bytes +
                  8 * 512 + 512 + 1024;
     st.tc_grid = std::min(p.m_tiles * p.n_tiles, kNumSMs);
+    {   // the grid stride in the mixed radix (img, ty, tx, nt) of the tile index (TileIter::next)
+        int g = st.tc_grid;
+        p.step_nt = g % p.n_tiles; g /= p.n_tiles;
+        p.step_tx = g % p.tiles_x; g /= p.tiles_x;
+        p.step_ty = g % p.tiles_y; g /= p.tiles_y;
+        p.step_img = g;
+    }
     p.nseg = (int)st.segs.size();
     p.flags = st.segs[0].flags & (SEG_RELU | SEG_DIRECT);
     p.bt_interior = cw.bt_lo_h * (cw.bt_lo_w + cw.bt_hi_w + 1) + cw.bt_lo_w;

@@ -1,12 +1,8 @@
 #!/bin/bash
-# Quick GPU iteration: selected tests (each group in its own process), then the bench.
+# quick GPU check after a kernel change: conv/net parity tests, then the bench line and per-launch table
 mkdir -p gpurun_out
-: > gpurun_out/summary.txt
-run() { local name=$1; shift; local to=$1; shift
-  timeout $to python -m pytest "$@" -q -m gpu -x --no-header -p no:cacheprovider > gpurun_out/$name.log 2>&1
-  echo "$name rc=$?" | tee -a gpurun_out/summary.txt; tail -4 gpurun_out/$name.log; }
-run stem 300 tests/test_net_gpu.py -k "s2d"
-run net_bf16 600 tests/test_net_gpu.py -k "bf16 or mini"
-run detect 300 tests/test_detect_gpu.py
-timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+timeout 900 python -m pytest tests/test_net_gpu.py tests/test_detect_gpu.py -q -m gpu -x --no-header -p no:cacheprovider 2>&1 | tail -4
+timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/q_bench.json 2> gpurun_out/q_bench.err; echo "bench rc=$?"
+python -c "
+import json; d=json.load(open('gpurun_out/q_bench.json')); print('fps', round(d['value']), 'ms/step', round(d['ms_per_step'],3), 'e2e', round(d['e2e']['value']), 'roof', round(d['roofline']['frac'],3))"
+python tools/show_launches.py gpurun_out/per_launch_ms.json
