@@ -10,7 +10,8 @@
 //   * Separate shared-memory rings for A (activations) and B (weights), each with full / empty mbarriers.
 //   * HALO mode for k x k convolutions (3x3 pad 1, 5x5 pad 2 of /root/reference/models/deploy.prototxt): per 64-channel
 //     chunk ONE TMA box brings the (BH+k-1) x (BW+k-1) input patch of the tile; it lands densely as
-//     [patch pixel][64 ch] = 128-byte swizzled rows.  Tap (r, s) is then the SAME shared-memory tile read through a
+//     [patch pixel][CK ch] = 128-byte swizzled rows (CK = 64), or 32-byte rows (CK = 16: the space-to-depth first
+//     convolution, whose pixels are 16 channels wide).  Tap (r, s) is then the SAME shared-memory tile read through a
 //     UMMA descriptor whose start address is shifted by r*(BW+k-1) + s rows: accumulator row i = py*(BW+k-1) + px
 //     reads patch pixel (py+r, px+s).  The 9 (25) taps re-use one load instead of 9 (25) shifted loads; rows with
 //     px >= BW are computed and discarded.  TAP mode (1x1, the space-to-depth first convolution) = one A box per K-block.
@@ -276,7 +277,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             const uint32_t a_lo_base = ((a_base & 0x3FFFFu) >> 4) | (1u << 16), a_lo_step = p.a_stage_bytes >> 4;
             const uint32_t b_lo_base = ((b_base & 0x3FFFFu) >> 4) | (1u << 16), b_lo_step = p.b_stage_bytes >> 4;
             const uint32_t b_tap_step = ((uint32_t)p.BN * span) >> 4;      // one tap tile inside a multi-tap B stage
-            const uint32_t row_step = (uint32_t)p.PW * 8u;      // HALO: one patch row = PW rows of 128 bytes, in 16-byte units
+            const uint32_t px_step = span >> 4;                  // HALO: one patch pixel = `span` bytes, in 16-byte units
+            const uint32_t row_step = (uint32_t)p.PW * px_step;  // HALO: one patch row = PW pixels
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
             int it = 0;
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                                 fence_after();
                                 if (PROF) FCNOD_PROF(1, it, ev);
                             }
-                            const uint32_t a_tap = a_row + (uint32_t)s * 8u;
+                            const uint32_t a_tap = a_row + (uint32_t)s * px_step;
                             const uint32_t b_tap = b_lo + (uint32_t)in_stage * b_tap_step;
 #pragma unroll
                             for (int k = 0; k < KSTEPS; ++k) {
@@ -430,44 +432,32 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 __syncwarp();
                 if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
             } else {
-                // ---- bf16 NHWC: drain 32 columns at a time; the TMEM load of the next chunk is in flight while this
-                //      one is biased / packed / staged.  Plain (non-volatile) shared-memory accesses: ptxas schedules them.
+                // ---- bf16 NHWC: drain 32 columns at a time: TMEM -> registers, + bias (staged in shared memory; the border
+                //      pixels of the first convolution take theirs from the class table), ReLU, pack, stage.
                 const bool any_g = __any_sync(0xffffffffu, gbias != nullptr);
-                uint32_t ra[32];
-                if (wcols > 0) {
-                    if (wcols >= 32) tmem_ld32(trow, ra);
-                    else tmem_ld16(trow, ra);
-                }
+                const float4* const bias4 = reinterpret_cast<const float4*>(bias_s);
                 for (int c = 0; c < wcols; c += 32) {
                     const int ncol = min(32, wcols - c);      // 32 or 16
-                    float bb[32];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 t4 = *reinterpret_cast<const float4*>(bias_s + c + 4 * j);
-                        bb[4 * j] = t4.x; bb[4 * j + 1] = t4.y; bb[4 * j + 2] = t4.z; bb[4 * j + 3] = t4.w;
-                    }
-                    if (any_g && gbias) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < ncol) bb[j] = __ldg(gbias + c + j);
-                    }
+                    uint32_t ra[32];
+                    if (ncol == 32) tmem_ld32(trow + (uint32_t)c, ra);
+                    else tmem_ld16(trow + (uint32_t)c, ra);
                     tmem_ld_wait_dep32(ra);
-                    uint32_t rc[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) rc[j] = ra[j];
-                    const int cn = c + 32;
-                    if (cn < wcols) {
-                        if (cn + 32 <= wcols) tmem_ld32(trow + (uint32_t)cn, ra);
-                        else tmem_ld16(trow + (uint32_t)cn, ra);
-                    }
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         if (8 * g < ncol) {
+                            float4 b0 = bias4[(c >> 2) + 2 * g], b1 = bias4[(c >> 2) + 2 * g + 1];
+                            if (any_g && gbias) {
+                                b0 = __ldg(reinterpret_cast<const float4*>(gbias + c + 8 * g));
+                                b1 = __ldg(reinterpret_cast<const float4*>(gbias + c + 8 * g + 4));
+                            }
                             float v[8];
+                            v[0] = __uint_as_float(ra[8 * g + 0]) + b0.x; v[1] = __uint_as_float(ra[8 * g + 1]) + b0.y;
+                            v[2] = __uint_as_float(ra[8 * g + 2]) + b0.z; v[3] = __uint_as_float(ra[8 * g + 3]) + b0.w;
+                            v[4] = __uint_as_float(ra[8 * g + 4]) + b1.x; v[5] = __uint_as_float(ra[8 * g + 5]) + b1.y;
+                            v[6] = __uint_as_float(ra[8 * g + 6]) + b1.z; v[7] = __uint_as_float(ra[8 * g + 7]) + b1.w;
+                            if (relu) {
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                v[j] = __uint_as_float(rc[8 * g + j]) + bb[8 * g + j];
-                                if (relu) v[j] = fmaxf(v[j], 0.f);
+                                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
                             }
                             uint4 pk;
                             __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);

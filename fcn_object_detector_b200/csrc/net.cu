@@ -651,10 +651,10 @@ const size_t kTcSmemBudget = 225 * 1024;
 
 // K layout of the packed weights (independent of the batch): channel-chunk width, HALO mode.
 void choose_tc_tiling(ConvWeights& cw) {
-    if (cw.s2d) {   // K-block = one kernel row of ka taps x 16 channels (or one tap, see setup_tc_step)
-        cw.CK = cw.ka * kS2dCpad;
+    if (cw.s2d) {   // K-block = one tap of the ka x ka convolution on the space-to-depth image: 16 channels = 32-byte rows
+        cw.CK = kS2dCpad;
         cw.n_cchunks = 1;
-        cw.halo = false;
+        cw.halo = true;
         return;
     }
     const char* nh = getenv("FCNOD_NO_HALO");
@@ -686,7 +686,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
     p.halo = cw.halo ? 1 : 0;
     if (cw.s2d) {
-        p.kh = cw.ka; p.kw = 1; p.CK = cw.ka * kS2dCpad;     // one K-block per kernel row (overlapping-window tensor map)
+        p.kh = p.kw = cw.ka; p.CK = kS2dCpad;                // HALO mode on the space-to-depth image, one K step per tap
         p.n_cchunks = 1;
         p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
         p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
@@ -811,9 +811,9 @@ void upload_weights(fcnod_net* net) {
             // bias[class(oh)][class(ow)][o] = b[o] + in_shift * sum over the taps that fall INSIDE the image.
             const int ka = cw.ka, off = cw.q - cw.pad, Kp = ka * ka * kS2dCpad;
             const int Nrows = (Cout + 15) / 16 * 16, Np = (int)align_up((size_t)(Cout + 7) / 8 * 8, 256) + 256;
-            // packed [K-block = kernel row ah][N][aw * 16 + (dy*2+dx)*Cin + c]
+            // packed [K-block = tap ah * ka + aw][N][(dy*2+dx)*Cin + c]  (HALO order: the taps of a kernel row adjacent)
             std::vector<bf16> w((size_t)Nrows * Kp, __float2bfloat16(0.f));
-            const size_t kbs = (size_t)Nrows * ka * kS2dCpad;
+            const size_t kbs = (size_t)Nrows * kS2dCpad;
             for (int o = 0; o < Cout; ++o)
                 for (int ah = 0; ah < ka; ++ah)
                     for (int aw = 0; aw < ka; ++aw)
@@ -822,7 +822,7 @@ void upload_weights(fcnod_net* net) {
                                 const int r = 2 * ah + dy - off, sx = 2 * aw + dx - off;
                                 if (r < 0 || r >= k || sx < 0 || sx >= k) continue;
                                 for (int c = 0; c < Cin; ++c)
-                                    w[ah * kbs + (size_t)o * ka * kS2dCpad + (size_t)aw * kS2dCpad + (dy * 2 + dx) * Cin + c] =
+                                    w[(size_t)(ah * ka + aw) * kbs + (size_t)o * kS2dCpad + (dy * 2 + dx) * Cin + c] =
                                         __float2bfloat16(cw.in_scale * cw.w[(((size_t)o * Cin + c) * k + r) * k + sx]);
                             }
             FCNOD_CUDA(cudaMalloc(&cw.d_w_tc, w.size() * 2));
@@ -969,12 +969,13 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         fill_tc_geometry(net, st, B);
         ConvTc2Params& p = st.tc;
         const uint32_t span = p.CK * 2;
-        cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)W2, (cuuint64_t)H2, (cuuint64_t)B};
+        (void)W2;
+        cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)Wp, (cuuint64_t)H2, (cuuint64_t)B};
         cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
-        cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
+        cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.PW, (cuuint32_t)(p.BH + p.kh - 1), 1};
         CUresult r = encode_map(&st.tmap_a, base, 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
-        encode_weight_map(st, cw, Nrows, cw.ka, L.name);
+        encode_weight_map(st, cw, Nrows, cw.ka * cw.ka, L.name);
         bind_tc_pointers(net, st);
         return;
     }
@@ -1097,7 +1098,11 @@ template <bool PROF>
 void launch_conv_tc2_p(const Step& st, cudaStream_t s) {
     const int ks = st.tc.CK / 16;
     const dim3 g(st.tc_grid), b(kConvTc2Threads);
-    if (st.tc.halo) { FCNOD_CHECK(ks == 4, "HALO mode needs CK = 64"); conv_tc2_kernel<4, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc); }
+    if (st.tc.halo) {
+        FCNOD_CHECK(ks == 4 || ks == 1, "HALO mode needs CK = 64 or 16");
+        if (ks == 4) conv_tc2_kernel<4, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+        else conv_tc2_kernel<1, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    }
     else if (ks == 4) conv_tc2_kernel<4, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
     else if (ks == 2) conv_tc2_kernel<2, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
     else conv_tc2_kernel<1, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
@@ -1113,6 +1118,8 @@ void conv_tc2_set_smem_limit() {
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
