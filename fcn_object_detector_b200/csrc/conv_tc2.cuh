@@ -53,7 +53,9 @@ struct ConvTc2Params {
     int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
     int halo;                // 1 = HALO mode
     int m_tiles, n_tiles, BN;
-    int step_nt, step_tx, step_ty, step_img;   // the grid size written in the mixed radix (img, ty, tx, nt): tile t -> t + grid
+    int mstride;                               // pixel tiles between two visits of one CTA = gridDim.x / n_tiles
+    int step_tx, step_ty, step_img;            // mstride written in the mixed radix (img, ty, tx)
+    int b_resident;                            // 1 = the B ring holds the whole K extent of the CTA's N tile: loaded once
     int a_stages, b_stages;
     int b_taps;              // K-blocks per B stage: 1, or kw in HALO mode (one kernel row of taps per TMA / barrier round)
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
@@ -135,20 +137,22 @@ __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
 }
 }  // namespace tc
 
-// Tile t = ((img * tiles_y + ty) * tiles_x + tx) * n_tiles + nt, walked with stride gridDim.x: one division chain at the
-// start, then carries (the stride's digits come precomputed in the parameters).
+// A CTA owns ONE N tile (nt = blockIdx.x % n_tiles: its weights can stay in shared memory) and walks the pixel tiles
+// mt = blockIdx.x / n_tiles, + mstride, ...; mt = (img * tiles_y + ty) * tiles_x + tx is decomposed once, then advanced
+// with carries (the stride's digits come precomputed in the parameters).
 struct TileIter {
-    int nt, tx, ty, img;
-    __device__ __forceinline__ void init(int t, const ConvTc2Params& p) {
-        nt = t % p.n_tiles;
-        const int mt = t / p.n_tiles, tpi = p.tiles_x * p.tiles_y;
+    int mt, tx, ty, img;
+    __device__ __forceinline__ void init(const ConvTc2Params& p) {
+        mt = (int)blockIdx.x / p.n_tiles;
+        const int tpi = p.tiles_x * p.tiles_y;
         img = mt / tpi;
         const int trem = mt - img * tpi;
         ty = trem / p.tiles_x;
         tx = trem - ty * p.tiles_x;
     }
+    __device__ __forceinline__ bool valid(const ConvTc2Params& p) const { return mt < p.m_tiles; }
     __device__ __forceinline__ void next(const ConvTc2Params& p) {
-        nt += p.step_nt; if (nt >= p.n_tiles) { nt -= p.n_tiles; ++tx; }
+        mt += p.mstride;
         tx += p.step_tx; if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
         ty += p.step_ty; if (ty >= p.tiles_y) { ty -= p.tiles_y; ++img; }
         img += p.step_img;
@@ -175,7 +179,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t tmem_slot = tempty0 + 16u;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int total_tiles = p.m_tiles * p.n_tiles;
+    const int my_nt = (int)blockIdx.x % p.n_tiles;
     const int taps = p.kh * p.kw;
     const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
 
@@ -217,10 +221,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
             int tile_i = 0;
             TileIter ti;
-            ti.init(blockIdx.x, p);
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++tile_i, ti.next(p)) {
+            ti.init(p);
+            const int n0 = my_nt * p.BN;
+            for (; ti.valid(p); ++tile_i, ti.next(p)) {
+                if (ringB && p.b_resident && tile_i > 0) break;      // resident weights: loaded with the first tile only
                 const int n_img = ti.img;
-                const int oh0 = ti.ty * p.BH - p.pad_h, ow0 = ti.tx * p.BW - p.pad_w, n0 = ti.nt * p.BN;
+                const int oh0 = ti.ty * p.BH - p.pad_h, ow0 = ti.tx * p.BW - p.pad_w;
                 if (!ringB) {
                     // ---- A: one box per channel chunk (HALO) or per (tap, chunk) (TAP)
                     for (int r = 0; r < (HALO ? 1 : p.kh); ++r)
@@ -282,7 +288,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
             int it = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const bool resident = p.b_resident != 0;
+            for (int mt = (int)blockIdx.x / p.n_tiles; mt < p.m_tiles; mt += p.mstride, ++it) {
                 const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
                 if (PROF) FCNOD_PROF(1, it, 61);
                 mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);          // the epilogue has drained this accumulator
@@ -300,7 +307,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                     for (int r = 0; r < (HALO ? p.kh : 1); ++r, a_row += row_step) {
                         int in_stage = 0;                  // taps already consumed from the current B stage
                         for (int s = 0; s < (HALO ? p.kw : 1); ++s) {
-                            if (in_stage == 0) {
+                            if (in_stage == 0 && !(resident && it > 0)) {
                                 mbar_wait_hint(bfull0 + 8u * sb, pb);
                                 fence_after();
                                 if (PROF) FCNOD_PROF(1, it, ev);
@@ -316,7 +323,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             }
                             if (++in_stage == p.b_taps) {
                                 in_stage = 0;
-                                umma_commit(bempty0 + 8u * sb);
+                                if (!resident) umma_commit(bempty0 + 8u * sb);
                                 if (PROF) FCNOD_PROF(3, it, ev);
                                 ++ev;
                                 b_lo += b_lo_step;
@@ -364,12 +371,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         size_t rb_ld = 0;
         int it = 0;
         TileIter ti;
-        ti.init(blockIdx.x, p);
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it, ti.next(p)) {
+        ti.init(p);
+        for (; ti.valid(p); ++it, ti.next(p)) {
             const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
             const int n_img = ti.img;
-            if (ti.nt != cur_nt) {
-                cur_nt = ti.nt;
+            if (cur_nt < 0) {
+                cur_nt = my_nt;
                 n0 = cur_nt * p.BN + wc0;               // first fused-N column of this warp
                 __syncwarp();
                 for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);

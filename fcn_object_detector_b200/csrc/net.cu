@@ -717,6 +717,8 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     //   tile time = max(MMA issue, L2->smem bytes, epilogue) + fixed;  total = rounds over 148 persistent CTAs
     const int N8 = (cw.Cout + 7) / 8 * 8;
     double best_cost = -1;
+    const char* nres = getenv("FCNOD_NO_RESIDENT");
+    const bool no_resident = nres && nres[0] == '1';
     // real 16-wide K steps per tap (the last chunk may be partly zero fill)
     const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);
     for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
@@ -725,34 +727,56 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
         const int half0 = ceil_div(BN, 32) * 16;
         const uint32_t row_bytes = (uint32_t)align_up((size_t)half0 * 2, 128);
         const size_t fixed = 8 * 32 * (size_t)row_bytes + 8 * 512 + 512 + 1024;
+        // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
+        const int mslots = std::max(1, std::min(p.m_tiles, kNumSMs / nt));
+        const long rounds = ((long)p.m_tiles + mslots - 1) / mslots;
         for (int bt = (p.halo ? p.kw : 1); bt >= 1; bt = (bt > 1 ? 1 : 0)) {       // B stage = kw taps (HALO) or 1
             const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024) * bt;
-            int a_st, b_st;
-            if (p.halo) {
-                a_st = 2;      // the next tile's patch loads while this one is multiplied
-                if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
-                if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
-                b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
-            } else {
-                const size_t pair = (size_t)p.a_stage_bytes + b_stage;
-                if (fixed + 2 * pair > kTcSmemBudget) continue;
-                a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
-            }
-            // tensor pipe: BN/2 cycles per K step, at least 32 (the 128 x 16 A slice streams from smem at 128 B/clk);
-            // the one issuing thread: ~300 cycles per barrier round (wait + commit) + ~25 per MMA
-            const double mma = ksteps_tile * std::max(BN / 2.0, 32.0);
-            const double rounds_b = (double)taps * p.n_cchunks / bt;
-            const double issue = rounds_b * 300.0 + ksteps_tile * 25.0;
-            const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
-            const double load = (a_bytes + (double)BN * Kp * 2) / 30.0;                 // ~30 B/clk/SM seen from L2
-            const double epi = 12.0 * BN;
-            const double tile = std::max(std::max(mma, issue), std::max(load, epi)) + 500.0;
-            const long rounds = ((long)p.m_tiles * nt + kNumSMs - 1) / kNumSMs;
-            const double cost = rounds * tile;
-            if (best_cost < 0 || cost < best_cost) {
-                best_cost = cost;
-                p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st; p.b_taps = bt;
-                p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
+            const int rounds_b = taps * p.n_cchunks / bt;                               // B stages consumed per tile
+            // B streaming decides the tiling; the weights then stay resident when that very tiling leaves room for them
+            // (shrinking the N tile to make them fit costs more in tensor-pipe time than the loads it saves)
+            for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident) {
+                int a_st, b_st;
+                const int a_min = p.halo ? 1 : 2, a_max = p.halo ? 2 : 8;
+                if (resident) {
+                    // the whole K extent of the N tile stays in shared memory (loaded once per CTA)
+                    const size_t bres = (size_t)rounds_b * b_stage;
+                    if (!(best_cost >= 0 && p.n_tiles == nt && p.BN == BN && p.b_taps == bt && !p.b_resident)) continue;
+                    if (rounds_b > 24 || fixed + bres + (size_t)std::max(a_min, 2) * p.a_stage_bytes > kTcSmemBudget) continue;
+                    b_st = rounds_b;
+                    a_st = (int)std::min<size_t>(a_max, (kTcSmemBudget - fixed - bres) / p.a_stage_bytes);
+                    best_cost = 1e30;      // force the comparison below: same tiling, resident weights
+                } else if (p.halo) {
+                    a_st = 2;      // the next tile's patch loads while this one is multiplied
+                    if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
+                    if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
+                    b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
+                } else {
+                    const size_t pair = (size_t)p.a_stage_bytes + b_stage;
+                    if (fixed + 2 * pair > kTcSmemBudget) continue;
+                    a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
+                }
+                // tensor pipe: BN/2 cycles per K step, at least 32 (the 128 x 16 A slice streams from smem at 128 B/clk);
+                // the one issuing thread: ~300 cycles per barrier round (wait + commit) + ~25 per MMA
+                // measured (tools/micro/mma_rate.cu): one M=128 K=16 instruction takes max(93, 43 + N/2) cycles with both
+                // operands in shared memory, whose bandwidth (128 B/clk) the operand reads share with TMA and the epilogue
+                const double mma = ksteps_tile * std::max(93.0, 43.0 + BN / 2.0);
+                const double issue = (resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b) * 300.0 +
+                                     ksteps_tile * 25.0;
+                const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
+                const double b_bytes = resident ? 0.0 : (double)BN * Kp * 2;
+                const double load = (a_bytes + b_bytes) / 30.0;                            // ~30 B/clk/SM seen from L2
+                const double epi = 12.0 * BN;
+                const double smem = (ksteps_tile * (4096.0 + 32.0 * BN) + a_bytes + b_bytes + 4.0 * 128 * BN) / 128.0;
+                double tile = std::max(std::max(std::max(mma, smem), issue), std::max(load, epi)) + 500.0;
+                if (a_st < 2) tile += 0.5 * a_bytes / 30.0;                                // no A prefetch across tiles
+                const double cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 30.0 : 0.0);
+                if (best_cost < 0 || cost < best_cost) {
+                    best_cost = cost;
+                    p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st; p.b_taps = bt;
+                    p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
+                    p.b_resident = resident;
+                }
             }
         }
     }
@@ -764,10 +788,10 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
     st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 8 * 32 * (size_t)p.row_bytes +
                  8 * 512 + 512 + 1024;
-    st.tc_grid = std::min(p.m_tiles * p.n_tiles, kNumSMs);
-    {   // the grid stride in the mixed radix (img, ty, tx, nt) of the tile index (TileIter::next)
-        int g = st.tc_grid;
-        p.step_nt = g % p.n_tiles; g /= p.n_tiles;
+    p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
+    st.tc_grid = p.mstride * p.n_tiles;
+    {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
+        int g = p.mstride;
         p.step_tx = g % p.tiles_x; g /= p.tiles_x;
         p.step_ty = g % p.tiles_y; g /= p.tiles_y;
         p.step_img = g;
@@ -1403,7 +1427,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
             o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {
