@@ -22,7 +22,7 @@ namespace fcnod {
 template <bool FAST>
 __device__ __forceinline__ float lrn_scale(float sc, float beta) {
     if (FAST) {
-        if (beta == 0.75f) { float r = rsqrtf(sc); return r * sqrtf(r); }
+        if (beta == 0.75f) { const float r = rsqrtf(sc); return r * (r * rsqrtf(r)); }   // sc^-0.5 * (sc^-0.5)^0.5, 2 MUFU
         return __powf(sc, -beta);
     }
     return powf(sc, -beta);
@@ -111,6 +111,66 @@ __global__ void __launch_bounds__(256) pool_tile_kernel(const T* __restrict__ in
                 const int oh = oh0 + a, ow = ow0 + b;
                 if (oh < Ho && ow < Wo) m[a][b].store(out + ((size_t)(n * Ho + oh) * Wo + ow) * ldo + cg * 8);
             }
+    }
+}
+
+// ---- max pool 3x3 (stride 1 or 2), register marching ------------------------------------------------------------
+// CTA = 8 channel groups (8 x 16 bytes = one 128-byte line per pixel) x 32 output columns; every thread marches down a
+// strip of RS output rows carrying the horizontal 3-max of the input rows it shares with the next output row.  The three
+// columns a thread reads are also read by its neighbours in the same CTA, so a pixel leaves L2 once and is re-used from
+// L1 (the 2x2-block kernel above fetched every pixel from L2 four times).
+template <typename T, int S>
+__global__ void __launch_bounds__(256) pool3_march_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W,
+                                                          int ldi, int Ho, int Wo, int ldo, int p, int cg_chunks, int col_chunks,
+                                                          int strips, int RS) {
+    const int CG = C >> 3;
+    int b = blockIdx.x;
+    const int cgc = b % cg_chunks; b /= cg_chunks;
+    const int cc = b % col_chunks; b /= col_chunks;
+    const int strip = b % strips;
+    const int n = b / strips;
+    const int cg = cgc * 8 + (threadIdx.x & 7);
+    const int ow = cc * 32 + (threadIdx.x >> 3);
+    if (cg >= CG || ow >= Wo) return;
+    const int oh_begin = strip * RS, oh_end = min(Ho, oh_begin + RS);
+    const int iw0 = ow * S - p;
+    const T* img = in + (size_t)n * H * W * ldi + cg * 8;
+    // Out-of-image rows / columns are CLAMPED instead of skipped: the clamped pixel lies inside the same window, so the
+    // maximum is unchanged, and the loads are unconditional (the compiler keeps several rows in flight).
+    const size_t o0 = (size_t)max(iw0, 0) * ldi, o1 = (size_t)min(iw0 + 1, W - 1) * ldi, o2 = (size_t)min(iw0 + 2, W - 1) * ldi;
+    auto hmax_row = [&](int ih, Pack8<T>& m) {      // max over the 3 columns of input row ih
+        const T* row = img + (size_t)min(max(ih, 0), H - 1) * W * ldi;
+        Pack8<T> x, y;
+        m.load(row + o0); x.load(row + o1); y.load(row + o2);
+        m.max_with(x); m.max_with(y);
+    };
+    T* o = out + ((size_t)(n * Ho + oh_begin) * Wo + ow) * ldo + cg * 8;
+    if (S == 1) {
+        Pack8<T> r0, r1;
+        hmax_row(oh_begin - p, r0);
+        hmax_row(oh_begin - p + 1, r1);
+#pragma unroll 4
+        for (int oh = oh_begin; oh < oh_end; ++oh, o += (size_t)Wo * ldo) {
+            Pack8<T> r2;
+            hmax_row(oh - p + 2, r2);
+            Pack8<T> m = r0;
+            m.max_with(r1); m.max_with(r2);
+            m.store(o);
+            r0 = r1; r1 = r2;
+        }
+    } else {
+        Pack8<T> carry;
+        hmax_row(oh_begin * 2 - p, carry);
+#pragma unroll 2
+        for (int oh = oh_begin; oh < oh_end; ++oh, o += (size_t)Wo * ldo) {
+            Pack8<T> a, c;
+            hmax_row(oh * 2 - p + 1, a);
+            hmax_row(oh * 2 - p + 2, c);
+            Pack8<T> m = carry;
+            m.max_with(a); m.max_with(c);
+            m.store(o);
+            carry = c;
+        }
     }
 }
 
@@ -321,14 +381,14 @@ __global__ void __launch_bounds__(256) pool_lrn_tile_kernel(const T* __restrict_
 
 // ---- LRN -> Pooling -------------------------------------------------------------------------------------------
 // One CTA per (image, TH x TW output tile).  smem: T [(S*(TH-1)+K) * (S*(TW-1)+K)][C].
-template <typename T, int K, int S, int HALF, bool FAST, int TH, int TW>
+template <typename T, int K, int S, int HALF, bool FAST, int TH, int TW, int CGT>   // CGT = C / 8 when known at compile time, else 0
 __global__ void __launch_bounds__(512) lrn_pool_kernel(const T* __restrict__ in, T* __restrict__ out, int C, int H, int W,
                                                        int ldi, int Ho, int Wo, int ldo, int p, int tiles_x, int tiles_y,
                                                        float alpha_over_n, float beta, float kk) {
     extern __shared__ __align__(16) unsigned char lp_smem_raw[];
     T* tile = reinterpret_cast<T*>(lp_smem_raw);
     constexpr int RH = S * (TH - 1) + K, RW = S * (TW - 1) + K;
-    const int CG = C >> 3;
+    const int CG = CGT ? CGT : (C >> 3);
     int b = blockIdx.x;
     const int tx = b % tiles_x; b /= tiles_x;
     const int ty = b % tiles_y;
@@ -351,18 +411,32 @@ __global__ void __launch_bounds__(512) lrn_pool_kernel(const T* __restrict__ in,
             a.load(row + cg * 8);
 #pragma unroll
             for (int j = 0; j < 8; ++j) x[HALF + j] = a.v[j];
+            if (HALF == 2 && sizeof(T) == 2) {
+                // the two channels either side of the group: one 32-bit load each (4-byte aligned: cg*8 - 2 and cg*8 + 8)
+                const __nv_bfloat162 lo = cg > 0 ? *reinterpret_cast<const __nv_bfloat162*>(row + cg * 8 - 2) : __nv_bfloat162();
+                const __nv_bfloat162 hi = cg + 1 < CG ? *reinterpret_cast<const __nv_bfloat162*>(row + cg * 8 + 8) : __nv_bfloat162();
+                x[0] = cg > 0 ? __low2float(lo) : 0.f; x[1] = cg > 0 ? __high2float(lo) : 0.f;
+                x[8 + HALF] = cg + 1 < CG ? __low2float(hi) : 0.f; x[8 + HALF + 1] = cg + 1 < CG ? __high2float(hi) : 0.f;
+            } else {
 #pragma unroll
-            for (int d = 0; d < HALF; ++d) {
-                const int cl = cg * 8 - HALF + d, ch = cg * 8 + 8 + d;
-                x[d] = cl >= 0 ? to_f32<T>(row[cl]) : 0.f;
-                x[8 + HALF + d] = ch < C ? to_f32<T>(row[ch]) : 0.f;
+                for (int d = 0; d < HALF; ++d) {
+                    const int cl = cg * 8 - HALF + d, ch = cg * 8 + 8 + d;
+                    x[d] = cl >= 0 ? to_f32<T>(row[cl]) : 0.f;
+                    x[8 + HALF + d] = ch < C ? to_f32<T>(row[ch]) : 0.f;
+                }
             }
+            // sliding sum of squares over the 2*HALF+1 window
+            float sq[8 + 2 * HALF];
+#pragma unroll
+            for (int j = 0; j < 8 + 2 * HALF; ++j) sq[j] = x[j] * x[j];
+            float acc = 0.f;
+#pragma unroll
+            for (int d = 0; d < 2 * HALF; ++d) acc += sq[d];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                float acc = 0.f;
-#pragma unroll
-                for (int d = 0; d <= 2 * HALF; ++d) acc += x[j + d] * x[j + d];
+                acc += sq[j + 2 * HALF];
                 o.v[j] = x[j + HALF] * lrn_scale<FAST>(kk + alpha_over_n * acc, beta);
+                acc -= sq[j];
             }
         } else {
 #pragma unroll

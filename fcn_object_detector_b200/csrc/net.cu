@@ -1053,6 +1053,21 @@ void launch_pool(const fcnod_net* net, const Step& st, const LayerDef& L, cudaSt
     const Blob& ib = net->blobs[st.in];
     const Blob& ob = net->blobs[st.out];
     long items = (long)net->batch * ob.H * ob.W * (ib.C / 8);
+    if (L.kernel == 3 && (L.stride == 1 || L.stride == 2) && L.pad <= 1 && ib.C % 8 == 0 && !getenv("FCNOD_POOL_V1")) {
+        // register-marching kernel: CTA = 8 channel groups x 32 output columns x a strip of output rows
+        const int cg_chunks = ceil_div(ib.C / 8, 8), col_chunks = ceil_div(ob.W, 32);
+        const int RS = ob.H <= 14 ? ob.H : 14, strips = ceil_div(ob.H, RS);
+        const long blocks = (long)net->batch * strips * col_chunks * cg_chunks;
+        if (L.stride == 1)
+            pool3_march_kernel<T, 1><<<(unsigned)blocks, 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), ib.C, ib.H,
+                                                                      ib.W, ib.ldc, ob.H, ob.W, ob.ldc, L.pad, cg_chunks, col_chunks,
+                                                                      strips, RS);
+        else
+            pool3_march_kernel<T, 2><<<(unsigned)blocks, 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), ib.C, ib.H,
+                                                                      ib.W, ib.ldc, ob.H, ob.W, ob.ldc, L.pad, cg_chunks, col_chunks,
+                                                                      strips, RS);
+        return;
+    }
     if (L.kernel == 3 && (L.stride == 1 || L.stride == 2) && items < (1L << 31)) {
         // 2x2 output pixels per thread from one shared input window
         long blocks2 = (long)net->batch * ((ob.H + 1) / 2) * ((ob.W + 1) / 2) * (ib.C / 8);
@@ -1221,9 +1236,14 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             constexpr int TH = 4, TW = 8;
             const int tx = ceil_div(ob.W, TW), ty = ceil_div(ob.H, TH);
             size_t smem = (size_t)(2 * (TH - 1) + 3) * (2 * (TW - 1) + 3) * ib.C * 2;
-            lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW><<<tx * ty * net->batch, 512, smem, s>>>(
-                (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad, tx,
-                ty, L->alpha / L->local_size, L->beta, L->lrn_k);
+            if (ib.C == 192)
+                lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW, 24><<<tx * ty * net->batch, 512, smem, s>>>(
+                    (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad,
+                    tx, ty, L->alpha / L->local_size, L->beta, L->lrn_k);
+            else
+                lrn_pool_kernel<bf16, 3, 2, 2, true, TH, TW, 0><<<tx * ty * net->batch, 512, smem, s>>>(
+                    (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad,
+                    tx, ty, L->alpha / L->local_size, L->beta, L->lrn_k);
             break;
         }
         case S_CONV_SIMT: launch_conv_simt(net, st, *L, s); break;
@@ -1357,7 +1377,8 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     FCNOD_CHECK(prop.major == 10, "fcnod_b200 is built for sm_100a (Blackwell B200) only; found sm_" +
                                       std::to_string(prop.major) + std::to_string(prop.minor));
     conv_tc2_set_smem_limit();
-    FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(lrn_pool_kernel<bf16, 3, 2, 2, true, 4, 8, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_tile_kernel<bf16, 3, 2, 2, true, 4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
