@@ -56,6 +56,10 @@ struct ConvTc2Params {
     int mstride;                               // pixel tiles between two visits of one CTA = gridDim.x / n_tiles
     int step_tx, step_ty, step_img;            // mstride written in the mixed radix (img, ty, tx)
     int b_resident;                            // 1 = the B ring holds the whole K extent of the CTA's N tile: loaded once
+    int a_bulk;                                // 1 = HALO patch rows come by cp.async.bulk from a padded, pre-swizzled image
+    const void* a_src;                         //     its base, row pitch and image pitch in bytes
+    unsigned a_row_pitch;
+    unsigned long long a_img_pitch;
     int a_stages, b_stages;
     int b_taps;              // K-blocks per B stage: 1, or kw in HALO mode (one kernel row of taps per TMA / barrier round)
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
@@ -127,6 +131,12 @@ __device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity) {
     }
     __trap();
 }
+// plain (non-tensor) bulk copy global -> shared, completion on an mbarrier
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
 // wait with back-off, for the warps that wait long (keeps their spinning out of the issue slots of the TMA / MMA threads)
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
     for (uint32_t it = 0; it < (1u << 22); ++it) {
@@ -159,8 +169,9 @@ struct TileIter {
     }
 };
 
-// KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0
-template <int KSTEPS, bool HALO, bool PROF>
+// KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0,
+// KK = kernel size known at compile time in HALO mode (3, 4, 5; 0 = read it from the parameters)
+template <int KSTEPS, bool HALO, bool PROF, int KK>
 __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                                       const __grid_constant__ CUtensorMap tmap_b,
                                                                       const __grid_constant__ ConvTc2Params p) {
@@ -235,7 +246,17 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                                 if ((idx & idx_mask) == par) {
                                     mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
                                     mbar_expect_tx(full0 + 8u * sg, p.a_tx_bytes);
-                                    tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
+                                    if (HALO && p.a_bulk) {
+                                        // one plain bulk copy per patch row: PW pixels x `span` bytes, contiguous in the image
+                                        const uint32_t rb = (uint32_t)p.PW * span;
+                                        const char* src = static_cast<const char*>(p.a_src) + (size_t)n_img * p.a_img_pitch +
+                                                          (size_t)oh0 * p.a_row_pitch + (size_t)ow0 * span;
+                                        const int rows = p.BH + p.kh - 1;
+                                        for (int pr = 0; pr < rows; ++pr)
+                                            bulk_load(dst + (uint32_t)pr * rb, src + (size_t)pr * p.a_row_pitch, rb, full0 + 8u * sg);
+                                    } else {
+                                        tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
+                                    }
                                 }
                                 dst += st_bytes;
                                 if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
@@ -275,7 +296,10 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             }
         }
     } else if (warp == kTcMmaWarp) {
-        // ================= MMA issuer (one thread; descriptors advanced with 32-bit adds, K steps unrolled) ============
+        // ================= MMA issuer (one thread) ====================================================================
+        // The issuing thread is latency-bound on its OWN instruction stream (about 100 cycles per tcgen05.mma even in a
+        // bare loop, tools/micro/mma_rate.cu), so the tap loops are unrolled at compile time (KK = kernel size) and a
+        // whole kernel row of taps shares one barrier round.
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | (8u << 24);
             // descriptor = {lo: start address >> 4 | LBO 1 << 16, hi: SBO (8 rows) >> 4 | version 1 << 14 | swizzle << 29}
@@ -285,50 +309,77 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             const uint32_t b_tap_step = ((uint32_t)p.BN * span) >> 4;      // one tap tile inside a multi-tap B stage
             const uint32_t px_step = span >> 4;                  // HALO: one patch pixel = `span` bytes, in 16-byte units
             const uint32_t row_step = (uint32_t)p.PW * px_step;  // HALO: one patch row = PW pixels
+            const int kh = HALO ? (KK ? KK : p.kh) : 1, kw = HALO ? (KK ? KK : p.kw) : 1;
+            const bool bt_row = p.b_taps > 1;                    // a B stage holds the kw taps of one kernel row
+            const bool resident = p.b_resident != 0;
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
             int it = 0;
-            const bool resident = p.b_resident != 0;
             for (int mt = (int)blockIdx.x / p.n_tiles; mt < p.m_tiles; mt += p.mstride, ++it) {
                 const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
                 if (PROF) FCNOD_PROF(1, it, 61);
-                mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);          // the epilogue has drained this accumulator
+                mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);     // the epilogue has drained this accumulator
                 fence_after();
                 if (PROF) FCNOD_PROF(1, it, 62);
                 const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
+                const bool wait_b = !(resident && it > 0);
                 uint32_t accum = 0;
                 int ev = 0;
                 int cc = 0;
+                // all K steps of one tap: A window a_tap x B tile b_tap
+                auto issue_tap = [&](uint32_t a_tap, uint32_t b_tap, int ks) {
+#pragma unroll
+                    for (int k = 0; k < KSTEPS; ++k) {
+                        if (KSTEPS == 1 || k < ks) {
+                            umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_tap + 2u * k, desc_hi, idesc, accum);
+                            accum = 1;
+                        }
+                    }
+                };
+                auto b_wait = [&]() {
+                    if (wait_b) {
+                        mbar_wait_hint(bfull0 + 8u * sb, pb);
+                        fence_after();
+                        if (PROF) FCNOD_PROF(1, it, ev);
+                    }
+                };
+                auto b_release = [&]() {
+                    if (!resident) umma_commit(bempty0 + 8u * sb);
+                    if (PROF) { FCNOD_PROF(3, it, ev); ++ev; }
+                    b_lo += b_lo_step;
+                    if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
+                };
                 for (int ai = 0; ai < a_iters; ++ai) {
                     mbar_wait_hint(afull0 + 8u * sa, pa);
                     const int ks = (cc == p.n_cchunks - 1) ? p.ksteps_last : KSTEPS;   // skip all-zero K steps
                     if (++cc == p.n_cchunks) cc = 0;
-                    uint32_t a_row = a_lo;
-                    for (int r = 0; r < (HALO ? p.kh : 1); ++r, a_row += row_step) {
-                        int in_stage = 0;                  // taps already consumed from the current B stage
-                        for (int s = 0; s < (HALO ? p.kw : 1); ++s) {
-                            if (in_stage == 0 && !(resident && it > 0)) {
-                                mbar_wait_hint(bfull0 + 8u * sb, pb);
-                                fence_after();
-                                if (PROF) FCNOD_PROF(1, it, ev);
-                            }
-                            const uint32_t a_tap = a_row + (uint32_t)s * px_step;
-                            const uint32_t b_tap = b_lo + (uint32_t)in_stage * b_tap_step;
+                    if (!HALO) {
+                        b_wait();
+                        issue_tap(a_lo, b_lo, ks);
+                        b_release();
+                    } else {
+                        uint32_t a_row = a_lo;
 #pragma unroll
-                            for (int k = 0; k < KSTEPS; ++k) {
-                                if (k < ks) {
-                                    umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_tap + 2u * k, desc_hi, idesc, accum);
-                                    accum = 1;
+                        for (int r = 0; r < (KK ? KK : 8); ++r) {
+                            if (!KK && r >= kh) break;
+                            if (bt_row) {
+                                b_wait();
+#pragma unroll
+                                for (int s = 0; s < (KK ? KK : 8); ++s) {
+                                    if (!KK && s >= kw) break;
+                                    issue_tap(a_row + (uint32_t)s * px_step, b_lo + (uint32_t)s * b_tap_step, ks);
+                                }
+                                b_release();
+                            } else {
+#pragma unroll
+                                for (int s = 0; s < (KK ? KK : 8); ++s) {
+                                    if (!KK && s >= kw) break;
+                                    b_wait();
+                                    issue_tap(a_row + (uint32_t)s * px_step, b_lo, ks);
+                                    b_release();
                                 }
                             }
-                            if (++in_stage == p.b_taps) {
-                                in_stage = 0;
-                                if (!resident) umma_commit(bempty0 + 8u * sb);
-                                if (PROF) FCNOD_PROF(3, it, ev);
-                                ++ev;
-                                b_lo += b_lo_step;
-                                if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
-                            }
+                            a_row += row_step;
                         }
                     }
                     umma_commit(aempty0 + 8u * sa);

@@ -468,12 +468,15 @@ __global__ void __launch_bounds__(512) lrn_pool_kernel(const T* __restrict__ in,
 }
 
 // ---- data (NCHW fp32) -> scale*x -> 2x2 space-to-depth NHWC bf16, W-padded -------------------------------------
-// out[n][h2][PADL + w2][(dy*2+dx)*C + c] = bf16(in[n][c][2*h2+dy][2*w2+dx]);  channels >= 4*C and the pad
-// columns stay zero (written once at allocation).  Feeds the first convolution (stride 2) as a stride-1
+// out[n][PADL + h2][PADL + w2][(dy*2+dx)*C + c] = bf16(in[n][c][2*h2+dy][2*w2+dx]);  channels >= 4*C and the pad
+// rows / columns stay zero (written once at allocation).  Feeds the first convolution (stride 2) as a stride-1
 // tensor-core convolution (see net.cu: plan_conv_s2d).
 template <int CT>   // CT = channel count known at compile time (1..4, 16 output channels per pixel), or 0 = generic
 __global__ void __launch_bounds__(256) input_s2d_kernel(const float* __restrict__ in, bf16* __restrict__ out, int N, int C_rt,
-                                                        int H, int W, int Wp, int padl, int ldc) {
+                                                        int H, int W, int Wp, int Hp, int padl, int ldc) {
+    // The image is stored [N][Hp][Wp][16] with padl zero rows above / zero columns left of pixel (0, 0), and PRE-SWIZZLED
+    // for the 32-byte shared-memory swizzle of the first convolution's A operand: the two 16-byte halves of a pixel are
+    // exchanged when bit 2 of its physical column is set (a bulk copy of a row then lands already swizzled).
     const int C = CT > 0 ? CT : C_rt;
     // one thread per space-to-depth pixel: 2 rows x float2 per channel in (coalesced over w2), ldc bf16 out as 16-byte stores
     const int H2 = H >> 1, W2 = W >> 1;
@@ -499,19 +502,20 @@ __global__ void __launch_bounds__(256) input_s2d_kernel(const float* __restrict_
                     v[3 * CT + c] = __float2bfloat16_rn(r1.y);
                 }
             }
-            uint4* o = reinterpret_cast<uint4*>(out + ((size_t)(n * H2 + h2) * Wp + padl + w2) * 16);
-            o[0] = *reinterpret_cast<const uint4*>(v);
-            o[1] = *reinterpret_cast<const uint4*>(v + 8);
         } else {
-            bf16* o = out + ((size_t)(n * H2 + h2) * Wp + padl + w2) * ldc;
             for (int c = 0; c < C; ++c) {
                 const float* src = in + ((size_t)(n * C + c) * H + 2 * h2) * W + 2 * w2;
-                o[0 * C + c] = __float2bfloat16_rn(src[0]);
-                o[1 * C + c] = __float2bfloat16_rn(src[1]);
-                o[2 * C + c] = __float2bfloat16_rn(src[W]);
-                o[3 * C + c] = __float2bfloat16_rn(src[W + 1]);
+                v[0 * C + c] = __float2bfloat16_rn(src[0]);
+                v[1 * C + c] = __float2bfloat16_rn(src[1]);
+                v[2 * C + c] = __float2bfloat16_rn(src[W]);
+                v[3 * C + c] = __float2bfloat16_rn(src[W + 1]);
             }
         }
+        const int xp = padl + w2;
+        const int swz = (xp >> 2) & 1;
+        uint4* o = reinterpret_cast<uint4*>(out + ((size_t)(n * Hp + padl + h2) * Wp + xp) * 16);
+        o[swz] = *reinterpret_cast<const uint4*>(v);
+        o[swz ^ 1] = *reinterpret_cast<const uint4*>(v + 8);
     }
 }
 

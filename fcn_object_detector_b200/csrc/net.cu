@@ -105,6 +105,25 @@ struct ConvWeights {
 
 const int kS2dCpad = 16;       // channels per space-to-depth pixel (4*Cin padded)
 
+// Geometry of the padded, pre-swizzled space-to-depth image that feeds the first convolution with plain bulk copies
+// (cp.async.bulk, one per patch row): box widths are multiples of 8 pixels so that the 32-byte-swizzle phase of a pixel
+// in shared memory, (x >> 2) & 1, is the same as that of its physical column in global memory.
+struct S2dGeom { int BW, PW, BH, tiles_x, tiles_y, Wp, Hp; };
+static S2dGeom s2d_geom(int H2, int W2, int ka) {
+    S2dGeom g;
+    for (int ntx = (W2 + 127) / 128;; ++ntx) {
+        g.BW = ((W2 + ntx - 1) / ntx + 7) / 8 * 8;
+        g.PW = (g.BW + ka - 1 + 7) / 8 * 8;
+        if (g.PW <= 128) break;
+    }
+    g.BH = std::max(1, std::min(H2, 128 / g.PW));
+    g.tiles_x = (W2 + g.BW - 1) / g.BW;
+    g.tiles_y = (H2 + g.BH - 1) / g.BH;
+    g.Wp = (g.tiles_x - 1) * g.BW + g.PW;
+    g.Hp = g.tiles_y * g.BH + ka - 1;
+    return g;
+}
+
 struct Step {
     StepKind kind;
     std::string desc;
@@ -113,7 +132,7 @@ struct Step {
     int layer2 = -1;           // second layer of a fused pair (Pool->LRN, LRN->Pool)
     int conv = -1;             // index into convs
     int s2d_buf = -1;          // S_S2D / s2d convolution: buffer index of the space-to-depth image
-    int s2d_wp = 0, s2d_padl = 0;
+    int s2d_wp = 0, s2d_hp = 0, s2d_padl = 0;    // padded space-to-depth image: width, height, zero columns / rows before (0, 0)
     bool s2d_overlap = false;  // one K-block per kernel row (overlapping-window tensor map) vs one per tap
     bool relu = false;
     int unary_op = 0;
@@ -473,10 +492,11 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                     int ka = (q - Cn.pad + Cn.kernel + 1) / 2;
                     ka = ka <= 1 ? 1 : (ka <= 2 ? 2 : 4);
                     mk.make(top);   // virtual
-                    Buffer bu; bu.C = kS2dCpad; bu.H = si.H / 2; bu.W = si.W / 2 + ka - 1 + (q / 2); bu.dtype = DT_BF16;
+                    const S2dGeom sg = s2d_geom(si.H / 2, si.W / 2, ka);
+                    Buffer bu; bu.C = kS2dCpad; bu.H = sg.Hp; bu.W = sg.Wp; bu.dtype = DT_BF16;
                     net->buffers.push_back(bu);
                     st.kind = S_S2D; st.in = 0; st.out = -1;
-                    st.s2d_buf = (int)net->buffers.size() - 1; st.s2d_wp = bu.W; st.s2d_padl = q / 2;
+                    st.s2d_buf = (int)net->buffers.size() - 1; st.s2d_wp = sg.Wp; st.s2d_hp = sg.Hp; st.s2d_padl = q / 2;
                     st.desc = "s2d " + L.name + " (Power folded into " + Cn.name + ")";
                     net->steps.push_back(st);
                     break;
@@ -542,7 +562,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                     for (size_t sj = 0; sj < net->steps.size(); ++sj)
                         if (net->steps[sj].kind == S_S2D && net->steps[sj].layer == s2d_conv[(int)i]) {
                             st.s2d_buf = net->steps[sj].s2d_buf; st.s2d_wp = net->steps[sj].s2d_wp;
-                            st.s2d_padl = net->steps[sj].s2d_padl;
+                            st.s2d_padl = net->steps[sj].s2d_padl; st.s2d_hp = net->steps[sj].s2d_hp;
                         }
                     FCNOD_CHECK(st.s2d_buf >= 0, "internal: no space-to-depth buffer for '" + L.name + "'");
                     st.s2d_overlap = true;
@@ -688,7 +708,8 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     if (cw.s2d) {
         p.kh = p.kw = cw.ka; p.CK = kS2dCpad;                // HALO mode on the space-to-depth image, one K step per tap
         p.n_cchunks = 1;
-        p.pad_h = cw.q / 2; p.pad_w = 0;   // the W padding is physical (s2d_padl zero columns)
+        p.pad_h = 0; p.pad_w = 0;          // the padding is physical (zero rows / columns of the space-to-depth image)
+        p.a_bulk = 1;                      // A patch rows arrive by cp.async.bulk from the pre-swizzled image
         p.bt_lo_h = cw.bt_lo_h; p.bt_hi_h = cw.bt_hi_h; p.bt_lo_w = cw.bt_lo_w; p.bt_hi_w = cw.bt_hi_w;
     }
     p.ksteps_last = p.CK / 16;
@@ -702,6 +723,10 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     p.BH = std::max(1, std::min(ob.H, 128 / p.PW));
     p.tiles_x = ceil_div(ob.W, p.BW);
     p.tiles_y = ceil_div(ob.H, p.BH);
+    if (cw.s2d) {
+        const S2dGeom sg = s2d_geom(ob.H, ob.W, cw.ka);
+        p.BW = sg.BW; p.PW = sg.PW; p.BH = sg.BH; p.tiles_x = sg.tiles_x; p.tiles_y = sg.tiles_y;
+    }
     p.m_tiles = p.tiles_x * p.tiles_y * batch;
     const int taps = p.kh * p.kw;
     const int Kp = taps * p.n_cchunks * p.CK;
@@ -994,13 +1019,19 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         ConvTc2Params& p = st.tc;
         const uint32_t span = p.CK * 2;
         (void)W2;
-        cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)Wp, (cuuint64_t)H2, (cuuint64_t)B};
-        cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)H2 * Wp * pix};
+        (void)H2;       // the tensor map is only a valid placeholder in bulk mode (the kernel prefetches it)
+        cuuint64_t dims[4] = {(cuuint64_t)p.CK, (cuuint64_t)Wp, (cuuint64_t)st.s2d_hp, (cuuint64_t)B};
+        cuuint64_t strides[3] = {pix, (cuuint64_t)Wp * pix, (cuuint64_t)st.s2d_hp * Wp * pix};
         cuuint32_t box[4] = {(cuuint32_t)p.CK, (cuuint32_t)p.PW, (cuuint32_t)(p.BH + p.kh - 1), 1};
         CUresult r = encode_map(&st.tmap_a, base, 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A, s2d) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
         encode_weight_map(st, cw, Nrows, cw.ka * cw.ka, L.name);
         bind_tc_pointers(net, st);
+        FCNOD_CHECK(st.s2d_hp >= p.tiles_y * p.BH + p.kh - 1 && Wp >= (p.tiles_x - 1) * p.BW + p.PW,
+                    "internal: space-to-depth image smaller than the bulk-copy patches of '" + L.name + "'");
+        p.a_src = base;
+        p.a_row_pitch = (unsigned)(Wp * pix);
+        p.a_img_pitch = (unsigned long long)st.s2d_hp * Wp * pix;
         return;
     }
     fill_tc_geometry(net, st, B);
@@ -1132,36 +1163,37 @@ void launch_conv_simt(const fcnod_net* net, const Step& st, const LayerDef& L, c
     else conv_simt_kernel<bf16, float><<<grid, 256, 0, s>>>(p);
 }
 
-// the instantiations of the tensor-core convolution: K steps per block (CK / 16) x HALO, + the profiled twins
-template <bool PROF>
-void launch_conv_tc2_p(const Step& st, cudaStream_t s) {
-    const int ks = st.tc.CK / 16;
+// the instantiations of the tensor-core convolution: K steps per block (CK / 16) x HALO x kernel size, + the profiled twins
+template <int KS, bool HALO, int KK>
+void launch_tc2_inst(const Step& st, cudaStream_t s, bool prof) {
     const dim3 g(st.tc_grid), b(kConvTc2Threads);
-    if (st.tc.halo) {
-        FCNOD_CHECK(ks == 4 || ks == 1, "HALO mode needs CK = 64 or 16");
-        if (ks == 4) conv_tc2_kernel<4, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
-        else conv_tc2_kernel<1, true, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
-    }
-    else if (ks == 4) conv_tc2_kernel<4, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
-    else if (ks == 2) conv_tc2_kernel<2, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
-    else conv_tc2_kernel<1, false, PROF><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    if (prof) conv_tc2_kernel<KS, HALO, true, KK><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    else conv_tc2_kernel<KS, HALO, false, KK><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
 }
 void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof) {
-    if (prof) launch_conv_tc2_p<true>(st, s);
-    else launch_conv_tc2_p<false>(st, s);
+    const int ks = st.tc.CK / 16;
+    if (st.tc.halo) {
+        FCNOD_CHECK(ks == 4 || ks == 1, "HALO mode needs CK = 64 or 16");
+        const int kk = st.tc.kh == st.tc.kw ? st.tc.kh : 0;
+        if (ks == 4 && kk == 3) launch_tc2_inst<4, true, 3>(st, s, prof);
+        else if (ks == 4 && kk == 5) launch_tc2_inst<4, true, 5>(st, s, prof);
+        else if (ks == 4) launch_tc2_inst<4, true, 0>(st, s, prof);
+        else if (kk == 4) launch_tc2_inst<1, true, 4>(st, s, prof);
+        else launch_tc2_inst<1, true, 0>(st, s, prof);
+    } else if (ks == 4) launch_tc2_inst<4, false, 0>(st, s, prof);
+    else if (ks == 2) launch_tc2_inst<2, false, 0>(st, s, prof);
+    else launch_tc2_inst<1, false, 0>(st, s, prof);
 }
-void conv_tc2_set_smem_limit() {
+template <int KS, bool HALO, int KK>
+void tc2_smem_attr() {
     const int lim = 227 * 1024;
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<KS, HALO, false, KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<KS, HALO, true, KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+}
+void conv_tc2_set_smem_limit() {      // per device, at net creation (outside any graph capture)
+    tc2_smem_attr<4, true, 3>(); tc2_smem_attr<4, true, 5>(); tc2_smem_attr<4, true, 0>();
+    tc2_smem_attr<1, true, 4>(); tc2_smem_attr<1, true, 0>();
+    tc2_smem_attr<4, false, 0>(); tc2_smem_attr<2, false, 0>(); tc2_smem_attr<1, false, 0>();
 }
 
 void launch_export(const fcnod_net* net, const Blob& b, float* dst, cudaStream_t s) {
@@ -1187,11 +1219,11 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             bf16* dst = (bf16*)net->buffers[st.s2d_buf].ptr;
             const int g = grid_for(items, 256);
             if (ib.C == 3)
-                input_s2d_kernel<3><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+                input_s2d_kernel<3><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_hp, st.s2d_padl, kS2dCpad);
             else if (ib.C == 1)
-                input_s2d_kernel<1><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+                input_s2d_kernel<1><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_hp, st.s2d_padl, kS2dCpad);
             else
-                input_s2d_kernel<0><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_padl, kS2dCpad);
+                input_s2d_kernel<0><<<g, 256, 0, s>>>(data_dev, dst, net->batch, ib.C, ib.H, ib.W, st.s2d_wp, st.s2d_hp, st.s2d_padl, kS2dCpad);
             break;
         }
         case S_POOL_LRN: {   // layer = Pooling, layer2 = LRN

@@ -14,6 +14,15 @@ __device__ __forceinline__ uint64_t desc128(uint32_t saddr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+__device__ __forceinline__ uint64_t desc32(uint32_t saddr) {      // K-major SWIZZLE_32B: 32-byte rows, 8-row groups 256 bytes apart
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(256 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)6 << 61;
+    return d;
+}
 __global__ void __launch_bounds__(128, 1) k(int N, int mode, int iters, long long* out) {
     extern __shared__ __align__(1024) uint8_t sm[];
     const uint32_t base = (smem_u32(sm) + 1023u) & ~1023u;
@@ -42,7 +51,11 @@ __global__ void __launch_bounds__(128, 1) k(int N, int mode, int iters, long lon
             const uint32_t stage = distinctA ? (uint32_t)(it & 3) : 0u;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
-                const uint64_t da = desc128(a + stage * 16384u) + 2 * ks, db = desc128(b + stage * 32768u) + 2 * ks;
+                uint64_t da = desc128(a + stage * 16384u) + 2 * ks, db = desc128(b + stage * 32768u) + 2 * ks;
+                if (mode & 8) {      // 32-byte-swizzled operands, A start shifted by ks pixels (the first convolution's taps)
+                    da = desc32(a + stage * 16384u + ((mode & 16) ? 0u : 32u * ks));
+                    db = desc32(b + (uint32_t)ks * (uint32_t)N * 32u);
+                }
                 if (ts) {
                     const uint32_t ta = tm + 448u + 8u * ks;    // A slice in TMEM (garbage is fine)
                     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -71,8 +84,11 @@ int main() {
     long long* d; cudaMalloc(&d, 8);
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     const int iters = 2000;
-    const char* names[8] = {"SS same-acc", "SS alt-acc", "TS same-acc", "TS alt-acc", "SS same-acc 4 stages", "SS alt-acc 4 stages", "TS same 4st", "TS alt 4st"};
-    for (int mode = 0; mode < 8; ++mode) {
+    const char* names[32] = {"SS same-acc", "SS alt-acc", "TS same-acc", "TS alt-acc", "SS same-acc 4 stages", "SS alt-acc 4 stages", "TS same 4st", "TS alt 4st", "SW32 shifted-A same-acc", "SW32 shifted-A alt-acc"};
+    names[24] = "SW32 aligned-A same-acc";
+    const int modes[6] = {0, 1, 2, 8, 9, 24};
+    for (int mi = 0; mi < 6; ++mi) {
+        const int mode = modes[mi];
         for (int N : {32, 64, 128, 192, 256}) {
             if ((mode & 1) && N > 192 && 0) continue;
             k<<<148, 128, 198 * 1024>>>(N, mode, iters, d);
