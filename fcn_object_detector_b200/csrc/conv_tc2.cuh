@@ -15,8 +15,8 @@
 //     UMMA descriptor whose start address is shifted by r*(BW+k-1) + s rows: accumulator row i = py*(BW+k-1) + px
 //     reads patch pixel (py+r, px+s).  The 9 (25) taps re-use one load instead of 9 (25) shifted loads; rows with
 //     px >= BW are computed and discarded.  TAP mode (1x1, the space-to-depth first convolution) = one A box per K-block.
-//   * Epilogue through shared memory, 8 warps: two per TMEM lane quadrant, each draining half of the columns of its
-//     32 accumulator rows: bias (staged in smem per tile) + ReLU, pack to bf16 into a private swizzled staging area,
+//   * Epilogue through shared memory, 16 warps (the epilogue is latency-bound per warp, so it is spread wide): four per
+//     TMEM lane quadrant, each draining a quarter of the columns of its 32 accumulator rows: bias (staged in smem per tile) + ReLU, pack to bf16 into a private swizzled staging area,
 //     read back so that consecutive lanes store consecutive 16-byte pieces of one pixel (full lines instead of 32
 //     scattered sectors per store).  No cross-warp synchronisation in the epilogue.
 //   * Horizontal fusion: N may be the concatenation of several convolutions reading the same input (the 1x1 /
@@ -65,8 +65,8 @@ struct ConvTc2Params {
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
     uint32_t tmem_cols;      // whole allocation (2 accumulators), power of two
     uint32_t acc_stride;     // columns between the two accumulators
-    uint32_t row_bytes;      // staging row pitch of one epilogue warp: its columns * 2, rounded up to 128
-    int cols_half0;          // columns drained by the first warp of each quadrant pair (multiple of 16); rest = BN - cols_half0
+    uint32_t row_bytes;      // staging row pitch of one epilogue warp: 32, 64 or 128 bytes (>= its columns * 2)
+    int cols_half0;          // columns drained by each of the four warps of a quadrant (multiple of 16; the last ones get the rest)
     int flags;               // SEG_RELU / SEG_DIRECT: uniform over the segments of one launch
     int bt_interior;         // bias_tab: class index of interior pixels (== the row `bias` points at)
     int nseg;
@@ -81,9 +81,10 @@ struct ConvTc2Params {
             p.prof[((role) * 8 + (tile)) * 64 + (ev)] = (unsigned long long)clock64();                  \
     } while (0)
 
-constexpr int kTcProducerWarps = 4;
-constexpr int kTcMmaWarp = 4;
-constexpr int kConvTc2Threads = 32 * (kTcProducerWarps + 1 + 8);   // 4 TMA warps + MMA warp + 8 epilogue warps
+constexpr int kTcProducerWarps = 3;
+constexpr int kTcMmaWarp = 3;
+constexpr int kTcEpiWarps = 16;     // four per TMEM lane quadrant, each draining a quarter of the columns
+constexpr int kConvTc2Threads = 32 * (kTcProducerWarps + 1 + kTcEpiWarps);   // 3 TMA warps + MMA warp + 16 epilogue warps
 
 namespace tc {
 // K-major SWIZZLE_128B descriptor for a start address that is only 128-byte (one row) aligned: the matrix base
@@ -182,8 +183,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t a_base = smem_base;
     const uint32_t b_base = a_base + (uint32_t)p.a_stages * p.a_stage_bytes;
     const uint32_t stage_base = b_base + (uint32_t)p.b_stages * p.b_stage_bytes;   // epilogue staging: 8 warps x 32 rows
-    const uint32_t bias_base = stage_base + 8u * 32u * p.row_bytes;                // 8 warps x 128 floats
-    const uint32_t bar_base = bias_base + 8u * 512u;
+    const uint32_t bias_base = stage_base;                                                // 64 floats per epilogue warp
+    const uint32_t bar_base = bias_base + (uint32_t)kTcEpiWarps * 256u;
     const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * p.a_stages;
     const uint32_t bfull0 = aempty0 + 8u * p.a_stages, bempty0 = bfull0 + 8u * p.b_stages;
     const uint32_t tfull0 = bempty0 + 8u * p.b_stages, tempty0 = tfull0 + 16u;
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
         for (int s = 0; s < p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 8); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, kTcEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -213,12 +214,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
     if (warp < kTcProducerWarps) {
-        // ================= TMA producers: warps 0,1 feed the A ring (even / odd loads), warps 2,3 the B ring ============
+        // ================= TMA producers: warp 0 feeds the A ring, warps 1,2 the B ring (even / odd loads) ==============
         // One thread per warp.  A single thread needs ~300 cycles per (wait, expect_tx, TMA) round, so the loads of a
         // ring are dealt round-robin to two warps; every stage has its own barriers, arrival order does not matter.
         if (lane == 0) {
-            const bool ringB = warp >= 2;
-            uint32_t par = (uint32_t)warp & 1u;
+            const bool ringB = warp >= 1;
+            uint32_t par = ringB ? (uint32_t)(warp - 1) & 1u : 0u;
             asm volatile("prefetch.tensormap [%0];" ::"l"(ringB ? &tmap_b : &tmap_a) : "memory");
             const uint32_t b_tx = (uint32_t)p.BN * span * (uint32_t)p.b_taps;
             const uint32_t nst = ringB ? (uint32_t)p.b_stages : (uint32_t)p.a_stages;
@@ -227,8 +228,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             const uint32_t full0 = ringB ? bfull0 : afull0, empty0 = ringB ? bempty0 : aempty0;
             // a one-stage ring is fed by ONE warp: with two, a warp's consecutive visits to the stage would be two
             // barrier phases apart, which a parity wait cannot tell from zero
-            uint32_t idx_mask = 1u;
-            if (nst < 2) { idx_mask = 0u; if (par) par = 2u; }      // par 2 never matches: the odd warp idles
+            uint32_t idx_mask = ringB ? 1u : 0u;                    // the A ring has one producer warp, the B ring two
+            if (ringB && nst < 2) { idx_mask = 0u; if (par) par = 2u; }      // par 2 never matches: the odd warp idles
             uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
             int tile_i = 0;
             TileIter ti;
@@ -393,59 +394,52 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     } else {
         // ================= epilogue: 8 warps; warp w drains TMEM lane quadrant w % 4, column half (w - 5) / 4 ===========
         // Everything that does not change from tile to tile is computed once: the lane's position inside the pixel box,
-        // the read-back mapping, and (per N tile) the bias staging and the destination segment of the lane's piece.
+        // the bias of the warp's columns (staged in shared memory) and the destination of each 16-column group.
         const int ew = warp - (kTcMmaWarp + 1);
-        const int q = warp & 3, half = ew >> 2;
+        const int q = warp & 3, part = ew >> 2;
         const int HW = p.H * p.W;
-        // this warp's columns inside the N tile: [wc0, wc0 + wcols), 16-column granular
-        const int wc0 = half ? p.cols_half0 : 0;
-        const int wcols = half ? p.BN - p.cols_half0 : p.cols_half0;
-        const uint32_t my_stage = stage_base + (uint32_t)ew * 32u * p.row_bytes;
-        const uint32_t my_row = my_stage + (uint32_t)lane * p.row_bytes;
-        const uint32_t my_bias = bias_base + (uint32_t)ew * 512u;                  // 128 floats
+        // this warp's columns inside the N tile: [wc0, wc0 + wcols), 16-column granular, at most 64
+        const int wc0 = min(part * p.cols_half0, p.BN);
+        const int wcols = min(p.cols_half0, p.BN - wc0);
+        const uint32_t my_bias = bias_base + (uint32_t)ew * 256u;                  // 64 floats
         uint8_t* const smem_gen = smem_raw2 + (smem_base - smem_u32(smem_raw2));    // generic view of smem_base
-        uint8_t* const stage_warp = smem_gen + (my_stage - smem_base);
-        uint8_t* const stage_row = smem_gen + (my_row - smem_base);
         float* const bias_s = reinterpret_cast<float*>(smem_gen + (my_bias - smem_base));
         const bool relu = (p.flags & SEG_RELU) != 0;
-        // read-back mapping: PL lanes cover the 16-byte pieces of one row, 32 / PL rows per instruction
-        const int cpr = wcols >> 3;
-        int PL = 1;
-        while (PL < cpr) PL <<= 1;
-        const int rb_piece = lane & (PL - 1), rb_sub = lane / PL, rb_rows = 32 / PL;
         const int m = q * 32 + lane;                // accumulator row
         const int py = m / p.PW, px = m - py * p.PW;
         const bool vpos = (py < p.BH) && (px < p.BW);
         const int ncc = p.bt_lo_w + p.bt_hi_w + 1;
-        int cur_nt = -1, n0 = 0;
-        bf16* rb_seg = nullptr;                     // destination of this lane's read-back piece, image 0
-        size_t rb_ld = 0;
+        const int n0 = my_nt * p.BN + wc0;          // first fused-N column of this warp
+        for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);
+        // destination of the j-th 16-column group (bf16 NHWC): base pointer for pixel 0 of image 0, pixel pitch, and how
+        // it may be stored: 0 = nothing, 1 / 2 = one / two 16-byte pieces, 3 = one 32-byte store (aligned)
+        bf16* grp_ptr[4];
+        int grp_ld[4], grp_mode[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            grp_ptr[j] = nullptr; grp_ld[j] = 0; grp_mode[j] = 0;
+            if (!(p.flags & SEG_DIRECT) && 16 * j < wcols) {
+                const int col = n0 + 16 * j;
+                int si = 0;
+#pragma unroll
+                for (int s = 1; s < 4; ++s)
+                    if (s < p.nseg && col >= p.seg[s].col0) si = s;
+                const int cl = col - p.seg[si].col0, left = p.seg[si].ncols - cl;   // segment boundaries: multiples of 8
+                if (left > 0) {
+                    grp_ptr[j] = static_cast<bf16*>(p.seg[si].out) + cl;
+                    grp_ld[j] = p.seg[si].ldo;
+                    grp_mode[j] = left >= 16 ? 2 : 1;
+                    if (grp_mode[j] == 2 && ((reinterpret_cast<uintptr_t>(grp_ptr[j]) | (uintptr_t)(2 * grp_ld[j])) & 31u) == 0) grp_mode[j] = 3;
+                }
+            }
+        }
+        __syncwarp();
         int it = 0;
         TileIter ti;
         ti.init(p);
         for (; ti.valid(p); ++it, ti.next(p)) {
             const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
             const int n_img = ti.img;
-            if (cur_nt < 0) {
-                cur_nt = my_nt;
-                n0 = cur_nt * p.BN + wc0;               // first fused-N column of this warp
-                __syncwarp();
-                for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);
-                rb_seg = nullptr;
-                if (!(p.flags & SEG_DIRECT) && rb_piece < cpr) {
-                    const int col = n0 + rb_piece * 8;
-                    int si = 0;
-#pragma unroll
-                    for (int s = 1; s < 4; ++s)
-                        if (s < p.nseg && col >= p.seg[s].col0) si = s;
-                    const int cl = col - p.seg[si].col0;
-                    if (cl < p.seg[si].ncols) {
-                        rb_ld = (size_t)p.seg[si].ldo;
-                        rb_seg = static_cast<bf16*>(p.seg[si].out) + cl;
-                    }
-                }
-                __syncwarp();
-            }
             const int oh = ti.ty * p.BH + py, ow = ti.tx * p.BW + px;
             const bool valid = vpos && (oh < p.H) && (ow < p.W);
             const int pix_in_img = valid ? oh * p.W + ow : -1;
@@ -454,7 +448,6 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 const int cls = border_class(oh, p.H, p.bt_lo_h, p.bt_hi_h) * ncc + border_class(ow, p.W, p.bt_lo_w, p.bt_hi_w);
                 if (cls != p.bt_interior) gbias = p.bias_tab + (size_t)cls * p.bt_ld + n0;
             }
-            bf16* const rb_out = rb_seg ? rb_seg + (size_t)n_img * HW * rb_ld : nullptr;
             if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 0);
             mbar_wait_sleep(tfull0 + 8u * acc, aphase);
             fence_after();
@@ -490,57 +483,74 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 __syncwarp();
                 if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
             } else {
-                // ---- bf16 NHWC: drain 32 columns at a time: TMEM -> registers, + bias (staged in shared memory; the border
-                //      pixels of the first convolution take theirs from the class table), ReLU, pack, stage.
+                // ---- bf16 NHWC: drain 32 columns at a time: TMEM -> registers, + bias (the border pixels of the first
+                //      convolution take theirs from the class table), ReLU, pack, and store straight from the registers: a
+                //      lane owns one pixel, a 16-column group is one full 32-byte sector of it (no shared-memory staging).
                 const bool any_g = __any_sync(0xffffffffu, gbias != nullptr);
                 const float4* const bias4 = reinterpret_cast<const float4*>(bias_s);
-                for (int c = 0; c < wcols; c += 32) {
-                    const int ncol = min(32, wcols - c);      // 32 or 16
-                    uint32_t ra[32];
-                    if (ncol == 32) tmem_ld32(trow + (uint32_t)c, ra);
-                    else tmem_ld16(trow + (uint32_t)c, ra);
-                    tmem_ld_wait_dep32(ra);
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        if (8 * g < ncol) {
-                            float4 b0 = bias4[(c >> 2) + 2 * g], b1 = bias4[(c >> 2) + 2 * g + 1];
-                            if (any_g && gbias) {
-                                b0 = __ldg(reinterpret_cast<const float4*>(gbias + c + 8 * g));
-                                b1 = __ldg(reinterpret_cast<const float4*>(gbias + c + 8 * g + 4));
-                            }
-                            float v[8];
-                            v[0] = __uint_as_float(ra[8 * g + 0]) + b0.x; v[1] = __uint_as_float(ra[8 * g + 1]) + b0.y;
-                            v[2] = __uint_as_float(ra[8 * g + 2]) + b0.z; v[3] = __uint_as_float(ra[8 * g + 3]) + b0.w;
-                            v[4] = __uint_as_float(ra[8 * g + 4]) + b1.x; v[5] = __uint_as_float(ra[8 * g + 5]) + b1.y;
-                            v[6] = __uint_as_float(ra[8 * g + 6]) + b1.z; v[7] = __uint_as_float(ra[8 * g + 7]) + b1.w;
-                            if (relu) {
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-                            }
-                            uint4 pk;
-                            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                            const uint32_t piece = (uint32_t)((c >> 3) + g);
-                            const uint32_t phys = (piece & ~7u) | ((piece ^ (uint32_t)lane) & 7u);
-                            *reinterpret_cast<uint4*>(stage_row + phys * 16u) = pk;
-                        }
-                    }
+                const size_t pix_off = (size_t)n_img * HW + (size_t)(valid ? pix_in_img : 0);
+                if (wcols <= 0) {      // a narrow N tile leaves this warp without columns: it only signs the accumulator off
+                    fence_before();
+                    __syncwarp();
+                    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
                 }
-                // the accumulator has left TMEM: hand the buffer back to the MMA warp
-                fence_before();
-                __syncwarp();
-                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
-                if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 2);
-                // coalesced read-back: PL consecutive lanes = consecutive 16-byte pieces of one pixel
-#pragma unroll 4
-                for (int i = 0; i < PL; ++i) {
-                    const int row = i * rb_rows + rb_sub;
-                    const int rv = __shfl_sync(0xffffffffu, pix_in_img, row);
-                    if (rb_out != nullptr && rv >= 0) {
-                        const uint32_t phys = ((uint32_t)rb_piece & ~7u) | (((uint32_t)rb_piece ^ (uint32_t)row) & 7u);
-                        const uint4 pk = *reinterpret_cast<const uint4*>(stage_warp + (uint32_t)row * p.row_bytes + phys * 16u);
-                        *reinterpret_cast<uint4*>(rb_out + (size_t)rv * rb_ld) = pk;
+#pragma unroll
+                for (int c = 0; c < 64; c += 32) {
+                    if (c < wcols) {
+                        const int ncol = min(32, wcols - c);      // 32 or 16
+                        uint32_t ra[32];
+                        if (ncol == 32) tmem_ld32(trow + (uint32_t)c, ra);
+                        else tmem_ld16(trow + (uint32_t)c, ra);
+                        tmem_ld_wait_dep32(ra);
+                        if (c + 32 >= wcols) {
+                            // the accumulator has left TMEM: hand the buffer back to the MMA warp
+                            fence_before();
+                            __syncwarp();
+                            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+                            if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 2);
+                        }
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            if (16 * h < ncol) {
+                                const int j = (c >> 4) + h;
+                                uint32_t pk[8];
+#pragma unroll
+                                for (int g = 0; g < 2; ++g) {
+                                    const int cb = c + 16 * h + 8 * g;
+                                    float4 b0 = bias4[cb >> 2], b1 = bias4[(cb >> 2) + 1];
+                                    if (any_g && gbias) {
+                                        b0 = __ldg(reinterpret_cast<const float4*>(gbias + cb));
+                                        b1 = __ldg(reinterpret_cast<const float4*>(gbias + cb + 4));
+                                    }
+                                    const uint32_t* r8 = ra + 16 * h + 8 * g;
+                                    float v[8];
+                                    v[0] = __uint_as_float(r8[0]) + b0.x; v[1] = __uint_as_float(r8[1]) + b0.y;
+                                    v[2] = __uint_as_float(r8[2]) + b0.z; v[3] = __uint_as_float(r8[3]) + b0.w;
+                                    v[4] = __uint_as_float(r8[4]) + b1.x; v[5] = __uint_as_float(r8[5]) + b1.y;
+                                    v[6] = __uint_as_float(r8[6]) + b1.z; v[7] = __uint_as_float(r8[7]) + b1.w;
+                                    if (relu) {
+#pragma unroll
+                                        for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+                                    }
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        const __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+                                        pk[4 * g + e] = *reinterpret_cast<const uint32_t*>(&h2);
+                                    }
+                                }
+                                if (valid && grp_mode[j] != 0) {
+                                    bf16* const d = grp_ptr[j] + pix_off * (size_t)grp_ld[j];
+                                    if (grp_mode[j] == 3) {
+                                        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                                     ::"l"(d), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]), "r"(pk[4]), "r"(pk[5]),
+                                                       "r"(pk[6]), "r"(pk[7]) : "memory");
+                                    } else {
+                                        *reinterpret_cast<uint4*>(d) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                                        if (grp_mode[j] == 2) *reinterpret_cast<uint4*>(d + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                                    }
+                                }
+                            }
+                        }
                     }
                 }
             }

@@ -749,9 +749,9 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > 256 || nt * BN - N8 >= BN) continue;
-        const int half0 = ceil_div(BN, 32) * 16;
-        const uint32_t row_bytes = (uint32_t)align_up((size_t)half0 * 2, 128);
-        const size_t fixed = 8 * 32 * (size_t)row_bytes + 8 * 512 + 512 + 1024;
+        const int half0 = ceil_div(BN, 64) * 16;      // columns per epilogue warp (four warps per TMEM lane quadrant)
+        const uint32_t row_bytes = half0 <= 16 ? 32u : (half0 <= 32 ? 64u : 128u);
+        const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;     // bias staging, barriers, alignment slack
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
         const int mslots = std::max(1, std::min(p.m_tiles, kNumSMs / nt));
         const long rounds = ((long)p.m_tiles + mslots - 1) / mslots;
@@ -811,8 +811,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
     p.acc_stride = acc;
     p.tmem_cols = std::max<uint32_t>(2 * acc, 32);
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
-    st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 8 * 32 * (size_t)p.row_bytes +
-                 8 * 512 + 512 + 1024;
+    st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 512 + 1024;
     p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
     st.tc_grid = p.mstride * p.n_tiles;
     {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
