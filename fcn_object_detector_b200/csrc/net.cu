@@ -762,7 +762,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
             // (shrinking the N tile to make them fit costs more in tensor-pipe time than the loads it saves)
             for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident) {
                 int a_st, b_st;
-                const int a_min = p.halo ? 1 : 2, a_max = p.halo ? 2 : 8;
+                const int a_min = p.halo ? 1 : 2, a_max = p.halo ? 4 : 8;
                 if (resident) {
                     // the whole K extent of the N tile stays in shared memory (loaded once per CTA)
                     const size_t bres = (size_t)rounds_b * b_stage;

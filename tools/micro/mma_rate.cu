@@ -42,9 +42,14 @@ __global__ void __launch_bounds__(128, 1) k(int N, int mode, int iters, long lon
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     uint32_t tm;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tm) : "r"(slot));
-    if (threadIdx.x == 0) {
+    const bool dual = (mode & 32) != 0;
+    if (threadIdx.x == 0 || (dual && threadIdx.x == 32)) {
+        const uint32_t w = threadIdx.x >> 5;
+        tm += w * 256u;
+        const uint32_t bar_w = bar + (dual ? 32u * w : 0u);
+        if (w) { asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_w)); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (8u << 24);
-        const bool alt = mode & 1, ts = mode & 2, distinctA = mode & 4;
+        const bool alt = (mode & 1) && !dual, ts = mode & 2, distinctA = mode & 4;
         long long t0 = clock64();
         for (int it = 0; it < iters; ++it) {
             const uint32_t d = tm + ((alt && (it & 1)) ? 256u : 0u);
@@ -68,14 +73,15 @@ __global__ void __launch_bounds__(128, 1) k(int N, int mode, int iters, long lon
                 }
             }
         }
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_w) : "memory");
         uint32_t ok = 0;
         while (!ok) {
             asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                         : "=r"(ok) : "r"(bar), "r"(0u) : "memory");
+                         : "=r"(ok) : "r"(bar_w), "r"(0u) : "memory");
         }
         long long t1 = clock64();
-        if (blockIdx.x == 0) out[0] = t1 - t0;
+        if (blockIdx.x == 0 && w == 0) out[0] = t1 - t0;
+        tm -= w * 256u;
     }
     __syncthreads();
     if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tm) : "memory");
@@ -84,10 +90,11 @@ int main() {
     long long* d; cudaMalloc(&d, 8);
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     const int iters = 2000;
-    const char* names[32] = {"SS same-acc", "SS alt-acc", "TS same-acc", "TS alt-acc", "SS same-acc 4 stages", "SS alt-acc 4 stages", "TS same 4st", "TS alt 4st", "SW32 shifted-A same-acc", "SW32 shifted-A alt-acc"};
+    const char* names[64] = {"SS same-acc", "SS alt-acc", "TS same-acc", "TS alt-acc", "SS same-acc 4 stages", "SS alt-acc 4 stages", "TS same 4st", "TS alt 4st", "SW32 shifted-A same-acc", "SW32 shifted-A alt-acc"};
     names[24] = "SW32 aligned-A same-acc";
-    const int modes[6] = {0, 1, 2, 8, 9, 24};
-    for (int mi = 0; mi < 6; ++mi) {
+    names[32] = "SS same-acc, TWO issuing warps (cycles per MMA per warp)";
+    const int modes[3] = {0, 32, 8};
+    for (int mi = 0; mi < 3; ++mi) {
         const int mode = modes[mi];
         for (int N : {32, 64, 128, 192, 256}) {
             if ((mode & 1) && N > 192 && 0) continue;
