@@ -56,6 +56,7 @@ struct ConvTc2Params {
     int mstride;                               // pixel tiles between two visits of one CTA = gridDim.x / n_tiles
     int step_tx, step_ty, step_img;            // mstride written in the mixed radix (img, ty, tx)
     int b_resident;                            // 1 = the B ring holds the whole K extent of the CTA's N tile: loaded once
+    int dual;                                  // 1 = two A/B rings and two MMA-issuing threads (even / odd pixel tiles)
     int a_bulk;                                // 1 = HALO patch rows come by cp.async.bulk from a padded, pre-swizzled image
     const void* a_src;                         //     its base, row pitch and image pitch in bytes
     unsigned a_row_pitch;
@@ -81,8 +82,9 @@ struct ConvTc2Params {
             p.prof[((role) * 8 + (tile)) * 64 + (ev)] = (unsigned long long)clock64();                  \
     } while (0)
 
-constexpr int kTcProducerWarps = 3;
-constexpr int kTcMmaWarp = 3;
+constexpr int kTcProducerWarps = 3;   // warps 0..3: MMA issuer 0, two TMA producers, MMA issuer 1 (DUAL mode)
+constexpr int kTcMmaWarp = 3;         // last non-epilogue warp: the epilogue warps start at kTcMmaWarp + 1
+constexpr int kTcAllocWarp = 0;       // allocates / frees tensor memory
 constexpr int kTcEpiWarps = 16;     // four per TMEM lane quadrant, each draining a quarter of the columns
 constexpr int kConvTc2Threads = 32 * (kTcProducerWarps + 1 + kTcEpiWarps);   // 3 TMA warps + MMA warp + 16 epilogue warps
 
@@ -180,14 +182,19 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     extern __shared__ __align__(1024) uint8_t smem_raw2[];
     const uint32_t smem_base = (smem_u32(smem_raw2) + 1023u) & ~1023u;
     const uint32_t span = (uint32_t)p.CK * 2u;
+    // Shared memory: [A rings][B rings][bias staging][barriers].  In DUAL mode there are two of each ring: even pixel tiles
+    // flow through ring 0 / accumulator 0 and are multiplied by MMA thread 0, odd ones through ring 1 / accumulator 1 by
+    // MMA thread 1.  One thread issues a tcgen05.mma about every 100 cycles whatever its size (tools/micro/mma_rate.cu);
+    // two threads double that, which is what the narrow-N layers need.  Resident weights are one region shared by both.
+    const int nr = p.dual ? 2 : 1, nrb = p.b_resident ? 1 : nr;
     const uint32_t a_base = smem_base;
-    const uint32_t b_base = a_base + (uint32_t)p.a_stages * p.a_stage_bytes;
-    const uint32_t stage_base = b_base + (uint32_t)p.b_stages * p.b_stage_bytes;   // epilogue staging: 8 warps x 32 rows
-    const uint32_t bias_base = stage_base;                                                // 64 floats per epilogue warp
+    const uint32_t a_ring_bytes = (uint32_t)p.a_stages * p.a_stage_bytes, b_ring_bytes = (uint32_t)p.b_stages * p.b_stage_bytes;
+    const uint32_t b_base = a_base + (uint32_t)nr * a_ring_bytes;
+    const uint32_t bias_base = b_base + (uint32_t)nrb * b_ring_bytes;                     // 64 floats per epilogue warp
     const uint32_t bar_base = bias_base + (uint32_t)kTcEpiWarps * 256u;
-    const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * p.a_stages;
-    const uint32_t bfull0 = aempty0 + 8u * p.a_stages, bempty0 = bfull0 + 8u * p.b_stages;
-    const uint32_t tfull0 = bempty0 + 8u * p.b_stages, tempty0 = tfull0 + 16u;
+    const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * nr * p.a_stages;
+    const uint32_t bfull0 = aempty0 + 8u * nr * p.a_stages, bempty0 = bfull0 + 8u * nrb * p.b_stages;
+    const uint32_t tfull0 = bempty0 + 8u * nrb * p.b_stages, tempty0 = tfull0 + 16u;
     const uint32_t tmem_slot = tempty0 + 16u;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -196,13 +203,13 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
-        for (int s = 0; s < p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
+        for (int s = 0; s < nr * p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
+        for (int s = 0; s < nrb * p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, kTcEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    if (warp == kTcMmaWarp) {
+    if (warp == kTcAllocWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -213,117 +220,128 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-    if (warp < kTcProducerWarps) {
-        // ================= TMA producers: warp 0 feeds the A ring, warps 1,2 the B ring (even / odd loads) ==============
-        // One thread per warp.  A single thread needs ~300 cycles per (wait, expect_tx, TMA) round, so the loads of a
-        // ring are dealt round-robin to two warps; every stage has its own barriers, arrival order does not matter.
+    if (warp == 1 || warp == 2 || (warp == 3 && !p.dual)) {
+        // ================= TMA producers (one thread per warp) ========================================================
+        // DUAL: warp 1 feeds ring 0 (even tiles), warp 2 ring 1 (odd tiles), each with the A and B loads of its tiles in
+        // the order the MMA thread consumes them.  Otherwise warp 1 feeds the A ring and warps 2, 3 the B ring (even / odd
+        // rounds: one thread needs a few hundred cycles per wait + expect_tx + TMA round).
         if (lane == 0) {
-            const bool ringB = warp >= 1;
-            uint32_t par = ringB ? (uint32_t)(warp - 1) & 1u : 0u;
-            asm volatile("prefetch.tensormap [%0];" ::"l"(ringB ? &tmap_b : &tmap_a) : "memory");
+            const int pw = warp - 1;
+            const bool doA = p.dual || pw == 0, doB = p.dual || pw >= 1;
+            // single mode, B ring with >= 2 stages: the two B warps take alternate rounds (a one-stage ring is fed by one
+            // warp: two visits of a warp to the stage would be two barrier phases apart, which a parity wait cannot see)
+            // (and the stage count must be even: then a warp always visits the same stages, one phase apart each time)
+            const bool b_split = !p.dual && p.b_stages >= 2 && (p.b_stages & 1) == 0 && !p.b_resident;
+            const uint32_t b_par = (uint32_t)(pw - 1) & 1u;
+            const bool idle = !p.dual && pw == 2 && !b_split;
+            uint32_t b_idx = 0;
+            const int ring = p.dual ? pw : 0;
+            const int first = p.dual ? pw : 0, step = p.dual ? 2 : 1;
+            if (doA) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
+            if (doB) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
             const uint32_t b_tx = (uint32_t)p.BN * span * (uint32_t)p.b_taps;
-            const uint32_t nst = ringB ? (uint32_t)p.b_stages : (uint32_t)p.a_stages;
-            const uint32_t st_bytes = ringB ? p.b_stage_bytes : p.a_stage_bytes;
-            const uint32_t ring_base = ringB ? b_base : a_base;
-            const uint32_t full0 = ringB ? bfull0 : afull0, empty0 = ringB ? bempty0 : aempty0;
-            // a one-stage ring is fed by ONE warp: with two, a warp's consecutive visits to the stage would be two
-            // barrier phases apart, which a parity wait cannot tell from zero
-            uint32_t idx_mask = ringB ? 1u : 0u;                    // the A ring has one producer warp, the B ring two
-            if (ringB && nst < 2) { idx_mask = 0u; if (par) par = 2u; }      // par 2 never matches: the odd warp idles
-            uint32_t sg = 0, ph = 0, idx = 0, dst = ring_base;
-            int tile_i = 0;
+            const uint32_t a_ring = a_base + (uint32_t)ring * a_ring_bytes;
+            const uint32_t b_ring = b_base + (p.b_resident ? 0u : (uint32_t)ring * b_ring_bytes);
+            const uint32_t af = afull0 + 8u * ring * p.a_stages, ae = aempty0 + 8u * ring * p.a_stages;
+            const uint32_t bf = bfull0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
+            const uint32_t be = bempty0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
+            uint32_t sa = 0, pha = 0, sb = 0, phb = 0;
+            const int n0 = my_nt * p.BN;
             TileIter ti;
             ti.init(p);
-            const int n0 = my_nt * p.BN;
-            for (; ti.valid(p); ++tile_i, ti.next(p)) {
-                if (ringB && p.b_resident && tile_i > 0) break;      // resident weights: loaded with the first tile only
+            if (first && ti.valid(p)) ti.next(p);
+            const bool load_b_once = p.b_resident != 0;
+            bool b_done = load_b_once && ring != 0;          // resident weights are loaded by ring 0's producer only
+            for (int tile_i = first; ti.valid(p) && !idle; tile_i += step) {
                 const int n_img = ti.img;
                 const int oh0 = ti.ty * p.BH - p.pad_h, ow0 = ti.tx * p.BW - p.pad_w;
-                if (!ringB) {
-                    // ---- A: one box per channel chunk (HALO) or per (tap, chunk) (TAP)
-                    for (int r = 0; r < (HALO ? 1 : p.kh); ++r)
-                        for (int s = 0; s < (HALO ? 1 : p.kw); ++s)
-                            for (int cc = 0; cc < p.n_cchunks; ++cc, ++idx) {
-                                if ((idx & idx_mask) == par) {
-                                    mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
-                                    mbar_expect_tx(full0 + 8u * sg, p.a_tx_bytes);
-                                    if (HALO && p.a_bulk) {
-                                        // one plain bulk copy per patch row: PW pixels x `span` bytes, contiguous in the image
-                                        const uint32_t rb = (uint32_t)p.PW * span;
-                                        const char* src = static_cast<const char*>(p.a_src) + (size_t)n_img * p.a_img_pitch +
-                                                          (size_t)oh0 * p.a_row_pitch + (size_t)ow0 * span;
-                                        const int rows = p.BH + p.kh - 1;
-                                        for (int pr = 0; pr < rows; ++pr)
-                                            bulk_load(dst + (uint32_t)pr * rb, src + (size_t)pr * p.a_row_pitch, rb, full0 + 8u * sg);
-                                    } else {
-                                        tma_load_4d(dst, &tmap_a, full0 + 8u * sg, cc * p.CK, ow0 + s, oh0 + r, n_img);
-                                    }
-                                }
-                                dst += st_bytes;
-                                if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
-                            }
-                } else {
-                    // ---- B: weights are packed [K-block][N][CK]; one box = b_taps consecutive K-blocks x BN rows.
-                    //      K-block order = consumption order of the MMA warp: TAP (r, s, cc); HALO (cc: r: s) -> block
-                    //      (r * n_cchunks + cc) * kw + s, so the kw taps of one kernel row are adjacent.
-                    int ev = 0;
-                    if (HALO) {
-                        for (int cc = 0; cc < p.n_cchunks; ++cc)
-                            for (int r = 0; r < p.kh; ++r)
-                                for (int s = 0; s < p.kw; s += p.b_taps, ++idx, ++ev) {
-                                    if ((idx & idx_mask) == par) {
-                                        mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
-                                        if (PROF) FCNOD_PROF(0, tile_i, ev);
-                                        mbar_expect_tx(full0 + 8u * sg, b_tx);
-                                        tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, (r * p.n_cchunks + cc) * p.kw + s);
-                                    }
-                                    dst += st_bytes;
-                                    if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
-                                }
+                const bool do_b = doB && !b_done;
+                auto load_a = [&](int cc, int r, int s) {
+                    mbar_wait_hint(ae + 8u * sa, pha ^ 1u);
+                    mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
+                    const uint32_t dst = a_ring + sa * p.a_stage_bytes;
+                    if (HALO && p.a_bulk) {
+                        // one plain bulk copy per patch row: PW pixels x `span` bytes, contiguous in the image
+                        const uint32_t rb = (uint32_t)p.PW * span;
+                        const char* src = static_cast<const char*>(p.a_src) + (size_t)n_img * p.a_img_pitch +
+                                          (size_t)oh0 * p.a_row_pitch + (size_t)ow0 * span;
+                        const int rows = p.BH + p.kh - 1;
+                        for (int pr = 0; pr < rows; ++pr)
+                            bulk_load(dst + (uint32_t)pr * rb, src + (size_t)pr * p.a_row_pitch, rb, af + 8u * sa);
                     } else {
-                        const int nkb = taps * p.n_cchunks;
-                        for (int kb = 0; kb < nkb; ++kb, ++idx, ++ev) {
-                            if ((idx & idx_mask) == par) {
-                                mbar_wait_hint(empty0 + 8u * sg, ph ^ 1u);
-                                if (PROF) FCNOD_PROF(0, tile_i, ev);
-                                mbar_expect_tx(full0 + 8u * sg, b_tx);
-                                tma_load_3d(dst, &tmap_b, full0 + 8u * sg, 0, n0, kb);
-                            }
-                            dst += st_bytes;
-                            if (++sg == nst) { sg = 0; ph ^= 1u; dst = ring_base; }
-                        }
+                        tma_load_4d(dst, &tmap_a, af + 8u * sa, cc * p.CK, ow0 + s, oh0 + r, n_img);
                     }
+                    if (++sa == (uint32_t)p.a_stages) { sa = 0; pha ^= 1u; }
+                };
+                auto load_b = [&](int kb) {      // kb = first K-block of the round, in the packed (= global) order
+                    if (!b_split || (b_idx & 1u) == b_par) {
+                        mbar_wait_hint(be + 8u * sb, phb ^ 1u);
+                        if (PROF) FCNOD_PROF(0, tile_i, 0);
+                        mbar_expect_tx(bf + 8u * sb, b_tx);
+                        tma_load_3d(b_ring + sb * p.b_stage_bytes, &tmap_b, bf + 8u * sb, 0, n0, kb);
+                    }
+                    ++b_idx;
+                    if (++sb == (uint32_t)p.b_stages) { sb = 0; phb ^= 1u; }
+                };
+                if (HALO) {
+                    // per channel chunk: the patch, then the kh * kw / b_taps weight rounds that multiply it
+                    // (weights are packed [(r * n_cchunks + cc) * kw + s]: the kw taps of a kernel row are adjacent)
+                    for (int cc = 0; cc < p.n_cchunks; ++cc) {
+                        if (doA) load_a(cc, 0, 0);
+                        if (do_b)
+                            for (int r = 0; r < p.kh; ++r)
+                                for (int s = 0; s < p.kw; s += p.b_taps) load_b((r * p.n_cchunks + cc) * p.kw + s);
+                    }
+                } else {
+                    int kb = 0;
+                    for (int r = 0; r < p.kh; ++r)
+                        for (int s = 0; s < p.kw; ++s)
+                            for (int cc = 0; cc < p.n_cchunks; ++cc, ++kb) {
+                                if (doA) load_a(cc, r, s);
+                                if (do_b) load_b(kb);
+                            }
                 }
+                if (load_b_once) b_done = true;
+                ti.next(p);
+                if (step == 2 && ti.valid(p)) ti.next(p);
             }
         }
-    } else if (warp == kTcMmaWarp) {
-        // ================= MMA issuer (one thread) ====================================================================
-        // The issuing thread is latency-bound on its OWN instruction stream (about 100 cycles per tcgen05.mma even in a
-        // bare loop, tools/micro/mma_rate.cu), so the tap loops are unrolled at compile time (KK = kernel size) and a
-        // whole kernel row of taps shares one barrier round.
-        if (lane == 0) {
+    } else if (warp == 0 || (warp == 3 && p.dual)) {
+        // ================= MMA issuers (one thread each; the second one only in DUAL mode) ============================
+        // The issuing thread is latency-bound on its OWN instruction stream, so the tap loops are unrolled at compile
+        // time (KK = kernel size) and a whole kernel row of taps shares one barrier round.
+        const int mw = warp == 0 ? 0 : 1;
+        if (lane == 0 && (mw == 0 || p.dual)) {
+            const int ring = mw;
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | (8u << 24);
             // descriptor = {lo: start address >> 4 | LBO 1 << 16, hi: SBO (8 rows) >> 4 | version 1 << 14 | swizzle << 29}
             const uint32_t desc_hi = ((8u * span) >> 4) | (1u << 14) | ((span == 128 ? 2u : (span == 64 ? 4u : 6u)) << 29);
-            const uint32_t a_lo_base = ((a_base & 0x3FFFFu) >> 4) | (1u << 16), a_lo_step = p.a_stage_bytes >> 4;
-            const uint32_t b_lo_base = ((b_base & 0x3FFFFu) >> 4) | (1u << 16), b_lo_step = p.b_stage_bytes >> 4;
+            const uint32_t a_ring = a_base + (uint32_t)ring * a_ring_bytes;
+            const uint32_t b_ring = b_base + (p.b_resident ? 0u : (uint32_t)ring * b_ring_bytes);
+            const uint32_t af = afull0 + 8u * ring * p.a_stages, ae = aempty0 + 8u * ring * p.a_stages;
+            const uint32_t bf = bfull0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
+            const uint32_t be = bempty0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
+            const uint32_t a_lo_base = ((a_ring & 0x3FFFFu) >> 4) | (1u << 16), a_lo_step = p.a_stage_bytes >> 4;
+            const uint32_t b_lo_base = ((b_ring & 0x3FFFFu) >> 4) | (1u << 16), b_lo_step = p.b_stage_bytes >> 4;
             const uint32_t b_tap_step = ((uint32_t)p.BN * span) >> 4;      // one tap tile inside a multi-tap B stage
             const uint32_t px_step = span >> 4;                  // HALO: one patch pixel = `span` bytes, in 16-byte units
             const uint32_t row_step = (uint32_t)p.PW * px_step;  // HALO: one patch row = PW pixels
             const int kh = HALO ? (KK ? KK : p.kh) : 1, kw = HALO ? (KK ? KK : p.kw) : 1;
             const bool bt_row = p.b_taps > 1;                    // a B stage holds the kw taps of one kernel row
             const bool resident = p.b_resident != 0;
+            const int it_step = p.dual ? 2 : 1;
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
-            int it = 0;
-            for (int mt = (int)blockIdx.x / p.n_tiles; mt < p.m_tiles; mt += p.mstride, ++it) {
+            int it = mw;
+            for (int mt = (int)blockIdx.x / p.n_tiles + mw * p.mstride; mt < p.m_tiles; mt += it_step * p.mstride, it += it_step) {
                 const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
-                if (PROF) FCNOD_PROF(1, it, 61);
+                const int itp = it < 8 ? it : 8;
+                if (PROF) FCNOD_PROF(1, itp, 61);
                 mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);     // the epilogue has drained this accumulator
                 fence_after();
-                if (PROF) FCNOD_PROF(1, it, 62);
+                if (PROF) FCNOD_PROF(1, itp, 62);
                 const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
-                const bool wait_b = !(resident && it > 0);
+                const bool wait_b = !(resident && it > mw);
                 uint32_t accum = 0;
                 int ev = 0;
                 int cc = 0;
@@ -339,19 +357,19 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 };
                 auto b_wait = [&]() {
                     if (wait_b) {
-                        mbar_wait_hint(bfull0 + 8u * sb, pb);
+                        mbar_wait_hint(bf + 8u * sb, pb);
                         fence_after();
-                        if (PROF) FCNOD_PROF(1, it, ev);
+                        if (PROF) FCNOD_PROF(1, itp, ev);
                     }
                 };
                 auto b_release = [&]() {
-                    if (!resident) umma_commit(bempty0 + 8u * sb);
-                    if (PROF) { FCNOD_PROF(3, it, ev); ++ev; }
+                    if (!resident) umma_commit(be + 8u * sb);
+                    if (PROF) { FCNOD_PROF(3, itp, ev); ++ev; }
                     b_lo += b_lo_step;
                     if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
                 };
                 for (int ai = 0; ai < a_iters; ++ai) {
-                    mbar_wait_hint(afull0 + 8u * sa, pa);
+                    mbar_wait_hint(af + 8u * sa, pa);
                     const int ks = (cc == p.n_cchunks - 1) ? p.ksteps_last : KSTEPS;   // skip all-zero K steps
                     if (++cc == p.n_cchunks) cc = 0;
                     if (!HALO) {
@@ -383,12 +401,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             a_row += row_step;
                         }
                     }
-                    umma_commit(aempty0 + 8u * sa);
+                    umma_commit(ae + 8u * sa);
                     a_lo += a_lo_step;
                     if (++sa == (uint32_t)p.a_stages) { sa = 0; pa ^= 1u; a_lo = a_lo_base; }
                 }
                 umma_commit(tfull0 + 8u * acc);
-                if (PROF) FCNOD_PROF(1, it, 63);
+                if (PROF) FCNOD_PROF(1, itp, 63);
             }
         }
     } else {
@@ -559,7 +577,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         }
     }
     __syncthreads();
-    if (warp == kTcMmaWarp) {
+    if (warp == kTcAllocWarp) {
         fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
     }

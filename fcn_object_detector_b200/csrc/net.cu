@@ -680,7 +680,9 @@ void choose_tc_tiling(ConvWeights& cw) {
     const char* nh = getenv("FCNOD_NO_HALO");
     cw.halo = cw.k > 1 && !(nh && nh[0] == '1');
     if (cw.halo) {
-        cw.CK = 64;     // HALO mode shifts the A descriptor by whole 128-byte rows: SWIZZLE_128B only
+        // HALO mode shifts the A descriptor by whole patch pixels of CK channels (128-, 64- or 32-byte swizzled rows):
+        // narrow inputs (the 5x5 branches: 16 .. 32 channels) take the narrowest block that holds them in one chunk
+        cw.CK = cw.Cin <= 16 ? 16 : (cw.Cin <= 32 ? 32 : 64);
     } else {
         // K-block width: minimise padded K with a small per-block cost
         int best = 64; long best_cost = -1;
@@ -785,6 +787,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
                 // the one issuing thread: ~300 cycles per barrier round (wait + commit) + ~25 per MMA
                 // measured (tools/micro/mma_rate.cu): one M=128 K=16 instruction takes max(93, 43 + N/2) cycles with both
                 // operands in shared memory, whose bandwidth (128 B/clk) the operand reads share with TMA and the epilogue
+                if (!resident && b_st >= 3) b_st &= ~1;      // two warps feed the B ring round-robin: even stage count
                 const double mma = ksteps_tile * std::max(93.0, 43.0 + BN / 2.0);
                 const double issue = (resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b) * 300.0 +
                                      ksteps_tile * 25.0;
@@ -806,12 +809,43 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
         }
     }
     FCNOD_CHECK(best_cost >= 0, "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
+    {
+        // DUAL mode (two rings, two MMA-issuing threads): worth it where the tensor pipe is starved by the ~100-cycle issue
+        // cadence of one thread, i.e. for narrow N tiles; the rings are re-sized to share the same shared memory.
+        const char* de = getenv("FCNOD_DUAL");
+        const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 160;
+        p.dual = 0;
+        if (p.BN <= dual_bn && p.m_tiles > 1) {
+            const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;
+            const size_t avail = kTcSmemBudget - fixed;
+            const int rounds_b = taps * p.n_cchunks / p.b_taps;
+            int a_st = 0, b_st = 0;
+            if (p.b_resident) {
+                const size_t bres = (size_t)rounds_b * p.b_stage_bytes;
+                a_st = (int)std::min<size_t>(p.halo ? 3 : 8, (avail - bres) / (2 * (size_t)p.a_stage_bytes));
+                b_st = rounds_b;
+                if (a_st < (p.halo ? 1 : 2) || 2 * a_st + b_st > 30) a_st = 0;
+            } else if (p.halo) {
+                for (a_st = 2; a_st >= 1; --a_st) {
+                    if (avail < 2 * (size_t)a_st * p.a_stage_bytes + 4 * (size_t)p.b_stage_bytes) continue;
+                    b_st = (int)std::min<size_t>(6, (avail - 2 * (size_t)a_st * p.a_stage_bytes) / (2 * (size_t)p.b_stage_bytes));
+                    break;
+                }
+            } else {
+                const size_t pair = (size_t)p.a_stage_bytes + p.b_stage_bytes;
+                a_st = b_st = (int)std::min<size_t>(7, avail / (2 * pair));
+                if (a_st < 2) a_st = 0;
+            }
+            if (a_st >= 1 && b_st >= 1) { p.dual = 1; p.a_stages = a_st; p.b_stages = b_st; }
+        }
+    }
     uint32_t acc = 32;
     while ((int)acc < p.BN) acc <<= 1;
     p.acc_stride = acc;
     p.tmem_cols = std::max<uint32_t>(2 * acc, 32);
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
-    st.tc_smem = (size_t)p.a_stages * p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 512 + 1024;
+    st.tc_smem = (size_t)(p.dual ? 2 : 1) * p.a_stages * p.a_stage_bytes +
+                 (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 512 + 1024;
     p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
     st.tc_grid = p.mstride * p.n_tiles;
     {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
@@ -1172,12 +1206,14 @@ void launch_tc2_inst(const Step& st, cudaStream_t s, bool prof) {
 void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof) {
     const int ks = st.tc.CK / 16;
     if (st.tc.halo) {
-        FCNOD_CHECK(ks == 4 || ks == 1, "HALO mode needs CK = 64 or 16");
         const int kk = st.tc.kh == st.tc.kw ? st.tc.kh : 0;
         if (ks == 4 && kk == 3) launch_tc2_inst<4, true, 3>(st, s, prof);
         else if (ks == 4 && kk == 5) launch_tc2_inst<4, true, 5>(st, s, prof);
         else if (ks == 4) launch_tc2_inst<4, true, 0>(st, s, prof);
+        else if (ks == 2 && kk == 5) launch_tc2_inst<2, true, 5>(st, s, prof);
+        else if (ks == 2) launch_tc2_inst<2, true, 0>(st, s, prof);
         else if (kk == 4) launch_tc2_inst<1, true, 4>(st, s, prof);
+        else if (kk == 5) launch_tc2_inst<1, true, 5>(st, s, prof);
         else launch_tc2_inst<1, true, 0>(st, s, prof);
     } else if (ks == 4) launch_tc2_inst<4, false, 0>(st, s, prof);
     else if (ks == 2) launch_tc2_inst<2, false, 0>(st, s, prof);
@@ -1191,7 +1227,8 @@ void tc2_smem_attr() {
 }
 void conv_tc2_set_smem_limit() {      // per device, at net creation (outside any graph capture)
     tc2_smem_attr<4, true, 3>(); tc2_smem_attr<4, true, 5>(); tc2_smem_attr<4, true, 0>();
-    tc2_smem_attr<1, true, 4>(); tc2_smem_attr<1, true, 0>();
+    tc2_smem_attr<1, true, 4>(); tc2_smem_attr<1, true, 0>(); tc2_smem_attr<1, true, 5>();
+    tc2_smem_attr<2, true, 5>(); tc2_smem_attr<2, true, 0>();
     tc2_smem_attr<4, false, 0>(); tc2_smem_attr<2, false, 0>(); tc2_smem_attr<1, false, 0>();
 }
 
@@ -1479,7 +1516,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
             o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {

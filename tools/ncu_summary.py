@@ -10,7 +10,7 @@ KEEP = ['Kernel Name', 'Grid Size', 'Block Size', 'gpu__time_duration.sum', 'dra
         'launch__occupancy_limit', 'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__cycles_active.avg',
         'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__throughput.avg.pct_of_peak_sustained_active',
         'launch__shared_mem_per_block', 'smsp__cycles_active.avg', 'sm__pipe_tensor_subpipe_hmma_cycles_active_realtime',
-        'dram__cycles_active.avg.pct']
+        'dram__cycles_active.avg.pct', 'smsp__inst_executed.sum', 'l1tex__t_sector_hit_rate.pct', 'smsp__issue_active.avg.pct_of_peak_sustained_active']
 raw = subprocess.run(['ncu', '-i', sys.argv[1], '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units, body = rows[0], rows[1], rows[2:]
