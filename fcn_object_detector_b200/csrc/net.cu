@@ -813,7 +813,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
         // DUAL mode (two rings, two MMA-issuing threads): worth it where the tensor pipe is starved by the ~100-cycle issue
         // cadence of one thread, i.e. for narrow N tiles; the rings are re-sized to share the same shared memory.
         const char* de = getenv("FCNOD_DUAL");
-        const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 160;
+        const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 256;
         p.dual = 0;
         if (p.BN <= dual_bn && p.m_tiles > 1) {
             const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;
@@ -826,10 +826,16 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
                 b_st = rounds_b;
                 if (a_st < (p.halo ? 1 : 2) || 2 * a_st + b_st > 30) a_st = 0;
             } else if (p.halo) {
-                for (a_st = 2; a_st >= 1; --a_st) {
-                    if (avail < 2 * (size_t)a_st * p.a_stage_bytes + 4 * (size_t)p.b_stage_bytes) continue;
-                    b_st = (int)std::min<size_t>(6, (avail - 2 * (size_t)a_st * p.a_stage_bytes) / (2 * (size_t)p.b_stage_bytes));
-                    break;
+                for (int pass = 0; pass < 2 && b_st == 0; ++pass) {
+                    if (pass == 1) {      // second try: one tap per B stage (smaller stages, more barrier rounds)
+                        if (p.b_taps == 1 || p.BN > 176) break;      // (measured: a loss for the widest N tiles)
+                        p.b_stage_bytes /= p.b_taps; p.b_taps = 1;
+                    }
+                    for (a_st = 2; a_st >= 1; --a_st) {
+                        if (avail < 2 * (size_t)a_st * p.a_stage_bytes + 4 * (size_t)p.b_stage_bytes) continue;
+                        b_st = (int)std::min<size_t>(pass ? 8 : 6, (avail - 2 * (size_t)a_st * p.a_stage_bytes) / (2 * (size_t)p.b_stage_bytes));
+                        break;
+                    }
                 }
             } else {
                 const size_t pair = (size_t)p.a_stage_bytes + p.b_stage_bytes;
