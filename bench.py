@@ -38,6 +38,26 @@ def peaks():
     return dict(bf16_burst=1590.0, bf16_sustained=1400.0, hbm=6650.0, which='fallback')
 
 
+def ncu_conv_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per conv_tc2 launch, from the newest committed `ncu --set full`
+    summary under profiles/ (tools/gpu_round.sh); (None, None) when there is none."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', '*_conv_tc2_ncu_full.csv')))
+    if not files:
+        return None, None
+    rows = {r[0]: r for r in csv.reader(open(files[-1])) if r}
+    try:
+        scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+        tot = 0.0
+        for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+            tot += sum(float(v) for v in rows[k][2:]) * scale[rows[k][1]]
+        n = len(rows['dram__bytes_read.sum']) - 2
+        return tot / n, os.path.basename(files[-1])
+    except (KeyError, ValueError):
+        return None, None
+
+
 class ClockSampler(object):
     """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
     Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
@@ -276,9 +296,11 @@ def run_ours(args):
         n_tc = sum('conv_tc' in d for d in plan)
         tot_ms = sum(per) + post_ms
         ach = tc_flop / (tc_ms * 1e-3) / 1e12
-        roof = {'bound': 'tensor', 'kernel': 'conv_tc_kernel (%d launches per step)' % n_tc, 'achieved': ach,
+        traffic, traffic_src = ncu_conv_traffic()
+        roof = {'bound': 'tensor', 'kernel': 'conv_tc2_kernel (%d launches per step)' % n_tc, 'achieved': ach,
                 'peak': pk['bf16_sustained'], 'peak_source': pk['which'] + ' sustained cuBLAS bf16', 'unit': 'TFLOP/s',
-                'frac': ach / pk['bf16_sustained'], 'traffic': None, 'share_of_step': tc_ms / tot_ms,
+                'frac': ach / pk['bf16_sustained'], 'traffic': traffic, 'traffic_unit': 'bytes per launch (dram read + write, ncu)',
+                'traffic_source': traffic_src, 'share_of_step': tc_ms / tot_ms,
                 'avg_launch_ms': tc_ms / n_tc, 'flop_per_launch': tc_flop / n_tc}
         os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
         with open(os.path.join(ROOT, 'gpurun_out', 'per_launch_ms.json'), 'w') as f:

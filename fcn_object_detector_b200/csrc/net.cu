@@ -171,6 +171,10 @@ struct fcnod_net {
     float* pre_scratch = 0;
     cudaGraphExec_t graph = 0;
     cudaStream_t stream = 0;
+    cudaStream_t copy_stream = 0;        // uploads of fcnod_detect's second half-batch, overlapped with the first one's compute
+    cudaEvent_t copy_ev[2] = {0, 0};
+    int32_t* pinned_big = 0;             // detections of a whole fcnod_detect call (all chunks)
+    size_t pinned_big_bytes = 0;
     float* pinned_in = 0;
     size_t pinned_in_bytes = 0;
     int32_t* pinned_out = 0;
@@ -1476,6 +1480,9 @@ int fcnod_net_destroy(fcnod_net* net) {
             if (net->convs[i].d_bias_tab) cudaFree(net->convs[i].d_bias_tab);
         }
         if (net->stream) cudaStreamDestroy(net->stream);
+        if (net->copy_stream) cudaStreamDestroy(net->copy_stream);
+        for (int i = 0; i < 2; ++i) if (net->copy_ev[i]) cudaEventDestroy(net->copy_ev[i]);
+        if (net->pinned_big) cudaFreeHost(net->pinned_big);
         delete net;
     }
     FCNOD_API_END
@@ -1692,6 +1699,61 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     FCNOD_CHECK(net && images && p && out_det && out_label && out_weight && out_count, "null argument");
     FCNOD_CHECK(src_h > 0 && src_w > 0, "bad source size");
     require_device(net);
+    // Large batches run as two half-batches: the upload of the second half overlaps the compute of the first one
+    // (frames are independent; the network simply runs at batch B/2 twice on the same buffers).
+    const int nchunk = (B >= 32 && B % 2 == 0 && !getenv("FCNOD_NO_CHUNK")) ? 2 : 1;
+    if (nchunk == 2) {
+        const int Bc = B / 2;
+        reshape(net, Bc);
+        const Blob& in = net->blobs[0];
+        FCNOD_CHECK(in.C == 3, "detect needs a 3-channel input blob");
+        cudaStream_t s = net->stream;
+        if (!net->copy_stream) {
+            FCNOD_CUDA(cudaStreamCreateWithFlags(&net->copy_stream, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) FCNOD_CUDA(cudaEventCreateWithFlags(&net->copy_ev[i], cudaEventDisableTiming));
+        }
+        const size_t cbytes = (size_t)Bc * src_h * src_w * 3, ibytes = 2 * cbytes;
+        if (net->img_dev_bytes < ibytes) {
+            if (net->img_dev) cudaFree(net->img_dev);
+            FCNOD_CUDA(cudaMalloc(&net->img_dev, ibytes));
+            net->img_dev_bytes = ibytes;
+        }
+        if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)Bc * 6 * 4));
+        ensure_detect_buffers(net);
+        const size_t per = (size_t)FCNOD_MAX_DET * 7 + 1, obytes = (size_t)B * per * 4;
+        if (net->pinned_big_bytes < obytes) {
+            if (net->pinned_big) cudaFreeHost(net->pinned_big);
+            FCNOD_CUDA(cudaMallocHost(&net->pinned_big, obytes));
+            net->pinned_big_bytes = obytes;
+        }
+        std::vector<int32_t> hw((size_t)Bc * 2);
+        for (int i = 0; i < Bc; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
+        FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice, s));
+        for (int c = 0; c < 2; ++c) {
+            FCNOD_CUDA(cudaMemcpyAsync(net->img_dev + c * cbytes, images + c * cbytes, cbytes, cudaMemcpyHostToDevice, net->copy_stream));
+            FCNOD_CUDA(cudaEventRecord(net->copy_ev[c], net->copy_stream));
+        }
+        int32_t* p_det = net->pinned_big;
+        int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
+        int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
+        int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
+        for (int c = 0; c < 2; ++c) {
+            FCNOD_CUDA(cudaStreamWaitEvent(s, net->copy_ev[c], 0));
+            preprocess_launch(net->img_dev + c * cbytes, Bc, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
+            detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+            const size_t o = (size_t)c * Bc;
+            FCNOD_CUDA(cudaMemcpyAsync(p_det + o * FCNOD_MAX_DET * 5, net->det_dev, (size_t)Bc * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost, s));
+            FCNOD_CUDA(cudaMemcpyAsync(p_lab + o * FCNOD_MAX_DET, net->label_dev, (size_t)Bc * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
+            FCNOD_CUDA(cudaMemcpyAsync(p_w + o * FCNOD_MAX_DET, net->weight_dev, (size_t)Bc * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
+            FCNOD_CUDA(cudaMemcpyAsync(p_cnt + o, net->count_dev, (size_t)Bc * 4, cudaMemcpyDeviceToHost, s));
+        }
+        FCNOD_CUDA(cudaStreamSynchronize(s));
+        memcpy(out_det, p_det, (size_t)B * FCNOD_MAX_DET * 5 * 4);
+        memcpy(out_label, p_lab, (size_t)B * FCNOD_MAX_DET * 4);
+        memcpy(out_weight, p_w, (size_t)B * FCNOD_MAX_DET * 4);
+        memcpy(out_count, p_cnt, (size_t)B * 4);
+        return 0;
+    }
     reshape(net, B);
     const Blob& in = net->blobs[0];
     FCNOD_CHECK(in.C == 3, "detect needs a 3-channel input blob");
@@ -1704,12 +1766,12 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     }
     if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)B * 6 * 4));
     ensure_detect_buffers(net);
-    FCNOD_CUDA(cudaMemcpyAsync(net->img_dev, images, ibytes, cudaMemcpyHostToDevice, s));
-    preprocess_launch(net->img_dev, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
     std::vector<int32_t> hw((size_t)B * 2);
     for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
     FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaStreamSynchronize(s));   // hw is a stack-lifetime host buffer
+    FCNOD_CUDA(cudaMemcpyAsync(net->img_dev, images, ibytes, cudaMemcpyHostToDevice, s));
+    preprocess_launch(net->img_dev, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
     detect_device(net, net->data_dev, net->srchw_dev, *p, s);
     copy_detections_out(net, B, out_det, out_label, out_weight, out_count, s);
     FCNOD_API_END
