@@ -142,9 +142,12 @@ class Net(object):
                 b._data = np.zeros(shp, dtype=np.float32)
             b._stale = False
 
-    def _sync_after_device_run(self, batch):
-        """The library ran a forward on its own (fcnod_detect*): resize the host mirrors, mark them stale."""
-        self._reshape(batch)
+    def _sync_after_device_run(self, batch=None):
+        """The library ran a forward on its own (fcnod_detect*): resize the host mirrors to the batch the net is at now
+        (fcnod_detect runs large batches as two half-batches, so that may not be the caller's batch), mark them stale."""
+        d = (C.c_int * 4)()
+        _lib.check(self._lib.fcnod_net_input_dims(self._h, d))
+        self._reshape(int(d[0]))
         for n, b in self.blobs.items():
             b._stale = True
 

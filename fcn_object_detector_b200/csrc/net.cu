@@ -1699,9 +1699,12 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     FCNOD_CHECK(net && images && p && out_det && out_label && out_weight && out_count, "null argument");
     FCNOD_CHECK(src_h > 0 && src_w > 0, "bad source size");
     require_device(net);
-    // Large batches run as two half-batches: the upload of the second half overlaps the compute of the first one
-    // (frames are independent; the network simply runs at batch B/2 twice on the same buffers).
-    const int nchunk = (B >= 32 && B % 2 == 0 && !getenv("FCNOD_NO_CHUNK")) ? 2 : 1;
+    // FCNOD_CHUNK=1: large batches run as two half-batches so that the upload of the second half overlaps the compute of
+    // the first one (frames are independent; the network runs at batch B/2 twice on the same buffers).  Opt-in: on the
+    // bench box (PCIe gen5, 38.5 MB per 64 frames) the two smaller forwards cost more than the overlap wins
+    // (14.8k vs 16.2k frames/s end to end).
+    const char* chunk_env = getenv("FCNOD_CHUNK");
+    const int nchunk = (B >= 32 && B % 2 == 0 && chunk_env && chunk_env[0] == '1') ? 2 : 1;
     if (nchunk == 2) {
         const int Bc = B / 2;
         reshape(net, Bc);
