@@ -132,6 +132,7 @@ struct Step {
     int layer2 = -1;           // second layer of a fused pair (Pool->LRN, LRN->Pool)
     int conv = -1;             // index into convs
     int s2d_buf = -1;          // S_S2D / s2d convolution: buffer index of the space-to-depth image
+    int tc_ncand = 0, tc_pick = -1;      // tensor-core tiling candidates (ranked by the model) and the one in use
     int s2d_wp = 0, s2d_hp = 0, s2d_padl = 0;    // padded space-to-depth image: width, height, zero columns / rows before (0, 0)
     bool s2d_overlap = false;  // one K-block per kernel row (overlapping-window tensor map) vs one per tap
     bool relu = false;
@@ -702,7 +703,7 @@ void choose_tc_tiling(ConvWeights& cw) {
 }
 
 // Everything of ConvTc2Params that does not need device pointers: pixel box, N tiling, pipeline depth.
-void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
+void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) {
     const ConvWeights& cw = net->convs[st.conv];
     const Blob& ob = net->blobs[st.out];
     ConvTc2Params& p = st.tc;
@@ -744,110 +745,81 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch) {
         p.a_tx_bytes = (uint32_t)(p.BW * p.BH) * span;
         p.a_stage_bytes = 128 * span;
     }
-    // N tiling: the candidate with the smallest modelled time that fits in shared memory.
-    //   tile time = max(MMA issue, L2->smem bytes, epilogue) + fixed;  total = rounds over 148 persistent CTAs
+    // N tiling / pipeline shape: every candidate that fits in shared memory, ranked by a per-tile model
+    //   tile time = max(MMA issue, smem bandwidth, L2->smem bytes, epilogue) + fixed;  total = rounds over the persistent CTAs
+    // (constants measured with tools/micro/mma_rate.cu and the conv timelines).  `pick` selects the pick-th best; the
+    // device autotuner (autotune_tc_steps) times the first few and keeps the fastest.
     const int N8 = (cw.Cout + 7) / 8 * 8;
-    double best_cost = -1;
     const char* nres = getenv("FCNOD_NO_RESIDENT");
     const bool no_resident = nres && nres[0] == '1';
-    // real 16-wide K steps per tap (the last chunk may be partly zero fill)
-    const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);
+    const char* de = getenv("FCNOD_DUAL");
+    const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 256;
+    const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);   // real 16-wide K steps
+    const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;     // bias staging, barriers, alignment slack
+    const size_t avail = kTcSmemBudget - fixed;
+    struct Cand { int nt, BN, a_st, b_st, bt, resident, dual; uint32_t b_stage; double cost; };
+    std::vector<Cand> cands;
     for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > 256 || nt * BN - N8 >= BN) continue;
-        const int half0 = ceil_div(BN, 64) * 16;      // columns per epilogue warp (four warps per TMEM lane quadrant)
-        const uint32_t row_bytes = half0 <= 16 ? 32u : (half0 <= 32 ? 64u : 128u);
-        const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;     // bias staging, barriers, alignment slack
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
         const int mslots = std::max(1, std::min(p.m_tiles, kNumSMs / nt));
         const long rounds = ((long)p.m_tiles + mslots - 1) / mslots;
         for (int bt = (p.halo ? p.kw : 1); bt >= 1; bt = (bt > 1 ? 1 : 0)) {       // B stage = kw taps (HALO) or 1
             const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024) * bt;
             const int rounds_b = taps * p.n_cchunks / bt;                               // B stages consumed per tile
-            // B streaming decides the tiling; the weights then stay resident when that very tiling leaves room for them
-            // (shrinking the N tile to make them fit costs more in tensor-pipe time than the loads it saves)
-            for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident) {
-                int a_st, b_st;
-                const int a_min = p.halo ? 1 : 2, a_max = p.halo ? 4 : 8;
-                if (resident) {
-                    // the whole K extent of the N tile stays in shared memory (loaded once per CTA)
-                    const size_t bres = (size_t)rounds_b * b_stage;
-                    if (!(best_cost >= 0 && p.n_tiles == nt && p.BN == BN && p.b_taps == bt && !p.b_resident)) continue;
-                    if (rounds_b > 24 || fixed + bres + (size_t)std::max(a_min, 2) * p.a_stage_bytes > kTcSmemBudget) continue;
-                    b_st = rounds_b;
-                    a_st = (int)std::min<size_t>(a_max, (kTcSmemBudget - fixed - bres) / p.a_stage_bytes);
-                    best_cost = 1e30;      // force the comparison below: same tiling, resident weights
-                } else if (p.halo) {
-                    a_st = 2;      // the next tile's patch loads while this one is multiplied
-                    if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) a_st = 1;
-                    if (fixed + (size_t)a_st * p.a_stage_bytes + 2 * (size_t)b_stage > kTcSmemBudget) continue;
-                    b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed - (size_t)a_st * p.a_stage_bytes) / b_stage);
-                } else {
-                    const size_t pair = (size_t)p.a_stage_bytes + b_stage;
-                    if (fixed + 2 * pair > kTcSmemBudget) continue;
-                    a_st = b_st = (int)std::min<size_t>(8, (kTcSmemBudget - fixed) / pair);
+            for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident)
+                for (int dual = 0; dual <= ((BN <= dual_bn && p.m_tiles > 1) ? 1 : 0); ++dual) {
+                    const int nr = dual ? 2 : 1;
+                    int a_st = 0, b_st = 0;
+                    if (resident) {
+                        // the whole K extent of the N tile stays in shared memory (loaded once per CTA, shared by both rings)
+                        const size_t bres = (size_t)rounds_b * b_stage;
+                        const int a_min = p.halo ? 1 : 2;
+                        if (rounds_b > 24 || bres + (size_t)nr * a_min * p.a_stage_bytes > avail) continue;
+                        b_st = rounds_b;
+                        a_st = (int)std::min<size_t>(p.halo ? (dual ? 3 : 4) : 8, (avail - bres) / ((size_t)nr * p.a_stage_bytes));
+                        if (nr * a_st + b_st > 30) a_st = (30 - b_st) / nr;
+                        if (a_st < a_min) continue;
+                    } else if (p.halo) {
+                        for (a_st = 2; a_st >= 1; --a_st) {
+                            if (avail < (size_t)nr * a_st * p.a_stage_bytes + (size_t)nr * 2 * b_stage) continue;
+                            b_st = (int)std::min<size_t>(bt > 1 ? 6 : 8, (avail - (size_t)nr * a_st * p.a_stage_bytes) / ((size_t)nr * b_stage));
+                            break;
+                        }
+                        if (a_st < 1) continue;
+                    } else {
+                        const size_t pair = (size_t)p.a_stage_bytes + b_stage;
+                        a_st = b_st = (int)std::min<size_t>(8, avail / (nr * pair));
+                        if (a_st < 2) continue;
+                    }
+                    if (!resident && !dual && b_st >= 3) b_st &= ~1;     // two warps feed the B ring round-robin: even count
+                    // one M=128 K=16 instruction: max(93, 43 + N/2) cycles from one issuing thread, ~max(68, 22 + N/2) from two;
+                    // the one issuing thread also spends ~300 cycles per barrier round (wait + commit)
+                    const double mma = ksteps_tile * (dual ? std::max(68.0, 22.0 + BN / 2.0) : std::max(93.0, 43.0 + BN / 2.0));
+                    const double brounds = resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b;
+                    const double issue = (brounds * 300.0 + ksteps_tile * 25.0) / (dual ? 2.0 : 1.0);
+                    const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
+                    const double b_bytes = resident ? 0.0 : (double)BN * Kp * 2;
+                    const double load = (a_bytes + b_bytes) / 32.0;                            // ~32 B/clk/SM seen from L2
+                    const double smem = (ksteps_tile * (4096.0 + 32.0 * BN) + a_bytes + b_bytes) / 128.0;
+                    const double epi = 300.0 + 10.0 * BN;
+                    double tile = std::max(std::max(std::max(mma, smem), issue), std::max(load, epi)) + 400.0;
+                    if (a_st < 2 && !dual) tile += 0.5 * a_bytes / 32.0;                       // no A prefetch across tiles
+                    Cand c = {nt, BN, a_st, b_st, bt, resident, dual, b_stage, 0.0};
+                    c.cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 32.0 : 0.0);
+                    cands.push_back(c);
                 }
-                // tensor pipe: BN/2 cycles per K step, at least 32 (the 128 x 16 A slice streams from smem at 128 B/clk);
-                // the one issuing thread: ~300 cycles per barrier round (wait + commit) + ~25 per MMA
-                // measured (tools/micro/mma_rate.cu): one M=128 K=16 instruction takes max(93, 43 + N/2) cycles with both
-                // operands in shared memory, whose bandwidth (128 B/clk) the operand reads share with TMA and the epilogue
-                if (!resident && b_st >= 3) b_st &= ~1;      // two warps feed the B ring round-robin: even stage count
-                const double mma = ksteps_tile * std::max(93.0, 43.0 + BN / 2.0);
-                const double issue = (resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b) * 300.0 +
-                                     ksteps_tile * 25.0;
-                const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
-                const double b_bytes = resident ? 0.0 : (double)BN * Kp * 2;
-                const double load = (a_bytes + b_bytes) / 30.0;                            // ~30 B/clk/SM seen from L2
-                const double epi = 12.0 * BN;
-                const double smem = (ksteps_tile * (4096.0 + 32.0 * BN) + a_bytes + b_bytes + 4.0 * 128 * BN) / 128.0;
-                double tile = std::max(std::max(std::max(mma, smem), issue), std::max(load, epi)) + 500.0;
-                if (a_st < 2) tile += 0.5 * a_bytes / 30.0;                                // no A prefetch across tiles
-                const double cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 30.0 : 0.0);
-                if (best_cost < 0 || cost < best_cost) {
-                    best_cost = cost;
-                    p.n_tiles = nt; p.BN = BN; p.a_stages = a_st; p.b_stages = b_st; p.b_taps = bt;
-                    p.b_stage_bytes = b_stage; p.row_bytes = row_bytes; p.cols_half0 = half0;
-                    p.b_resident = resident;
-                }
-            }
         }
     }
-    FCNOD_CHECK(best_cost >= 0, "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
+    FCNOD_CHECK(!cands.empty(), "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
+    std::stable_sort(cands.begin(), cands.end(), [](const Cand& x, const Cand& y) { return x.cost < y.cost; });
+    st.tc_ncand = (int)cands.size();
     {
-        // DUAL mode (two rings, two MMA-issuing threads): worth it where the tensor pipe is starved by the ~100-cycle issue
-        // cadence of one thread, i.e. for narrow N tiles; the rings are re-sized to share the same shared memory.
-        const char* de = getenv("FCNOD_DUAL");
-        const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 256;
-        p.dual = 0;
-        if (p.BN <= dual_bn && p.m_tiles > 1) {
-            const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;
-            const size_t avail = kTcSmemBudget - fixed;
-            const int rounds_b = taps * p.n_cchunks / p.b_taps;
-            int a_st = 0, b_st = 0;
-            if (p.b_resident) {
-                const size_t bres = (size_t)rounds_b * p.b_stage_bytes;
-                a_st = (int)std::min<size_t>(p.halo ? 3 : 8, (avail - bres) / (2 * (size_t)p.a_stage_bytes));
-                b_st = rounds_b;
-                if (a_st < (p.halo ? 1 : 2) || 2 * a_st + b_st > 30) a_st = 0;
-            } else if (p.halo) {
-                for (int pass = 0; pass < 2 && b_st == 0; ++pass) {
-                    if (pass == 1) {      // second try: one tap per B stage (smaller stages, more barrier rounds)
-                        if (p.b_taps == 1 || p.BN > 176) break;      // (measured: a loss for the widest N tiles)
-                        p.b_stage_bytes /= p.b_taps; p.b_taps = 1;
-                    }
-                    for (a_st = 2; a_st >= 1; --a_st) {
-                        if (avail < 2 * (size_t)a_st * p.a_stage_bytes + 4 * (size_t)p.b_stage_bytes) continue;
-                        b_st = (int)std::min<size_t>(pass ? 8 : 6, (avail - 2 * (size_t)a_st * p.a_stage_bytes) / (2 * (size_t)p.b_stage_bytes));
-                        break;
-                    }
-                }
-            } else {
-                const size_t pair = (size_t)p.a_stage_bytes + p.b_stage_bytes;
-                a_st = b_st = (int)std::min<size_t>(7, avail / (2 * pair));
-                if (a_st < 2) a_st = 0;
-            }
-            if (a_st >= 1 && b_st >= 1) { p.dual = 1; p.a_stages = a_st; p.b_stages = b_st; }
-        }
+        const Cand& c = cands[std::min<size_t>(pick < 0 ? 0 : pick, cands.size() - 1)];
+        p.n_tiles = c.nt; p.BN = c.BN; p.a_stages = c.a_st; p.b_stages = c.b_st; p.b_taps = c.bt;
+        p.b_stage_bytes = c.b_stage; p.row_bytes = 0; p.cols_half0 = ceil_div(c.BN, 64) * 16;   // columns per epilogue warp
+        p.b_resident = c.resident; p.dual = c.dual;
     }
     uint32_t acc = 32;
     while ((int)acc < p.BN) acc <<= 1;
@@ -1058,7 +1030,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         const int H2 = ob.H, W2 = ob.W, Wp = st.s2d_wp;
         void* base = net->buffers[st.s2d_buf].ptr;
         const cuuint64_t pix = kS2dCpad * 2;
-        fill_tc_geometry(net, st, B);
+        fill_tc_geometry(net, st, B, st.tc_pick);
         ConvTc2Params& p = st.tc;
         const uint32_t span = p.CK * 2;
         (void)W2;
@@ -1077,7 +1049,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         p.a_img_pitch = (unsigned long long)st.s2d_hp * Wp * pix;
         return;
     }
-    fill_tc_geometry(net, st, B);
+    fill_tc_geometry(net, st, B, st.tc_pick);
     ConvTc2Params& p = st.tc;
     const uint32_t span = cw.CK * 2;
     {
@@ -1089,6 +1061,45 @@ void setup_tc_step(fcnod_net* net, Step& st) {
     }
     encode_weight_map(st, cw, Nrows, cw.k * cw.k * cw.n_cchunks, L.name);
     bind_tc_pointers(net, st);
+}
+
+void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof);
+
+// The tiling model ranks the candidates; the device has the last word: the first few are timed on the real buffers
+// (contents are irrelevant, every tiling computes the same sums in the same K order) and the fastest one is kept.
+// FCNOD_AUTOTUNE=0 keeps the model's first choice; FCNOD_AUTOTUNE=n times n candidates (default 10).
+void autotune_tc_steps(fcnod_net* net) {
+    const char* e = getenv("FCNOD_AUTOTUNE");
+    const int ntry = e ? atoi(e) : 10;
+    if (ntry <= 1) return;
+    cudaEvent_t e0, e1;
+    FCNOD_CUDA(cudaEventCreate(&e0));
+    FCNOD_CUDA(cudaEventCreate(&e1));
+    cudaStream_t s = net->stream;
+    for (size_t i = 0; i < net->steps.size(); ++i) {
+        Step& st = net->steps[i];
+        if (st.kind != S_CONV_TC) continue;
+        int best = 0;
+        float best_ms = 0.f;
+        const int n = std::min(ntry, st.tc_ncand);
+        for (int c = 0; c < n; ++c) {
+            st.tc_pick = c;
+            setup_tc_step(net, st);
+            launch_conv_tc2(st, s, false);                       // warm-up (instruction cache, L2)
+            FCNOD_CUDA(cudaEventRecord(e0, s));
+            for (int r = 0; r < 3; ++r) launch_conv_tc2(st, s, false);
+            FCNOD_CUDA(cudaEventRecord(e1, s));
+            FCNOD_CUDA(cudaEventSynchronize(e1));
+            FCNOD_CUDA(cudaGetLastError());
+            float ms = 0.f;
+            FCNOD_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            if (c == 0 || ms < best_ms) { best_ms = ms; best = c; }
+        }
+        st.tc_pick = best;
+        setup_tc_step(net, st);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
 }
 
 void reshape(fcnod_net* net, int batch) {
@@ -1118,7 +1129,8 @@ void reshape(fcnod_net* net, int batch) {
     const Blob& in = net->blobs[0];
     FCNOD_CUDA(cudaMalloc(&net->data_dev, (size_t)batch * in.C * in.H * in.W * 4));
     for (size_t i = 0; i < net->steps.size(); ++i)
-        if (net->steps[i].kind == S_CONV_TC) setup_tc_step(net, net->steps[i]);
+        if (net->steps[i].kind == S_CONV_TC) { net->steps[i].tc_pick = -1; setup_tc_step(net, net->steps[i]); }
+    autotune_tc_steps(net);
 }
 
 // ------------------------------------------------------------------------------------ execution
@@ -1529,7 +1541,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
             o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {
