@@ -63,6 +63,8 @@ SIGNATURES = {
     'fcnod_preprocess': (_I, [_P, _I, _I, _I, _I, _I, _P]),
     'fcnod_preprocess_device': (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
     'fcnod_detect': (_I, [_P, _P, _I, _I, _I, C.POINTER(PostnetParams), _P, _P, _P, _P]),
+    'fcnod_detect_submit': (_I, [_P, _P, _I, _I, _I, C.POINTER(PostnetParams), C.POINTER(C.c_int32)]),
+    'fcnod_detect_collect': (_I, [_P, C.c_int32, _P, _P, _P, _P]),
     'fcnod_detect_from_data': (_I, [_P, _P, _I, C.POINTER(PostnetParams), _P, _P, _P, _P]),
     'fcnod_detect_device': (_I, [_P, _P, _I, C.POINTER(PostnetParams), C.POINTER(_P), C.POINTER(_P),
                                  C.POINTER(_P), C.POINTER(_P), _P]),

@@ -42,9 +42,16 @@ def build(force=False, verbose=False):
     objdir = os.path.join(HERE, 'build')
     os.makedirs(objdir, exist_ok=True)
 
+    # headers rebuild everything; a changed .cu / .cpp rebuilds only its own object
+    hdrs = [p for p in _deps() if p.endswith(('.h', '.cuh'))] + [os.path.abspath(__file__)]
+    hdr_t = max(os.path.getmtime(p) for p in hdrs)
+
     def compile_one(item):
         src, extra = item
         obj = os.path.join(objdir, src + '.o')
+        if not force and os.path.exists(obj) and \
+                os.path.getmtime(obj) > max(hdr_t, os.path.getmtime(os.path.join(CSRC, src))):
+            return obj
         cmd = [NVCC] + COMMON + extra + ['-c', os.path.join(CSRC, src), '-o', obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:

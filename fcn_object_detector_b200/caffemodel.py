@@ -67,6 +67,23 @@ def xavier_weights(conv_shapes, seed=0):
     return out
 
 
-def write_synthetic_caffemodel(path, seed=0, **kw):
+def firing_heads(layers, box=(-40.0, -40.0, 56.0, 56.0), cvg_bias=-0.6):
+    """Xavier heads give boxes a few pixels tall, which vote_boxes' `height >= 20` test (:346) always drops.  Give the
+    regressor a bias that makes every cell propose a box of `box` (x1,y1,x2,y2 relative to its cell) plus the random
+    part, and pull the coverage down so that only part of the grid fires: neighbouring proposals then cluster and
+    survive, which is what a trained snapshot does.  For tests that need detections to compare."""
+    out = []
+    for name, typ, blobs in layers:
+        w, b = blobs
+        if name == 'bbox/regressor':
+            b = np.tile(np.asarray(box, np.float32), w.shape[0] // 4)
+        elif name == 'cvg/classifier':
+            b = np.full_like(b, cvg_bias)
+        out.append((name, typ, [w, b]))
+    return out
+
+
+def write_synthetic_caffemodel(path, seed=0, firing=False, **kw):
     from .netspec import conv_shapes
-    return write_caffemodel(path, xavier_weights(conv_shapes(**kw), seed))
+    layers = xavier_weights(conv_shapes(**kw), seed)
+    return write_caffemodel(path, firing_heads(layers) if firing else layers)

@@ -179,6 +179,17 @@ struct fcnod_net {
     float* pinned_in = 0;
     size_t pinned_in_bytes = 0;
     int32_t* pinned_out = 0;
+    // streaming detect (fcnod_detect_submit / _collect): two batches in flight
+    struct DetectSlot {
+        uint8_t* img = 0;                // device copy of the batch's frames
+        size_t img_bytes = 0;
+        int32_t* pinned = 0;             // [B*2 src_hw | det | label | weight | count]
+        size_t pinned_bytes = 0;
+        cudaEvent_t up = 0, done = 0;    // upload finished (copy stream) / detections on the host (compute stream)
+        int B = 0;
+        int ticket = -1;                 // -1 = free
+    } slots[2];
+    int next_ticket = 0, oldest_ticket = 0;
 };
 
 namespace fcnod {
@@ -1495,6 +1506,12 @@ int fcnod_net_destroy(fcnod_net* net) {
         if (net->copy_stream) cudaStreamDestroy(net->copy_stream);
         for (int i = 0; i < 2; ++i) if (net->copy_ev[i]) cudaEventDestroy(net->copy_ev[i]);
         if (net->pinned_big) cudaFreeHost(net->pinned_big);
+        for (int i = 0; i < 2; ++i) {
+            if (net->slots[i].img) cudaFree(net->slots[i].img);
+            if (net->slots[i].pinned) cudaFreeHost(net->slots[i].pinned);
+            if (net->slots[i].up) cudaEventDestroy(net->slots[i].up);
+            if (net->slots[i].done) cudaEventDestroy(net->slots[i].done);
+        }
         delete net;
     }
     FCNOD_API_END
@@ -1789,6 +1806,97 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     preprocess_launch(net->img_dev, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
     detect_device(net, net->data_dev, net->srchw_dev, *p, s);
     copy_detections_out(net, B, out_det, out_label, out_weight, out_count, s);
+    FCNOD_API_END
+}
+
+int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h, int src_w, const fcnod_postnet_params* p,
+                        int32_t* ticket) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && images && p && ticket, "null argument");
+    FCNOD_CHECK(B > 0 && src_h > 0 && src_w > 0, "bad batch or source size");
+    require_device(net);
+    const int in_flight = net->next_ticket - net->oldest_ticket;
+    FCNOD_CHECK(in_flight < 2, "two batches already in flight: collect the oldest ticket first");
+    if (B != net->batch) {
+        FCNOD_CHECK(in_flight == 0, "collect the batches in flight before changing the batch size");
+        reshape(net, B);
+    }
+    const Blob& in = net->blobs[0];
+    FCNOD_CHECK(in.C == 3, "detect needs a 3-channel input blob");
+    cudaStream_t s = net->stream;
+    if (!net->copy_stream) {
+        FCNOD_CUDA(cudaStreamCreateWithFlags(&net->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) FCNOD_CUDA(cudaEventCreateWithFlags(&net->copy_ev[i], cudaEventDisableTiming));
+    }
+    fcnod_net::DetectSlot& sl = net->slots[net->next_ticket & 1];
+    FCNOD_CHECK(sl.ticket < 0, "internal: slot still owned by an uncollected ticket");
+    if (!sl.up) {
+        FCNOD_CUDA(cudaEventCreateWithFlags(&sl.up, cudaEventDisableTiming));
+        FCNOD_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
+    const size_t ibytes = (size_t)B * src_h * src_w * 3;
+    if (sl.img_bytes < ibytes) {
+        if (sl.img) cudaFree(sl.img);
+        sl.img = 0; sl.img_bytes = 0;
+        FCNOD_CUDA(cudaMalloc(&sl.img, ibytes));
+        sl.img_bytes = ibytes;
+    }
+    const size_t obytes = (size_t)B * (2 + FCNOD_MAX_DET * 7 + 1) * 4;
+    if (sl.pinned_bytes < obytes) {
+        if (sl.pinned) cudaFreeHost(sl.pinned);
+        sl.pinned = 0; sl.pinned_bytes = 0;
+        FCNOD_CUDA(cudaMallocHost(&sl.pinned, obytes));
+        sl.pinned_bytes = obytes;
+    }
+    if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)B * 6 * 4));
+    ensure_detect_buffers(net);
+    // upload on the copy stream: overlaps whatever the compute stream is still doing for the previous ticket.
+    // The slot's previous reader (the prelude of ticket-2) finished before that ticket was collected.
+    FCNOD_CUDA(cudaMemcpyAsync(sl.img, images, ibytes, cudaMemcpyHostToDevice, net->copy_stream));
+    FCNOD_CUDA(cudaEventRecord(sl.up, net->copy_stream));
+    int32_t* hw = sl.pinned;
+    for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
+    FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
+    preprocess_launch(sl.img, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
+    detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+    int32_t* p_det = sl.pinned + (size_t)B * 2;
+    int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
+    int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
+    int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
+    FCNOD_CUDA(cudaMemcpyAsync(p_det, net->det_dev, (size_t)B * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(p_lab, net->label_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(p_w, net->weight_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(p_cnt, net->count_dev, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaEventRecord(sl.done, s));
+    sl.B = B;
+    sl.ticket = net->next_ticket;
+    *ticket = net->next_ticket++;
+    FCNOD_API_END
+}
+
+int fcnod_detect_collect(fcnod_net* net, int32_t ticket, int32_t* out_det, int32_t* out_label, int32_t* out_weight,
+                         int32_t* out_count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && out_det && out_label && out_weight && out_count, "null argument");
+    require_device(net);
+    FCNOD_CHECK(net->oldest_ticket < net->next_ticket, "no batch in flight");
+    FCNOD_CHECK(ticket == net->oldest_ticket, "tickets are collected in submission order");
+    fcnod_net::DetectSlot& sl = net->slots[ticket & 1];
+    FCNOD_CHECK(sl.ticket == ticket, "internal: ticket / slot mismatch");
+    // whatever happens below, the ticket is consumed (a device fault is sticky anyway)
+    sl.ticket = -1;
+    ++net->oldest_ticket;
+    FCNOD_CUDA(cudaEventSynchronize(sl.done));
+    const int B = sl.B;
+    const int32_t* p_det = sl.pinned + (size_t)B * 2;
+    const int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
+    const int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
+    const int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
+    memcpy(out_det, p_det, (size_t)B * FCNOD_MAX_DET * 5 * 4);
+    memcpy(out_label, p_lab, (size_t)B * FCNOD_MAX_DET * 4);
+    memcpy(out_weight, p_w, (size_t)B * FCNOD_MAX_DET * 4);
+    memcpy(out_count, p_cnt, (size_t)B * 4);
     FCNOD_API_END
 }
 

@@ -44,49 +44,71 @@ __global__ void __launch_bounds__(256) pre_minmax_kernel(const uint8_t* __restri
     }
 }
 
+// A frame holds at most 3 x 256 distinct normalised values ((p - mean_c) - min) / range: each CTA (one frame,
+// a band of output rows) evaluates them once into shared memory in float64 -- the same expression, so the
+// same bits, as evaluating it per tap -- and the resample is table reads + the two lerps.
 template <int VEC>
-__global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __restrict__ img, int B, int src_h, int src_w,
+__global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __restrict__ img, int src_h, int src_w,
                                                            int net_h, int net_w, const int* __restrict__ mm,
                                                            float* __restrict__ data) {
-    const int wv = net_w / VEC;
-    const long total = (long)B * net_h * wv;
+    __shared__ double lut[3][256];
+    __shared__ float lutf[3][256];
+    const int b = blockIdx.y;
     const bool same = (src_h == net_h && src_w == net_w);
-    const double sy = (double)src_h / (double)net_h, sx = (double)src_w / (double)net_w;
-    for (long t = blockIdx.x * (long)blockDim.x + threadIdx.x; t < total; t += (long)gridDim.x * blockDim.x) {
-        const int xv = (int)(t % wv);
-        const long r = t / wv;
-        const int oy = (int)(r % net_h), b = (int)(r / net_h);
+    {
         const int* m = mm + b * 6;
-        double mn = fmin(fmin((double)m[0] - mean64(0), (double)m[1] - mean64(1)), (double)m[2] - mean64(2));
-        double mx = fmax(fmax((double)m[3] - mean64(0), (double)m[4] - mean64(1)), (double)m[5] - mean64(2));
+        const double mn = fmin(fmin((double)m[0] - mean64(0), (double)m[1] - mean64(1)), (double)m[2] - mean64(2));
+        const double mx = fmax(fmax((double)m[3] - mean64(0), (double)m[4] - mean64(1)), (double)m[5] - mean64(2));
         const double range = mx - mn;
-        const uint8_t* p = img + (size_t)b * src_h * src_w * 3;
-        double fyd = ((double)oy + 0.5) * sy - 0.5;
-        int y0 = (int)floor(fyd);
-        double ay = fyd - (double)y0;
-        if (y0 < 0) { y0 = 0; ay = 0.0; }
-        if (y0 >= src_h - 1) { y0 = src_h - 1; ay = 0.0; }
-        const int y1 = min(y0 + 1, src_h - 1);
+        for (int i = threadIdx.x; i < 768; i += blockDim.x) {
+            const int c = i >> 8, v = i & 255;
+            const double q = (((double)v - mean64(c)) - mn) / range;
+            lut[c][v] = q;
+            lutf[c][v] = (float)q;
+        }
+    }
+    __syncthreads();
+    const int wv = net_w / VEC;
+    const int rows_per = (net_h + gridDim.x - 1) / gridDim.x;
+    const int row0 = blockIdx.x * rows_per, row1 = min(row0 + rows_per, net_h);
+    const uint8_t* p = img + (size_t)b * src_h * src_w * 3;
+    const double sy = (double)src_h / (double)net_h, sx = (double)src_w / (double)net_w;
+    const int total = (row1 - row0) * wv;
+    for (int t = threadIdx.x; t < total; t += blockDim.x) {
+        const int xv = t % wv;
+        const int oy = row0 + t / wv;
         float res[3][VEC];
+        if (same) {
+            const uint8_t* q = p + ((size_t)oy * src_w + xv * VEC) * 3;
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) {
-            const int ox = xv * VEC + v;
-            double fxd = ((double)ox + 0.5) * sx - 0.5;
-            int x0 = (int)floor(fxd);
-            double ax = fxd - (double)x0;
-            if (x0 < 0) { x0 = 0; ax = 0.0; }
-            if (x0 >= src_w - 1) { x0 = src_w - 1; ax = 0.0; }
-            const int x1 = min(x0 + 1, src_w - 1);
+            for (int v = 0; v < VEC; ++v)
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const double mc = mean64(c);
-                const double p00 = (((double)p[((size_t)y0 * src_w + x0) * 3 + c] - mc) - mn) / range;
-                if (same) { res[c][v] = (float)p00; continue; }
-                const double p01 = (((double)p[((size_t)y0 * src_w + x1) * 3 + c] - mc) - mn) / range;
-                const double p10 = (((double)p[((size_t)y1 * src_w + x0) * 3 + c] - mc) - mn) / range;
-                const double p11 = (((double)p[((size_t)y1 * src_w + x1) * 3 + c] - mc) - mn) / range;
-                const double tp = p00 * (1.0 - ax) + p01 * ax, bt = p10 * (1.0 - ax) + p11 * ax;
-                res[c][v] = (float)(tp * (1.0 - ay) + bt * ay);
+                for (int c = 0; c < 3; ++c) res[c][v] = lutf[c][q[v * 3 + c]];
+        } else {
+            double fyd = ((double)oy + 0.5) * sy - 0.5;
+            int y0 = (int)floor(fyd);
+            double ay = fyd - (double)y0;
+            if (y0 < 0) { y0 = 0; ay = 0.0; }
+            if (y0 >= src_h - 1) { y0 = src_h - 1; ay = 0.0; }
+            const int y1 = min(y0 + 1, src_h - 1);
+            const uint8_t* r0 = p + (size_t)y0 * src_w * 3;
+            const uint8_t* r1 = p + (size_t)y1 * src_w * 3;
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) {
+                const int ox = xv * VEC + v;
+                double fxd = ((double)ox + 0.5) * sx - 0.5;
+                int x0 = (int)floor(fxd);
+                double ax = fxd - (double)x0;
+                if (x0 < 0) { x0 = 0; ax = 0.0; }
+                if (x0 >= src_w - 1) { x0 = src_w - 1; ax = 0.0; }
+                const int x1 = min(x0 + 1, src_w - 1);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const double p00 = lut[c][r0[x0 * 3 + c]], p01 = lut[c][r0[x1 * 3 + c]];
+                    const double p10 = lut[c][r1[x0 * 3 + c]], p11 = lut[c][r1[x1 * 3 + c]];
+                    const double tp = p00 * (1.0 - ax) + p01 * ax, bt = p10 * (1.0 - ax) + p11 * ax;
+                    res[c][v] = (float)(tp * (1.0 - ay) + bt * ay);
+                }
             }
         }
 #pragma unroll
@@ -98,14 +120,6 @@ __global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __rest
                 for (int v = 0; v < VEC; ++v) o[v] = res[c][v];
         }
     }
-}
-
-int grid_1d(long items, int threads) {
-    long b = (items + threads - 1) / threads;
-    long cap = 148L * 16;
-    if (b > cap) b = cap;
-    if (b < 1) b = 1;
-    return (int)b;
 }
 
 }  // namespace
@@ -120,10 +134,13 @@ void preprocess_launch(const uint8_t* images_dev, int B, int src_h, int src_w, i
     FCNOD_CUDA(cudaGetLastError());
     pre_minmax_kernel<<<dim3(32, B), 256, 0, s>>>(images_dev, (long)src_h * src_w, mm);
     FCNOD_CUDA(cudaGetLastError());
+    // bands of output rows per frame: about 16 CTAs per SM in flight over the whole batch, at least 4 rows a band
+    int bands = ceil_div(148 * 16, B);
+    bands = max(1, min(bands, ceil_div(net_h, 4)));
     if (net_w % 4 == 0)
-        pre_resample_kernel<4><<<grid_1d((long)B * net_h * (net_w / 4), 256), 256, 0, s>>>(images_dev, B, src_h, src_w, net_h, net_w, mm, data_dev);
+        pre_resample_kernel<4><<<dim3(bands, B), 256, 0, s>>>(images_dev, src_h, src_w, net_h, net_w, mm, data_dev);
     else
-        pre_resample_kernel<1><<<grid_1d((long)B * net_h * net_w, 256), 256, 0, s>>>(images_dev, B, src_h, src_w, net_h, net_w, mm, data_dev);
+        pre_resample_kernel<1><<<dim3(bands, B), 256, 0, s>>>(images_dev, src_h, src_w, net_h, net_w, mm, data_dev);
     FCNOD_CUDA(cudaGetLastError());
 }
 

@@ -93,6 +93,52 @@ class FCNObjectDetector(object):
         self.__net._sync_after_device_run(B)
         return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64)) for b in range(B)]
 
+    def predict_stream(self, batches):
+        """Generator over an iterable of (B,H,W,3) uint8 BGR batches (the node's image stream, :134-147, batched).
+        Yields predict_batch's result for every batch, in order, keeping two batches in flight
+        (fcnod_detect_submit / fcnod_detect_collect): the upload of batch i+1 overlaps the compute of batch i.
+        A batch's array must not be overwritten before its result is yielded; page-locked arrays overlap."""
+        L = _lib.lib()
+        M = _lib.FCNOD_MAX_DET
+        p = self._params()
+        pending = []
+
+        def collect():
+            ticket, images, B = pending.pop(0)
+            det = np.empty((B, M, 5), np.int32)
+            lab = np.empty((B, M), np.int32)
+            wgt = np.empty((B, M), np.int32)
+            cnt = np.empty((B,), np.int32)
+            _lib.check(L.fcnod_detect_collect(self.__net.handle, ticket, _lib.ptr(det), _lib.ptr(lab), _lib.ptr(wgt),
+                                              _lib.ptr(cnt)))
+            return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64)) for b in range(B)]
+
+        try:
+            for images in batches:
+                images = np.ascontiguousarray(images, dtype=np.uint8)
+                if images.ndim != 4 or images.shape[3] != 3:
+                    raise ValueError('images must be (B,H,W,3) uint8 BGR')
+                B, H, W, _ = images.shape
+                if pending and pending[0][2] != B:           # the batch size changes only with nothing in flight
+                    while pending:
+                        yield collect()
+                ticket = C.c_int32(-1)
+                _lib.check(L.fcnod_detect_submit(self.__net.handle, _lib.ptr(images), B, H, W, C.byref(p),
+                                                 C.byref(ticket)))
+                pending.append((ticket.value, images, B))
+                if len(pending) == 2:
+                    yield collect()
+            while pending:
+                yield collect()
+        finally:
+            # an abandoned generator must not leave tickets in flight
+            while pending:
+                try:
+                    collect()
+                except Exception:
+                    pending.clear()
+            self.__net._sync_after_device_run()
+
     def predict_data(self, data):
         """data: (B,3,H,W) float32 blob contents (post-prelude).  Returns per-frame (boxes, labels, weights)."""
         data = np.ascontiguousarray(data, dtype=np.float32)

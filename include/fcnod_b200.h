@@ -116,6 +116,17 @@ int fcnod_preprocess_device(const uint8_t* images_dev, int B, int src_h, int src
  * Uses blobs `coverage` / `bboxes`. */
 int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int src_w, const fcnod_postnet_params* p,
                  int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);
+/* Streaming form of fcnod_detect for a caller that feeds batch after batch (the detector node's image
+ * callback, scripts/fcn_object_detector.py:134-147, batched): submit() enqueues the upload, the prelude, the
+ * network and the post-net of one batch and returns a ticket at once; collect() blocks until that batch's
+ * detections are in host memory.  Two batches may be in flight: the upload of batch i+1 (own copy stream, own
+ * device image slot) overlaps the compute of batch i.  `images` must stay valid until its collect() and
+ * should be page-locked, otherwise the upload is synchronous.  Tickets are collected in submission order;
+ * the batch size may only change while nothing is in flight. */
+int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h, int src_w,
+                        const fcnod_postnet_params* p, int32_t* ticket);
+int fcnod_detect_collect(fcnod_net* net, int32_t ticket, int32_t* out_det, int32_t* out_label, int32_t* out_weight,
+                         int32_t* out_count);
 /* Same, starting from blob `data` already in HOST memory (B*3*H*W float32). */
 int fcnod_detect_from_data(fcnod_net* net, const float* data_host, int B, const fcnod_postnet_params* p,
                            int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);

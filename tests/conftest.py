@@ -31,6 +31,17 @@ def model_files(tmp_path_factory):
 
 
 @pytest.fixture(scope='session')
+def firing_model_files(tmp_path_factory):
+    """Same net, heads biased so that random frames yield detections (caffemodel.firing_heads)."""
+    from fcn_object_detector_b200.caffemodel import write_synthetic_caffemodel
+    from fcn_object_detector_b200.netspec import write_deploy_prototxt
+    d = tmp_path_factory.mktemp('model_firing')
+    proto = write_deploy_prototxt(str(d / 'deploy.prototxt'))
+    cm = write_synthetic_caffemodel(str(d / 'snapshot_iter_1000.caffemodel'), seed=0, firing=True)
+    return proto, cm
+
+
+@pytest.fixture(scope='session')
 def oracle_net(model_files):
     from oracle import prototxt
     from oracle.caffemodel_io import read_caffemodel

@@ -64,3 +64,79 @@ def test_detect_batch_bf16_consistency(model_files):
     for b in range(4):
         ob, ol = postnet_ref.postnet(cov[b], bb[b], imgs[b].shape, prob_thresh=0.45, min_boxes=1)
         assert np.array_equal(res[b][0], ob) and np.array_equal(res[b][1], ol)
+
+
+def test_predict_stream_equals_predict_batch(firing_model_files):
+    """Streaming submit/collect (two batches in flight, upload overlapped with compute) returns, batch for batch,
+    exactly what the one-call path returns -- including across a batch-size change and a source-size change."""
+    from fcn_object_detector_b200.detector import FCNObjectDetector
+    proto, cm = firing_model_files
+    rs = np.random.RandomState(11)
+    batches = [rs.randint(0, 256, (4, 480, 640, 3)).astype(np.uint8) for _ in range(4)]
+    batches += [rs.randint(0, 256, (2, 448, 448, 3)).astype(np.uint8) for _ in range(3)]
+    batches += [rs.randint(0, 256, (2, 300, 200, 3)).astype(np.uint8)]
+    det = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='bf16', detection_threshold=0.45,
+                            min_boxes=1)
+    want = [det.predict_batch(b) for b in batches]
+    got = list(det.predict_stream(iter(batches)))
+    assert len(got) == len(want)
+    ndet = 0
+    for g, w in zip(got, want):
+        assert len(g) == len(w)
+        for (gb, gl), (wb, wl) in zip(g, w):
+            assert np.array_equal(gb, wb) and np.array_equal(gl, wl)
+            ndet += len(wb)
+    assert ndet >= len(batches)          # the biased heads fire on every frame
+    # the one-call path still works after streaming, and an abandoned stream leaves nothing in flight
+    it = det.predict_stream(iter(batches[:3]))
+    next(it)
+    it.close()
+    again = det.predict_batch(batches[0])
+    assert all(np.array_equal(a[0], b[0]) for a, b in zip(again, want[0]))
+
+
+def test_detect_submit_collect_errors(model_files):
+    import ctypes as C
+    from fcn_object_detector_b200 import _lib
+    from fcn_object_detector_b200.detector import FCNObjectDetector
+    proto, cm = model_files
+    det = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='bf16')
+    L = _lib.lib()
+    h = det.net.handle
+    p = _lib.default_postnet_params()
+    imgs = np.zeros((2, 448, 448, 3), np.uint8)
+    M = _lib.FCNOD_MAX_DET
+    out = [np.zeros((2, M, 5), np.int32), np.zeros((2, M), np.int32), np.zeros((2, M), np.int32), np.zeros((2,), np.int32)]
+    ptrs = [_lib.ptr(o) for o in out]
+    t = [C.c_int32(-1) for _ in range(3)]
+    assert L.fcnod_detect_collect(h, 0, *ptrs) != 0                       # nothing in flight
+    assert L.fcnod_detect_submit(h, _lib.ptr(imgs), 2, 448, 448, C.byref(p), C.byref(t[0])) == 0
+    assert L.fcnod_detect_submit(h, _lib.ptr(imgs), 2, 448, 448, C.byref(p), C.byref(t[1])) == 0
+    assert L.fcnod_detect_submit(h, _lib.ptr(imgs), 2, 448, 448, C.byref(p), C.byref(t[2])) != 0   # a third one
+    assert b'in flight' in L.fcnod_last_error()
+    assert L.fcnod_detect_collect(h, t[1].value, *ptrs) != 0              # out of order
+    assert L.fcnod_detect_collect(h, t[0].value, *ptrs) == 0
+    imgs4 = np.zeros((4, 448, 448, 3), np.uint8)
+    assert L.fcnod_detect_submit(h, _lib.ptr(imgs4), 4, 448, 448, C.byref(p), C.byref(t[2])) != 0  # batch change in flight
+    assert L.fcnod_detect_collect(h, t[1].value, *ptrs) == 0
+
+
+def test_run_detector_firing_heads_matches_oracle(firing_model_files):
+    """fp32, heads that fire: boxes and labels equal the oracle post-net on the GPU's own maps, non-empty, at a
+    source size that exercises resize_detection; the maps match the oracle net to 1e-5."""
+    from fcn_object_detector_b200.detector import FCNObjectDetector
+    from oracle import prototxt
+    from oracle.caffemodel_io import read_caffemodel
+    proto, cm = firing_model_files
+    img = np.random.RandomState(5).randint(0, 256, (480, 640, 3)).astype(np.uint8)
+    det = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='fp32', detection_threshold=0.45)
+    boxes, labels = det.predict(img)
+    cov = det.net.blobs['coverage'].data[0].copy(); bb = det.net.blobs['bboxes'].data[0].copy()
+    ob, ol = postnet_ref.postnet(cov, bb, img.shape, prob_thresh=0.45)
+    assert len(ob) > 0
+    assert np.array_equal(boxes, ob) and np.array_equal(labels, ol)
+    x = postnet_ref.preprocess(img, 448, 448)[None]
+    exp = net_ref.forward(prototxt.layers(prototxt.load(proto)), read_caffemodel(cm), x, want=['coverage', 'bboxes'])
+    assert rel_err(cov, exp['coverage'][0]) < 1e-5 and rel_err(bb, exp['bboxes'][0]) < 1e-5
+    eb, el = postnet_ref.postnet(exp['coverage'][0], exp['bboxes'][0], img.shape, prob_thresh=0.45)
+    assert len(eb) == len(ob)
