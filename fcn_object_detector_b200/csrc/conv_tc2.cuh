@@ -64,10 +64,15 @@ struct ConvTc2Params {
     int a_stages, b_stages;
     int b_taps;              // K-blocks per B stage: 1, or kw in HALO mode (one kernel row of taps per TMA / barrier round)
     uint32_t a_stage_bytes, b_stage_bytes, a_tx_bytes;
-    uint32_t tmem_cols;      // whole allocation (2 accumulators), power of two
-    uint32_t acc_stride;     // columns between the two accumulators
-    uint32_t row_bytes;      // staging row pitch of one epilogue warp: 32, 64 or 128 bytes (>= its columns * 2)
-    int cols_half0;          // columns drained by each of the four warps of a quadrant (multiple of 16; the last ones get the rest)
+    uint32_t tmem_cols;      // whole allocation (2 or 4 accumulators), power of two
+    uint32_t acc_stride;     // columns between two accumulators
+    uint32_t acc_lg;         // log2(number of accumulators): 1, or 2 when 4 * acc_stride <= 512
+    // Epilogue groups: the 16 epilogue warps drain one tile together (egroups = 1, four warps per TMEM lane quadrant, each
+    // a quarter of the columns), or split into 2 / 4 groups that drain alternate tiles (8 / 4 warps per tile, each warp up
+    // to 64 columns).  A tile costs every warp that touches it a fixed ~150 instructions (coordinates, barrier, addresses):
+    // with narrow N tiles that overhead, paid 16 times per tile, is what bounds the kernel.
+    uint32_t egroups;
+    int cols_half0;          // columns drained by each warp of a quadrant's group (multiple of 16; the last ones get the rest)
     int flags;               // SEG_RELU / SEG_DIRECT: uniform over the segments of one launch
     int bt_interior;         // bias_tab: class index of interior pixels (== the row `bias` points at)
     int nseg;
@@ -194,8 +199,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t bar_base = bias_base + (uint32_t)kTcEpiWarps * 256u;
     const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * nr * p.a_stages;
     const uint32_t bfull0 = aempty0 + 8u * nr * p.a_stages, bempty0 = bfull0 + 8u * nrb * p.b_stages;
-    const uint32_t tfull0 = bempty0 + 8u * nrb * p.b_stages, tempty0 = tfull0 + 16u;
-    const uint32_t tmem_slot = tempty0 + 16u;
+    const uint32_t tfull0 = bempty0 + 8u * nrb * p.b_stages, tempty0 = tfull0 + 32u;     // up to 4 accumulators
+    const uint32_t tmem_slot = tempty0 + 32u;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int my_nt = (int)blockIdx.x % p.n_tiles;
@@ -205,7 +210,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     if (threadIdx.x == 0) {
         for (int s = 0; s < nr * p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
         for (int s = 0; s < nrb * p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, kTcEpiWarps); }
+        for (int a = 0; a < 4; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, kTcEpiWarps / p.egroups); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -334,7 +339,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             uint32_t a_lo = a_lo_base, b_lo = b_lo_base;
             int it = mw;
             for (int mt = (int)blockIdx.x / p.n_tiles + mw * p.mstride; mt < p.m_tiles; mt += it_step * p.mstride, it += it_step) {
-                const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
+                const uint32_t acc = (uint32_t)it & ((1u << p.acc_lg) - 1u), aphase = ((uint32_t)it >> p.acc_lg) & 1u;
                 const int itp = it < 8 ? it : 8;
                 if (PROF) FCNOD_PROF(1, itp, 61);
                 mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);     // the epilogue has drained this accumulator
@@ -414,7 +419,9 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         // Everything that does not change from tile to tile is computed once: the lane's position inside the pixel box,
         // the bias of the warp's columns (staged in shared memory) and the destination of each 16-column group.
         const int ew = warp - (kTcMmaWarp + 1);
-        const int q = warp & 3, part = ew >> 2;
+        const int q = warp & 3;
+        const int egrp = (ew >> 2) & (int)(p.egroups - 1u);          // which tiles: it % egroups == egrp
+        const int part = (ew >> 2) / (int)p.egroups;                 // which columns of them
         const int HW = p.H * p.W;
         // this warp's columns inside the N tile: [wc0, wc0 + wcols), 16-column granular, at most 64
         const int wc0 = min(part * p.cols_half0, p.BN);
@@ -452,11 +459,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             }
         }
         __syncwarp();
-        int it = 0;
+        int it = egrp;
         TileIter ti;
         ti.init(p);
-        for (; ti.valid(p); ++it, ti.next(p)) {
-            const uint32_t acc = (uint32_t)it & 1u, aphase = ((uint32_t)it >> 1) & 1u;
+        for (int k = 0; k < egrp; ++k) ti.next(p);
+        for (; ti.valid(p); it += (int)p.egroups) {
+            const uint32_t acc = (uint32_t)it & ((1u << p.acc_lg) - 1u), aphase = ((uint32_t)it >> p.acc_lg) & 1u;
             const int n_img = ti.img;
             const int oh = ti.ty * p.BH + py, ow = ti.tx * p.BW + px;
             const bool valid = vpos && (oh < p.H) && (ow < p.W);
@@ -574,6 +582,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             }
             __syncwarp();
             if (PROF && ew == 0 && lane == 0) FCNOD_PROF(2, it, 3);
+            for (uint32_t k = 0; k < p.egroups; ++k) ti.next(p);
         }
     }
     __syncthreads();

@@ -766,7 +766,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     const char* de = getenv("FCNOD_DUAL");
     const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 256;
     const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);   // real 16-wide K steps
-    const size_t fixed = (size_t)kTcEpiWarps * 256 + 512 + 1024;     // bias staging, barriers, alignment slack
+    const size_t fixed = (size_t)kTcEpiWarps * 256 + 1024 + 1024;     // bias staging, barriers, alignment slack
     const size_t avail = kTcSmemBudget - fixed;
     struct Cand { int nt, BN, a_st, b_st, bt, resident, dual; uint32_t b_stage; double cost; };
     std::vector<Cand> cands;
@@ -829,16 +829,24 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     {
         const Cand& c = cands[std::min<size_t>(pick < 0 ? 0 : pick, cands.size() - 1)];
         p.n_tiles = c.nt; p.BN = c.BN; p.a_stages = c.a_st; p.b_stages = c.b_st; p.b_taps = c.bt;
-        p.b_stage_bytes = c.b_stage; p.row_bytes = 0; p.cols_half0 = ceil_div(c.BN, 64) * 16;   // columns per epilogue warp
+        p.b_stage_bytes = c.b_stage;
         p.b_resident = c.resident; p.dual = c.dual;
     }
     uint32_t acc = 32;
     while ((int)acc < p.BN) acc <<= 1;
     p.acc_stride = acc;
-    p.tmem_cols = std::max<uint32_t>(2 * acc, 32);
+    // four accumulators when they fit the 512 TMEM columns; narrow N tiles are drained by 4 (or 8) warps each, alternate
+    // tiles by alternate warp groups, instead of by all 16 (ConvTc2Params::egroups)
+    p.acc_lg = 4 * acc <= 512 ? 2 : 1;
+    static const int egroups_env = getenv("FCNOD_EGROUPS") ? atoi(getenv("FCNOD_EGROUPS")) : 0;
+    p.egroups = p.BN <= 64 ? 4 : (p.BN <= 128 ? 2 : 1);
+    if (egroups_env == 1 || egroups_env == 2) p.egroups = std::min<uint32_t>(p.egroups, (uint32_t)egroups_env);
+    if (p.acc_lg == 1 && p.egroups > 2) p.egroups = 2;
+    p.cols_half0 = ceil_div(p.BN, 16 * (4 / (int)p.egroups)) * 16;   // columns per epilogue warp (<= 64)
+    p.tmem_cols = std::max<uint32_t>((1u << p.acc_lg) * acc, 32);
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
     st.tc_smem = (size_t)(p.dual ? 2 : 1) * p.a_stages * p.a_stage_bytes +
-                 (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 512 + 1024;
+                 (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 1024 + 1024;
     p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
     st.tc_grid = p.mstride * p.n_tiles;
     {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
@@ -1558,7 +1566,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
             o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " eg=" << st.tc.egroups << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {

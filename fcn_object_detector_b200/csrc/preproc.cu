@@ -22,11 +22,40 @@ __global__ void pre_init_kernel(int* mm, int B) {
     if (i < B * 6) mm[i] = (i % 6) < 3 ? 255 : 0;     // [b][0..2] = min per channel, [b][3..5] = max
 }
 
+// Byte-wise SIMD (__vminu4 / __vmaxu4) over 48-byte chunks (16 pixels, three 128-bit loads).  A 12-byte period is three
+// words whose bytes carry channels (0,1,2,0) (1,2,0,1) (2,0,1,2): one packed accumulator per word phase, unpacked
+// at the end.  Frames that do not start on a 16-byte boundary take the scalar loop.
 __global__ void __launch_bounds__(256) pre_minmax_kernel(const uint8_t* __restrict__ img, long npix, int* __restrict__ mm) {
     const int b = blockIdx.y;
     const uint8_t* p = img + (size_t)b * npix * 3;
     int mn[3] = {255, 255, 255}, mx[3] = {0, 0, 0};
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < npix; i += (long)gridDim.x * blockDim.x) {
+    const long tid = blockIdx.x * (long)blockDim.x + threadIdx.x, nthr = (long)gridDim.x * blockDim.x;
+    long done = 0;                                                     // pixels covered by the vector part
+    if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const long nchunk = npix / 16;
+        const uint4* pv = reinterpret_cast<const uint4*>(p);
+        unsigned lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+        for (long i = tid; i < nchunk; i += nthr) {
+            const uint4 q0 = __ldg(pv + 3 * i), q1 = __ldg(pv + 3 * i + 1), q2 = __ldg(pv + 3 * i + 2);
+            // word phases: q0 = 0 1 2 0, q1 = 1 2 0 1, q2 = 2 0 1 2
+            lo[0] = __vminu4(lo[0], __vminu4(__vminu4(q0.x, q0.w), __vminu4(q1.z, q2.y)));
+            lo[1] = __vminu4(lo[1], __vminu4(__vminu4(q0.y, q1.x), __vminu4(q1.w, q2.z)));
+            lo[2] = __vminu4(lo[2], __vminu4(__vminu4(q0.z, q1.y), __vminu4(q2.x, q2.w)));
+            hi[0] = __vmaxu4(hi[0], __vmaxu4(__vmaxu4(q0.x, q0.w), __vmaxu4(q1.z, q2.y)));
+            hi[1] = __vmaxu4(hi[1], __vmaxu4(__vmaxu4(q0.y, q1.x), __vmaxu4(q1.w, q2.z)));
+            hi[2] = __vmaxu4(hi[2], __vmaxu4(__vmaxu4(q0.z, q1.y), __vmaxu4(q2.x, q2.w)));
+        }
+#pragma unroll
+        for (int ph = 0; ph < 3; ++ph)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int c = (ph + k) % 3;                            // byte k of a phase-ph word
+                mn[c] = min(mn[c], (int)((lo[ph] >> (8 * k)) & 255u));
+                mx[c] = max(mx[c], (int)((hi[ph] >> (8 * k)) & 255u));
+            }
+        done = nchunk * 16;
+    }
+    for (long i = done + tid; i < npix; i += nthr) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) { int v = p[i * 3 + c]; mn[c] = min(mn[c], v); mx[c] = max(mx[c], v); }
     }
@@ -80,10 +109,22 @@ __global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __rest
         float res[3][VEC];
         if (same) {
             const uint8_t* q = p + ((size_t)oy * src_w + xv * VEC) * 3;
+            bool wide = false;
+            if constexpr (VEC == 4) {
+                if ((reinterpret_cast<uintptr_t>(q) & 3) == 0) {
+                    const unsigned* qw = reinterpret_cast<const unsigned*>(q);
+                    const unsigned w[3] = {__ldg(qw), __ldg(qw + 1), __ldg(qw + 2)};
 #pragma unroll
-            for (int v = 0; v < VEC; ++v)
+                    for (int k = 0; k < 12; ++k) res[k % 3][k / 3] = lutf[k % 3][(w[k >> 2] >> (8 * (k & 3))) & 255u];
+                    wide = true;
+                }
+            }
+            if (!wide) {
 #pragma unroll
-                for (int c = 0; c < 3; ++c) res[c][v] = lutf[c][q[v * 3 + c]];
+                for (int v = 0; v < VEC; ++v)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) res[c][v] = lutf[c][q[v * 3 + c]];
+            }
         } else {
             double fyd = ((double)oy + 0.5) * sy - 0.5;
             int y0 = (int)floor(fyd);

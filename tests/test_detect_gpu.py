@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 def test_preprocess_matches_oracle():
     from fcn_object_detector_b200.detector import preprocess
     rs = np.random.RandomState(0)
-    for shape in ((448, 448), (480, 640), (300, 200)):
+    for shape in ((448, 448), (480, 640), (300, 200), (301, 203)):     # the last: frames off the 16-byte grid
         imgs = rs.randint(0, 256, (3,) + shape + (3,)).astype(np.uint8)
         got = preprocess(imgs)
         for b in range(3):
