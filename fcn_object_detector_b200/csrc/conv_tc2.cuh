@@ -111,6 +111,15 @@ __device__ __forceinline__ void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, u
         ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accum)
         : "memory");
 }
+// One lane of a CONVERGED warp.  The MMA warps run their whole loop with all 32 lanes and elect the lane only around the
+// tcgen05 instructions: descriptors and barrier addresses are then warp-uniform values the compiler keeps in uniform
+// registers.  Under `if (lane == 0)` it had to broadcast them register by register in a waterfall loop before every
+// UTCHMMA (ELECT + 5 R2UR.BROADCAST + BRA.U.ANY), which is what cost ~100 cycles per instruction.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 // tcgen05.wait::ld that also ties the 32 destination registers to the wait, so that no read of them can be
 // scheduled above it
 __device__ __forceinline__ void tmem_ld_wait_dep32(uint32_t* r) {
@@ -202,7 +211,9 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t tfull0 = bempty0 + 8u * nrb * p.b_stages, tempty0 = tfull0 + 32u;     // up to 4 accumulators
     const uint32_t tmem_slot = tempty0 + 32u;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warp index through a shuffle: provably warp-uniform for the compiler (role branches and everything derived from the
+    // role stay in uniform registers)
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int my_nt = (int)blockIdx.x % p.n_tiles;
     const int taps = p.kh * p.kw;
     const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
@@ -224,6 +235,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
     if (warp == 1 || warp == 2 || (warp == 3 && !p.dual)) {
         // ================= TMA producers (one thread per warp) ========================================================
@@ -316,7 +328,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         // The issuing thread is latency-bound on its OWN instruction stream, so the tap loops are unrolled at compile
         // time (KK = kernel size) and a whole kernel row of taps shares one barrier round.
         const int mw = warp == 0 ? 0 : 1;
-        if (lane == 0 && (mw == 0 || p.dual)) {
+        if (mw == 0 || p.dual) {      // all 32 lanes, converged; one elected lane issues
             const int ring = mw;
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | (8u << 24);
             // descriptor = {lo: start address >> 4 | LBO 1 << 16, hi: SBO (8 rows) >> 4 | version 1 << 14 | swizzle << 29}
@@ -341,10 +353,11 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             for (int mt = (int)blockIdx.x / p.n_tiles + mw * p.mstride; mt < p.m_tiles; mt += it_step * p.mstride, it += it_step) {
                 const uint32_t acc = (uint32_t)it & ((1u << p.acc_lg) - 1u), aphase = ((uint32_t)it >> p.acc_lg) & 1u;
                 const int itp = it < 8 ? it : 8;
-                if (PROF) FCNOD_PROF(1, itp, 61);
+                if (PROF && lane == 0) FCNOD_PROF(1, itp, 61);
                 mbar_wait_hint(tempty0 + 8u * acc, aphase ^ 1u);     // the epilogue has drained this accumulator
+                __syncwarp();
                 fence_after();
-                if (PROF) FCNOD_PROF(1, itp, 62);
+                if (PROF && lane == 0) FCNOD_PROF(1, itp, 62);
                 const uint32_t tmem_d = tmem_base + acc * p.acc_stride;
                 const bool wait_b = !(resident && it > mw);
                 uint32_t accum = 0;
@@ -355,7 +368,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
 #pragma unroll
                     for (int k = 0; k < KSTEPS; ++k) {
                         if (KSTEPS == 1 || k < ks) {
-                            umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_tap + 2u * k, desc_hi, idesc, accum);
+                            if (elect_one()) umma_bf16_lohi(tmem_d, a_tap + 2u * k, b_tap + 2u * k, desc_hi, idesc, accum);
                             accum = 1;
                         }
                     }
@@ -363,18 +376,20 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 auto b_wait = [&]() {
                     if (wait_b) {
                         mbar_wait_hint(bf + 8u * sb, pb);
+                        __syncwarp();
                         fence_after();
-                        if (PROF) FCNOD_PROF(1, itp, ev);
+                        if (PROF && lane == 0) FCNOD_PROF(1, itp, ev);
                     }
                 };
                 auto b_release = [&]() {
-                    if (!resident) umma_commit(be + 8u * sb);
-                    if (PROF) { FCNOD_PROF(3, itp, ev); ++ev; }
+                    if (!resident && elect_one()) umma_commit(be + 8u * sb);
+                    if (PROF) { if (lane == 0) FCNOD_PROF(3, itp, ev); ++ev; }
                     b_lo += b_lo_step;
                     if (++sb == (uint32_t)p.b_stages) { sb = 0; pb ^= 1u; b_lo = b_lo_base; }
                 };
                 for (int ai = 0; ai < a_iters; ++ai) {
                     mbar_wait_hint(af + 8u * sa, pa);
+                    __syncwarp();
                     const int ks = (cc == p.n_cchunks - 1) ? p.ksteps_last : KSTEPS;   // skip all-zero K steps
                     if (++cc == p.n_cchunks) cc = 0;
                     if (!HALO) {
@@ -406,12 +421,12 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                             a_row += row_step;
                         }
                     }
-                    umma_commit(ae + 8u * sa);
+                    if (elect_one()) umma_commit(ae + 8u * sa);
                     a_lo += a_lo_step;
                     if (++sa == (uint32_t)p.a_stages) { sa = 0; pa ^= 1u; a_lo = a_lo_base; }
                 }
-                umma_commit(tfull0 + 8u * acc);
-                if (PROF) FCNOD_PROF(1, itp, 63);
+                if (elect_one()) umma_commit(tfull0 + 8u * acc);
+                if (PROF && lane == 0) FCNOD_PROF(1, itp, 63);
             }
         }
     } else {

@@ -33,7 +33,7 @@ for s in steps:
     print(plan[s][:200])
     t0 = int(out[out > 0].min())
     rel = lambda v: int(v) - t0 if v else -1
-    for tile in range(3):
+    for tile in range(8):
         n = 14
         print(' tile %d  B issue   %s' % (tile, [rel(v) for v in out[0, tile, :60] if v][:n]))
         print('         B landed  %s' % ([rel(v) for v in out[1, tile, :60] if v][:n]))
