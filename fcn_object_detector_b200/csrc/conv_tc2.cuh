@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         // DUAL: warp 1 feeds ring 0 (even tiles), warp 2 ring 1 (odd tiles), each with the A and B loads of its tiles in
         // the order the MMA thread consumes them.  Otherwise warp 1 feeds the A ring and warps 2, 3 the B ring (even / odd
         // rounds: one thread needs a few hundred cycles per wait + expect_tx + TMA round).
-        if (lane == 0) {
+        {   // all 32 lanes, converged (waits by every lane); one elected lane issues the copies
             const int pw = warp - 1;
             const bool doA = p.dual || pw == 0, doB = p.dual || pw >= 1;
             // single mode, B ring with >= 2 stages: the two B warps take alternate rounds (a one-stage ring is fed by one
@@ -254,8 +254,9 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             uint32_t b_idx = 0;
             const int ring = p.dual ? pw : 0;
             const int first = p.dual ? pw : 0, step = p.dual ? 2 : 1;
-            if (doA) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
-            if (doB) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+            if (doA && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
+            if (doB && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+            __syncwarp();
             const uint32_t b_tx = (uint32_t)p.BN * span * (uint32_t)p.b_taps;
             const uint32_t a_ring = a_base + (uint32_t)ring * a_ring_bytes;
             const uint32_t b_ring = b_base + (p.b_resident ? 0u : (uint32_t)ring * b_ring_bytes);
@@ -275,9 +276,11 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 const bool do_b = doB && !b_done;
                 auto load_a = [&](int cc, int r, int s) {
                     mbar_wait_hint(ae + 8u * sa, pha ^ 1u);
-                    mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
+                    __syncwarp();
                     const uint32_t dst = a_ring + sa * p.a_stage_bytes;
-                    if (HALO && p.a_bulk) {
+                    if (!elect_one()) {
+                    } else if (HALO && p.a_bulk) {
+                        mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
                         // one plain bulk copy per patch row: PW pixels x `span` bytes, contiguous in the image
                         const uint32_t rb = (uint32_t)p.PW * span;
                         const char* src = static_cast<const char*>(p.a_src) + (size_t)n_img * p.a_img_pitch +
@@ -286,16 +289,22 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                         for (int pr = 0; pr < rows; ++pr)
                             bulk_load(dst + (uint32_t)pr * rb, src + (size_t)pr * p.a_row_pitch, rb, af + 8u * sa);
                     } else {
+                        mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
                         tma_load_4d(dst, &tmap_a, af + 8u * sa, cc * p.CK, ow0 + s, oh0 + r, n_img);
                     }
+                    __syncwarp();
                     if (++sa == (uint32_t)p.a_stages) { sa = 0; pha ^= 1u; }
                 };
                 auto load_b = [&](int kb) {      // kb = first K-block of the round, in the packed (= global) order
                     if (!b_split || (b_idx & 1u) == b_par) {
                         mbar_wait_hint(be + 8u * sb, phb ^ 1u);
-                        if (PROF) FCNOD_PROF(0, tile_i, 0);
-                        mbar_expect_tx(bf + 8u * sb, b_tx);
-                        tma_load_3d(b_ring + sb * p.b_stage_bytes, &tmap_b, bf + 8u * sb, 0, n0, kb);
+                        __syncwarp();
+                        if (PROF && lane == 0) FCNOD_PROF(0, tile_i, 0);
+                        if (elect_one()) {
+                            mbar_expect_tx(bf + 8u * sb, b_tx);
+                            tma_load_3d(b_ring + sb * p.b_stage_bytes, &tmap_b, bf + 8u * sb, 0, n0, kb);
+                        }
+                        __syncwarp();
                     }
                     ++b_idx;
                     if (++sb == (uint32_t)p.b_stages) { sb = 0; phb ^= 1u; }
