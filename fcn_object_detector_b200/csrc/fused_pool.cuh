@@ -19,10 +19,17 @@
 namespace fcnod {
 
 // (k + a*s)^-beta.  FAST: beta == 0.75 via rsqrt/sqrt (2 MUFU), else exp2/log2; !FAST: powf (fp32 parity mode).
+__device__ __forceinline__ float rsqrt_ftz(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 template <bool FAST>
 __device__ __forceinline__ float lrn_scale(float sc, float beta) {
     if (FAST) {
-        if (beta == 0.75f) { const float r = rsqrtf(sc); return r * (r * rsqrtf(r)); }   // sc^-0.5 * (sc^-0.5)^0.5, 2 MUFU
+        // sc^-0.5 * (sc^-0.5)^0.5: 2 MUFU.  sc >= k = 1 and its rsqrt are never denormal, so the bare MUFU.RSQ
+        // (rsqrt.approx.ftz) returns what rsqrtf() does without rsqrtf's denormal pre/post-scaling instructions.
+        if (beta == 0.75f) { const float r = rsqrt_ftz(sc); return r * (r * rsqrt_ftz(r)); }
         return __powf(sc, -beta);
     }
     return powf(sc, -beta);
@@ -464,6 +471,125 @@ __global__ void __launch_bounds__(512) lrn_pool_kernel(const T* __restrict__ in,
                 m.max_with(x);
             }
         m.store(out + ((size_t)(n * Ho + oh) * Wo + ow) * ldo + cg * 8);
+    }
+}
+
+// ---- LRN(5) -> Pooling (3x3 stride 2), register marching --------------------------------------------------------
+// A warp = 8 output columns x 4 channel groups (lane = column * 4 + group; the 4 groups of a pixel are 64 contiguous
+// bytes), marching down RS output rows.  Every lane normalises the two input pixels (2*ow - p, 2*ow - p + 1) of its column
+// for each input row; the third pixel of the window is the first pixel of the next column and comes from lane + 4 by
+// shuffle, so the 8th column of a warp only feeds the 7th and a warp yields 7 output columns (1/8 of the LRN work is
+// redone by the neighbouring warp; no shared memory, no barriers, no divergent work).  The row maximum of the input row
+// shared with the next output row is carried in registers.  x^-0.75 costs 2 MUFU per element, which at 16 MUFU lanes per
+// clock and SM is this kernel's floor (about 80 us for conv2/norm2 at batch 64); everything else is trimmed to fit under it.
+template <int RS, bool FAST>
+__global__ void __launch_bounds__(256) lrn5_pool3s2_march_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int C, int H,
+                                                                 int W, int ldi, int Ho, int Wo, int ldo, int p, int colblocks,
+                                                                 float alpha_over_n, float kk) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int cl = lane >> 2, cgl = lane & 3;
+    const int CG = C >> 3;
+    const int task = blockIdx.x * 8 + wid;                 // (channel-group block, column block)
+    const int cb = task % colblocks, gb = task / colblocks;
+    if (gb * 4 >= CG) return;
+    const int cg = gb * 4 + cgl;
+    const int n = blockIdx.z;
+    const int oh0 = blockIdx.y * RS;
+    const int ow = cb * 7 + cl;
+    const int iw0 = 2 * ow - p;                            // this lane's two input columns: iw0, iw0 + 1
+    const bool va = iw0 >= 0 && iw0 < W, vb = iw0 + 1 >= 0 && iw0 + 1 < W;
+    const int ca = min(max(iw0, 0), W - 1), cbx = min(max(iw0 + 1, 0), W - 1);
+    const bool has_lo = cg > 0, has_hi = cg + 1 < CG;
+    const int c_lo = has_lo ? cg * 8 - 2 : 0, c_hi = has_hi ? cg * 8 + 8 : 0;
+    const bf16* img = in + (size_t)n * H * W * ldi;
+    constexpr uint32_t NEG = 0xff80ff80u;
+
+    // normalised 8 channels of one pixel, packed bf16x2 x 4 (all -inf when the pixel lies outside the image)
+    auto lrn_px = [&](const uint4 q, const uint32_t lo, const uint32_t hi, const bool valid, uint32_t* o) {
+        float x[12];
+        x[0] = has_lo ? __uint_as_float(lo << 16) : 0.f; x[1] = has_lo ? __uint_as_float(lo & 0xffff0000u) : 0.f;
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { x[2 + 2 * j] = __uint_as_float(w[j] << 16); x[3 + 2 * j] = __uint_as_float(w[j] & 0xffff0000u); }
+        x[10] = has_hi ? __uint_as_float(hi << 16) : 0.f; x[11] = has_hi ? __uint_as_float(hi & 0xffff0000u) : 0.f;
+        float sq[12];
+#pragma unroll
+        for (int j = 0; j < 12; ++j) sq[j] = x[j] * x[j];
+        float acc = sq[0] + sq[1] + sq[2] + sq[3];
+        float y[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            acc += sq[j + 4];
+            const float r = rsqrt_ftz(kk + alpha_over_n * acc);      // beta == 0.75 only (the host checks): v^-0.75 = r*r*sqrt(r)
+            y[j] = x[j + 2] * (r * (r * rsqrt_ftz(r)));
+            acc -= sq[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(y[2 * j], y[2 * j + 1]);
+            o[j] = valid ? *reinterpret_cast<const uint32_t*>(&h2) : NEG;
+        }
+    };
+    auto max4 = [](uint32_t* a, const uint32_t* b) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 m = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a[j]), *reinterpret_cast<const __nv_bfloat162*>(&b[j]));
+            a[j] = *reinterpret_cast<const uint32_t*>(&m);
+        }
+    };
+    // horizontal 3-max of input row ih for this lane's output column
+    struct Raw { uint4 qa, qb; uint32_t la, ha, lb, hb; };
+    // per-lane base pointers of the six loads of a row (own 8 channels and the two neighbour pairs of both pixels); a row
+    // then costs one 64-bit multiply and six pointer additions
+    const bf16* const pa0 = img + (size_t)ca * ldi + cg * 8;
+    const bf16* const pb0 = img + (size_t)cbx * ldi + cg * 8;
+    const int d_lo = c_lo - cg * 8, d_hi = c_hi - cg * 8;
+    const size_t pitch = (size_t)W * ldi;
+    auto load_row = [&](int ih, Raw& r) {
+        const size_t off = (size_t)min(max(ih, 0), H - 1) * pitch;
+        const bf16* pa = pa0 + off;
+        const bf16* pb = pb0 + off;
+        r.qa = __ldg(reinterpret_cast<const uint4*>(pa));
+        r.qb = __ldg(reinterpret_cast<const uint4*>(pb));
+        r.la = __ldg(reinterpret_cast<const uint32_t*>(pa + d_lo)); r.ha = __ldg(reinterpret_cast<const uint32_t*>(pa + d_hi));
+        r.lb = __ldg(reinterpret_cast<const uint32_t*>(pb + d_lo)); r.hb = __ldg(reinterpret_cast<const uint32_t*>(pb + d_hi));
+    };
+    auto row_max = [&](int ih, const Raw& r, uint32_t* m) {
+        const bool vr = ih >= 0 && ih < H;
+        uint32_t b[4], t[4];
+        lrn_px(r.qa, r.la, r.ha, vr && va, m);
+        lrn_px(r.qb, r.lb, r.hb, vr && vb, b);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = __shfl_down_sync(0xffffffffu, m[j], 4);     // first pixel of the next column
+        max4(m, b);
+        max4(m, t);
+    };
+
+    int ih = 2 * oh0 - p;
+    uint32_t carry[4];
+    {
+        Raw r0;
+        load_row(ih, r0);
+        row_max(ih, r0, carry);
+    }
+    const bool col_ok = cl < 7 && ow < Wo;
+#pragma unroll 1
+    for (int o = 0; o < RS; ++o) {
+        const int oh = oh0 + o;
+        if (oh >= Ho) break;
+        Raw r1, r2;
+        load_row(ih + 1, r1);
+        load_row(ih + 2, r2);
+        uint32_t m1[4], m2[4];
+        row_max(ih + 1, r1, m1);
+        row_max(ih + 2, r2, m2);
+        max4(carry, m1);
+        max4(carry, m2);
+        if (col_ok)
+            *reinterpret_cast<uint4*>(out + ((size_t)(n * Ho + oh) * Wo + ow) * ldo + cg * 8) = make_uint4(carry[0], carry[1], carry[2], carry[3]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) carry[j] = m2[j];
+        ih += 2;
     }
 }
 

@@ -1342,6 +1342,15 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
             const Blob& ib = net->blobs[st.in];
             const Blob& ob = net->blobs[st.out];
             FCNOD_CHECK(ib.dtype == DT_BF16 && ob.dtype == DT_BF16, "lrn+pool: bf16 only");
+            static const bool lp_v1 = getenv("FCNOD_LRNPOOL_V1") != nullptr;
+            if (!lp_v1 && ib.C % 32 == 0 && L->beta == 0.75f) {       // register-marching form: warps of 8 columns x 4 channel groups
+                constexpr int RS = 8;
+                const int colblocks = ceil_div(ob.W, 7), tasks = colblocks * (ib.C / 32);
+                lrn5_pool3s2_march_kernel<RS, true><<<dim3(ceil_div(tasks, 8), ceil_div(ob.H, RS), net->batch), 256, 0, s>>>(
+                    (const bf16*)view_ptr(net, ib), (bf16*)view_ptr(net, ob), ib.C, ib.H, ib.W, ib.ldc, ob.H, ob.W, ob.ldc, P.pad,
+                    colblocks, L->alpha / L->local_size, L->lrn_k);
+                break;
+            }
             constexpr int TH = 4, TW = 8;
             const int tx = ceil_div(ob.W, TW), ty = ceil_div(ob.H, TH);
             size_t smem = (size_t)(2 * (TH - 1) + 3) * (2 * (TW - 1) + 3) * ib.C * 2;
