@@ -1161,7 +1161,8 @@ void launch_pool(const fcnod_net* net, const Step& st, const LayerDef& L, cudaSt
     if (L.kernel == 3 && (L.stride == 1 || L.stride == 2) && L.pad <= 1 && ib.C % 8 == 0 && !getenv("FCNOD_POOL_V1")) {
         // register-marching kernel: CTA = 8 channel groups x 32 output columns x a strip of output rows
         const int cg_chunks = ceil_div(ib.C / 8, 8), col_chunks = ceil_div(ob.W, 32);
-        const int RS = ob.H <= 14 ? ob.H : 14, strips = ceil_div(ob.H, RS);
+        static const int rs_env = getenv("FCNOD_POOL_RS") ? atoi(getenv("FCNOD_POOL_RS")) : 0;
+        const int RS = rs_env > 0 ? std::min(rs_env, ob.H) : (ob.H <= 14 ? ob.H : 14), strips = ceil_div(ob.H, RS);
         const long blocks = (long)net->batch * strips * col_chunks * cg_chunks;
         if (L.stride == 1)
             pool3_march_kernel<T, 1><<<(unsigned)blocks, 256, 0, s>>>((const T*)view_ptr(net, ib), (T*)view_ptr(net, ob), ib.C, ib.H,
