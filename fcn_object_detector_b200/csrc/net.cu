@@ -190,6 +190,8 @@ struct fcnod_net {
         int ticket = -1;                 // -1 = free
     } slots[2];
     int next_ticket = 0, oldest_ticket = 0;
+    cudaGraphExec_t sgraph = 0;          // forward + post-net from data_dev / srchw_dev, replayed by every submit
+    fcnod_postnet_params sgraph_p;       // the thresholds baked into it
 };
 
 namespace fcnod {
@@ -991,6 +993,7 @@ void free_activations(fcnod_net* net) {
     if (net->img_dev) { cudaFree(net->img_dev); net->img_dev = 0; net->img_dev_bytes = 0; }
     if (net->pre_scratch) { cudaFree(net->pre_scratch); net->pre_scratch = 0; }
     if (net->graph) { cudaGraphExecDestroy(net->graph); net->graph = 0; }
+    if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
     if (net->pinned_in) { cudaFreeHost(net->pinned_in); net->pinned_in = 0; net->pinned_in_bytes = 0; }
     if (net->pinned_out) { cudaFreeHost(net->pinned_out); net->pinned_out = 0; }
 }
@@ -1868,6 +1871,25 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
     }
     if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)B * 6 * 4));
     ensure_detect_buffers(net);
+    // forward + post-net as one graph (built on first use, rebuilt when the batch or the thresholds change)
+    static const bool no_sgraph = getenv("FCNOD_NO_STREAM_GRAPH") != nullptr;
+    if (!no_sgraph && (!net->sgraph || memcmp(&net->sgraph_p, p, sizeof(*p)) != 0)) {
+        if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+        cudaGraph_t g = 0;
+        FCNOD_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        try {
+            detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+        } catch (...) {
+            cudaStreamEndCapture(s, &g);
+            if (g) cudaGraphDestroy(g);
+            throw;
+        }
+        FCNOD_CUDA(cudaStreamEndCapture(s, &g));
+        cudaError_t ge = cudaGraphInstantiate(&net->sgraph, g, 0);
+        cudaGraphDestroy(g);
+        FCNOD_CUDA(ge);
+        net->sgraph_p = *p;
+    }
     // upload on the copy stream: overlaps whatever the compute stream is still doing for the previous ticket.
     // The slot's previous reader (the prelude of ticket-2) finished before that ticket was collected.
     FCNOD_CUDA(cudaMemcpyAsync(sl.img, images, ibytes, cudaMemcpyHostToDevice, net->copy_stream));
@@ -1877,7 +1899,8 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
     FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
     preprocess_launch(sl.img, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
-    detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+    if (net->sgraph) FCNOD_CUDA(cudaGraphLaunch(net->sgraph, s));
+    else detect_device(net, net->data_dev, net->srchw_dev, *p, s);
     int32_t* p_det = sl.pinned + (size_t)B * 2;
     int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
     int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
