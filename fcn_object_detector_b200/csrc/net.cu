@@ -807,7 +807,9 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
                         if (a_st < 2) continue;
                     }
                     if (!resident && !dual && b_st >= 3) b_st &= ~1;     // two warps feed the B ring round-robin: even count
-                    // one M=128 K=16 instruction: max(93, 43 + N/2) cycles from one issuing thread, ~max(68, 22 + N/2) from two;
+                    // one M=128 K=16 instruction: max(93, 43 + N/2) cycles from one issuing thread, ~max(68, 22 + N/2) from two
+                    // (measured before the MMA warps issued converged through uniform registers, see conv_tc2.cuh; the issue
+                    // floor is lower now, the N/2 tensor term is not -- the ranking only orders candidates for the autotuner);
                     // the one issuing thread also spends ~300 cycles per barrier round (wait + commit)
                     const double mma = ksteps_tile * (dual ? std::max(68.0, 22.0 + BN / 2.0) : std::max(93.0, 43.0 + BN / 2.0));
                     const double brounds = resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b;
