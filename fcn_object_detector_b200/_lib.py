@@ -56,8 +56,15 @@ SIGNATURES = {
     'fcnod_net_output_device': (_I, [_P, _STR, C.POINTER(_P)]),
     'fcnod_net_run_step': (_I, [_P, _I, _I, _P]),
     'fcnod_net_profile_conv_step': (_I, [_P, _I, _P, _SZ]),
+    'fcnod_net_tc_candidates': (_I, [_P, _I]),
+    'fcnod_net_tc_pick': (_I, [_P, _I]),
+    'fcnod_net_set_tc_pick': (_I, [_P, _I, _I]),
+    'fcnod_net_step_outputs': (_I, [_P, _I, _P, _SZ]),
+    'fcnod_net_autotune_candidates': (_I, []),
+    'fcnod_net_blob_checksum': (_I, [_P, _STR, C.POINTER(C.c_ulonglong)]),
     'fcnod_postnet_default_params': (None, [C.POINTER(PostnetParams)]),
     'fcnod_postnet_scratch_bytes': (_SZ, [_I, _I]),
+    'fcnod_postnet_prepare': (_I, [C.POINTER(PostnetParams)]),
     'fcnod_postnet_device': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P, _P, _P]),
     'fcnod_postnet': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P]),
     'fcnod_preprocess': (_I, [_P, _I, _I, _I, _I, _I, _P]),

@@ -1,7 +1,6 @@
-// Persistent bf16 implicit-GEMM convolution on the 5th-generation tensor cores (sm_100a); second generation of
-// conv_tc.cuh (which stays as the simple one-tile-per-CTA form, selectable with FCNOD_CONV_V1=1).
+// Persistent bf16 implicit-GEMM convolution on the 5th-generation tensor cores (sm_100a).
 //
-// GEMM view  D[M = pixels][N = Cout] = A[M][K] * B[N][K]^T,  K = kh*kw*Cin_pad, as in conv_tc.cuh.  What changes:
+// GEMM view  D[M = pixels][N = Cout] = A[M][K] * B[N][K]^T,  K = kh*kw*Cin_pad (helpers in conv_tc.cuh):
 //
 //   * ONE CTA per SM looping over (pixel tile, N tile) pairs: TMEM allocation, barrier initialisation and
 //     tensor-map prefetch are paid once per launch instead of once per 112-pixel tile.
@@ -52,6 +51,8 @@ struct ConvTc2Params {
     int BW, BH, tiles_x, tiles_y;
     int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
     int halo;                // 1 = HALO mode
+    int flat;                // 1 = 1x1 convolution over the flattened pixel index (H = 1, W = batch * H * W: 128-pixel tiles
+                             //     that ignore image and row boundaries; host-side bookkeeping only)
     int m_tiles, n_tiles, BN;
     int mstride;                               // pixel tiles between two visits of one CTA = gridDim.x / n_tiles
     int step_tx, step_ty, step_img;            // mstride written in the mixed radix (img, ty, tx)
@@ -198,8 +199,8 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t span = (uint32_t)p.CK * 2u;
     // Shared memory: [A rings][B rings][bias staging][barriers].  In DUAL mode there are two of each ring: even pixel tiles
     // flow through ring 0 / accumulator 0 and are multiplied by MMA thread 0, odd ones through ring 1 / accumulator 1 by
-    // MMA thread 1.  One thread issues a tcgen05.mma about every 100 cycles whatever its size (tools/micro/mma_rate.cu);
-    // two threads double that, which is what the narrow-N layers need.  Resident weights are one region shared by both.
+    // MMA thread 1: narrow-N tiles are bound by the issuing thread's own instruction stream (barrier rounds, commits), and
+    // two issuing threads overlap them.  Resident weights are one region shared by both.
     const int nr = p.dual ? 2 : 1, nrb = p.b_resident ? 1 : nr;
     const uint32_t a_base = smem_base;
     const uint32_t a_ring_bytes = (uint32_t)p.a_stages * p.a_stage_bytes, b_ring_bytes = (uint32_t)p.b_stages * p.b_stage_bytes;

@@ -160,4 +160,25 @@ __global__ void export_nchw_kernel(const T* __restrict__ in, float* __restrict__
     }
 }
 
+// ---- position-sensitive 64-bit checksum of a blob view (test aid) ---------------------------------
+// sum over elements of (bit pattern + 1) * (2 * index + 1) mod 2^64, index = pixel * C + channel.  Two tilings of one
+// convolution accumulate every output in the same K order, so their blobs must agree bit for bit: the candidate sweep
+// of tests/test_plan_gpu.py compares checksums instead of copying gigabytes to the host.
+template <typename T> __device__ __forceinline__ unsigned long long elem_bits(T v);
+template <> __device__ __forceinline__ unsigned long long elem_bits<float>(float v) { return __float_as_uint(v); }
+template <> __device__ __forceinline__ unsigned long long elem_bits<bf16>(bf16 v) { return __bfloat16_as_ushort(v); }
+template <typename T>
+__global__ void checksum_kernel(const T* __restrict__ in, long npix, int C, int ld, unsigned long long* __restrict__ out) {
+    const long total = npix * C;
+    unsigned long long h = 0;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long pix = i / C;
+        const int c = (int)(i - pix * C);
+        h += (elem_bits<T>(in[pix * ld + c]) + 1ull) * (2ull * (unsigned long long)i + 1ull);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, h);
+}
+
 }  // namespace fcnod

@@ -13,6 +13,8 @@ void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg
                     const int32_t* src_hw, const fcnod_postnet_params& p, void* scratch, int32_t* out_det,
                     int32_t* out_label, int32_t* out_weight, int32_t* out_count, cudaStream_t stream);
 int postnet_num_launches();
+// per-device one-time set-up (kernel attribute, SimilarRects table for `eps`): call before capturing a graph
+void postnet_prepare(double eps);
 
 // preproc.cu
 void preprocess_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, float* data_dev,

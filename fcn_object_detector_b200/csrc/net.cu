@@ -153,6 +153,8 @@ using namespace fcnod;
 
 struct fcnod_net {
     int device = 0, precision = 0, batch = 0;
+    int capacity = 0;                      // frames the activation buffers were allocated for (>= batch)
+    std::map<int, std::vector<int> > tc_picks;   // batch -> tiling pick of every step (autotuned once per batch size)
     NetDef def;
     std::vector<Blob> blobs;
     std::map<std::string, int> blob_index;
@@ -716,12 +718,17 @@ void choose_tc_tiling(ConvWeights& cw) {
 }
 
 // Everything of ConvTc2Params that does not need device pointers: pixel box, N tiling, pipeline depth.
+// Pixel tilings of one launch: the spatial box (BW x BH pixels of one image, halo patches in HALO mode) and, for plain
+// 1x1 convolutions, the FLAT tiling: the pixel index runs over batch * H * W and a tile is any 128 consecutive pixels.
+// A 28x28 image holds 7 boxes of 28x4 = 112 pixels (448 tiles per 64 frames = 3.03 rounds over 148 SMs); flat, the same
+// 50,176 pixels are 392 full 128-row tiles (2.65 rounds, 3 instead of 4).
+struct TcGeo { int flat, H, W, BW, PW, BH, tiles_x, tiles_y, m_tiles; uint32_t a_tx, a_stage; };
+
 void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) {
     const ConvWeights& cw = net->convs[st.conv];
     const Blob& ob = net->blobs[st.out];
     ConvTc2Params& p = st.tc;
     memset(&p, 0, sizeof(p));
-    p.H = ob.H; p.W = ob.W;     // == input size for the stride-1 "same" convolutions; == s2d image size for s2d
     p.kh = p.kw = cw.k; p.pad_h = p.pad_w = cw.pad;
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
     p.halo = cw.halo ? 1 : 0;
@@ -735,29 +742,45 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     p.ksteps_last = p.CK / 16;
     if (!cw.s2d) p.ksteps_last = std::min(p.CK / 16, ceil_div(cw.Cin - (p.n_cchunks - 1) * p.CK, 16));
     const uint32_t span = p.CK * 2;
-    // pixel box: the fewest boxes per image row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
     const int halo_w = p.halo ? p.kw - 1 : 0, halo_h = p.halo ? p.kh - 1 : 0;
-    const int bw_max = 128 - halo_w;
-    p.BW = ceil_div(ob.W, ceil_div(ob.W, bw_max));
-    p.PW = p.BW + halo_w;
-    p.BH = std::max(1, std::min(ob.H, 128 / p.PW));
-    p.tiles_x = ceil_div(ob.W, p.BW);
-    p.tiles_y = ceil_div(ob.H, p.BH);
-    if (cw.s2d) {
-        const S2dGeom sg = s2d_geom(ob.H, ob.W, cw.ka);
-        p.BW = sg.BW; p.PW = sg.PW; p.BH = sg.BH; p.tiles_x = sg.tiles_x; p.tiles_y = sg.tiles_y;
+    std::vector<TcGeo> geos;
+    {   // spatial box: the fewest boxes per image row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
+        TcGeo g;
+        g.flat = 0; g.H = ob.H; g.W = ob.W;   // == input size for the stride-1 "same" convolutions; == s2d image size for s2d
+        const int bw_max = 128 - halo_w;
+        g.BW = ceil_div(ob.W, ceil_div(ob.W, bw_max));
+        g.PW = g.BW + halo_w;
+        g.BH = std::max(1, std::min(ob.H, 128 / g.PW));
+        g.tiles_x = ceil_div(ob.W, g.BW);
+        g.tiles_y = ceil_div(ob.H, g.BH);
+        if (cw.s2d) {
+            const S2dGeom sg = s2d_geom(ob.H, ob.W, cw.ka);
+            g.BW = sg.BW; g.PW = sg.PW; g.BH = sg.BH; g.tiles_x = sg.tiles_x; g.tiles_y = sg.tiles_y;
+        }
+        g.m_tiles = g.tiles_x * g.tiles_y * batch;
+        if (p.halo) {
+            g.a_tx = (uint32_t)(g.PW * (g.BH + halo_h)) * span;
+            const int rows = std::max(128 + halo_h * g.PW + halo_w, g.PW * (g.BH + halo_h));
+            g.a_stage = (uint32_t)align_up((size_t)rows * span, 1024);
+        } else {
+            g.a_tx = (uint32_t)(g.BW * g.BH) * span;
+            g.a_stage = 128 * span;
+        }
+        geos.push_back(g);
     }
-    p.m_tiles = p.tiles_x * p.tiles_y * batch;
+    static const bool flat_off = getenv("FCNOD_FLAT") && getenv("FCNOD_FLAT")[0] == '0';
+    const long npix = (long)batch * ob.H * ob.W;
+    if (!flat_off && !p.halo && !cw.s2d && cw.k == 1 && cw.pad == 0 && !(st.segs[0].flags & SEG_DIRECT) &&
+        npix < (1L << 30) && geos[0].BW * geos[0].BH < 128) {
+        TcGeo g;
+        g.flat = 1; g.H = 1; g.W = (int)npix;
+        g.BW = g.PW = 128; g.BH = 1;
+        g.tiles_x = ceil_div((int)npix, 128); g.tiles_y = 1; g.m_tiles = g.tiles_x;
+        g.a_tx = 128 * span; g.a_stage = 128 * span;
+        geos.push_back(g);
+    }
     const int taps = p.kh * p.kw;
     const int Kp = taps * p.n_cchunks * p.CK;
-    if (p.halo) {
-        p.a_tx_bytes = (uint32_t)(p.PW * (p.BH + halo_h)) * span;
-        const int rows = std::max(128 + halo_h * p.PW + halo_w, p.PW * (p.BH + halo_h));
-        p.a_stage_bytes = (uint32_t)align_up((size_t)rows * span, 1024);
-    } else {
-        p.a_tx_bytes = (uint32_t)(p.BW * p.BH) * span;
-        p.a_stage_bytes = 128 * span;
-    }
     // N tiling / pipeline shape: every candidate that fits in shared memory, ranked by a per-tile model
     //   tile time = max(MMA issue, smem bandwidth, L2->smem bytes, epilogue) + fixed;  total = rounds over the persistent CTAs
     // (constants measured with tools/micro/mma_rate.cu and the conv timelines).  `pick` selects the pick-th best; the
@@ -770,39 +793,41 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);   // real 16-wide K steps
     const size_t fixed = (size_t)kTcEpiWarps * 256 + 1024 + 1024;     // bias staging, barriers, alignment slack
     const size_t avail = kTcSmemBudget - fixed;
-    struct Cand { int nt, BN, a_st, b_st, bt, resident, dual; uint32_t b_stage; double cost; };
+    struct Cand { int geo, nt, BN, a_st, b_st, bt, resident, dual; uint32_t b_stage; double cost; };
     std::vector<Cand> cands;
-    for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
+    for (size_t gi = 0; gi < geos.size(); ++gi) {
+      const TcGeo& G = geos[gi];
+      for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > 256 || nt * BN - N8 >= BN) continue;
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
-        const int mslots = std::max(1, std::min(p.m_tiles, kNumSMs / nt));
-        const long rounds = ((long)p.m_tiles + mslots - 1) / mslots;
+        const int mslots = std::max(1, std::min(G.m_tiles, kNumSMs / nt));
+        const long rounds = ((long)G.m_tiles + mslots - 1) / mslots;
         for (int bt = (p.halo ? p.kw : 1); bt >= 1; bt = (bt > 1 ? 1 : 0)) {       // B stage = kw taps (HALO) or 1
             const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024) * bt;
             const int rounds_b = taps * p.n_cchunks / bt;                               // B stages consumed per tile
             for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident)
-                for (int dual = 0; dual <= ((BN <= dual_bn && p.m_tiles > 1) ? 1 : 0); ++dual) {
+                for (int dual = 0; dual <= ((BN <= dual_bn && G.m_tiles > 1) ? 1 : 0); ++dual) {
                     const int nr = dual ? 2 : 1;
                     int a_st = 0, b_st = 0;
                     if (resident) {
                         // the whole K extent of the N tile stays in shared memory (loaded once per CTA, shared by both rings)
                         const size_t bres = (size_t)rounds_b * b_stage;
                         const int a_min = p.halo ? 1 : 2;
-                        if (rounds_b > 24 || bres + (size_t)nr * a_min * p.a_stage_bytes > avail) continue;
+                        if (rounds_b > 24 || bres + (size_t)nr * a_min * G.a_stage > avail) continue;
                         b_st = rounds_b;
-                        a_st = (int)std::min<size_t>(p.halo ? (dual ? 3 : 4) : 8, (avail - bres) / ((size_t)nr * p.a_stage_bytes));
+                        a_st = (int)std::min<size_t>(p.halo ? (dual ? 3 : 4) : 8, (avail - bres) / ((size_t)nr * G.a_stage));
                         if (nr * a_st + b_st > 30) a_st = (30 - b_st) / nr;
                         if (a_st < a_min) continue;
                     } else if (p.halo) {
                         for (a_st = 2; a_st >= 1; --a_st) {
-                            if (avail < (size_t)nr * a_st * p.a_stage_bytes + (size_t)nr * 2 * b_stage) continue;
-                            b_st = (int)std::min<size_t>(bt > 1 ? 6 : 8, (avail - (size_t)nr * a_st * p.a_stage_bytes) / ((size_t)nr * b_stage));
+                            if (avail < (size_t)nr * a_st * G.a_stage + (size_t)nr * 2 * b_stage) continue;
+                            b_st = (int)std::min<size_t>(bt > 1 ? 6 : 8, (avail - (size_t)nr * a_st * G.a_stage) / ((size_t)nr * b_stage));
                             break;
                         }
                         if (a_st < 1) continue;
                     } else {
-                        const size_t pair = (size_t)p.a_stage_bytes + b_stage;
+                        const size_t pair = (size_t)G.a_stage + b_stage;
                         a_st = b_st = (int)std::min<size_t>(8, avail / (nr * pair));
                         if (a_st < 2) continue;
                     }
@@ -814,18 +839,19 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
                     const double mma = ksteps_tile * (dual ? std::max(68.0, 22.0 + BN / 2.0) : std::max(93.0, 43.0 + BN / 2.0));
                     const double brounds = resident ? (double)(p.halo ? p.n_cchunks : taps * p.n_cchunks) : (double)rounds_b;
                     const double issue = (brounds * 300.0 + ksteps_tile * 25.0) / (dual ? 2.0 : 1.0);
-                    const double a_bytes = p.halo ? (double)p.n_cchunks * p.a_tx_bytes : (double)taps * p.n_cchunks * p.a_tx_bytes;
+                    const double a_bytes = p.halo ? (double)p.n_cchunks * G.a_tx : (double)taps * p.n_cchunks * G.a_tx;
                     const double b_bytes = resident ? 0.0 : (double)BN * Kp * 2;
                     const double load = (a_bytes + b_bytes) / 32.0;                            // ~32 B/clk/SM seen from L2
                     const double smem = (ksteps_tile * (4096.0 + 32.0 * BN) + a_bytes + b_bytes) / 128.0;
                     const double epi = 300.0 + 10.0 * BN;
                     double tile = std::max(std::max(std::max(mma, smem), issue), std::max(load, epi)) + 400.0;
                     if (a_st < 2 && !dual) tile += 0.5 * a_bytes / 32.0;                       // no A prefetch across tiles
-                    Cand c = {nt, BN, a_st, b_st, bt, resident, dual, b_stage, 0.0};
+                    Cand c = {(int)gi, nt, BN, a_st, b_st, bt, resident, dual, b_stage, 0.0};
                     c.cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 32.0 : 0.0);
                     cands.push_back(c);
                 }
         }
+      }
     }
     FCNOD_CHECK(!cands.empty(), "no tensor-core tiling fits in shared memory for '" + st.desc + "'");
     std::stable_sort(cands.begin(), cands.end(), [](const Cand& x, const Cand& y) { return x.cost < y.cost; });
@@ -835,6 +861,10 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
         p.n_tiles = c.nt; p.BN = c.BN; p.a_stages = c.a_st; p.b_stages = c.b_st; p.b_taps = c.bt;
         p.b_stage_bytes = c.b_stage;
         p.b_resident = c.resident; p.dual = c.dual;
+        const TcGeo& G = geos[c.geo];
+        p.flat = G.flat; p.H = G.H; p.W = G.W; p.BW = G.BW; p.PW = G.PW; p.BH = G.BH;
+        p.tiles_x = G.tiles_x; p.tiles_y = G.tiles_y; p.m_tiles = G.m_tiles;
+        p.a_tx_bytes = G.a_tx; p.a_stage_bytes = G.a_stage;
     }
     uint32_t acc = 32;
     while ((int)acc < p.BN) acc <<= 1;
@@ -979,6 +1009,12 @@ void upload_weights(fcnod_net* net) {
 }
 
 // ------------------------------------------------------------------------------------ (re)allocation
+// captured graphs hold kernel parameters (tensor maps, tilings, batch): any change of those invalidates them
+void drop_graphs(fcnod_net* net) {
+    if (net->graph) { cudaGraphExecDestroy(net->graph); net->graph = 0; }
+    if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+}
+
 void free_activations(fcnod_net* net) {
     for (size_t i = 0; i < net->buffers.size(); ++i)
         if (net->buffers[i].ptr) { cudaFree(net->buffers[i].ptr); net->buffers[i].ptr = 0; }
@@ -994,8 +1030,7 @@ void free_activations(fcnod_net* net) {
     if (net->srchw_dev) { cudaFree(net->srchw_dev); net->srchw_dev = 0; }
     if (net->img_dev) { cudaFree(net->img_dev); net->img_dev = 0; net->img_dev_bytes = 0; }
     if (net->pre_scratch) { cudaFree(net->pre_scratch); net->pre_scratch = 0; }
-    if (net->graph) { cudaGraphExecDestroy(net->graph); net->graph = 0; }
-    if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+    drop_graphs(net);
     if (net->pinned_in) { cudaFreeHost(net->pinned_in); net->pinned_in = 0; net->pinned_in_bytes = 0; }
     if (net->pinned_out) { cudaFreeHost(net->pinned_out); net->pinned_out = 0; }
 }
@@ -1080,6 +1115,10 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         cuuint64_t dims[4] = {(cuuint64_t)ib.C, (cuuint64_t)ib.W, (cuuint64_t)ib.H, (cuuint64_t)B};
         cuuint64_t strides[3] = {(cuuint64_t)ib.ldc * 2, (cuuint64_t)ib.W * ib.ldc * 2, (cuuint64_t)ib.H * ib.W * ib.ldc * 2};
         cuuint32_t box[4] = {(cuuint32_t)cw.CK, (cuuint32_t)p.PW, (cuuint32_t)(p.halo ? p.BH + p.kh - 1 : p.BH), 1};
+        if (p.flat) {   // all pixels of the batch as one row: [C][B*H*W][1][1]
+            dims[1] = (cuuint64_t)B * ib.H * ib.W; dims[2] = 1; dims[3] = 1;
+            strides[1] = dims[1] * ib.ldc * 2; strides[2] = strides[1];
+        }
         CUresult r = encode_map(&st.tmap_a, view_ptr(net, ib), 4, dims, strides, box, span, CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
         FCNOD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(A) failed for '" + L.name + "' (" + std::to_string((int)r) + ")");
     }
@@ -1091,10 +1130,11 @@ void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof);
 
 // The tiling model ranks the candidates; the device has the last word: the first few are timed on the real buffers
 // (contents are irrelevant, every tiling computes the same sums in the same K order) and the fastest one is kept.
-// FCNOD_AUTOTUNE=0 keeps the model's first choice; FCNOD_AUTOTUNE=n times n candidates (default 10).
+// FCNOD_AUTOTUNE=0 keeps the model's first choice; FCNOD_AUTOTUNE=n times n candidates (default 12).
+const int kAutotuneDefault = 12;
 void autotune_tc_steps(fcnod_net* net) {
     const char* e = getenv("FCNOD_AUTOTUNE");
-    const int ntry = e ? atoi(e) : 10;
+    const int ntry = e ? atoi(e) : kAutotuneDefault;
     if (ntry <= 1) return;
     cudaEvent_t e0, e1;
     FCNOD_CUDA(cudaEventCreate(&e0));
@@ -1137,24 +1177,40 @@ void reshape(fcnod_net* net, int batch) {
     require_device(net);
     if (batch == net->batch && !net->buffers.empty() && net->buffers[0].ptr) return;
     FCNOD_CUDA(cudaDeviceSynchronize());
-    free_activations(net);
+    drop_graphs(net);
+    // Buffers are [batch][H][W][C] with the batch outermost: a smaller batch runs in a prefix of a larger allocation
+    // (the zero padding of the space-to-depth image sits at the same offsets), so alternating batch sizes -- the
+    // node's batch-1 run_detector next to batched calls -- neither reallocates nor re-times the tilings.
+    if (batch > net->capacity) {
+        free_activations(net);
+        net->capacity = batch;
+        for (size_t i = 0; i < net->buffers.size(); ++i) {
+            Buffer& b = net->buffers[i];
+            size_t bytes = (size_t)batch * b.C * b.H * b.W * dsize(b.dtype);
+            FCNOD_CUDA(cudaMalloc(&b.ptr, bytes));
+            FCNOD_CUDA(cudaMemset(b.ptr, 0, bytes));
+        }
+        net->out_dev.assign(net->outputs.size(), (float*)0);
+        for (size_t i = 0; i < net->outputs.size(); ++i) {
+            const Blob& b = net->blobs[net->outputs[i]];
+            FCNOD_CUDA(cudaMalloc(&net->out_dev[i], (size_t)batch * b.C * b.H * b.W * 4));
+        }
+        const Blob& in = net->blobs[0];
+        FCNOD_CUDA(cudaMalloc(&net->data_dev, (size_t)batch * in.C * in.H * in.W * 4));
+    }
     net->batch = batch;
-    for (size_t i = 0; i < net->buffers.size(); ++i) {
-        Buffer& b = net->buffers[i];
-        size_t bytes = (size_t)batch * b.C * b.H * b.W * dsize(b.dtype);
-        FCNOD_CUDA(cudaMalloc(&b.ptr, bytes));
-        FCNOD_CUDA(cudaMemset(b.ptr, 0, bytes));
-    }
-    net->out_dev.assign(net->outputs.size(), (float*)0);
-    for (size_t i = 0; i < net->outputs.size(); ++i) {
-        const Blob& b = net->blobs[net->outputs[i]];
-        FCNOD_CUDA(cudaMalloc(&net->out_dev[i], (size_t)batch * b.C * b.H * b.W * 4));
-    }
-    const Blob& in = net->blobs[0];
-    FCNOD_CUDA(cudaMalloc(&net->data_dev, (size_t)batch * in.C * in.H * in.W * 4));
+    std::map<int, std::vector<int> >::const_iterator pk = net->tc_picks.find(batch);
     for (size_t i = 0; i < net->steps.size(); ++i)
-        if (net->steps[i].kind == S_CONV_TC) { net->steps[i].tc_pick = -1; setup_tc_step(net, net->steps[i]); }
-    autotune_tc_steps(net);
+        if (net->steps[i].kind == S_CONV_TC) {
+            net->steps[i].tc_pick = pk != net->tc_picks.end() ? pk->second[i] : -1;
+            setup_tc_step(net, net->steps[i]);
+        }
+    if (pk == net->tc_picks.end()) {
+        autotune_tc_steps(net);
+        std::vector<int> picks(net->steps.size(), -1);
+        for (size_t i = 0; i < net->steps.size(); ++i) picks[i] = net->steps[i].tc_pick;
+        net->tc_picks[batch] = picks;
+    }
 }
 
 // ------------------------------------------------------------------------------------ execution
@@ -1414,7 +1470,7 @@ void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s) {
 }
 
 void ensure_detect_buffers(fcnod_net* net) {
-    const int B = net->batch;
+    const int B = net->capacity;
     const int c_cvg = net->blobs[blob_id(net, "coverage")].C;
     if (!net->post_scratch) FCNOD_CUDA(cudaMalloc(&net->post_scratch, postnet_scratch_bytes(B, c_cvg)));
     if (!net->det_dev) FCNOD_CUDA(cudaMalloc(&net->det_dev, (size_t)B * FCNOD_MAX_DET * 5 * 4));
@@ -1580,7 +1636,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         o << i << ": " << st.desc;
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
-            o << " [" << (st.tc.halo ? "halo " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
+            o << " [" << (st.tc.halo ? "halo " : "") << (st.tc.flat ? "flat " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
               << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " eg=" << st.tc.egroups << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
@@ -1659,7 +1715,81 @@ int fcnod_net_run_step(fcnod_net* net, int step, int reps, void* stream) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(net && step >= 0 && step < (int)net->steps.size(), "bad step index");
     require_device(net);
-    for (int i = 0; i < reps; ++i) run_step(net, net->steps[step], net->data_dev, (cudaStream_t)stream);
+    cudaStream_t s = stream ? (cudaStream_t)stream : net->stream;      // NULL = the net's own stream
+    for (int i = 0; i < reps; ++i) run_step(net, net->steps[step], net->data_dev, s);
+    FCNOD_API_END
+}
+
+int fcnod_net_tc_candidates(const fcnod_net* net, int step) {
+    if (!net || step < 0 || step >= (int)net->steps.size() || net->steps[step].kind != S_CONV_TC) return 0;
+    return net->steps[step].tc_ncand;
+}
+
+int fcnod_net_tc_pick(const fcnod_net* net, int step) {
+    if (!net || step < 0 || step >= (int)net->steps.size() || net->steps[step].kind != S_CONV_TC) return -1;
+    return net->steps[step].tc_pick < 0 ? 0 : net->steps[step].tc_pick;
+}
+
+int fcnod_net_set_tc_pick(fcnod_net* net, int step, int pick) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && step >= 0 && step < (int)net->steps.size(), "bad step index");
+    Step& st = net->steps[step];
+    FCNOD_CHECK(st.kind == S_CONV_TC, "step is not a tensor-core convolution");
+    FCNOD_CHECK(pick >= 0 && pick < st.tc_ncand, "tiling candidate out of range");
+    require_device(net);
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    drop_graphs(net);
+    st.tc_pick = pick;
+    setup_tc_step(net, st);
+    std::map<int, std::vector<int> >::iterator pk = net->tc_picks.find(net->batch);
+    if (pk != net->tc_picks.end()) pk->second[step] = pick;
+    FCNOD_API_END
+}
+
+int fcnod_net_autotune_candidates(void) {
+    const char* e = getenv("FCNOD_AUTOTUNE");
+    return e ? atoi(e) : kAutotuneDefault;
+}
+
+int fcnod_net_step_outputs(const fcnod_net* net, int step, char* buf, size_t buflen) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && buf && buflen > 0 && step >= 0 && step < (int)net->steps.size(), "bad argument");
+    const Step& st = net->steps[step];
+    std::string o;
+    if (st.kind == S_CONV_TC) {
+        for (size_t i = 0; i < st.segs.size(); ++i) {
+            const int bi = (st.segs[i].flags & SEG_DIRECT) ? st.segs[i].direct_blob : st.segs[i].blob;
+            o += (i ? "," : "") + net->blobs[bi].name;
+        }
+    } else if (st.out >= 0) {
+        o = net->blobs[st.out].name;
+    }
+    FCNOD_CHECK(o.size() + 1 <= buflen, "buffer too small");
+    memcpy(buf, o.c_str(), o.size() + 1);
+    FCNOD_API_END
+}
+
+int fcnod_net_blob_checksum(fcnod_net* net, const char* blob, unsigned long long* out) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && blob && out, "null argument");
+    require_device(net);
+    const Blob& b = net->blobs[blob_id(net, blob)];
+    FCNOD_CHECK(b.buf != -2, std::string("blob '") + blob + "' is fused away in this plan");
+    FCNOD_CHECK(b.buf >= 0 || b.is_output, "the input blob has no checksum");
+    unsigned long long* d = 0;
+    FCNOD_CUDA(cudaMalloc(&d, 8));
+    cudaError_t e = cudaMemsetAsync(d, 0, 8, net->stream);
+    const long npix = (long)net->batch * b.H * b.W;
+    if (e == cudaSuccess) {
+        if (b.is_output) checksum_kernel<float><<<kNumSMs * 4, 256, 0, net->stream>>>(net->out_dev[b.out_index], npix * b.C, 1, 1, d);
+        else if (b.dtype == DT_F32) checksum_kernel<float><<<kNumSMs * 4, 256, 0, net->stream>>>((const float*)view_ptr(net, b), npix, b.C, b.ldc, d);
+        else checksum_kernel<bf16><<<kNumSMs * 4, 256, 0, net->stream>>>((const bf16*)view_ptr(net, b), npix, b.C, b.ldc, d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(net->stream);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d, 8, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    FCNOD_CUDA(e);
     FCNOD_API_END
 }
 
@@ -1773,7 +1903,7 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
             FCNOD_CUDA(cudaMalloc(&net->img_dev, ibytes));
             net->img_dev_bytes = ibytes;
         }
-        if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)Bc * 6 * 4));
+        if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)net->capacity * 6 * 4));
         ensure_detect_buffers(net);
         const size_t per = (size_t)FCNOD_MAX_DET * 7 + 1, obytes = (size_t)B * per * 4;
         if (net->pinned_big_bytes < obytes) {
@@ -1819,7 +1949,7 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
         FCNOD_CUDA(cudaMalloc(&net->img_dev, ibytes));
         net->img_dev_bytes = ibytes;
     }
-    if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)B * 6 * 4));
+    if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)net->capacity * 6 * 4));
     ensure_detect_buffers(net);
     std::vector<int32_t> hw((size_t)B * 2);
     for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
@@ -1871,12 +2001,13 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
         FCNOD_CUDA(cudaMallocHost(&sl.pinned, obytes));
         sl.pinned_bytes = obytes;
     }
-    if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)B * 6 * 4));
+    if (!net->pre_scratch) FCNOD_CUDA(cudaMalloc(&net->pre_scratch, (size_t)net->capacity * 6 * 4));
     ensure_detect_buffers(net);
     // forward + post-net as one graph (built on first use, rebuilt when the batch or the thresholds change)
     static const bool no_sgraph = getenv("FCNOD_NO_STREAM_GRAPH") != nullptr;
     if (!no_sgraph && (!net->sgraph || memcmp(&net->sgraph_p, p, sizeof(*p)) != 0)) {
         if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+        postnet_prepare(p->eps);          // per-device one-time set-up happens outside the capture (submit may be the first call)
         cudaGraph_t g = 0;
         FCNOD_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
         try {

@@ -20,6 +20,10 @@
 // Kernel 2 (assemble_kernel): one warp per frame concatenates the per-class lists in
 //   class order and rescales.
 #include <cmath>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <vector>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -301,7 +305,8 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
         }
         nout += tot;
     }
-    if (threadIdx.x == 0) cls_cnt[b * ncls + cls] = min(nout, FCNOD_MAX_DET);
+    // the untruncated number of kept clusters: more than FCNOD_MAX_DET means the list was cut (the reference has no cap)
+    if (threadIdx.x == 0) cls_cnt[b * ncls + cls] = nout;
 }
 
 __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32_t* __restrict__ cls_cnt, int B, int ncls,
@@ -316,9 +321,9 @@ __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32
         diffx = (double)src_hw[2 * b + 1] / (double)net_w;
         diffy = (double)src_hw[2 * b] / (double)net_h;
     }
-    int total = 0;
+    int total = 0, total_all = 0;
     for (int c = 0; c < ncls; ++c) {
-        const int k = cls_cnt[b * ncls + c];
+        const int k_all = cls_cnt[b * ncls + c], k = min(k_all, FCNOD_MAX_DET);
         const int32_t* src = cls_det + ((size_t)b * ncls + c) * FCNOD_MAX_DET * 6;
         for (int i = lane; i < k; i += 32) {
             const int d = total + i;
@@ -333,8 +338,10 @@ __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32
             out_weight[b * FCNOD_MAX_DET + d] = src[i * 6 + 5];
         }
         total += k;
+        total_all += k_all;
     }
-    if (lane == 0) out_count[b] = min(total, FCNOD_MAX_DET);
+    // out_count = every cluster the reference would have returned; only the first FCNOD_MAX_DET of them are stored
+    if (lane == 0) out_count[b] = total_all;
 }
 
 }  // namespace
@@ -342,7 +349,52 @@ __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32
 size_t postnet_scratch_bytes(int B, int c_cvg) {
     return (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1) * sizeof(int32_t) + kDeltaTable * sizeof(int32_t);
 }
-int postnet_num_launches() { return 3; }
+int postnet_num_launches() { return 2; }
+
+namespace {
+// Per device: the kernel's dynamic shared-memory limit (set once) and the SimilarRects threshold tables T(m), one per
+// eps value seen, built on the host with the very double expression of delta_table_kernel (IEEE multiply + floor: same
+// bits) and kept for the life of the process -- a replayed CUDA graph does not rebuild it every step.
+struct PostDevState {
+    bool attr_set = false;
+    std::map<unsigned long long, int*> tables;     // bit pattern of eps -> device table
+};
+std::mutex g_post_mutex;
+PostDevState g_post_state[64];
+
+// The table for `eps` on the current device, or nullptr when it is not cached and cannot be built right now (the
+// calling thread is capturing a graph: the caller then builds it in-stream into its scratch area).
+const int* postnet_prepare_locked(double eps, cudaStream_t stream) {
+    int dev = 0;
+    FCNOD_CUDA(cudaGetDevice(&dev));
+    FCNOD_CHECK(dev >= 0 && dev < 64, "postnet: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_post_mutex);
+    PostDevState& st = g_post_state[dev];
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (stream) FCNOD_CUDA(cudaStreamIsCapturing(stream, &cap));
+    if (!st.attr_set) {
+        FCNOD_CHECK(cap == cudaStreamCaptureStatusNone, "postnet: first use on this device inside a graph capture; call "
+                    "fcnod_postnet_prepare (or any post-net entry point) once before capturing");
+        FCNOD_CUDA(cudaFuncSetAttribute(decode_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        st.attr_set = true;
+    }
+    unsigned long long key;
+    memcpy(&key, &eps, 8);
+    std::map<unsigned long long, int*>::iterator it = st.tables.find(key);
+    if (it != st.tables.end()) return it->second;
+    if (cap != cudaStreamCaptureStatusNone) return nullptr;
+    std::vector<int> host(kDeltaTable);
+    for (int m = 0; m < kDeltaTable; ++m) host[m] = (int)floor(eps * (double)m * 0.5);
+    int* d = 0;
+    FCNOD_CUDA(cudaMalloc(&d, kDeltaTable * sizeof(int)));
+    cudaError_t e = cudaMemcpy(d, host.data(), kDeltaTable * sizeof(int), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(d); FCNOD_CUDA(e); }
+    st.tables[key] = d;
+    return d;
+}
+}  // namespace
+
+void postnet_prepare(double eps) { postnet_prepare_locked(eps, 0); }
 
 void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                     const int32_t* src_hw, const fcnod_postnet_params& p, void* scratch, int32_t* out_det,
@@ -366,17 +418,14 @@ void postnet_launch(const float* coverage, const float* bboxes, int B, int c_cvg
     P.net_w = p.net_w; P.net_h = p.net_h;
     int32_t* cls_det = static_cast<int32_t*>(scratch);
     int32_t* cls_cnt = cls_det + (size_t)B * ncls * FCNOD_MAX_DET * 6;
-    int* delta_tab = static_cast<int*>(scratch) + (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1);
-    delta_table_kernel<<<kDeltaTable / 256, 256, 0, stream>>>(p.eps, delta_tab);
-    FCNOD_CUDA(cudaGetLastError());
-    const size_t adj_bytes = (size_t)8 * gh * gw * sizeof(unsigned);
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    FCNOD_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {     // first call on a device happens outside any graph capture
-        FCNOD_CUDA(cudaFuncSetAttribute(decode_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-        attr_set[dev] = true;
+    const int* delta_tab = postnet_prepare_locked(p.eps, stream);
+    if (!delta_tab) {   // new eps while capturing: the table is built in-stream (and becomes part of the graph)
+        int* tab = static_cast<int*>(scratch) + (size_t)B * c_cvg * (FCNOD_MAX_DET * 6 + 1);
+        delta_table_kernel<<<kDeltaTable / 256, 256, 0, stream>>>(p.eps, tab);
+        FCNOD_CUDA(cudaGetLastError());
+        delta_tab = tab;
     }
+    const size_t adj_bytes = (size_t)8 * gh * gw * sizeof(unsigned);
     decode_group_kernel<<<dim3(ncls, B), kThreads, adj_bytes, stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, delta_tab, cls_det, cls_cnt);
     FCNOD_CUDA(cudaGetLastError());
     assemble_kernel<<<ceil_div(B, 4), 128, 0, stream>>>(cls_det, cls_cnt, B, ncls, src_hw, p.net_w, p.net_h, out_det,
@@ -397,6 +446,13 @@ void fcnod_postnet_default_params(fcnod_postnet_params* p) {
 }
 
 size_t fcnod_postnet_scratch_bytes(int B, int c_cvg) { return postnet_scratch_bytes(B, c_cvg); }
+
+int fcnod_postnet_prepare(const fcnod_postnet_params* p) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(p, "null argument");
+    postnet_prepare(p->eps);
+    FCNOD_API_END
+}
 
 int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                          const int32_t* src_hw, const fcnod_postnet_params* p, void* scratch, int32_t* out_det,

@@ -19,6 +19,24 @@ from . import caffe_shim as caffe
 log = logging.getLogger('fcn_object_detector')
 
 
+def _unpack(det, lab, wgt, cnt, weights=False, overflow=None):
+    """Per-frame arrays out of the fixed-size C-ABI buffers.  `cnt[b]` is the number of detections the reference would
+    return; the library stores the first FCNOD_MAX_DET of them.  A frame with more is reported, never silently cut:
+    a warning is logged and (frame index, total) is appended to `overflow`."""
+    M = _lib.FCNOD_MAX_DET
+    out = []
+    for b in range(len(cnt)):
+        total = int(cnt[b])
+        n = min(total, M)
+        if total > M:
+            log.warning('frame %d: %d detections, only the first %d are returned (FCNOD_MAX_DET)', b, total, M)
+            if overflow is not None:
+                overflow.append((b, total))
+        row = (det[b, :n].astype(np.int64), lab[b, :n].astype(np.int64))
+        out.append(row + (wgt[b, :n].astype(np.int64),) if weights else row)
+    return out
+
+
 class FCNObjectDetector(object):
     def __init__(self, pretrained_weights=None, deployment_prototxt=None, detection_threshold=0.5, min_boxes=3,
                  nms_eps=0.2, device_id=0, manifest=None, stride=16, precision='bf16'):
@@ -33,6 +51,7 @@ class FCNObjectDetector(object):
         self.__device_id = device_id
         self.__stride = stride            # upstream literal is 16/2 (:360); the deploy net is stride 16 (A2)
         self.__precision = precision
+        self.overflow = []                # (frame index, untruncated count) of the last call's frames that exceeded FCNOD_MAX_DET
         if self.is_file_valid():
             self.load_caffe_model()
             log.info('DETECTOR SETUP SUCCESSFUL')
@@ -91,7 +110,8 @@ class FCNObjectDetector(object):
         _lib.check(_lib.lib().fcnod_detect(self.__net.handle, _lib.ptr(images), B, H, W, C.byref(p), _lib.ptr(det),
                                            _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
         self.__net._sync_after_device_run(B)
-        return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64)) for b in range(B)]
+        self.overflow = []
+        return _unpack(det, lab, wgt, cnt, overflow=self.overflow)
 
     def predict_stream(self, batches):
         """Generator over an iterable of (B,H,W,3) uint8 BGR batches (the node's image stream, :134-147, batched).
@@ -111,7 +131,8 @@ class FCNObjectDetector(object):
             cnt = np.empty((B,), np.int32)
             _lib.check(L.fcnod_detect_collect(self.__net.handle, ticket, _lib.ptr(det), _lib.ptr(lab), _lib.ptr(wgt),
                                               _lib.ptr(cnt)))
-            return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64)) for b in range(B)]
+            self.overflow = []
+            return _unpack(det, lab, wgt, cnt, overflow=self.overflow)
 
         try:
             for images in batches:
@@ -152,8 +173,8 @@ class FCNObjectDetector(object):
         _lib.check(_lib.lib().fcnod_detect_from_data(self.__net.handle, _lib.ptr(data), B, C.byref(p), _lib.ptr(det),
                                                      _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
         self.__net._sync_after_device_run(B)
-        return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64), wgt[b, :cnt[b]].astype(np.int64))
-                for b in range(B)]
+        self.overflow = []
+        return _unpack(det, lab, wgt, cnt, weights=True, overflow=self.overflow)
 
     def callback(self, cv_img):
         return self.run_detector(cv_img)
@@ -181,9 +202,10 @@ class FCNObjectDetector(object):
             self.labels.append(str(oname))
 
 
-def postnet(coverage, bboxes, src_hw=None, **params):
+def postnet(coverage, bboxes, src_hw=None, overflow=None, **params):
     """Post-net stage alone on host arrays: coverage (B,Cc,G,G), bboxes (B,Cb,G,G) float32.
-    Returns per-frame (boxes (K,5) int, labels (K,), weights (K,))."""
+    Returns per-frame (boxes (K,5) int, labels (K,), weights (K,)).  Frames with more than FCNOD_MAX_DET detections
+    are cut to the first FCNOD_MAX_DET, logged, and appended to `overflow` (a list) as (frame, total)."""
     coverage = np.ascontiguousarray(coverage, dtype=np.float32)
     bboxes = np.ascontiguousarray(bboxes, dtype=np.float32)
     B, Cc, gh, gw = coverage.shape
@@ -195,8 +217,7 @@ def postnet(coverage, bboxes, src_hw=None, **params):
     p = _lib.default_postnet_params(**params)
     _lib.check(_lib.lib().fcnod_postnet(_lib.ptr(coverage), _lib.ptr(bboxes), B, Cc, Cb, gh, gw, _lib.ptr(hw), C.byref(p),
                                         _lib.ptr(det), _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
-    return [(det[b, :cnt[b]].astype(np.int64), lab[b, :cnt[b]].astype(np.int64), wgt[b, :cnt[b]].astype(np.int64))
-            for b in range(B)]
+    return _unpack(det, lab, wgt, cnt, weights=True, overflow=overflow)
 
 
 def preprocess(images, net_h=448, net_w=448):

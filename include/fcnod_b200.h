@@ -39,7 +39,7 @@ extern "C" {
 #define FCNOD_PRECISION_FP32 0 /* SIMT fp32 everywhere (parity mode, 1e-5) */
 #define FCNOD_PRECISION_BF16 1 /* bf16 activations/weights, fp32 accumulate, tcgen05 convolutions */
 
-#define FCNOD_MAX_DET 64 /* detections kept per frame */
+#define FCNOD_MAX_DET 64 /* detections STORED per frame; out_count reports how many there were (see fcnod_postnet_device) */
 
 typedef struct fcnod_net fcnod_net;
 
@@ -70,8 +70,23 @@ int fcnod_net_forward_device(fcnod_net* net, const float* data_dev, void* stream
 int fcnod_net_blob_read(fcnod_net* net, const char* blob, float* host_out, size_t count);
 /* Device address of an OUTPUT blob (NCHW float32), valid until reshape/destroy. */
 int fcnod_net_output_device(fcnod_net* net, const char* blob, const float** dev_ptr);
-/* Run only the n-th planned launch `reps` times (profiling aid). */
+/* Run only the n-th planned launch `reps` times (profiling aid); stream NULL = the net's own stream. */
 int fcnod_net_run_step(fcnod_net* net, int step, int reps, void* stream);
+/* Tensor-core tiling of a planned convolution launch.  The planner enumerates the legal tilings of every launch
+ * (fcnod_net_tc_candidates: how many; 0 = not a tensor-core step), ranks them with a cost model, and on the first
+ * reshape to a batch size times the best-ranked ones on the device and keeps the fastest; the picks are cached per
+ * batch size, so a handle always runs the same plan for the same batch (fcnod_net_describe prints `pick=i/n`).
+ * fcnod_net_set_tc_pick forces candidate `pick` for the current batch (parity tests sweep every candidate the
+ * autotuner may choose); every candidate accumulates in the same K order, i.e. all of them produce the same bits. */
+int fcnod_net_tc_candidates(const fcnod_net* net, int step);
+int fcnod_net_tc_pick(const fcnod_net* net, int step);
+int fcnod_net_set_tc_pick(fcnod_net* net, int step, int pick);
+/* Comma-separated names of the blobs planned launch `step` writes (a fused launch writes several). */
+int fcnod_net_step_outputs(const fcnod_net* net, int step, char* buf, size_t buflen);
+/* How many tiling candidates the autotuner times per launch (FCNOD_AUTOTUNE, default 12; <= 1: none). */
+int fcnod_net_autotune_candidates(void);
+/* Position-sensitive 64-bit checksum of a materialised blob, computed on the device (test aid). */
+int fcnod_net_blob_checksum(fcnod_net* net, const char* blob, unsigned long long* out);
 /* Profiling aid: run a tensor-core convolution step once and return the clock64 timeline of its CTA 0:
  * out[4 roles (TMA producer: B-load issue; MMA issuer: B-load landed; first epilogue warp; MMA issuer: tap issued)]
  * [8 tiles][64 events] (count must be 2048). */
@@ -94,8 +109,14 @@ void fcnod_postnet_default_params(fcnod_postnet_params* p);
  * src_hw [B][2] int32 = source image (height,width) per frame, or NULL for net size.
  * out_det [B][FCNOD_MAX_DET][5] int32 = x1,y1,x2,y2,int(log(weight)) in source pixels,
  * out_label [B][FCNOD_MAX_DET] int32, out_weight [B][FCNOD_MAX_DET] int32 (cluster size),
- * out_count [B] int32.  scratch: fcnod_postnet_scratch_bytes(B, c_cvg) bytes of device memory. */
+ * out_count [B] int32 = the number of detections the reference would return for the frame (it has no cap,
+ * scripts/fcn_object_detector.py:104-124).  Only the first FCNOD_MAX_DET of them (class order, then cluster order;
+ * at most FCNOD_MAX_DET per class) are stored: out_count[b] > FCNOD_MAX_DET reports the truncation, and the caller
+ * reads min(out_count[b], FCNOD_MAX_DET) rows.  scratch: fcnod_postnet_scratch_bytes(B, c_cvg) bytes of device memory.
+ * The first post-net call on a device (or fcnod_postnet_prepare) must happen outside CUDA-graph capture. */
 size_t fcnod_postnet_scratch_bytes(int B, int c_cvg);
+/* One-time per-device set-up for these thresholds (kernel attribute, SimilarRects table of p->eps); optional. */
+int fcnod_postnet_prepare(const fcnod_postnet_params* p);
 int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                          const int32_t* src_hw, const fcnod_postnet_params* p, void* scratch,
                          int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count,

@@ -140,3 +140,45 @@ def test_run_detector_firing_heads_matches_oracle(firing_model_files):
     assert rel_err(cov, exp['coverage'][0]) < 1e-5 and rel_err(bb, exp['bboxes'][0]) < 1e-5
     eb, el = postnet_ref.postnet(exp['coverage'][0], exp['bboxes'][0], img.shape, prob_thresh=0.45)
     assert len(eb) == len(ob)
+
+
+def test_predict_stream_first_call_in_fresh_process(firing_model_files):
+    """fcnod_detect_submit captures forward + post-net into a graph on first use: it must work when it is the very
+    first post-net call of the process (per-device post-net set-up happens before the capture starts)."""
+    import os
+    import subprocess
+    import sys
+    from tests.util import ROOT
+    proto, cm = firing_model_files
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "from fcn_object_detector_b200.detector import FCNObjectDetector\n"
+        "det = FCNObjectDetector(pretrained_weights=%r, deployment_prototxt=%r, precision='bf16', detection_threshold=0.45, min_boxes=1)\n"
+        "rs = np.random.RandomState(11)\n"
+        "batches = [rs.randint(0, 256, (2, 448, 448, 3)).astype(np.uint8) for _ in range(3)]\n"
+        "got = list(det.predict_stream(iter(batches)))\n"
+        "want = [det.predict_batch(b) for b in batches]\n"
+        "assert all(np.array_equal(g[0], w[0]) for gg, ww in zip(got, want) for g, w in zip(gg, ww))\n"
+        "print('stream-first ok', sum(len(g[0]) for gg in got for g in gg))\n" % (ROOT, cm, proto))
+    r = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, FCNOD_AUTOTUNE='0'))
+    assert r.returncode == 0 and 'stream-first ok' in r.stdout, (r.stdout[-2000:], r.stderr[-2000:])
+
+
+def test_alternating_batch_sizes_keep_their_plans(model_files):
+    """run_detector (batch 1) next to batched calls: the buffers are kept and each batch size keeps the tiling picks
+    it was first given (no re-autotune, same results)."""
+    from fcn_object_detector_b200.detector import FCNObjectDetector
+    proto, cm = model_files
+    rs = np.random.RandomState(21)
+    one = rs.randint(0, 256, (1, 448, 448, 3)).astype(np.uint8)
+    four = rs.randint(0, 256, (4, 448, 448, 3)).astype(np.uint8)
+    det = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='bf16', detection_threshold=0.3, min_boxes=1)
+    r4 = det.predict_batch(four); plan4 = det.net.describe(); cov4 = det.net.blobs['coverage'].data.copy()
+    r1 = det.predict_batch(one); plan1 = det.net.describe(); cov1 = det.net.blobs['coverage'].data.copy()
+    for _ in range(2):
+        det.predict_batch(four)
+        assert det.net.describe() == plan4 and np.array_equal(det.net.blobs['coverage'].data, cov4)
+        det.predict_batch(one)
+        assert det.net.describe() == plan1 and np.array_equal(det.net.blobs['coverage'].data, cov1)

@@ -101,3 +101,31 @@ def test_large_batch_property():
     for b in range(8, 256):
         assert np.array_equal(got[b][0], got[b % 8][0]) and np.array_equal(got[b][1], got[b % 8][1])
     compare(cov[:8], bb[:8])
+
+
+def test_overflow_is_reported_not_silent():
+    """The reference keeps every cluster (fcn_object_detector.py:104-124); the C ABI stores FCNOD_MAX_DET per frame.
+    More than that must come back as out_count > FCNOD_MAX_DET with the first FCNOD_MAX_DET rows intact."""
+    from fcn_object_detector_b200 import _lib
+    M = _lib.FCNOD_MAX_DET
+    rs = np.random.RandomState(11)
+    cov = np.zeros((3, 4, 28, 28), np.float32)
+    bb = np.zeros((3, 16, 28, 28), np.float32)
+    bb[:, 2::4] = 30.0; bb[:, 3::4] = 30.0                     # 30 x 30 boxes: pass the height filter
+    bb += rs.uniform(-1, 1, bb.shape).astype(np.float32)
+    cov[0, 1, ::2, ::2] = 0.9                                   # frame 0: 196 isolated candidates in class 0 alone
+    cov[1, 1, :6, ::2] = 0.9; cov[1, 2, :4, ::2] = 0.9          # frame 1: 84 + 56 over two classes (class 0 alone overflows)
+    cov[2, 3, 0, :10] = 0.9                                     # frame 2: 10, no overflow
+    kw = dict(min_boxes=0, prob_thresh=0.5)
+    overflow = []
+    got = run_gpu(cov, bb, overflow=overflow, **kw)
+    totals = {}
+    for b in range(3):
+        ob, ol = oracle(cov[b], bb[b], (448, 448, 3), prob_thresh=0.5, min_boxes=0, eps=0.2, stride=16, skip_background=True)
+        totals[b] = len(ol)
+        k = min(len(ol), M)
+        assert len(got[b][0]) == k
+        # (frame 1: the per-class lists are capped at M too, so the stored rows are class 0's first M)
+        assert np.array_equal(got[b][0], ob[:k]) and np.array_equal(got[b][1], ol[:k])
+    assert totals[0] == 196 and totals[1] == 140 and totals[2] == 10
+    assert overflow == [(0, 196), (1, 140)], overflow
