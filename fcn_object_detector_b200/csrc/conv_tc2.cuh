@@ -21,6 +21,12 @@
 //   * Horizontal fusion: N may be the concatenation of several convolutions reading the same input (the 1x1 /
 //     3x3_reduce / 5x5_reduce branches of an inception module, deploy.prototxt:163-377): up to four output SEGMENTS
 //     with their own destination views; boundaries are multiples of 8 channels.
+//   * POOL mode (the `pool -> pool_proj` branch of an inception module, deploy.prototxt:331-377 and its eight siblings):
+//     the 3x3 / stride 1 / pad 1 max-pool is computed on the A-operand path.  TMA brings the raw (BH+2) x (BW+2) halo patch
+//     of a 64-channel chunk into a ring of its own; eight of the epilogue warps take the maximum of the nine neighbours
+//     (three 128-bit shared-memory loads per patch row, running row maxima in registers) and write the pooled
+//     [BW*BH pixels][64 ch] tile in the swizzled K-major layout the MMA reads.  The pooled blob never exists in HBM.
+//     Zero fill stands in for Caffe's clipped windows: the planner only fuses when the input is non-negative.
 //   * "Direct" segments (the fp32 heads, deploy.prototxt:2118-2175) are written straight from registers as NCHW
 //     float32 (lanes = consecutive pixels), with an optional sigmoid (coverage/sig :2144-2149).
 #pragma once
@@ -51,6 +57,10 @@ struct ConvTc2Params {
     int BW, BH, tiles_x, tiles_y;
     int PW;                  // accumulator row pitch per image row: BW (TAP) or BW + kw - 1 (HALO)
     int halo;                // 1 = HALO mode
+    int pool;                // 1 = POOL mode: a 3x3 / stride 1 / pad 1 max-pool of the (non-negative) input is applied on the way
+                             //     to the A operand (raw halo patches by TMA -> eight pooling warps -> UMMA layout)
+    int r_stages;            //     raw-patch ring: stages, bytes per stage, bytes per TMA box
+    uint32_t r_stage_bytes, r_tx_bytes;
     int flat;                // 1 = 1x1 convolution over the flattened pixel index (H = 1, W = batch * H * W: 128-pixel tiles
                              //     that ignore image and row boundaries; host-side bookkeeping only)
     int m_tiles, n_tiles, BN;
@@ -189,7 +199,7 @@ struct TileIter {
 
 // KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0,
 // KK = kernel size known at compile time in HALO mode (3, 4, 5; 0 = read it from the parameters)
-template <int KSTEPS, bool HALO, bool PROF, int KK>
+template <int KSTEPS, bool HALO, bool PROF, int KK, bool POOL = false>
 __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                                       const __grid_constant__ CUtensorMap tmap_b,
                                                                       const __grid_constant__ ConvTc2Params p) {
@@ -205,12 +215,17 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const uint32_t a_base = smem_base;
     const uint32_t a_ring_bytes = (uint32_t)p.a_stages * p.a_stage_bytes, b_ring_bytes = (uint32_t)p.b_stages * p.b_stage_bytes;
     const uint32_t b_base = a_base + (uint32_t)nr * a_ring_bytes;
-    const uint32_t bias_base = b_base + (uint32_t)nrb * b_ring_bytes;                     // 64 floats per epilogue warp
+    const uint32_t raw_base = b_base + (uint32_t)nrb * b_ring_bytes;                      // POOL mode: raw halo patches
+    const uint32_t bias_base = raw_base + (POOL ? (uint32_t)p.r_stages * p.r_stage_bytes : 0u);   // 64 floats per epilogue warp
     const uint32_t bar_base = bias_base + (uint32_t)kTcEpiWarps * 256u;
     const uint32_t afull0 = bar_base, aempty0 = afull0 + 8u * nr * p.a_stages;
     const uint32_t bfull0 = aempty0 + 8u * nr * p.a_stages, bempty0 = bfull0 + 8u * nrb * p.b_stages;
     const uint32_t tfull0 = bempty0 + 8u * nrb * p.b_stages, tempty0 = tfull0 + 32u;     // up to 4 accumulators
     const uint32_t tmem_slot = tempty0 + 32u;
+    const uint32_t rfull0 = tmem_slot + 8u, rempty0 = rfull0 + 8u * (POOL ? p.r_stages : 0);
+    // POOL mode: warps 4..11 pool, warps 12..19 drain the accumulators (TMEM lane quadrant = warp % 4 either way)
+    constexpr int kPoolWarps = POOL ? 8 : 0;
+    constexpr int kEpiFirst = kTcMmaWarp + 1 + kPoolWarps, NE = kTcEpiWarps - kPoolWarps;
 
     // warp index through a shuffle: provably warp-uniform for the compiler (role branches and everything derived from the
     // role stay in uniform registers)
@@ -220,9 +235,11 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
     const int a_iters = HALO ? p.n_cchunks : taps * p.n_cchunks;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < nr * p.a_stages; ++s) { mbar_init(afull0 + 8u * s, 1); mbar_init(aempty0 + 8u * s, 1); }
+        for (int s = 0; s < nr * p.a_stages; ++s) { mbar_init(afull0 + 8u * s, POOL ? kPoolWarps : 1); mbar_init(aempty0 + 8u * s, 1); }
         for (int s = 0; s < nrb * p.b_stages; ++s) { mbar_init(bfull0 + 8u * s, 1); mbar_init(bempty0 + 8u * s, 1); }
-        for (int a = 0; a < 4; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, kTcEpiWarps / p.egroups); }
+        for (int a = 0; a < 4; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, NE / p.egroups); }
+        if (POOL)
+            for (int s = 0; s < p.r_stages; ++s) { mbar_init(rfull0 + 8u * s, 1); mbar_init(rempty0 + 8u * s, kPoolWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -259,11 +276,14 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
             if (doB && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
             __syncwarp();
             const uint32_t b_tx = (uint32_t)p.BN * span * (uint32_t)p.b_taps;
-            const uint32_t a_ring = a_base + (uint32_t)ring * a_ring_bytes;
+            // (POOL mode: the "A" loads of this warp are the raw halo patches, into their own ring)
+            const uint32_t a_ring = POOL ? raw_base : a_base + (uint32_t)ring * a_ring_bytes;
             const uint32_t b_ring = b_base + (p.b_resident ? 0u : (uint32_t)ring * b_ring_bytes);
-            const uint32_t af = afull0 + 8u * ring * p.a_stages, ae = aempty0 + 8u * ring * p.a_stages;
+            const uint32_t af = POOL ? rfull0 : afull0 + 8u * ring * p.a_stages, ae = POOL ? rempty0 : aempty0 + 8u * ring * p.a_stages;
             const uint32_t bf = bfull0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
             const uint32_t be = bempty0 + (p.b_resident ? 0u : 8u * ring * p.b_stages);
+            const uint32_t pa_stage = POOL ? p.r_stage_bytes : p.a_stage_bytes, pa_tx = POOL ? p.r_tx_bytes : p.a_tx_bytes;
+            const uint32_t pa_stages = (uint32_t)(POOL ? p.r_stages : p.a_stages);
             uint32_t sa = 0, pha = 0, sb = 0, phb = 0;
             const int n0 = my_nt * p.BN;
             TileIter ti;
@@ -278,10 +298,10 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 auto load_a = [&](int cc, int r, int s) {
                     mbar_wait_hint(ae + 8u * sa, pha ^ 1u);
                     __syncwarp();
-                    const uint32_t dst = a_ring + sa * p.a_stage_bytes;
+                    const uint32_t dst = a_ring + sa * pa_stage;
                     if (!elect_one()) {
                     } else if (HALO && p.a_bulk) {
-                        mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
+                        mbar_expect_tx(af + 8u * sa, pa_tx);
                         // one plain bulk copy per patch row: PW pixels x `span` bytes, contiguous in the image
                         const uint32_t rb = (uint32_t)p.PW * span;
                         const char* src = static_cast<const char*>(p.a_src) + (size_t)n_img * p.a_img_pitch +
@@ -290,11 +310,11 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                         for (int pr = 0; pr < rows; ++pr)
                             bulk_load(dst + (uint32_t)pr * rb, src + (size_t)pr * p.a_row_pitch, rb, af + 8u * sa);
                     } else {
-                        mbar_expect_tx(af + 8u * sa, p.a_tx_bytes);
+                        mbar_expect_tx(af + 8u * sa, pa_tx);
                         tma_load_4d(dst, &tmap_a, af + 8u * sa, cc * p.CK, ow0 + s, oh0 + r, n_img);
                     }
                     __syncwarp();
-                    if (++sa == (uint32_t)p.a_stages) { sa = 0; pha ^= 1u; }
+                    if (++sa == pa_stages) { sa = 0; pha ^= 1u; }
                 };
                 auto load_b = [&](int kb) {      // kb = first K-block of the round, in the packed (= global) order
                     if (!b_split || (b_idx & 1u) == b_par) {
@@ -439,11 +459,68 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 if (PROF && lane == 0) FCNOD_PROF(1, itp, 63);
             }
         }
+    } else if (POOL && warp < kEpiFirst) {
+        // ================= POOL mode: 3x3 / stride 1 / pad 1 max-pool between the raw patch ring and the A ring ==========
+        // thread = (16-byte channel chunk j of the 128-byte pixel row, patch column): it marches down the patch rows with
+        // the horizontal 3-maxima of the two previous rows in registers.  A quarter-warp reads / writes the 8 chunks of one
+        // pixel = one 128-byte line (the swizzle permutes chunks inside the line): conflict-free.
+        const int pt = (int)threadIdx.x - 32 * (kTcMmaWarp + 1);
+        const uint32_t j = (uint32_t)pt & 7u;
+        const int c0 = pt >> 3, RW = p.BW + 2, rows = p.BH + 2;
+        auto lds128 = [](uint32_t a) {
+            uint4 v;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+            return v;
+        };
+        auto max2 = [](uint32_t a, uint32_t b) {
+            const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+            return *reinterpret_cast<const uint32_t*>(&r);
+        };
+        auto max3 = [&](const uint4& a, const uint4& b, const uint4& c) {
+            return make_uint4(max2(max2(a.x, b.x), c.x), max2(max2(a.y, b.y), c.y), max2(max2(a.z, b.z), c.z), max2(max2(a.w, b.w), c.w));
+        };
+        uint32_t sr = 0, phr = 0, sa = 0, pha = 0;
+        TileIter ti;
+        ti.init(p);
+        for (; ti.valid(p); ti.next(p)) {
+            for (int cc = 0; cc < p.n_cchunks; ++cc) {
+                mbar_wait(rfull0 + 8u * sr, phr);                  // the raw patch has landed
+                mbar_wait(aempty0 + 8u * sa, pha ^ 1u);            // the MMA has finished with this A stage
+                const uint32_t raw = raw_base + sr * p.r_stage_bytes, dst = a_base + sa * p.a_stage_bytes;
+                for (int col = c0; col < p.BW; col += 32) {
+                    uint4 h0 = make_uint4(0, 0, 0, 0), h1 = h0;
+#pragma unroll 2
+                    for (int pr = 0; pr < rows; ++pr) {
+                        const uint32_t r0 = (uint32_t)(pr * RW + col);
+                        const uint4 a = lds128(raw + r0 * 128u + ((j ^ (r0 & 7u)) << 4));
+                        const uint4 b = lds128(raw + (r0 + 1u) * 128u + ((j ^ ((r0 + 1u) & 7u)) << 4));
+                        const uint4 c = lds128(raw + (r0 + 2u) * 128u + ((j ^ ((r0 + 2u) & 7u)) << 4));
+                        const uint4 h = max3(a, b, c);
+                        if (pr >= 2) {
+                            const uint32_t m = (uint32_t)((pr - 2) * p.BW + col);
+                            const uint4 o = max3(h0, h1, h);
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                                         ::"r"(dst + m * 128u + ((j ^ (m & 7u)) << 4)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+                        }
+                        h0 = h1; h1 = h;
+                    }
+                }
+                // generic-proxy stores -> visible to the tensor core's async-proxy reads, then hand both stages over
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(afull0 + 8u * sa) : "memory");
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rempty0 + 8u * sr) : "memory");
+                }
+                if (++sr == (uint32_t)p.r_stages) { sr = 0; phr ^= 1u; }
+                if (++sa == (uint32_t)p.a_stages) { sa = 0; pha ^= 1u; }
+            }
+        }
     } else {
-        // ================= epilogue: 8 warps; warp w drains TMEM lane quadrant w % 4, column half (w - 5) / 4 ===========
+        // ================= epilogue: 16 warps (8 in POOL mode); warp w drains TMEM lane quadrant w % 4 ==================
         // Everything that does not change from tile to tile is computed once: the lane's position inside the pixel box,
         // the bias of the warp's columns (staged in shared memory) and the destination of each 16-column group.
-        const int ew = warp - (kTcMmaWarp + 1);
+        const int ew = warp - kEpiFirst;
         const int q = warp & 3;
         const int egrp = (ew >> 2) & (int)(p.egroups - 1u);          // which tiles: it % egroups == egrp
         const int part = (ew >> 2) / (int)p.egroups;                 // which columns of them

@@ -93,6 +93,7 @@ struct ConvWeights {
     float* d_bias = 0;         // padded
     int CK = 0, n_cchunks = 0, BN = 0, n_tiles = 0;
     bool halo = false;         // k x k taps served from one shared-memory patch per channel chunk (conv_tc2.cuh)
+    bool pool = false;         // a 3x3 / stride 1 / pad 1 max-pool of the input runs on the A-operand path (POOL mode)
     // space-to-depth form of a stride-2 convolution on the (Power-transformed) network input
     bool s2d = false;
     int ka = 0;                // taps per axis after space-to-depth (padded to 1/2/4)
@@ -144,6 +145,11 @@ struct Step {
     ConvTc2Params tc;
     size_t tc_smem = 0;
     int tc_grid = 0;
+    // lanes (plan_lanes): independent branches of the layer graph run on different streams
+    int lane = 0;
+    std::vector<int> waits;    // steps on OTHER lanes whose completion event this step waits for
+    bool signal = false;       // some later step on another lane waits for this one
+    cudaEvent_t ev = 0;
 };
 
 }  // namespace
@@ -174,6 +180,9 @@ struct fcnod_net {
     float* pre_scratch = 0;
     cudaGraphExec_t graph = 0;
     cudaStream_t stream = 0;
+    cudaStream_t lane_stream[2] = {0, 0};  // lanes 1, 2 of the forward (lane 0 = the caller's stream)
+    cudaEvent_t fork_ev = 0, join_ev[2] = {0, 0};
+    int n_lanes = 1;
     cudaStream_t copy_stream = 0;        // uploads of fcnod_detect's second half-batch, overlapped with the first one's compute
     cudaEvent_t copy_ev[2] = {0, 0};
     int32_t* pinned_big = 0;             // detections of a whole fcnod_detect call (all chunks)
@@ -230,6 +239,7 @@ int grid_for(long work_items, int threads) {
 }
 
 void choose_tc_tiling(ConvWeights& cw);
+void plan_lanes(fcnod_net* net);
 
 // ------------------------------------------------------------------------------------ planning
 void build_plan(fcnod_net* net, const WeightMap& weights) {
@@ -243,6 +253,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
     std::map<std::string, int> producer;        // blob -> first layer writing it (not in-place)
     std::map<std::string, std::vector<int> > consumers;
     std::map<std::string, int> inplace_ops;     // blob -> number of in-place layers rewriting it
+    std::map<std::string, bool> nonneg;         // blob is >= 0 everywhere (ReLU / Sigmoid outputs and what pools, LRNs, concats make of them)
     shp[def.input_name] = Shape{def.input_dims[1], def.input_dims[2], def.input_dims[3]};
     for (size_t i = 0; i < def.layers.size(); ++i) {
         const LayerDef& L = def.layers[i];
@@ -273,6 +284,17 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             default: break;
         }
         FCNOD_CHECK(o.H > 0 && o.W > 0, "layer '" + L.name + "' produces an empty blob");
+        switch (L.type) {
+            case L_RELU: case L_SIGMOID: nonneg[L.top[0]] = true; break;
+            case L_POOL: case L_LRN: case L_DROPOUT: nonneg[L.top[0]] = nonneg[L.bottom[0]] && (L.type != L_LRN || L.lrn_k > 0.f); break;
+            case L_CONCAT: {
+                bool all = true;
+                for (size_t b = 0; b < L.bottom.size(); ++b) all = all && nonneg[L.bottom[b]];
+                nonneg[L.top[0]] = all;
+                break;
+            }
+            default: nonneg[L.top[0]] = false; break;
+        }
         if (shp.count(L.top[0])) {
             Shape e = shp[L.top[0]];
             FCNOD_CHECK(e.C == o.C && e.H == o.H && e.W == o.W, "in-place layer '" + L.name + "' changes shape");
@@ -452,6 +474,32 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
         }
     }
 
+    // ---- pass 2c: max-pool 3x3 / stride 1 / pad 1 feeding exactly one 1x1 tensor-core convolution (the `pool ->
+    // pool_proj` branch of every inception module, deploy.prototxt:331-377): the pool runs on the convolution's A-operand
+    // path (conv_tc2.cuh POOL mode) and its blob is never materialised.  Zero fill replaces the clipped windows, which
+    // is only the same thing when the input is non-negative.
+    std::map<int, int> pool_of;                  // conv layer -> pool layer folded into it
+    std::set<int> pool_fused;                    // pool layers folded away
+    if (bf && fuse && !getenv("FCNOD_NO_POOLPROJ")) {
+        for (size_t i = 0; i < def.layers.size(); ++i) {
+            const LayerDef& L = def.layers[i];
+            if (L.type != L_POOL || !L.pool_max || L.kernel != 3 || L.stride != 1 || L.pad != 1) continue;
+            const std::string& top = L.top[0];
+            if (L.bottom[0] == top || inplace_ops.count(top) || outputs.count(top) || virt.count(top) || alias.count(top)) continue;
+            if (!consumers.count(top) || consumers[top].size() != 1) continue;
+            const int ci = consumers[top][0];
+            const LayerDef& Cn = def.layers[ci];
+            if (Cn.type != L_CONV || Cn.kernel != 1 || Cn.stride != 1 || Cn.pad != 0 || Cn.bottom.size() != 1) continue;
+            if (!tc_layers.count(ci) || group.count(ci) || group_leader.count(ci) || direct_blob.count(ci)) continue;
+            const std::string& src = L.bottom[0];
+            if (!nonneg[src] || virt.count(src) || dt[src] != DT_BF16 || src == def.input_name) continue;
+            int off, ldc; std::string root;
+            slice_of(src, off, ldc, root);
+            if (shp[src].C % 8 || off % 8 || ldc % 8) continue;
+            pool_of[ci] = (int)i; pool_fused.insert((int)i); virt.insert(top);
+        }
+    }
+
     // ---- create blobs + buffers in definition order
     net->blobs.clear(); net->blob_index.clear(); net->buffers.clear();
     struct Maker {
@@ -528,7 +576,8 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             }
             case L_CONV: {
                 if (group_leader.count((int)i)) break;      // emitted with its group leader
-                st.in = blob_id(net, L.bottom[0]);
+                const bool pooled = pool_of.count((int)i) > 0;
+                st.in = blob_id(net, pooled ? def.layers[pool_of[(int)i]].bottom[0] : L.bottom[0]);
                 const bool is_s2d = s2d_conv.count((int)i) > 0;
                 const bool tc_ok = tc_layers.count((int)i) > 0;
                 FCNOD_CHECK(is_s2d || net->blobs[st.in].buf >= 0, "Convolution directly on the NCHW input is not supported; insert a Power layer ('" + L.name + "')");
@@ -536,6 +585,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 if (group.count((int)i)) members = group[(int)i];
                 const int Cin = net->blobs[st.in].C;
                 ConvWeights cw; cw.Cin = Cin; cw.k = L.kernel; cw.stride = L.stride; cw.pad = L.pad; cw.Cout = 0;
+                cw.pool = pooled;
                 std::string names;
                 for (size_t m = 0; m < members.size(); ++m) {
                     const int li = members[m];
@@ -602,6 +652,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 std::ostringstream d;
                 d << (tc_ok ? "conv_tc " : "conv_simt ") << names << " " << L.kernel << "x" << L.kernel << "/" << L.stride
                   << " Cin=" << cw.Cin << " Cout=" << cw.Cout << (st.relu ? " +relu" : "") << (is_s2d ? " +s2d+power" : "");
+                if (pooled) d << " +maxpool3x3(" << def.layers[pool_of[(int)i]].name << ")";
                 for (size_t m = 0; m < st.segs.size(); ++m)
                     if (st.segs[m].flags & SEG_DIRECT) d << ((st.segs[m].flags & SEG_SIGMOID) ? " +sigmoid" : "") << " +nchw";
                 st.desc = d.str();
@@ -624,6 +675,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_POOL: {
+                if (pool_fused.count((int)i)) { mk.make(top); break; }      // runs inside its 1x1 consumer (POOL mode)
                 if (fuse_first.count((int)i)) { mk.make(top); break; }      // Pool -> LRN: emitted at the LRN
                 if (fuse_second.count((int)i)) {                            // LRN -> Pool
                     const LayerDef& F = def.layers[fuse_second[(int)i]];
@@ -684,6 +736,99 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             Step st; st.kind = S_EXPORT; st.in = (int)i; st.desc = "export " + net->blobs[i].name;
             net->steps.push_back(st);
         }
+    plan_lanes(net);
+}
+
+// ------------------------------------------------------------------------------------ lanes
+// The layer graph is not a chain: inside an inception module (deploy.prototxt:163-377) the 3x3 and the 5x5 convolution
+// only need their own reduce outputs, and `pool -> pool_proj` only needs the module's input.  Every launch is a
+// persistent grid whose last round leaves most SMs idle (448 tiles on 148 SMs = 3.03 rounds); launches that do not
+// depend on each other go to different streams ("lanes") so that the block scheduler fills one kernel's tail -- and its
+// prologue -- with the CTAs of the next.  Dependencies are derived from the buffer regions every step reads and writes
+// (RAW, WAR and WAW); cross-lane edges become event waits, which stream capture turns into graph edges.
+struct Region { int buf, c0, c1; };
+bool overlaps(const Region& a, const Region& b) { return a.buf == b.buf && a.c0 < b.c1 && b.c0 < a.c1; }
+
+void plan_lanes(fcnod_net* net) {
+    const int kLanes = 3, kOutBase = 1 << 20;
+    const size_t n = net->steps.size();
+    static const bool off = getenv("FCNOD_LANES") && atoi(getenv("FCNOD_LANES")) <= 1;
+    std::vector<std::vector<Region> > rd(n), wr(n);
+    auto blob_region = [&](int bi) {
+        const Blob& b = net->blobs[bi];
+        Region r = {b.buf, b.c_off, b.c_off + b.C};      // buf -1 = the NCHW input
+        return r;
+    };
+    for (size_t i = 0; i < n; ++i) {
+        const Step& st = net->steps[i];
+        switch (st.kind) {
+            case S_S2D: rd[i].push_back(blob_region(0)); wr[i].push_back(Region{st.s2d_buf, 0, 1 << 30}); break;
+            case S_CONV_SIMT: case S_CONV_TC:
+                if (net->convs[st.conv].s2d) rd[i].push_back(Region{st.s2d_buf, 0, 1 << 30});
+                else rd[i].push_back(blob_region(st.in));
+                for (size_t k = 0; k < st.segs.size(); ++k) {
+                    if (st.segs[k].flags & SEG_DIRECT) wr[i].push_back(Region{kOutBase + st.segs[k].direct_blob, 0, 1 << 30});
+                    else wr[i].push_back(blob_region(st.segs[k].blob));
+                }
+                break;
+            case S_COPY: {
+                rd[i].push_back(blob_region(st.in));
+                const Blob& ob = net->blobs[st.out];
+                wr[i].push_back(Region{ob.buf, ob.c_off + st.unary_op, ob.c_off + st.unary_op + net->blobs[st.in].C});
+                break;
+            }
+            case S_EXPORT: rd[i].push_back(blob_region(st.in)); wr[i].push_back(Region{kOutBase + st.in, 0, 1 << 30}); break;
+            default: rd[i].push_back(blob_region(st.in)); wr[i].push_back(blob_region(st.out)); break;
+        }
+    }
+    int last_on[kLanes];
+    for (int l = 0; l < kLanes; ++l) last_on[l] = -1;
+    net->n_lanes = 1;
+    for (size_t j = 0; j < n; ++j) {
+        Step& st = net->steps[j];
+        st.lane = 0; st.waits.clear(); st.signal = false;
+        if (off) continue;
+        std::vector<int> deps;
+        for (size_t i = 0; i < j; ++i) {
+            bool dep = false;
+            for (size_t a = 0; a < wr[i].size() && !dep; ++a) {
+                for (size_t b = 0; b < rd[j].size() && !dep; ++b) dep = overlaps(wr[i][a], rd[j][b]);
+                for (size_t b = 0; b < wr[j].size() && !dep; ++b) dep = overlaps(wr[i][a], wr[j][b]);
+            }
+            for (size_t a = 0; a < rd[i].size() && !dep; ++a)
+                for (size_t b = 0; b < wr[j].size() && !dep; ++b) dep = overlaps(rd[i][a], wr[j][b]);
+            if (dep) deps.push_back((int)i);
+        }
+        int lane = 0;
+        if (!deps.empty()) {
+            const int dmax = deps.back();
+            if (last_on[net->steps[dmax].lane] == dmax) {
+                lane = net->steps[dmax].lane;                 // continue the chain of the newest dependency
+            } else {                                           // a branch: the lane that has been idle the longest
+                lane = -1;
+                for (int l = 0; l < kLanes; ++l)
+                    if (l != net->steps[j - 1].lane && (lane < 0 || last_on[l] < last_on[lane])) lane = l;
+            }
+        }
+        st.lane = lane;
+        // one wait per other lane: its newest dependency (events of a lane complete in order)
+        for (int l = 0; l < kLanes; ++l) {
+            if (l == lane) continue;
+            int newest = -1;
+            for (size_t d = 0; d < deps.size(); ++d)
+                if (net->steps[deps[d]].lane == l) newest = deps[d];
+            if (newest < 0) continue;
+            // already implied by an earlier step of this lane that waited for it (or for something newer on lane l)?
+            bool implied = false;
+            for (size_t i = 0; i < j && !implied; ++i)
+                if (net->steps[i].lane == lane)
+                    for (size_t w = 0; w < net->steps[i].waits.size(); ++w)
+                        if (net->steps[net->steps[i].waits[w]].lane == l && net->steps[i].waits[w] >= newest) implied = true;
+            if (!implied) { st.waits.push_back(newest); net->steps[newest].signal = true; }
+        }
+        last_on[lane] = (int)j;
+        net->n_lanes = std::max(net->n_lanes, lane + 1);
+    }
 }
 
 // ------------------------------------------------------------------------------------ tcgen05 tiling (host only)
@@ -695,6 +840,12 @@ void choose_tc_tiling(ConvWeights& cw) {
         cw.CK = kS2dCpad;
         cw.n_cchunks = 1;
         cw.halo = true;
+        return;
+    }
+    if (cw.pool) {  // POOL mode pools 64-channel chunks (128-byte swizzled rows on both sides of the pooling warps)
+        cw.halo = false;
+        cw.CK = 64;
+        cw.n_cchunks = (cw.Cin + 63) / 64;
         return;
     }
     const char* nh = getenv("FCNOD_NO_HALO");
@@ -732,6 +883,8 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     p.kh = p.kw = cw.k; p.pad_h = p.pad_w = cw.pad;
     p.n_cchunks = cw.n_cchunks; p.CK = cw.CK;
     p.halo = cw.halo ? 1 : 0;
+    p.pool = cw.pool ? 1 : 0;
+    if (cw.pool) p.pad_h = p.pad_w = 1;    // the raw patch starts one pixel up / left of the tile
     if (cw.s2d) {
         p.kh = p.kw = cw.ka; p.CK = kS2dCpad;                // HALO mode on the space-to-depth image, one K step per tap
         p.n_cchunks = 1;
@@ -770,7 +923,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     }
     static const bool flat_off = getenv("FCNOD_FLAT") && getenv("FCNOD_FLAT")[0] == '0';
     const long npix = (long)batch * ob.H * ob.W;
-    if (!flat_off && !p.halo && !cw.s2d && cw.k == 1 && cw.pad == 0 && !(st.segs[0].flags & SEG_DIRECT) &&
+    if (!flat_off && !p.halo && !cw.s2d && !cw.pool && cw.k == 1 && cw.pad == 0 && !(st.segs[0].flags & SEG_DIRECT) &&
         npix < (1L << 30) && geos[0].BW * geos[0].BH < 128) {
         TcGeo g;
         g.flat = 1; g.H = 1; g.W = (int)npix;
@@ -792,14 +945,20 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     const int dual_bn = de ? (de[0] == '0' ? 0 : (de[0] == '1' ? 256 : atoi(de))) : 256;
     const double ksteps_tile = (double)taps * ((p.n_cchunks - 1) * (p.CK / 16) + p.ksteps_last);   // real 16-wide K steps
     const size_t fixed = (size_t)kTcEpiWarps * 256 + 1024 + 1024;     // bias staging, barriers, alignment slack
-    const size_t avail = kTcSmemBudget - fixed;
-    struct Cand { int geo, nt, BN, a_st, b_st, bt, resident, dual; uint32_t b_stage; double cost; };
+    struct Cand { int geo, nt, BN, a_st, b_st, bt, resident, dual, r_st; uint32_t b_stage; double cost; };
     std::vector<Cand> cands;
+    // POOL mode: raw halo patches of (BW+2) x (BH+2) pixels x 64 channels in a ring of their own (2..4 stages); the eight
+    // remaining epilogue warps drain at most 128 columns; one issuing thread
+    const uint32_t r_tx = cw.pool ? (uint32_t)((geos[0].BW + 2) * (geos[0].BH + 2)) * span : 0;
+    const uint32_t r_stage = (uint32_t)align_up(r_tx, 1024);
+    for (int r_st = cw.pool ? 2 : 0; r_st <= (cw.pool ? 4 : 0); ++r_st)
     for (size_t gi = 0; gi < geos.size(); ++gi) {
       const TcGeo& G = geos[gi];
-      for (int nt = ceil_div(N8, 256); nt <= ceil_div(N8, 16); ++nt) {
+      if ((size_t)r_st * r_stage + 4 * (size_t)G.a_stage > kTcSmemBudget - fixed) continue;
+      const size_t avail = kTcSmemBudget - fixed - (size_t)r_st * r_stage;
+      for (int nt = ceil_div(N8, cw.pool ? 128 : 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
-        if (BN > 256 || nt * BN - N8 >= BN) continue;
+        if (BN > (cw.pool ? 128 : 256) || nt * BN - N8 >= BN) continue;
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
         const int mslots = std::max(1, std::min(G.m_tiles, kNumSMs / nt));
         const long rounds = ((long)G.m_tiles + mslots - 1) / mslots;
@@ -807,7 +966,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
             const uint32_t b_stage = (uint32_t)align_up((size_t)BN * span, 1024) * bt;
             const int rounds_b = taps * p.n_cchunks / bt;                               // B stages consumed per tile
             for (int resident = 0; resident <= (no_resident ? 0 : 1); ++resident)
-                for (int dual = 0; dual <= ((BN <= dual_bn && G.m_tiles > 1) ? 1 : 0); ++dual) {
+                for (int dual = 0; dual <= ((BN <= dual_bn && G.m_tiles > 1 && !cw.pool) ? 1 : 0); ++dual) {
                     const int nr = dual ? 2 : 1;
                     int a_st = 0, b_st = 0;
                     if (resident) {
@@ -846,7 +1005,11 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
                     const double epi = 300.0 + 10.0 * BN;
                     double tile = std::max(std::max(std::max(mma, smem), issue), std::max(load, epi)) + 400.0;
                     if (a_st < 2 && !dual) tile += 0.5 * a_bytes / 32.0;                       // no A prefetch across tiles
-                    Cand c = {(int)gi, nt, BN, a_st, b_st, bt, resident, dual, b_stage, 0.0};
+                    if (cw.pool) {   // per 64-channel chunk: ~4.5 + 1 shared-memory 128-bit accesses per pooled 16-byte piece
+                        const double pool = p.n_cchunks * ((double)r_tx + 5.5 * G.a_tx) / 128.0 + 300.0;
+                        tile = std::max(tile, pool) + (r_st < 3 ? 0.25 * pool : 0.0);
+                    }
+                    Cand c = {(int)gi, nt, BN, a_st, b_st, bt, resident, dual, r_st, b_stage, 0.0};
                     c.cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 32.0 : 0.0);
                     cands.push_back(c);
                 }
@@ -861,6 +1024,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
         p.n_tiles = c.nt; p.BN = c.BN; p.a_stages = c.a_st; p.b_stages = c.b_st; p.b_taps = c.bt;
         p.b_stage_bytes = c.b_stage;
         p.b_resident = c.resident; p.dual = c.dual;
+        p.r_stages = c.r_st; p.r_stage_bytes = r_stage; p.r_tx_bytes = r_tx;
         const TcGeo& G = geos[c.geo];
         p.flat = G.flat; p.H = G.H; p.W = G.W; p.BW = G.BW; p.PW = G.PW; p.BH = G.BH;
         p.tiles_x = G.tiles_x; p.tiles_y = G.tiles_y; p.m_tiles = G.m_tiles;
@@ -876,11 +1040,14 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     p.egroups = p.BN <= 64 ? 4 : (p.BN <= 128 ? 2 : 1);
     if (egroups_env == 1 || egroups_env == 2) p.egroups = std::min<uint32_t>(p.egroups, (uint32_t)egroups_env);
     if (p.acc_lg == 1 && p.egroups > 2) p.egroups = 2;
-    p.cols_half0 = ceil_div(p.BN, 16 * (4 / (int)p.egroups)) * 16;   // columns per epilogue warp (<= 64)
+    const int epi_per_quadrant = cw.pool ? 2 : 4;                    // POOL mode: eight of the sixteen warps pool
+    if (cw.pool) p.egroups = p.BN <= 64 ? 2 : 1;
+    p.cols_half0 = ceil_div(p.BN, 16 * (epi_per_quadrant / (int)p.egroups)) * 16;   // columns per epilogue warp (<= 64)
     p.tmem_cols = std::max<uint32_t>((1u << p.acc_lg) * acc, 32);
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
     st.tc_smem = (size_t)(p.dual ? 2 : 1) * p.a_stages * p.a_stage_bytes +
-                 (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)kTcEpiWarps * 256 + 1024 + 1024;
+                 (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)p.r_stages * p.r_stage_bytes +
+                 (size_t)kTcEpiWarps * 256 + 1024 + 1024;
     p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
     st.tc_grid = p.mstride * p.n_tiles;
     {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
@@ -1115,6 +1282,7 @@ void setup_tc_step(fcnod_net* net, Step& st) {
         cuuint64_t dims[4] = {(cuuint64_t)ib.C, (cuuint64_t)ib.W, (cuuint64_t)ib.H, (cuuint64_t)B};
         cuuint64_t strides[3] = {(cuuint64_t)ib.ldc * 2, (cuuint64_t)ib.W * ib.ldc * 2, (cuuint64_t)ib.H * ib.W * ib.ldc * 2};
         cuuint32_t box[4] = {(cuuint32_t)cw.CK, (cuuint32_t)p.PW, (cuuint32_t)(p.halo ? p.BH + p.kh - 1 : p.BH), 1};
+        if (p.pool) { box[1] = (cuuint32_t)(p.BW + 2); box[2] = (cuuint32_t)(p.BH + 2); }     // raw halo patch of the 3x3 pool
         if (p.flat) {   // all pixels of the batch as one row: [C][B*H*W][1][1]
             dims[1] = (cuuint64_t)B * ib.H * ib.W; dims[2] = 1; dims[3] = 1;
             strides[1] = dims[1] * ib.ldc * 2; strides[2] = strides[1];
@@ -1308,7 +1476,12 @@ void launch_tc2_inst(const Step& st, cudaStream_t s, bool prof) {
 }
 void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof) {
     const int ks = st.tc.CK / 16;
-    if (st.tc.halo) {
+    if (st.tc.pool) {
+        FCNOD_CHECK(ks == 4 && !st.tc.halo && !st.tc.dual, "internal: POOL mode needs 64-channel blocks, one issuer");
+        const dim3 g(st.tc_grid), b(kConvTc2Threads);
+        if (prof) conv_tc2_kernel<4, false, true, 0, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+        else conv_tc2_kernel<4, false, false, 0, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    } else if (st.tc.halo) {
         const int kk = st.tc.kh == st.tc.kw ? st.tc.kh : 0;
         if (ks == 4 && kk == 3) launch_tc2_inst<4, true, 3>(st, s, prof);
         else if (ks == 4 && kk == 5) launch_tc2_inst<4, true, 5>(st, s, prof);
@@ -1333,6 +1506,8 @@ void conv_tc2_set_smem_limit() {      // per device, at net creation (outside an
     tc2_smem_attr<1, true, 4>(); tc2_smem_attr<1, true, 0>(); tc2_smem_attr<1, true, 5>();
     tc2_smem_attr<2, true, 5>(); tc2_smem_attr<2, true, 0>();
     tc2_smem_attr<4, false, 0>(); tc2_smem_attr<2, false, 0>(); tc2_smem_attr<1, false, 0>();
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, false, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, true, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 }
 
 void launch_export(const fcnod_net* net, const Blob& b, float* dst, cudaStream_t s) {
@@ -1466,7 +1641,28 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
 void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s) {
     FCNOD_CHECK(net->device >= 0, "plan-only handle (device < 0): no compute is possible; there is no CPU fallback");
     FCNOD_CHECK(net->batch > 0, "net not reshaped");
-    for (size_t i = 0; i < net->steps.size(); ++i) run_step(net, net->steps[i], data_dev, s);
+    if (net->n_lanes <= 1) {
+        for (size_t i = 0; i < net->steps.size(); ++i) run_step(net, net->steps[i], data_dev, s);
+        return;
+    }
+    // lane 0 = the caller's stream; the others fork from it here and join it again at the end (under stream capture the
+    // event waits become graph edges: independent branches are independent graph nodes)
+    cudaStream_t lanes[3] = {s, net->lane_stream[0], net->lane_stream[1]};
+    bool forked[3] = {true, false, false};
+    FCNOD_CUDA(cudaEventRecord(net->fork_ev, s));
+    for (size_t i = 0; i < net->steps.size(); ++i) {
+        const Step& st = net->steps[i];
+        cudaStream_t ls = lanes[st.lane];
+        if (!forked[st.lane]) { FCNOD_CUDA(cudaStreamWaitEvent(ls, net->fork_ev, 0)); forked[st.lane] = true; }
+        for (size_t w = 0; w < st.waits.size(); ++w) FCNOD_CUDA(cudaStreamWaitEvent(ls, net->steps[st.waits[w]].ev, 0));
+        run_step(net, st, data_dev, ls);
+        if (st.signal) FCNOD_CUDA(cudaEventRecord(st.ev, ls));
+    }
+    for (int l = 1; l < 3; ++l)
+        if (forked[l]) {
+            FCNOD_CUDA(cudaEventRecord(net->join_ev[l - 1], lanes[l]));
+            FCNOD_CUDA(cudaStreamWaitEvent(s, net->join_ev[l - 1], 0));
+        }
 }
 
 void ensure_detect_buffers(fcnod_net* net) {
@@ -1562,6 +1758,13 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_tile_kernel<bf16, 3, 2, 2, true, 4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
+    for (int l = 0; l < 2; ++l) {
+        FCNOD_CUDA(cudaStreamCreateWithFlags(&net->lane_stream[l], cudaStreamNonBlocking));
+        FCNOD_CUDA(cudaEventCreateWithFlags(&net->join_ev[l], cudaEventDisableTiming));
+    }
+    FCNOD_CUDA(cudaEventCreateWithFlags(&net->fork_ev, cudaEventDisableTiming));
+    for (size_t i = 0; i < net->steps.size(); ++i)
+        if (net->steps[i].signal) FCNOD_CUDA(cudaEventCreateWithFlags(&net->steps[i].ev, cudaEventDisableTiming));
     upload_weights(net.get());
     reshape(net.get(), net->def.input_dims[0] > 0 ? net->def.input_dims[0] : 1);
     *out = net.release();
@@ -1582,6 +1785,12 @@ int fcnod_net_destroy(fcnod_net* net) {
             if (net->convs[i].d_bias_tab) cudaFree(net->convs[i].d_bias_tab);
         }
         if (net->stream) cudaStreamDestroy(net->stream);
+        for (int l = 0; l < 2; ++l) {
+            if (net->lane_stream[l]) cudaStreamDestroy(net->lane_stream[l]);
+            if (net->join_ev[l]) cudaEventDestroy(net->join_ev[l]);
+        }
+        if (net->fork_ev) cudaEventDestroy(net->fork_ev);
+        for (size_t i = 0; i < net->steps.size(); ++i) if (net->steps[i].ev) cudaEventDestroy(net->steps[i].ev);
         if (net->copy_stream) cudaStreamDestroy(net->copy_stream);
         for (int i = 0; i < 2; ++i) if (net->copy_ev[i]) cudaEventDestroy(net->copy_ev[i]);
         if (net->pinned_big) cudaFreeHost(net->pinned_big);
@@ -1634,10 +1843,15 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
     for (size_t i = 0; i < net->steps.size(); ++i) {
         const Step& st = net->steps[i];
         o << i << ": " << st.desc;
+        if (net->n_lanes > 1) {
+            o << " {lane " << st.lane;
+            for (size_t w = 0; w < st.waits.size(); ++w) o << (w ? "," : " after ") << st.waits[w];
+            o << "}";
+        }
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
-            o << " [" << (st.tc.halo ? "halo " : "") << (st.tc.flat ? "flat " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
-              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.dual ? " dual" : "") << " eg=" << st.tc.egroups << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
+            o << " [" << (st.tc.halo ? "halo " : "") << (st.tc.flat ? "flat " : "") << (st.tc.pool ? "pool " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
+              << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.pool ? "+" + std::to_string(st.tc.r_stages) + "raw" : std::string()) << (st.tc.dual ? " dual" : "") << " eg=" << st.tc.egroups << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }
         if (st.out >= 0) {

@@ -52,6 +52,12 @@ TC_CASES = [
     ('odd_hw', 20, 36, 32, [(48, 3), (16, 5)], 3),
     ('cin48_k5', 28, 28, 48, [(128, 5)], 1),
     ('big_w', 12, 160, 64, [(64, 3)], 1),
+    # max-pool 3x3/1 fused into the A-operand path of its 1x1 consumer (POOL mode)
+    ('poolproj_28', 28, 28, 192, [(64, 1), (32, 'p')], 2),
+    ('poolproj_56', 56, 56, 192, [(32, 'p'), (64, 3)], 1),
+    ('poolproj_odd', 20, 36, 72, [(48, 'p')], 3),              # channel tail (72 = 64 + 8), ragged tiles
+    ('poolproj_n160', 28, 28, 128, [(160, 'p')], 1),           # two N tiles
+    ('poolproj_k832', 28, 28, 832, [(128, 'p')], 4),           # 13 channel chunks, streamed weights
 ]
 
 
@@ -68,6 +74,8 @@ def test_conv_tc_mini_nets(case, tmp_path):
     exp = oracle_forward(proto, cm, x, bf16=True, want=want, tc_layers=tc_layers)
     got, plan = gpu_forward(proto, cm, x, 'bf16', want)
     assert 'conv_simt br' not in plan and 'conv_simt final' not in plan, plan     # every branch + the head on tcgen05
+    if any(k == 'p' for _c, k in branches):
+        assert '+maxpool3x3' in plan and '\npool ' not in plan and ': pool ' not in plan, plan
     assert all(('br%d ' % i) in plan or ('br%d\n' % i) in plan for i in range(len(branches))), plan
     for k in names:
         # stored bf16: allow one bf16 ulp of the blob's magnitude
@@ -76,6 +84,30 @@ def test_conv_tc_mini_nets(case, tmp_path):
     # and against the true fp32 oracle at the bf16 tolerance
     ref = oracle_forward(proto, cm, x, want=['out'])
     assert rel_err(got['out'], ref['out']) < TOL_BF16
+
+
+def test_pool_of_signed_input_is_not_fused(tmp_path):
+    """POOL mode substitutes zero fill for Caffe's clipped pooling windows, which is only valid on non-negative input:
+    a pool behind a convolution WITHOUT ReLU must stay a separate launch (and still match the oracle)."""
+    from fcn_object_detector_b200.caffemodel import write_caffemodel
+    from tests.util import _conv_txt
+    rs = np.random.RandomState(5)
+    txt = 'input: "data"\ninput_shape { dim: 2 dim: 3 dim: 28 dim: 28 }\n'
+    txt += 'layer { name: "xf" type: "Power" bottom: "data" top: "x" power_param { shift: -0.5 } }\n'
+    txt += _conv_txt('pre', 'x', 'pre', 64, 1, relu=False)
+    txt += 'layer { name: "pl" type: "Pooling" bottom: "pre" top: "pl" pooling_param { pool: MAX kernel_size: 3 stride: 1 pad: 1 } }\n'
+    txt += _conv_txt('proj', 'pl', 'out', 32, 1, relu=False)
+    layers = [('pre', 'Convolution', [rs.uniform(-1, 1, (64, 3, 1, 1)).astype(np.float32), rs.uniform(-0.5, 0.1, 64).astype(np.float32)]),
+              ('proj', 'Convolution', [rs.uniform(-0.2, 0.2, (32, 64, 1, 1)).astype(np.float32), rs.uniform(-0.2, 0.2, 32).astype(np.float32)])]
+    proto = str(tmp_path / 'signed.prototxt')
+    open(proto, 'w').write(txt)
+    cm = write_caffemodel(str(tmp_path / 'signed.caffemodel'), layers)
+    x = rs.uniform(0, 1, (2, 3, 28, 28)).astype(np.float32)
+    got, plan = gpu_forward(proto, cm, x, 'bf16', ['pl', 'out'])
+    assert '+maxpool3x3' not in plan and 'pool pl' in plan, plan
+    ref = oracle_forward(proto, cm, x, want=['pl', 'out'])
+    assert (ref['pl'] < 0).any()
+    assert rel_err(got['pl'], ref['pl']) < TOL_BF16 and rel_err(got['out'], ref['out']) < TOL_BF16
 
 
 STEM_CASES = [

@@ -119,7 +119,7 @@ def test_every_autotune_candidate_gives_the_same_bits(net64):
         assert [_checksum(net, o) for o in outs] == base
         d = plan[step]
         families.add(('s2d' if '+s2d' in d else 'halo' if '[halo' in d else 'heads' if '+nchw' in d else '1x1',
-                      d.split(' CK=')[1].split(' ')[0]))
+                      d.split('CK=')[1].split(' ')[0]))
     assert swept >= 40
     # conv1 (space-to-depth), 3x3 HALO CK=64, 5x5 HALO CK=16/32, fused 1x1, heads
     assert {('s2d', '16'), ('halo', '64'), ('halo', '32'), ('halo', '16'), ('1x1', '64'), ('heads', '64')} <= families, families

@@ -40,12 +40,18 @@ def write_mini_net(dirpath, tag, H, W, cin, branches, batch=1, seed=0, final=8):
     tops = []
     for i, (cout, k) in enumerate(branches):
         n = 'br%d' % i
-        txt += _conv_txt(n, 'pre', n, cout, k, pad=(k - 1) // 2)
+        if k == 'p':      # max-pool 3x3 / stride 1 / pad 1 -> 1x1 (the inception `pool -> pool_proj` branch)
+            txt += ('layer { name: "%sp" type: "Pooling" bottom: "pre" top: "%sp" pooling_param { pool: MAX kernel_size: 3 '
+                    'stride: 1 pad: 1 } }\n' % (n, n))
+            txt += _conv_txt(n, n + 'p', n, cout, 1)
+            k = 1
+        else:
+            txt += _conv_txt(n, 'pre', n, cout, k, pad=(k - 1) // 2)
         s = np.sqrt(3.0 / (cin * k * k))
         layers.append((n, 'Convolution', [rs.uniform(-s, s, (cout, cin, k, k)).astype(np.float32),
                                           rs.uniform(-0.2, 0.2, cout).astype(np.float32)]))
         tops.append(n)
-    ctot = sum(c for c, k in branches)
+    ctot = sum(c for c, _k in branches)
     if len(tops) > 1:
         txt += 'layer { name: "cat" type: "Concat" %s top: "cat" }\n' % ' '.join('bottom: "%s"' % t for t in tops)
         last = 'cat'
