@@ -299,6 +299,7 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                     mbar_wait_hint(ae + 8u * sa, pha ^ 1u);
                     __syncwarp();
                     const uint32_t dst = a_ring + sa * pa_stage;
+                    if (PROF && POOL && lane == 0) FCNOD_PROF(0, tile_i, 16 + cc);      // raw patch: stage free, TMA issued
                     if (!elect_one()) {
                     } else if (HALO && p.a_bulk) {
                         mbar_expect_tx(af + 8u * sa, pa_tx);
@@ -461,50 +462,70 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         }
     } else if (POOL && warp < kEpiFirst) {
         // ================= POOL mode: 3x3 / stride 1 / pad 1 max-pool between the raw patch ring and the A ring ==========
-        // thread = (16-byte channel chunk j of the 128-byte pixel row, patch column): it marches down the patch rows with
-        // the horizontal 3-maxima of the two previous rows in registers.  A quarter-warp reads / writes the 8 chunks of one
-        // pixel = one 128-byte line (the swizzle permutes chunks inside the line): conflict-free.
+        // The kernel is shared-memory-bandwidth bound in this mode (raw patch in + out, pooled tile in + out, weights in +
+        // out: ~110 KB per 64-channel chunk at 128 B/clk), so every raw byte is read exactly ONCE: warp w owns the 16-byte
+        // channel chunk w of the 128-byte pixel rows, lane = patch column.  A lane marches down its column keeping the last
+        // two rows (vertical 3-max in registers); the horizontal 3-max takes the two right-hand neighbours by shuffle, once
+        // per OUTPUT row.  32 lanes load 32 columns and produce 30: wider boxes take ceil(BW / 30) passes.  Consecutive
+        // lanes touch consecutive pixel rows, whose swizzle phases differ: loads and stores are bank-conflict free.
         const int pt = (int)threadIdx.x - 32 * (kTcMmaWarp + 1);
-        const uint32_t j = (uint32_t)pt & 7u;
-        const int c0 = pt >> 3, RW = p.BW + 2, rows = p.BH + 2;
+        const uint32_t j = (uint32_t)(pt >> 5);
+        const int RW = p.BW + 2, rows = p.BH + 2;
         auto lds128 = [](uint32_t a) {
             uint4 v;
             asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
             return v;
         };
-        auto max2 = [](uint32_t a, uint32_t b) {
-            const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+        auto max3w = [](uint32_t a, uint32_t b, uint32_t c) {
+            const __nv_bfloat162 r = __hmax2(__hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b)),
+                                             *reinterpret_cast<const __nv_bfloat162*>(&c));
             return *reinterpret_cast<const uint32_t*>(&r);
         };
         auto max3 = [&](const uint4& a, const uint4& b, const uint4& c) {
-            return make_uint4(max2(max2(a.x, b.x), c.x), max2(max2(a.y, b.y), c.y), max2(max2(a.z, b.z), c.z), max2(max2(a.w, b.w), c.w));
+            return make_uint4(max3w(a.x, b.x, c.x), max3w(a.y, b.y, c.y), max3w(a.z, b.z, c.z), max3w(a.w, b.w, c.w));
+        };
+        auto down = [](const uint4& v, int d) {
+            return make_uint4(__shfl_down_sync(0xffffffffu, v.x, d), __shfl_down_sync(0xffffffffu, v.y, d),
+                              __shfl_down_sync(0xffffffffu, v.z, d), __shfl_down_sync(0xffffffffu, v.w, d));
         };
         uint32_t sr = 0, phr = 0, sa = 0, pha = 0;
         TileIter ti;
         ti.init(p);
-        for (; ti.valid(p); ti.next(p)) {
+        const bool stamp = PROF && pt == 0;
+        (void)pt;
+        for (int tile_i = 0; ti.valid(p); ti.next(p), ++tile_i) {
             for (int cc = 0; cc < p.n_cchunks; ++cc) {
+                if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 8 + 4 * cc);
                 mbar_wait(rfull0 + 8u * sr, phr);                  // the raw patch has landed
+                if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 9 + 4 * cc);
                 mbar_wait(aempty0 + 8u * sa, pha ^ 1u);            // the MMA has finished with this A stage
+                if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 10 + 4 * cc);
                 const uint32_t raw = raw_base + sr * p.r_stage_bytes, dst = a_base + sa * p.a_stage_bytes;
-                for (int col = c0; col < p.BW; col += 32) {
-                    uint4 h0 = make_uint4(0, 0, 0, 0), h1 = h0;
-#pragma unroll 2
-                    for (int pr = 0; pr < rows; ++pr) {
-                        const uint32_t r0 = (uint32_t)(pr * RW + col);
-                        const uint4 a = lds128(raw + r0 * 128u + ((j ^ (r0 & 7u)) << 4));
-                        const uint4 b = lds128(raw + (r0 + 1u) * 128u + ((j ^ ((r0 + 1u) & 7u)) << 4));
-                        const uint4 c = lds128(raw + (r0 + 2u) * 128u + ((j ^ ((r0 + 2u) & 7u)) << 4));
-                        const uint4 h = max3(a, b, c);
-                        if (pr >= 2) {
-                            const uint32_t m = (uint32_t)((pr - 2) * p.BW + col);
-                            const uint4 o = max3(h0, h1, h);
-                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
-                                         ::"r"(dst + m * 128u + ((j ^ (m & 7u)) << 4)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+                for (int seg = 0; seg < p.BW; seg += 30) {
+                    const int col = seg + lane;                       // patch column loaded, and output column produced
+                    const bool ld = col < RW, st = lane < 30 && col < p.BW;
+                    // four output rows per pass: their six input rows are loaded back to back (one latency, not six), then
+                    // the vertical maxima, the shuffles and the stores of the four rows overlap
+                    for (int ob = 0; ob < p.BH; ob += 4) {
+                        uint4 a[6];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) {
+                            const uint32_t r0 = (uint32_t)((ob + k) * RW + col);
+                            a[k] = make_uint4(0, 0, 0, 0);
+                            if (ld && ob + k < rows) a[k] = lds128(raw + r0 * 128u + ((j ^ (r0 & 7u)) << 4));
                         }
-                        h0 = h1; h1 = h;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const uint4 v = max3(a[k], a[k + 1], a[k + 2]);    // own column, rows ob+k .. ob+k+2
+                            const uint4 o = max3(v, down(v, 1), down(v, 2));
+                            const uint32_t m = (uint32_t)((ob + k) * p.BW + col);
+                            if (st && ob + k < p.BH)
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                                             ::"r"(dst + m * 128u + ((j ^ (m & 7u)) << 4)), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+                        }
                     }
                 }
+                if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 11 + 4 * cc);
                 // generic-proxy stores -> visible to the tensor core's async-proxy reads, then hand both stages over
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();

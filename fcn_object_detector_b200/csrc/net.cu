@@ -900,7 +900,9 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     {   // spatial box: the fewest boxes per image row, as wide as they can be made equal (224 -> 2 x 112, not 128 + 96)
         TcGeo g;
         g.flat = 0; g.H = ob.H; g.W = ob.W;   // == input size for the stride-1 "same" convolutions; == s2d image size for s2d
-        const int bw_max = 128 - halo_w;
+        // POOL mode: boxes at most 30 pixels wide -- one shuffle pass of the pooling warps (32 lanes load 32 patch
+        // columns, 30 come out) and a squarer box, i.e. less halo: 28x4 needs a 30x6 patch (1.6x), 56x2 a 58x4 one (2.1x)
+        const int bw_max = cw.pool ? 30 : 128 - halo_w;
         g.BW = ceil_div(ob.W, ceil_div(ob.W, bw_max));
         g.PW = g.BW + halo_w;
         g.BH = std::max(1, std::min(ob.H, 128 / g.PW));
@@ -951,10 +953,10 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     // remaining epilogue warps drain at most 128 columns; one issuing thread
     const uint32_t r_tx = cw.pool ? (uint32_t)((geos[0].BW + 2) * (geos[0].BH + 2)) * span : 0;
     const uint32_t r_stage = (uint32_t)align_up(r_tx, 1024);
-    for (int r_st = cw.pool ? 2 : 0; r_st <= (cw.pool ? 4 : 0); ++r_st)
+    for (int r_st = cw.pool ? 2 : 0; r_st <= (cw.pool ? 6 : 0); ++r_st)
     for (size_t gi = 0; gi < geos.size(); ++gi) {
       const TcGeo& G = geos[gi];
-      if ((size_t)r_st * r_stage + 4 * (size_t)G.a_stage > kTcSmemBudget - fixed) continue;
+      if ((size_t)r_st * r_stage + 2 * (size_t)G.a_stage > kTcSmemBudget - fixed) continue;
       const size_t avail = kTcSmemBudget - fixed - (size_t)r_st * r_stage;
       for (int nt = ceil_div(N8, cw.pool ? 128 : 256); nt <= ceil_div(N8, 16); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
@@ -1007,7 +1009,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
                     if (a_st < 2 && !dual) tile += 0.5 * a_bytes / 32.0;                       // no A prefetch across tiles
                     if (cw.pool) {   // per 64-channel chunk: ~4.5 + 1 shared-memory 128-bit accesses per pooled 16-byte piece
                         const double pool = p.n_cchunks * ((double)r_tx + 5.5 * G.a_tx) / 128.0 + 300.0;
-                        tile = std::max(tile, pool) + (r_st < 3 ? 0.25 * pool : 0.0);
+                        tile = std::max(tile, pool) + (r_st < 4 ? 0.1 * (4 - r_st) * pool : 0.0);
                     }
                     Cand c = {(int)gi, nt, BN, a_st, b_st, bt, resident, dual, r_st, b_stage, 0.0};
                     c.cost = rounds * tile + (resident ? (double)BN * Kp * 2 / 32.0 : 0.0);

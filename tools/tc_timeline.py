@@ -40,3 +40,6 @@ for s in steps:
         print('         tap sent  %s' % ([rel(v) for v in out[3, tile, :60] if v][:n]))
         print('         mma start %d tempty-ok %d commit %d' % (rel(out[1, tile, 61]), rel(out[1, tile, 62]), rel(out[1, tile, 63])))
         print('         epi  wait %d tfull-ok %d tmem-released %d done %d' % tuple(rel(out[2, tile, i]) for i in range(4)))
+        if out[2, tile, 8:].any():      # POOL mode: raw-patch TMA issue per chunk; pooling warp 0: start / raw landed / A stage free / pooled
+            print('         raw issue %s' % [rel(v) for v in out[0, tile, 16:32] if v])
+            print('         pool      %s' % [tuple(rel(out[2, tile, 8 + 4 * c + k]) for k in range(4)) for c in range(14) if out[2, tile, 8 + 4 * c]])
