@@ -41,6 +41,8 @@ SIGNATURES = {
     'fcnod_version': (_I, []),
     'fcnod_last_error': (_STR, []),
     'fcnod_device_count': (_I, [C.POINTER(_I)]),
+    'fcnod_host_alloc': (_I, [_SZ, C.POINTER(_P)]),
+    'fcnod_host_free': (_I, [_P]),
     'fcnod_net_create': (_I, [_STR, _STR, _I, _I, C.POINTER(_P)]),
     'fcnod_net_destroy': (_I, [_P]),
     'fcnod_net_reshape': (_I, [_P, _I]),
@@ -66,6 +68,8 @@ SIGNATURES = {
     'fcnod_postnet_scratch_bytes': (_SZ, [_I, _I]),
     'fcnod_postnet_prepare': (_I, [C.POINTER(PostnetParams)]),
     'fcnod_postnet_device': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P, _P, _P]),
+    'fcnod_decode_device': (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(PostnetParams), _I, _P, _P, _P, _P, _P]),
+    'fcnod_decode': (_I, [_P, _P, _I, _I, _I, _I, _I, C.POINTER(PostnetParams), _I, _P, _P, _P, _P]),
     'fcnod_postnet': (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(PostnetParams), _P, _P, _P, _P]),
     'fcnod_preprocess': (_I, [_P, _I, _I, _I, _I, _I, _P]),
     'fcnod_preprocess_device': (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
@@ -126,3 +130,19 @@ def default_postnet_params(**kw):
             raise AttributeError(k)
         setattr(p, k, v)
     return p
+
+
+def pinned_empty(shape, dtype):
+    """numpy array in page-locked host memory (fcnod_host_alloc): copies to / from the device are then true DMA.
+    The memory is released when the array (and every view of it) is garbage collected."""
+    import weakref
+
+    import numpy as np
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) if len(shape) else 1
+    nbytes = max(1, n * dtype.itemsize)
+    p = C.c_void_p()
+    check(lib().fcnod_host_alloc(nbytes, C.byref(p)))
+    buf = (C.c_char * nbytes).from_address(p.value)
+    weakref.finalize(buf, lib().fcnod_host_free, C.c_void_p(p.value))
+    return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)

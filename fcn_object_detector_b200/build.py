@@ -3,8 +3,7 @@
     python -m fcn_object_detector_b200.build [--force]
 
 The shared library is the product's only compute path; nothing here falls back
-to CPU code.  The oracle's C restatement (oracle/c) is built separately by
-__graft_entry__.build().
+to CPU code.
 """
 import os
 import subprocess
@@ -20,7 +19,7 @@ COMMON = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-st
           '-Xcompiler', '-fPIC', '-Xcompiler', '-Wall', '-Xptxas', '-v']
 # parity-critical translation units: no FMA contraction
 SOURCES = [('net.cu', []), ('postnet.cu', ['-fmad=false']), ('layer.cu', ['-fmad=false']),
-           ('preproc.cu', ['-fmad=false']), ('netdef.cpp', [])]
+           ('preproc.cu', ['-fmad=false']), ('netdef.cpp', []), ('workspace.cpp', [])]
 
 
 def _deps():

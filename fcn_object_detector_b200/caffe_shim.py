@@ -51,14 +51,24 @@ def set_precision(name):
 
 
 class Blob(object):
-    """Host mirror of a blob (NCHW float32).  For net blobs `.data` is refreshed lazily."""
+    """Host mirror of a blob (NCHW float32).  For net blobs `.data` is refreshed lazily.
+    pinned=True keeps `.data` in page-locked memory (fcnod_host_alloc), like Caffe's own SyncedMemory in GPU mode:
+    the copies of the layer / detector entry points are then true DMA."""
 
-    def __init__(self, shape=(0,), net=None, name=None):
+    def __init__(self, shape=(0,), net=None, name=None, pinned=False):
         self._net = net
         self._name = name
-        self._data = np.zeros(shape, dtype=np.float32)
+        self._pinned = pinned
+        self._data = self._alloc(shape)
         self._stale = False
         self.diff = None
+
+    def _alloc(self, shape):
+        if self._pinned:
+            a = _lib.pinned_empty(tuple(shape), np.float32)
+            a[...] = 0
+            return a
+        return np.zeros(shape, dtype=np.float32)
 
     @property
     def data(self):
@@ -98,7 +108,7 @@ class Blob(object):
                                       'resizing needs a new prototxt)')
             self._net._reshape(dims[0])
         elif dims != self._data.shape:
-            self._data = np.zeros(dims, dtype=np.float32)
+            self._data = self._alloc(dims)
 
 
 class Net(object):

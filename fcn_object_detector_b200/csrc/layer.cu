@@ -15,6 +15,7 @@
 // the reference's evaluation order, no fast-math, explicit __fdiv_rn.
 #include "common.cuh"
 #include "kernels.h"
+#include "workspace.h"
 
 namespace fcnod {
 namespace {
@@ -243,43 +244,55 @@ __device__ __forceinline__ LabelVals label_vals(int cx, int cy, int s, int bx, i
     return v;
 }
 
-// One thread per grid cell; rects applied in order (later rects overwrite, like the python loop :81-107).
-// NCHW outputs: for a fixed channel consecutive threads write consecutive addresses (coalesced).
+// One thread per V horizontally adjacent grid cells (V = 4: every store is 128 bits; V = 1 when the grid width or the
+// pointers do not allow it); classes in the outer loop, the rects of a class applied in order (later rects overwrite,
+// like the python loop :81-107 -- rects of different classes touch different channels).  Write-only and HBM-bound:
+// (C + 16 C) x gh x gw floats per image, each byte written once (zeros included).
+template <int V>
 __global__ void __launch_bounds__(256) label_raster_kernel(const int32_t* __restrict__ rects, const int32_t* __restrict__ labels,
                                                            const int32_t* __restrict__ nrect, const AugGeom* __restrict__ geom,
                                                            int N, int R, int gh, int gw, int stride, int C,
                                                            float* __restrict__ fg, float* __restrict__ bbox,
                                                            float* __restrict__ size, float* __restrict__ obj,
                                                            float* __restrict__ cvg) {
-    const int plane = gh * gw;
-    const long total = (long)N * plane;
+    const int plane = gh * gw, pv = plane / V;
+    const long total = (long)N * pv;
     for (long t = blockIdx.x * (long)blockDim.x + threadIdx.x; t < total; t += (long)gridDim.x * blockDim.x) {
-        const int n = (int)(t / plane), cell = (int)(t - (long)n * plane);
-        const int j = cell / gw, i = cell - j * gw;
-        const int cx = i * stride, cy = j * stride;
-        float* pfg = fg + (size_t)n * C * plane + cell;
-        float* pb = bbox + (size_t)n * 4 * C * plane + cell;
-        float* ps = size + (size_t)n * 4 * C * plane + cell;
-        float* po = obj + (size_t)n * 4 * C * plane + cell;
-        float* pc = cvg + (size_t)n * 4 * C * plane + cell;
-        for (int c = 0; c < C; ++c) pfg[(size_t)c * plane] = 0.f;
-        for (int c = 0; c < 4 * C; ++c) {
-            pb[(size_t)c * plane] = 0.f; ps[(size_t)c * plane] = 0.f; po[(size_t)c * plane] = 0.f; pc[(size_t)c * plane] = 0.f;
-        }
+        const int n = (int)(t / pv), cell = V * (int)(t - (long)n * pv);
+        const int j = cell / gw, i0 = cell - j * gw;
+        const int cy = j * stride;
         const int nr = geom ? 1 : (nrect ? min(nrect[n], R) : R);
-        for (int q = 0; q < nr; ++q) {
-            int bx, by, bw, bh, lab;
-            if (geom) { bx = geom[n].rect[0]; by = geom[n].rect[1]; bw = geom[n].rect[2]; bh = geom[n].rect[3]; lab = geom[n].label; }
-            else { const int32_t* r = rects + ((size_t)n * R + q) * 4; bx = r[0]; by = r[1]; bw = r[2]; bh = r[3]; lab = labels[(size_t)n * R + q]; }
-            if (lab < 0 || lab >= C) continue;       // python would raise IndexError; here the rect is ignored
-            if (!cell_labelled(cx, cy, stride, bx, by, bw, bh)) continue;
-            const LabelVals v = label_vals(cx, cy, stride, bx, by, bw, bh);
-            const size_t k = (size_t)4 * lab * plane;
-            pb[k] = v.b0; pb[k + plane] = v.b1; pb[k + 2 * (size_t)plane] = v.b2; pb[k + 3 * (size_t)plane] = v.b3;
-            ps[k] = v.s0; ps[k + plane] = v.s1; ps[k + 2 * (size_t)plane] = v.s0; ps[k + 3 * (size_t)plane] = v.s1;
-            po[k] = v.obj; po[k + plane] = v.obj; po[k + 2 * (size_t)plane] = v.obj; po[k + 3 * (size_t)plane] = v.obj;
-            pc[k] = 1.f; pc[k + plane] = 1.f; pc[k + 2 * (size_t)plane] = 1.f; pc[k + 3 * (size_t)plane] = 1.f;
-            pfg[(size_t)lab * plane] = 1.f;
+        for (int c = 0; c < C; ++c) {
+            float vb[4][V], vs[2][V], vo[V], vc[V];
+#pragma unroll
+            for (int v = 0; v < V; ++v) { vb[0][v] = vb[1][v] = vb[2][v] = vb[3][v] = 0.f; vs[0][v] = vs[1][v] = 0.f; vo[v] = 0.f; vc[v] = 0.f; }
+            for (int q = 0; q < nr; ++q) {
+                int bx, by, bw, bh, lab;
+                if (geom) { bx = geom[n].rect[0]; by = geom[n].rect[1]; bw = geom[n].rect[2]; bh = geom[n].rect[3]; lab = geom[n].label; }
+                else { const int32_t* r = rects + ((size_t)n * R + q) * 4; bx = r[0]; by = r[1]; bw = r[2]; bh = r[3]; lab = labels[(size_t)n * R + q]; }
+                if (lab != c) continue;              // labels outside [0, C): python would raise IndexError; here the rect is ignored
+#pragma unroll
+                for (int v = 0; v < V; ++v) {
+                    const int cx = (i0 + v) * stride;
+                    if (!cell_labelled(cx, cy, stride, bx, by, bw, bh)) continue;
+                    const LabelVals L = label_vals(cx, cy, stride, bx, by, bw, bh);
+                    vb[0][v] = L.b0; vb[1][v] = L.b1; vb[2][v] = L.b2; vb[3][v] = L.b3;
+                    vs[0][v] = L.s0; vs[1][v] = L.s1; vo[v] = L.obj; vc[v] = 1.f;
+                }
+            }
+            auto put = [&](float* base, const float (&x)[V]) {
+                if (V == 4) *reinterpret_cast<float4*>(base) = make_float4(x[0], x[1], x[2], x[3]);
+                else base[0] = x[0];
+            };
+            const size_t o1 = ((size_t)n * C + c) * plane + cell, o4 = ((size_t)n * 4 * C + 4 * c) * plane + cell;
+            put(fg + o1, vc);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                put(bbox + o4 + (size_t)k * plane, vb[k]);
+                put(size + o4 + (size_t)k * plane, vs[k & 1]);
+                put(obj + o4 + (size_t)k * plane, vo);
+                put(cvg + o4 + (size_t)k * plane, vc);
+            }
         }
     }
 }
@@ -290,6 +303,20 @@ int grid_1d(long items, int threads) {
     if (b > cap) b = cap;
     if (b < 1) b = 1;
     return (int)b;
+}
+
+void launch_label_raster(const int32_t* rects, const int32_t* labels, const int32_t* nrect, const AugGeom* geom, int N, int R,
+                         int gh, int gw, int stride, int C, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                         cudaStream_t s) {
+    const uintptr_t al = reinterpret_cast<uintptr_t>(fg) | reinterpret_cast<uintptr_t>(bbox) | reinterpret_cast<uintptr_t>(size) |
+                         reinterpret_cast<uintptr_t>(obj) | reinterpret_cast<uintptr_t>(cvg);
+    if (gw % 4 == 0 && al % 16 == 0)
+        label_raster_kernel<4><<<grid_1d((long)N * gh * gw / 4, 256), 256, 0, s>>>(rects, labels, nrect, geom, N, R, gh, gw, stride, C,
+                                                                                    fg, bbox, size, obj, cvg);
+    else
+        label_raster_kernel<1><<<grid_1d((long)N * gh * gw, 256), 256, 0, s>>>(rects, labels, nrect, geom, N, R, gh, gw, stride, C,
+                                                                                fg, bbox, size, obj, cvg);
+    FCNOD_CUDA(cudaGetLastError());
 }
 
 void check_layer_dims(int N, int net_h, int net_w, int stride, int C) {
@@ -312,9 +339,8 @@ int fcnod_label_raster_device(const int32_t* rects, const int32_t* labels, const
     check_layer_dims(N, net_h, net_w, stride, num_classes);
     FCNOD_CHECK(R > 0, "R must be positive");
     const int gh = net_h / stride, gw = net_w / stride;      // Python-2 integer division (:284, layer :60-61)
-    label_raster_kernel<<<grid_1d((long)N * gh * gw, 256), 256, 0, (cudaStream_t)stream>>>(
-        rects, labels, nrect, (const AugGeom*)0, N, R, gh, gw, stride, num_classes, fg, bbox, size, obj, cvg);
-    FCNOD_CUDA(cudaGetLastError());
+    launch_label_raster(rects, labels, nrect, (const AugGeom*)0, N, R, gh, gw, stride, num_classes, fg, bbox, size, obj, cvg,
+                        (cudaStream_t)stream);
     FCNOD_API_END
 }
 
@@ -326,29 +352,24 @@ int fcnod_label_raster(const int32_t* rects, const int32_t* labels, const int32_
     FCNOD_CHECK(R > 0, "R must be positive");
     const int gh = net_h / stride, gw = net_w / stride;
     const size_t plane = (size_t)gh * gw, nfg = (size_t)N * num_classes * plane, n4 = nfg * 4;
-    int32_t *d_r = 0, *d_l = 0, *d_n = 0;
-    float* d_out = 0;
-    struct Guard { void** p[4]; ~Guard() { for (int i = 0; i < 4; ++i) if (*p[i]) cudaFree(*p[i]); } }
-        g = {{(void**)&d_r, (void**)&d_l, (void**)&d_n, (void**)&d_out}};
-    FCNOD_CUDA(cudaMalloc(&d_r, (size_t)N * R * 4 * 4));
-    FCNOD_CUDA(cudaMalloc(&d_l, (size_t)N * R * 4));
-    FCNOD_CUDA(cudaMalloc(&d_out, (nfg + 4 * n4) * 4));
-    FCNOD_CUDA(cudaMemcpy(d_r, rects, (size_t)N * R * 4 * 4, cudaMemcpyHostToDevice));
-    FCNOD_CUDA(cudaMemcpy(d_l, labels, (size_t)N * R * 4, cudaMemcpyHostToDevice));
-    if (nrect) {
-        FCNOD_CUDA(cudaMalloc(&d_n, (size_t)N * 4));
-        FCNOD_CUDA(cudaMemcpy(d_n, nrect, (size_t)N * 4, cudaMemcpyHostToDevice));
-    }
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded((size_t)N * R * 16) + 2 * Workspace::padded((size_t)N * R * 4) + Workspace::padded((nfg + 4 * n4) * 4));
+    int32_t* d_r = ws.take<int32_t>((size_t)N * R * 4);
+    int32_t* d_l = ws.take<int32_t>((size_t)N * R);
+    int32_t* d_n = nrect ? ws.take<int32_t>((size_t)N) : 0;
+    float* d_out = ws.take<float>(nfg + 4 * n4);
+    FCNOD_CUDA(cudaMemcpyAsync(d_r, rects, (size_t)N * R * 4 * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_l, labels, (size_t)N * R * 4, cudaMemcpyHostToDevice, s));
+    if (nrect) FCNOD_CUDA(cudaMemcpyAsync(d_n, nrect, (size_t)N * 4, cudaMemcpyHostToDevice, s));
     float *dfg = d_out, *db = dfg + nfg, *ds = db + n4, *dobj = ds + n4, *dc = dobj + n4;
-    label_raster_kernel<<<grid_1d((long)N * gh * gw, 256), 256>>>(d_r, d_l, d_n, (const AugGeom*)0, N, R, gh, gw, stride,
-                                                                  num_classes, dfg, db, ds, dobj, dc);
-    FCNOD_CUDA(cudaGetLastError());
-    FCNOD_CUDA(cudaDeviceSynchronize());
-    FCNOD_CUDA(cudaMemcpy(fg, dfg, nfg * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(bbox, db, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(size, ds, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(obj, dobj, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(cvg, dc, n4 * 4, cudaMemcpyDeviceToHost));
+    launch_label_raster(d_r, d_l, d_n, (const AugGeom*)0, N, R, gh, gw, stride, num_classes, dfg, db, ds, dobj, dc, s);
+    FCNOD_CUDA(cudaMemcpyAsync(fg, dfg, nfg * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(bbox, db, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(size, ds, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(obj, dobj, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(cvg, dc, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
     FCNOD_API_END
 }
 
@@ -374,9 +395,8 @@ int fcnod_aug_forward_device(const float* data_in, const float* label, const fcn
     else
         aug_resample_kernel<1><<<grid_1d((long)N * net_h * net_w, 256), 256, 0, s>>>(data_in, src_h, src_w, geom, N, net_h, net_w, top_data);
     FCNOD_CUDA(cudaGetLastError());
-    label_raster_kernel<<<grid_1d((long)N * gh * gw, 256), 256, 0, s>>>((const int32_t*)0, (const int32_t*)0, (const int32_t*)0, geom,
-                                                                         N, 1, gh, gw, stride, num_classes, fg, bbox, size, obj, cvg);
-    FCNOD_CUDA(cudaGetLastError());
+    launch_label_raster((const int32_t*)0, (const int32_t*)0, (const int32_t*)0, geom, N, 1, gh, gw, stride, num_classes, fg, bbox,
+                        size, obj, cvg, s);
     FCNOD_API_END
 }
 
@@ -389,33 +409,32 @@ int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_
     const int gh = net_h / stride, gw = net_w / stride;
     const size_t nin = (size_t)N * 3 * src_h * src_w, ntop = (size_t)N * 3 * net_h * net_w;
     const size_t plane = (size_t)gh * gw, nfg = (size_t)N * num_classes * plane, n4 = nfg * 4;
-    float *d_in = 0, *d_label = 0, *d_out = 0;
-    fcnod_aug_draw* d_draw = 0;
-    int32_t* d_rect = 0;
-    void* d_scr = 0;
-    struct Guard { void** p[6]; ~Guard() { for (int i = 0; i < 6; ++i) if (*p[i]) cudaFree(*p[i]); } }
-        g = {{(void**)&d_in, (void**)&d_label, (void**)&d_out, (void**)&d_draw, (void**)&d_rect, &d_scr}};
-    FCNOD_CUDA(cudaMalloc(&d_in, nin * 4));
-    FCNOD_CUDA(cudaMalloc(&d_label, (size_t)N * 5 * 4));
-    FCNOD_CUDA(cudaMalloc(&d_draw, (size_t)N * sizeof(fcnod_aug_draw)));
-    FCNOD_CUDA(cudaMalloc(&d_rect, (size_t)N * 4 * 4));
-    FCNOD_CUDA(cudaMalloc(&d_scr, fcnod_aug_scratch_bytes(N)));
-    FCNOD_CUDA(cudaMalloc(&d_out, (ntop + nfg + 4 * n4) * 4));
-    FCNOD_CUDA(cudaMemcpy(d_in, data_in, nin * 4, cudaMemcpyHostToDevice));
-    FCNOD_CUDA(cudaMemcpy(d_label, label, (size_t)N * 5 * 4, cudaMemcpyHostToDevice));
-    FCNOD_CUDA(cudaMemcpy(d_draw, draws, (size_t)N * sizeof(fcnod_aug_draw), cudaMemcpyHostToDevice));
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded(nin * 4) + Workspace::padded((size_t)N * 5 * 4) + Workspace::padded((size_t)N * sizeof(fcnod_aug_draw)) +
+               Workspace::padded((size_t)N * 16) + Workspace::padded(fcnod_aug_scratch_bytes(N)) +
+               Workspace::padded((ntop + nfg + 4 * n4) * 4));
+    float* d_in = ws.take<float>(nin);
+    float* d_label = ws.take<float>((size_t)N * 5);
+    fcnod_aug_draw* d_draw = ws.take<fcnod_aug_draw>((size_t)N);
+    int32_t* d_rect = ws.take<int32_t>((size_t)N * 4);
+    void* d_scr = ws.take<char>(fcnod_aug_scratch_bytes(N));
+    float* d_out = ws.take<float>(ntop + nfg + 4 * n4);
+    FCNOD_CUDA(cudaMemcpyAsync(d_in, data_in, nin * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_label, label, (size_t)N * 5 * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_draw, draws, (size_t)N * sizeof(fcnod_aug_draw), cudaMemcpyHostToDevice, s));
     float *dtop = d_out, *dfg = dtop + ntop, *db = dfg + nfg, *ds = db + n4, *dobj = ds + n4, *dc = dobj + n4;
     int rc = fcnod_aug_forward_device(d_in, d_label, d_draw, N, src_h, src_w, net_h, net_w, stride, num_classes, dtop, dfg, db,
-                                      ds, dobj, dc, d_rect, d_scr, 0);
+                                      ds, dobj, dc, d_rect, d_scr, s);
     FCNOD_CHECK(rc == 0, fcnod_last_error());
-    FCNOD_CUDA(cudaDeviceSynchronize());
-    FCNOD_CUDA(cudaMemcpy(top_data, dtop, ntop * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(fg, dfg, nfg * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(bbox, db, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(size, ds, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(obj, dobj, n4 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(cvg, dc, n4 * 4, cudaMemcpyDeviceToHost));
-    if (rects_out) FCNOD_CUDA(cudaMemcpy(rects_out, d_rect, (size_t)N * 4 * 4, cudaMemcpyDeviceToHost));
+    FCNOD_CUDA(cudaMemcpyAsync(top_data, dtop, ntop * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(fg, dfg, nfg * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(bbox, db, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(size, ds, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(obj, dobj, n4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(cvg, dc, n4 * 4, cudaMemcpyDeviceToHost, s));
+    if (rects_out) FCNOD_CUDA(cudaMemcpyAsync(rects_out, d_rect, (size_t)N * 4 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
     FCNOD_API_END
 }
 

@@ -27,6 +27,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "workspace.h"
 
 namespace fcnod {
 namespace {
@@ -309,6 +310,86 @@ __global__ void __launch_bounds__(kThreads) decode_group_kernel(const float* __r
     if (threadIdx.x == 0) cls_cnt[b * ncls + cls] = nout;
 }
 
+// ---- standalone decode = gridbox_to_boxes (scripts/fcn_object_detector.py:357-394) for every (frame, class) ------
+// threshold -> ordered compaction -> float64 boxes, no clustering.  HBM-bound: every coverage / bbox value of the used
+// rows is read exactly once with 128-bit loads (a thread owns 4 consecutive cells), candidates leave as 32-byte box
+// records + (cell, score).  One CTA of 256 threads per (frame, class): 784 cells = 196 threads x 4 cells.
+constexpr int kDecThreads = 256;
+__global__ void __launch_bounds__(kDecThreads) decode_kernel(const float* __restrict__ coverage, const float* __restrict__ bboxes,
+                                                            int c_cvg, int c_bbox, int gh, int gw, PostParams P, int cap,
+                                                            double* __restrict__ out_boxes /*[B][ncls][cap][4]*/,
+                                                            int32_t* __restrict__ out_cell /*[B][ncls][cap]*/,
+                                                            float* __restrict__ out_score /*[B][ncls][cap]*/,
+                                                            int32_t* __restrict__ out_count /*[B][ncls]*/) {
+    __shared__ int warp_tot[kDecThreads / 32];
+    const int cls = blockIdx.x, b = blockIdx.y, ncls = gridDim.x;
+    const int cch = cls + (P.skip_bg ? 1 : 0);
+    const int plane = gh * gw, ncell = P.rows_used * gw;
+    const float* cv = coverage + ((size_t)b * c_cvg + cch) * plane;
+    const float* bb = bboxes + ((size_t)b * c_bbox + 4 * cls) * plane;
+    const size_t slot = (size_t)b * ncls + cls;
+    double* ob = out_boxes + slot * cap * 4;
+    int32_t* oc = out_cell + slot * cap;
+    float* os = out_score + slot * cap;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vec = (plane % 4 == 0) && ((reinterpret_cast<uintptr_t>(coverage) | reinterpret_cast<uintptr_t>(bboxes)) % 16 == 0);
+    int n = 0;
+    for (int base = 0; base < ncell; base += 4 * kDecThreads) {
+        const int i0 = base + 4 * (int)threadIdx.x;
+        float c[4], v[4][4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { c[k] = -INFINITY; v[0][k] = v[1][k] = v[2][k] = v[3][k] = 0.f; }
+        if (vec && i0 + 3 < ncell) {
+            const float4 c4 = __ldg(reinterpret_cast<const float4*>(cv + i0));
+            c[0] = c4.x; c[1] = c4.y; c[2] = c4.z; c[3] = c4.w;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(bb + (size_t)q * plane + i0));
+                v[q][0] = t.x; v[q][1] = t.y; v[q][2] = t.z; v[q][3] = t.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (i0 + k < ncell) {
+                    c[k] = __ldg(cv + i0 + k);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[q][k] = __ldg(bb + (size_t)q * plane + i0 + k);
+                }
+        }
+        int cnt = 0;
+        bool f[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { f[k] = i0 + k < ncell && c[k] >= P.prob_thresh; cnt += f[k] ? 1 : 0; }
+        // exclusive scan of the per-thread counts: warp shuffle scan + cross-warp totals (order = row-major cell order)
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int wbase = 0, tot = 0;
+#pragma unroll
+        for (int w = 0; w < kDecThreads / 32; ++w) { const int t = warp_tot[w]; if (w < warp) wbase += t; tot += t; }
+        __syncthreads();
+        int k_out = n + wbase + incl - cnt;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (f[k]) {
+                if (k_out < cap) {
+                    const int i = i0 + k, y = i / gw, x = i - y * gw;
+                    const double mx = (double)(x * P.cell_w), my = (double)(y * P.cell_h);
+                    double2* o2 = reinterpret_cast<double2*>(ob + (size_t)k_out * 4);
+                    o2[0] = make_double2((double)v[0][k] + mx, (double)v[1][k] + my);
+                    o2[1] = make_double2((double)v[2][k] + mx, (double)v[3][k] + my);
+                    oc[k_out] = i;
+                    os[k_out] = c[k];
+                }
+                ++k_out;
+            }
+        n += tot;
+    }
+    if (threadIdx.x == 0) out_count[slot] = n;          // untruncated; rows beyond `cap` are not stored
+}
+
 __global__ void assemble_kernel(const int32_t* __restrict__ cls_det, const int32_t* __restrict__ cls_cnt, int B, int ncls,
                                 const int32_t* __restrict__ src_hw, int net_w, int net_h, int32_t* __restrict__ out_det,
                                 int32_t* __restrict__ out_label, int32_t* __restrict__ out_weight,
@@ -464,6 +545,30 @@ int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int 
     FCNOD_API_END
 }
 
+int fcnod_decode_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                        const fcnod_postnet_params* p, int cap, double* out_boxes, int32_t* out_cell, float* out_score,
+                        int32_t* out_count, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(coverage && bboxes && p && out_boxes && out_cell && out_score && out_count, "null argument");
+    FCNOD_CHECK(B > 0 && c_cvg > 0 && gh > 0 && gw > 0 && cap > 0, "decode: bad dimensions");
+    FCNOD_CHECK(p->stride > 0 && p->net_w >= p->stride && p->net_h >= p->stride, "decode: bad stride / net size");
+    const int ncls = c_cvg - (p->skip_background ? 1 : 0);
+    FCNOD_CHECK(ncls > 0, "decode: no foreground coverage channel");
+    FCNOD_CHECK(c_bbox >= 4 * ncls, "decode: bboxes has fewer than 4 channels per foreground class");
+    FCNOD_CHECK(B <= 65535, "decode: at most 65535 frames per launch");
+    PostParams P;
+    memset(&P, 0, sizeof(P));
+    P.prob_thresh = p->prob_thresh;
+    const int grid_sz_x = p->net_w / p->stride, grid_sz_y = p->net_h / p->stride;
+    P.cell_w = p->net_w / grid_sz_x; P.cell_h = p->net_h / grid_sz_y;
+    P.rows_used = std::min(gh, std::min(grid_sz_y, grid_sz_x));
+    P.skip_bg = p->skip_background ? 1 : 0;
+    decode_kernel<<<dim3(ncls, B), kDecThreads, 0, (cudaStream_t)stream>>>(coverage, bboxes, c_cvg, c_bbox, gh, gw, P, cap, out_boxes,
+                                                                          out_cell, out_score, out_count);
+    FCNOD_CUDA(cudaGetLastError());
+    FCNOD_API_END
+}
+
 int fcnod_postnet(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                   const int32_t* src_hw, const fcnod_postnet_params* p, int32_t* out_det, int32_t* out_label,
                   int32_t* out_weight, int32_t* out_count) {
@@ -471,35 +576,60 @@ int fcnod_postnet(const float* coverage, const float* bboxes, int B, int c_cvg, 
     FCNOD_CHECK(coverage && bboxes && p && out_det && out_label && out_weight && out_count, "null argument");
     FCNOD_CHECK(B > 0 && c_cvg > 0 && c_bbox > 0 && gh > 0 && gw > 0, "postnet: bad dimensions");
     const size_t ncv = (size_t)B * c_cvg * gh * gw, nbb = (size_t)B * c_bbox * gh * gw;
-    float *d_cv = 0, *d_bb = 0;
-    int32_t *d_hw = 0, *d_det = 0, *d_lab = 0, *d_w = 0, *d_cnt = 0;
-    void* d_scr = 0;
-    struct Guard {
-        void** p[8]; int n;
-        ~Guard() { for (int i = 0; i < n; ++i) if (*p[i]) cudaFree(*p[i]); }
-    } g = {{(void**)&d_cv, (void**)&d_bb, (void**)&d_hw, (void**)&d_det, (void**)&d_lab, (void**)&d_w, (void**)&d_cnt, &d_scr}, 8};
-    FCNOD_CUDA(cudaMalloc(&d_cv, ncv * 4));
-    FCNOD_CUDA(cudaMalloc(&d_bb, nbb * 4));
-    FCNOD_CUDA(cudaMalloc(&d_det, (size_t)B * FCNOD_MAX_DET * 5 * 4));
-    FCNOD_CUDA(cudaMalloc(&d_lab, (size_t)B * FCNOD_MAX_DET * 4));
-    FCNOD_CUDA(cudaMalloc(&d_w, (size_t)B * FCNOD_MAX_DET * 4));
-    FCNOD_CUDA(cudaMalloc(&d_cnt, (size_t)B * 4));
-    FCNOD_CUDA(cudaMalloc(&d_scr, postnet_scratch_bytes(B, c_cvg)));
-    FCNOD_CUDA(cudaMemcpy(d_cv, coverage, ncv * 4, cudaMemcpyHostToDevice));
-    FCNOD_CUDA(cudaMemcpy(d_bb, bboxes, nbb * 4, cudaMemcpyHostToDevice));
-    if (src_hw) {
-        FCNOD_CUDA(cudaMalloc(&d_hw, (size_t)B * 2 * 4));
-        FCNOD_CUDA(cudaMemcpy(d_hw, src_hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice));
-    }
-    FCNOD_CUDA(cudaMemset(d_det, 0, (size_t)B * FCNOD_MAX_DET * 5 * 4));
-    FCNOD_CUDA(cudaMemset(d_lab, 0, (size_t)B * FCNOD_MAX_DET * 4));
-    FCNOD_CUDA(cudaMemset(d_w, 0, (size_t)B * FCNOD_MAX_DET * 4));
-    postnet_launch(d_cv, d_bb, B, c_cvg, c_bbox, gh, gw, d_hw, *p, d_scr, d_det, d_lab, d_w, d_cnt, 0);
-    FCNOD_CUDA(cudaDeviceSynchronize());
-    FCNOD_CUDA(cudaMemcpy(out_det, d_det, (size_t)B * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(out_label, d_lab, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(out_weight, d_w, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost));
-    FCNOD_CUDA(cudaMemcpy(out_count, d_cnt, (size_t)B * 4, cudaMemcpyDeviceToHost));
+    const size_t M = FCNOD_MAX_DET, scr = postnet_scratch_bytes(B, c_cvg);
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded(ncv * 4) + Workspace::padded(nbb * 4) + Workspace::padded((size_t)B * 2 * 4) +
+               Workspace::padded((size_t)B * (M * 7 + 1) * 4) + Workspace::padded(scr));
+    float* d_cv = ws.take<float>(ncv);
+    float* d_bb = ws.take<float>(nbb);
+    int32_t* d_hw = src_hw ? ws.take<int32_t>((size_t)B * 2) : 0;
+    int32_t* d_det = ws.take<int32_t>((size_t)B * (M * 7 + 1));      // det | label | weight | count, contiguous
+    int32_t* d_lab = d_det + (size_t)B * M * 5;
+    int32_t* d_w = d_lab + (size_t)B * M;
+    int32_t* d_cnt = d_w + (size_t)B * M;
+    void* d_scr = ws.take<char>(scr);
+    FCNOD_CUDA(cudaMemcpyAsync(d_cv, coverage, ncv * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_bb, bboxes, nbb * 4, cudaMemcpyHostToDevice, s));
+    if (src_hw) FCNOD_CUDA(cudaMemcpyAsync(d_hw, src_hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemsetAsync(d_det, 0, (size_t)B * (M * 7 + 1) * 4, s));
+    postnet_launch(d_cv, d_bb, B, c_cvg, c_bbox, gh, gw, d_hw, *p, d_scr, d_det, d_lab, d_w, d_cnt, s);
+    FCNOD_CUDA(cudaMemcpyAsync(out_det, d_det, (size_t)B * M * 5 * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_label, d_lab, (size_t)B * M * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_weight, d_w, (size_t)B * M * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_count, d_cnt, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
+    FCNOD_API_END
+}
+
+int fcnod_decode(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                 const fcnod_postnet_params* p, int cap, double* out_boxes, int32_t* out_cell, float* out_score,
+                 int32_t* out_count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(coverage && bboxes && p && out_boxes && out_cell && out_score && out_count, "null argument");
+    FCNOD_CHECK(B > 0 && c_cvg > 0 && c_bbox > 0 && gh > 0 && gw > 0 && cap > 0, "decode: bad dimensions");
+    const int ncls = c_cvg - (p->skip_background ? 1 : 0);
+    FCNOD_CHECK(ncls > 0, "decode: no foreground coverage channel");
+    const size_t ncv = (size_t)B * c_cvg * gh * gw, nbb = (size_t)B * c_bbox * gh * gw, slots = (size_t)B * ncls;
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded(ncv * 4) + Workspace::padded(nbb * 4) + Workspace::padded(slots * cap * 32) +
+               2 * Workspace::padded(slots * cap * 4) + Workspace::padded(slots * 4));
+    float* d_cv = ws.take<float>(ncv);
+    float* d_bb = ws.take<float>(nbb);
+    double* d_box = ws.take<double>(slots * cap * 4);
+    int32_t* d_cell = ws.take<int32_t>(slots * cap);
+    float* d_score = ws.take<float>(slots * cap);
+    int32_t* d_cnt = ws.take<int32_t>(slots);
+    FCNOD_CUDA(cudaMemcpyAsync(d_cv, coverage, ncv * 4, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_bb, bboxes, nbb * 4, cudaMemcpyHostToDevice, s));
+    int rc = fcnod_decode_device(d_cv, d_bb, B, c_cvg, c_bbox, gh, gw, p, cap, d_box, d_cell, d_score, d_cnt, s);
+    FCNOD_CHECK(rc == 0, fcnod_last_error());
+    FCNOD_CUDA(cudaMemcpyAsync(out_boxes, d_box, slots * cap * 32, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_cell, d_cell, slots * cap * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_score, d_score, slots * cap * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(out_count, d_cnt, slots * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
     FCNOD_API_END
 }
 

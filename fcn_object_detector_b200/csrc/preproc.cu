@@ -9,6 +9,7 @@
 // Pass 2: normalise in float64 and resample; one thread per 4 output pixels, float4 stores.
 #include "common.cuh"
 #include "kernels.h"
+#include "workspace.h"
 
 namespace fcnod {
 namespace {
@@ -203,19 +204,17 @@ int fcnod_preprocess(const uint8_t* images, int B, int src_h, int src_w, int net
     FCNOD_API_BEGIN
     FCNOD_CHECK(images && data_out, "null argument");
     FCNOD_CHECK(B > 0 && src_h > 0 && src_w > 0 && net_h > 0 && net_w > 0, "preprocess: bad dimensions");
-    uint8_t* d_img = 0;
-    float* d_out = 0;
-    void* d_scr = 0;
-    struct Guard { void** p[3]; ~Guard() { for (int i = 0; i < 3; ++i) if (*p[i]) cudaFree(*p[i]); } }
-        g = {{(void**)&d_img, (void**)&d_out, &d_scr}};
     const size_t nin = (size_t)B * src_h * src_w * 3, nout = (size_t)B * 3 * net_h * net_w;
-    FCNOD_CUDA(cudaMalloc(&d_img, nin));
-    FCNOD_CUDA(cudaMalloc(&d_out, nout * 4));
-    FCNOD_CUDA(cudaMalloc(&d_scr, (size_t)B * 6 * 4));
-    FCNOD_CUDA(cudaMemcpy(d_img, images, nin, cudaMemcpyHostToDevice));
-    preprocess_launch(d_img, B, src_h, src_w, net_h, net_w, d_out, d_scr, 0);
-    FCNOD_CUDA(cudaDeviceSynchronize());
-    FCNOD_CUDA(cudaMemcpy(data_out, d_out, nout * 4, cudaMemcpyDeviceToHost));
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded(nin) + Workspace::padded(nout * 4) + Workspace::padded((size_t)B * 6 * 4));
+    uint8_t* d_img = ws.take<uint8_t>(nin);
+    float* d_out = ws.take<float>(nout);
+    int* d_scr = ws.take<int>((size_t)B * 6);
+    FCNOD_CUDA(cudaMemcpyAsync(d_img, images, nin, cudaMemcpyHostToDevice, s));
+    preprocess_launch(d_img, B, src_h, src_w, net_h, net_w, d_out, d_scr, s);
+    FCNOD_CUDA(cudaMemcpyAsync(data_out, d_out, nout * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
     FCNOD_API_END
 }
 

@@ -220,6 +220,45 @@ def postnet(coverage, bboxes, src_hw=None, overflow=None, **params):
     return _unpack(det, lab, wgt, cnt, weights=True, overflow=overflow)
 
 
+def gridbox_to_boxes(net_cvg, net_boxes, prob_thresh=0.5, im_w=448, im_h=448, stride=16):
+    """`gridbox_to_boxes` of scripts/fcn_object_detector.py:357-394 on the device (fcnod_decode), one class map:
+    net_cvg (G,G) float32, net_boxes (4,G,G) float32.  Returns (boxes (n,4) float64 [x1,y1,x2,y2],
+    cvgs (n,3) [x, y, score], mask (rows_used, G) bool) exactly as the reference does."""
+    net_cvg = np.ascontiguousarray(net_cvg, dtype=np.float32)
+    net_boxes = np.ascontiguousarray(net_boxes, dtype=np.float32)
+    gh, gw = net_cvg.shape
+    cap = gh * gw
+    boxes = np.zeros((cap, 4), np.float64); cell = np.zeros((cap,), np.int32)
+    score = np.zeros((cap,), np.float32); cnt = np.zeros((1,), np.int32)
+    p = _lib.default_postnet_params(prob_thresh=float(prob_thresh), net_w=int(im_w), net_h=int(im_h), stride=int(stride),
+                                    skip_background=0)
+    _lib.check(_lib.lib().fcnod_decode(_lib.ptr(net_cvg), _lib.ptr(net_boxes), 1, 1, 4, gh, gw, C.byref(p), cap,
+                                       _lib.ptr(boxes), _lib.ptr(cell), _lib.ptr(score), _lib.ptr(cnt)))
+    n = int(cnt[0])
+    rows_used = min(gh, int(im_h // stride), int(im_w // stride))
+    mask = np.zeros((rows_used, gw), bool)
+    y, x = np.divmod(cell[:n], gw)
+    mask[y, x] = True
+    cvgs = np.transpose(np.vstack((x, y, score[:n].astype(np.float64)))) if n else np.zeros((0, 3))
+    return boxes[:n].copy(), cvgs, mask
+
+
+def decode_batch(coverage, bboxes, cap=None, **params):
+    """fcnod_decode on a batch: coverage (B,Cc,G,G), bboxes (B,Cb,G,G).  Returns (boxes (B,ncls,cap,4) float64,
+    cell (B,ncls,cap) int32, score (B,ncls,cap) float32, count (B,ncls) int32)."""
+    coverage = np.ascontiguousarray(coverage, dtype=np.float32)
+    bboxes = np.ascontiguousarray(bboxes, dtype=np.float32)
+    B, Cc, gh, gw = coverage.shape
+    p = _lib.default_postnet_params(**params)
+    ncls = Cc - (1 if p.skip_background else 0)
+    cap = gh * gw if cap is None else int(cap)
+    boxes = np.zeros((B, ncls, cap, 4), np.float64); cell = np.zeros((B, ncls, cap), np.int32)
+    score = np.zeros((B, ncls, cap), np.float32); cnt = np.zeros((B, ncls), np.int32)
+    _lib.check(_lib.lib().fcnod_decode(_lib.ptr(coverage), _lib.ptr(bboxes), B, Cc, bboxes.shape[1], gh, gw, C.byref(p), cap,
+                                       _lib.ptr(boxes), _lib.ptr(cell), _lib.ptr(score), _lib.ptr(cnt)))
+    return boxes, cell, score, cnt
+
+
 def preprocess(images, net_h=448, net_w=448):
     """Prelude alone: (B,H,W,3) uint8 BGR -> (B,3,net_h,net_w) float32."""
     images = np.ascontiguousarray(images, dtype=np.uint8)

@@ -44,6 +44,10 @@ extern "C" {
 typedef struct fcnod_net fcnod_net;
 
 int fcnod_version(void);
+/* Page-locked host memory for the buffers handed to the HOST-buffer entry points: their copies are then true DMA at
+ * full PCIe rate (Caffe's own blobs are page-locked in GPU mode; numpy arrays are not). */
+int fcnod_host_alloc(size_t bytes, void** out);
+int fcnod_host_free(void* p);
 const char* fcnod_last_error(void);
 int fcnod_device_count(int* count);
 
@@ -121,7 +125,19 @@ int fcnod_postnet_device(const float* coverage, const float* bboxes, int B, int 
                          const int32_t* src_hw, const fcnod_postnet_params* p, void* scratch,
                          int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count,
                          void* stream);
-/* Same with HOST buffers (allocates, copies, synchronises). */
+/* Decode alone = gridbox_to_boxes (scripts/fcn_object_detector.py:357-394) for every (frame, foreground class):
+ * coverage >= prob_thresh, candidates in row-major cell order, boxes = float32 regressor outputs + integer cell
+ * origin evaluated in float64 (x1, y1, x2, y2), no clustering.  Device buffers:
+ * out_boxes [B][ncls][cap][4] float64, out_cell [B][ncls][cap] int32 (cell index y*gw + x, i.e. the `mask`),
+ * out_score [B][ncls][cap] float32 (the coverage value), out_count [B][ncls] int32 = candidates found (may exceed
+ * cap: only the first cap are stored).  ncls = c_cvg - skip_background.  Async on `stream`. */
+int fcnod_decode_device(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                        const fcnod_postnet_params* p, int cap, double* out_boxes, int32_t* out_cell, float* out_score,
+                        int32_t* out_count, void* stream);
+int fcnod_decode(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
+                 const fcnod_postnet_params* p, int cap, double* out_boxes, int32_t* out_cell, float* out_score,
+                 int32_t* out_count);   /* HOST buffers */
+/* Same with HOST buffers (copies in / out through the calling thread's cached device workspace, synchronises). */
 int fcnod_postnet(const float* coverage, const float* bboxes, int B, int c_cvg, int c_bbox, int gh, int gw,
                   const int32_t* src_hw, const fcnod_postnet_params* p,
                   int32_t* out_det, int32_t* out_label, int32_t* out_weight, int32_t* out_count);

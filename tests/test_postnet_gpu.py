@@ -129,3 +129,30 @@ def test_overflow_is_reported_not_silent():
         assert np.array_equal(got[b][0], ob[:k]) and np.array_equal(got[b][1], ol[:k])
     assert totals[0] == 196 and totals[1] == 140 and totals[2] == 10
     assert overflow == [(0, 196), (1, 140)], overflow
+
+
+def test_gridbox_to_boxes_matches_reference_function():
+    """Standalone decode kernel = gridbox_to_boxes (fcn_object_detector.py:357-394): boxes (float64), cvgs and mask
+    bit-exact against the oracle, at stride 16, at the literal stride 8 (grid 56 clamped to the 28-row map) and on a
+    map whose width is not a multiple of 4 (scalar loads)."""
+    from fcn_object_detector_b200.detector import decode_batch, gridbox_to_boxes
+    rs = np.random.RandomState(17)
+    for (g, stride, thr) in ((28, 16, 0.5), (28, 8, 0.5), (28, 16, 0.0), (28, 16, 1.1), (27, 16, 0.4), (14, 32, 0.6)):
+        cvg = rs.uniform(0, 1, (g, g)).astype(np.float32)
+        box = rs.normal(0, 20, (4, g, g)).astype(np.float32)
+        eb, ec, em = postnet_ref.gridbox_to_boxes(cvg, box, thr, 448, 448, stride)
+        gb, gc, gm = gridbox_to_boxes(cvg, box, thr, 448, 448, stride)
+        assert gb.dtype == np.float64 and gb.shape == eb.shape, (g, stride, thr, gb.shape, eb.shape)
+        assert np.array_equal(gb.view(np.uint64), np.ascontiguousarray(eb, np.float64).view(np.uint64))
+        assert np.array_equal(gc, np.asarray(ec, np.float64).reshape(-1, 3))
+        assert np.array_equal(gm, em)
+    # batch form, several classes, capped output: counts are untruncated, the first `cap` rows are stored
+    cov = rs.uniform(0, 1, (5, 4, 28, 28)).astype(np.float32)
+    bb = rs.normal(0, 20, (5, 16, 28, 28)).astype(np.float32)
+    boxes, cell, score, cnt = decode_batch(cov, bb, cap=100, prob_thresh=0.5)
+    for b in range(5):
+        for c in range(3):
+            eb, ec, em = postnet_ref.gridbox_to_boxes(cov[b, c + 1], bb[b, 4 * c:4 * c + 4], 0.5, 448, 448, 16)
+            assert cnt[b, c] == len(eb) > 100
+            assert np.array_equal(boxes[b, c], eb[:100])
+            assert np.array_equal(score[b, c], np.asarray(ec)[:100, 2].astype(np.float32))
