@@ -81,6 +81,8 @@ SIGNATURES = {
                                  C.POINTER(_P), C.POINTER(_P), _P]),
     'fcnod_detect_graph_build': (_I, [_P, _P, _I, C.POINTER(PostnetParams), _P]),
     'fcnod_detect_graph_launch': (_I, [_P, _P]),
+    'fcnod_caffemodel_blob': (_I, [_STR, _STR, _I, C.POINTER(_I * 4), C.POINTER(_I), _P, _SZ]),
+    'fcnod_datum_decode': (_I, [_P, _SZ, C.POINTER(_I * 3), C.POINTER(_I), _P, _SZ]),
     'fcnod_label_raster_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P]),
     'fcnod_label_raster': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     'fcnod_aug_scratch_bytes': (_SZ, [_I]),

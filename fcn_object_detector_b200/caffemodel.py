@@ -3,7 +3,7 @@
 The upstream launch file points at `models/snapshot_iter_1000.caffemodel`
 (/root/reference/launch/fcn_object_detector.launch:8) which is not shipped
 (/root/reference/.MISSING_LARGE_BLOBS:1).  The product reads such files in C++
-(csrc/caffemodel.cpp); this module only *writes* them, so that tests, smoke and
+(csrc/netdef.cpp); this module only *writes* them, so that tests, smoke and
 bench can synthesise weights with the fillers the prototxt declares (xavier
 weights, constant bias -- /root/reference/models/deploy.prototxt:38-45).
 
@@ -31,8 +31,15 @@ def _ld(field, payload):
     return _varint((field << 3) | 2) + _varint(len(payload)) + payload
 
 
-def _blob(arr, legacy=False):
+RAW_TYPES = {'double': (0, '<f8'), 'float': (1, '<f4'), 'half': (2, '<f2')}     # NVCaffe enum Type [ext]
+
+
+def _blob(arr, legacy=False, raw=None):
     arr = np.ascontiguousarray(arr, dtype='<f4')
+    if raw is not None:       # NVCaffe: shape=7, raw_data_type=10 (varint), raw_data=12 (bytes)
+        code, dt = RAW_TYPES[raw]
+        shape = _ld(1, b''.join(_varint(d) for d in arr.shape))
+        return _ld(7, shape) + _varint((10 << 3) | 0) + _varint(code) + _ld(12, arr.astype(dt).tobytes())
     if legacy:
         dims = list(arr.shape)
         dims = [1] * (4 - len(dims)) + dims
@@ -42,13 +49,14 @@ def _blob(arr, legacy=False):
     return _ld(7, shape) + _ld(5, arr.tobytes())
 
 
-def write_caffemodel(path, layers, net_name='fcn_detector', legacy_shape=False):
-    """layers: iterable of (name, type, [ndarray blobs])."""
+def write_caffemodel(path, layers, net_name='fcn_detector', legacy_shape=False, raw=None):
+    """layers: iterable of (name, type, [ndarray blobs]).  raw = 'float' | 'half' | 'double' writes the blobs the way
+    NVCaffe snapshots do (raw_data_type + raw_data instead of the packed float `data` field)."""
     body = _ld(1, net_name.encode())
     for name, typ, blobs in layers:
         lp = _ld(1, name.encode()) + _ld(2, typ.encode())
         for b in blobs:
-            lp += _ld(7, _blob(b, legacy_shape))
+            lp += _ld(7, _blob(b, legacy_shape, raw))
         body += _ld(100, lp)
     with open(path, 'wb') as f:
         f.write(body)

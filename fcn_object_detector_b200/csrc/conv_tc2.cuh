@@ -493,6 +493,23 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         ti.init(p);
         const bool stamp = PROF && pt == 0;
         (void)pt;
+        // Fast path (boxes up to 30 x 4, i.e. every launch of the deploy net): one pass, and the swizzled offsets of the six
+        // loads and four stores of a lane are the same for every chunk of every tile -- computed once.  Lanes / rows outside
+        // the patch read a clamped address (their results are never stored).
+        const bool fast = p.BW <= 30 && p.BH <= 4;
+        uint32_t loff[6], soff[4];
+        bool sp[4];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const uint32_t r0 = (uint32_t)(min(k, rows - 1) * RW + min(lane, RW - 1));
+            loff[k] = r0 * 128u + ((j ^ (r0 & 7u)) << 4);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t m = (uint32_t)(k * p.BW + lane);
+            soff[k] = m * 128u + ((j ^ (m & 7u)) << 4);
+            sp[k] = lane < p.BW && k < p.BH;
+        }
         for (int tile_i = 0; ti.valid(p); ti.next(p), ++tile_i) {
             for (int cc = 0; cc < p.n_cchunks; ++cc) {
                 if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 8 + 4 * cc);
@@ -501,6 +518,23 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 mbar_wait(aempty0 + 8u * sa, pha ^ 1u);            // the MMA has finished with this A stage
                 if (stamp && cc < 14) FCNOD_PROF(2, tile_i, 10 + 4 * cc);
                 const uint32_t raw = raw_base + sr * p.r_stage_bytes, dst = a_base + sa * p.a_stage_bytes;
+                if (fast) {
+                    uint4 a[6];
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) a[k] = lds128(raw + loff[k]);
+                    uint4 v[4], h1[4], h2[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) v[k] = max3(a[k], a[k + 1], a[k + 2]);       // own column, rows k .. k+2
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { h1[k] = down(v[k], 1); h2[k] = down(v[k], 2); }   // 32 shuffles in flight
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint4 o = max3(v[k], h1[k], h2[k]);
+                        if (sp[k])
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                                         ::"r"(dst + soff[k]), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+                    }
+                } else
                 for (int seg = 0; seg < p.BW; seg += 30) {
                     const int col = seg + lane;                       // patch column loaded, and output column produced
                     const bool ld = col < RW, st = lane < 30 && col < p.BW;

@@ -1725,6 +1725,40 @@ int fcnod_device_count(int* count) {
     FCNOD_API_END
 }
 
+int fcnod_caffemodel_blob(const char* caffemodel_path, const char* layer, int index, int dims[4], int* ndim, float* out,
+                          size_t out_count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(caffemodel_path && layer && dims && ndim, "null argument");
+    const WeightMap w = read_caffemodel(caffemodel_path);
+    WeightMap::const_iterator it = w.find(layer);
+    FCNOD_CHECK(it != w.end(), std::string("caffemodel has no blobs for layer '") + layer + "'");
+    FCNOD_CHECK(index >= 0 && index < (int)it->second.size(), "blob index out of range");
+    const HostBlob& b = it->second[index];
+    FCNOD_CHECK(b.shape.size() <= 4, "blob has more than 4 dimensions");
+    *ndim = (int)b.shape.size();
+    for (int i = 0; i < 4; ++i) dims[i] = i < *ndim ? b.shape[i] : 1;
+    if (out) {
+        FCNOD_CHECK(out_count == b.data.size(), "caffemodel_blob: out_count does not match the blob");
+        memcpy(out, b.data.data(), b.data.size() * 4);
+    }
+    FCNOD_API_END
+}
+
+int fcnod_datum_decode(const uint8_t* buf, size_t len, int dims[3], int* label, float* out, size_t out_count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(buf && dims, "null argument");
+    const Datum d = decode_datum(buf, len);
+    dims[0] = d.channels; dims[1] = d.height; dims[2] = d.width;
+    if (label) *label = d.has_label ? d.label : -1;
+    if (out) {
+        const size_t n = (size_t)d.channels * d.height * d.width;
+        FCNOD_CHECK(out_count == n, "datum_decode: out_count must equal channels x height x width");
+        if (!d.floats.empty()) memcpy(out, d.floats.data(), n * 4);
+        else for (size_t i = 0; i < n; ++i) out[i] = (float)d.bytes[i];
+    }
+    FCNOD_API_END
+}
+
 int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int device, int precision, fcnod_net** out) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(out, "out is null");

@@ -166,6 +166,18 @@ NetDef parse_prototxt_text(const std::string& text) {
             d.pad = (int)p->num("pad", 0);
             d.bias_term = p->str("bias_term", "true") != "false";
             if (d.num_output <= 0) throw std::runtime_error("prototxt: '" + d.name + "' num_output missing");
+            // square kernels, one stride / pad, dense, ungrouped -- everything models/deploy.prototxt uses.  Anything else
+            // would silently compute a different convolution: refuse it.
+            static const char* const unsupported[] = {"kernel_h", "kernel_w", "pad_h", "pad_w", "stride_h", "stride_w"};
+            for (size_t u = 0; u < sizeof(unsupported) / sizeof(unsupported[0]); ++u)
+                if (p->has(unsupported[u]))
+                    throw std::runtime_error("prototxt: '" + d.name + "': convolution_param." + unsupported[u] + " is not supported (square kernels only)");
+            if (p->all("kernel_size").size() > 1 || p->all("stride").size() > 1 || p->all("pad").size() > 1)
+                throw std::runtime_error("prototxt: '" + d.name + "': per-axis kernel_size / stride / pad lists are not supported");
+            if ((int)p->num("dilation", 1) != 1) throw std::runtime_error("prototxt: '" + d.name + "': dilation != 1 is not supported");
+            if ((int)p->num("group", 1) != 1) throw std::runtime_error("prototxt: '" + d.name + "': group != 1 is not supported");
+            if ((int)p->num("axis", 1) != 1) throw std::runtime_error("prototxt: '" + d.name + "': convolution axis != 1 is not supported");
+            if (d.kernel <= 0 || d.stride <= 0 || d.pad < 0) throw std::runtime_error("prototxt: '" + d.name + "': bad kernel_size / stride / pad");
         } else if (d.type == L_POOL) {
             const Msg* p = L.sub("pooling_param");
             if (!p) throw std::runtime_error("prototxt: '" + d.name + "' lacks pooling_param");
@@ -174,6 +186,12 @@ NetDef parse_prototxt_text(const std::string& text) {
             d.stride = (int)p->num("stride", 1);
             d.pad = (int)p->num("pad", 0);
             if (!d.pool_max) throw std::runtime_error("prototxt: '" + d.name + "': only MAX pooling is supported");
+            static const char* const unsupported[] = {"kernel_h", "kernel_w", "pad_h", "pad_w", "stride_h", "stride_w"};
+            for (size_t u = 0; u < sizeof(unsupported) / sizeof(unsupported[0]); ++u)
+                if (p->has(unsupported[u]))
+                    throw std::runtime_error("prototxt: '" + d.name + "': pooling_param." + unsupported[u] + " is not supported (square windows only)");
+            if (p->str("global_pooling", "false") == "true") throw std::runtime_error("prototxt: '" + d.name + "': global_pooling is not supported");
+            if (d.kernel <= 0 || d.stride <= 0 || d.pad < 0) throw std::runtime_error("prototxt: '" + d.name + "': bad kernel_size / stride / pad");
         } else if (d.type == L_LRN) {
             const Msg* p = L.sub("lrn_param");
             if (p) {
@@ -210,6 +228,12 @@ NetDef parse_prototxt_file(const std::string& path) {
 // LayerParameter{name=1, blobs=7}; V1LayerParameter{name=4, blobs=6};
 // BlobProto{num=1, channels=2, height=3, width=4, data=5, shape=7, double_data=8};
 // BlobShape{dim=1}.
+// NVCaffe (the fork the reference trained with: train/train.sh:19) stores weights, unless store_blobs_in_old_format is
+// set, as BlobProto{raw_data_type=10 (enum Type: DOUBLE=0, FLOAT=1, FLOAT16=2), raw_data=12 (bytes)} [ext: field and
+// enum numbers from NVCaffe 0.16/0.17's caffe.proto, not vendored upstream and not verifiable here].  The element width
+// is taken from len(raw_data) / count (4, 2 or 8 bytes: float32, IEEE half, float64), which does not depend on the enum
+// numbering; a declared type that contradicts it is an error.
+// Datum{channels=1, height=2, width=3, data=4 (bytes), label=5, float_data=6, encoded=7}.
 namespace {
 
 struct Reader {
@@ -252,11 +276,31 @@ struct Reader {
     }
 };
 
+float half_to_float(uint16_t h) {
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1Fu, man = h & 0x3FFu, bits;
+    if (exp == 0) {
+        if (man == 0) bits = sign;
+        else {                                  // subnormal: renormalise
+            int e = -1;
+            do { ++e; man <<= 1; } while (!(man & 0x400u));
+            bits = sign | ((uint32_t)(127 - 15 - e) << 23) | ((man & 0x3FFu) << 13);
+        }
+    } else if (exp == 31) bits = sign | 0x7F800000u | (man << 13);
+    else bits = sign | ((exp + 112u) << 23) | (man << 13);
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
+
 HostBlob read_blob(Reader r) {
     HostBlob b;
     int legacy[4] = {1, 1, 1, 1};
     bool has_legacy = false, has_shape = false;
     std::vector<double> dd;
+    const uint8_t* raw = 0;
+    size_t raw_len = 0;
+    int raw_type = -1;
     while (!r.done()) {
         int wt; Reader s; uint64_t v = 0;
         int f = r.field(&wt, &s, &v);
@@ -270,6 +314,10 @@ HostBlob read_blob(Reader r) {
         } else if (f == 8 && wt == 2) {
             size_t n = (size_t)(s.end - s.p) / 8;
             for (size_t i = 0; i < n; ++i) { double x; memcpy(&x, s.p + 8 * i, 8); dd.push_back(x); }
+        } else if (f == 10 && wt == 0) {
+            raw_type = (int)v;
+        } else if (f == 12 && wt == 2) {
+            raw = s.p; raw_len = (size_t)(s.end - s.p);
         } else if (f == 7 && wt == 2) {
             has_shape = true;
             while (!s.done()) {
@@ -285,11 +333,52 @@ HostBlob read_blob(Reader r) {
     if (!has_shape) { (void)has_legacy; b.shape.assign(legacy, legacy + 4); }
     size_t n = 1;
     for (size_t i = 0; i < b.shape.size(); ++i) n *= (size_t)b.shape[i];
+    if (b.data.empty() && raw && n > 0) {       // NVCaffe raw_data
+        if (raw_len % n) throw std::runtime_error("caffemodel: raw_data length is not a multiple of the blob's element count");
+        const size_t es = raw_len / n;
+        const int expect = es == 8 ? 0 : (es == 4 ? 1 : (es == 2 ? 2 : -2));
+        if (expect == -2) throw std::runtime_error("caffemodel: raw_data with " + std::to_string(es) + "-byte elements is not supported");
+        if (raw_type >= 0 && raw_type != expect)
+            throw std::runtime_error("caffemodel: raw_data_type " + std::to_string(raw_type) + " contradicts the element width of raw_data (" +
+                                     std::to_string(es) + " bytes)");
+        b.data.resize(n);
+        for (size_t i = 0; i < n; ++i) {
+            if (es == 4) memcpy(&b.data[i], raw + 4 * i, 4);
+            else if (es == 8) { double x; memcpy(&x, raw + 8 * i, 8); b.data[i] = (float)x; }
+            else { uint16_t h; memcpy(&h, raw + 2 * i, 2); b.data[i] = half_to_float(h); }
+        }
+    }
     if (n != b.data.size()) throw std::runtime_error("caffemodel: blob shape does not match its data length");
     return b;
 }
 
 }  // namespace
+
+Datum decode_datum(const uint8_t* buf, size_t len) {
+    Datum d;
+    Reader r; r.p = buf; r.end = buf + len;
+    while (!r.done()) {
+        int wt; Reader s; uint64_t v = 0;
+        const int f = r.field(&wt, &s, &v);
+        if (f == 1 && wt == 0) d.channels = (int)v;
+        else if (f == 2 && wt == 0) d.height = (int)v;
+        else if (f == 3 && wt == 0) d.width = (int)v;
+        else if (f == 4 && wt == 2) d.bytes.assign(s.p, s.end);
+        else if (f == 5 && wt == 0) { d.label = (int)v; d.has_label = true; }
+        else if (f == 6 && wt == 5) { uint32_t u = (uint32_t)v; float x; memcpy(&x, &u, 4); d.floats.push_back(x); }   // unpacked (proto2 default)
+        else if (f == 6 && wt == 2) {                                                                              // packed
+            const size_t n = (size_t)(s.end - s.p) / 4, old = d.floats.size();
+            d.floats.resize(old + n);
+            memcpy(d.floats.data() + old, s.p, n * 4);
+        } else if (f == 7 && wt == 0) d.encoded = v != 0;
+    }
+    if (d.encoded) throw std::runtime_error("Datum: encoded (compressed) images are not supported");
+    const size_t n = (size_t)d.channels * d.height * d.width;
+    if (d.channels <= 0 || d.height <= 0 || d.width <= 0) throw std::runtime_error("Datum: missing channels / height / width");
+    if (!d.bytes.empty() && !d.floats.empty()) throw std::runtime_error("Datum: both data and float_data are set");
+    if ((d.bytes.empty() ? d.floats.size() : d.bytes.size()) != n) throw std::runtime_error("Datum: data length does not match channels x height x width");
+    return d;
+}
 
 WeightMap read_caffemodel(const std::string& path) {
     std::ifstream f(path.c_str(), std::ios::binary);

@@ -5,8 +5,10 @@
 // /root/reference/models/deploy.prototxt:1-2178 uses.  No protoc / libprotobuf:
 // the text format is parsed by a small recursive-descent reader and the binary
 // format by a wire-format walker (field numbers from caffe.proto, listed in
-// caffemodel.cpp).
+// netdef.cpp).
 #pragma once
+#include <stdint.h>
+
 #include <map>
 #include <string>
 #include <vector>
@@ -42,7 +44,17 @@ struct HostBlob {
 };
 typedef std::map<std::string, std::vector<HostBlob> > WeightMap;
 
-// Both throw std::runtime_error with a message on malformed input.
+// caffe.proto Datum: one record of the LMDBs that feed the layer's two bottoms
+// (/root/reference/scripts/misc/create_training_lmdb.py:172-185 writes them with caffe.io.array_to_datum).
+struct Datum {
+    int channels = 0, height = 0, width = 0, label = 0;
+    bool has_label = false, encoded = false;
+    std::vector<uint8_t> bytes;     // Datum.data (uint8 arrays)
+    std::vector<float> floats;      // Datum.float_data (every other dtype; packed or not)
+};
+Datum decode_datum(const uint8_t* buf, size_t len);
+
+// All throw std::runtime_error with a message on malformed input.
 NetDef parse_prototxt_file(const std::string& path);
 NetDef parse_prototxt_text(const std::string& text);
 WeightMap read_caffemodel(const std::string& path);

@@ -176,6 +176,20 @@ int fcnod_detect_device(fcnod_net* net, const float* data_dev, int B, const fcno
 int fcnod_detect_graph_build(fcnod_net* net, const float* data_dev, int B, const fcnod_postnet_params* p, void* stream);
 int fcnod_detect_graph_launch(fcnod_net* net, void* stream);
 
+/* ---- on-disk formats (host only, no CUDA) ------------------------------------------------------------------
+ * One weight blob of a .caffemodel as the network loader sees it (float32): V2 `layer` / V1 `layers` records,
+ * BlobProto.data (packed or not), double_data, `shape` or legacy num/channels/height/width, and NVCaffe's
+ * raw_data_type / raw_data (float32, IEEE half, float64).  out may be NULL to query dims / ndim. */
+int fcnod_caffemodel_blob(const char* caffemodel_path, const char* layer, int index, int dims[4], int* ndim, float* out,
+                          size_t out_count);
+
+/* ---- B1: wire format of the layer's two bottoms ------------------------------------------------------------
+ * One caffe.proto `Datum` record as create_training_lmdb.py:172-185 writes it (caffe.io.array_to_datum): dims =
+ * channels, height, width AS STORED (the image datum is written un-transposed: an HxWx3 image arrives as channels = H,
+ * height = W, width = 3); uint8 `data` and (packed or unpacked) `float_data` both come back as float32.  out may be NULL
+ * to query the dims; label = -1 when the record has none.  Encoded (compressed) datums are refused. */
+int fcnod_datum_decode(const uint8_t* buf, size_t len, int dims[3], int* label, float* out, size_t out_count);
+
 /* ---- B1: training-side layer ------------------------------------------------------------- */
 /* Label rasteriser.  rects [N][R][4] int32 (x,y,w,h at net resolution), labels [N][R] int32,
  * nrect [N] int32 (<= R).  Outputs NCHW float32: fg [N][C][gh][gw]; bbox,size,obj,cvg [N][4C][gh][gw]. */

@@ -2,7 +2,8 @@
 
 Independent of the product's C++ reader.  Accepts V2 `layer` (field 100) and V1
 `layers` (field 2) messages, BlobProto.data packed or unpacked, `shape` or
-legacy num/channels/height/width, and `double_data` (field 8).
+legacy num/channels/height/width, `double_data` (field 8), and NVCaffe's
+`raw_data_type` (field 10) / `raw_data` (field 12) [ext: NVCaffe caffe.proto].
 Call site being restated: caffe.Net(proto, weights, caffe.TEST),
 /root/reference/scripts/fcn_object_detector.py:317.
 """
@@ -64,7 +65,14 @@ def _blob(buf):
     shape = None
     chunks = []
     dchunks = []
+    raw, raw_type = None, None
     for f, wt, v in _fields(buf):
+        if f == 10 and wt == 0:
+            raw_type = v
+            continue
+        if f == 12 and wt == 2:
+            raw = bytes(v)
+            continue
         if f in (1, 2, 3, 4) and wt == 0:
             legacy[f] = v
         elif f == 5:
@@ -75,12 +83,15 @@ def _blob(buf):
             for f2, wt2, v2 in _fields(v):
                 if f2 == 1:
                     shape = (shape or []) + (_varints(v2) if wt2 == 2 else [v2])
-    if chunks:
-        data = np.frombuffer(b''.join(chunks), dtype='<f4').astype(np.float32)
-    else:
-        data = np.frombuffer(b''.join(dchunks), dtype='<f8').astype(np.float32)
     if shape is None:
         shape = [legacy.get(k, 1) for k in (1, 2, 3, 4)]
+    if chunks:
+        data = np.frombuffer(b''.join(chunks), dtype='<f4').astype(np.float32)
+    elif dchunks:
+        data = np.frombuffer(b''.join(dchunks), dtype='<f8').astype(np.float32)
+    else:       # NVCaffe raw storage: DOUBLE = 0, FLOAT = 1, FLOAT16 = 2
+        dt = {0: '<f8', 1: '<f4', 2: '<f2'}[raw_type]
+        data = np.frombuffer(raw, dtype=dt).astype(np.float32)
     return data.reshape(shape)
 
 

@@ -174,3 +174,105 @@ def test_detector_without_files_is_inert():
     from fcn_object_detector_b200.detector import FCNObjectDetector
     d = FCNObjectDetector(pretrained_weights=None, deployment_prototxt=None)
     assert d.net is None and d.labels == []
+
+
+# ----------------------------------------------------------------------------- on-disk formats
+def _cpp_blob(path, layer, index):
+    from fcn_object_detector_b200 import _lib
+    L = _lib.lib()
+    dims = (C.c_int * 4)(); nd = C.c_int()
+    _lib.check(L.fcnod_caffemodel_blob(path.encode(), layer.encode(), index, C.byref(dims), C.byref(nd), None, 0))
+    out = np.empty(tuple(dims)[:nd.value], np.float32)
+    _lib.check(L.fcnod_caffemodel_blob(path.encode(), layer.encode(), index, C.byref(dims), C.byref(nd), _lib.ptr(out), out.size))
+    return out
+
+
+def test_caffemodel_nvcaffe_raw_data(built_lib, model_files, tmp_path):
+    """NVCaffe snapshots (the reference trained with NVCaffe: train/train.sh:19) store blobs as raw_data_type + raw_data.
+    float32 / IEEE half / float64 payloads: the C++ loader, the oracle's reader and the written arrays agree."""
+    from fcn_object_detector_b200 import _lib
+    from fcn_object_detector_b200.caffemodel import write_caffemodel, xavier_weights
+    from fcn_object_detector_b200.netspec import conv_shapes
+    from oracle.caffemodel_io import read_caffemodel
+    proto, _ = model_files
+    layers = xavier_weights(conv_shapes(), 3)
+    # include values that exercise half subnormals / exact halves
+    layers[0][2][1][:6] = [0.0, -0.0, 6.1035e-05, 5.96e-08, 65504.0, -1.5]
+    for raw, tol in (('float', 0.0), ('double', 0.0), ('half', None)):
+        p = write_caffemodel(str(tmp_path / ('raw_%s.caffemodel' % raw)), layers, raw=raw)
+        ref = read_caffemodel(p)
+        for name, _t, blobs in (layers[0], layers[7], layers[-1]):
+            for i, arr in enumerate(blobs):
+                got = _cpp_blob(p, name, i)
+                want = arr.astype('<f2').astype(np.float32) if raw == 'half' else arr
+                assert got.shape == arr.shape
+                assert np.array_equal(got.view(np.uint32), np.ascontiguousarray(want).view(np.uint32)), (raw, name, i)
+                assert np.array_equal(ref[name][i], want)
+        h = C.c_void_p()
+        _lib.check(_lib.lib().fcnod_net_create(proto.encode(), p.encode(), -1, 1, C.byref(h)))     # and the planner takes it
+        _lib.lib().fcnod_net_destroy(h)
+    # a declared type that contradicts the payload width is refused, not mis-read
+    good = open(str(tmp_path / 'raw_float.caffemodel'), 'rb').read()
+    bad = good.replace(bytes([10 << 3, 1]), bytes([10 << 3, 2]), 1)
+    (tmp_path / 'bad_type.caffemodel').write_bytes(bad)
+    h = C.c_void_p()
+    assert _lib.lib().fcnod_net_create(proto.encode(), str(tmp_path / 'bad_type.caffemodel').encode(), -1, 1, C.byref(h)) != 0
+    assert b'raw_data_type' in _lib.lib().fcnod_last_error()
+
+
+def test_prototxt_unsupported_params_are_refused(built_lib, model_files, tmp_path):
+    """dilation / group / per-axis kernels would silently compute something else: the loader must say so."""
+    from fcn_object_detector_b200 import _lib
+    L = _lib.lib()
+    _, cm = model_files
+    head = 'input: "data"\ninput_shape { dim: 1 dim: 3 dim: 8 dim: 8 }\n'
+    conv = 'layer { name: "c" type: "Convolution" bottom: "data" top: "c" convolution_param { num_output: 8 kernel_size: 3 %s } }\n'
+    pool = 'layer { name: "p" type: "Pooling" bottom: "data" top: "p" pooling_param { pool: MAX kernel_size: 3 %s } }\n'
+    for body, word in ((conv % 'dilation: 2', b'dilation'), (conv % 'group: 2', b'group'), (conv % 'kernel_h: 3', b'kernel_h'),
+                       (conv % 'pad_w: 1', b'pad_w'), (pool % 'stride_h: 2', b'stride_h'), (pool % 'global_pooling: true', b'global_pooling')):
+        f = tmp_path / 'bad.prototxt'
+        f.write_text(head + body)
+        h = C.c_void_p()
+        assert L.fcnod_net_create(str(f).encode(), cm.encode(), -1, 1, C.byref(h)) != 0
+        assert word in L.fcnod_last_error(), (word, L.fcnod_last_error())
+
+
+def _datum_bytes(arr, label=None, packed=False):
+    """caffe.io.array_to_datum(arr, label).SerializeToString(), restated: uint8 -> data (4), else float_data (6)."""
+    from fcn_object_detector_b200.caffemodel import _ld, _varint
+    import struct
+    c, h, w = arr.shape
+    out = b''.join(_varint((f << 3) | 0) + _varint(v) for f, v in ((1, c), (2, h), (3, w)))
+    if arr.dtype == np.uint8:
+        out += _ld(4, arr.tobytes())
+    elif packed:
+        out += _ld(6, arr.astype('<f4').tobytes())
+    else:       # proto2 `repeated float` without [packed = true]: one tag + 4 bytes per element
+        out += b''.join(bytes([(6 << 3) | 5]) + struct.pack('<f', float(v)) for v in arr.astype(np.float32).flat)
+    if label is not None:
+        out += _varint((5 << 3) | 0) + _varint(label)
+    return out
+
+
+def test_lmdb_datum_records_decode_into_the_layer_bottoms(built_lib):
+    """create_training_lmdb.py:172-185: image datum = float H x W x 3 stored un-transposed, label datum = (1,1,5)."""
+    from fcn_object_detector_b200.lmdb_datum import datums_to_bottoms, decode_datum, image_to_chw
+    rs = np.random.RandomState(0)
+    imgs = [rs.uniform(0, 1, (12, 16, 3)).astype(np.float32) for _ in range(3)]
+    labs = [np.asarray([[[4 + i, 5, 6, 7, 0]]], np.float64) for i in range(3)]
+    for packed in (False, True):
+        data_in, label = datums_to_bottoms([_datum_bytes(a, packed=packed) for a in imgs], [_datum_bytes(l, packed=packed) for l in labs])
+        assert data_in.shape == (3, 3, 12, 16) and label.shape == (3, 1, 1, 5)
+        for i in range(3):
+            assert np.array_equal(data_in[i], imgs[i].transpose(2, 0, 1))
+            assert np.array_equal(label[i, 0, 0], labs[i].reshape(-1).astype(np.float32))
+    # uint8 data + label field; an already C x H x W datum passes through
+    u8 = rs.randint(0, 256, (3, 10, 14)).astype(np.uint8)
+    arr, lab = decode_datum(_datum_bytes(u8, label=2))
+    assert lab == 2 and np.array_equal(arr, u8.astype(np.float32)) and image_to_chw(arr) is arr
+    # malformed records fail loudly
+    from fcn_object_detector_b200._lib import FcnodError
+    with pytest.raises(FcnodError):
+        decode_datum(_datum_bytes(u8)[:-5])
+    with pytest.raises(FcnodError):
+        decode_datum(_datum_bytes(u8) + bytes([(7 << 3) | 0, 1]))        # encoded = true
