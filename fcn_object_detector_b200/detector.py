@@ -220,6 +220,61 @@ def postnet(coverage, bboxes, src_hw=None, overflow=None, **params):
     return _unpack(det, lab, wgt, cnt, weights=True, overflow=overflow)
 
 
+class MultiGpuDetector(object):
+    """One process, several GPUs (the reference node is ONE process: scripts/fcn_object_detector.py:307-308).
+    A replica of the detector (own handle, own streams, own CUDA graph, replicated weights) lives on every device of
+    `device_ids`; `predict_batch` splits the frames contiguously over the replicas (sharding.shard_range), submits every
+    shard with the asynchronous fcnod_detect_submit -- uploads and compute of all devices run at once -- and then
+    collects them in order.  Frames are independent: no data-path collective, results are concatenated on the host."""
+
+    def __init__(self, pretrained_weights, deployment_prototxt, device_ids, **kw):
+        if not device_ids:
+            raise ValueError('device_ids must name at least one CUDA device')
+        self.device_ids = list(device_ids)
+        self.replicas = [FCNObjectDetector(pretrained_weights=pretrained_weights, deployment_prototxt=deployment_prototxt,
+                                           device_id=d, **kw) for d in self.device_ids]
+        self.overflow = []
+
+    def predict_batch(self, images):
+        from .sharding import shard_range
+        images = np.ascontiguousarray(images, dtype=np.uint8)
+        if images.ndim != 4 or images.shape[3] != 3:
+            raise ValueError('images must be (B,H,W,3) uint8 BGR')
+        B, H, W, _ = images.shape
+        L = _lib.lib()
+        M = _lib.FCNOD_MAX_DET
+        world = len(self.replicas)
+        pending = []
+        for r, det in enumerate(self.replicas):
+            lo, hi = shard_range(B, r, world)
+            if hi == lo:
+                continue
+            p = det._params()
+            ticket = C.c_int32(-1)
+            shard = images[lo:hi]
+            _lib.check(L.fcnod_detect_submit(det.net.handle, _lib.ptr(shard), hi - lo, H, W, C.byref(p), C.byref(ticket)))
+            pending.append((det, ticket.value, lo, hi, shard))
+        out, self.overflow = [], []
+        for det, ticket, lo, hi, _shard in pending:
+            n = hi - lo
+            d = np.empty((n, M, 5), np.int32); lab = np.empty((n, M), np.int32)
+            wgt = np.empty((n, M), np.int32); cnt = np.empty((n,), np.int32)
+            _lib.check(L.fcnod_detect_collect(det.net.handle, ticket, _lib.ptr(d), _lib.ptr(lab), _lib.ptr(wgt), _lib.ptr(cnt)))
+            ov = []
+            out.extend(_unpack(d, lab, wgt, cnt, overflow=ov))
+            self.overflow.extend((lo + b, t) for b, t in ov)
+            det.net._sync_after_device_run()
+        return out
+
+    def run_detector(self, cv_img):
+        return self.replicas[0].run_detector(cv_img)
+
+    def close(self):
+        for det in self.replicas:
+            if det.net is not None:
+                det.net.close()
+
+
 def gridbox_to_boxes(net_cvg, net_boxes, prob_thresh=0.5, im_w=448, im_h=448, stride=16):
     """`gridbox_to_boxes` of scripts/fcn_object_detector.py:357-394 on the device (fcnod_decode), one class map:
     net_cvg (G,G) float32, net_boxes (4,G,G) float32.  Returns (boxes (n,4) float64 [x1,y1,x2,y2],

@@ -75,3 +75,58 @@ def test_predict_sharded_world2_gloo(n_frames):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert got == [(0, True), (1, True)]
+
+
+def test_multi_gpu_detector_splits_and_orders(monkeypatch):
+    """MultiGpuDetector (one process, one replica per device) on CPU with the C ABI stubbed out: the split is the
+    contiguous shard_range one, every shard is SUBMITTED before any is collected, results come back in frame order."""
+    import ctypes as C
+    from fcn_object_detector_b200 import _lib, detector as D
+    log = []
+
+    class FakeNet(object):
+        def __init__(self, dev):
+            self.handle = dev
+        def _sync_after_device_run(self, batch=None):
+            pass
+        def close(self):
+            pass
+
+    class FakeDet(object):
+        def __init__(self, pretrained_weights=None, deployment_prototxt=None, device_id=0, **kw):
+            self.net = FakeNet(device_id)
+        def _params(self):
+            return _lib.PostnetParams()
+
+    class FakeLib(object):
+        def __init__(self):
+            self.shards = {}
+        def fcnod_detect_submit(self, h, images, B, H, W, p, ticket):
+            arr = np.ctypeslib.as_array(C.cast(images, C.POINTER(C.c_uint8)), shape=(B, H, W, 3))
+            self.shards[h] = arr[:, 0, 0, 0].copy()
+            log.append(('submit', h, B))
+            ticket._obj.value = 7
+            return 0
+        def fcnod_detect_collect(self, h, ticket, det, lab, wgt, cnt):
+            tags = self.shards[h]
+            n = len(tags)
+            d = np.ctypeslib.as_array(C.cast(det, C.POINTER(C.c_int32)), shape=(n, _lib.FCNOD_MAX_DET, 5))
+            c = np.ctypeslib.as_array(C.cast(cnt, C.POINTER(C.c_int32)), shape=(n,))
+            la = np.ctypeslib.as_array(C.cast(lab, C.POINTER(C.c_int32)), shape=(n, _lib.FCNOD_MAX_DET))
+            c[:] = 1; d[:, 0, 0] = tags; d[:, 0, 1] = h; la[:, 0] = 0
+            log.append(('collect', h, n))
+            return 0
+        def fcnod_last_error(self):
+            return b''
+    fake = FakeLib()
+    monkeypatch.setattr(D, 'FCNObjectDetector', FakeDet)
+    monkeypatch.setattr(_lib, 'lib', lambda: fake)
+    m = D.MultiGpuDetector('w', 'p', device_ids=[0, 1, 2])
+    imgs = np.zeros((8, 4, 4, 3), np.uint8)
+    imgs[:, 0, 0, 0] = np.arange(8) + 10
+    res = m.predict_batch(imgs)
+    assert [int(r[0][0, 0]) for r in res] == list(range(10, 18))                  # frame order kept
+    assert [int(r[0][0, 1]) for r in res] == [0, 0, 0, 1, 1, 1, 2, 2]             # 3 + 3 + 2, contiguous
+    assert [e[0] for e in log] == ['submit'] * 3 + ['collect'] * 3               # all devices busy before any wait
+    res = m.predict_batch(imgs[:2])                                               # fewer frames than devices
+    assert len(res) == 2 and [e for e in log[6:]] == [('submit', 0, 1), ('submit', 1, 1), ('collect', 0, 1), ('collect', 1, 1)]
