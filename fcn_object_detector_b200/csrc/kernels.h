@@ -20,5 +20,8 @@ void postnet_prepare(double eps);
 void preprocess_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, float* data_dev,
                        void* scratch, cudaStream_t stream);
 int preprocess_num_launches();
+// prelude straight into the padded, pre-swizzled bf16 space-to-depth image of the first convolution (no fp32 `data`)
+void preprocess_s2d_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, void* s2d_dev, int Wp,
+                           int Hp, int padl, void* scratch, cudaStream_t stream);
 
 }  // namespace fcnod

@@ -183,6 +183,12 @@ struct fcnod_net {
     cudaStream_t lane_stream[2] = {0, 0};  // lanes 1, 2 of the forward (lane 0 = the caller's stream)
     cudaEvent_t fork_ev = 0, join_ev[2] = {0, 0};
     int n_lanes = 1;
+    // detect paths on the fused bf16 plan: the prelude writes the first convolution's space-to-depth operand directly and
+    // the fp32 blob `data` is only materialised when somebody reads it (from the frames still on the device)
+    bool fused_prelude = false;
+    bool data_valid = true;
+    const uint8_t* data_img = 0;
+    int data_img_b = 0, data_img_h = 0, data_img_w = 0;
     cudaStream_t copy_stream = 0;        // uploads of fcnod_detect's second half-batch, overlapped with the first one's compute
     cudaEvent_t copy_ev[2] = {0, 0};
     int32_t* pinned_big = 0;             // detections of a whole fcnod_detect call (all chunks)
@@ -737,6 +743,8 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
             net->steps.push_back(st);
         }
     plan_lanes(net);
+    net->fused_prelude = !net->steps.empty() && net->steps[0].kind == S_S2D && net->blobs[0].C == 3 &&
+                         net->blobs[0].H % 2 == 0 && net->blobs[0].W % 2 == 0 && !getenv("FCNOD_NO_PRELUDE_FUSION");
 }
 
 // ------------------------------------------------------------------------------------ lanes
@@ -1640,11 +1648,12 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
     FCNOD_CUDA(cudaGetLastError());
 }
 
-void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s) {
+void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool skip_input_step = false) {
     FCNOD_CHECK(net->device >= 0, "plan-only handle (device < 0): no compute is possible; there is no CPU fallback");
     FCNOD_CHECK(net->batch > 0, "net not reshaped");
+    const size_t first = skip_input_step ? 1 : 0;       // the input step's output was produced by the fused prelude
     if (net->n_lanes <= 1) {
-        for (size_t i = 0; i < net->steps.size(); ++i) run_step(net, net->steps[i], data_dev, s);
+        for (size_t i = first; i < net->steps.size(); ++i) run_step(net, net->steps[i], data_dev, s);
         return;
     }
     // lane 0 = the caller's stream; the others fork from it here and join it again at the end (under stream capture the
@@ -1657,7 +1666,7 @@ void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s) {
         cudaStream_t ls = lanes[st.lane];
         if (!forked[st.lane]) { FCNOD_CUDA(cudaStreamWaitEvent(ls, net->fork_ev, 0)); forked[st.lane] = true; }
         for (size_t w = 0; w < st.waits.size(); ++w) FCNOD_CUDA(cudaStreamWaitEvent(ls, net->steps[st.waits[w]].ev, 0));
-        run_step(net, st, data_dev, ls);
+        if (i >= first) run_step(net, st, data_dev, ls);
         if (st.signal) FCNOD_CUDA(cudaEventRecord(st.ev, ls));
     }
     for (int l = 1; l < 3; ++l)
@@ -1680,8 +1689,8 @@ void ensure_detect_buffers(fcnod_net* net) {
 }
 
 void detect_device(fcnod_net* net, const float* data_dev, const int32_t* srchw_dev, const fcnod_postnet_params& p,
-                   cudaStream_t s) {
-    forward_device(net, data_dev, s);
+                   cudaStream_t s, bool skip_input_step = false) {
+    forward_device(net, data_dev, s, skip_input_step);
     int ic = blob_id(net, "coverage"), ib = blob_id(net, "bboxes");
     const Blob& bc = net->blobs[ic];
     const Blob& bb = net->blobs[ib];
@@ -1690,6 +1699,23 @@ void detect_device(fcnod_net* net, const float* data_dev, const int32_t* srchw_d
     ensure_detect_buffers(net);
     postnet_launch(net->out_dev[bc.out_index], net->out_dev[bb.out_index], net->batch, bc.C, bb.C, bc.H, bc.W, srchw_dev, p,
                    net->post_scratch, net->det_dev, net->label_dev, net->weight_dev, net->count_dev, s);
+}
+
+// Prelude of the detect paths: uint8 frames on the device -> the network's input.  Fused plan: straight into the first
+// convolution's space-to-depth image (returns true: the forward then skips its input step); otherwise into blob `data`.
+bool detect_prelude(fcnod_net* net, const uint8_t* img, int B, int src_h, int src_w, cudaStream_t s) {
+    const Blob& in = net->blobs[0];
+    net->data_img = img; net->data_img_b = B; net->data_img_h = src_h; net->data_img_w = src_w;
+    if (net->fused_prelude) {
+        const Step& st = net->steps[0];
+        preprocess_s2d_launch(img, B, src_h, src_w, in.H, in.W, net->buffers[st.s2d_buf].ptr, st.s2d_wp, st.s2d_hp, st.s2d_padl,
+                              net->pre_scratch, s);
+        net->data_valid = false;
+        return true;
+    }
+    preprocess_launch(img, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
+    net->data_valid = true;
+    return false;
 }
 
 void copy_detections_out(fcnod_net* net, int B, int32_t* out_det, int32_t* out_label, int32_t* out_weight,
@@ -1919,6 +1945,7 @@ int fcnod_net_forward(fcnod_net* net, const float* data_host) {
     const Blob& in = net->blobs[0];
     size_t bytes = (size_t)net->batch * in.C * in.H * in.W * 4;
     FCNOD_CUDA(cudaMemcpyAsync(net->data_dev, data_host, bytes, cudaMemcpyHostToDevice, net->stream));
+    net->data_valid = true;
     forward_device(net, net->data_dev, net->stream);
     FCNOD_CUDA(cudaStreamSynchronize(net->stream));
     FCNOD_API_END
@@ -1934,6 +1961,13 @@ int fcnod_net_blob_read(fcnod_net* net, const char* blob, float* host_out, size_
     FCNOD_CHECK(b.buf != -2, std::string("blob '") + blob + "' is fused away in the bf16 plan and never materialised; "
                 "create the net with FCNOD_PRECISION_FP32, or set FCNOD_NO_FUSION=1, to inspect it");
     if (b.buf < 0) {
+        if (!net->data_valid) {      // the detect path fed the first convolution directly: materialise `data` now
+            FCNOD_CHECK(net->data_img && net->data_img_b == net->batch, "blob 'data' of the last detect call is no longer available");
+            FCNOD_CUDA(cudaStreamSynchronize(net->stream));
+            preprocess_launch(net->data_img, net->batch, net->data_img_h, net->data_img_w, b.H, b.W, net->data_dev, net->pre_scratch, net->stream);
+            FCNOD_CUDA(cudaStreamSynchronize(net->stream));
+            net->data_valid = true;
+        }
         FCNOD_CUDA(cudaMemcpy(host_out, net->data_dev, n * 4, cudaMemcpyDeviceToHost));
     } else if (b.is_output) {
         FCNOD_CUDA(cudaStreamSynchronize(net->stream));
@@ -2120,6 +2154,7 @@ int fcnod_detect_from_data(fcnod_net* net, const float* data_host, int B, const 
     size_t bytes = (size_t)B * in.C * in.H * in.W * 4;
     cudaStream_t s = net->stream;
     FCNOD_CUDA(cudaMemcpyAsync(net->data_dev, data_host, bytes, cudaMemcpyHostToDevice, s));
+    net->data_valid = true;
     detect_device(net, net->data_dev, 0, *p, s);
     copy_detections_out(net, B, out_det, out_label, out_weight, out_count, s);
     FCNOD_API_END
@@ -2174,8 +2209,8 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
         int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
         for (int c = 0; c < 2; ++c) {
             FCNOD_CUDA(cudaStreamWaitEvent(s, net->copy_ev[c], 0));
-            preprocess_launch(net->img_dev + c * cbytes, Bc, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
-            detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+            const bool skip = detect_prelude(net, net->img_dev + c * cbytes, Bc, src_h, src_w, s);
+            detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip);
             const size_t o = (size_t)c * Bc;
             FCNOD_CUDA(cudaMemcpyAsync(p_det + o * FCNOD_MAX_DET * 5, net->det_dev, (size_t)Bc * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost, s));
             FCNOD_CUDA(cudaMemcpyAsync(p_lab + o * FCNOD_MAX_DET, net->label_dev, (size_t)Bc * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
@@ -2206,8 +2241,8 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaStreamSynchronize(s));   // hw is a stack-lifetime host buffer
     FCNOD_CUDA(cudaMemcpyAsync(net->img_dev, images, ibytes, cudaMemcpyHostToDevice, s));
-    preprocess_launch(net->img_dev, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
-    detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+    const bool skip = detect_prelude(net, net->img_dev, B, src_h, src_w, s);
+    detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip);
     copy_detections_out(net, B, out_det, out_label, out_weight, out_count, s);
     FCNOD_API_END
 }
@@ -2261,7 +2296,7 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
         cudaGraph_t g = 0;
         FCNOD_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
         try {
-            detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+            detect_device(net, net->data_dev, net->srchw_dev, *p, s, net->fused_prelude);
         } catch (...) {
             cudaStreamEndCapture(s, &g);
             if (g) cudaGraphDestroy(g);
@@ -2281,9 +2316,9 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
     for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
     FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
-    preprocess_launch(sl.img, B, src_h, src_w, in.H, in.W, net->data_dev, net->pre_scratch, s);
+    const bool skip = detect_prelude(net, sl.img, B, src_h, src_w, s);
     if (net->sgraph) FCNOD_CUDA(cudaGraphLaunch(net->sgraph, s));
-    else detect_device(net, net->data_dev, net->srchw_dev, *p, s);
+    else detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip);
     int32_t* p_det = sl.pinned + (size_t)B * 2;
     int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
     int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;

@@ -164,9 +164,103 @@ __global__ void __launch_bounds__(256) pre_resample_kernel(const uint8_t* __rest
     }
 }
 
+// Prelude straight into the first convolution's operand: the same values pre_resample_kernel would write into the
+// fp32 blob `data` (same table, same float64 lerps, same float rounding), rounded to bf16 and stored as the padded,
+// pre-swizzled 2x2 space-to-depth image (fused_pool.cuh: input_s2d_kernel) -- the 154 MB fp32 `data` round trip of a
+// 64-frame batch never happens on the detect path.  One thread per space-to-depth pixel (2 x 2 net pixels x 3 channels).
+__global__ void __launch_bounds__(256) pre_s2d_kernel(const uint8_t* __restrict__ img, int src_h, int src_w, int net_h, int net_w,
+                                                      const int* __restrict__ mm, bf16* __restrict__ out, int Wp, int Hp, int padl) {
+    __shared__ double lut[3][256];
+    __shared__ float lutf[3][256];
+    const int b = blockIdx.y;
+    const bool same = (src_h == net_h && src_w == net_w);
+    {
+        const int* m = mm + b * 6;
+        const double mn = fmin(fmin((double)m[0] - mean64(0), (double)m[1] - mean64(1)), (double)m[2] - mean64(2));
+        const double mx = fmax(fmax((double)m[3] - mean64(0), (double)m[4] - mean64(1)), (double)m[5] - mean64(2));
+        const double range = mx - mn;
+        for (int i = threadIdx.x; i < 768; i += blockDim.x) {
+            const int c = i >> 8, v = i & 255;
+            const double q = (((double)v - mean64(c)) - mn) / range;
+            lut[c][v] = q;
+            lutf[c][v] = (float)q;
+        }
+    }
+    __syncthreads();
+    const int H2 = net_h >> 1, W2 = net_w >> 1;
+    const int rows_per = (H2 + gridDim.x - 1) / gridDim.x;
+    const int row0 = blockIdx.x * rows_per, row1 = min(row0 + rows_per, H2);
+    const uint8_t* p = img + (size_t)b * src_h * src_w * 3;
+    const double sy = (double)src_h / (double)net_h, sx = (double)src_w / (double)net_w;
+    const int total = (row1 - row0) * W2;
+    for (int t = threadIdx.x; t < total; t += blockDim.x) {
+        const int w2 = t % W2, h2 = row0 + t / W2;
+        __align__(16) bf16 v[16];
+#pragma unroll
+        for (int j = 12; j < 16; ++j) v[j] = __float2bfloat16_rn(0.f);
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy) {
+            const int oy = 2 * h2 + dy;
+            if (same) {
+                const uint8_t* q = p + ((size_t)oy * src_w + 2 * w2) * 3;       // two pixels = 6 bytes
+#pragma unroll
+                for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) v[(dy * 2 + dx) * 3 + c] = __float2bfloat16_rn(lutf[c][q[dx * 3 + c]]);
+            } else {
+                double fyd = ((double)oy + 0.5) * sy - 0.5;
+                int y0 = (int)floor(fyd);
+                double ay = fyd - (double)y0;
+                if (y0 < 0) { y0 = 0; ay = 0.0; }
+                if (y0 >= src_h - 1) { y0 = src_h - 1; ay = 0.0; }
+                const int y1 = min(y0 + 1, src_h - 1);
+                const uint8_t* r0 = p + (size_t)y0 * src_w * 3;
+                const uint8_t* r1 = p + (size_t)y1 * src_w * 3;
+#pragma unroll
+                for (int dx = 0; dx < 2; ++dx) {
+                    const int ox = 2 * w2 + dx;
+                    double fxd = ((double)ox + 0.5) * sx - 0.5;
+                    int x0 = (int)floor(fxd);
+                    double ax = fxd - (double)x0;
+                    if (x0 < 0) { x0 = 0; ax = 0.0; }
+                    if (x0 >= src_w - 1) { x0 = src_w - 1; ax = 0.0; }
+                    const int x1 = min(x0 + 1, src_w - 1);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const double p00 = lut[c][r0[x0 * 3 + c]], p01 = lut[c][r0[x1 * 3 + c]];
+                        const double p10 = lut[c][r1[x0 * 3 + c]], p11 = lut[c][r1[x1 * 3 + c]];
+                        const double tp = p00 * (1.0 - ax) + p01 * ax, bt = p10 * (1.0 - ax) + p11 * ax;
+                        v[(dy * 2 + dx) * 3 + c] = __float2bfloat16_rn((float)(tp * (1.0 - ay) + bt * ay));
+                    }
+                }
+            }
+        }
+        const int xp = padl + w2;
+        const int swz = (xp >> 2) & 1;
+        uint4* o = reinterpret_cast<uint4*>(out + ((size_t)(b * Hp + padl + h2) * Wp + xp) * 16);
+        o[swz] = *reinterpret_cast<const uint4*>(v);
+        o[swz ^ 1] = *reinterpret_cast<const uint4*>(v + 8);
+    }
+}
+
 }  // namespace
 
 int preprocess_num_launches() { return 3; }
+
+void preprocess_s2d_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, void* s2d_dev, int Wp,
+                           int Hp, int padl, void* scratch, cudaStream_t s) {
+    FCNOD_CHECK(B > 0 && src_h > 0 && src_w > 0 && net_h > 0 && net_w > 0 && net_h % 2 == 0 && net_w % 2 == 0, "preprocess: bad dimensions");
+    int* mm = static_cast<int*>(scratch);
+    pre_init_kernel<<<ceil_div(B * 6, 128), 128, 0, s>>>(mm, B);
+    FCNOD_CUDA(cudaGetLastError());
+    pre_minmax_kernel<<<dim3(32, B), 256, 0, s>>>(images_dev, (long)src_h * src_w, mm);
+    FCNOD_CUDA(cudaGetLastError());
+    int bands = ceil_div(148 * 16, B);
+    bands = max(1, min(bands, ceil_div(net_h / 2, 4)));
+    pre_s2d_kernel<<<dim3(bands, B), 256, 0, s>>>(images_dev, src_h, src_w, net_h, net_w, mm, static_cast<bf16*>(s2d_dev), Wp, Hp, padl);
+    FCNOD_CUDA(cudaGetLastError());
+}
+
 
 void preprocess_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, float* data_dev,
                        void* scratch, cudaStream_t s) {

@@ -182,3 +182,25 @@ def test_alternating_batch_sizes_keep_their_plans(model_files):
         assert det.net.describe() == plan4 and np.array_equal(det.net.blobs['coverage'].data, cov4)
         det.predict_batch(one)
         assert det.net.describe() == plan1 and np.array_equal(det.net.blobs['coverage'].data, cov1)
+
+
+def test_fused_prelude_feeds_conv1_and_data_blob_is_materialised_on_demand(model_files, monkeypatch):
+    """On the bf16 plan the detect paths write the first convolution's space-to-depth operand straight from the uint8 frames
+    (no fp32 `data` round trip).  Results equal the unfused prelude's bit for bit, and `blobs['data']` still answers."""
+    from fcn_object_detector_b200.detector import FCNObjectDetector, preprocess
+    proto, cm = model_files
+    rs = np.random.RandomState(8)
+    for shape in ((448, 448), (480, 640), (301, 203)):
+        imgs = rs.randint(0, 256, (3,) + shape + (3,)).astype(np.uint8)
+        det = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='bf16', detection_threshold=0.3, min_boxes=1)
+        res = det.predict_batch(imgs)
+        cov = det.net.blobs['coverage'].data.copy(); bb = det.net.blobs['bboxes'].data.copy()
+        data = det.net.blobs['data'].data.copy()
+        assert np.array_equal(data, preprocess(imgs))
+        monkeypatch.setenv('FCNOD_NO_PRELUDE_FUSION', '1')
+        ref = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, precision='bf16', detection_threshold=0.3, min_boxes=1)
+        monkeypatch.delenv('FCNOD_NO_PRELUDE_FUSION')
+        res2 = ref.predict_batch(imgs)
+        assert np.array_equal(ref.net.blobs['coverage'].data, cov) and np.array_equal(ref.net.blobs['bboxes'].data, bb)
+        assert all(np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) for a, b in zip(res, res2))
+        det.net.close(); ref.net.close()
