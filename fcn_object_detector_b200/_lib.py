@@ -88,6 +88,9 @@ SIGNATURES = {
     'fcnod_aug_scratch_bytes': (_SZ, [_I]),
     'fcnod_aug_forward_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_train_head_scratch_bytes': (_SZ, []),
+    'fcnod_train_head_forward_device': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P, _P, _P]),
+    'fcnod_train_head_forward': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P]),
 }
 
 _lib = None

@@ -222,6 +222,23 @@ int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_
                       float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
                       int32_t* rects_out);
 
+/* ---- training head of models/train_val.prototxt (forward part) --------------------------
+ * Slice / Eltwise-PROD mask and normalisation chain (:36-72, :2237-2266), L1Loss x loss_weight (:2267-2274) and
+ * EuclideanLoss (:2275-2281) on the network's two outputs and the layer's five label grids, all NCHW float32:
+ * coverage, cvg_label [N][C][gh][gw]; bboxes, bbox_label, size_block, obj_block, cvg_block [N][4C][gh][gw].
+ * losses[0] = loss_bbox = sum|pred - target| / N (BEFORE its loss_weight), losses[1] = loss_coverage =
+ * sum (coverage - cvg_label)^2 / (2N).  d_coverage / d_bboxes (may be NULL) receive the gradients of
+ * loss_coverage + bbox_loss_weight * loss_bbox with respect to the two outputs (the first step of the backward pass).
+ * scratch: fcnod_train_head_scratch_bytes() bytes of device memory.  Sums are float64 in a fixed order. */
+size_t fcnod_train_head_scratch_bytes(void);
+int fcnod_train_head_forward_device(const float* coverage, const float* bboxes, const float* cvg_label, const float* bbox_label,
+                                    const float* size_block, const float* obj_block, const float* cvg_block, int N, int num_classes,
+                                    int gh, int gw, float bbox_loss_weight, float* losses, float* d_coverage, float* d_bboxes,
+                                    void* scratch, void* stream);
+int fcnod_train_head_forward(const float* coverage, const float* bboxes, const float* cvg_label, const float* bbox_label,
+                             const float* size_block, const float* obj_block, const float* cvg_block, int N, int num_classes, int gh,
+                             int gw, float bbox_loss_weight, float* losses, float* d_coverage, float* d_bboxes);   /* HOST buffers */
+
 #ifdef __cplusplus
 }
 #endif
