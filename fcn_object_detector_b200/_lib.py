@@ -25,6 +25,12 @@ class PostnetParams(C.Structure):
                 ('skip_background', C.c_int), ('min_height', C.c_int)]
 
 
+class PhotoDraw(C.Structure):
+    _fields_ = [('blur_kind', C.c_int32), ('blur_k', C.c_int32), ('gauss_radius', C.c_int32), ('_pad0', C.c_int32),
+                ('gauss_w', C.c_double * 13), ('sharpen', C.c_float * 9), ('add', C.c_int32 * 3), ('mul', C.c_float * 3),
+                ('_pad1', C.c_int32), ('gray_alpha', C.c_double)]
+
+
 class AugDraw(C.Structure):
     _fields_ = [('flip', C.c_int32), ('shift_x', C.c_int32), ('shift_y', C.c_int32),
                 ('sign_x', C.c_int32), ('sign_y', C.c_int32), ('_pad', C.c_int32),
@@ -88,6 +94,8 @@ SIGNATURES = {
     'fcnod_aug_scratch_bytes': (_SZ, [_I]),
     'fcnod_aug_forward_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_photo_augment_device': (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
+    'fcnod_photo_augment': (_I, [_P, _P, _P, _I, _I, _I, _P]),
     'fcnod_train_head_scratch_bytes': (_SZ, []),
     'fcnod_train_head_forward_device': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P, _P, _P]),
     'fcnod_train_head_forward': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P]),

@@ -24,4 +24,8 @@ int preprocess_num_launches();
 void preprocess_s2d_launch(const uint8_t* images_dev, int B, int src_h, int src_w, int net_h, int net_w, void* s2d_dev, int Wp,
                            int Hp, int padl, void* scratch, cudaStream_t stream);
 
+// photo.cu: in -> out (tmp is scratch); sizes may be null
+void photo_launch(const uint8_t* in, uint8_t* out, uint8_t* tmp, const int32_t* sizes, const fcnod_photo_draw* draws, int N, int H,
+                  int W, cudaStream_t stream);
+
 }  // namespace fcnod

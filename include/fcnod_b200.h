@@ -222,6 +222,27 @@ int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_
                       float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
                       int32_t* rects_out);
 
+/* ---- photometric augmentation of the layer (argumentation_engine.py:308-322, imgaug chain) ----
+ * Host-made draws for one image.  blur_kind: 0 none, 1 GaussianBlur (gauss_radius = int(4 sigma + 0.5) <= 12, gauss_w[i] =
+ * normalised weight at distance i, computed on the host as scipy.ndimage does), 2 AverageBlur (blur_k in 2..7),
+ * 3 MedianBlur (blur_k in {3, 5, 7}).  sharpen = the 3x3 filter2D matrix (1-a) * identity + a * [[-1..],[-1, 8+l, -1],[..]]
+ * in float32, row-major (identity = off).  add / mul per channel (equal entries when not per_channel).  gray_alpha 0 = off. */
+typedef struct fcnod_photo_draw {
+    int32_t blur_kind, blur_k, gauss_radius, _pad0;
+    double gauss_w[13];
+    float sharpen[9];
+    int32_t add[3];
+    float mul[3];
+    int32_t _pad1;
+    double gray_alpha;
+} fcnod_photo_draw;
+/* images / out / tmp: [N][H][W][3] uint8 (three distinct buffers); sizes [N][2] int32 = valid (h, w) of each image inside
+ * the common H x W pitch, rows packed at the image's own width (NULL: every image is H x W).  Three launches. */
+int fcnod_photo_augment_device(const uint8_t* images, const int32_t* sizes, const fcnod_photo_draw* draws, int N, int H, int W,
+                               uint8_t* out, uint8_t* tmp, void* stream);
+int fcnod_photo_augment(const uint8_t* images, const int32_t* sizes, const fcnod_photo_draw* draws, int N, int H, int W,
+                        uint8_t* out);   /* HOST buffers */
+
 /* ---- training head of models/train_val.prototxt (forward part) --------------------------
  * Slice / Eltwise-PROD mask and normalisation chain (:36-72, :2237-2266), L1Loss x loss_weight (:2267-2274) and
  * EuclideanLoss (:2275-2281) on the network's two outputs and the layer's five label grids, all NCHW float32:

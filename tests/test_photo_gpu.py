@@ -1,0 +1,70 @@
+"""GPU: photometric augmentation (imgaug chain of argumentation_engine.py:308-322) through the C ABI, bit-exact against the
+scipy / cv2 calls imgaug makes, given the same draws."""
+import numpy as np
+import pytest
+
+from oracle import photo_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(images, draws, sizes=None):
+    from fcn_object_detector_b200.photometric import photo_augment
+    got = photo_augment(images, draws, sizes)
+    bad = 0
+    for i, d in enumerate(draws):
+        h, w = (images.shape[1], images.shape[2]) if sizes is None else sizes[i]
+        src = images[i].reshape(-1)[:h * w * 3].reshape(h, w, 3)
+        exp = photo_ref.apply(src, d)
+        g = got[i].reshape(-1)[:h * w * 3].reshape(h, w, 3)
+        nbad, worst = int((g != exp).sum()), int(np.abs(g.astype(int) - exp).max())
+        if d['sharpen_alpha'] == 0.0:
+            assert nbad == 0, (i, d, worst, nbad)
+        else:
+            # cv2.filter2D accumulates with or without FMA depending on the host CPU's SIMD dispatch (the same call gives
+            # different bits on different machines): a sum that lands within an ulp of x.5 may round the other way.  The
+            # device restates the non-FMA order; allow the rare one-grey-level flip (amplified at most by Multiply 1.25).
+            assert worst <= 2 and nbad <= max(2, int(0.005 * g.size)), (i, d, worst, nbad)
+        bad += nbad
+    return got
+
+
+def test_each_stage_alone_matches_the_library_call():
+    from fcn_object_detector_b200.photometric import IDENTITY
+    rs = np.random.RandomState(0)
+    img = rs.randint(0, 256, (1, 61, 83, 3)).astype(np.uint8)
+    img[0, :5, :5] = 0; img[0, -6:, -6:] = 255                       # saturation at both ends
+    cases = [dict(IDENTITY)]
+    cases += [dict(IDENTITY, blur_kind=1, sigma=s) for s in (0.0011, 0.3, 0.8, 1.7, 2.999)]
+    cases += [dict(IDENTITY, blur_kind=2, blur_k=k) for k in range(2, 8)]
+    cases += [dict(IDENTITY, blur_kind=3, blur_k=k) for k in (3, 5, 7)]
+    cases += [dict(IDENTITY, sharpen_alpha=a, sharpen_lightness=l) for a, l in ((0.37, 1.2), (1.0, 0.75), (0.91, 1.5), (0.05, 1.0))]
+    cases += [dict(IDENTITY, add=a) for a in ([21, 21, 21], [-2, 0, 7], [-2, -2, -2])]
+    cases += [dict(IDENTITY, mul=m) for m in ([1.25, 1.25, 1.25], [0.75, 1.0, 1.1234567], [0.9999999, 1.0000001, 0.8])]
+    cases += [dict(IDENTITY, gray_alpha=a) for a in (0.0005, 0.0011, 0.25, 0.5)]
+    for d in cases:
+        _check(img, [d])
+
+
+def test_random_chains_batch_and_ragged_sizes():
+    """The whole chain with drawn parameters, a batch of images, and crops of different sizes inside one pitch (the layer
+    augments crops: every image's borders are its own)."""
+    from fcn_object_detector_b200.photometric import draw_photo
+    rs = np.random.RandomState(4)
+    N, H, W = 12, 96, 128
+    imgs = rs.randint(0, 256, (N, H, W, 3)).astype(np.uint8)
+    draws = [draw_photo(rs) for _ in range(N)]
+    assert {d['blur_kind'] for d in draws} >= {1, 2, 3}
+    _check(imgs, draws)
+    sizes = np.asarray([[int(rs.randint(8, H + 1)), int(rs.randint(8, W + 1))] for _ in range(N)], np.int32)
+    sizes[0] = [H, W]; sizes[1] = [1, 9]; sizes[2] = [7, 1]          # degenerate crops: 1-pixel-high / wide
+    _check(imgs, draws, sizes)
+
+
+def test_tiny_images_and_large_kernels():
+    from fcn_object_detector_b200.photometric import IDENTITY
+    rs = np.random.RandomState(9)
+    img = rs.randint(0, 256, (1, 3, 4, 3)).astype(np.uint8)
+    for d in (dict(IDENTITY, blur_kind=1, sigma=2.9), dict(IDENTITY, blur_kind=2, blur_k=7), dict(IDENTITY, blur_kind=3, blur_k=7),
+              dict(IDENTITY, sharpen_alpha=1.0, sharpen_lightness=1.5)):
+        _check(img, [d])
