@@ -94,6 +94,9 @@ SIGNATURES = {
     'fcnod_aug_scratch_bytes': (_SZ, [_I]),
     'fcnod_aug_forward_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_aug_photo_scratch_bytes': (_SZ, [_I, _I, _I]),
+    'fcnod_aug_forward_photo_device': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_aug_forward_photo': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_photo_augment_device': (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
     'fcnod_photo_augment': (_I, [_P, _P, _P, _I, _I, _I, _P]),
     'fcnod_train_head_scratch_bytes': (_SZ, []),

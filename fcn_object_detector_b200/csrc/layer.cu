@@ -119,20 +119,48 @@ __device__ __forceinline__ long src_index(const AugGeom& g, int src_h, int src_w
     return (long)fy * src_w + fx;
 }
 
+// Pixel (y, x), channel c of image n's crop.  U8 = false: straight from the float bottom `data_in` (CHW planes) through
+// the flip / crop mapping; U8 = true: from the photometrically augmented crop (uint8 HWC, rows packed at the crop width,
+// flip and crop already applied by aug_crop_u8_kernel).
+template <bool U8>
+__device__ __forceinline__ float crop_px(const void* __restrict__ base, const AugGeom& g, int src_h, int src_w, int n, int c, int y, int x) {
+    if (U8) return (float)static_cast<const uint8_t*>(base)[(size_t)n * src_h * src_w * 3 + ((size_t)y * g.cw + x) * 3 + c];
+    return static_cast<const float*>(base)[((size_t)n * 3 + c) * src_h * src_w + src_index(g, src_h, src_w, y, x)];
+}
+
+// flipped + cropped source -> uint8 HWC crop (the image `color_space_argumentation` sees, argumentation_engine.py:176), and
+// its (h, w) for the photometric kernels.  Pixel values of the bottom are integers 0..255 held in floats.
+__global__ void __launch_bounds__(256) aug_crop_u8_kernel(const float* __restrict__ data_in, int src_h, int src_w,
+                                                          const AugGeom* __restrict__ geom, uint8_t* __restrict__ crop,
+                                                          int32_t* __restrict__ sizes) {
+    const int n = blockIdx.y;
+    const AugGeom g = geom[n];
+    if (blockIdx.x == 0 && threadIdx.x == 0) { sizes[2 * n] = g.ch; sizes[2 * n + 1] = g.cw; }
+    const long npx = (long)g.cw * g.ch;
+    uint8_t* o = crop + (size_t)n * src_h * src_w * 3;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < npx; i += (long)gridDim.x * blockDim.x) {
+        const int y = (int)(i / g.cw), x = (int)(i - (long)y * g.cw);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float v = crop_px<false>(data_in, g, src_h, src_w, n, c, y, x);
+            o[i * 3 + c] = (uint8_t)fminf(fmaxf(v, 0.f), 255.f);
+        }
+    }
+}
+
 // grid (chunks, N): fp32 min / max of (pixel - mean_c) over the crop, all 3 channels
-__global__ void __launch_bounds__(256) aug_minmax_kernel(const float* __restrict__ data_in, int src_h, int src_w,
+template <bool U8>
+__global__ void __launch_bounds__(256) aug_minmax_kernel(const void* __restrict__ data_in, int src_h, int src_w,
                                                          AugGeom* __restrict__ geom) {
     const int n = blockIdx.y;
     const AugGeom g = geom[n];
     const long npx = (long)g.cw * g.ch;
     float mn = INFINITY, mx = -INFINITY;
-    const float* img = data_in + (size_t)n * 3 * src_h * src_w;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < npx; i += (long)gridDim.x * blockDim.x) {
         const int y = (int)(i / g.cw), x = (int)(i - (long)y * g.cw);
-        const long si = src_index(g, src_h, src_w, y, x);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const float v = __fsub_rn(img[(size_t)c * src_h * src_w + si], mean_of(c));
+            const float v = __fsub_rn(crop_px<U8>(data_in, g, src_h, src_w, n, c, y, x), mean_of(c));
             mn = fminf(mn, v); mx = fmaxf(mx, v);
         }
     }
@@ -154,8 +182,8 @@ __global__ void __launch_bounds__(256) aug_minmax_kernel(const float* __restrict
 }
 
 // thread per VEC horizontally adjacent output pixels, all 3 channels; NCHW fp32 out
-template <int VEC>
-__global__ void __launch_bounds__(256) aug_resample_kernel(const float* __restrict__ data_in, int src_h, int src_w,
+template <int VEC, bool U8>
+__global__ void __launch_bounds__(256) aug_resample_kernel(const void* __restrict__ data_in, int src_h, int src_w,
                                                            const AugGeom* __restrict__ geom, int N, int net_h, int net_w,
                                                            float* __restrict__ top) {
     const int wv = net_w / VEC;
@@ -174,7 +202,6 @@ __global__ void __launch_bounds__(256) aug_resample_kernel(const float* __restri
         } else {
             const float mn = dec_f32(g.mn_enc), mx = dec_f32(g.mx_enc);
             const float range = __fsub_rn(mx, mn);
-            const float* img = data_in + (size_t)n * 3 * src_h * src_w;
             const bool same = (g.cw == net_w && g.ch == net_h);
             const double sy = (double)g.ch / (double)net_h, sx = (double)g.cw / (double)net_w;
             double fyd = ((double)oy + 0.5) * sy - 0.5;
@@ -192,18 +219,15 @@ __global__ void __launch_bounds__(256) aug_resample_kernel(const float* __restri
                 if (x0 < 0) { x0 = 0; ax = 0.f; }
                 if (x0 >= g.cw - 1) { x0 = g.cw - 1; ax = 0.f; }
                 const int x1 = min(x0 + 1, g.cw - 1);
-                const long i00 = src_index(g, src_h, src_w, y0, x0), i01 = src_index(g, src_h, src_w, y0, x1);
-                const long i10 = src_index(g, src_h, src_w, y1, x0), i11 = src_index(g, src_h, src_w, y1, x1);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const float* pl = img + (size_t)c * src_h * src_w;
                     const float m = mean_of(c);
                     // (im - min) / (max - min) in fp32 (:302), then bilinear
-                    const float p00 = __fdiv_rn(__fsub_rn(__fsub_rn(pl[i00], m), mn), range);
+                    const float p00 = __fdiv_rn(__fsub_rn(__fsub_rn(crop_px<U8>(data_in, g, src_h, src_w, n, c, y0, x0), m), mn), range);
                     if (same) { res[c][v] = p00; continue; }
-                    const float p01 = __fdiv_rn(__fsub_rn(__fsub_rn(pl[i01], m), mn), range);
-                    const float p10 = __fdiv_rn(__fsub_rn(__fsub_rn(pl[i10], m), mn), range);
-                    const float p11 = __fdiv_rn(__fsub_rn(__fsub_rn(pl[i11], m), mn), range);
+                    const float p01 = __fdiv_rn(__fsub_rn(__fsub_rn(crop_px<U8>(data_in, g, src_h, src_w, n, c, y0, x1), m), mn), range);
+                    const float p10 = __fdiv_rn(__fsub_rn(__fsub_rn(crop_px<U8>(data_in, g, src_h, src_w, n, c, y1, x0), m), mn), range);
+                    const float p11 = __fdiv_rn(__fsub_rn(__fsub_rn(crop_px<U8>(data_in, g, src_h, src_w, n, c, y1, x1), m), mn), range);
                     const float tp = p00 * (1.f - ax) + p01 * ax, bt = p10 * (1.f - ax) + p11 * ax;
                     res[c][v] = tp * (1.f - ay) + bt * ay;
                 }
@@ -375,12 +399,18 @@ int fcnod_label_raster(const int32_t* rects, const int32_t* labels, const int32_
 
 size_t fcnod_aug_scratch_bytes(int N) { return (size_t)(N > 0 ? N : 0) * sizeof(AugGeom); }
 
-int fcnod_aug_forward_device(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N, int src_h,
-                             int src_w, int net_h, int net_w, int stride, int num_classes, float* top_data, float* fg,
-                             float* bbox, float* size, float* obj, float* cvg, int32_t* rects_out, void* scratch,
-                             void* stream) {
+size_t fcnod_aug_photo_scratch_bytes(int N, int src_h, int src_w) {
+    if (N <= 0 || src_h <= 0 || src_w <= 0) return 0;
+    return 3 * align_up((size_t)N * src_h * src_w * 3, 256) + align_up((size_t)N * 8, 256);
+}
+
+int fcnod_aug_forward_photo_device(const float* data_in, const float* label, const fcnod_aug_draw* draws,
+                                   const fcnod_photo_draw* photo, int N, int src_h, int src_w, int net_h, int net_w, int stride,
+                                   int num_classes, float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                                   int32_t* rects_out, void* scratch, void* photo_scratch, void* stream) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(data_in && label && draws && top_data && fg && bbox && size && obj && cvg && scratch, "null argument");
+    FCNOD_CHECK(!photo || photo_scratch, "photo draws need photo_scratch (fcnod_aug_photo_scratch_bytes)");
     check_layer_dims(N, net_h, net_w, stride, num_classes);
     FCNOD_CHECK(src_h > 0 && src_w > 0, "layer: bad source size");
     cudaStream_t s = (cudaStream_t)stream;
@@ -388,21 +418,51 @@ int fcnod_aug_forward_device(const float* data_in, const float* label, const fcn
     const int gh = net_h / stride, gw = net_w / stride;
     aug_geometry_kernel<<<ceil_div(N, 128), 128, 0, s>>>(label, draws, N, src_h, src_w, net_h, net_w, geom, rects_out);
     FCNOD_CUDA(cudaGetLastError());
-    aug_minmax_kernel<<<dim3(32, N), 256, 0, s>>>(data_in, src_h, src_w, geom);
-    FCNOD_CUDA(cudaGetLastError());
-    if (net_w % 4 == 0)
-        aug_resample_kernel<4><<<grid_1d((long)N * net_h * (net_w / 4), 256), 256, 0, s>>>(data_in, src_h, src_w, geom, N, net_h, net_w, top_data);
-    else
-        aug_resample_kernel<1><<<grid_1d((long)N * net_h * net_w, 256), 256, 0, s>>>(data_in, src_h, src_w, geom, N, net_h, net_w, top_data);
+    const long np4 = (long)N * net_h * (net_w / 4), np1 = (long)N * net_h * net_w;
+    if (photo) {
+        // T4 (argumentation_engine.py:176): the flipped, cropped uint8 image goes through the imgaug chain before demeaning
+        const size_t img_bytes = align_up((size_t)N * src_h * src_w * 3, 256);
+        uint8_t* crop = static_cast<uint8_t*>(photo_scratch);
+        uint8_t* aug = crop + img_bytes;
+        uint8_t* tmp = aug + img_bytes;
+        int32_t* sizes = reinterpret_cast<int32_t*>(tmp + img_bytes);
+        aug_crop_u8_kernel<<<dim3(32, N), 256, 0, s>>>(data_in, src_h, src_w, geom, crop, sizes);
+        FCNOD_CUDA(cudaGetLastError());
+        photo_launch(crop, aug, tmp, sizes, photo, N, src_h, src_w, s);
+        aug_minmax_kernel<true><<<dim3(32, N), 256, 0, s>>>(aug, src_h, src_w, geom);
+        FCNOD_CUDA(cudaGetLastError());
+        if (net_w % 4 == 0) aug_resample_kernel<4, true><<<grid_1d(np4, 256), 256, 0, s>>>(aug, src_h, src_w, geom, N, net_h, net_w, top_data);
+        else aug_resample_kernel<1, true><<<grid_1d(np1, 256), 256, 0, s>>>(aug, src_h, src_w, geom, N, net_h, net_w, top_data);
+    } else {
+        aug_minmax_kernel<false><<<dim3(32, N), 256, 0, s>>>(data_in, src_h, src_w, geom);
+        FCNOD_CUDA(cudaGetLastError());
+        if (net_w % 4 == 0) aug_resample_kernel<4, false><<<grid_1d(np4, 256), 256, 0, s>>>(data_in, src_h, src_w, geom, N, net_h, net_w, top_data);
+        else aug_resample_kernel<1, false><<<grid_1d(np1, 256), 256, 0, s>>>(data_in, src_h, src_w, geom, N, net_h, net_w, top_data);
+    }
     FCNOD_CUDA(cudaGetLastError());
     launch_label_raster((const int32_t*)0, (const int32_t*)0, (const int32_t*)0, geom, N, 1, gh, gw, stride, num_classes, fg, bbox,
                         size, obj, cvg, s);
     FCNOD_API_END
 }
 
+int fcnod_aug_forward_device(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N, int src_h,
+                             int src_w, int net_h, int net_w, int stride, int num_classes, float* top_data, float* fg,
+                             float* bbox, float* size, float* obj, float* cvg, int32_t* rects_out, void* scratch,
+                             void* stream) {
+    return fcnod_aug_forward_photo_device(data_in, label, draws, 0, N, src_h, src_w, net_h, net_w, stride, num_classes, top_data, fg,
+                                          bbox, size, obj, cvg, rects_out, scratch, 0, stream);
+}
+
 int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N, int src_h, int src_w,
                       int net_h, int net_w, int stride, int num_classes, float* top_data, float* fg, float* bbox, float* size,
                       float* obj, float* cvg, int32_t* rects_out) {
+    return fcnod_aug_forward_photo(data_in, label, draws, 0, N, src_h, src_w, net_h, net_w, stride, num_classes, top_data, fg, bbox,
+                                   size, obj, cvg, rects_out);
+}
+
+int fcnod_aug_forward_photo(const float* data_in, const float* label, const fcnod_aug_draw* draws, const fcnod_photo_draw* photo,
+                            int N, int src_h, int src_w, int net_h, int net_w, int stride, int num_classes, float* top_data,
+                            float* fg, float* bbox, float* size, float* obj, float* cvg, int32_t* rects_out) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(data_in && label && draws && top_data && fg && bbox && size && obj && cvg, "null argument");
     check_layer_dims(N, net_h, net_w, stride, num_classes);
@@ -413,19 +473,23 @@ int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_
     cudaStream_t s = ws.stream();
     ws.reserve(Workspace::padded(nin * 4) + Workspace::padded((size_t)N * 5 * 4) + Workspace::padded((size_t)N * sizeof(fcnod_aug_draw)) +
                Workspace::padded((size_t)N * 16) + Workspace::padded(fcnod_aug_scratch_bytes(N)) +
-               Workspace::padded((ntop + nfg + 4 * n4) * 4));
+               Workspace::padded((ntop + nfg + 4 * n4) * 4) +
+               (photo ? Workspace::padded((size_t)N * sizeof(fcnod_photo_draw)) + Workspace::padded(fcnod_aug_photo_scratch_bytes(N, src_h, src_w)) : 0));
     float* d_in = ws.take<float>(nin);
     float* d_label = ws.take<float>((size_t)N * 5);
     fcnod_aug_draw* d_draw = ws.take<fcnod_aug_draw>((size_t)N);
     int32_t* d_rect = ws.take<int32_t>((size_t)N * 4);
     void* d_scr = ws.take<char>(fcnod_aug_scratch_bytes(N));
     float* d_out = ws.take<float>(ntop + nfg + 4 * n4);
+    fcnod_photo_draw* d_photo = photo ? ws.take<fcnod_photo_draw>((size_t)N) : 0;
+    void* d_pscr = photo ? ws.take<char>(fcnod_aug_photo_scratch_bytes(N, src_h, src_w)) : 0;
+    if (photo) FCNOD_CUDA(cudaMemcpyAsync(d_photo, photo, (size_t)N * sizeof(fcnod_photo_draw), cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaMemcpyAsync(d_in, data_in, nin * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaMemcpyAsync(d_label, label, (size_t)N * 5 * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaMemcpyAsync(d_draw, draws, (size_t)N * sizeof(fcnod_aug_draw), cudaMemcpyHostToDevice, s));
     float *dtop = d_out, *dfg = dtop + ntop, *db = dfg + nfg, *ds = db + n4, *dobj = ds + n4, *dc = dobj + n4;
-    int rc = fcnod_aug_forward_device(d_in, d_label, d_draw, N, src_h, src_w, net_h, net_w, stride, num_classes, dtop, dfg, db,
-                                      ds, dobj, dc, d_rect, d_scr, s);
+    int rc = fcnod_aug_forward_photo_device(d_in, d_label, d_draw, d_photo, N, src_h, src_w, net_h, net_w, stride, num_classes, dtop,
+                                            dfg, db, ds, dobj, dc, d_rect, d_scr, d_pscr, s);
     FCNOD_CHECK(rc == 0, fcnod_last_error());
     FCNOD_CUDA(cudaMemcpyAsync(top_data, dtop, ntop * 4, cudaMemcpyDeviceToHost, s));
     FCNOD_CUDA(cudaMemcpyAsync(fg, dfg, nfg * 4, cudaMemcpyDeviceToHost, s));

@@ -11,8 +11,11 @@ setup/reshape/forward/backward follow
 maths is identical -- SURVEY.md F5/A4).  The random draws are made here, on the
 host, in the reference's order (argumentation_engine.py:146,165-166,200-202) with
 Python's `random`; everything else (flip, crop, demean, resize, label grids) runs
-in libfcnod_b200 (fcnod_aug_forward).  Colour-space augmentation (imgaug, :176)
-is photometric only and not part of this path.
+in libfcnod_b200 (fcnod_aug_forward).  Colour-space augmentation (the imgaug chain at
+argumentation_engine.py:176,308-322) is photometric only -- it cannot change the label grids --
+and is OFF by default so that the grids and the image top are reproducible from the geometric
+draws alone; `layer.color_aug = True` (or passing `photo=` draws to forward) runs it on the device
+where the reference has it, between the crop and the demeaning (photometric.py, fcnod_aug_forward_photo).
 """
 import ctypes as C
 import math
@@ -71,7 +74,10 @@ class DataArgumentationLayer(caffe.Layer):
             raise ValueError('Parameter string missing or data type is wrong!')
         self.rng = random.Random()
         self.rng.seed()
+        self.color_aug = getattr(self, 'color_aug', False)
+        self.np_rng = np.random.RandomState()          # imgaug draws from numpy's generator (imgaug/imgaug.py:30)
         self.last_draws = None
+        self.last_photo = None
         self.last_rects = None
 
     def reshape(self, bottom, top):
@@ -86,23 +92,31 @@ class DataArgumentationLayer(caffe.Layer):
         top[4].reshape(n_images, channels, out_size_y, out_size_x)             # obj-block
         top[5].reshape(n_images, channels, out_size_y, out_size_x)             # coverage-block
 
-    def forward(self, bottom, top, draws=None):
+    def forward(self, bottom, top, draws=None, photo=None):
         data_in = np.ascontiguousarray(bottom[0].data, dtype=np.float32)
         label = np.ascontiguousarray(np.asarray(bottom[1].data, dtype=np.float32).reshape(data_in.shape[0], -1)[:, :5])
         N, _, src_h, src_w = data_in.shape
         if draws is None:
             draws = [draw_augmentation(self.rng, src_w, src_h, [int(v) for v in label[i, :4]]) for i in range(N)]
         darr = (_lib.AugDraw * N)(*draws)
+        if photo is None and self.color_aug:
+            from .photometric import draw_photo
+            photo = [draw_photo(self.np_rng) for _ in range(N)]
+        parr = None
+        if photo is not None:
+            from .photometric import make_draw
+            parr = (_lib.PhotoDraw * N)(*[make_draw(d) for d in photo])
         rects = np.zeros((N, 4), np.int32)
         outs = [top[i].data for i in range(6)]
         for o in outs:
             if o.dtype != np.float32 or not o.flags['C_CONTIGUOUS']:
                 raise ValueError('top blobs must be contiguous float32')
-        _lib.check(_lib.lib().fcnod_aug_forward(_lib.ptr(data_in), _lib.ptr(label), darr, N, src_h, src_w,
-                                                self.image_size_y, self.image_size_x, self.stride, self.num_classes,
-                                                _lib.ptr(outs[0]), _lib.ptr(outs[1]), _lib.ptr(outs[2]), _lib.ptr(outs[3]),
-                                                _lib.ptr(outs[4]), _lib.ptr(outs[5]), _lib.ptr(rects)))
+        _lib.check(_lib.lib().fcnod_aug_forward_photo(_lib.ptr(data_in), _lib.ptr(label), darr, parr, N, src_h, src_w,
+                                                      self.image_size_y, self.image_size_x, self.stride, self.num_classes,
+                                                      _lib.ptr(outs[0]), _lib.ptr(outs[1]), _lib.ptr(outs[2]), _lib.ptr(outs[3]),
+                                                      _lib.ptr(outs[4]), _lib.ptr(outs[5]), _lib.ptr(rects)))
         self.last_draws = draws
+        self.last_photo = photo
         self.last_rects = rects
 
     def backward(self, top, propagate_down, bottom):

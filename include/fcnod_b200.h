@@ -243,6 +243,18 @@ int fcnod_photo_augment_device(const uint8_t* images, const int32_t* sizes, cons
 int fcnod_photo_augment(const uint8_t* images, const int32_t* sizes, const fcnod_photo_draw* draws, int N, int H, int W,
                         uint8_t* out);   /* HOST buffers */
 
+/* The layer forward WITH the photometric stage where the reference has it (argumentation_engine.py:176: after flip + crop,
+ * before demean + resize): the flipped / cropped source is materialised as a uint8 crop, run through the chain above with
+ * every crop's own borders, and demeaned / resampled from there.  photo = NULL is fcnod_aug_forward*. */
+size_t fcnod_aug_photo_scratch_bytes(int N, int src_h, int src_w);
+int fcnod_aug_forward_photo_device(const float* data_in, const float* label, const fcnod_aug_draw* draws,
+                                   const fcnod_photo_draw* photo, int N, int src_h, int src_w, int net_h, int net_w, int stride,
+                                   int num_classes, float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                                   int32_t* rects_out, void* scratch, void* photo_scratch, void* stream);
+int fcnod_aug_forward_photo(const float* data_in, const float* label, const fcnod_aug_draw* draws, const fcnod_photo_draw* photo,
+                            int N, int src_h, int src_w, int net_h, int net_w, int stride, int num_classes, float* top_data,
+                            float* fg, float* bbox, float* size, float* obj, float* cvg, int32_t* rects_out);   /* HOST buffers */
+
 /* ---- training head of models/train_val.prototxt (forward part) --------------------------
  * Slice / Eltwise-PROD mask and normalisation chain (:36-72, :2237-2266), L1Loss x loss_weight (:2267-2274) and
  * EuclideanLoss (:2275-2281) on the network's two outputs and the layer's five label grids, all NCHW float32:

@@ -180,9 +180,10 @@ def resize_rect(rect, src_w, src_h, net_w, net_h):
     return (int(xt), int(yt), int(xb - xt), int(yb - yt))
 
 
-def augment_one(img_hwc, rect, draw, net_w, net_h):
+def augment_one(img_hwc, rect, draw, net_w, net_h, photo=None):
     """random_argumentation (:143-188, one rect) + resize_image_and_labels (:114-138).
-    draw = dict(flip, f1, f2, shift_x, shift_y, sign_x, sign_y).  Returns (img float32 HWC, rect)."""
+    draw = dict(flip, f1, f2, shift_x, shift_y, sign_x, sign_y); photo = optional draws of the colour augmentation (:176,
+    oracle.photo_ref), applied to the uint8 crop.  Returns (img float32 HWC, rect)."""
     H, W = img_hwc.shape[:2]
     flag = draw['flip']
     if -2 < flag < 2:
@@ -194,13 +195,16 @@ def augment_one(img_hwc, rect, draw, net_w, net_h):
     (x, y, w, h), r = crop_window(W, H, r, draw['f1'], draw['f2'], draw['shift_x'],
                                   draw['shift_y'], draw['sign_x'], draw['sign_y'])
     roi = im[int(y):int(y + h), int(x):int(x + w)]
+    if photo is not None and roi.size:
+        from . import photo_ref
+        roi = photo_ref.apply(np.clip(roi, 0, 255).astype(np.uint8), photo).astype(np.float32)     # :176
     roi = demean_f32(np.ascontiguousarray(roi))
     out = resize_bilinear(roi, net_w, net_h).astype(np.float32)
     r = resize_rect(r, roi.shape[1], roi.shape[0], net_w, net_h)
     return out, r, roi.shape[:2]
 
 
-def layer_forward(data_in, label, draws, net_w=448, net_h=448, stride=16, num_classes=1):
+def layer_forward(data_in, label, draws, net_w=448, net_h=448, stride=16, num_classes=1, photo=None):
     """README.md:60-76 contract: data_in (N,3,Hs,Ws), label (N,1,1,5)=[x,y,w,h,label].
     Returns the 6 tops (float32): data, coverage-label, bbox-label, size-block, obj-block, coverage-block."""
     N = data_in.shape[0]
@@ -213,7 +217,7 @@ def layer_forward(data_in, label, draws, net_w=448, net_h=448, stride=16, num_cl
         lab = np.asarray(label[i]).reshape(-1)
         rect = [int(v) for v in lab[:4]]
         cls = int(lab[4])
-        im, r, _ = augment_one(img, rect, draws[i], net_w, net_h)
+        im, r, _ = augment_one(img, rect, draws[i], net_w, net_h, None if photo is None else photo[i])
         fg, bl, sl, ol, cl = bounding_box_parameterized_labels(net_h, net_w, stride, num_classes, [r], [cls])
         top[0][i] = im.transpose(2, 0, 1)
         top[1][i] = fg; top[2][i] = bl; top[3][i] = sl; top[4][i] = ol; top[5][i] = cl

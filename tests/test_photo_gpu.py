@@ -68,3 +68,59 @@ def test_tiny_images_and_large_kernels():
     for d in (dict(IDENTITY, blur_kind=1, sigma=2.9), dict(IDENTITY, blur_kind=2, blur_k=7), dict(IDENTITY, blur_kind=3, blur_k=7),
               dict(IDENTITY, sharpen_alpha=1.0, sharpen_lightness=1.5)):
         _check(img, [d])
+
+
+def test_layer_forward_with_colour_augmentation():
+    """The layer with the photometric stage where the reference has it (argumentation_engine.py:176): label grids still
+    bit-exact (the stage cannot touch them), image top within 1e-5 of the oracle that applies the same draws to the uint8 crop
+    (draws without sharpening, whose cv2 arithmetic is not bit-stable across host CPUs; sharpened draws within 2 grey levels)."""
+    import random
+    from fcn_object_detector_b200 import _lib
+    from fcn_object_detector_b200.data_argumentation_layer import DataArgumentationLayer
+    from fcn_object_detector_b200.photometric import IDENTITY, draw_photo
+    from oracle import layer_ref
+    from tests.test_layer_gpu import _B
+    from tests.util import bits_equal
+    rs = np.random.RandomState(3)
+    N, Hs, Ws = 8, 240, 320
+    data = rs.randint(0, 256, (N, 3, Hs, Ws)).astype(np.float32)
+    lab = np.zeros((N, 1, 1, 5), np.float32)
+    rng = random.Random(7)
+    draws, photo = [], []
+    for i in range(N):
+        w, h = int(rs.randint(24, 120)), int(rs.randint(24, 120))
+        rect = [int(rs.randint(0, Ws - w)), int(rs.randint(0, Hs - h)), w, h]
+        lab[i, 0, 0] = rect + [0]
+        draws.append(layer_ref.draw_params(rng, Ws, Hs, rect))
+        d = draw_photo(rs)
+        if i % 2 == 0:
+            d.update(sharpen_alpha=0.0)                        # identity matrix: every stage bit-stable
+        photo.append(d)
+    L = DataArgumentationLayer()
+    L.param_str = '448, 448,16, 1'
+    bottom = [_B(data), _B(lab)]
+    top = [_B(np.zeros((1,), np.float32)) for _ in range(6)]
+    L.setup(bottom, top); L.reshape(bottom, top)
+    cdraws = []
+    for d in draws:
+        a = _lib.AugDraw()
+        for k, v in d.items():
+            setattr(a, k, v)
+        cdraws.append(a)
+    L.forward(bottom, top, draws=cdraws, photo=photo)
+    exp, rects = layer_ref.layer_forward(data, lab, draws, photo=photo)
+    assert np.array_equal(L.last_rects, np.asarray(rects, np.int32))
+    for k in range(1, 6):
+        assert bits_equal(top[k].data, exp[k]), k
+    for i in range(N):
+        err = np.abs(top[0].data[i] - exp[0][i]).max()
+        assert err < (1e-5 if photo[i]['sharpen_alpha'] == 0.0 else 2.5 / 255.0), (i, err, photo[i])
+    # and it is not a no-op
+    plain = [_B(np.zeros((1,), np.float32)) for _ in range(6)]
+    L.reshape(bottom, plain); L.forward(bottom, plain, draws=cdraws)
+    assert np.abs(plain[0].data - top[0].data).max() > 0.01
+    assert all(bits_equal(plain[k].data, top[k].data) for k in range(1, 6))
+    # color_aug = True draws its own parameters
+    L.color_aug = True
+    L.forward(bottom, top, draws=cdraws)
+    assert L.last_photo is not None and len(L.last_photo) == N
