@@ -25,6 +25,11 @@ class PostnetParams(C.Structure):
                 ('skip_background', C.c_int), ('min_height', C.c_int)]
 
 
+class Paste(C.Structure):
+    _fields_ = [('roi_offset', C.c_int32), ('w', C.c_int32), ('h', C.c_int32), ('cx', C.c_int32), ('cy', C.c_int32),
+                ('label', C.c_int32)]
+
+
 class PhotoDraw(C.Structure):
     _fields_ = [('blur_kind', C.c_int32), ('blur_k', C.c_int32), ('gauss_radius', C.c_int32), ('_pad0', C.c_int32),
                 ('gauss_w', C.c_double * 13), ('sharpen', C.c_float * 9), ('add', C.c_int32 * 3), ('mul', C.c_float * 3),
@@ -97,6 +102,8 @@ SIGNATURES = {
     'fcnod_aug_photo_scratch_bytes': (_SZ, [_I, _I, _I]),
     'fcnod_aug_forward_photo_device': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward_photo': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_composite_device': (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P]),
+    'fcnod_composite': (_I, [_P, _P, _I, _I, _I, _P, _P, _SZ, _P, _P]),
     'fcnod_photo_augment_device': (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
     'fcnod_photo_augment': (_I, [_P, _P, _P, _I, _I, _I, _P]),
     'fcnod_train_head_scratch_bytes': (_SZ, []),

@@ -229,3 +229,103 @@ int fcnod_photo_augment(const uint8_t* images, const int32_t* sizes, const fcnod
 }
 
 }  // extern "C"
+
+// ---- copy-paste synthesis: the compositing loop of ArgumentationEngineMapping.argument ------------------------------
+// /root/reference/scripts/data_argumentation_layer/argumentation_engine.py:723-728: for every placed proposal, in order,
+//     for j in range(h): for i in range(w): nx, ny = i + cx, j + cy
+//         if im_msk[j, i, 0] > 0 and nx < im_x and ny < im_y: img_output[ny, nx] = im_roi[j, i]; mask_output[ny, nx] = label + 1
+// (the per-pixel Python loop the HEAD layer spends its time in).  Here one thread owns one output pixel and walks the
+// image's proposals in order, keeping the LAST one that covers it with a set mask bit -- the same result as the sequential
+// overwrites.  Negative cx / cy (a proposal wider than the background) index from the far side, as numpy does.
+namespace fcnod {
+namespace {
+
+__global__ void __launch_bounds__(256) composite_kernel(uint8_t* __restrict__ images, uint8_t* __restrict__ masks, int H, int W,
+                                                        const uint8_t* __restrict__ rois, const uint8_t* __restrict__ roi_masks,
+                                                        const fcnod_paste* __restrict__ pastes, const int32_t* __restrict__ begin) {
+    const int n = blockIdx.y;
+    const int p0 = begin[n], p1 = begin[n + 1];
+    if (p0 == p1) return;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < H * W; t += gridDim.x * blockDim.x) {
+        const int y = t / W, x = t - y * W;
+        int hit = -1, hi = 0, hj = 0;
+        for (int q = p0; q < p1; ++q) {
+            const fcnod_paste P = pastes[q];
+            // Which (j, i) of the patch land on (y, x)?  ny = j + cy equals y directly, or -- numpy's negative indexing --
+            // ny = y - H < 0 wraps to y.  Up to two candidates per axis; the reference's loops run j, then i, upwards and the
+            // last write wins, so candidates are visited in that order.
+            const int jc[2] = {y - H - P.cy, y - P.cy}, ic[2] = {x - W - P.cx, x - P.cx};
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const int j = jc[a];
+                if (j < 0 || j >= P.h || (a == 0 ? j + P.cy >= 0 : j + P.cy < 0)) continue;
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const int i = ic[b];
+                    if (i < 0 || i >= P.w || (b == 0 ? i + P.cx >= 0 : i + P.cx < 0)) continue;
+                    if (roi_masks[(size_t)P.roi_offset + (size_t)j * P.w + i] > 0) { hit = q; hi = i; hj = j; }
+                }
+            }
+        }
+        if (hit >= 0) {
+            const fcnod_paste P = pastes[hit];
+            const uint8_t* s = rois + ((size_t)P.roi_offset + (size_t)hj * P.w + hi) * 3;
+            uint8_t* o = images + ((size_t)n * H * W + t) * 3;
+            o[0] = s[0]; o[1] = s[1]; o[2] = s[2];
+            masks[(size_t)n * H * W + t] = (uint8_t)(P.label + 1);
+        }
+    }
+}
+
+}  // namespace
+}  // namespace fcnod
+
+extern "C" {
+
+int fcnod_composite_device(uint8_t* images, uint8_t* masks, int N, int H, int W, const uint8_t* rois, const uint8_t* roi_masks,
+                           const fcnod_paste* pastes, const int32_t* paste_begin, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(images && masks && rois && roi_masks && pastes && paste_begin, "null argument");
+    FCNOD_CHECK(N > 0 && H > 0 && W > 0, "composite: bad dimensions");
+    const dim3 grid((unsigned)std::min(148 * 8 / N + 1, ceil_div(H * W, 256)), (unsigned)N);
+    composite_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(images, masks, H, W, rois, roi_masks, pastes, paste_begin);
+    FCNOD_CUDA(cudaGetLastError());
+    FCNOD_API_END
+}
+
+int fcnod_composite(uint8_t* images, uint8_t* masks, int N, int H, int W, const uint8_t* rois, const uint8_t* roi_masks,
+                    size_t roi_pixels, const fcnod_paste* pastes, const int32_t* paste_begin) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(images && masks && rois && roi_masks && pastes && paste_begin, "null argument");
+    FCNOD_CHECK(N > 0 && H > 0 && W > 0, "composite: bad dimensions");
+    const int np = paste_begin[N];
+    FCNOD_CHECK(np >= 0, "composite: bad paste table");
+    for (int q = 0; q < np; ++q)
+        FCNOD_CHECK(pastes[q].w > 0 && pastes[q].h > 0 && pastes[q].roi_offset >= 0 &&
+                    (size_t)pastes[q].roi_offset + (size_t)pastes[q].w * pastes[q].h <= roi_pixels, "composite: paste outside the ROI buffer");
+    const size_t ni = (size_t)N * H * W;
+    Workspace& ws = workspace();
+    cudaStream_t s = ws.stream();
+    ws.reserve(Workspace::padded(ni * 3) + Workspace::padded(ni) + Workspace::padded(roi_pixels * 3) + Workspace::padded(roi_pixels) +
+               Workspace::padded((size_t)(np + 1) * sizeof(fcnod_paste)) + Workspace::padded((size_t)(N + 1) * 4));
+    uint8_t* d_img = ws.take<uint8_t>(ni * 3); uint8_t* d_msk = ws.take<uint8_t>(ni);
+    uint8_t* d_roi = ws.take<uint8_t>(roi_pixels * 3 + 1); uint8_t* d_rm = ws.take<uint8_t>(roi_pixels + 1);
+    fcnod_paste* d_p = ws.take<fcnod_paste>((size_t)np + 1);
+    int32_t* d_b = ws.take<int32_t>((size_t)N + 1);
+    FCNOD_CUDA(cudaMemcpyAsync(d_img, images, ni * 3, cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_msk, masks, ni, cudaMemcpyHostToDevice, s));
+    if (roi_pixels) {
+        FCNOD_CUDA(cudaMemcpyAsync(d_roi, rois, roi_pixels * 3, cudaMemcpyHostToDevice, s));
+        FCNOD_CUDA(cudaMemcpyAsync(d_rm, roi_masks, roi_pixels, cudaMemcpyHostToDevice, s));
+    }
+    if (np) FCNOD_CUDA(cudaMemcpyAsync(d_p, pastes, (size_t)np * sizeof(fcnod_paste), cudaMemcpyHostToDevice, s));
+    FCNOD_CUDA(cudaMemcpyAsync(d_b, paste_begin, (size_t)(N + 1) * 4, cudaMemcpyHostToDevice, s));
+    int rc = fcnod_composite_device(d_img, d_msk, N, H, W, d_roi, d_rm, d_p, d_b, s);
+    FCNOD_CHECK(rc == 0, fcnod_last_error());
+    FCNOD_CUDA(cudaMemcpyAsync(images, d_img, ni * 3, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaMemcpyAsync(masks, d_msk, ni, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
+    FCNOD_API_END
+}
+
+}  // extern "C"

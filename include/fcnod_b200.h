@@ -243,6 +243,20 @@ int fcnod_photo_augment_device(const uint8_t* images, const int32_t* sizes, cons
 int fcnod_photo_augment(const uint8_t* images, const int32_t* sizes, const fcnod_photo_draw* draws, int N, int H, int W,
                         uint8_t* out);   /* HOST buffers */
 
+/* ---- copy-paste synthesis: the compositing loop of ArgumentationEngineMapping.argument (argumentation_engine.py:723-728)
+ * One placed proposal: its w x h BGR patch starts at pixel `roi_offset` of the packed ROI buffer (`rois` 3 bytes per
+ * pixel, `roi_masks` 1 byte per pixel = mask[..., 0]), and lands with its top-left corner at (cx, cy) of background
+ * `image`; pixels whose mask byte is > 0 and that fall inside the background overwrite it, and the label mask gets
+ * label + 1.  Proposals of one image are applied in table order (later ones win); paste_begin [N + 1] indexes the table. */
+typedef struct fcnod_paste {
+    int32_t roi_offset, w, h, cx, cy, label;
+} fcnod_paste;
+int fcnod_composite_device(uint8_t* images /*[N][H][W][3] in/out*/, uint8_t* masks /*[N][H][W] in/out*/, int N, int H, int W,
+                           const uint8_t* rois, const uint8_t* roi_masks, const fcnod_paste* pastes, const int32_t* paste_begin,
+                           void* stream);
+int fcnod_composite(uint8_t* images, uint8_t* masks, int N, int H, int W, const uint8_t* rois, const uint8_t* roi_masks,
+                    size_t roi_pixels, const fcnod_paste* pastes, const int32_t* paste_begin);   /* HOST buffers */
+
 /* The layer forward WITH the photometric stage where the reference has it (argumentation_engine.py:176: after flip + crop,
  * before demean + resize): the flipped / cropped source is materialised as a uint8 crop, run through the chain above with
  * every crop's own borders, and demeaned / resampled from there.  photo = NULL is fcnod_aug_forward*. */
