@@ -204,3 +204,25 @@ def test_fused_prelude_feeds_conv1_and_data_blob_is_materialised_on_demand(model
         assert np.array_equal(ref.net.blobs['coverage'].data, cov) and np.array_equal(ref.net.blobs['bboxes'].data, bb)
         assert all(np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) for a, b in zip(res, res2))
         det.net.close(); ref.net.close()
+
+
+def test_multi_gpu_detector_one_process(firing_model_files):
+    """One process, one replica per device: the sharded result equals the single-device result frame for frame."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 CUDA devices')
+    from fcn_object_detector_b200.detector import FCNObjectDetector, MultiGpuDetector
+    proto, cm = firing_model_files
+    rs = np.random.RandomState(31)
+    imgs = rs.randint(0, 256, (7, 448, 448, 3)).astype(np.uint8)
+    kw = dict(precision='bf16', detection_threshold=0.45, min_boxes=1)
+    one = FCNObjectDetector(pretrained_weights=cm, deployment_prototxt=proto, **kw)
+    want = one.predict_batch(imgs)
+    multi = MultiGpuDetector(cm, proto, device_ids=list(range(torch.cuda.device_count())), **kw)
+    got = multi.predict_batch(imgs)
+    assert len(got) == len(want) and sum(len(w[0]) for w in want) > 0
+    for g, w in zip(got, want):
+        assert np.array_equal(g[0], w[0]) and np.array_equal(g[1], w[1])
+    got2 = multi.predict_batch(imgs[:1])
+    assert np.array_equal(got2[0][0], want[0][0])
+    multi.close()
