@@ -186,7 +186,7 @@ def _events_ms(torch, fn, reps):
     return a.elapsed_time(b) / reps
 
 
-def bandwidth_kernels(torch, L, _lib, stream, pk):
+def bandwidth_kernels(torch, L, _lib, stream, pk, reps=20):
     """decode (gridbox_to_boxes) and label_raster are launch-latency bound at the configured batches (3 MB / 1.7 MB):
     their HBM roofline is measured at 4096 frames / images per launch, as SURVEY.md 8(d) asks, plus the config batch."""
     out = {}
@@ -204,7 +204,7 @@ def bandwidth_kernels(torch, L, _lib, stream, pk):
         def run():
             _lib.check(L.fcnod_decode_device(cov.data_ptr(), bb.data_ptr(), B, 4, 16, 28, 28, C.byref(p), cap, boxes.data_ptr(),
                                              cell.data_ptr(), score.data_ptr(), cnt.data_ptr(), stream))
-        ms = _events_ms(torch, run, 20)
+        ms = _events_ms(torch, run, reps)
         ncand = int(cnt.sum().item())
         algo = B * DECODE_BYTES_PER_FRAME + ncand * 40 + B * 3 * 4      # maps read + 40 B per candidate + counts written
         out['decode_b%d' % B] = {'frames': B, 'ms': ms, 'candidates': ncand, 'algorithmic_bytes': algo,
@@ -223,7 +223,7 @@ def bandwidth_kernels(torch, L, _lib, stream, pk):
         def run():
             _lib.check(L.fcnod_label_raster_device(d_r.data_ptr(), d_l.data_ptr(), None, N, 1, 448, 448, 16, 1, fg.data_ptr(),
                                                    o4[0].data_ptr(), o4[1].data_ptr(), o4[2].data_ptr(), o4[3].data_ptr(), stream))
-        ms = _events_ms(torch, run, 20)
+        ms = _events_ms(torch, run, reps)
         algo = N * (RASTER_BYTES_PER_IMAGE + 20)
         out['label_raster_n%d' % N] = {'images': N, 'ms': ms, 'algorithmic_bytes': algo, 'achieved_gbs': algo / ms / 1e6,
                                        'frac_of_hbm_peak': algo / ms / 1e6 / pk['hbm']}

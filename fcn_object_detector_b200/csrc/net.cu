@@ -180,8 +180,10 @@ struct fcnod_net {
     float* pre_scratch = 0;
     cudaGraphExec_t graph = 0;
     cudaStream_t stream = 0;
-    cudaStream_t lane_stream[2] = {0, 0};  // lanes 1, 2 of the forward (lane 0 = the caller's stream)
-    cudaEvent_t fork_ev = 0, join_ev[2] = {0, 0};
+    // the forward's lanes: internal streams with descending priority (lane 0 carries the critical chain); they fork from
+    // the caller's stream at the start of a forward and join it again at the end
+    cudaStream_t lane_stream[3] = {0, 0, 0};
+    cudaEvent_t fork_ev = 0, join_ev[3] = {0, 0, 0};
     int n_lanes = 1;
     // detect paths on the fused bf16 plan: the prelude writes the first convolution's space-to-depth operand directly and
     // the fp32 blob `data` is only materialised when somebody reads it (from the frames still on the device)
@@ -809,10 +811,15 @@ void plan_lanes(fcnod_net* net) {
         }
         int lane = 0;
         if (!deps.empty()) {
-            const int dmax = deps.back();
-            if (last_on[net->steps[dmax].lane] == dmax) {
-                lane = net->steps[dmax].lane;                 // continue the chain of the newest dependency
-            } else {                                           // a branch: the lane that has been idle the longest
+            // continue a chain: among the dependencies that are still the last step of their lane, the one on the lowest
+            // (= highest-priority) lane.  Lane 0 thus carries fused-1x1 -> 3x3 -> next module's fused-1x1 -> ... (the
+            // critical chain); the 5x5 and pool_proj branches hang off it on lanes 1 and 2.
+            lane = -1;
+            for (size_t d = 0; d < deps.size(); ++d) {
+                const int l = net->steps[deps[d]].lane;
+                if (last_on[l] == deps[d] && (lane < 0 || l < lane)) lane = l;
+            }
+            if (lane < 0) {                                    // a branch: the lane that has been idle the longest
                 lane = -1;
                 for (int l = 0; l < kLanes; ++l)
                     if (l != net->steps[j - 1].lane && (lane < 0 || last_on[l] < last_on[lane])) lane = l;
@@ -1658,8 +1665,8 @@ void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool 
     }
     // lane 0 = the caller's stream; the others fork from it here and join it again at the end (under stream capture the
     // event waits become graph edges: independent branches are independent graph nodes)
-    cudaStream_t lanes[3] = {s, net->lane_stream[0], net->lane_stream[1]};
-    bool forked[3] = {true, false, false};
+    cudaStream_t lanes[3] = {net->lane_stream[0], net->lane_stream[1], net->lane_stream[2]};
+    bool forked[3] = {false, false, false};
     FCNOD_CUDA(cudaEventRecord(net->fork_ev, s));
     for (size_t i = 0; i < net->steps.size(); ++i) {
         const Step& st = net->steps[i];
@@ -1669,10 +1676,10 @@ void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool 
         if (i >= first) run_step(net, st, data_dev, ls);
         if (st.signal) FCNOD_CUDA(cudaEventRecord(st.ev, ls));
     }
-    for (int l = 1; l < 3; ++l)
+    for (int l = 0; l < 3; ++l)
         if (forked[l]) {
-            FCNOD_CUDA(cudaEventRecord(net->join_ev[l - 1], lanes[l]));
-            FCNOD_CUDA(cudaStreamWaitEvent(s, net->join_ev[l - 1], 0));
+            FCNOD_CUDA(cudaEventRecord(net->join_ev[l], lanes[l]));
+            FCNOD_CUDA(cudaStreamWaitEvent(s, net->join_ev[l], 0));
         }
 }
 
@@ -1820,9 +1827,15 @@ int fcnod_net_create(const char* prototxt_path, const char* caffemodel_path, int
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_kernel<bf16, 3, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(pool_lrn_tile_kernel<bf16, 3, 2, 2, true, 4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     FCNOD_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
-    for (int l = 0; l < 2; ++l) {
-        FCNOD_CUDA(cudaStreamCreateWithFlags(&net->lane_stream[l], cudaStreamNonBlocking));
-        FCNOD_CUDA(cudaEventCreateWithFlags(&net->join_ev[l], cudaEventDisableTiming));
+    {
+        int prio_least = 0, prio_greatest = 0;
+        FCNOD_CUDA(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));      // numerically lower = more urgent
+        static const bool flat_prio = getenv("FCNOD_LANE_PRIORITY") && getenv("FCNOD_LANE_PRIORITY")[0] == '0';
+        for (int l = 0; l < 3; ++l) {
+            const int prio = flat_prio ? prio_least : std::min(prio_least, prio_greatest + l);
+            FCNOD_CUDA(cudaStreamCreateWithPriority(&net->lane_stream[l], cudaStreamNonBlocking, prio));
+            FCNOD_CUDA(cudaEventCreateWithFlags(&net->join_ev[l], cudaEventDisableTiming));
+        }
     }
     FCNOD_CUDA(cudaEventCreateWithFlags(&net->fork_ev, cudaEventDisableTiming));
     for (size_t i = 0; i < net->steps.size(); ++i)
@@ -1847,7 +1860,7 @@ int fcnod_net_destroy(fcnod_net* net) {
             if (net->convs[i].d_bias_tab) cudaFree(net->convs[i].d_bias_tab);
         }
         if (net->stream) cudaStreamDestroy(net->stream);
-        for (int l = 0; l < 2; ++l) {
+        for (int l = 0; l < 3; ++l) {
             if (net->lane_stream[l]) cudaStreamDestroy(net->lane_stream[l]);
             if (net->join_ev[l]) cudaEventDestroy(net->join_ev[l]);
         }

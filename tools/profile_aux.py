@@ -71,5 +71,5 @@ print('postnet ok', sum(len(o[0]) for o in out))
 # ---- bandwidth kernels at the roofline batch (4096 frames / images per launch): standalone decode + label raster
 import torch  # noqa: E402
 import bench  # noqa: E402
-bw = bench.bandwidth_kernels(torch, _lib.lib(), _lib, torch.cuda.current_stream().cuda_stream, bench.peaks())
+bw = bench.bandwidth_kernels(torch, _lib.lib(), _lib, torch.cuda.current_stream().cuda_stream, bench.peaks(), reps=1)
 print('bandwidth ok', {k: round(v['frac_of_hbm_peak'], 3) for k, v in bw.items() if isinstance(v, dict)})
