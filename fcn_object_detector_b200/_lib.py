@@ -73,6 +73,7 @@ SIGNATURES = {
     'fcnod_net_tc_pick': (_I, [_P, _I]),
     'fcnod_net_set_tc_pick': (_I, [_P, _I, _I]),
     'fcnod_net_step_outputs': (_I, [_P, _I, _P, _SZ]),
+    'fcnod_net_step_lane': (_I, [_P, _I, C.POINTER(_I), _P, _I, C.POINTER(_I), _P, _I, C.POINTER(_I)]),
     'fcnod_net_autotune_candidates': (_I, []),
     'fcnod_net_blob_checksum': (_I, [_P, _STR, C.POINTER(C.c_ulonglong)]),
     'fcnod_postnet_default_params': (None, [C.POINTER(PostnetParams)]),

@@ -149,6 +149,7 @@ struct Step {
     int lane = 0;
     std::vector<int> waits;    // steps on OTHER lanes whose completion event this step waits for
     bool signal = false;       // some later step on another lane waits for this one
+    std::vector<int> deps;     // every earlier step this one depends on (RAW / WAR / WAW on a buffer region)
     cudaEvent_t ev = 0;
 };
 
@@ -796,8 +797,7 @@ void plan_lanes(fcnod_net* net) {
     net->n_lanes = 1;
     for (size_t j = 0; j < n; ++j) {
         Step& st = net->steps[j];
-        st.lane = 0; st.waits.clear(); st.signal = false;
-        if (off) continue;
+        st.lane = 0; st.waits.clear(); st.signal = false; st.deps.clear();
         std::vector<int> deps;
         for (size_t i = 0; i < j; ++i) {
             bool dep = false;
@@ -809,6 +809,8 @@ void plan_lanes(fcnod_net* net) {
                 for (size_t b = 0; b < wr[j].size() && !dep; ++b) dep = overlaps(rd[i][a], wr[j][b]);
             if (dep) deps.push_back((int)i);
         }
+        st.deps = deps;
+        if (off) continue;
         int lane = 0;
         if (!deps.empty()) {
             // continue a chain: among the dependencies that are still the last step of their lane, the one on the lowest
@@ -2040,6 +2042,18 @@ int fcnod_net_set_tc_pick(fcnod_net* net, int step, int pick) {
     setup_tc_step(net, st);
     std::map<int, std::vector<int> >::iterator pk = net->tc_picks.find(net->batch);
     if (pk != net->tc_picks.end()) pk->second[step] = pick;
+    FCNOD_API_END
+}
+
+int fcnod_net_step_lane(const fcnod_net* net, int step, int* lane, int* deps, int deps_cap, int* n_deps, int* waits, int waits_cap,
+                        int* n_waits) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(net && lane && n_deps && n_waits && step >= 0 && step < (int)net->steps.size(), "bad argument");
+    const Step& st = net->steps[step];
+    *lane = st.lane;
+    *n_deps = (int)st.deps.size(); *n_waits = (int)st.waits.size();
+    for (int i = 0; i < *n_deps && i < deps_cap && deps; ++i) deps[i] = st.deps[i];
+    for (int i = 0; i < *n_waits && i < waits_cap && waits; ++i) waits[i] = st.waits[i];
     FCNOD_API_END
 }
 

@@ -87,6 +87,10 @@ int fcnod_net_tc_pick(const fcnod_net* net, int step);
 int fcnod_net_set_tc_pick(fcnod_net* net, int step, int pick);
 /* Comma-separated names of the blobs planned launch `step` writes (a fused launch writes several). */
 int fcnod_net_step_outputs(const fcnod_net* net, int step, char* buf, size_t buflen);
+/* Lane plan of launch `step` (host only): the lane (stream / graph branch) it runs on, every earlier launch it depends on
+ * through a buffer region (RAW / WAR / WAW), and the launches on OTHER lanes whose completion event it waits for. */
+int fcnod_net_step_lane(const fcnod_net* net, int step, int* lane, int* deps, int deps_cap, int* n_deps, int* waits, int waits_cap,
+                        int* n_waits);
 /* How many tiling candidates the autotuner times per launch (FCNOD_AUTOTUNE, default 12; <= 1: none). */
 int fcnod_net_autotune_candidates(void);
 /* Position-sensitive 64-bit checksum of a materialised blob, computed on the device (test aid). */

@@ -276,3 +276,49 @@ def test_lmdb_datum_records_decode_into_the_layer_bottoms(built_lib):
         decode_datum(_datum_bytes(u8)[:-5])
     with pytest.raises(FcnodError):
         decode_datum(_datum_bytes(u8) + bytes([(7 << 3) | 0, 1]))        # encoded = true
+
+
+def test_lane_plan_orders_every_dependency(built_lib, model_files):
+    """The forward runs independent launches on three lanes (streams / graph branches) joined by event waits.  Structural
+    check on the plan-only handle: for every launch, each launch it depends on through a buffer region is ordered before it
+    -- by lane order, by one of its waits, or transitively -- and the inception branches really are spread over the lanes."""
+    from fcn_object_detector_b200 import _lib
+    L = _lib.lib()
+    proto, cm = model_files
+    h = C.c_void_p()
+    _lib.check(L.fcnod_net_create(proto.encode(), cm.encode(), -1, 1, C.byref(h)))
+    n = L.fcnod_net_launches_per_forward(h)
+    lanes, deps, waits = [], [], []
+    for i in range(n):
+        lane, nd, nw = C.c_int(), C.c_int(), C.c_int()
+        d = (C.c_int * 64)(); w = (C.c_int * 8)()
+        _lib.check(L.fcnod_net_step_lane(h, i, C.byref(lane), d, 64, C.byref(nd), w, 8, C.byref(nw)))
+        assert nd.value <= 64 and nw.value <= 8
+        lanes.append(lane.value); deps.append(list(d[:nd.value])); waits.append(list(w[:nw.value]))
+    done_before = []            # launches guaranteed complete when launch i starts
+    last_on = {}
+    for i in range(n):
+        s = set()
+        if lanes[i] in last_on:
+            p = last_on[lanes[i]]
+            s |= done_before[p] | {p}
+        for w in waits[i]:
+            assert w < i and lanes[w] != lanes[i]
+            s |= done_before[w] | {w}
+        for d in deps[i]:
+            assert d in s, 'launch %d depends on %d, which nothing orders before it' % (i, d)
+        done_before.append(s)
+        last_on[lanes[i]] = i
+    assert set(lanes) == {0, 1, 2}
+    desc = (C.c_char * (1 << 17))()
+    _lib.check(L.fcnod_net_describe(h, desc, len(desc)))
+    plan = desc.value.decode().splitlines()
+    # the critical chain (fused 1x1 -> 3x3) of every module stays on lane 0; 5x5 and pool_proj hang off on lanes 1 and 2
+    for i, line in enumerate(plan):
+        if '/3x3 3x3/1' in line or '/1x1 + ' in line:
+            assert lanes[i] == 0, line
+        if '/5x5 5x5/1' in line:
+            assert lanes[i] == 1, line
+        if '+maxpool3x3' in line:
+            assert lanes[i] == 2, line
+    L.fcnod_net_destroy(h)
