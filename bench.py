@@ -465,22 +465,26 @@ def run_ours(args):
         n_pool = sum('+maxpool3x3' in d for d in plan)
         tot_ms = sum(per) + post_ms
         ach = tc_flop / (tc_ms * 1e-3) / 1e12
-        # the same without the launches that also pool (their time includes the max-pool that used to be ten launches of its own)
-        pure_ms = sum(t for t, d in zip(per, plan) if 'conv_tc' in d and '+maxpool3x3' not in d)
-        pure_flop = sum(2.0 * macs[d] * B for d in plan if 'conv_tc' in d and '+maxpool3x3' not in d)
+        # the same without the launches that also pool or normalise (their time includes the max-pool / LRN work that used to
+        # be launches of its own: ten pools, and the LRN half of the LRN+pool launch)
+        def pure(d):
+            return 'conv_tc' in d and '+maxpool3x3' not in d and '+lrn(' not in d
+        pure_ms = sum(t for t, d in zip(per, plan) if pure(d))
+        pure_flop = sum(2.0 * macs[d] * B for d in plan if pure(d))
+        n_lrn = sum('+lrn(' in d for d in plan)
         ach_pure = pure_flop / (pure_ms * 1e-3) / 1e12
         whole = world * B * args.steps * FLOP_PER_FRAME / (ms * 1e-3) / 1e12 / world    # per GPU
         traffic, ncu_pipe, ncu_src = ncu_conv_summary()
         # Each conv launch is timed ALONE for a few tens of microseconds at full clocks: the denominator is the BURST
         # cuBLAS bf16 peak of MEASURED_PEAKS.json (the sustained figure is reported beside it).
         roof = {'bound': 'tensor',
-                'kernel': 'conv_tc2_kernel (%d launches per step; %d of them also run the inception max-pool on their A-operand path)'
-                          % (n_tc, n_pool),
+                'kernel': 'conv_tc2_kernel (%d launches per step; %d of them also run the inception max-pool on their A-operand path, '
+                          '%d the LRN in their epilogue)' % (n_tc, n_pool, n_lrn),
                 'achieved': ach, 'peak': pk['bf16_burst'], 'peak_source': pk['which'] + ', burst cuBLAS bf16 (launches timed alone)',
                 'unit': 'TFLOP/s', 'frac': ach / pk['bf16_burst'],
                 'peak_sustained': pk['bf16_sustained'], 'frac_vs_sustained': ach / pk['bf16_sustained'],
-                'excluding_pool_fused_launches': {'launches': n_tc - n_pool, 'achieved': ach_pure, 'frac': ach_pure / pk['bf16_burst'],
-                                                  'share_of_conv_flop': pure_flop / tc_flop},
+                'excluding_pool_and_lrn_fused_launches': {'launches': n_tc - n_pool - n_lrn, 'achieved': ach_pure,
+                                                          'frac': ach_pure / pk['bf16_burst'], 'share_of_conv_flop': pure_flop / tc_flop},
                 'whole_step_achieved': whole, 'whole_step_frac': whole / pk['bf16_burst'],
                 'ncu_tensor_pipe_pct_time_weighted': ncu_pipe,
                 'traffic': traffic, 'traffic_unit': 'bytes per launch (dram read + write, ncu)', 'ncu_source': ncu_src,

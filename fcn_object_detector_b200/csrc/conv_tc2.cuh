@@ -27,6 +27,10 @@
 //     (three 128-bit shared-memory loads per patch row, running row maxima in registers) and write the pooled
 //     [BW*BH pixels][64 ch] tile in the swizzled K-major layout the MMA reads.  The pooled blob never exists in HBM.
 //     Zero fill stands in for Caffe's clipped windows: the planner only fuses when the input is non-negative.
+//   * LRN epilogue (conv2/3x3 -> conv2/norm2, deploy.prototxt:108-151): when the convolution's whole channel extent is one
+//     N tile, the across-channel LRN of its ReLU'd output is applied by the epilogue warps on the fp32 accumulators (two
+//     MUFU per element, executed by warps that otherwise wait for the tensor pipe); a warp reads 16 extra TMEM columns
+//     either side of its own for the +-2 channel window.  The un-normalised blob never exists.
 //   * "Direct" segments (the fp32 heads, deploy.prototxt:2118-2175) are written straight from registers as NCHW
 //     float32 (lanes = consecutive pixels), with an optional sigmoid (coverage/sig :2144-2149).
 #pragma once
@@ -34,6 +38,7 @@
 
 #include "common.cuh"
 #include "conv_tc.cuh"
+#include "fused_pool.cuh"
 
 namespace fcnod {
 
@@ -61,6 +66,8 @@ struct ConvTc2Params {
                              //     to the A operand (raw halo patches by TMA -> eight pooling warps -> UMMA layout)
     int r_stages;            //     raw-patch ring: stages, bytes per stage, bytes per TMA box
     uint32_t r_stage_bytes, r_tx_bytes;
+    int lrn;                 // 1 = LRN (across channels, local_size 5, beta 0.75) of the ReLU'd output in the epilogue: needs
+    float lrn_aon, lrn_k;    //     n_tiles == 1 (a pixel's whole channel extent is one TMEM row); scale = lrn_k + lrn_aon * sum x^2
     int flat;                // 1 = 1x1 convolution over the flattened pixel index (H = 1, W = batch * H * W: 128-pixel tiles
                              //     that ignore image and row boundaries; host-side bookkeeping only)
     int m_tiles, n_tiles, BN;
@@ -137,6 +144,10 @@ __device__ __forceinline__ void tmem_ld_wait_dep32(uint32_t* r) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
     asm volatile("" : "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]) :: "memory");
 }
+// the same for a 16-register load
+__device__ __forceinline__ void tmem_ld_wait_dep16(uint32_t* r) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
@@ -199,7 +210,7 @@ struct TileIter {
 
 // KSTEPS = CK / 16 (UMMA K = 16 bf16), HALO = k x k taps from one shared-memory patch, PROF = clock64 timeline of CTA 0,
 // KK = kernel size known at compile time in HALO mode (3, 4, 5; 0 = read it from the parameters)
-template <int KSTEPS, bool HALO, bool PROF, int KK, bool POOL = false>
+template <int KSTEPS, bool HALO, bool PROF, int KK, bool POOL = false, bool LRN = false>
 __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                                                       const __grid_constant__ CUtensorMap tmap_b,
                                                                       const __grid_constant__ ConvTc2Params p) {
@@ -593,6 +604,13 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
         const int ncc = p.bt_lo_w + p.bt_hi_w + 1;
         const int n0 = my_nt * p.BN + wc0;          // first fused-N column of this warp
         for (int j = lane; j < wcols; j += 32) bias_s[j] = __ldg(p.bias + n0 + j);
+        // LRN epilogue: bias of the two columns either side of this warp's range (the neighbouring warps' columns)
+        float lrn_bl0 = 0.f, lrn_bl1 = 0.f, lrn_br0 = 0.f, lrn_br1 = 0.f;
+        if (LRN && wcols > 0) {
+            if (wc0 > 0) { lrn_bl0 = __ldg(p.bias + n0 - 2); lrn_bl1 = __ldg(p.bias + n0 - 1); }
+            if (wc0 + wcols < p.BN) { lrn_br0 = __ldg(p.bias + n0 + wcols); lrn_br1 = __ldg(p.bias + n0 + wcols + 1); }
+        }
+        (void)lrn_bl0; (void)lrn_bl1; (void)lrn_br0; (void)lrn_br1;
         // destination of the j-th 16-column group (bf16 NHWC): base pointer for pixel 0 of image 0, pixel pitch, and how
         // it may be stored: 0 = nothing, 1 / 2 = one / two 16-byte pieces, 3 = one 32-byte store (aligned)
         bf16* grp_ptr[4];
@@ -665,6 +683,76 @@ __global__ void __launch_bounds__(kConvTc2Threads, 1) conv_tc2_kernel(const __gr
                 fence_before();
                 __syncwarp();
                 if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+            } else if (LRN) {
+                // ---- ReLU + LRN(5) + bf16 NHWC.  A warp owns up to 48 columns (three 16-column blocks).  All of them, plus
+                //      the two columns either side (the neighbouring warps' blocks; zeros outside the channel range), leave
+                //      TMEM first and the accumulator is handed back BEFORE the arithmetic: the tensor pipe never waits for
+                //      the MUFU work.  y = relu(acc + bias); out = y * (k + a/n * sum_{+-2} y^2)^-0.75.
+                const size_t pix_off = (size_t)n_img * HW + (size_t)(valid ? pix_in_img : 0);
+                float y[48], yl0 = 0.f, yl1 = 0.f, yr0 = 0.f, yr1 = 0.f;
+                uint32_t r[16];
+                if (wcols > 0 && wc0 > 0) {
+                    tmem_ld16(trow - 16u, r);
+                    tmem_ld_wait_dep16(r);
+                    yl0 = fmaxf(__uint_as_float(r[14]) + lrn_bl0, 0.f); yl1 = fmaxf(__uint_as_float(r[15]) + lrn_bl1, 0.f);
+                }
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    if (16 * b < wcols) {
+                        tmem_ld16(trow + 16u * b, r);
+                        tmem_ld_wait_dep16(r);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) y[16 * b + j] = fmaxf(__uint_as_float(r[j]) + bias_s[16 * b + j], 0.f);
+                    }
+                }
+                if (wcols > 0 && wc0 + wcols < p.BN) {
+                    tmem_ld16(trow + (uint32_t)wcols, r);
+                    tmem_ld_wait_dep16(r);
+                    yr0 = fmaxf(__uint_as_float(r[0]) + lrn_br0, 0.f); yr1 = fmaxf(__uint_as_float(r[1]) + lrn_br1, 0.f);
+                }
+                fence_before();
+                __syncwarp();
+                if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    if (16 * b < wcols) {
+                        const bool last = 16 * (b + 1) >= wcols;
+                        float sq[20];
+                        sq[0] = b == 0 ? yl0 : y[b == 0 ? 0 : 16 * b - 2]; sq[1] = b == 0 ? yl1 : y[b == 0 ? 0 : 16 * b - 1];
+                        sq[18] = (b == 2 || last) ? yr0 : y[b == 2 ? 0 : 16 * b + 16]; sq[19] = (b == 2 || last) ? yr1 : y[b == 2 ? 0 : 16 * b + 17];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) sq[2 + j] = y[16 * b + j];
+#pragma unroll
+                        for (int j = 0; j < 20; ++j) sq[j] *= sq[j];
+                        float pr[19];                                 // pair sums: 3 adds per window instead of 4
+#pragma unroll
+                        for (int j = 0; j < 19; ++j) pr[j] = sq[j] + sq[j + 1];
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            float o[2];
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                const int j = 2 * e + h;
+                                const float ssum = (pr[j] + pr[j + 2]) + sq[j + 4];
+                                o[h] = y[16 * b + j] * lrn_scale<true>(fmaf(p.lrn_aon, ssum, p.lrn_k), 0.75f);
+                            }
+                            const __nv_bfloat162 h2 = __floats2bfloat162_rn(o[0], o[1]);
+                            pk[e] = *reinterpret_cast<const uint32_t*>(&h2);
+                        }
+                        if (valid && grp_mode[b] != 0) {
+                            bf16* const d = grp_ptr[b] + pix_off * (size_t)grp_ld[b];
+                            if (grp_mode[b] == 3) {
+                                asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                             ::"l"(d), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]), "r"(pk[4]), "r"(pk[5]),
+                                               "r"(pk[6]), "r"(pk[7]) : "memory");
+                            } else {
+                                *reinterpret_cast<uint4*>(d) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                                if (grp_mode[b] == 2) *reinterpret_cast<uint4*>(d + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                            }
+                        }
+                    }
+                }
             } else {
                 // ---- bf16 NHWC: drain 32 columns at a time: TMEM -> registers, + bias (the border pixels of the first
                 //      convolution take theirs from the class table), ReLU, pack, and store straight from the registers: a

@@ -94,6 +94,8 @@ struct ConvWeights {
     int CK = 0, n_cchunks = 0, BN = 0, n_tiles = 0;
     bool halo = false;         // k x k taps served from one shared-memory patch per channel chunk (conv_tc2.cuh)
     bool pool = false;         // a 3x3 / stride 1 / pad 1 max-pool of the input runs on the A-operand path (POOL mode)
+    bool lrn = false;          // the LRN that follows (local_size 5, beta 0.75) runs in the epilogue; needs one N tile
+    float lrn_aon = 0.f, lrn_k = 1.f;
     // space-to-depth form of a stride-2 convolution on the (Power-transformed) network input
     bool s2d = false;
     int ka = 0;                // taps per axis after space-to-depth (padded to 1/2/4)
@@ -509,6 +511,39 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
         }
     }
 
+    // ---- pass 2d: Convolution (+ReLU) -> LRN(5, beta 0.75) with the whole channel extent in one N tile (conv2/3x3 ->
+    // conv2/norm2, deploy.prototxt:108-151): the LRN runs in the convolution's epilogue, the un-normalised blob is never
+    // materialised.  Takes precedence over the LRN -> Pool fusion, which then reverts to a plain pooling launch.
+    std::map<int, int> lrn_of;                   // conv layer -> LRN layer folded into its epilogue
+    std::set<int> lrn_fused;
+    if (bf && fuse && !getenv("FCNOD_NO_CONV_LRN")) {
+        for (size_t i = 0; i < def.layers.size(); ++i) {
+            const LayerDef& R = def.layers[i];
+            if (R.type != L_LRN || R.local_size != 5 || R.beta != 0.75f || R.bottom[0] == R.top[0]) continue;
+            const std::string& src = R.bottom[0];
+            if (!producer.count(src) || outputs.count(src) || virt.count(src) || alias.count(src)) continue;
+            const int ci = producer[src];
+            const LayerDef& Cn = def.layers[ci];
+            if (Cn.type != L_CONV || !tc_layers.count(ci) || group.count(ci) || group_leader.count(ci) || direct_blob.count(ci) ||
+                s2d_conv.count(ci) || pool_of.count(ci)) continue;
+            if (Cn.num_output > 192 || Cn.num_output % 16) continue;          // <= 48 columns per epilogue warp
+            if ((Cn.kernel != 1 && Cn.kernel != 3) || shp[Cn.bottom[0]].C <= 32) continue;      // the instantiations that exist: CK = 64
+            if (!consumers.count(src) || consumers[src].size() != 1 || consumers[src][0] != (int)i) continue;
+            // exactly one in-place layer on the convolution's top, and it is the ReLU right behind it
+            if (!inplace_ops.count(src) || inplace_ops[src] != 1 || (size_t)ci + 1 >= def.layers.size() ||
+                def.layers[ci + 1].type != L_RELU || def.layers[ci + 1].top[0] != src) continue;
+            if (inplace_ops.count(R.top[0]) || outputs.count(R.top[0]) || alias.count(R.top[0]) || dt[R.top[0]] != DT_BF16) continue;
+            // undo an LRN -> Pool fusion of this LRN: the pool becomes a plain launch again
+            if (fuse_first.count((int)i)) {
+                const int pl = fuse_first[(int)i];
+                fuse_second.erase(pl); fuse_first.erase((int)i);
+                virt.erase(R.top[0]);
+            }
+            if (fuse_second.count((int)i)) continue;        // Pool -> LRN pairs are left alone
+            lrn_of[ci] = (int)i; lrn_fused.insert((int)i); virt.insert(src);
+        }
+    }
+
     // ---- create blobs + buffers in definition order
     net->blobs.clear(); net->blob_index.clear(); net->buffers.clear();
     struct Maker {
@@ -612,6 +647,11 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                     Step::Seg sg;
                     sg.name = M.name;
                     sg.blob = mk.make(mtop);
+                    if (lrn_of.count(li)) {       // the epilogue normalises: what is written is the LRN's top
+                        const LayerDef& R = def.layers[lrn_of[li]];
+                        sg.blob = mk.make(R.top[0]);
+                        cw.lrn = true; cw.lrn_aon = R.alpha / R.local_size; cw.lrn_k = R.lrn_k;
+                    }
                     sg.direct_blob = -1;
                     sg.col0 = (cw.Cout + 7) / 8 * 8;
                     sg.ncols = M.num_output;
@@ -662,6 +702,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 d << (tc_ok ? "conv_tc " : "conv_simt ") << names << " " << L.kernel << "x" << L.kernel << "/" << L.stride
                   << " Cin=" << cw.Cin << " Cout=" << cw.Cout << (st.relu ? " +relu" : "") << (is_s2d ? " +s2d+power" : "");
                 if (pooled) d << " +maxpool3x3(" << def.layers[pool_of[(int)i]].name << ")";
+                if (lrn_of.count((int)i)) d << " +lrn(" << def.layers[lrn_of[(int)i]].name << ")";
                 for (size_t m = 0; m < st.segs.size(); ++m)
                     if (st.segs[m].flags & SEG_DIRECT) d << ((st.segs[m].flags & SEG_SIGMOID) ? " +sigmoid" : "") << " +nchw";
                 st.desc = d.str();
@@ -701,6 +742,7 @@ void build_plan(fcnod_net* net, const WeightMap& weights) {
                 break;
             }
             case L_LRN: {
+                if (lrn_fused.count((int)i)) { mk.make(top); break; }       // runs in its convolution's epilogue
                 if (fuse_first.count((int)i)) { mk.make(top); break; }      // LRN -> Pool: emitted at the Pool
                 if (fuse_second.count((int)i)) {                            // Pool -> LRN
                     const LayerDef& F = def.layers[fuse_second[(int)i]];
@@ -975,7 +1017,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
       const TcGeo& G = geos[gi];
       if ((size_t)r_st * r_stage + 2 * (size_t)G.a_stage > kTcSmemBudget - fixed) continue;
       const size_t avail = kTcSmemBudget - fixed - (size_t)r_st * r_stage;
-      for (int nt = ceil_div(N8, cw.pool ? 128 : 256); nt <= ceil_div(N8, 16); ++nt) {
+      for (int nt = ceil_div(N8, cw.pool ? 128 : 256); nt <= (cw.lrn ? 1 : ceil_div(N8, 16)); ++nt) {
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > (cw.pool ? 128 : 256) || nt * BN - N8 >= BN) continue;
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
@@ -994,7 +1036,11 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
                         const int a_min = p.halo ? 1 : 2;
                         if (rounds_b > 24 || bres + (size_t)nr * a_min * G.a_stage > avail) continue;
                         b_st = rounds_b;
-                        a_st = (int)std::min<size_t>(p.halo ? (dual ? 3 : 4) : 8, (avail - bres) / ((size_t)nr * G.a_stage));
+                        // halo patches stream from HBM / L2 with ~1 us of latency and a tile consumes one in well under that:
+                        // as many patch stages as shared memory allows (FCNOD_HALO_STAGES caps it; 3 / 4 before round 2)
+                        static const int halo_cap = getenv("FCNOD_HALO_STAGES") ? atoi(getenv("FCNOD_HALO_STAGES")) : 0;
+                        const size_t a_cap = p.halo ? (halo_cap > 0 ? (size_t)halo_cap : (dual ? 6 : 8)) : 8;
+                        a_st = (int)std::min<size_t>(a_cap, (avail - bres) / ((size_t)nr * G.a_stage));
                         if (nr * a_st + b_st > 30) a_st = (30 - b_st) / nr;
                         if (a_st < a_min) continue;
                     } else if (p.halo) {
@@ -1061,6 +1107,8 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     if (p.acc_lg == 1 && p.egroups > 2) p.egroups = 2;
     const int epi_per_quadrant = cw.pool ? 2 : 4;                    // POOL mode: eight of the sixteen warps pool
     if (cw.pool) p.egroups = p.BN <= 64 ? 2 : 1;
+    if (cw.lrn) p.egroups = p.BN <= 48 ? 4 : (p.BN <= 96 ? 2 : 1);   // the LRN epilogue keeps <= 48 columns per warp in registers
+    if (p.acc_lg == 1 && p.egroups > 2) p.egroups = 2;
     p.cols_half0 = ceil_div(p.BN, 16 * (epi_per_quadrant / (int)p.egroups)) * 16;   // columns per epilogue warp (<= 64)
     p.tmem_cols = std::max<uint32_t>((1u << p.acc_lg) * acc, 32);
     p.bt_ld = (int)align_up((size_t)N8, 256) + 256;
@@ -1075,6 +1123,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
         p.step_ty = g % p.tiles_y; g /= p.tiles_y;
         p.step_img = g;
     }
+    p.lrn = cw.lrn ? 1 : 0; p.lrn_aon = cw.lrn_aon; p.lrn_k = cw.lrn_k;
     p.nseg = (int)st.segs.size();
     p.flags = st.segs[0].flags & (SEG_RELU | SEG_DIRECT);
     p.bt_interior = cw.bt_lo_h * (cw.bt_lo_w + cw.bt_hi_w + 1) + cw.bt_lo_w;
@@ -1500,6 +1549,13 @@ void launch_conv_tc2(const Step& st, cudaStream_t s, bool prof) {
         const dim3 g(st.tc_grid), b(kConvTc2Threads);
         if (prof) conv_tc2_kernel<4, false, true, 0, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
         else conv_tc2_kernel<4, false, false, 0, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+    } else if (st.tc.lrn) {
+        const dim3 g(st.tc_grid), b(kConvTc2Threads);
+        const bool k3 = st.tc.halo && st.tc.kh == 3 && st.tc.kw == 3;
+        FCNOD_CHECK(ks == 4 && (k3 || !st.tc.halo) && st.tc.n_tiles == 1, "internal: LRN epilogue needs 64-channel blocks, a 3x3 or 1x1 kernel, one N tile");
+        if (k3) conv_tc2_kernel<4, true, false, 3, false, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+        else conv_tc2_kernel<4, false, false, 0, false, true><<<g, b, st.tc_smem, s>>>(st.tmap_a, st.tmap_b, st.tc);
+        FCNOD_CHECK(!prof, "the LRN-epilogue instantiations have no profiled twin");
     } else if (st.tc.halo) {
         const int kk = st.tc.kh == st.tc.kw ? st.tc.kh : 0;
         if (ks == 4 && kk == 3) launch_tc2_inst<4, true, 3>(st, s, prof);
@@ -1525,6 +1581,8 @@ void conv_tc2_set_smem_limit() {      // per device, at net creation (outside an
     tc2_smem_attr<1, true, 4>(); tc2_smem_attr<1, true, 0>(); tc2_smem_attr<1, true, 5>();
     tc2_smem_attr<2, true, 5>(); tc2_smem_attr<2, true, 0>();
     tc2_smem_attr<4, false, 0>(); tc2_smem_attr<2, false, 0>(); tc2_smem_attr<1, false, 0>();
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, true, false, 3, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, false, 0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, false, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     FCNOD_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<4, false, true, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
 }
@@ -1929,7 +1987,7 @@ int fcnod_net_describe(const fcnod_net* net, char* buf, size_t buflen) {
         }
         if (st.kind == S_CONV_TC) {
             const ConvWeights& cw = net->convs[st.conv];
-            o << " [" << (st.tc.halo ? "halo " : "") << (st.tc.flat ? "flat " : "") << (st.tc.pool ? "pool " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
+            o << " [" << (st.tc.halo ? "halo " : "") << (st.tc.flat ? "flat " : "") << (st.tc.pool ? "pool " : "") << (st.tc.lrn ? "lrn " : "") << "CK=" << st.tc.CK << " BN=" << st.tc.BN << "x" << st.tc.n_tiles << " box=" << st.tc.BW
               << "x" << st.tc.BH << " stages=" << st.tc.a_stages << "+" << st.tc.b_stages << "x" << st.tc.b_taps << (st.tc.b_resident ? "R" : "") << (st.tc.pool ? "+" + std::to_string(st.tc.r_stages) + "raw" : std::string()) << (st.tc.dual ? " dual" : "") << " eg=" << st.tc.egroups << " pick=" << st.tc_pick << "/" << st.tc_ncand << " tiles=" << st.tc.m_tiles * st.tc.n_tiles
               << " grid=" << st.tc_grid << " smem=" << st.tc_smem << "]";
         }

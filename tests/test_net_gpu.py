@@ -128,10 +128,12 @@ def test_s2d_conv_and_fused_pool_lrn(case, tmp_path, monkeypatch):
     proto, cm = write_stem_net(str(tmp_path), tag, H, W, batch=batch, seed=len(tag), k=k, pad=pad, cout=cout, shift=shift,
                                scale=scale, c2=c2)
     x = np.random.RandomState(4).uniform(0, 1, (batch, 3, H, W)).astype(np.float32)
-    want = ['c1', 'n1', 'c2', 'p2', 'out']
+    want = ['c1', 'n1', 'n2', 'p2', 'out']
     ref = oracle_forward(proto, cm, x, want=want)
     got, plan = gpu_forward(proto, cm, x, 'bf16', want)
-    assert '+s2d+power' in plan and 'pool+lrn' in plan and 'lrn+pool' in plan and 'conv_simt' not in plan, plan
+    # Pool -> LRN is one launch; the second LRN runs in the epilogue of the 3x3 convolution before it (its pool is then a
+    # plain launch), or, where that does not apply, LRN -> Pool is one launch
+    assert '+s2d+power' in plan and 'pool+lrn' in plan and ('+lrn(n2)' in plan or 'lrn+pool' in plan) and 'conv_simt' not in plan, plan
     errs = {n: rel_err(got[n], ref[n]) for n in want}
     # c1 is stored in bf16 (1 ulp = 2^-8 of the value); later blobs accumulate a few such roundings
     assert errs['c1'] < 1.0 / 128, errs
@@ -143,18 +145,28 @@ def test_s2d_conv_and_fused_pool_lrn(case, tmp_path, monkeypatch):
     net.blobs['data'].reshape(*x.shape); net.blobs['data'].data[...] = x; net.forward()
     with pytest.raises(FcnodError):
         net.blobs['p1'].data
+    if '+lrn(n2)' in plan:
+        with pytest.raises(FcnodError):
+            net.blobs['c2'].data            # the un-normalised convolution output is never materialised
     net.close()
     monkeypatch.setenv('FCNOD_NO_FUSION', '1')
-    unf, plan2 = gpu_forward(proto, cm, x, 'bf16', want + ['p1', 'n2'])
+    unf, plan2 = gpu_forward(proto, cm, x, 'bf16', want + ['p1', 'c2'])
     assert 'pool+lrn' not in plan2 and 'conv_simt' in plan2
-    for n in ('n1', 'p2', 'out'):
+    for n in ('n1', 'n2', 'p2', 'out'):
         assert rel_err(got[n], unf[n]) < 2e-2, (n, rel_err(got[n], unf[n]))
+    # and with the epilogue LRN switched off the LRN -> Pool launch takes over, with the same result
+    monkeypatch.delenv('FCNOD_NO_FUSION')
+    monkeypatch.setenv('FCNOD_NO_CONV_LRN', '1')
+    alt, plan3 = gpu_forward(proto, cm, x, 'bf16', ['p2', 'out'])
+    assert 'lrn+pool' in plan3 and '+lrn(' not in plan3
+    for n in ('p2', 'out'):
+        assert rel_err(got[n], alt[n]) < 2e-2, (n, rel_err(got[n], alt[n]))
 
 
 def test_bf16_full_net_within_tolerance(model_files):
     proto, cm = model_files
     x = np.random.RandomState(2).uniform(0, 1, (2, 3, 448, 448)).astype(np.float32)
-    want = ['conv1/7x7_s2', 'pool1/norm1', 'conv2/3x3', 'pool2/3x3_s2', 'inception_3a/output', 'inception_4e/output',
+    want = ['conv1/7x7_s2', 'pool1/norm1', 'conv2/norm2', 'pool2/3x3_s2', 'inception_3a/output', 'inception_4e/output',
             'inception_5b/output', 'coverage', 'bboxes']
     exp = oracle_forward(proto, cm, x, want=want)
     got, plan = gpu_forward(proto, cm, x, 'bf16', want)
