@@ -152,6 +152,9 @@ struct Step {
     std::vector<int> waits;    // steps on OTHER lanes whose completion event this step waits for
     bool signal = false;       // some later step on another lane waits for this one
     std::vector<int> deps;     // every earlier step this one depends on (RAW / WAR / WAW on a buffer region)
+    int grid_cap = 0;          // > 0: this launch may use only that many CTAs (its share of the SMs while independent launches of
+                               //      other lanes run beside it, see partition_lane_groups)
+    float solo_ms = 0.f;       // launch time alone on the whole device (autotuner)
     cudaEvent_t ev = 0;
 };
 
@@ -164,6 +167,7 @@ struct fcnod_net {
     int device = 0, precision = 0, batch = 0;
     int capacity = 0;                      // frames the activation buffers were allocated for (>= batch)
     std::map<int, std::vector<int> > tc_picks;   // batch -> tiling pick of every step (autotuned once per batch size)
+    std::map<int, std::vector<int> > tc_caps;    // batch -> grid cap of every step (partition_lane_groups)
     NetDef def;
     std::vector<Blob> blobs;
     std::map<std::string, int> blob_index;
@@ -995,6 +999,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     }
     const int taps = p.kh * p.kw;
     const int Kp = taps * p.n_cchunks * p.CK;
+    const int sms = st.grid_cap > 0 ? st.grid_cap : kNumSMs;       // CTAs this launch may occupy
     // N tiling / pipeline shape: every candidate that fits in shared memory, ranked by a per-tile model
     //   tile time = max(MMA issue, smem bandwidth, L2->smem bytes, epilogue) + fixed;  total = rounds over the persistent CTAs
     // (constants measured with tools/micro/mma_rate.cu and the conv timelines).  `pick` selects the pick-th best; the
@@ -1021,6 +1026,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
         const int BN = ceil_div(ceil_div(N8, nt), 16) * 16;
         if (BN > (cw.pool ? 128 : 256) || nt * BN - N8 >= BN) continue;
         // a CTA owns one N tile: grid = a multiple of nt; pixel tiles are dealt to the grid / nt CTAs of each N tile
+        // (ranked for the whole device whatever the launch's grid cap: a pick index must always mean the same tiling)
         const int mslots = std::max(1, std::min(G.m_tiles, kNumSMs / nt));
         const long rounds = ((long)G.m_tiles + mslots - 1) / mslots;
         for (int bt = (p.halo ? p.kw : 1); bt >= 1; bt = (bt > 1 ? 1 : 0)) {       // B stage = kw taps (HALO) or 1
@@ -1115,7 +1121,7 @@ void fill_tc_geometry(const fcnod_net* net, Step& st, int batch, int pick = -1) 
     st.tc_smem = (size_t)(p.dual ? 2 : 1) * p.a_stages * p.a_stage_bytes +
                  (size_t)((p.dual && !p.b_resident) ? 2 : 1) * p.b_stages * p.b_stage_bytes + (size_t)p.r_stages * p.r_stage_bytes +
                  (size_t)kTcEpiWarps * 256 + 1024 + 1024;
-    p.mstride = std::max(1, std::min(p.m_tiles, kNumSMs / p.n_tiles));
+    p.mstride = std::max(1, std::min(p.m_tiles, std::max(sms, p.n_tiles) / p.n_tiles));
     st.tc_grid = p.mstride * p.n_tiles;
     {   // the pixel-tile stride in the mixed radix (img, ty, tx) of the tile index (TileIter::next)
         int g = p.mstride;
@@ -1396,7 +1402,118 @@ void autotune_tc_steps(fcnod_net* net) {
             if (c == 0 || ms < best_ms) { best_ms = ms; best = c; }
         }
         st.tc_pick = best;
+        st.solo_ms = best_ms / 3.f;
         setup_tc_step(net, st);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+}
+
+void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool skip_input_step = false);
+
+// Independent launches of different lanes (the 3x3, the 5x5 and the pool_proj convolution of one inception module) only
+// overlap at their tails while each of them asks for all 148 SMs: the first one takes the device, the others start as its
+// CTAs retire.  Here every such group gets a PARTITION of the SMs instead -- grids that add up to 148, sized from the
+// launches' solo times so that all members finish together -- so that they run side by side from the start: no member
+// pays its own last, mostly empty round (448 tiles on 148 SMs = 3.03 rounds), and three prologues overlap.  The device
+// has the last word: the whole forward is timed with and without each group's partition and the faster form is kept.
+void partition_lane_groups(fcnod_net* net) {
+    // Opt-in (FCNOD_PARTITION=1).  Measured on the bench (batch 64): the device check keeps the partition for 4 of the 9
+    // inception modules and the step goes from 1.840 to 1.832 ms -- inside the run-to-run noise -- while every partitioned
+    // launch, timed alone for the roofline table, looks slower than it is in the step.  Not worth it by default.
+    static const bool on = getenv("FCNOD_PARTITION") && getenv("FCNOD_PARTITION")[0] == '1';
+    if (!on || net->n_lanes <= 1) return;
+    const size_t n = net->steps.size();
+    std::vector<std::vector<int> > groups;
+    std::vector<int> cur;
+    for (size_t j = 0; j < n; ++j) {
+        bool dep = false;
+        for (size_t g = 0; g < cur.size() && !dep; ++g)
+            dep = std::find(net->steps[j].deps.begin(), net->steps[j].deps.end(), cur[g]) != net->steps[j].deps.end();
+        if (dep) { groups.push_back(cur); cur.clear(); }
+        cur.push_back((int)j);
+    }
+    groups.push_back(cur);
+    const double F = 0.004;     // ms of a launch that do not scale with its rounds (prologue, pipeline fill, drain)
+    std::vector<std::vector<int> > planned;
+    for (size_t gi = 0; gi < groups.size(); ++gi) {
+        const std::vector<int>& G = groups[gi];
+        if (G.size() < 2 || G.size() > 3) continue;
+        bool ok = true;
+        std::set<int> lanes;
+        for (size_t k = 0; k < G.size(); ++k) {
+            const Step& st = net->steps[G[k]];
+            ok = ok && st.kind == S_CONV_TC && st.solo_ms > 0.f;
+            lanes.insert(st.lane);
+        }
+        if (!ok || lanes.size() != G.size()) continue;
+        // per-round time of every member from its solo launch
+        double tau[3]; int tiles[3], nt[3];
+        for (size_t k = 0; k < G.size(); ++k) {
+            const Step& st = net->steps[G[k]];
+            nt[k] = st.tc.n_tiles; tiles[k] = st.tc.m_tiles;
+            const int slots = std::max(1, std::min(tiles[k], kNumSMs / nt[k]));
+            const int rounds = (tiles[k] + slots - 1) / slots;
+            tau[k] = std::max((double)st.solo_ms - F, 0.3 * st.solo_ms) / rounds;
+        }
+        auto cost = [&](int k, int g) {
+            const int slots = std::max(1, g / nt[k]);
+            return F + (double)((tiles[k] + slots - 1) / slots) * tau[k];
+        };
+        double best = 1e30; int bg[3] = {0, 0, 0};
+        if (G.size() == 2) {
+            for (int g0 = nt[0]; g0 + nt[1] <= kNumSMs; g0 += nt[0]) {
+                const int g1 = (kNumSMs - g0) / nt[1] * nt[1];
+                const double t = std::max(cost(0, g0), cost(1, g1));
+                if (t < best) { best = t; bg[0] = g0; bg[1] = g1; }
+            }
+        } else {
+            for (int g0 = nt[0]; g0 + nt[1] + nt[2] <= kNumSMs; g0 += nt[0])
+                for (int g1 = nt[1]; g0 + g1 + nt[2] <= kNumSMs; g1 += nt[1]) {
+                    const int g2 = (kNumSMs - g0 - g1) / nt[2] * nt[2];
+                    const double t = std::max(std::max(cost(0, g0), cost(1, g1)), cost(2, g2));
+                    if (t < best) { best = t; bg[0] = g0; bg[1] = g1; bg[2] = g2; }
+                }
+        }
+        if (best >= 1e30) continue;
+        for (size_t k = 0; k < G.size(); ++k) { net->steps[G[k]].grid_cap = bg[k]; setup_tc_step(net, net->steps[G[k]]); }
+        planned.push_back(G);
+    }
+    if (planned.empty()) return;
+    // device check: the forward with all partitions, then each group reverted in turn; keep what is faster
+    cudaEvent_t e0, e1;
+    FCNOD_CUDA(cudaEventCreate(&e0));
+    FCNOD_CUDA(cudaEventCreate(&e1));
+    cudaStream_t s = net->stream;
+    auto time_forward = [&]() {
+        float best_ms = 1e30f;
+        forward_device(net, net->data_dev, s, false);
+        for (int rep = 0; rep < 3; ++rep) {
+            FCNOD_CUDA(cudaEventRecord(e0, s));
+            for (int r = 0; r < 2; ++r) forward_device(net, net->data_dev, s, false);
+            FCNOD_CUDA(cudaEventRecord(e1, s));
+            FCNOD_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            FCNOD_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            best_ms = std::min(best_ms, ms);
+        }
+        FCNOD_CUDA(cudaGetLastError());
+        return best_ms;
+    };
+    float t_cur = time_forward();
+    for (size_t gi = 0; gi < planned.size(); ++gi) {
+        std::vector<int> saved;
+        for (size_t k = 0; k < planned[gi].size(); ++k) {
+            Step& st = net->steps[planned[gi][k]];
+            saved.push_back(st.grid_cap);
+            st.grid_cap = 0; setup_tc_step(net, st);
+        }
+        const float t_off = time_forward();
+        if (t_off < t_cur) { t_cur = t_off; continue; }          // this group is better off with full grids
+        for (size_t k = 0; k < planned[gi].size(); ++k) {
+            Step& st = net->steps[planned[gi][k]];
+            st.grid_cap = saved[k]; setup_tc_step(net, st);
+        }
     }
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
@@ -1439,13 +1556,16 @@ void reshape(fcnod_net* net, int batch) {
     for (size_t i = 0; i < net->steps.size(); ++i)
         if (net->steps[i].kind == S_CONV_TC) {
             net->steps[i].tc_pick = pk != net->tc_picks.end() ? pk->second[i] : -1;
+            net->steps[i].grid_cap = pk != net->tc_picks.end() ? net->tc_caps[batch][i] : 0;
             setup_tc_step(net, net->steps[i]);
         }
     if (pk == net->tc_picks.end()) {
         autotune_tc_steps(net);
-        std::vector<int> picks(net->steps.size(), -1);
-        for (size_t i = 0; i < net->steps.size(); ++i) picks[i] = net->steps[i].tc_pick;
+        partition_lane_groups(net);
+        std::vector<int> picks(net->steps.size(), -1), caps(net->steps.size(), 0);
+        for (size_t i = 0; i < net->steps.size(); ++i) { picks[i] = net->steps[i].tc_pick; caps[i] = net->steps[i].grid_cap; }
         net->tc_picks[batch] = picks;
+        net->tc_caps[batch] = caps;
     }
 }
 
@@ -1715,7 +1835,7 @@ void run_step(fcnod_net* net, const Step& st, const float* data_dev, cudaStream_
     FCNOD_CUDA(cudaGetLastError());
 }
 
-void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool skip_input_step = false) {
+void forward_device(fcnod_net* net, const float* data_dev, cudaStream_t s, bool skip_input_step) {
     FCNOD_CHECK(net->device >= 0, "plan-only handle (device < 0): no compute is possible; there is no CPU fallback");
     FCNOD_CHECK(net->batch > 0, "net not reshaped");
     const size_t first = skip_input_step ? 1 : 0;       // the input step's output was produced by the fused prelude
