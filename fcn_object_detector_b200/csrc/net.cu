@@ -196,6 +196,7 @@ struct fcnod_net {
     // the fp32 blob `data` is only materialised when somebody reads it (from the frames still on the device)
     bool fused_prelude = false;
     bool data_valid = true;
+    int srchw_b = 0, srchw_h = 0, srchw_w = 0;      // what srchw_dev holds (streaming detect)
     const uint8_t* data_img = 0;
     int data_img_b = 0, data_img_h = 0, data_img_w = 0;
     cudaStream_t copy_stream = 0;        // uploads of fcnod_detect's second half-batch, overlapped with the first one's compute
@@ -211,7 +212,13 @@ struct fcnod_net {
         size_t img_bytes = 0;
         int32_t* pinned = 0;             // [B*2 src_hw | det | label | weight | count]
         size_t pinned_bytes = 0;
-        cudaEvent_t up = 0, done = 0;    // upload finished (copy stream) / detections on the host (compute stream)
+        cudaEvent_t up = 0, done = 0;    // upload (+ prelude) finished (copy stream) / detections on the host (compute stream)
+        // fused-prelude plan: the slot's own space-to-depth image, min/max scratch and graph (conv1 reads THIS image), so that
+        // the prelude of batch i+1 runs on the copy stream while batch i is still computing
+        void* s2d = 0;
+        void* mm = 0;
+        cudaGraphExec_t graph = 0;
+        fcnod_postnet_params graph_p;
         int B = 0;
         int ticket = -1;                 // -1 = free
     } slots[2];
@@ -1254,6 +1261,8 @@ void upload_weights(fcnod_net* net) {
 void drop_graphs(fcnod_net* net) {
     if (net->graph) { cudaGraphExecDestroy(net->graph); net->graph = 0; }
     if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+    for (int i = 0; i < 2; ++i)
+        if (net->slots[i].graph) { cudaGraphExecDestroy(net->slots[i].graph); net->slots[i].graph = 0; }
 }
 
 void free_activations(fcnod_net* net) {
@@ -1264,13 +1273,16 @@ void free_activations(fcnod_net* net) {
     if (net->data_dev) { cudaFree(net->data_dev); net->data_dev = 0; }
     if (net->scratch_export) { cudaFree(net->scratch_export); net->scratch_export = 0; net->scratch_export_elems = 0; }
     if (net->post_scratch) { cudaFree(net->post_scratch); net->post_scratch = 0; }
-    if (net->det_dev) { cudaFree(net->det_dev); net->det_dev = 0; }
-    if (net->label_dev) { cudaFree(net->label_dev); net->label_dev = 0; }
-    if (net->weight_dev) { cudaFree(net->weight_dev); net->weight_dev = 0; }
-    if (net->count_dev) { cudaFree(net->count_dev); net->count_dev = 0; }
+    if (net->det_dev) { cudaFree(net->det_dev); net->det_dev = 0; }      // one block: det | label | weight | count
+    net->label_dev = net->weight_dev = net->count_dev = 0;
     if (net->srchw_dev) { cudaFree(net->srchw_dev); net->srchw_dev = 0; }
+    net->srchw_b = 0;
     if (net->img_dev) { cudaFree(net->img_dev); net->img_dev = 0; net->img_dev_bytes = 0; }
     if (net->pre_scratch) { cudaFree(net->pre_scratch); net->pre_scratch = 0; }
+    for (int i = 0; i < 2; ++i) {
+        if (net->slots[i].s2d) { cudaFree(net->slots[i].s2d); net->slots[i].s2d = 0; }
+        if (net->slots[i].mm) { cudaFree(net->slots[i].mm); net->slots[i].mm = 0; }
+    }
     drop_graphs(net);
     if (net->pinned_in) { cudaFreeHost(net->pinned_in); net->pinned_in = 0; net->pinned_in_bytes = 0; }
     if (net->pinned_out) { cudaFreeHost(net->pinned_out); net->pinned_out = 0; }
@@ -1867,10 +1879,12 @@ void ensure_detect_buffers(fcnod_net* net) {
     const int B = net->capacity;
     const int c_cvg = net->blobs[blob_id(net, "coverage")].C;
     if (!net->post_scratch) FCNOD_CUDA(cudaMalloc(&net->post_scratch, postnet_scratch_bytes(B, c_cvg)));
-    if (!net->det_dev) FCNOD_CUDA(cudaMalloc(&net->det_dev, (size_t)B * FCNOD_MAX_DET * 5 * 4));
-    if (!net->label_dev) FCNOD_CUDA(cudaMalloc(&net->label_dev, (size_t)B * FCNOD_MAX_DET * 4));
-    if (!net->weight_dev) FCNOD_CUDA(cudaMalloc(&net->weight_dev, (size_t)B * FCNOD_MAX_DET * 4));
-    if (!net->count_dev) FCNOD_CUDA(cudaMalloc(&net->count_dev, (size_t)B * 4));
+    // detections of a batch are ONE contiguous block laid out for the CURRENT batch size b: det [b][M][5] | label [b][M] |
+    // weight [b][M] | count [b] -- the layout of the pinned result buffers, so that they leave the device in one copy
+    if (!net->det_dev) FCNOD_CUDA(cudaMalloc(&net->det_dev, (size_t)B * (FCNOD_MAX_DET * 7 + 1) * 4));
+    net->label_dev = net->det_dev + (size_t)net->batch * FCNOD_MAX_DET * 5;
+    net->weight_dev = net->label_dev + (size_t)net->batch * FCNOD_MAX_DET;
+    net->count_dev = net->weight_dev + (size_t)net->batch * FCNOD_MAX_DET;
     if (!net->srchw_dev) FCNOD_CUDA(cudaMalloc(&net->srchw_dev, (size_t)B * 2 * 4));
     if (!net->pinned_out) FCNOD_CUDA(cudaMallocHost(&net->pinned_out, (size_t)B * (FCNOD_MAX_DET * 7 + 1) * 4));
 }
@@ -1912,10 +1926,8 @@ void copy_detections_out(fcnod_net* net, int B, int32_t* out_det, int32_t* out_l
     int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
     int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
     int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
-    FCNOD_CUDA(cudaMemcpyAsync(p_det, net->det_dev, (size_t)B * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_lab, net->label_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_w, net->weight_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_cnt, net->count_dev, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    FCNOD_CHECK(B == net->batch, "internal: detection buffers are laid out for another batch size");
+    FCNOD_CUDA(cudaMemcpyAsync(p_det, net->det_dev, (size_t)B * (FCNOD_MAX_DET * 7 + 1) * 4, cudaMemcpyDeviceToHost, s));
     FCNOD_CUDA(cudaStreamSynchronize(s));
     memcpy(out_det, p_det, (size_t)B * FCNOD_MAX_DET * 5 * 4);
     memcpy(out_label, p_lab, (size_t)B * FCNOD_MAX_DET * 4);
@@ -2405,6 +2417,7 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
         }
         std::vector<int32_t> hw((size_t)Bc * 2);
         for (int i = 0; i < Bc; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
+        net->srchw_b = 0;      // (the streaming path's cache of what srchw_dev holds)
         FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice, s));
         for (int c = 0; c < 2; ++c) {
             FCNOD_CUDA(cudaMemcpyAsync(net->img_dev + c * cbytes, images + c * cbytes, cbytes, cudaMemcpyHostToDevice, net->copy_stream));
@@ -2445,6 +2458,7 @@ int fcnod_detect(fcnod_net* net, const uint8_t* images, int B, int src_h, int sr
     ensure_detect_buffers(net);
     std::vector<int32_t> hw((size_t)B * 2);
     for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
+    net->srchw_b = 0;
     FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice, s));
     FCNOD_CUDA(cudaStreamSynchronize(s));   // hw is a stack-lifetime host buffer
     FCNOD_CUDA(cudaMemcpyAsync(net->img_dev, images, ibytes, cudaMemcpyHostToDevice, s));
@@ -2497,43 +2511,88 @@ int fcnod_detect_submit(fcnod_net* net, const uint8_t* images, int B, int src_h,
     ensure_detect_buffers(net);
     // forward + post-net as one graph (built on first use, rebuilt when the batch or the thresholds change)
     static const bool no_sgraph = getenv("FCNOD_NO_STREAM_GRAPH") != nullptr;
-    if (!no_sgraph && (!net->sgraph || memcmp(&net->sgraph_p, p, sizeof(*p)) != 0)) {
-        if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+    static const bool no_slot_prelude = getenv("FCNOD_NO_SLOT_PRELUDE") != nullptr;
+    auto capture = [&](cudaGraphExec_t* out, bool skip_input) {
         postnet_prepare(p->eps);          // per-device one-time set-up happens outside the capture (submit may be the first call)
         cudaGraph_t g = 0;
         FCNOD_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
         try {
-            detect_device(net, net->data_dev, net->srchw_dev, *p, s, net->fused_prelude);
+            detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip_input);
         } catch (...) {
             cudaStreamEndCapture(s, &g);
             if (g) cudaGraphDestroy(g);
             throw;
         }
         FCNOD_CUDA(cudaStreamEndCapture(s, &g));
-        cudaError_t ge = cudaGraphInstantiate(&net->sgraph, g, 0);
+        cudaError_t ge = cudaGraphInstantiate(out, g, 0);
         cudaGraphDestroy(g);
         FCNOD_CUDA(ge);
-        net->sgraph_p = *p;
-    }
-    // upload on the copy stream: overlaps whatever the compute stream is still doing for the previous ticket.
-    // The slot's previous reader (the prelude of ticket-2) finished before that ticket was collected.
-    FCNOD_CUDA(cudaMemcpyAsync(sl.img, images, ibytes, cudaMemcpyHostToDevice, net->copy_stream));
-    FCNOD_CUDA(cudaEventRecord(sl.up, net->copy_stream));
+    };
     int32_t* hw = sl.pinned;
     for (int i = 0; i < B; ++i) { hw[2 * i] = src_h; hw[2 * i + 1] = src_w; }
-    FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
-    FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
-    const bool skip = detect_prelude(net, sl.img, B, src_h, src_w, s);
-    if (net->sgraph) FCNOD_CUDA(cudaGraphLaunch(net->sgraph, s));
-    else detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip);
+    // the per-frame source sizes on the device change only when the caller's frames do: no copy per batch
+    const bool hw_same = net->srchw_b == B && net->srchw_h == src_h && net->srchw_w == src_w;
+    net->srchw_b = B; net->srchw_h = src_h; net->srchw_w = src_w;
+    if (net->fused_prelude && !no_sgraph && !no_slot_prelude) {
+        // Slot-private prelude: the frames are uploaded AND turned into this slot's space-to-depth image on the copy stream,
+        // overlapping the previous batch's network; the slot's graph has conv1 read that image.
+        const Step& s0 = net->steps[0];
+        Buffer& sb = net->buffers[s0.s2d_buf];
+        if (!sl.s2d) {
+            const size_t bytes = (size_t)net->capacity * sb.C * sb.H * sb.W * dsize(sb.dtype);
+            FCNOD_CUDA(cudaMalloc(&sl.s2d, bytes));
+            FCNOD_CUDA(cudaMemset(sl.s2d, 0, bytes));            // the zero padding of the image is written once
+            FCNOD_CUDA(cudaMalloc(&sl.mm, (size_t)net->capacity * 6 * 4));
+        }
+        if (!sl.graph || memcmp(&sl.graph_p, p, sizeof(*p)) != 0) {
+            if (sl.graph) { cudaGraphExecDestroy(sl.graph); sl.graph = 0; }
+            void* const keep = sb.ptr;
+            sb.ptr = sl.s2d;                                      // conv1's operand = this slot's image, for the capture only
+            for (size_t i = 0; i < net->steps.size(); ++i)
+                if (net->steps[i].kind == S_CONV_TC && net->convs[net->steps[i].conv].s2d) setup_tc_step(net, net->steps[i]);
+            try {
+                capture(&sl.graph, true);
+            } catch (...) {
+                sb.ptr = keep;
+                for (size_t i = 0; i < net->steps.size(); ++i)
+                    if (net->steps[i].kind == S_CONV_TC && net->convs[net->steps[i].conv].s2d) setup_tc_step(net, net->steps[i]);
+                throw;
+            }
+            sb.ptr = keep;
+            for (size_t i = 0; i < net->steps.size(); ++i)
+                if (net->steps[i].kind == S_CONV_TC && net->convs[net->steps[i].conv].s2d) setup_tc_step(net, net->steps[i]);
+            sl.graph_p = *p;
+        }
+        FCNOD_CUDA(cudaMemcpyAsync(sl.img, images, ibytes, cudaMemcpyHostToDevice, net->copy_stream));
+        preprocess_s2d_launch(sl.img, B, src_h, src_w, in.H, in.W, sl.s2d, s0.s2d_wp, s0.s2d_hp, s0.s2d_padl, sl.mm, net->copy_stream);
+        FCNOD_CUDA(cudaEventRecord(sl.up, net->copy_stream));
+        net->data_img = sl.img; net->data_img_b = B; net->data_img_h = src_h; net->data_img_w = src_w;
+        net->data_valid = false;
+        if (!hw_same) FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
+        FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
+        FCNOD_CUDA(cudaGraphLaunch(sl.graph, s));
+    } else {
+        if (!no_sgraph && (!net->sgraph || memcmp(&net->sgraph_p, p, sizeof(*p)) != 0)) {
+            if (net->sgraph) { cudaGraphExecDestroy(net->sgraph); net->sgraph = 0; }
+            capture(&net->sgraph, net->fused_prelude);
+            net->sgraph_p = *p;
+        }
+        // upload on the copy stream: overlaps whatever the compute stream is still doing for the previous ticket.
+        // The slot's previous reader (the prelude of ticket-2) finished before that ticket was collected.
+        FCNOD_CUDA(cudaMemcpyAsync(sl.img, images, ibytes, cudaMemcpyHostToDevice, net->copy_stream));
+        FCNOD_CUDA(cudaEventRecord(sl.up, net->copy_stream));
+        FCNOD_CUDA(cudaMemcpyAsync(net->srchw_dev, hw, (size_t)B * 2 * 4, cudaMemcpyHostToDevice, s));
+        FCNOD_CUDA(cudaStreamWaitEvent(s, sl.up, 0));
+        const bool skip = detect_prelude(net, sl.img, B, src_h, src_w, s);
+        if (net->sgraph) FCNOD_CUDA(cudaGraphLaunch(net->sgraph, s));
+        else detect_device(net, net->data_dev, net->srchw_dev, *p, s, skip);
+    }
     int32_t* p_det = sl.pinned + (size_t)B * 2;
     int32_t* p_lab = p_det + (size_t)B * FCNOD_MAX_DET * 5;
     int32_t* p_w = p_lab + (size_t)B * FCNOD_MAX_DET;
     int32_t* p_cnt = p_w + (size_t)B * FCNOD_MAX_DET;
-    FCNOD_CUDA(cudaMemcpyAsync(p_det, net->det_dev, (size_t)B * FCNOD_MAX_DET * 5 * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_lab, net->label_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_w, net->weight_dev, (size_t)B * FCNOD_MAX_DET * 4, cudaMemcpyDeviceToHost, s));
-    FCNOD_CUDA(cudaMemcpyAsync(p_cnt, net->count_dev, (size_t)B * 4, cudaMemcpyDeviceToHost, s));
+    (void)p_lab; (void)p_w; (void)p_cnt;       // one block on the device, one block in the pinned buffer: one copy
+    FCNOD_CUDA(cudaMemcpyAsync(p_det, net->det_dev, (size_t)B * (FCNOD_MAX_DET * 7 + 1) * 4, cudaMemcpyDeviceToHost, s));
     FCNOD_CUDA(cudaEventRecord(sl.done, s));
     sl.B = B;
     sl.ticket = net->next_ticket;
