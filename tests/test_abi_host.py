@@ -46,7 +46,7 @@ def test_plan_only_handle(built_lib, model_files):
             # deploy mode: every convolution on tcgen05 (conv1 through the space-to-depth fold), fused pool/LRN pairs
             assert not any('conv_simt' in l for l in plan) and len(plan) < 77
             assert any('+s2d+power' in l for l in plan) and any(l.split()[1] == 's2d' for l in plan)
-            assert any(l.split()[1] == 'pool+lrn' for l in plan) and any(l.split()[1] == 'lrn+pool' for l in plan)
+            assert any(l.split()[1] == 'pool+lrn' for l in plan) and any('+lrn(conv2/norm2)' in l for l in plan)
         assert not any('relu' == l.split()[1] for l in plan)          # all 57 ReLUs fused into conv epilogues
         assert not any('concat-copy' in l for l in plan)              # all 9 Concats eliminated
         d = (C.c_int * 4)()
