@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, 'libfcnod_b200.so')
 FCNOD_PRECISION_FP32 = 0
 FCNOD_PRECISION_BF16 = 1
 FCNOD_MAX_DET = 64
+FCNOD_AUG_NOALLOC_MAX_N = 4096
 
 
 class FcnodError(RuntimeError):
@@ -100,6 +101,7 @@ SIGNATURES = {
     'fcnod_aug_scratch_bytes': (_SZ, [_I]),
     'fcnod_aug_forward_device': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    'fcnod_aug_forward_device_noalloc': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_photo_scratch_bytes': (_SZ, [_I, _I, _I]),
     'fcnod_aug_forward_photo_device': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'fcnod_aug_forward_photo': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),

@@ -505,3 +505,62 @@ int fcnod_aug_forward_photo(const float* data_in, const float* label, const fcno
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------ allocation-free variant
+// For callers that may not allocate device memory (stream capture, serving loops, harnesses that forbid cudaMalloc): the
+// layer forward with its per-image geometry records (the `scratch` argument of fcnod_aug_forward_device) in a fixed
+// array that lives in the library's image.  No counterpart in the reference.
+//   * every GPU that loads the library holds FCNOD_AUG_NOALLOC_MAX_N * sizeof(AugGeom) = 4096 * 48 B = 192 KiB until exit;
+//   * all calls on one device share the array: calls that overlap on the GPU (different streams, different threads) race;
+//   * the array keeps the last call's records; aug_geometry_kernel rewrites every field of records [0, N) at the start of
+//     each call, the min / max accumulators of aug_minmax_kernel included, so nothing has to be cleared between calls.
+// In host code `g_aug_noalloc_scratch` is only a handle for the symbol, not a device address: the address is looked up
+// once per device with cudaGetSymbolAddress (no allocation) and that pointer is what the kernels receive.
+#include <mutex>
+
+namespace {
+
+constexpr int kAugNoallocMaxN = 4096;       // == FCNOD_AUG_NOALLOC_MAX_N (include/fcnod_b200.h)
+constexpr int kAugNoallocMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_aug_noalloc_scratch[(size_t)kAugNoallocMaxN * sizeof(AugGeom)];
+
+void* aug_noalloc_scratch_ptr() {
+    static std::mutex mu;
+    static void* addr[kAugNoallocMaxDevices] = {};
+    int dev = -1;
+    FCNOD_CUDA(cudaGetDevice(&dev));
+    FCNOD_CHECK(dev >= 0 && dev < kAugNoallocMaxDevices, "aug noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = 0;
+        FCNOD_CUDA(cudaGetSymbolAddress(&p, g_aug_noalloc_scratch));      // this device's copy: the device is current here
+        FCNOD_CHECK(p != 0, "aug noalloc: cudaGetSymbolAddress returned a null address");
+        addr[dev] = p;
+    }
+    return addr[dev];
+}
+
+}  // namespace
+
+extern "C" {
+
+int fcnod_aug_forward_device_noalloc(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N, int src_h,
+                                     int src_w, int net_h, int net_w, int stride, int num_classes, float* top_data, float* fg,
+                                     float* bbox, float* size, float* obj, float* cvg, int32_t* rects_out, void* stream) {
+    FCNOD_API_BEGIN
+    static_assert(kAugNoallocMaxN == FCNOD_AUG_NOALLOC_MAX_N, "header and kernel disagree on the limit");
+    if (N > kAugNoallocMaxN) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "fcnod_aug_forward_device_noalloc: N = %d images exceeds FCNOD_AUG_NOALLOC_MAX_N = %d "
+                 "(the fixed scratch array); split the batch or use fcnod_aug_forward_device with caller scratch", N, kAugNoallocMaxN);
+        FCNOD_CHECK(false, msg);
+    }
+    void* scratch = aug_noalloc_scratch_ptr();
+    int rc = fcnod_aug_forward_photo_device(data_in, label, draws, 0, N, src_h, src_w, net_h, net_w, stride, num_classes, top_data, fg,
+                                            bbox, size, obj, cvg, rects_out, scratch, 0, stream);
+    if (rc != 0) return rc;      // last-error string already set by the callee
+    FCNOD_API_END
+}
+
+}  // extern "C"

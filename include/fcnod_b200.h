@@ -226,6 +226,21 @@ int fcnod_aug_forward(const float* data_in, const float* label, const fcnod_aug_
                       float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
                       int32_t* rects_out);
 
+/* Allocation-free variant of fcnod_aug_forward_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that may not allocate device memory (stream capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same arguments, results and error behaviour as fcnod_aug_forward_device minus `scratch`: the
+ * per-image geometry records live in a fixed `static __device__` array inside the library (FCNOD_AUG_NOALLOC_MAX_N * 48 B
+ * = 192 KiB, held by every GPU that loads the library until exit).  N > FCNOD_AUG_NOALLOC_MAX_N is refused with an error
+ * string that names the limit.  The call makes no cudaMalloc / cudaFree / allocating library call; the first call on a
+ * device looks the array's address up (cudaGetSymbolAddress) with that device current.  All calls on a device share
+ * the array: calls that overlap on the GPU (other streams or threads) race -- serialise them.  Nothing needs clearing
+ * between calls (every record in [0, N) is rewritten by the first kernel of each call). */
+#define FCNOD_AUG_NOALLOC_MAX_N 4096
+int fcnod_aug_forward_device_noalloc(const float* data_in, const float* label, const fcnod_aug_draw* draws, int N,
+                                     int src_h, int src_w, int net_h, int net_w, int stride, int num_classes,
+                                     float* top_data, float* fg, float* bbox, float* size, float* obj, float* cvg,
+                                     int32_t* rects_out, void* stream);
+
 /* ---- photometric augmentation of the layer (argumentation_engine.py:308-322, imgaug chain) ----
  * Host-made draws for one image.  blur_kind: 0 none, 1 GaussianBlur (gauss_radius = int(4 sigma + 0.5) <= 12, gauss_w[i] =
  * normalised weight at distance i, computed on the host as scipy.ndimage does), 2 AverageBlur (blur_k in 2..7),
