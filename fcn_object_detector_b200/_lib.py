@@ -37,6 +37,12 @@ class PhotoDraw(C.Structure):
                 ('_pad1', C.c_int32), ('gray_alpha', C.c_double)]
 
 
+class SolverParams(C.Structure):
+    _fields_ = [('base_lr', C.c_float), ('gamma', C.c_float), ('stepsize', C.c_int32), ('momentum', C.c_float),
+                ('momentum2', C.c_float), ('delta', C.c_float), ('weight_decay', C.c_float), ('bbox_loss_weight', C.c_float),
+                ('dropout_ratio_override', C.c_float), ('seed', C.c_uint64)]
+
+
 class AugDraw(C.Structure):
     _fields_ = [('flip', C.c_int32), ('shift_x', C.c_int32), ('shift_y', C.c_int32),
                 ('sign_x', C.c_int32), ('sign_y', C.c_int32), ('_pad', C.c_int32),
@@ -112,6 +118,21 @@ SIGNATURES = {
     'fcnod_train_head_scratch_bytes': (_SZ, []),
     'fcnod_train_head_forward_device': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P, _P, _P]),
     'fcnod_train_head_forward': (_I, [_P] * 7 + [_I, _I, _I, _I, C.c_float, _P, _P, _P]),
+    'fcnod_solver_defaults': (_I, [_P]),
+    'fcnod_trainer_create': (_I, [_STR, _STR, _I, _I, _I, _I, _P, C.POINTER(_P)]),
+    'fcnod_trainer_destroy': (_I, [_P]),
+    'fcnod_trainer_info': (_I, [_P, C.POINTER(_I), C.POINTER(_SZ)]),
+    'fcnod_trainer_buffers': (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
+    'fcnod_trainer_forward_backward_device': (_I, [_P] * 7 + [_P]),
+    'fcnod_trainer_apply_update': (_I, [_P, C.c_float, _P]),
+    'fcnod_trainer_losses': (_I, [_P, _P, _P]),
+    'fcnod_trainer_iteration': (_I, [_P]),
+    'fcnod_trainer_step': (_I, [_P] * 8),
+    'fcnod_trainer_param_read': (_I, [_P, _STR, _I, _I, _P, C.POINTER(_SZ)]),
+    'fcnod_trainer_param_layer': (_STR, [_P, _I]),
+    'fcnod_trainer_blob_read': (_I, [_P, _STR, _I, C.POINTER(_I), _P, _SZ]),
+    'fcnod_trainer_dropout_mask': (_I, [_P, _P, _SZ, C.POINTER(_I)]),
+    'fcnod_trainer_pool_argmax': (_I, [_P, _STR, _P, _SZ, C.POINTER(_I)]),
 }
 
 _lib = None

@@ -19,7 +19,7 @@ COMMON = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-st
           '-Xcompiler', '-fPIC', '-Xcompiler', '-Wall', '-Xptxas', '-v']
 # parity-critical translation units: no FMA contraction
 SOURCES = [('net.cu', []), ('postnet.cu', ['-fmad=false']), ('layer.cu', ['-fmad=false']),
-           ('preproc.cu', ['-fmad=false']), ('train_head.cu', ['-fmad=false']), ('photo.cu', ['-fmad=false']), ('netdef.cpp', []), ('workspace.cpp', [])]
+           ('preproc.cu', ['-fmad=false']), ('train_head.cu', ['-fmad=false']), ('photo.cu', ['-fmad=false']), ('train_net.cu', []), ('netdef.cpp', []), ('workspace.cpp', [])]
 
 
 def _deps():

@@ -23,6 +23,7 @@ struct ConvSimtParams {
     int Ho, Wo, Cout, ldo, ldw;
     int kh, kw, stride, pad;
     int relu;
+    int accum;           // out += result (data gradient of a blob with several consumers, train_net.cu)
 };
 
 template <typename TIn, typename TOut>
@@ -109,6 +110,7 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(ConvSimtParams p) {
             if (n >= p.Cout) continue;
             float v = acc[i][j] + (p.bias ? p.bias[n] : 0.f);
             if (p.relu) v = fmaxf(v, 0.f);
+            if (p.accum) v += to_f32<TOut>(out[m * p.ldo + n]);
             out[m * p.ldo + n] = from_f32<TOut>(v);
         }
     }

@@ -1658,7 +1658,7 @@ void launch_conv_simt(const fcnod_net* net, const Step& st, const LayerDef& L, c
     p.in = view_ptr(net, ib); p.w = cw.d_w_simt; p.bias = cw.d_bias; p.out = view_ptr(net, ob);
     p.N = net->batch; p.H = ib.H; p.W = ib.W; p.Cin = ib.C; p.ldi = ib.ldc;
     p.Ho = ob.H; p.Wo = ob.W; p.Cout = cw.Cout; p.ldo = ob.ldc; p.ldw = cw.ldw;
-    p.kh = p.kw = cw.k; p.stride = L.stride; p.pad = L.pad; p.relu = st.relu ? 1 : 0;
+    p.kh = p.kw = cw.k; p.stride = L.stride; p.pad = L.pad; p.relu = st.relu ? 1 : 0; p.accum = 0;
     long M = (long)net->batch * ob.H * ob.W;
     dim3 grid((unsigned)((M + 63) / 64), (unsigned)(cw.ldw / 64));
     if (ib.dtype == DT_F32 && ob.dtype == DT_F32) conv_simt_kernel<float, float><<<grid, 256, 0, s>>>(p);

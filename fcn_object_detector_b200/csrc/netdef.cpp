@@ -134,7 +134,7 @@ LayerType type_of(const std::string& s) {
 
 }  // namespace
 
-NetDef parse_prototxt_text(const std::string& text) {
+NetDef parse_prototxt_text(const std::string& text, bool train) {
     Lexer lx(text);
     Msg root = parse_msg(lx, true);
     NetDef net;
@@ -142,9 +142,11 @@ NetDef parse_prototxt_text(const std::string& text) {
     std::vector<std::string> dims;
     if (const Msg* shp = root.sub("input_shape")) dims = shp->all("dim");
     else dims = root.all("input_dim");
-    if (net.input_name.empty() || dims.size() != 4)
-        throw std::runtime_error("prototxt: need `input:` and a 4-d input_shape / input_dim");
-    for (int i = 0; i < 4; ++i) net.input_dims[i] = atoi(dims[i].c_str());
+    if (net.input_name.empty() || dims.size() != 4) {
+        if (!train) throw std::runtime_error("prototxt: need `input:` and a 4-d input_shape / input_dim");
+    } else {
+        for (int i = 0; i < 4; ++i) net.input_dims[i] = atoi(dims[i].c_str());
+    }
     for (size_t i = 0; i < root.subs.size(); ++i) {
         if (root.subs[i].first != "layer") continue;
         const Msg& L = root.subs[i].second;
@@ -154,6 +156,21 @@ NetDef parse_prototxt_text(const std::string& text) {
         d.type = type_of(d.type_name);
         d.bottom = L.all("bottom");
         d.top = L.all("top");
+        if (train && (d.type_name == "Data" || d.type_name == "Slice" || d.type_name == "Eltwise" || d.type_name == "L1Loss" ||
+                      d.type_name == "EuclideanLoss")) {
+            TrainSideLayer t;
+            t.name = d.name; t.type_name = d.type_name; t.bottom = d.bottom; t.top = d.top;
+            if (const Msg* sp = L.sub("slice_param")) {
+                std::vector<std::string> pts = sp->all("slice_point");
+                for (size_t k = 0; k < pts.size(); ++k) t.slice_points.push_back(atoi(pts[k].c_str()));
+                if ((int)sp->num("slice_dim", sp->num("axis", 1)) != 1)
+                    throw std::runtime_error("prototxt: '" + d.name + "': only channel slicing is supported");
+            }
+            if (const Msg* ep = L.sub("eltwise_param")) t.eltwise_op = ep->str("operation", "SUM");
+            t.loss_weight = (float)L.num("loss_weight", 1.0);
+            net.train_side.push_back(t);
+            continue;
+        }
         if (d.type == L_UNKNOWN)
             throw std::runtime_error("prototxt: layer '" + d.name + "' has unsupported type '" + d.type_name + "'");
         if (d.top.size() != 1) throw std::runtime_error("prototxt: layer '" + d.name + "' must have exactly one top");
@@ -165,6 +182,15 @@ NetDef parse_prototxt_text(const std::string& text) {
             d.stride = (int)p->num("stride", 1);
             d.pad = (int)p->num("pad", 0);
             d.bias_term = p->str("bias_term", "true") != "false";
+            {
+                int np = 0;
+                for (size_t k = 0; k < L.subs.size() && np < 2; ++k)
+                    if (L.subs[k].first == "param") {
+                        d.lr_mult[np] = (float)L.subs[k].second.num("lr_mult", 1.0);
+                        d.decay_mult[np] = (float)L.subs[k].second.num("decay_mult", 1.0);
+                        ++np;
+                    }
+            }
             if (d.num_output <= 0) throw std::runtime_error("prototxt: '" + d.name + "' num_output missing");
             // square kernels, one stride / pad, dense, ungrouped -- everything models/deploy.prototxt uses.  Anything else
             // would silently compute a different convolution: refuse it.
@@ -202,6 +228,8 @@ NetDef parse_prototxt_text(const std::string& text) {
                 if (p->str("norm_region", "ACROSS_CHANNELS") != "ACROSS_CHANNELS")
                     throw std::runtime_error("prototxt: '" + d.name + "': only ACROSS_CHANNELS LRN is supported");
             }
+        } else if (d.type == L_DROPOUT) {
+            if (const Msg* p = L.sub("dropout_param")) d.dropout_ratio = (float)p->num("dropout_ratio", 0.5);
         } else if (d.type == L_POWER) {
             const Msg* p = L.sub("power_param");
             if (p) {
@@ -212,15 +240,20 @@ NetDef parse_prototxt_text(const std::string& text) {
         }
         net.layers.push_back(d);
     }
+    if (net.input_name.empty()) {
+        // train form: the network input is the bottom of the first body layer (`data`, train_val.prototxt:27-35)
+        if (net.layers.empty() || net.layers[0].bottom.size() != 1) throw std::runtime_error("prototxt: no body layers");
+        net.input_name = net.layers[0].bottom[0];
+    }
     return net;
 }
 
-NetDef parse_prototxt_file(const std::string& path) {
+NetDef parse_prototxt_file(const std::string& path, bool train) {
     std::ifstream f(path.c_str());
     if (!f) throw std::runtime_error("cannot open prototxt '" + path + "'");
     std::stringstream ss;
     ss << f.rdbuf();
-    return parse_prototxt_text(ss.str());
+    return parse_prototxt_text(ss.str(), train);
 }
 
 // ------------------------------------------------------------------ caffemodel (protobuf wire format)

@@ -30,12 +30,29 @@ struct LayerDef {
     float alpha = 1.f, beta = 0.75f, lrn_k = 1.f;
     // Power
     float power = 1.f, scale = 1.f, shift = 0.f;
+    // training side: Dropout ratio, and the `param { lr_mult decay_mult }` records of a Convolution (weights, bias);
+    // caffe.proto defaults where a record is absent
+    float dropout_ratio = 0.5f;
+    float lr_mult[2] = {1.f, 1.f}, decay_mult[2] = {1.f, 1.f};
+};
+
+// Layers of models/train_val.prototxt that are not part of the network body: the two LMDB Data layers (:1-26), the label
+// Slice (:36-52), the Eltwise PROD normalisers / masks (:53-72, :2237-2266) and the two losses (:2267-2281).  The trainer
+// implements that head as one fused kernel (train_head.cu); the parser records what the file says so the trainer can
+// verify that it IS the head it implements.
+struct TrainSideLayer {
+    std::string name, type_name;
+    std::vector<std::string> bottom, top;
+    std::vector<int> slice_points;
+    std::string eltwise_op;
+    float loss_weight = 1.f;
 };
 
 struct NetDef {
     std::string input_name;
     int input_dims[4] = {0, 0, 0, 0};
     std::vector<LayerDef> layers;
+    std::vector<TrainSideLayer> train_side;     // train form only
 };
 
 struct HostBlob {
@@ -55,8 +72,11 @@ struct Datum {
 Datum decode_datum(const uint8_t* buf, size_t len);
 
 // All throw std::runtime_error with a message on malformed input.
-NetDef parse_prototxt_file(const std::string& path);
-NetDef parse_prototxt_text(const std::string& text);
+// train = false: the deploy form (`input:` + 4-d shape, body layers only; anything else is refused).
+// train = true : also accepts the train_val form: no `input:` needed (the input is the bottom of the first body layer, dims
+//                come from the caller), Data / Slice / Eltwise / L1Loss / EuclideanLoss layers go to NetDef::train_side.
+NetDef parse_prototxt_file(const std::string& path, bool train = false);
+NetDef parse_prototxt_text(const std::string& text, bool train = false);
 WeightMap read_caffemodel(const std::string& path);
 
 }  // namespace fcnod

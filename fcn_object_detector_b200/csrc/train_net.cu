@@ -1,0 +1,1024 @@
+// One training iteration of /root/reference/models/train_val.prototxt on the device (BASELINE config 5):
+// forward at TRAIN phase, the fused loss head (train_head.cu), the backward pass of every layer of the body, and Caffe's
+// ADAM ApplyUpdate (/root/reference/train/bounding_box/solver.prototxt:3-15).  fp32 storage and arithmetic throughout: this
+// is the PARITY engine of the training step (1e-4 against torch autograd over the same graph in the tests), the
+// counterpart of the fp32 inference plan; convolutions run on the SIMT implicit-GEMM kernel (conv_simt.cuh) in all three
+// roles:
+//   forward   y  = conv(x, W) + b                                   conv_simt_kernel
+//   dgrad     dx = conv(dy, rot180(W)^T), pad k-1-p                 conv_simt_kernel on weights re-packed by dgrad_pack_kernel
+//   wgrad     dW[(r,s,c)][co] = sum_px x[px + (r,s)][c] * dy[px][co]   wgrad_simt_kernel (split over pixel chunks, fp32 atomics)
+// Layer semantics restated [ext: Caffe layer sources, not vendored upstream]:
+//   Pooling MAX  forward keeps the index of the FIRST maximum of the clipped window in row-major scan order (pooling_layer.cpp's
+//                `>` against -FLT_MAX); backward routes the gradient to that element
+//   LRN          scale = k + alpha/n * sum x^2 over the clipped channel window, y = x * scale^-beta;
+//                dx_c = dy_c * scale_c^-beta - 2 alpha beta / n * x_c * sum_{c' in window} dy_c' * y_c' / scale_c'
+//   Dropout      TRAIN: y = x * mask / (1 - ratio), mask ~ Bernoulli(1 - ratio) per element; same mask in backward
+//   ReLU         in place on the convolution's top: dy *= (y > 0)
+//   Sigmoid      dx = dy * y * (1 - y)
+//   Concat       tops of the branches ARE channel slices of the concat blob (data and diff): no copy either way
+//   Split        a blob with several consumers sums their gradients: the first writer of a diff overwrites, later ones add
+// Activations are NHWC fp32; parameters live in ONE flat fp32 buffer (weights packed [(r,s,c)][Cout padded to 64], then the
+// bias, every blob padded to 256 floats) with the gradients, and ADAM's two moments, in three more buffers of the same
+// layout, so the gradient all-reduce of a multi-GPU step is one collective over one contiguous buffer and the update is one
+// launch.  Padding entries have zero gradient and stay zero.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <vector>
+
+#include "common.cuh"
+#include "conv_simt.cuh"
+#include "kernels.h"
+#include "netdef.h"
+
+namespace fcnod {
+namespace {
+
+inline int grid1(long n, int threads) { return (int)std::min<long>((n + threads - 1) / threads, 148L * 32); }
+
+// ------------------------------------------------------------------------------------------------ layout kernels
+// data NCHW fp32 -> NHWC with the Power layer applied (train_val.prototxt:27-35: shift + scale * x, power 1)
+__global__ void nchw_to_nhwc_power_kernel(const float* __restrict__ in, float* __restrict__ out, int N, int C, int H, int W,
+                                          float scale, float shift) {
+    const long total = (long)N * C * H * W;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        long t = i / C;
+        const int w = (int)(t % W); t /= W;
+        const int h = (int)(t % H);
+        const int n = (int)(t / H);
+        out[i] = __fadd_rn(shift, __fmul_rn(scale, in[((long)(n * C + c) * H + h) * W + w]));
+    }
+}
+
+// NHWC view (ldc, channel offset folded into the pointer) <-> dense NCHW
+__global__ void nhwc_to_nchw_kernel(const float* __restrict__ in, int ldc, float* __restrict__ out, int N, int C, int H, int W) {
+    const long total = (long)N * C * H * W;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int w = (int)(i % W);
+        long t = i / W;
+        const int h = (int)(t % H); t /= H;
+        const int c = (int)(t % C);
+        const int n = (int)(t / C);
+        out[i] = in[((long)(n * H + h) * W + w) * ldc + c];
+    }
+}
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, int ldc, int N, int C, int H, int W) {
+    const long total = (long)N * C * H * W;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int w = (int)(i % W);
+        long t = i / W;
+        const int h = (int)(t % H); t /= H;
+        const int c = (int)(t % C);
+        const int n = (int)(t / C);
+        out[((long)(n * H + h) * W + w) * ldc + c] = in[i];
+    }
+}
+__global__ void u8_nhwc_to_nchw_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int N, int C, int H, int W) {
+    const long total = (long)N * C * H * W;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int w = (int)(i % W);
+        long t = i / W;
+        const int h = (int)(t % H); t /= H;
+        const int c = (int)(t % C);
+        const int n = (int)(t / C);
+        out[i] = in[((long)(n * H + h) * W + w) * C + c];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ pooling
+struct PoolGeo { int N, C, H, W, Ho, Wo, k, s, p, ldi, ldo; };
+
+__global__ void pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
+    const long total = (long)g.N * g.Ho * g.Wo * g.C;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % g.C);
+        long t = i / g.C;
+        const int pw = (int)(t % g.Wo); t /= g.Wo;
+        const int ph = (int)(t % g.Ho);
+        const int n = (int)(t / g.Ho);
+        const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
+        const int hs = max(h0, 0), ws = max(w0, 0);
+        const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
+        float best = -3.402823466e+38f;
+        int bi = 0;
+        for (int h = hs; h < he; ++h)
+            for (int w = ws; w < we; ++w) {
+                const float v = x[((long)(n * g.H + h) * g.W + w) * g.ldi + c];
+                if (v > best) { best = v; bi = (h - h0) * g.k + (w - w0); }
+            }
+        y[((long)(n * g.Ho + ph) * g.Wo + pw) * g.ldo + c] = best;
+        idx[i] = (uint8_t)bi;
+    }
+}
+
+__global__ void pool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ idx, float* __restrict__ dx, PoolGeo g,
+                                int accum) {
+    const long total = (long)g.N * g.H * g.W * g.C;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % g.C);
+        long t = i / g.C;
+        const int w = (int)(t % g.W); t /= g.W;
+        const int h = (int)(t % g.H);
+        const int n = (int)(t / g.H);
+        const int ph0 = (h + g.p < g.k) ? 0 : (h + g.p - g.k) / g.s + 1, ph1 = min((h + g.p) / g.s + 1, g.Ho);
+        const int pw0 = (w + g.p < g.k) ? 0 : (w + g.p - g.k) / g.s + 1, pw1 = min((w + g.p) / g.s + 1, g.Wo);
+        float acc = 0.f;
+        for (int ph = ph0; ph < ph1; ++ph)
+            for (int pw = pw0; pw < pw1; ++pw) {
+                const long o = ((long)(n * g.Ho + ph) * g.Wo + pw);
+                const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
+                if (idx[o * g.C + c] == local) acc += dy[o * g.ldo + c];
+            }
+        const long xi = ((long)(n * g.H + h) * g.W + w) * g.ldi + c;
+        dx[xi] = accum ? dx[xi] + acc : acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ LRN (across channels)
+__global__ void lrn_fwd_kernel(const float* __restrict__ x, int ldi, float* __restrict__ y, int ldo, float* __restrict__ scale,
+                               long npix, int C, int n, float alpha_over_n, float beta, float k) {
+    const long total = npix * C;
+    const int half = n / 2;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long px = i / C;
+        const float* xp = x + px * ldi;
+        float s = 0.f;
+        for (int cc = max(c - half, 0); cc <= min(c + half, C - 1); ++cc) s = fmaf(xp[cc], xp[cc], s);
+        const float sc = fmaf(alpha_over_n, s, k);
+        scale[i] = sc;
+        y[px * ldo + c] = xp[c] * powf(sc, -beta);
+    }
+}
+
+__global__ void lrn_bwd_kernel(const float* __restrict__ x, int ldi, const float* __restrict__ y, const float* __restrict__ dy,
+                               int ldo, const float* __restrict__ scale, float* __restrict__ dx, long npix, int C, int n,
+                               float alpha_over_n, float beta, int accum) {
+    const long total = npix * C;
+    const int half = n / 2;
+    const float cr = 2.f * alpha_over_n * beta;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long px = i / C;
+        float s = 0.f;
+        for (int cc = max(c - half, 0); cc <= min(c + half, C - 1); ++cc)
+            s += dy[px * ldo + cc] * y[px * ldo + cc] / scale[px * C + cc];
+        const float v = dy[px * ldo + c] * powf(scale[i], -beta) - cr * x[px * ldi + c] * s;
+        const long xi = px * ldi + c;
+        dx[xi] = accum ? dx[xi] + v : v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ elementwise
+__device__ __forceinline__ uint32_t mix32(uint64_t z) {        // splitmix64 finaliser
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return (uint32_t)((z ^ (z >> 31)) >> 32);
+}
+
+// Bernoulli(1 - ratio) keep mask: counter-based (seed, iteration, element index), so a step is reproducible
+__global__ void dropout_mask_kernel(uint8_t* __restrict__ mask, long total, uint64_t seed, uint64_t iter, float ratio) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const uint32_t u = mix32(seed * 0x100000001b3ull + iter * 0x9e3779b97f4a7c15ull + (uint64_t)i);
+        mask[i] = ((float)(u >> 8) * (1.f / 16777216.f) >= ratio) ? 1 : 0;
+    }
+}
+// y = x * mask * scale (forward) and dx (+)= dy * mask * scale (backward): same kernel
+__global__ void dropout_apply_kernel(const float* __restrict__ in, const uint8_t* __restrict__ mask, float* __restrict__ out,
+                                     long total, float scale, int accum) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const float v = mask[i] ? __fmul_rn(in[i], scale) : 0.f;
+        out[i] = accum ? out[i] + v : v;
+    }
+}
+__global__ void copy_or_add_kernel(const float* __restrict__ in, float* __restrict__ out, long total, int accum) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
+        out[i] = accum ? out[i] + in[i] : in[i];
+}
+__global__ void sigmoid_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long total) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
+        y[i] = 1.f / (1.f + expf(-x[i]));
+}
+__global__ void sigmoid_bwd_kernel(const float* __restrict__ y, const float* __restrict__ dy, float* __restrict__ dx, long total,
+                                   int accum) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const float v = dy[i] * y[i] * (1.f - y[i]);
+        dx[i] = accum ? dx[i] + v : v;
+    }
+}
+// in-place ReLU backward on a channel slice: dy = y > 0 ? dy : 0
+__global__ void relu_mask_kernel(const float* __restrict__ y, float* __restrict__ dy, long npix, int C, int ldc) {
+    const long total = npix * C;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long o = (i / C) * ldc + (i % C);
+        if (!(y[o] > 0.f)) dy[o] = 0.f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ convolution backward
+// bias gradient: db[c] += sum over pixels of dy[px][c].  grid (ceil(C / 32), pixel chunks), block 32 x 8.
+__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ dy, int ldc, int C, long npix, long chunk,
+                                                         float* __restrict__ db) {
+    __shared__ float red[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const long p0 = blockIdx.y * chunk, p1 = min(p0 + chunk, npix);
+    float s = 0.f;
+    if (c < C)
+        for (long p = p0 + threadIdx.y; p < p1; p += 8) s += dy[p * ldc + c];
+    red[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a += red[j][threadIdx.x];
+        atomicAdd(db + c, a);
+    }
+}
+
+struct WgradParams {
+    const float* x;     // bottom, NHWC view
+    const float* dy;    // top diff, NHWC view
+    float* g;           // [K][ldw] packed weight gradient (accumulated with atomics; zeroed by the caller)
+    int N, H, W, Cin, ldi;
+    int Ho, Wo, Cout, ldo, ldw;
+    int k, stride, pad;
+    long chunk;         // pixels per blockIdx.z
+};
+
+// G[kk][co] += sum_m A[m][kk] * dy[m][co], A = im2col(x) gathered on the fly, kk = (r*k + s)*Cin + c.
+// Tile 64 (kk) x 64 (co), 16 pixels per step, 256 threads, 4x4 register micro-tile.
+__global__ void __launch_bounds__(256) wgrad_simt_kernel(WgradParams p) {
+    constexpr int BK = 64, BN = 64, BP = 16;
+    __shared__ float As[BP][BK + 4];
+    __shared__ float Bs[BP][BN + 4];
+    const int tid = threadIdx.x;
+    const int tx = tid % 16, ty = tid / 16;
+    const int K = p.k * p.k * p.Cin;
+    const long M = (long)p.N * p.Ho * p.Wo;
+    const int k0 = blockIdx.x * BK, n0 = blockIdx.y * BN;
+    const long m_begin = blockIdx.z * p.chunk, m_end = min(m_begin + p.chunk, M);
+
+    // this thread's gather column: kk = k0 + tid % 64 -> (c, r, s), fixed for the whole loop
+    const int kl = tid % BK, prow = tid / BK;        // pixel rows prow, prow + 4, prow + 8, prow + 12
+    const int kk = k0 + kl;
+    const bool kok = kk < K;
+    int c = 0, r = 0, s = 0;
+    if (kok) { c = kk % p.Cin; const int rs = kk / p.Cin; s = rs % p.k; r = rs / p.k; }
+    const int co = n0 + tid % BN;
+    const bool cok = co < p.Cout;
+
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (long m0 = m_begin; m0 < m_end; m0 += BP) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const long m = m0 + prow + 4 * i;
+            float a = 0.f, b = 0.f;
+            if (m < m_end) {
+                const int ow = (int)(m % p.Wo);
+                const long t = m / p.Wo;
+                const int oh = (int)(t % p.Ho);
+                const int n = (int)(t / p.Ho);
+                const int ih = oh * p.stride - p.pad + r, iw = ow * p.stride - p.pad + s;
+                if (kok && ih >= 0 && ih < p.H && iw >= 0 && iw < p.W) a = p.x[((long)(n * p.H + ih) * p.W + iw) * p.ldi + c];
+                if (cok) b = p.dy[m * p.ldo + co];
+            }
+            As[prow + 4 * i][kl] = a;
+            Bs[prow + 4 * i][tid % BN] = b;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < BP; ++q) {
+            float a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[q][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[q][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = k0 + ty * 4 + i;
+        if (row >= K) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int col = n0 + tx * 4 + j;
+            if (col < p.Cout) atomicAdd(p.g + (long)row * p.ldw + col, acc[i][j]);
+        }
+    }
+}
+
+// weights packed for the forward, P[((r*k + s)*Cin + c)][ldw] (co fastest), re-packed for the data gradient:
+// T[((r'*k + s')*Cout + co)][ldt] (c fastest) = P[(((k-1-r')*k + (k-1-s'))*Cin + c)][co]
+__global__ void dgrad_pack_kernel(const float* __restrict__ P, int ldw, float* __restrict__ T, int ldt, int Cin, int Cout, int k) {
+    const long total = (long)k * k * Cout * ldt;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % ldt);
+        long t = i / ldt;
+        const int co = (int)(t % Cout);
+        const int rs = (int)(t / Cout);
+        const int r = rs / k, s = rs % k;
+        T[i] = c < Cin ? P[((long)((k - 1 - r) * k + (k - 1 - s)) * Cin + c) * ldw + co] : 0.f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ solver
+struct AdamArgs {
+    float rate, correction, b1, b2, eps, weight_decay, grad_scale;
+};
+// One launch over the flat parameter buffer; meta[i / 256] = (lr_mult, decay_mult) of the blob that owns element i.
+// Caffe's order: Normalize / all-reduce scale, Regularize (L2), ComputeUpdateValue (ADAM), Update.
+__global__ void adam_kernel(float* __restrict__ w, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            const float2* __restrict__ meta, long total, AdamArgs a) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const float2 mt = meta[i >> 8];
+        float gi = __fmul_rn(g[i], a.grad_scale);
+        gi = __fadd_rn(gi, __fmul_rn(__fmul_rn(a.weight_decay, mt.y), w[i]));
+        const float mi = __fadd_rn(__fmul_rn(a.b1, m[i]), __fmul_rn(1.f - a.b1, gi));
+        const float vi = __fadd_rn(__fmul_rn(a.b2, v[i]), __fmul_rn(1.f - a.b2, __fmul_rn(gi, gi)));
+        m[i] = mi; v[i] = vi;
+        const float step = __fmul_rn(__fmul_rn(__fmul_rn(a.rate, mt.x), a.correction), __fdiv_rn(mi, __fadd_rn(__fsqrt_rn(vi), a.eps)));
+        w[i] = __fsub_rn(w[i], step);
+        g[i] = gi;
+    }
+}
+
+}  // namespace
+}  // namespace fcnod
+
+using namespace fcnod;
+
+// =================================================================================================== the trainer
+namespace {
+
+struct TBuf { int C = 0, H = 0, W = 0; float* data = 0; float* diff = 0; };
+struct TBlob {
+    std::string name;
+    int C = 0, H = 0, W = 0;
+    int buf = -1, c_off = 0, ldc = 0;
+    bool needs_grad = true;      // false for the network input and its Power transform
+    bool diff_written = false;   // per backward pass; slices of a concat blob share the flag of the concat blob
+    int root = -1;               // blob whose flag this one shares (-1: itself)
+};
+struct TConv {
+    int Cout = 0, Cin = 0, k = 1, stride = 1, pad = 0, K = 0, ldw = 0, ldt = 0;
+    size_t w_off = 0, b_off = 0;     // floats into the flat parameter buffer
+    float* d_wt = 0;                 // dgrad packing [(r,s,co)][ldt], rebuilt every step
+    float lr_mult[2], decay_mult[2];
+    std::string name;
+};
+struct TLayer {
+    LayerDef def;
+    int in = -1, out = -1, conv = -1;
+    bool relu = false, skip = false;
+    uint8_t* idx = 0;      // Pooling: argmax of every output element
+    float* scale = 0;      // LRN: the scale blob
+    uint8_t* mask = 0;     // Dropout: keep mask (NHWC order)
+};
+
+}  // namespace
+
+struct fcnod_trainer {
+    int device = 0, batch = 0, in_c = 3, in_h = 0, in_w = 0, num_classes = 1;
+    fcnod_solver_params solver;
+    NetDef def;
+    std::vector<TBlob> blobs;
+    std::map<std::string, int> blob_index;
+    std::vector<TBuf> bufs;
+    std::vector<TConv> convs;
+    std::vector<TLayer> layers;
+    size_t n_params = 0;                      // floats in each flat buffer (multiple of 256)
+    float *params = 0, *grads = 0, *m = 0, *v = 0;
+    float2* meta = 0;
+    int cov_blob = -1, box_blob = -1, gh = 0, gw = 0;
+    float *cov_nchw = 0, *box_nchw = 0, *dcov_nchw = 0, *dbox_nchw = 0, *losses_dev = 0;
+    void* head_scratch = 0;
+    uint8_t* mask_nchw = 0;
+    float* stage = 0;                         // host-buffer step: device copies of the inputs
+    int iter = 0;
+    cudaStream_t stream = 0;
+    std::vector<void*> allocs;
+};
+
+namespace {
+
+template <typename T> T* dalloc(fcnod_trainer* t, size_t n) {
+    void* p = 0;
+    FCNOD_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    t->allocs.push_back(p);
+    return static_cast<T*>(p);
+}
+
+int blob_of(fcnod_trainer* t, const std::string& n) {
+    std::map<std::string, int>::iterator it = t->blob_index.find(n);
+    FCNOD_CHECK(it != t->blob_index.end(), "trainer: unknown blob '" + n + "'");
+    return it->second;
+}
+float* bdata(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].data + b.c_off; }
+float* bdiff(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].diff + b.c_off; }
+TBlob& root_of(fcnod_trainer* t, int b) { return t->blobs[t->blobs[b].root >= 0 ? t->blobs[b].root : b]; }
+// first writer of a diff overwrites, later writers accumulate (Caffe's Split layer)
+int claim_diff(fcnod_trainer* t, int b) {
+    TBlob& r = root_of(t, b);
+    const int accum = r.diff_written ? 1 : 0;
+    r.diff_written = true;
+    return accum;
+}
+
+int caffe_pool_out_t(int h, int k, int s, int p) {
+    int o = (int)std::ceil((h + 2 * p - k) / (double)s) + 1;
+    if (p > 0 && (o - 1) * s >= h + p) --o;
+    return o;
+}
+
+// the train-side layers of a train_val-form prototxt must be the head train_head.cu implements
+void verify_train_side(const NetDef& def, int num_classes, float bbox_loss_weight) {
+    for (size_t i = 0; i < def.train_side.size(); ++i) {
+        const TrainSideLayer& L = def.train_side[i];
+        if (L.type_name == "Slice") {
+            const int c = num_classes;
+            const int want[4] = {c, 5 * c, 9 * c, 13 * c};
+            FCNOD_CHECK(L.slice_points.size() == 4 && L.top.size() == 5, "trainer: '" + L.name + "': expected 4 slice points / 5 tops");
+            for (int k = 0; k < 4; ++k)
+                FCNOD_CHECK(L.slice_points[k] == want[k], "trainer: '" + L.name + "': slice points do not match num_classes (expected c, 5c, 9c, 13c)");
+        } else if (L.type_name == "Eltwise") {
+            FCNOD_CHECK(L.eltwise_op == "PROD" && L.bottom.size() == 2, "trainer: '" + L.name + "': only two-input Eltwise PROD is part of the head");
+        } else if (L.type_name == "L1Loss") {
+            FCNOD_CHECK(std::fabs(L.loss_weight - bbox_loss_weight) < 1e-6f, "trainer: '" + L.name + "': loss_weight differs from the solver parameters' bbox_loss_weight");
+        } else if (L.type_name == "EuclideanLoss") {
+            FCNOD_CHECK(std::fabs(L.loss_weight - 1.f) < 1e-6f, "trainer: '" + L.name + "': loss_weight != 1 is not supported");
+        }
+    }
+}
+
+void build_trainer(fcnod_trainer* t, const WeightMap& weights) {
+    const NetDef& def = t->def;
+    const int N = t->batch;
+    // ---- shapes, concat aliasing
+    std::map<std::string, std::pair<std::string, int> > slice_of;   // branch top -> (concat top, channel offset)
+    std::map<std::string, int> chans, hs, ws;
+    chans[def.input_name] = t->in_c; hs[def.input_name] = t->in_h; ws[def.input_name] = t->in_w;
+    for (size_t i = 0; i < def.layers.size(); ++i) {
+        const LayerDef& L = def.layers[i];
+        FCNOD_CHECK(!L.bottom.empty() && chans.count(L.bottom[0]), "trainer: layer '" + L.name + "' reads an undefined blob");
+        const int C = chans[L.bottom[0]], H = hs[L.bottom[0]], W = ws[L.bottom[0]];
+        int oc = C, oh = H, ow = W;
+        if (L.type == L_CONV) {
+            oc = L.num_output;
+            oh = (H + 2 * L.pad - L.kernel) / L.stride + 1;
+            ow = (W + 2 * L.pad - L.kernel) / L.stride + 1;
+        } else if (L.type == L_POOL) {
+            oh = caffe_pool_out_t(H, L.kernel, L.stride, L.pad);
+            ow = caffe_pool_out_t(W, L.kernel, L.stride, L.pad);
+        } else if (L.type == L_CONCAT) {
+            oc = 0;
+            for (size_t b = 0; b < L.bottom.size(); ++b) {
+                FCNOD_CHECK(chans.count(L.bottom[b]) && hs[L.bottom[b]] == H && ws[L.bottom[b]] == W, "trainer: concat '" + L.name + "' shape mismatch");
+                slice_of[L.bottom[b]] = std::make_pair(L.top[0], oc);
+                oc += chans[L.bottom[b]];
+            }
+        }
+        chans[L.top[0]] = oc; hs[L.top[0]] = oh; ws[L.top[0]] = ow;
+    }
+    // ---- blobs + buffers
+    auto add_blob = [&](const std::string& name) -> int {
+        if (t->blob_index.count(name)) return t->blob_index[name];
+        TBlob b;
+        b.name = name; b.C = chans[name]; b.H = hs[name]; b.W = ws[name];
+        std::map<std::string, std::pair<std::string, int> >::iterator so = slice_of.find(name);
+        if (so != slice_of.end()) {
+            // the concat top's buffer is created on first sight of any of its branches
+            const std::string& top = so->second.first;
+            int rb;
+            if (t->blob_index.count(top)) rb = t->blob_index[top];
+            else {
+                TBlob r;
+                r.name = top; r.C = chans[top]; r.H = hs[top]; r.W = ws[top];
+                TBuf bf; bf.C = r.C; bf.H = r.H; bf.W = r.W;
+                t->bufs.push_back(bf);
+                r.buf = (int)t->bufs.size() - 1; r.ldc = r.C;
+                t->blobs.push_back(r);
+                rb = (int)t->blobs.size() - 1;
+                t->blob_index[top] = rb;
+            }
+            b.buf = t->blobs[rb].buf; b.c_off = so->second.second; b.ldc = t->blobs[rb].C; b.root = rb;
+        } else {
+            TBuf bf; bf.C = b.C; bf.H = b.H; bf.W = b.W;
+            t->bufs.push_back(bf);
+            b.buf = (int)t->bufs.size() - 1; b.ldc = b.C;
+        }
+        t->blobs.push_back(b);
+        t->blob_index[name] = (int)t->blobs.size() - 1;
+        return (int)t->blobs.size() - 1;
+    };
+    add_blob(def.input_name);
+    t->blobs[0].needs_grad = false;
+    size_t off = 0;
+    std::vector<float2> meta;
+    for (size_t i = 0; i < def.layers.size(); ++i) {
+        const LayerDef& L = def.layers[i];
+        TLayer tl;
+        tl.def = L;
+        tl.in = blob_of(t, L.bottom[0]);
+        const bool in_place = L.top[0] == L.bottom[0];
+        tl.out = in_place ? tl.in : add_blob(L.top[0]);
+        if (L.type == L_POWER) {
+            FCNOD_CHECK(L.power == 1.f && tl.in == 0, "trainer: only the input Power layer (power 1) is supported");
+            t->blobs[tl.out].needs_grad = false;
+        } else if (L.type == L_RELU) {
+            FCNOD_CHECK(in_place && !t->layers.empty() && t->layers.back().def.type == L_CONV && t->layers.back().out == tl.in,
+                        "trainer: ReLU '" + L.name + "' must run in place on the convolution before it");
+            t->layers.back().relu = true;
+            tl.skip = true;
+        } else if (L.type == L_CONV) {
+            FCNOD_CHECK(!in_place, "trainer: in-place convolution");
+            TConv c;
+            c.name = L.name;
+            c.Cout = L.num_output; c.Cin = t->blobs[tl.in].C; c.k = L.kernel; c.stride = L.stride; c.pad = L.pad;
+            c.K = c.k * c.k * c.Cin; c.ldw = (c.Cout + 63) / 64 * 64; c.ldt = (c.Cin + 63) / 64 * 64;
+            for (int q = 0; q < 2; ++q) { c.lr_mult[q] = L.lr_mult[q]; c.decay_mult[q] = L.decay_mult[q]; }
+            FCNOD_CHECK(L.bias_term, "trainer: convolution '" + L.name + "' without a bias term is not supported");
+            const size_t wn = ((size_t)c.K * c.ldw + 255) / 256 * 256, bn = ((size_t)c.ldw + 255) / 256 * 256;
+            c.w_off = off; off += wn;
+            c.b_off = off; off += bn;
+            for (size_t q = 0; q < wn / 256; ++q) meta.push_back(make_float2(c.lr_mult[0], c.decay_mult[0]));
+            for (size_t q = 0; q < bn / 256; ++q) meta.push_back(make_float2(c.lr_mult[1], c.decay_mult[1]));
+            if (t->blobs[tl.in].needs_grad) {
+                FCNOD_CHECK(c.stride == 1 && 2 * c.pad == c.k - 1, "trainer: data gradient of '" + L.name + "' needs a stride-1 'same' convolution");
+                c.d_wt = dalloc<float>(t, (size_t)c.k * c.k * c.Cout * c.ldt);
+            }
+            t->convs.push_back(c);
+            tl.conv = (int)t->convs.size() - 1;
+        } else if (L.type == L_POOL) {
+            FCNOD_CHECK(L.kernel * L.kernel <= 255, "trainer: pooling window too large");
+            tl.idx = dalloc<uint8_t>(t, (size_t)N * t->blobs[tl.out].H * t->blobs[tl.out].W * t->blobs[tl.out].C);
+        } else if (L.type == L_LRN) {
+            tl.scale = dalloc<float>(t, (size_t)N * t->blobs[tl.out].H * t->blobs[tl.out].W * t->blobs[tl.out].C);
+        } else if (L.type == L_DROPOUT) {
+            FCNOD_CHECK(t->blobs[tl.in].ldc == t->blobs[tl.in].C && t->blobs[tl.out].ldc == t->blobs[tl.out].C, "trainer: dropout on a sliced blob");
+            FCNOD_CHECK(!t->mask_nchw, "trainer: more than one Dropout layer");
+            const size_t n = (size_t)N * t->blobs[tl.out].H * t->blobs[tl.out].W * t->blobs[tl.out].C;
+            tl.mask = dalloc<uint8_t>(t, n);
+            t->mask_nchw = dalloc<uint8_t>(t, n);
+        } else if (L.type == L_CONCAT) {
+            tl.skip = true;
+        } else if (L.type == L_SIGMOID) {
+            FCNOD_CHECK(t->blobs[tl.in].ldc == t->blobs[tl.in].C, "trainer: sigmoid on a sliced blob");
+        }
+        t->layers.push_back(tl);
+    }
+    // ---- activations
+    for (size_t i = 0; i < t->bufs.size(); ++i) {
+        TBuf& b = t->bufs[i];
+        const size_t n = (size_t)N * b.C * b.H * b.W;
+        b.data = dalloc<float>(t, n);
+        b.diff = dalloc<float>(t, n);
+    }
+    // ---- parameters
+    t->n_params = off;
+    t->params = dalloc<float>(t, off); t->grads = dalloc<float>(t, off); t->m = dalloc<float>(t, off); t->v = dalloc<float>(t, off);
+    t->meta = dalloc<float2>(t, meta.size());
+    FCNOD_CUDA(cudaMemcpy(t->meta, meta.data(), meta.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    FCNOD_CUDA(cudaMemset(t->grads, 0, off * 4)); FCNOD_CUDA(cudaMemset(t->m, 0, off * 4)); FCNOD_CUDA(cudaMemset(t->v, 0, off * 4));
+    std::vector<float> host(off, 0.f);
+    for (size_t ci = 0; ci < t->convs.size(); ++ci) {
+        const TConv& c = t->convs[ci];
+        WeightMap::const_iterator it = weights.find(c.name);
+        FCNOD_CHECK(it != weights.end() && it->second.size() >= 2, "trainer: the snapshot has no weights for '" + c.name + "'");
+        const HostBlob& w = it->second[0];
+        const HostBlob& b = it->second[1];
+        FCNOD_CHECK(w.data.size() == (size_t)c.Cout * c.K && b.data.size() == (size_t)c.Cout, "trainer: weight shape mismatch for '" + c.name + "'");
+        for (int co = 0; co < c.Cout; ++co)
+            for (int cc = 0; cc < c.Cin; ++cc)
+                for (int rs = 0; rs < c.k * c.k; ++rs)
+                    host[c.w_off + ((size_t)rs * c.Cin + cc) * c.ldw + co] = w.data[((size_t)co * c.Cin + cc) * c.k * c.k + rs];
+        for (int co = 0; co < c.Cout; ++co) host[c.b_off + co] = b.data[co];
+    }
+    FCNOD_CUDA(cudaMemcpy(t->params, host.data(), off * 4, cudaMemcpyHostToDevice));
+    // ---- head
+    t->cov_blob = blob_of(t, "coverage"); t->box_blob = blob_of(t, "bboxes");
+    const TBlob& cb = t->blobs[t->cov_blob];
+    const TBlob& bb = t->blobs[t->box_blob];
+    FCNOD_CHECK(bb.C == 4 * cb.C && bb.H == cb.H && bb.W == cb.W, "trainer: `bboxes` must have 4 channels per `coverage` channel");
+    t->num_classes = cb.C; t->gh = cb.H; t->gw = cb.W;
+    const size_t n1 = (size_t)N * cb.C * cb.H * cb.W;
+    t->cov_nchw = dalloc<float>(t, n1); t->dcov_nchw = dalloc<float>(t, n1);
+    t->box_nchw = dalloc<float>(t, 4 * n1); t->dbox_nchw = dalloc<float>(t, 4 * n1);
+    t->losses_dev = dalloc<float>(t, 2);
+    t->head_scratch = dalloc<char>(t, fcnod_train_head_scratch_bytes());
+}
+
+void launch_conv(const float* in, int ldi, int H, int W, int Cin, const float* w, int ldw, const float* bias, float* out, int ldo,
+                 int Ho, int Wo, int Cout, int N, int k, int stride, int pad, int relu, int accum, cudaStream_t s) {
+    ConvSimtParams p;
+    p.in = in; p.w = w; p.bias = bias; p.out = out;
+    p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.ldi = ldi;
+    p.Ho = Ho; p.Wo = Wo; p.Cout = Cout; p.ldo = ldo; p.ldw = ldw;
+    p.kh = p.kw = k; p.stride = stride; p.pad = pad; p.relu = relu; p.accum = accum;
+    const long M = (long)N * Ho * Wo;
+    dim3 grid((unsigned)((M + 63) / 64), (unsigned)(ldw / 64));
+    conv_simt_kernel<float, float><<<grid, 256, 0, s>>>(p);
+    FCNOD_CUDA(cudaGetLastError());
+}
+
+void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
+    const int N = t->batch;
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        TLayer& L = t->layers[li];
+        if (L.skip) continue;
+        const TBlob& ib = t->blobs[L.in];
+        const TBlob& ob = t->blobs[L.out];
+        const long in_px = (long)N * ib.H * ib.W, out_px = (long)N * ob.H * ob.W;
+        switch (L.def.type) {
+        case L_POWER:
+            nchw_to_nhwc_power_kernel<<<grid1(in_px * ib.C, 256), 256, 0, s>>>(data_nchw, bdata(t, ob), N, ib.C, ib.H, ib.W, L.def.scale, L.def.shift);
+            break;
+        case L_CONV: {
+            const TConv& c = t->convs[L.conv];
+            launch_conv(bdata(t, ib), ib.ldc, ib.H, ib.W, c.Cin, t->params + c.w_off, c.ldw, t->params + c.b_off, bdata(t, ob), ob.ldc,
+                        ob.H, ob.W, c.Cout, N, c.k, c.stride, c.pad, L.relu ? 1 : 0, 0, s);
+            break;
+        }
+        case L_POOL: {
+            PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
+            pool_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), bdata(t, ob), L.idx, g);
+            break;
+        }
+        case L_LRN:
+            lrn_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), ib.ldc, bdata(t, ob), ob.ldc, L.scale, out_px, ob.C,
+                                                                      L.def.local_size, L.def.alpha / (float)L.def.local_size, L.def.beta, L.def.lrn_k);
+            break;
+        case L_DROPOUT: {
+            const long n = out_px * ob.C;
+            if (t->solver.dropout_ratio_override >= 0.f) L.def.dropout_ratio = t->solver.dropout_ratio_override;
+            dropout_mask_kernel<<<grid1(n, 256), 256, 0, s>>>(L.mask, n, t->solver.seed, (uint64_t)t->iter, L.def.dropout_ratio);
+            dropout_apply_kernel<<<grid1(n, 256), 256, 0, s>>>(bdata(t, ib), L.mask, bdata(t, ob), n, 1.f / (1.f - L.def.dropout_ratio), 0);
+            break;
+        }
+        case L_SIGMOID:
+            sigmoid_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), bdata(t, ob), out_px * ob.C);
+            break;
+        default:
+            FCNOD_CHECK(false, "trainer: layer type '" + L.def.type_name + "' has no training forward");
+        }
+        FCNOD_CUDA(cudaGetLastError());
+    }
+}
+
+void backward(fcnod_trainer* t, cudaStream_t s) {
+    const int N = t->batch;
+    for (size_t b = 0; b < t->blobs.size(); ++b) t->blobs[b].diff_written = false;
+    root_of(t, t->cov_blob).diff_written = true;      // written by the head
+    root_of(t, t->box_blob).diff_written = true;
+    for (size_t li = t->layers.size(); li-- > 0;) {
+        TLayer& L = t->layers[li];
+        if (L.skip) continue;
+        const TBlob& ib = t->blobs[L.in];
+        const TBlob& ob = t->blobs[L.out];
+        const long in_px = (long)N * ib.H * ib.W, out_px = (long)N * ob.H * ob.W;
+        if (!root_of(t, L.out).diff_written) {
+            // nothing consumed this top (not the case in train_val.prototxt): its gradient is zero
+            FCNOD_CHECK(ob.ldc == ob.C, "trainer: unconsumed sliced blob");
+            FCNOD_CUDA(cudaMemsetAsync(bdiff(t, ob), 0, (size_t)out_px * ob.C * 4, s));
+            root_of(t, L.out).diff_written = true;
+        }
+        switch (L.def.type) {
+        case L_POWER:
+            break;
+        case L_SIGMOID:
+            sigmoid_bwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ob), bdiff(t, ob), bdiff(t, ib), out_px * ob.C, claim_diff(t, L.in));
+            break;
+        case L_DROPOUT: {
+            const long n = out_px * ob.C;
+            dropout_apply_kernel<<<grid1(n, 256), 256, 0, s>>>(bdiff(t, ob), L.mask, bdiff(t, ib), n, 1.f / (1.f - L.def.dropout_ratio), claim_diff(t, L.in));
+            break;
+        }
+        case L_POOL: {
+            PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
+            pool_bwd_kernel<<<grid1(in_px * ib.C, 256), 256, 0, s>>>(bdiff(t, ob), L.idx, bdiff(t, ib), g, claim_diff(t, L.in));
+            break;
+        }
+        case L_LRN:
+            lrn_bwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), ib.ldc, bdata(t, ob), bdiff(t, ob), ob.ldc, L.scale, bdiff(t, ib),
+                                                                      out_px, ob.C, L.def.local_size, L.def.alpha / (float)L.def.local_size, L.def.beta,
+                                                                      claim_diff(t, L.in));
+            break;
+        case L_CONV: {
+            const TConv& c = t->convs[L.conv];
+            float* dy = bdiff(t, ob);
+            if (L.relu) {
+                relu_mask_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ob), dy, out_px, ob.C, ob.ldc);
+                FCNOD_CUDA(cudaGetLastError());
+            }
+            {   // bias
+                const long chunk = std::max<long>(256, (out_px + 147) / 148);
+                dim3 grid((unsigned)((c.Cout + 31) / 32), (unsigned)((out_px + chunk - 1) / chunk));
+                bias_grad_kernel<<<grid, dim3(32, 8), 0, s>>>(dy, ob.ldc, c.Cout, out_px, chunk, t->grads + c.b_off);
+                FCNOD_CUDA(cudaGetLastError());
+            }
+            {   // weights
+                WgradParams p;
+                p.x = bdata(t, ib); p.dy = dy; p.g = t->grads + c.w_off;
+                p.N = N; p.H = ib.H; p.W = ib.W; p.Cin = c.Cin; p.ldi = ib.ldc;
+                p.Ho = ob.H; p.Wo = ob.W; p.Cout = c.Cout; p.ldo = ob.ldc; p.ldw = c.ldw;
+                p.k = c.k; p.stride = c.stride; p.pad = c.pad;
+                const int tiles = ((c.K + 63) / 64) * (c.ldw / 64);
+                long nz = std::max<long>(1, (148L * 6 + tiles - 1) / tiles);
+                nz = std::min<long>(nz, std::max<long>(1, out_px / 256));
+                p.chunk = ((out_px + nz - 1) / nz + 15) / 16 * 16;
+                nz = (out_px + p.chunk - 1) / p.chunk;
+                dim3 grid((unsigned)((c.K + 63) / 64), (unsigned)(c.ldw / 64), (unsigned)nz);
+                wgrad_simt_kernel<<<grid, 256, 0, s>>>(p);
+                FCNOD_CUDA(cudaGetLastError());
+            }
+            if (ib.needs_grad) {
+                dgrad_pack_kernel<<<grid1((long)c.k * c.k * c.Cout * c.ldt, 256), 256, 0, s>>>(t->params + c.w_off, c.ldw, c.d_wt, c.ldt, c.Cin, c.Cout, c.k);
+                FCNOD_CUDA(cudaGetLastError());
+                launch_conv(dy, ob.ldc, ob.H, ob.W, c.Cout, c.d_wt, c.ldt, 0, bdiff(t, ib), ib.ldc, ib.H, ib.W, c.Cin, N, c.k, 1, c.k - 1 - c.pad, 0,
+                            claim_diff(t, L.in), s);
+            }
+            break;
+        }
+        default:
+            FCNOD_CHECK(false, "trainer: layer type '" + L.def.type_name + "' has no backward");
+        }
+        FCNOD_CUDA(cudaGetLastError());
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int fcnod_solver_defaults(fcnod_solver_params* p) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(p, "null argument");
+    // /root/reference/train/bounding_box/solver.prototxt:3-15 (+ caffe.proto defaults for momentum2 / delta)
+    p->base_lr = 1e-4f; p->gamma = 0.1f; p->stepsize = 10000; p->momentum = 0.9f; p->momentum2 = 0.999f; p->delta = 1e-8f;
+    p->weight_decay = 1e-7f; p->bbox_loss_weight = 2.0f; p->dropout_ratio_override = -1.f; p->seed = 1;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_create(const char* prototxt_path, const char* caffemodel_path, int device, int batch, int height, int width,
+                         const fcnod_solver_params* solver, fcnod_trainer** out) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(prototxt_path && caffemodel_path && out, "null argument");
+    FCNOD_CHECK(batch > 0 && height > 0 && width > 0, "trainer: bad batch / input size");
+    int count = 0;
+    FCNOD_CHECK(cudaGetDeviceCount(&count) == cudaSuccess && count > 0, "no CUDA device: the trainer has no CPU fallback");
+    FCNOD_CHECK(device >= 0 && device < count, "trainer: device ordinal out of range");
+    FCNOD_CUDA(cudaSetDevice(device));
+    fcnod_trainer* t = new fcnod_trainer();
+    try {
+        t->device = device; t->batch = batch; t->in_h = height; t->in_w = width;
+        if (solver) t->solver = *solver; else fcnod_solver_defaults(&t->solver);
+        t->def = parse_prototxt_file(prototxt_path, true);
+        if (t->def.input_dims[1] > 0) t->in_c = t->def.input_dims[1];
+        WeightMap weights = read_caffemodel(caffemodel_path);
+        build_trainer(t, weights);
+        verify_train_side(t->def, t->num_classes, t->solver.bbox_loss_weight);
+        FCNOD_CUDA(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
+    } catch (...) {
+        for (size_t i = 0; i < t->allocs.size(); ++i) cudaFree(t->allocs[i]);
+        delete t;
+        throw;
+    }
+    *out = t;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_destroy(fcnod_trainer* t) {
+    FCNOD_API_BEGIN
+    if (t) {
+        cudaSetDevice(t->device);
+        cudaDeviceSynchronize();
+        for (size_t i = 0; i < t->allocs.size(); ++i) cudaFree(t->allocs[i]);
+        if (t->stream) cudaStreamDestroy(t->stream);
+        delete t;
+    }
+    FCNOD_API_END
+}
+
+int fcnod_trainer_info(const fcnod_trainer* t, int dims[7], size_t* n_params) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t, "null argument");
+    if (dims) { dims[0] = t->batch; dims[1] = t->in_c; dims[2] = t->in_h; dims[3] = t->in_w; dims[4] = t->num_classes; dims[5] = t->gh; dims[6] = t->gw; }
+    if (n_params) *n_params = t->n_params;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_buffers(fcnod_trainer* t, float** params, float** grads, float** m, float** v) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t, "null argument");
+    if (params) *params = t->params;
+    if (grads) *grads = t->grads;
+    if (m) *m = t->m;
+    if (v) *v = t->v;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label,
+                                          const float* size_block, const float* obj_block, const float* cvg_block, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && data && cvg_label && bbox_label && size_block && obj_block && cvg_block, "null argument");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    const int N = t->batch, C = t->num_classes;
+    FCNOD_CUDA(cudaMemsetAsync(t->grads, 0, t->n_params * 4, s));
+    forward(t, data, s);
+    const TBlob& cb = t->blobs[t->cov_blob];
+    const TBlob& bb = t->blobs[t->box_blob];
+    const long n1 = (long)N * C * t->gh * t->gw;
+    nhwc_to_nchw_kernel<<<grid1(n1, 256), 256, 0, s>>>(bdata(t, cb), cb.ldc, t->cov_nchw, N, C, t->gh, t->gw);
+    nhwc_to_nchw_kernel<<<grid1(4 * n1, 256), 256, 0, s>>>(bdata(t, bb), bb.ldc, t->box_nchw, N, 4 * C, t->gh, t->gw);
+    FCNOD_CUDA(cudaGetLastError());
+    int rc = fcnod_train_head_forward_device(t->cov_nchw, t->box_nchw, cvg_label, bbox_label, size_block, obj_block, cvg_block, N, C, t->gh,
+                                             t->gw, t->solver.bbox_loss_weight, t->losses_dev, t->dcov_nchw, t->dbox_nchw, t->head_scratch, s);
+    FCNOD_CHECK(rc == 0, fcnod_last_error());
+    nchw_to_nhwc_kernel<<<grid1(n1, 256), 256, 0, s>>>(t->dcov_nchw, bdiff(t, cb), cb.ldc, N, C, t->gh, t->gw);
+    nchw_to_nhwc_kernel<<<grid1(4 * n1, 256), 256, 0, s>>>(t->dbox_nchw, bdiff(t, bb), bb.ldc, N, 4 * C, t->gh, t->gw);
+    FCNOD_CUDA(cudaGetLastError());
+    backward(t, s);
+    FCNOD_API_END
+}
+
+int fcnod_trainer_apply_update(fcnod_trainer* t, float grad_scale, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t, "null argument");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    const fcnod_solver_params& sp = t->solver;
+    AdamArgs a;
+    const int tt = t->iter + 1;
+    a.rate = (float)((double)sp.base_lr * std::pow((double)sp.gamma, (double)(sp.stepsize > 0 ? t->iter / sp.stepsize : 0)));
+    a.correction = (float)(std::sqrt(1.0 - std::pow((double)sp.momentum2, (double)tt)) / (1.0 - std::pow((double)sp.momentum, (double)tt)));
+    a.b1 = sp.momentum; a.b2 = sp.momentum2; a.eps = sp.delta; a.weight_decay = sp.weight_decay; a.grad_scale = grad_scale;
+    adam_kernel<<<grid1((long)t->n_params, 256), 256, 0, s>>>(t->params, t->grads, t->m, t->v, t->meta, (long)t->n_params, a);
+    FCNOD_CUDA(cudaGetLastError());
+    ++t->iter;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_losses(fcnod_trainer* t, float losses[2], void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && losses, "null argument");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    FCNOD_CUDA(cudaMemcpyAsync(losses, t->losses_dev, 8, cudaMemcpyDeviceToHost, s));
+    FCNOD_CUDA(cudaStreamSynchronize(s));
+    FCNOD_API_END
+}
+
+int fcnod_trainer_iteration(const fcnod_trainer* t) { return t ? t->iter : -1; }
+
+// Host-buffer form of one iteration on one GPU: upload, forward + backward, ApplyUpdate, losses back.
+int fcnod_trainer_step(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label, const float* size_block,
+                       const float* obj_block, const float* cvg_block, float losses[2]) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && data && cvg_label && bbox_label && size_block && obj_block && cvg_block, "null argument");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    const size_t n1 = (size_t)t->batch * t->num_classes * t->gh * t->gw, nd = (size_t)t->batch * t->in_c * t->in_h * t->in_w;
+    if (!t->stage) t->stage = dalloc<float>(t, nd + 17 * n1);
+    const float* src[6] = {data, cvg_label, bbox_label, size_block, obj_block, cvg_block};
+    const size_t cnt[6] = {nd, n1, 4 * n1, 4 * n1, 4 * n1, 4 * n1};
+    float* dst[6];
+    float* q = t->stage;
+    for (int i = 0; i < 6; ++i) { dst[i] = q; q += cnt[i]; }
+    for (int i = 0; i < 6; ++i) FCNOD_CUDA(cudaMemcpyAsync(dst[i], src[i], cnt[i] * 4, cudaMemcpyHostToDevice, t->stream));
+    int rc = fcnod_trainer_forward_backward_device(t, dst[0], dst[1], dst[2], dst[3], dst[4], dst[5], t->stream);
+    FCNOD_CHECK(rc == 0, fcnod_last_error());
+    rc = fcnod_trainer_apply_update(t, 1.f, t->stream);
+    FCNOD_CHECK(rc == 0, fcnod_last_error());
+    if (losses) {
+        rc = fcnod_trainer_losses(t, losses, t->stream);
+        FCNOD_CHECK(rc == 0, fcnod_last_error());
+    } else {
+        FCNOD_CUDA(cudaStreamSynchronize(t->stream));
+    }
+    FCNOD_API_END
+}
+
+// which: 0 = value, 1 = gradient (after the last backward; after ApplyUpdate: the regularised, scaled gradient), 2 = ADAM m, 3 = v.
+// index: 0 = weights in Caffe's [Cout][Cin][k][k] order, 1 = bias.  out == NULL: only *count is returned.
+int fcnod_trainer_param_read(fcnod_trainer* t, const char* layer, int index, int which, float* out, size_t* count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && layer && (index == 0 || index == 1) && which >= 0 && which <= 3, "trainer: bad argument");
+    const TConv* c = 0;
+    for (size_t i = 0; i < t->convs.size(); ++i)
+        if (t->convs[i].name == layer) c = &t->convs[i];
+    FCNOD_CHECK(c, std::string("trainer: no convolution named '") + layer + "'");
+    const size_t n = index == 0 ? (size_t)c->Cout * c->K : (size_t)c->Cout;
+    if (count) {
+        const size_t cap = *count;
+        *count = n;
+        if (!out) return 0;
+        FCNOD_CHECK(cap >= n, "trainer: output buffer too small");
+    }
+    FCNOD_CHECK(out, "null argument");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    FCNOD_CUDA(cudaDeviceSynchronize());      // whichever stream the caller ran the step on
+    const float* base = which == 0 ? t->params : which == 1 ? t->grads : which == 2 ? t->m : t->v;
+    if (index == 1) {
+        FCNOD_CUDA(cudaMemcpy(out, base + c->b_off, n * 4, cudaMemcpyDeviceToHost));
+    } else {
+        std::vector<float> packed((size_t)c->K * c->ldw);
+        FCNOD_CUDA(cudaMemcpy(packed.data(), base + c->w_off, packed.size() * 4, cudaMemcpyDeviceToHost));
+        const int kk = c->k * c->k;
+        for (int co = 0; co < c->Cout; ++co)
+            for (int cc = 0; cc < c->Cin; ++cc)
+                for (int rs = 0; rs < kk; ++rs)
+                    out[((size_t)co * c->Cin + cc) * kk + rs] = packed[((size_t)rs * c->Cin + cc) * c->ldw + co];
+    }
+    FCNOD_API_END
+}
+
+const char* fcnod_trainer_param_layer(const fcnod_trainer* t, int i) {
+    if (!t || i < 0 || i >= (int)t->convs.size()) return 0;
+    return t->convs[i].name.c_str();
+}
+
+// which: 0 = data, 1 = diff; dense NCHW float32 out; dims = C, H, W of the blob (out may be NULL to query them)
+int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which, int dims[3], float* out, size_t count) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && blob && (which == 0 || which == 1), "trainer: bad argument");
+    const TBlob& b = t->blobs[blob_of(t, blob)];
+    if (dims) { dims[0] = b.C; dims[1] = b.H; dims[2] = b.W; }
+    if (!out) return 0;
+    const size_t n = (size_t)t->batch * b.C * b.H * b.W;
+    FCNOD_CHECK(count >= n, "trainer: output buffer too small");
+    FCNOD_CHECK(b.buf != t->blobs[0].buf, "trainer: the network input is not kept in NHWC form");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    float* tmp = 0;
+    FCNOD_CUDA(cudaMalloc((void**)&tmp, n * 4));
+    nhwc_to_nchw_kernel<<<grid1((long)n, 256), 256, 0, t->stream>>>(which == 0 ? bdata(t, b) : bdiff(t, b), b.ldc, tmp, t->batch, b.C, b.H, b.W);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, n * 4, cudaMemcpyDeviceToHost, t->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    cudaFree(tmp);
+    FCNOD_CUDA(e);
+    FCNOD_API_END
+}
+
+// The argmax the last forward kept for a Pooling layer: for every output element the position of the selected input inside
+// its k x k window, dh * k + dw relative to the UNCLIPPED window origin (ph * stride - pad, pw * stride - pad); [N][C][Ho][Wo].
+int fcnod_trainer_pool_argmax(fcnod_trainer* t, const char* layer, uint8_t* out, size_t count, int dims[3]) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && layer, "null argument");
+    const TLayer* pl = 0;
+    for (size_t i = 0; i < t->layers.size(); ++i)
+        if (t->layers[i].def.type == L_POOL && t->layers[i].def.name == layer) pl = &t->layers[i];
+    FCNOD_CHECK(pl, std::string("trainer: no Pooling layer named '") + layer + "'");
+    const TBlob& b = t->blobs[pl->out];
+    if (dims) { dims[0] = b.C; dims[1] = b.H; dims[2] = b.W; }
+    if (!out) return 0;
+    const size_t n = (size_t)t->batch * b.C * b.H * b.W;
+    FCNOD_CHECK(count >= n, "trainer: output buffer too small");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    uint8_t* tmp = 0;
+    FCNOD_CUDA(cudaMalloc((void**)&tmp, n));
+    u8_nhwc_to_nchw_kernel<<<grid1((long)n, 256), 256, 0, t->stream>>>(pl->idx, tmp, t->batch, b.C, b.H, b.W);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, n, cudaMemcpyDeviceToHost, t->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    cudaFree(tmp);
+    FCNOD_CUDA(e);
+    FCNOD_API_END
+}
+
+// The keep mask the last forward drew for the Dropout layer, as Caffe's rand_vec_ is shaped: [N][C][H][W] uint8.
+int fcnod_trainer_dropout_mask(fcnod_trainer* t, uint8_t* out, size_t count, int dims[3]) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t, "null argument");
+    const TLayer* dl = 0;
+    for (size_t i = 0; i < t->layers.size(); ++i)
+        if (t->layers[i].def.type == L_DROPOUT) dl = &t->layers[i];
+    FCNOD_CHECK(dl, "trainer: the network has no Dropout layer");
+    const TBlob& b = t->blobs[dl->out];
+    if (dims) { dims[0] = b.C; dims[1] = b.H; dims[2] = b.W; }
+    if (!out) return 0;
+    const size_t n = (size_t)t->batch * b.C * b.H * b.W;
+    FCNOD_CHECK(count >= n, "trainer: output buffer too small");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    u8_nhwc_to_nchw_kernel<<<grid1((long)n, 256), 256, 0, t->stream>>>(dl->mask, t->mask_nchw, t->batch, b.C, b.H, b.W);
+    FCNOD_CUDA(cudaGetLastError());
+    FCNOD_CUDA(cudaMemcpyAsync(out, t->mask_nchw, n, cudaMemcpyDeviceToHost, t->stream));
+    FCNOD_CUDA(cudaStreamSynchronize(t->stream));
+    FCNOD_API_END
+}
+
+}  // extern "C"

@@ -25,11 +25,15 @@ _INCEPTION = [
 ]
 
 
+# the one convolution whose bias learns at lr_mult 1.0 upstream (models/train_val.prototxt, models/deploy.prototxt): kept
+_BIAS_LR_MULT = {'inception_5b/3x3_reduce': 1.0}
+
+
 def _conv(name, bottom, top, num_output, kernel, pad=0, stride=1, bias=0.2):
     s = ['layer {', '  name: "%s"' % name, '  type: "Convolution"',
          '  bottom: "%s"' % bottom, '  top: "%s"' % top,
          '  param { lr_mult: 1.0 decay_mult: 1.0 }',
-         '  param { lr_mult: 2.0 decay_mult: 0.0 }',
+         '  param { lr_mult: %s decay_mult: 0.0 }' % repr(_BIAS_LR_MULT.get(name, 2.0)),
          '  convolution_param {', '    num_output: %d' % num_output]
     if pad:
         s.append('    pad: %d' % pad)
@@ -114,6 +118,59 @@ def deploy_prototxt(batch=1, height=448, width=448, num_cvg=4, num_bbox=16):
     o += _simple('coverage/sig', 'Sigmoid', ['cvg/classifier'], 'coverage')
     o += _conv('bbox/regressor', 'pool5/drop_s1', 'bboxes', num_bbox, 1, bias=0.0)
     return '\n'.join(o) + '\n'
+
+
+def _body(num_cvg, num_bbox):
+    """The layers between `deploy_transform` and the two heads (shared by the deploy and the train_val forms)."""
+    text = deploy_prototxt(num_cvg=num_cvg, num_bbox=num_bbox)
+    return text[text.index('layer {'):]
+
+
+def train_val_prototxt(num_classes=1, bbox_loss_weight=2.0, lmdb_features='lmdb/features', lmdb_labels='lmdb/labels'):
+    """Text of the training network in the form of /root/reference/models/train_val.prototxt:1-2281: two LMDB Data layers
+    (:1-26), the input Power (:27-35), the label Slice (:36-52), the two label normalisers (:53-72), the network body with
+    num_classes / 4 num_classes head channels, the three Eltwise masks (:2237-2266) and the two losses (:2267-2281)."""
+    c = num_classes
+    o = []
+    for name, top, src in (('train_data', 'data', lmdb_features), ('train_label', 'label', lmdb_labels)):
+        o += ['layer {', '  name: "%s"' % name, '  type: "Data"', '  top: "%s"' % top, '  include { phase: TRAIN }',
+              '  data_param {', '    source: "%s"' % src, '    batch_size: 1', '    backend: LMDB', '  }', '}']
+    body = _body(c, 4 * c).rstrip('\n').split('\n')
+    # the Power layer is the first layer record of the body: the Slice and the normalisers follow it as in the upstream file
+    end_power = body.index('}') + 1
+    o += body[:end_power]
+    o += ['layer {', '  name: "slice-label"', '  type: "Slice"', '  bottom: "label"', '  top: "coverage-label"',
+          '  top: "bbox-label"', '  top: "size-block"', '  top: "obj-block"', '  top: "coverage-block"', '  slice_param {',
+          '    slice_dim: 1', '    slice_point: %d' % c, '    slice_point: %d' % (5 * c), '    slice_point: %d' % (9 * c),
+          '    slice_point: %d' % (13 * c), '  }', '}']
+    prod = ['eltwise_param {', '  operation: PROD', '}']
+    o += _simple('bb-label-norm', 'Eltwise', ['bbox-label', 'size-block'], 'bbox-label-norm', prod)
+    o += _simple('bb-obj-norm', 'Eltwise', ['bbox-label-norm', 'obj-block'], 'bbox-obj-label-norm', prod)
+    o += body[end_power:]
+    o += _simple('bbox_mask', 'Eltwise', ['bboxes', 'coverage-block'], 'bboxes-masked', prod)
+    o += _simple('bbox-norm', 'Eltwise', ['bboxes-masked', 'size-block'], 'bboxes-masked-norm', prod)
+    o += _simple('bbox-obj-norm', 'Eltwise', ['bboxes-masked-norm', 'obj-block'], 'bboxes-obj-masked-norm', prod)
+    o += _simple('bbox_loss', 'L1Loss', ['bboxes-obj-masked-norm', 'bbox-obj-label-norm'], 'loss_bbox',
+                 ['loss_weight: %s' % repr(float(bbox_loss_weight))])
+    o += _simple('coverage_loss', 'EuclideanLoss', ['coverage', 'coverage-label'], 'loss_coverage')
+    return '\n'.join(o) + '\n'
+
+
+def write_train_val_prototxt(path, **kw):
+    with open(path, 'w') as f:
+        f.write(train_val_prototxt(**kw))
+    return path
+
+
+def solver_prototxt():
+    """Text with the values of /root/reference/train/bounding_box/solver.prototxt:3-15."""
+    return ('net: "bounding_box/train_val.prototxt"\nsnapshot_prefix: "snapshots/snapshot"\nbase_lr: 1e-04\nmax_iter: 1\n'
+            'iter_size: 1\nlr_policy: "step"\ngamma: 0.1\nmomentum: 0.9\nweight_decay: 1e-07\nstepsize: 10000\nsnapshot: 5000\n'
+            'solver_type: ADAM\nsolver_mode: GPU\ndisplay: 20\ndebug_info: false\n')
+
+
+def conv_shape_dict(num_cvg=4, num_bbox=16):
+    return {name: (cout, cin, k, k) for name, cout, cin, k, _ in conv_shapes(num_cvg, num_bbox)}
 
 
 def write_deploy_prototxt(path, **kw):

@@ -305,6 +305,49 @@ int fcnod_train_head_forward(const float* coverage, const float* bboxes, const f
                              const float* size_block, const float* obj_block, const float* cvg_block, int N, int num_classes, int gh,
                              int gw, float bbox_loss_weight, float* losses, float* d_coverage, float* d_bboxes);   /* HOST buffers */
 
+/* ---- one training iteration of models/train_val.prototxt (BASELINE config 5) --------------
+ * Replaces what `caffe train --solver=bounding_box/solver.prototxt` (train/train.sh:19) runs per iteration on one GPU:
+ * Net::ForwardBackward over models/train_val.prototxt (body :27-35,76-2232 at TRAIN phase, Dropout :2164-2172 active,
+ * head :36-72,2237-2281) and SGDSolver::ApplyUpdate with solver_type ADAM (train/bounding_box/solver.prototxt:3-15).
+ * The data / label inputs are the six tops of the DataArgumentationLayer (fcnod_aug_forward_device): `data`
+ * [N][3][H][W] float32 and the five label grids, NCHW float32, device pointers for the _device form.
+ * prototxt: the train_val form (Data / Slice / Eltwise / loss layers are checked against the fused head and otherwise
+ * skipped) or the deploy form with 1 / 4 head channels; caffemodel: the snapshot training starts from.
+ * fp32 storage and arithmetic (the parity engine: 1e-4 against autograd over the same graph).  Parameters, gradients
+ * and ADAM's moments are four flat float32 device buffers of one layout (fcnod_trainer_buffers, n_params floats each):
+ * a data-parallel caller all-reduces `grads` (SUM) between forward_backward and apply_update and passes
+ * grad_scale = 1 / world_size, which is what Caffe's NCCL solver does. */
+typedef struct fcnod_trainer fcnod_trainer;
+typedef struct fcnod_solver_params {
+    float base_lr, gamma;            /* lr_policy "step": rate = base_lr * gamma^floor(iter / stepsize) */
+    int32_t stepsize;
+    float momentum, momentum2, delta, weight_decay;   /* ADAM beta1, beta2, epsilon; L2 decay */
+    float bbox_loss_weight;          /* loss_weight of bbox_loss (train_val.prototxt:2273) */
+    float dropout_ratio_override;    /* < 0: the prototxt's dropout_ratio; 0 switches dropout off */
+    uint64_t seed;                   /* dropout masks are a function of (seed, iteration, element) */
+} fcnod_solver_params;
+int fcnod_solver_defaults(fcnod_solver_params* p);   /* the values of train/bounding_box/solver.prototxt */
+int fcnod_trainer_create(const char* prototxt_path, const char* caffemodel_path, int device, int batch, int height, int width,
+                         const fcnod_solver_params* solver /* NULL = defaults */, fcnod_trainer** out);
+int fcnod_trainer_destroy(fcnod_trainer* t);
+int fcnod_trainer_info(const fcnod_trainer* t, int dims[7] /* N, C, H, W, num_classes, grid h, grid w */, size_t* n_params);
+int fcnod_trainer_buffers(fcnod_trainer* t, float** params, float** grads, float** m, float** v);   /* device pointers */
+int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label,
+                                          const float* size_block, const float* obj_block, const float* cvg_block, void* stream);
+int fcnod_trainer_apply_update(fcnod_trainer* t, float grad_scale, void* stream);
+int fcnod_trainer_losses(fcnod_trainer* t, float losses[2] /* loss_bbox (unweighted), loss_coverage */, void* stream);
+int fcnod_trainer_iteration(const fcnod_trainer* t);
+int fcnod_trainer_step(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label, const float* size_block,
+                       const float* obj_block, const float* cvg_block, float losses[2]);   /* HOST buffers, one GPU */
+/* Introspection (snapshots, tests).  which: 0 value, 1 gradient, 2 ADAM m, 3 ADAM v; index: 0 weights in Caffe's
+ * [Cout][Cin][k][k] order, 1 bias.  out == NULL: *count receives the element count. */
+int fcnod_trainer_param_read(fcnod_trainer* t, const char* layer, int index, int which, float* out, size_t* count);
+const char* fcnod_trainer_param_layer(const fcnod_trainer* t, int i);   /* i-th convolution's name, NULL past the end */
+int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which /* 0 data, 1 diff */, int dims[3], float* out, size_t count);
+int fcnod_trainer_dropout_mask(fcnod_trainer* t, uint8_t* out /* [N][C][H][W] */, size_t count, int dims[3]);
+/* argmax of a Pooling layer's last forward: dh * k + dw inside the unclipped window, [N][C][Ho][Wo] uint8 */
+int fcnod_trainer_pool_argmax(fcnod_trainer* t, const char* layer, uint8_t* out, size_t count, int dims[3]);
+
 #ifdef __cplusplus
 }
 #endif

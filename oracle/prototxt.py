@@ -110,6 +110,9 @@ def layers(net):
                        bias_term=_one(p, 'bias_term', True),
                        bias_value=_one(_one(p, 'bias_filler', {}), 'value', 0.0),
                        weight_filler=_one(_one(p, 'weight_filler', {}), 'type', 'constant'))
+            pr = L.get('param', [])
+            rec.update(lr_mult=[_one(x, 'lr_mult', 1.0) for x in pr] + [1.0] * (2 - len(pr)),
+                       decay_mult=[_one(x, 'decay_mult', 1.0) for x in pr] + [1.0] * (2 - len(pr)))
         elif t == 'Pooling':
             p = _one(L, 'pooling_param', {})
             rec.update(pool=_one(p, 'pool', 'MAX'), kernel=_one(p, 'kernel_size'),

@@ -1,0 +1,215 @@
+"""GPU: one training iteration of models/train_val.prototxt (csrc/train_net.cu through the C ABI) against the CPU oracle
+(oracle/train_net_ref.py: torch autograd over the restated forward graph + Caffe's ADAM ApplyUpdate).
+
+Sizes the oracle finishes in seconds: the full network body on 2 frames of 128x160 (label grids 8x10).  Gates (fp32 engine):
+activations and their gradients 1e-4, weight / bias gradients 2e-4, losses 1e-5 (all max|a-b| / max|b| per blob), updated
+weights 1e-6 absolute after the first ApplyUpdate.  The dropout mask is drawn on the device and read back, so both sides
+use the same one.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import prototxt, train_net_ref
+from tests.util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+N, H, W = 2, 128, 160
+GH, GW = H // 16, W // 16
+
+
+@pytest.fixture(scope='module')
+def train_files(tmp_path_factory):
+    from fcn_object_detector_b200 import netspec
+    from fcn_object_detector_b200.caffemodel import write_synthetic_caffemodel
+    d = tmp_path_factory.mktemp('train')
+    proto = netspec.write_train_val_prototxt(str(d / 'train_val.prototxt'))
+    cm = write_synthetic_caffemodel(str(d / 'init.caffemodel'), seed=3, num_cvg=1, num_bbox=4)
+    solver = str(d / 'solver.prototxt')
+    with open(solver, 'w') as f:
+        f.write(netspec.solver_prototxt())
+    return proto, cm, solver
+
+
+def _inputs(seed=0):
+    """Synthetic tops of the augmentation layer: an image and label grids with the layer's structure (a rectangle of
+    foreground cells; bbox-label in pixels; size-block = 1 / rect size; obj-block = 1 / cells; coverage-block = mask)."""
+    rs = np.random.RandomState(seed)
+    data = rs.uniform(0, 255, (N, 3, H, W)).astype(np.float32)
+    cvg = np.zeros((N, 1, GH, GW), np.float32)
+    bbox = np.zeros((N, 4, GH, GW), np.float32)
+    size = np.zeros((N, 4, GH, GW), np.float32)
+    obj = np.zeros((N, 4, GH, GW), np.float32)
+    cblk = np.zeros((N, 4, GH, GW), np.float32)
+    for n in range(N):
+        y0, x0 = rs.randint(0, GH - 3), rs.randint(0, GW - 4)
+        hh, ww = rs.randint(2, 4), rs.randint(2, 5)
+        cvg[n, 0, y0:y0 + hh, x0:x0 + ww] = 1
+        cblk[n, :, y0:y0 + hh, x0:x0 + ww] = 1
+        bbox[n, :, y0:y0 + hh, x0:x0 + ww] = rs.uniform(-40, 40, (4, hh, ww))
+        size[n, 0::2, y0:y0 + hh, x0:x0 + ww] = 1.0 / (16 * ww)
+        size[n, 1::2, y0:y0 + hh, x0:x0 + ww] = 1.0 / (16 * hh)
+        obj[n, :, y0:y0 + hh, x0:x0 + ww] = 1.0 / (hh * ww)
+    return data, (cvg, bbox, size, obj, cblk)
+
+
+def _oracle_weights(cm):
+    from oracle.caffemodel_io import read_caffemodel
+    return read_caffemodel(cm)
+
+
+@pytest.fixture(scope='module')
+def solver(train_files):
+    from fcn_object_detector_b200.trainer import Solver
+    proto, cm, sp = train_files
+    s = Solver(proto, cm, batch=N, height=H, width=W, solver_prototxt=sp, seed=7)
+    yield s
+    s.close()
+
+
+def test_solver_reads_the_reference_solver_values(solver):
+    p = solver.params
+    f = np.float32
+    assert (f(p.base_lr), f(p.gamma), p.stepsize) == (f(1e-4), f(0.1), 10000)
+    assert (f(p.momentum), f(p.momentum2), f(p.delta), f(p.weight_decay)) == (f(0.9), f(0.999), f(1e-8), f(1e-7))
+    assert (solver.num_classes, solver.grid_h, solver.grid_w) == (1, GH, GW)
+    assert len(solver.layers) == 59 and solver.layers[0] == 'conv1/7x7_s2' and solver.layers[-1] == 'bbox/regressor'
+
+
+def test_forward_backward_and_update_match_the_oracle(solver, train_files):
+    import torch
+    proto, cm, _ = train_files
+    layers = prototxt.layers(prototxt.parse(open(proto).read()))
+    weights = {k: [np.asarray(a, np.float32) for a in v] for k, v in _oracle_weights(cm).items()}
+    data, grids = _inputs(0)
+    dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+    stream = torch.cuda.current_stream().cuda_stream
+    solver.forward_backward_device([t.data_ptr() for t in dev], stream=stream)
+    torch.cuda.synchronize()
+    got_loss = solver.losses(stream)
+    mask = solver.dropout_mask()
+    assert mask.shape == (N, 1024, GH, GW) and 0.5 < mask.mean() < 0.7        # keep probability 0.6
+
+    want = ['conv1/7x7_s2', 'pool1/norm1', 'conv2/norm2', 'pool2/3x3_s2', 'inception_3a/output', 'inception_3b/pool', 'pool3/3x3_s2',
+            'inception_4e/output', 'inception_5b/output', 'pool5/drop_s1', 'coverage', 'bboxes']
+    # Max-pool routing.  (1) The device's selection obeys Caffe's rule on the device's own inputs, bit for bit: first maximum
+    # of the clipped window in row-major order.  (2) The oracle then backpropagates through the SAME selection: where two
+    # inputs of a window differ by less than the two forwards do (1e-6), the other forward may select the other element, and
+    # gradients routed to another pixel are not an error of either side.
+    pools = {L['name']: L for L in layers if L['type'] == 'Pooling'}
+    assert len(pools) == 12
+    argmax = {name: solver.pool_argmax(name) for name in pools}
+    for name in ('pool1/3x3_s2', 'pool2/3x3_s2', 'inception_3b/pool', 'pool3/3x3_s2', 'inception_5a/pool'):
+        L = pools[name]
+        y, idx = train_net_ref.caffe_pool_argmax(solver.blob(L['bottom'][0]), L['kernel'], L['stride'], L['pad'])
+        assert np.array_equal(y.view(np.uint32), solver.blob(name).view(np.uint32)), name
+        assert np.array_equal(idx, argmax[name]), name
+    ref = train_net_ref.forward_backward(layers, weights, data, grids, dropout_mask=mask, want=want, pool_argmax=argmax)
+    free = train_net_ref.forward_backward(layers, weights, data, grids, dropout_mask=mask, want=('coverage',))
+    assert abs(free['loss_coverage'] - ref['loss_coverage']) < 1e-6 * abs(ref['loss_coverage'])      # same forward values
+
+    # ---- forward
+    for k in want:
+        e = rel_err(solver.blob(k), ref['blobs'][k])
+        assert e < 1e-4, ('data', k, e)
+    assert abs(got_loss['loss_bbox'] - ref['loss_bbox']) <= 1e-5 * max(1.0, abs(ref['loss_bbox']))
+    assert abs(got_loss['loss_coverage'] - ref['loss_coverage']) <= 1e-5 * max(1.0, abs(ref['loss_coverage']))
+    # ---- gradients of the activations (ReLU is in place: Caffe's diff of a convolution top is the gradient AFTER the ReLU
+    # mask, autograd's retained gradient of the ReLU output is the one before it; compare blobs that are not ReLU tops)
+    for k in ('pool1/norm1', 'conv2/norm2', 'pool2/3x3_s2', 'inception_3b/pool', 'pool3/3x3_s2', 'pool5/drop_s1', 'coverage', 'bboxes'):
+        e = rel_err(solver.blob(k, 'diff'), ref['blob_grads'][k])
+        assert e < 1e-4, ('diff', k, e)
+    # ---- gradients of all 59 x 2 parameter blobs
+    worst = 0.0
+    for name in solver.layers:
+        gw, gb = ref['grads'][name]
+        ew = rel_err(solver.param(name, 0, 'grad').reshape(gw.shape), gw)
+        eb = rel_err(solver.param(name, 1, 'grad'), gb)
+        worst = max(worst, ew, eb)
+        assert ew < 2e-4 and eb < 2e-4, (name, ew, eb)
+    # ---- ApplyUpdate, twice (the second one exercises the moments and the bias correction at t = 2)
+    state = {}
+    grads = {k: [solver.param(k, 0, 'grad').reshape(weights[k][0].shape), solver.param(k, 1, 'grad')] for k in solver.layers}
+    solver.apply_update(1.0, stream)
+    mults = train_net_ref.multipliers(layers)
+    assert mults['inception_5b/3x3_reduce'][0] == [1.0, 1.0] and mults['conv1/7x7_s2'][0] == [1.0, 2.0]
+    new_w = train_net_ref.adam_update(weights, grads, state, 0, mults=mults)
+    for name in solver.layers:
+        assert np.abs(solver.param(name, 0).reshape(new_w[name][0].shape) - new_w[name][0]).max() < 1e-6, name
+        assert np.abs(solver.param(name, 1) - new_w[name][1]).max() < 1e-6, name
+    # first ADAM step: every weight with a gradient well above delta moves by rate * lr_mult (known answer)
+    # (m = 0.1 g, v = 0.001 g^2, correction = sqrt(0.001) / 0.1: step = 1e-4 * g / (|g| + 1e-8 / sqrt(0.001)) -> 1e-4 * sign(g))
+    g = grads['conv2/3x3'][0].astype(np.float64)
+    moved = weights['conv2/3x3'][0].astype(np.float64) - solver.param('conv2/3x3', 0).reshape(g.shape)
+    big = np.abs(g) > 1e-5            # well above weight_decay * w (4e-9)
+    assert big.sum() > 100
+    assert np.allclose(moved[big], 1e-4 * g[big] / (np.abs(g[big]) + 1e-8 / np.sqrt(0.001)), rtol=2e-3, atol=1e-8)
+    assert solver.iter == 1
+    solver.forward_backward_device([t.data_ptr() for t in dev], stream=stream)
+    grads2 = {k: [solver.param(k, 0, 'grad').reshape(weights[k][0].shape), solver.param(k, 1, 'grad')] for k in solver.layers}
+    solver.apply_update(1.0, stream)
+    new_w2 = train_net_ref.adam_update(new_w, grads2, state, 1, mults=mults)
+    for name in ('conv1/7x7_s2', 'inception_4c/5x5', 'inception_5b/3x3_reduce', 'cvg/classifier', 'bbox/regressor'):
+        assert np.abs(solver.param(name, 0).reshape(new_w2[name][0].shape) - new_w2[name][0]).max() < 2e-6, name
+        assert np.abs(solver.param(name, 1) - new_w2[name][1]).max() < 2e-6, name
+    os.makedirs('gpurun_out', exist_ok=True)
+    with open('gpurun_out/train_parity.txt', 'w') as f:
+        f.write('worst relative error over the 118 parameter gradients (fp32 engine vs torch autograd, %dx%dx%d): %.3g\n' % (N, H, W, worst))
+
+
+def test_dropout_masks_are_reproducible_and_change_per_iteration(train_files):
+    import torch
+    from fcn_object_detector_b200.trainer import Solver
+    proto, cm, sp = train_files
+    data, grids = _inputs(1)
+    dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+    masks = []
+    for seed in (7, 7, 8):
+        s = Solver(proto, cm, batch=N, height=H, width=W, solver_prototxt=sp, seed=seed)
+        try:
+            s.forward_backward_device([t.data_ptr() for t in dev])
+            m0 = s.dropout_mask()
+            s.apply_update()
+            s.forward_backward_device([t.data_ptr() for t in dev])
+            masks.append((m0, s.dropout_mask()))
+        finally:
+            s.close()
+    assert np.array_equal(masks[0][0], masks[1][0]) and np.array_equal(masks[0][1], masks[1][1])
+    assert not np.array_equal(masks[0][0], masks[0][1]) and not np.array_equal(masks[0][0], masks[2][0])
+
+
+def test_training_reduces_the_loss_and_the_snapshot_loads_in_the_detector(train_files, tmp_path):
+    """Host-buffer iterations on a fixed minibatch: the loss goes down; the snapshot written afterwards is a .caffemodel the
+    inference engine loads, and its fp32 forward reproduces the trainer's own TEST-phase coverage (dropout off)."""
+    from fcn_object_detector_b200 import netspec
+    from fcn_object_detector_b200.trainer import Solver
+    import fcn_object_detector_b200.caffe_shim as caffe
+    proto, cm, sp = train_files
+    data, grids = _inputs(2)
+    s = Solver(proto, cm, batch=N, height=H, width=W, solver_prototxt=sp, seed=3, dropout_ratio_override=0.0, base_lr=1e-3)
+    try:
+        losses = [s.step(data, grids)['loss'] for _ in range(12)]
+        assert losses[-1] < 0.7 * losses[0], losses
+        assert all(np.isfinite(losses))
+        snap = s.snapshot(str(tmp_path / 'snapshot_iter_12.caffemodel'), netspec.conv_shape_dict(num_cvg=1, num_bbox=4))
+        # one more forward (no update needed: compare activations of the current weights)
+        import torch
+        dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+        s.forward_backward_device([t.data_ptr() for t in dev])
+        cov_train, box_train = s.blob('coverage'), s.blob('bboxes')
+    finally:
+        s.close()
+    deploy = netspec.write_deploy_prototxt(str(tmp_path / 'deploy.prototxt'), batch=N, height=H, width=W, num_cvg=1, num_bbox=4)
+    net = caffe.Net(deploy, snap, caffe.TEST, device=0, precision='fp32')
+    try:
+        net.blobs['data'].reshape(N, 3, H, W)
+        net.blobs['data'].data[...] = data
+        net.forward()
+        cov_deploy, box_deploy = net.blobs['coverage'].data.copy(), net.blobs['bboxes'].data.copy()
+    finally:
+        net.close()
+    # two fp32 engines (different tilings and sigmoid formulations): the linear head at 1e-5, the sigmoid output at 1e-4
+    assert rel_err(box_deploy, box_train) < 1e-5
+    assert rel_err(cov_deploy, cov_train) < 1e-4
