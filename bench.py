@@ -498,7 +498,7 @@ def run_ours(args):
             json.dump([{'step': i, 'ms': t, 'desc': d} for i, (t, d) in enumerate(zip(per, plan))] +
                       [{'step': len(plan), 'ms': post_ms, 'desc': 'postnet decode_group_kernel + assemble_kernel'}], f, indent=1)
         # ---- CPU baseline: the oracle on the host cores, bounded sample; extra sections (N = 1 only)
-        cpu = layer = latency = bwk = None
+        cpu = layer = latency = bwk = train = None
         if world == 1 and not args.no_cpu_baseline:
             frames = 4
             ncpu = len(os.sched_getaffinity(0))
@@ -512,6 +512,12 @@ def run_ours(args):
             bwk = bandwidth_kernels(torch, L, _lib, stream, pk)
             layer = layer_section(torch, L, _lib, pk)
             latency = latency_section(torch, det, proto, cm)
+            # BASELINE config 5 (training step, batch 32) in short form; the full line: --workload train
+            try:
+                import bench_train
+                train = bench_train.run_ours(args, section=True)
+            except Exception as e:       # the headline line must survive a failure of an extra section
+                train = {'error': '%s: %s' % (type(e).__name__, e)}
         wl = ('deploy.prototxt fwd + coverage decode + groupRectangles NMS, batch %d/GPU @448x448, bf16 tcgen05 convs, synthetic '
               'xavier weights (seed 0) with firing heads, one CUDA graph per step' % B)
         line = {'metric': METRIC, 'value': fps, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
@@ -530,7 +536,7 @@ def run_ours(args):
                 'gpu_launches': launches_per_step * args.steps,
                 'roofline': roof, 'cpu_baseline': cpu,
                 'tflops_whole_step': world * B * args.steps * FLOP_PER_FRAME / (ms * 1e-3) / 1e12,
-                'latency_batch1': latency, 'layer': layer, 'bandwidth_kernels': bwk, 'plan': plan}
+                'latency_batch1': latency, 'layer': layer, 'bandwidth_kernels': bwk, 'train': train, 'plan': plan}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -545,11 +551,16 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--global-batch', type=int, default=0,
                     help='strong scaling (BASELINE config 4): this many frames per step split evenly over the ranks')
+    ap.add_argument('--workload', default='detect', choices=['detect', 'train'],
+                    help="detect = BASELINE config 3 / 4 (the headline metric); train = BASELINE config 5 (bench_train.py)")
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-extras', action='store_true', help='skip the layer / latency / bandwidth-kernel sections')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
-    if args.impl == 'reference':
+    if args.workload == 'train':
+        import bench_train
+        (bench_train.run_reference if args.impl == 'reference' else bench_train.run_ours)(args)
+    elif args.impl == 'reference':
         run_reference(args)
     else:
         run_ours(args)

@@ -834,7 +834,7 @@ int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, c
     FCNOD_API_BEGIN
     FCNOD_CHECK(t && data && cvg_label && bbox_label && size_block && obj_block && cvg_block, "null argument");
     FCNOD_CUDA(cudaSetDevice(t->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    cudaStream_t s = (cudaStream_t)stream;      // NULL = the legacy default stream, as everywhere in this ABI
     const int N = t->batch, C = t->num_classes;
     FCNOD_CUDA(cudaMemsetAsync(t->grads, 0, t->n_params * 4, s));
     forward(t, data, s);
@@ -858,7 +858,7 @@ int fcnod_trainer_apply_update(fcnod_trainer* t, float grad_scale, void* stream)
     FCNOD_API_BEGIN
     FCNOD_CHECK(t, "null argument");
     FCNOD_CUDA(cudaSetDevice(t->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    cudaStream_t s = (cudaStream_t)stream;      // NULL = the legacy default stream, as everywhere in this ABI
     const fcnod_solver_params& sp = t->solver;
     AdamArgs a;
     const int tt = t->iter + 1;
@@ -875,7 +875,7 @@ int fcnod_trainer_losses(fcnod_trainer* t, float losses[2], void* stream) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(t && losses, "null argument");
     FCNOD_CUDA(cudaSetDevice(t->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : t->stream;
+    cudaStream_t s = (cudaStream_t)stream;      // NULL = the legacy default stream, as everywhere in this ABI
     FCNOD_CUDA(cudaMemcpyAsync(losses, t->losses_dev, 8, cudaMemcpyDeviceToHost, s));
     FCNOD_CUDA(cudaStreamSynchronize(s));
     FCNOD_API_END
