@@ -553,6 +553,8 @@ def main():
                     help='strong scaling (BASELINE config 4): this many frames per step split evenly over the ranks')
     ap.add_argument('--workload', default='detect', choices=['detect', 'train'],
                     help="detect = BASELINE config 3 / 4 (the headline metric); train = BASELINE config 5 (bench_train.py)")
+    ap.add_argument('--train-precision', default='bf16', choices=['fp32', 'bf16'],
+                    help='--workload train: fp32 = SIMT parity engine, bf16 = tcgen05 GEMM engine (fp32 master weights)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-extras', action='store_true', help='skip the layer / latency / bandwidth-kernel sections')
     args = ap.parse_args()

@@ -113,7 +113,8 @@ def run_ours(args, section=False):
     L = _lib.lib()
     proto, cm = train_files()
     B = BATCH
-    solver = Solver(proto, cm, batch=B, height=NET, width=NET, device=local, seed=1 + rank)
+    prec = getattr(args, 'train_precision', 'bf16')
+    solver = Solver(proto, cm, batch=B, height=NET, width=NET, device=local, seed=1 + rank, precision=prec)
     stream = torch.cuda.current_stream().cuda_stream
 
     src, lab, draws = layer_inputs(B, seed=10 + rank)
@@ -204,9 +205,10 @@ def run_ours(args, section=False):
     out = None
     if rank == 0:
         phases = {}
-        for name, fn in (('augmentation_layer', aug), ('forward_backward', fwd_bwd), ('allreduce', allreduce), ('adam_update', update)):
-            fn()
-            phases[name + '_ms'] = timed(fn, 3) / 3 if world == 1 else None
+        if world == 1:        # (with several ranks a phase timed on rank 0 alone would leave the others out of the collective)
+            for name, fn in (('augmentation_layer', aug), ('forward_backward', fwd_bwd), ('adam_update', update)):
+                fn()
+                phases[name + '_ms'] = timed(fn, 3) / 3
         # launches per step, counted from the layer list: forward 1 per layer that computes (+1 dropout mask), head 6,
         # backward 5 per convolution (mask, bias, wgrad, pack, dgrad; conv1 has no pack / dgrad, the heads no mask) + 1 per
         # other layer, 1 memset, 1 ADAM, 4 of the augmentation layer
@@ -218,11 +220,13 @@ def run_ours(args, section=False):
         fb_ms = phases['forward_backward_ms'] if world == 1 else ms / steps
         out = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': steps, 'warmup': warm, 'ms_per_step': ms / steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if prec == 'fp32' else 'bf16', 'data': 'synthetic',
             'config': {'workload': 'train_val.prototxt training step, batch %d/GPU @448x448: DataArgumentationLayer forward on the '
                                    'device (480x640 sources) + TRAIN forward + loss head + backward + %s + ADAM (solver.prototxt '
-                                   'values), fp32 SIMT parity engine' % (B, 'NCCL all-reduce of %d fp32 gradients' % solver.n_params if world > 1
-                                                                         else 'no all-reduce (1 GPU)'),
+                                   'values), %s' % (B, 'NCCL all-reduce of %d fp32 gradients' % solver.n_params if world > 1
+                                                                         else 'no all-reduce (1 GPU)',
+                                                                         'fp32 SIMT parity engine' if prec == 'fp32' else
+                                                                         'bf16 engine: convolutions as tcgen05 GEMMs (forward, dgrad, wgrad), fp32 master weights'),
                        'l2': 'activations of a step (>6 GB) exceed L2; no flush needed'},
             'losses_after_timed_steps': l0,
             'e2e': {'value': e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8, 'steps': e_steps,
@@ -230,12 +234,13 @@ def run_ours(args, section=False):
                            '-> all_reduce -> fcnod_trainer_apply_update -> fcnod_trainer_losses'},
             'gpu_launches': launches * steps,
             'phases': phases,
-            'roofline': {'bound': 'tensor', 'kernel': 'conv_simt_kernel / wgrad_simt_kernel (fp32 FFMA, not on the tensor pipe)',
+            'roofline': {'bound': 'tensor',
+                         'kernel': 'conv_simt_kernel / wgrad_simt_kernel (fp32 FFMA, not on the tensor pipe)' if prec == 'fp32' else
+                                   'gemm_tc_kernel (tcgen05, 3 GEMMs per convolution: forward, data gradient, weight gradient)',
                          'achieved': flop / (fb_ms * 1e-3) / 1e12, 'peak': pk['bf16_burst'], 'unit': 'TFLOP/s',
                          'frac': flop / (fb_ms * 1e-3) / 1e12 / pk['bf16_burst'], 'traffic': None,
-                         'note': 'algorithmic FLOP = 3 x forward convolution FLOP x batch over the forward + backward time; the parity '
-                                 'engine computes in fp32 on the CUDA cores, so the fraction of the bf16 tensor peak is small by design: '
-                                 'moving dgrad / wgrad to tcgen05 is the next step (DESIGN.md 9)'},
+                         'note': 'algorithmic FLOP = 3 x forward convolution FLOP x batch over the WHOLE forward + backward time (im2col, '
+                                 'pooling, LRN and the other elementwise launches included), against the burst bf16 peak'},
         }
         if clocks:
             out['clocks'] = clocks

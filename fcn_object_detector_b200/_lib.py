@@ -40,7 +40,7 @@ class PhotoDraw(C.Structure):
 class SolverParams(C.Structure):
     _fields_ = [('base_lr', C.c_float), ('gamma', C.c_float), ('stepsize', C.c_int32), ('momentum', C.c_float),
                 ('momentum2', C.c_float), ('delta', C.c_float), ('weight_decay', C.c_float), ('bbox_loss_weight', C.c_float),
-                ('dropout_ratio_override', C.c_float), ('seed', C.c_uint64)]
+                ('dropout_ratio_override', C.c_float), ('seed', C.c_uint64), ('precision', C.c_int32), ('reserved', C.c_int32)]
 
 
 class AugDraw(C.Structure):
@@ -133,6 +133,7 @@ SIGNATURES = {
     'fcnod_trainer_blob_read': (_I, [_P, _STR, _I, C.POINTER(_I), _P, _SZ]),
     'fcnod_trainer_dropout_mask': (_I, [_P, _P, _SZ, C.POINTER(_I)]),
     'fcnod_trainer_pool_argmax': (_I, [_P, _STR, _P, _SZ, C.POINTER(_I)]),
+    'fcnod_gemm_bf16_device': (_I, [_I, _P, _I, _P, _I, _I, _I, _I, _P, _I, _I, _P, _I, _I, _P]),
 }
 
 _lib = None

@@ -1,0 +1,216 @@
+// tcgen05 GEMM of the training step (train_net.cu, bf16 engine): the three matrix products of a convolution layer of
+// /root/reference/models/train_val.prototxt on the 5th-generation tensor cores, fp32 accumulation in TMEM.
+//
+//   forward   Y[px][Cout]  = X_col[px][Kc]  * Wf[Cout][Kc]^T      K-major operands  (MNMAJ = false)
+//   dgrad     dX_col[px][Kc] = dY[px][Cout] * Wb[Kc][Cout]^T      K-major operands  (MNMAJ = false)
+//   wgrad     dW[Kc][Cout] += X_col[px][Kc]^T * dY[px][Cout]      reduction over PIXELS: both operands are stored with the
+//             reduction index as the OUTER dimension (NHWC: a pixel is a row of channels), i.e. "MN-major" in UMMA terms
+//             (MNMAJ = true).  No transposed copies are made: the TMA boxes {64 channels, PK pixels} land as PK rows of 128
+//             swizzled bytes, which is the canonical MN-major SWIZZLE_128B layout (64-element MN blocks LBO apart, 8-row K
+//             groups SBO = 1024 bytes apart), and the instruction descriptor sets a_major = b_major = 1.
+//             The pixel range is split over CTAs (split-K); partial tiles are added to the fp32 gradient with red.global.
+// X_col is the activation matrix itself for 1x1 convolutions and an im2col matrix (bf16, written by im2col_kernel) for
+// k x k ones.  One CTA = 6 warps: warp 0 TMA producer, warp 1 MMA issuer (+ TMEM allocation), warps 2..5 epilogue (one TMEM
+// lane quadrant each).  Persistent over output tiles, two accumulators in TMEM so the epilogue of a tile overlaps the MMAs
+// of the next.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+#include "conv_tc.cuh"
+
+namespace fcnod {
+
+struct GemmTcParams {
+    int M, N, K;               // D is M x N, reduction length K (MNMAJ: M = Cout, N = Kc, K = pixels)
+    int BN;                    // N tile: multiple of 16 (K-major) / of 64 (MN-major), <= 256
+    int tiles_m, tiles_n, splits;
+    int k_blocks;              // reduction blocks (64 elements K-major / PK pixels MN-major) of the whole K
+    int kb_per_split;          // MNMAJ: reduction blocks per split
+    int stages;
+    uint32_t a_stage_bytes, b_stage_bytes, tmem_cols;
+    // epilogue, K-major
+    void* out; int ldo; int out_f32;      // row-major M x N view, leading dimension ldo elements
+    const float* bias;                    // [N] or null
+    int relu, accum;                      // accum: out += result
+    // epilogue, MN-major
+    float* gout; int ldg;                 // gout[n * ldg + m] += D[m][n]
+};
+
+constexpr int kGemmThreads = 192;
+constexpr int kGemmPK = 64;               // pixels per reduction block of the MN-major form
+
+template <bool MNMAJ>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmTcParams p) {
+    using namespace tc;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
+    const uint32_t bar_base = smem_base + (uint32_t)p.stages * stage_bytes;
+    const uint32_t full0 = bar_base, empty0 = full0 + 8u * p.stages;
+    const uint32_t tfull0 = empty0 + 8u * p.stages, tempty0 = tfull0 + 16u, tmem_slot = tempty0 + 16u;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
+
+    const int n_work = p.tiles_m * p.tiles_n * p.splits;
+    const int kb_total = p.k_blocks;
+
+    if (warp == 0) {
+        // ================================================================== TMA producer
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+            uint32_t s = 0, ph = 0;
+            for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+                const int tn = w % p.tiles_n, tm = (w / p.tiles_n) % p.tiles_m, sp = w / (p.tiles_n * p.tiles_m);
+                const int m0 = tm * 128, n0 = tn * p.BN;
+                const int kb0 = MNMAJ ? sp * p.kb_per_split : 0;
+                const int kb1 = MNMAJ ? min(kb0 + p.kb_per_split, kb_total) : kb_total;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(empty0 + 8u * s, ph ^ 1u);
+                    const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + p.a_stage_bytes;
+                    mbar_expect_tx(full0 + 8u * s, stage_bytes);
+                    if (!MNMAJ) {
+                        tma_load_2d(a_dst, &tmap_a, full0 + 8u * s, kb * 64, m0);
+                        tma_load_2d(b_dst, &tmap_b, full0 + 8u * s, kb * 64, n0);
+                    } else {
+                        const int px = kb * kGemmPK;
+#pragma unroll 1
+                        for (int i = 0; i < 2; ++i) tma_load_2d(a_dst + i * (kGemmPK * 128), &tmap_a, full0 + 8u * s, m0 + 64 * i, px);
+#pragma unroll 1
+                        for (int i = 0; i < p.BN / 64; ++i) tma_load_2d(b_dst + i * (kGemmPK * 128), &tmap_b, full0 + 8u * s, n0 + 64 * i, px);
+                    }
+                    if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================================================== MMA issuer
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (MNMAJ ? ((1u << 15) | (1u << 16)) : 0u) |
+                                   ((uint32_t)(p.BN >> 3) << 17) | (8u << 24);
+            // descriptor high word: SBO >> 4 | version 1 << 14 | SWIZZLE_128B (2) << 29; both forms have 8-row groups 1024 B apart
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t lbo = MNMAJ ? ((uint32_t)(kGemmPK * 128) >> 4) : 1u;
+            uint32_t s = 0, ph = 0, it = 0;
+            for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
+                const int sp = w / (p.tiles_n * p.tiles_m);
+                const int kb0 = MNMAJ ? sp * p.kb_per_split : 0;
+                const int kb1 = MNMAJ ? min(kb0 + p.kb_per_split, kb_total) : kb_total;
+                const uint32_t acc = it & 1u, acc_ph = (it >> 1) & 1u;
+                mbar_wait(tempty0 + 8u * acc, acc_ph ^ 1u);
+                fence_after();
+                const uint32_t tmem_d = tmem_base + acc * (uint32_t)p.BN;
+                uint32_t accum = 0;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(full0 + 8u * s, ph);
+                    fence_after();
+                    const uint32_t a_s = smem_base + s * stage_bytes, b_s = a_s + p.a_stage_bytes;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        // K-major: 16 elements = 32 bytes along the swizzled row; MN-major: 16 pixel rows = 2048 bytes
+                        const uint32_t adv = MNMAJ ? (uint32_t)k * 2048u : (uint32_t)k * 32u;
+                        const uint64_t da = ((uint64_t)desc_hi << 32) | (uint64_t)(((a_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)lbo << 16);
+                        const uint64_t db = ((uint64_t)desc_hi << 32) | (uint64_t)(((b_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)lbo << 16);
+                        umma_bf16(tmem_d, da, db, idesc, accum);
+                        accum = 1;
+                    }
+                    umma_commit(empty0 + 8u * s);
+                    if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
+                }
+                umma_commit(tfull0 + 8u * acc);
+            }
+        }
+    } else {
+        // ================================================================== epilogue: 4 warps, TMEM lane quadrant = warp % 4
+        const int q = warp & 3;
+        uint32_t it = 0;
+        for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
+            const int tn = w % p.tiles_n, tm = (w / p.tiles_n) % p.tiles_m;
+            const int m0 = tm * 128, n0 = tn * p.BN;
+            const uint32_t acc = it & 1u, acc_ph = (it >> 1) & 1u;
+            mbar_wait(tfull0 + 8u * acc, acc_ph);
+            fence_after();
+            const int row = m0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + acc * (uint32_t)p.BN + ((uint32_t)(q * 32) << 16);
+            for (int c0 = 0; c0 < p.BN; c0 += 16) {
+                uint32_t r[16];
+                tmem_ld16(taddr + (uint32_t)c0, r);
+                tmem_ld_wait();
+                const int n = n0 + c0;
+                if (n >= p.N) continue;
+                if (MNMAJ) {
+                    if (row < p.M) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (n + j < p.N) atomicAdd(p.gout + (long)(n + j) * p.ldg + row, __uint_as_float(r[j]));
+                    }
+                } else if (row < p.M) {
+                    float v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        v[j] = __uint_as_float(r[j]);
+                        if (p.bias && n + j < p.N) v[j] += p.bias[n + j];
+                        if (p.relu) v[j] = fmaxf(v[j], 0.f);
+                    }
+                    const bool full = n + 16 <= p.N;
+                    if (p.out_f32) {
+                        float* o = static_cast<float*>(p.out) + (long)row * p.ldo + n;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (full || n + j < p.N) o[j] = p.accum ? o[j] + v[j] : v[j];
+                    } else {
+                        bf16* o = static_cast<bf16*>(p.out) + (long)row * p.ldo + n;
+                        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+                            uint4 w4[2];
+                            if (p.accum) {
+                                w4[0] = reinterpret_cast<const uint4*>(o)[0];
+                                w4[1] = reinterpret_cast<const uint4*>(o)[1];
+                                const bf16* old = reinterpret_cast<const bf16*>(w4);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) v[j] += __bfloat162float(old[j]);
+                            }
+                            __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(w4);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) h2[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            reinterpret_cast<uint4*>(o)[0] = w4[0];
+                            reinterpret_cast<uint4*>(o)[1] = w4[1];
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (n + j < p.N) o[j] = __float2bfloat16_rn(p.accum ? __bfloat162float(o[j]) + v[j] : v[j]);
+                        }
+                    }
+                }
+            }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+    }
+}
+
+}  // namespace fcnod

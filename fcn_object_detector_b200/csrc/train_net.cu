@@ -29,6 +29,7 @@
 
 #include "common.cuh"
 #include "conv_simt.cuh"
+#include "gemm_tc.cuh"
 #include "kernels.h"
 #include "netdef.h"
 
@@ -39,7 +40,8 @@ inline int grid1(long n, int threads) { return (int)std::min<long>((n + threads 
 
 // ------------------------------------------------------------------------------------------------ layout kernels
 // data NCHW fp32 -> NHWC with the Power layer applied (train_val.prototxt:27-35: shift + scale * x, power 1)
-__global__ void nchw_to_nhwc_power_kernel(const float* __restrict__ in, float* __restrict__ out, int N, int C, int H, int W,
+template <typename T>
+__global__ void nchw_to_nhwc_power_kernel(const float* __restrict__ in, T* __restrict__ out, int N, int C, int H, int W,
                                           float scale, float shift) {
     const long total = (long)N * C * H * W;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -48,12 +50,13 @@ __global__ void nchw_to_nhwc_power_kernel(const float* __restrict__ in, float* _
         const int w = (int)(t % W); t /= W;
         const int h = (int)(t % H);
         const int n = (int)(t / H);
-        out[i] = __fadd_rn(shift, __fmul_rn(scale, in[((long)(n * C + c) * H + h) * W + w]));
+        out[i] = from_f32<T>(__fadd_rn(shift, __fmul_rn(scale, in[((long)(n * C + c) * H + h) * W + w])));
     }
 }
 
 // NHWC view (ldc, channel offset folded into the pointer) <-> dense NCHW
-__global__ void nhwc_to_nchw_kernel(const float* __restrict__ in, int ldc, float* __restrict__ out, int N, int C, int H, int W) {
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ in, int ldc, float* __restrict__ out, int N, int C, int H, int W) {
     const long total = (long)N * C * H * W;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int w = (int)(i % W);
@@ -61,10 +64,11 @@ __global__ void nhwc_to_nchw_kernel(const float* __restrict__ in, int ldc, float
         const int h = (int)(t % H); t /= H;
         const int c = (int)(t % C);
         const int n = (int)(t / C);
-        out[i] = in[((long)(n * H + h) * W + w) * ldc + c];
+        out[i] = to_f32<T>(in[((long)(n * H + h) * W + w) * ldc + c]);
     }
 }
-__global__ void nchw_to_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, int ldc, int N, int C, int H, int W) {
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ in, T* __restrict__ out, int ldc, int N, int C, int H, int W) {
     const long total = (long)N * C * H * W;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int w = (int)(i % W);
@@ -72,7 +76,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ in, float* __restr
         const int h = (int)(t % H); t /= H;
         const int c = (int)(t % C);
         const int n = (int)(t / C);
-        out[((long)(n * H + h) * W + w) * ldc + c] = in[i];
+        out[((long)(n * H + h) * W + w) * ldc + c] = from_f32<T>(in[i]);
     }
 }
 __global__ void u8_nhwc_to_nchw_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int N, int C, int H, int W) {
@@ -90,7 +94,8 @@ __global__ void u8_nhwc_to_nchw_kernel(const uint8_t* __restrict__ in, uint8_t* 
 // ------------------------------------------------------------------------------------------------ pooling
 struct PoolGeo { int N, C, H, W, Ho, Wo, k, s, p, ldi, ldo; };
 
-__global__ void pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
+template <typename T>
+__global__ void pool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
     const long total = (long)g.N * g.Ho * g.Wo * g.C;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int c = (int)(i % g.C);
@@ -105,15 +110,16 @@ __global__ void pool_fwd_kernel(const float* __restrict__ x, float* __restrict__
         int bi = 0;
         for (int h = hs; h < he; ++h)
             for (int w = ws; w < we; ++w) {
-                const float v = x[((long)(n * g.H + h) * g.W + w) * g.ldi + c];
+                const float v = to_f32<T>(x[((long)(n * g.H + h) * g.W + w) * g.ldi + c]);
                 if (v > best) { best = v; bi = (h - h0) * g.k + (w - w0); }
             }
-        y[((long)(n * g.Ho + ph) * g.Wo + pw) * g.ldo + c] = best;
+        y[((long)(n * g.Ho + ph) * g.Wo + pw) * g.ldo + c] = from_f32<T>(best);
         idx[i] = (uint8_t)bi;
     }
 }
 
-__global__ void pool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ idx, float* __restrict__ dx, PoolGeo g,
+template <typename T>
+__global__ void pool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ idx, T* __restrict__ dx, PoolGeo g,
                                 int accum) {
     const long total = (long)g.N * g.H * g.W * g.C;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -129,32 +135,34 @@ __global__ void pool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __r
             for (int pw = pw0; pw < pw1; ++pw) {
                 const long o = ((long)(n * g.Ho + ph) * g.Wo + pw);
                 const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
-                if (idx[o * g.C + c] == local) acc += dy[o * g.ldo + c];
+                if (idx[o * g.C + c] == local) acc += to_f32<T>(dy[o * g.ldo + c]);
             }
         const long xi = ((long)(n * g.H + h) * g.W + w) * g.ldi + c;
-        dx[xi] = accum ? dx[xi] + acc : acc;
+        dx[xi] = from_f32<T>(accum ? to_f32<T>(dx[xi]) + acc : acc);
     }
 }
 
 // ------------------------------------------------------------------------------------------------ LRN (across channels)
-__global__ void lrn_fwd_kernel(const float* __restrict__ x, int ldi, float* __restrict__ y, int ldo, float* __restrict__ scale,
+template <typename T>
+__global__ void lrn_fwd_kernel(const T* __restrict__ x, int ldi, T* __restrict__ y, int ldo, float* __restrict__ scale,
                                long npix, int C, int n, float alpha_over_n, float beta, float k) {
     const long total = npix * C;
     const int half = n / 2;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         const long px = i / C;
-        const float* xp = x + px * ldi;
+        const T* xp = x + px * ldi;
         float s = 0.f;
-        for (int cc = max(c - half, 0); cc <= min(c + half, C - 1); ++cc) s = fmaf(xp[cc], xp[cc], s);
+        for (int cc = max(c - half, 0); cc <= min(c + half, C - 1); ++cc) { const float xv = to_f32<T>(xp[cc]); s = fmaf(xv, xv, s); }
         const float sc = fmaf(alpha_over_n, s, k);
         scale[i] = sc;
-        y[px * ldo + c] = xp[c] * powf(sc, -beta);
+        y[px * ldo + c] = from_f32<T>(to_f32<T>(xp[c]) * powf(sc, -beta));
     }
 }
 
-__global__ void lrn_bwd_kernel(const float* __restrict__ x, int ldi, const float* __restrict__ y, const float* __restrict__ dy,
-                               int ldo, const float* __restrict__ scale, float* __restrict__ dx, long npix, int C, int n,
+template <typename T>
+__global__ void lrn_bwd_kernel(const T* __restrict__ x, int ldi, const T* __restrict__ y, const T* __restrict__ dy,
+                               int ldo, const float* __restrict__ scale, T* __restrict__ dx, long npix, int C, int n,
                                float alpha_over_n, float beta, int accum) {
     const long total = npix * C;
     const int half = n / 2;
@@ -164,10 +172,10 @@ __global__ void lrn_bwd_kernel(const float* __restrict__ x, int ldi, const float
         const long px = i / C;
         float s = 0.f;
         for (int cc = max(c - half, 0); cc <= min(c + half, C - 1); ++cc)
-            s += dy[px * ldo + cc] * y[px * ldo + cc] / scale[px * C + cc];
-        const float v = dy[px * ldo + c] * powf(scale[i], -beta) - cr * x[px * ldi + c] * s;
+            s += to_f32<T>(dy[px * ldo + cc]) * to_f32<T>(y[px * ldo + cc]) / scale[px * C + cc];
+        const float v = to_f32<T>(dy[px * ldo + c]) * powf(scale[i], -beta) - cr * to_f32<T>(x[px * ldi + c]) * s;
         const long xi = px * ldi + c;
-        dx[xi] = accum ? dx[xi] + v : v;
+        dx[xi] = from_f32<T>(accum ? to_f32<T>(dx[xi]) + v : v);
     }
 }
 
@@ -187,47 +195,49 @@ __global__ void dropout_mask_kernel(uint8_t* __restrict__ mask, long total, uint
     }
 }
 // y = x * mask * scale (forward) and dx (+)= dy * mask * scale (backward): same kernel
-__global__ void dropout_apply_kernel(const float* __restrict__ in, const uint8_t* __restrict__ mask, float* __restrict__ out,
+template <typename T>
+__global__ void dropout_apply_kernel(const T* __restrict__ in, const uint8_t* __restrict__ mask, T* __restrict__ out,
                                      long total, float scale, int accum) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const float v = mask[i] ? __fmul_rn(in[i], scale) : 0.f;
-        out[i] = accum ? out[i] + v : v;
+        const float v = mask[i] ? __fmul_rn(to_f32<T>(in[i]), scale) : 0.f;
+        out[i] = from_f32<T>(accum ? to_f32<T>(out[i]) + v : v);
     }
 }
-__global__ void copy_or_add_kernel(const float* __restrict__ in, float* __restrict__ out, long total, int accum) {
+template <typename T>
+__global__ void sigmoid_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long total) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
-        out[i] = accum ? out[i] + in[i] : in[i];
+        y[i] = from_f32<T>(1.f / (1.f + expf(-to_f32<T>(x[i]))));
 }
-__global__ void sigmoid_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long total) {
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
-        y[i] = 1.f / (1.f + expf(-x[i]));
-}
-__global__ void sigmoid_bwd_kernel(const float* __restrict__ y, const float* __restrict__ dy, float* __restrict__ dx, long total,
+template <typename T>
+__global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long total,
                                    int accum) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const float v = dy[i] * y[i] * (1.f - y[i]);
-        dx[i] = accum ? dx[i] + v : v;
+        const float yv = to_f32<T>(y[i]);
+        const float v = to_f32<T>(dy[i]) * yv * (1.f - yv);
+        dx[i] = from_f32<T>(accum ? to_f32<T>(dx[i]) + v : v);
     }
 }
 // in-place ReLU backward on a channel slice: dy = y > 0 ? dy : 0
-__global__ void relu_mask_kernel(const float* __restrict__ y, float* __restrict__ dy, long npix, int C, int ldc) {
+template <typename T>
+__global__ void relu_mask_kernel(const T* __restrict__ y, T* __restrict__ dy, long npix, int C, int ldc) {
     const long total = npix * C;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const long o = (i / C) * ldc + (i % C);
-        if (!(y[o] > 0.f)) dy[o] = 0.f;
+        if (!(to_f32<T>(y[o]) > 0.f)) dy[o] = from_f32<T>(0.f);
     }
 }
 
 // ------------------------------------------------------------------------------------------------ convolution backward
 // bias gradient: db[c] += sum over pixels of dy[px][c].  grid (ceil(C / 32), pixel chunks), block 32 x 8.
-__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ dy, int ldc, int C, long npix, long chunk,
+template <typename T>
+__global__ void __launch_bounds__(256) bias_grad_kernel(const T* __restrict__ dy, int ldc, int C, long npix, long chunk,
                                                          float* __restrict__ db) {
     __shared__ float red[8][33];
     const int c = blockIdx.x * 32 + threadIdx.x;
     const long p0 = blockIdx.y * chunk, p1 = min(p0 + chunk, npix);
     float s = 0.f;
     if (c < C)
-        for (long p = p0 + threadIdx.y; p < p1; p += 8) s += dy[p * ldc + c];
+        for (long p = p0 + threadIdx.y; p < p1; p += 8) s += to_f32<T>(dy[p * ldc + c]);
     red[threadIdx.y][threadIdx.x] = s;
     __syncthreads();
     if (threadIdx.y == 0 && c < C) {
@@ -239,8 +249,8 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
 }
 
 struct WgradParams {
-    const float* x;     // bottom, NHWC view
-    const float* dy;    // top diff, NHWC view
+    const void* x;      // bottom, NHWC view
+    const void* dy;     // top diff, NHWC view
     float* g;           // [K][ldw] packed weight gradient (accumulated with atomics; zeroed by the caller)
     int N, H, W, Cin, ldi;
     int Ho, Wo, Cout, ldo, ldw;
@@ -250,6 +260,7 @@ struct WgradParams {
 
 // G[kk][co] += sum_m A[m][kk] * dy[m][co], A = im2col(x) gathered on the fly, kk = (r*k + s)*Cin + c.
 // Tile 64 (kk) x 64 (co), 16 pixels per step, 256 threads, 4x4 register micro-tile.
+template <typename T>
 __global__ void __launch_bounds__(256) wgrad_simt_kernel(WgradParams p) {
     constexpr int BK = 64, BN = 64, BP = 16;
     __shared__ float As[BP][BK + 4];
@@ -269,6 +280,8 @@ __global__ void __launch_bounds__(256) wgrad_simt_kernel(WgradParams p) {
     if (kok) { c = kk % p.Cin; const int rs = kk / p.Cin; s = rs % p.k; r = rs / p.k; }
     const int co = n0 + tid % BN;
     const bool cok = co < p.Cout;
+    const T* px_ = static_cast<const T*>(p.x);
+    const T* pdy = static_cast<const T*>(p.dy);
 
     float acc[4][4];
 #pragma unroll
@@ -287,8 +300,8 @@ __global__ void __launch_bounds__(256) wgrad_simt_kernel(WgradParams p) {
                 const int oh = (int)(t % p.Ho);
                 const int n = (int)(t / p.Ho);
                 const int ih = oh * p.stride - p.pad + r, iw = ow * p.stride - p.pad + s;
-                if (kok && ih >= 0 && ih < p.H && iw >= 0 && iw < p.W) a = p.x[((long)(n * p.H + ih) * p.W + iw) * p.ldi + c];
-                if (cok) b = p.dy[m * p.ldo + co];
+                if (kok && ih >= 0 && ih < p.H && iw >= 0 && iw < p.W) a = to_f32<T>(px_[((long)(n * p.H + ih) * p.W + iw) * p.ldi + c]);
+                if (cok) b = to_f32<T>(pdy[m * p.ldo + co]);
             }
             As[prow + 4 * i][kl] = a;
             Bs[prow + 4 * i][tid % BN] = b;
@@ -355,6 +368,274 @@ __global__ void adam_kernel(float* __restrict__ w, float* __restrict__ g, float*
     }
 }
 
+// ------------------------------------------------------------------------------------------------ bf16 engine: 8 channels per thread
+// Same arithmetic as the generic kernels above on 16-byte groups of channels (all blobs of the network have C % 8 == 0 except
+// the 3-channel input and the two heads, which keep the generic kernels).
+struct BF8 {
+    uint4 v;
+    __device__ __forceinline__ float get(int q) const { return __bfloat162float(reinterpret_cast<const bf16*>(&v)[q]); }
+    __device__ __forceinline__ void set(int q, float f) { reinterpret_cast<bf16*>(&v)[q] = __float2bfloat16_rn(f); }
+};
+__device__ __forceinline__ BF8 ld8(const bf16* p) { BF8 r; r.v = *reinterpret_cast<const uint4*>(p); return r; }
+__device__ __forceinline__ void st8(bf16* p, const BF8& r) { *reinterpret_cast<uint4*>(p) = r.v; }
+
+__global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
+    const int cv = g.C / 8;
+    const long total = (long)g.N * g.Ho * g.Wo * cv;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * 8;
+        long t = i / cv;
+        const int pw = (int)(t % g.Wo); t /= g.Wo;
+        const int ph = (int)(t % g.Ho);
+        const int n = (int)(t / g.Ho);
+        const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
+        const int hs = max(h0, 0), ws = max(w0, 0);
+        const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
+        float best[8];
+        int bi[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { best[q] = -3.402823466e+38f; bi[q] = 0; }
+        for (int h = hs; h < he; ++h)
+            for (int w = ws; w < we; ++w) {
+                const BF8 v = ld8(x + ((long)(n * g.H + h) * g.W + w) * g.ldi + c);
+                const int loc = (h - h0) * g.k + (w - w0);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float f = v.get(q);
+                    if (f > best[q]) { best[q] = f; bi[q] = loc; }
+                }
+            }
+        const long o = (long)(n * g.Ho + ph) * g.Wo + pw;
+        BF8 r;
+        uint2 ib;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { r.set(q, best[q]); reinterpret_cast<uint8_t*>(&ib)[q] = (uint8_t)bi[q]; }
+        st8(y + o * g.ldo + c, r);
+        *reinterpret_cast<uint2*>(idx + o * g.C + c) = ib;
+    }
+}
+
+__global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, PoolGeo g, int accum) {
+    const int cv = g.C / 8;
+    const long total = (long)g.N * g.H * g.W * cv;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * 8;
+        long t = i / cv;
+        const int w = (int)(t % g.W); t /= g.W;
+        const int h = (int)(t % g.H);
+        const int n = (int)(t / g.H);
+        const int ph0 = (h + g.p < g.k) ? 0 : (h + g.p - g.k) / g.s + 1, ph1 = min((h + g.p) / g.s + 1, g.Ho);
+        const int pw0 = (w + g.p < g.k) ? 0 : (w + g.p - g.k) / g.s + 1, pw1 = min((w + g.p) / g.s + 1, g.Wo);
+        float acc[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+        for (int ph = ph0; ph < ph1; ++ph)
+            for (int pw = pw0; pw < pw1; ++pw) {
+                const long o = (long)(n * g.Ho + ph) * g.Wo + pw;
+                const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
+                const uint2 ib = *reinterpret_cast<const uint2*>(idx + o * g.C + c);
+                const BF8 d = ld8(dy + o * g.ldo + c);
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (reinterpret_cast<const uint8_t*>(&ib)[q] == local) acc[q] += d.get(q);
+            }
+        bf16* o = dx + ((long)(n * g.H + h) * g.W + w) * g.ldi + c;
+        BF8 r;
+        if (accum) {
+            r = ld8(o);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] += r.get(q);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) r.set(q, acc[q]);
+        st8(o, r);
+    }
+}
+
+__global__ void relu_mask8_kernel(const bf16* __restrict__ y, bf16* __restrict__ dy, long npix, int C, int ldc) {
+    const int cv = C / 8;
+    const long total = npix * cv;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long o = (i / cv) * ldc + (i % cv) * 8;
+        const BF8 a = ld8(y + o);
+        BF8 d = ld8(dy + o);
+        bool any = false;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            if (!(a.get(q) > 0.f)) { d.set(q, 0.f); any = true; }
+        if (any) st8(dy + o, d);
+    }
+}
+
+// LRN, 8 channels per thread; the two neighbours on either side come from scalar loads (L1 hits)
+__global__ void lrn_fwd8_kernel(const bf16* __restrict__ x, int ldi, bf16* __restrict__ y, int ldo, float* __restrict__ scale, long npix,
+                                int C, float alpha_over_n, float beta, float k) {
+    const int cv = C / 8;
+    const long total = npix * cv;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * 8;
+        const long px = i / cv;
+        const bf16* xp = x + px * ldi;
+        float v[12];
+        const BF8 a = ld8(xp + c);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q + 2] = a.get(q);
+        v[0] = c >= 2 ? __bfloat162float(xp[c - 2]) : 0.f; v[1] = c >= 1 ? __bfloat162float(xp[c - 1]) : 0.f;
+        v[10] = c + 8 < C ? __bfloat162float(xp[c + 8]) : 0.f; v[11] = c + 9 < C ? __bfloat162float(xp[c + 9]) : 0.f;
+        BF8 r;
+        float sc[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            float s = 0.f;
+#pragma unroll
+            for (int d = 0; d < 5; ++d) s = fmaf(v[q + d], v[q + d], s);
+            sc[q] = fmaf(alpha_over_n, s, k);
+            r.set(q, v[q + 2] * powf(sc[q], -beta));
+        }
+        st8(y + px * ldo + c, r);
+        float4* so = reinterpret_cast<float4*>(scale + px * C + c);
+        so[0] = make_float4(sc[0], sc[1], sc[2], sc[3]);
+        so[1] = make_float4(sc[4], sc[5], sc[6], sc[7]);
+    }
+}
+
+__global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16* __restrict__ y, const bf16* __restrict__ dy, int ldo,
+                                const float* __restrict__ scale, bf16* __restrict__ dx, long npix, int C, float alpha_over_n, float beta,
+                                int accum) {
+    const int cv = C / 8;
+    const long total = npix * cv;
+    const float cr = 2.f * alpha_over_n * beta;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * 8;
+        const long px = i / cv;
+        float ratio[12], sc[8], dyv[8];
+#pragma unroll
+        for (int q = 0; q < 12; ++q) {
+            const int cc = c - 2 + q;
+            ratio[q] = 0.f;
+            if (cc >= 0 && cc < C) {
+                const float d = __bfloat162float(dy[px * ldo + cc]), s = scale[px * C + cc];
+                ratio[q] = d * __bfloat162float(y[px * ldo + cc]) / s;
+                if (q >= 2 && q < 10) { sc[q - 2] = s; dyv[q - 2] = d; }
+            }
+        }
+        const BF8 xv = ld8(x + px * ldi + c);
+        bf16* o = dx + px * ldi + c;
+        BF8 r;
+        if (accum) r = ld8(o);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const float s = ratio[q] + ratio[q + 1] + ratio[q + 2] + ratio[q + 3] + ratio[q + 4];
+            float v = dyv[q] * powf(sc[q], -beta) - cr * xv.get(q) * s;
+            if (accum) v += r.get(q);
+            r.set(q, v);
+        }
+        st8(o, r);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ bf16 engine helpers
+// im2col for the tensor-core GEMMs: col[px][(r*k + s)*Cin + c] = x[n][oh*stride - pad + r][ow*stride - pad + s][c] (0 outside),
+// rows of ldk elements (Kc rounded up to 8: a TMA row pitch is a multiple of 16 bytes; the padding columns are zeroed).
+// VEC = 8: 16-byte moves (Cin % 8 == 0 and the view 16-byte aligned), VEC = 1: scalar (the first convolution, Cin = 3).
+template <int VEC>      // VEC = 8: Cin % 8 == 0, whole 16-byte groups copied; VEC = 1: any Cin, gathered per element
+__global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restrict__ col, int ldk, int N, int H, int W, int Cin,
+                              int Ho, int Wo, int k, int stride, int pad) {
+    const int kc = k * k * Cin;
+    const int per_row = ldk / 8;
+    const long total = (long)N * Ho * Wo * per_row;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int j = (int)(i % per_row) * 8;
+        const long m = i / per_row;
+        const int ow = (int)(m % Wo);
+        const long t = m / Wo;
+        const int oh = (int)(t % Ho);
+        const int n = (int)(t / Ho);
+        if (VEC == 8) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (j < kc) {
+                const int c = j % Cin, rs = j / Cin, r = rs / k, s2 = rs % k;
+                const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
+                if (ih >= 0 && ih < H && iw >= 0 && iw < W)
+                    v = *reinterpret_cast<const uint4*>(x + ((long)(n * H + ih) * W + iw) * ldi + c);
+            }
+            *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
+        } else {
+            // few input channels (the first convolution, Cin = 3): every element gathered on its own, still one 16-byte store
+            uint4 v;
+            bf16* e = reinterpret_cast<bf16*>(&v);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int jj = j + q;
+                bf16 a = __float2bfloat16_rn(0.f);
+                if (jj < kc) {
+                    const int c = jj % Cin, rs = jj / Cin, r = rs / k, s2 = rs % k;
+                    const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
+                    if (ih >= 0 && ih < H && iw >= 0 && iw < W) a = x[((long)(n * H + ih) * W + iw) * ldi + c];
+                }
+                e[q] = a;
+            }
+            *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
+        }
+    }
+}
+
+// data gradient of a stride-1 k x k convolution from the column gradient dcol = dY * W (the adjoint of im2col):
+// dx[n][h][w][c] (+)= sum_{r,s} dcol[(n, h + pad - r, w + pad - s)][(r*k + s)*Cin + c]; 8 channels per thread.
+__global__ void col2im_kernel(const bf16* __restrict__ dcol, int ldk, bf16* __restrict__ dx, int ldi, int N, int H, int W, int Cin,
+                              int k, int pad, int accum) {
+    const int cv = Cin / 8;
+    const long total = (long)N * H * W * cv;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cv) * 8;
+        const long m = i / cv;
+        const int w = (int)(m % W);
+        const long t = m / W;
+        const int h = (int)(t % H);
+        const int n = (int)(t / H);
+        float acc[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+        for (int r = 0; r < k; ++r) {
+            const int oh = h + pad - r;
+            if (oh < 0 || oh >= H) continue;
+            for (int s2 = 0; s2 < k; ++s2) {
+                const int ow = w + pad - s2;
+                if (ow < 0 || ow >= W) continue;
+                const uint4 v = *reinterpret_cast<const uint4*>(dcol + ((long)(n * H + oh) * W + ow) * ldk + (r * k + s2) * Cin + c);
+                const bf16* e = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(e[q]);
+            }
+        }
+        bf16* o = dx + m * ldi + c;
+        uint4 ov;
+        bf16* oe = reinterpret_cast<bf16*>(&ov);
+        if (accum) {
+            ov = *reinterpret_cast<const uint4*>(o);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(oe[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) oe[q] = __float2bfloat16_rn(acc[q]);
+        *reinterpret_cast<uint4*>(o) = ov;
+    }
+}
+
+// bf16 copies of the parameters, refreshed before every forward: `wb` = the flat buffer cast as it is (packed [Kc][ldw]: the
+// B operand of the data-gradient GEMM), `wf` = its transpose [Cout][ldk] per convolution (B operand of the forward GEMM).
+__global__ void cast_flat_kernel(const float* __restrict__ in, bf16* __restrict__ out, long total) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
+        out[i] = __float2bfloat16_rn(in[i]);
+}
+__global__ void pack_wf_kernel(const float* __restrict__ P, int ldw, bf16* __restrict__ wf, int ldk, int Kc, int Cout) {
+    const long total = (long)Cout * ldk;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int j = (int)(i % ldk), co = (int)(i / ldk);
+        wf[i] = __float2bfloat16_rn(j < Kc ? P[(long)j * ldw + co] : 0.f);
+    }
+}
+
 }  // namespace
 }  // namespace fcnod
 
@@ -363,7 +644,7 @@ using namespace fcnod;
 // =================================================================================================== the trainer
 namespace {
 
-struct TBuf { int C = 0, H = 0, W = 0; float* data = 0; float* diff = 0; };
+struct TBuf { int C = 0, H = 0, W = 0; char* data = 0; char* diff = 0; };   // NHWC, float32 or bf16 (trainer precision)
 struct TBlob {
     std::string name;
     int C = 0, H = 0, W = 0;
@@ -375,7 +656,12 @@ struct TBlob {
 struct TConv {
     int Cout = 0, Cin = 0, k = 1, stride = 1, pad = 0, K = 0, ldw = 0, ldt = 0;
     size_t w_off = 0, b_off = 0;     // floats into the flat parameter buffer
-    float* d_wt = 0;                 // dgrad packing [(r,s,co)][ldt], rebuilt every step
+    float* d_wt = 0;                 // SIMT dgrad packing [(r,s,co)][ldt], rebuilt every step
+    // bf16 engine (tensor cores): transposed bf16 weights [Cout][ldk] (forward B operand), im2col row pitch, GEMM plans
+    bool tc = false;
+    bf16* d_wf = 0;
+    int ldk = 0;
+    int g_fwd = -1, g_dgrad = -1, g_wgrad = -1;
     float lr_mult[2], decay_mult[2];
     std::string name;
 };
@@ -388,10 +674,23 @@ struct TLayer {
     uint8_t* mask = 0;     // Dropout: keep mask (NHWC order)
 };
 
+struct GemmPlan {
+    CUtensorMap ta, tb;
+    GemmTcParams p;
+    int grid = 0;
+    size_t smem = 0;
+    bool mn = false;
+};
+
 }  // namespace
 
 struct fcnod_trainer {
     int device = 0, batch = 0, in_c = 3, in_h = 0, in_w = 0, num_classes = 1;
+    int prec = 0;                             // 0: float32 storage, SIMT convolutions; 1: bf16 storage, tcgen05 GEMMs
+    size_t esz = 4;
+    bf16* wb = 0;                             // bf16 copy of the flat parameter buffer
+    bf16* col = 0;                            // im2col / column-gradient scratch
+    std::vector<GemmPlan> gemms;
     fcnod_solver_params solver;
     NetDef def;
     std::vector<TBlob> blobs;
@@ -426,8 +725,9 @@ int blob_of(fcnod_trainer* t, const std::string& n) {
     FCNOD_CHECK(it != t->blob_index.end(), "trainer: unknown blob '" + n + "'");
     return it->second;
 }
-float* bdata(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].data + b.c_off; }
-float* bdiff(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].diff + b.c_off; }
+char* bdata(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].data + (size_t)b.c_off * t->esz; }
+char* bdiff(fcnod_trainer* t, const TBlob& b) { return t->bufs[b.buf].diff + (size_t)b.c_off * t->esz; }
+template <typename T> T* as(char* p) { return reinterpret_cast<T*>(p); }
 TBlob& root_of(fcnod_trainer* t, int b) { return t->blobs[t->blobs[b].root >= 0 ? t->blobs[b].root : b]; }
 // first writer of a diff overwrites, later writers accumulate (Caffe's Split layer)
 int claim_diff(fcnod_trainer* t, int b) {
@@ -462,6 +762,8 @@ void verify_train_side(const NetDef& def, int num_classes, float bbox_loss_weigh
         }
     }
 }
+
+void build_tc(fcnod_trainer* t);
 
 void build_trainer(fcnod_trainer* t, const WeightMap& weights) {
     const NetDef& def = t->def;
@@ -583,8 +885,8 @@ void build_trainer(fcnod_trainer* t, const WeightMap& weights) {
     for (size_t i = 0; i < t->bufs.size(); ++i) {
         TBuf& b = t->bufs[i];
         const size_t n = (size_t)N * b.C * b.H * b.W;
-        b.data = dalloc<float>(t, n);
-        b.diff = dalloc<float>(t, n);
+        b.data = dalloc<char>(t, n * t->esz);
+        b.diff = dalloc<char>(t, n * t->esz);
     }
     // ---- parameters
     t->n_params = off;
@@ -618,9 +920,156 @@ void build_trainer(fcnod_trainer* t, const WeightMap& weights) {
     t->box_nchw = dalloc<float>(t, 4 * n1); t->dbox_nchw = dalloc<float>(t, 4 * n1);
     t->losses_dev = dalloc<float>(t, 2);
     t->head_scratch = dalloc<char>(t, fcnod_train_head_scratch_bytes());
+    if (t->prec == 1) build_tc(t);
 }
 
-void launch_conv(const float* in, int ldi, int H, int W, int Cin, const float* w, int ldw, const float* bias, float* out, int ldo,
+// ------------------------------------------------------------------------------------------------ tensor-core GEMM plans
+typedef CUresult (*EncodeTiledFnT)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFnT encode_tiled_fn() {
+    static EncodeTiledFnT fn = 0;
+    if (!fn) {
+        void* p = 0;
+        cudaDriverEntryPointQueryResult qres;
+        FCNOD_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+        FCNOD_CHECK(p && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = (EncodeTiledFnT)p;
+    }
+    return fn;
+}
+
+// 2-d bf16 tensor map: `inner` contiguous elements per row, `rows` rows `pitch` elements apart, box {64, box_rows}, SWIZZLE_128B
+void encode_2d(CUtensorMap* m, const void* base, long inner, long rows, long pitch, int box_rows, const char* what) {
+    FCNOD_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (pitch * 2) % 16 == 0, std::string("trainer: TMA operand not 16-byte aligned: ") + what);
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = encode_tiled_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FCNOD_CHECK(r == CUDA_SUCCESS, std::string("cuTensorMapEncodeTiled failed for ") + what + " (" + std::to_string((int)r) + ")");
+}
+
+int pow2_at_least(int v) { int p = 32; while (p < v) p <<= 1; return p; }
+
+void finish_plan(GemmPlan& g) {
+    GemmTcParams& p = g.p;
+    const size_t stage = (size_t)p.a_stage_bytes + p.b_stage_bytes;
+    p.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (200 * 1024) / stage));
+    p.tmem_cols = (uint32_t)pow2_at_least(2 * p.BN);
+    g.smem = (size_t)p.stages * stage + 16 * p.stages + 64 + 1024;
+    g.grid = std::min(p.tiles_m * p.tiles_n * p.splits, 148);
+}
+
+// D[M][N] = A[M][K] * B[N][K]^T (+ bias, ReLU, accumulate), all row-major with the given leading dimensions
+GemmPlan plan_gemm_k(const bf16* A, int lda, long M, int K, const bf16* B, int ldb, int N, void* out, int ldo, int out_f32,
+                     const float* bias, int relu, const char* what) {
+    GemmPlan g;
+    memset(&g.p, 0, sizeof g.p);
+    GemmTcParams& p = g.p;
+    p.M = (int)M; p.N = N; p.K = K;
+    const int nt = (N + 255) / 256;
+    p.BN = std::min(256, (((N + nt - 1) / nt) + 15) / 16 * 16);
+    p.tiles_m = (int)((M + 127) / 128); p.tiles_n = (N + p.BN - 1) / p.BN; p.splits = 1;
+    p.k_blocks = (K + 63) / 64; p.kb_per_split = p.k_blocks;
+    p.a_stage_bytes = 128 * 128; p.b_stage_bytes = (uint32_t)p.BN * 128;
+    p.out = out; p.ldo = ldo; p.out_f32 = out_f32; p.bias = bias; p.relu = relu; p.accum = 0;
+    encode_2d(&g.ta, A, K, M, lda, 128, what);
+    encode_2d(&g.tb, B, K, N, ldb, p.BN, what);
+    g.mn = false;
+    finish_plan(g);
+    return g;
+}
+
+// G[n][m] += sum_px A[px][m] * B[px][n]  (m < Mco, n < Ncols): the weight gradient, reduction over pixels, split over CTAs
+GemmPlan plan_gemm_mn(const bf16* A, int lda, int Mco, const bf16* B, int ldb, int Ncols, long PX, float* gout, int ldg,
+                      const char* what) {
+    GemmPlan g;
+    memset(&g.p, 0, sizeof g.p);
+    GemmTcParams& p = g.p;
+    p.M = Mco; p.N = Ncols; p.K = (int)PX;
+    const int nt = (Ncols + 255) / 256;
+    p.BN = std::min(256, (((Ncols + nt - 1) / nt) + 63) / 64 * 64);
+    p.tiles_m = (Mco + 127) / 128; p.tiles_n = (Ncols + p.BN - 1) / p.BN;
+    p.k_blocks = (int)((PX + kGemmPK - 1) / kGemmPK);
+    int splits = std::max(1, std::min(p.k_blocks, (148 * 2 + p.tiles_m * p.tiles_n - 1) / (p.tiles_m * p.tiles_n)));
+    p.kb_per_split = (p.k_blocks + splits - 1) / splits;
+    p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+    p.a_stage_bytes = 2 * kGemmPK * 128; p.b_stage_bytes = (uint32_t)(p.BN / 64) * kGemmPK * 128;
+    p.gout = gout; p.ldg = ldg;
+    encode_2d(&g.ta, A, Mco, PX, lda, kGemmPK, what);
+    encode_2d(&g.tb, B, Ncols, PX, ldb, kGemmPK, what);
+    g.mn = true;
+    finish_plan(g);
+    return g;
+}
+
+int add_plan(fcnod_trainer* t, const GemmPlan& g) {
+    t->gemms.push_back(g);
+    return (int)t->gemms.size() - 1;
+}
+
+void run_plan(const GemmPlan& g, int accum, cudaStream_t s) {
+    static bool attr = false;        // same value every time; a race writes the same thing twice
+    if (!attr) {
+        FCNOD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        FCNOD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr = true;
+    }
+    GemmTcParams p = g.p;
+    p.accum = accum;
+    if (g.mn) gemm_tc_kernel<true><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, p);
+    else gemm_tc_kernel<false><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, p);
+    FCNOD_CUDA(cudaGetLastError());
+}
+void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) { run_plan(t->gemms[id], accum, s); }
+
+// bf16 engine: scratch, bf16 weights and the three GEMM plans of every convolution (pointers are fixed for the trainer's life)
+void build_tc(fcnod_trainer* t) {
+    const int N = t->batch;
+    size_t col_elems = 8;
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        TLayer& L = t->layers[li];
+        if (L.def.type != L_CONV) continue;
+        TConv& c = t->convs[L.conv];
+        const TBlob& ib = t->blobs[L.in];
+        const TBlob& ob = t->blobs[L.out];
+        // tensor cores need 16-byte rows on both sides of the output view; the 1- and 4-channel heads stay on the SIMT kernels
+        c.tc = ob.ldc % 8 == 0 && ob.c_off % 8 == 0 && c.Cout % 8 == 0;
+        if (!c.tc) continue;
+        c.ldk = (c.K + 7) / 8 * 8;
+        if (!(c.k == 1 && c.stride == 1)) col_elems = std::max(col_elems, (size_t)N * ob.H * ob.W * c.ldk);
+    }
+    t->col = dalloc<bf16>(t, col_elems);
+    t->wb = dalloc<bf16>(t, t->n_params);
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        TLayer& L = t->layers[li];
+        if (L.def.type != L_CONV) continue;
+        TConv& c = t->convs[L.conv];
+        if (!c.tc) continue;
+        const TBlob& ib = t->blobs[L.in];
+        const TBlob& ob = t->blobs[L.out];
+        const long PX = (long)N * ob.H * ob.W;
+        const bool direct = c.k == 1 && c.stride == 1;
+        if (direct) FCNOD_CHECK(ib.ldc % 8 == 0 && ib.c_off % 8 == 0, "trainer: input view of '" + c.name + "' is not 16-byte aligned");
+        c.d_wf = dalloc<bf16>(t, (size_t)c.Cout * c.ldk);
+        const bf16* X = direct ? as<bf16>(bdata(t, ib)) : t->col;
+        const int ldx = direct ? ib.ldc : c.ldk;
+        c.g_fwd = add_plan(t, plan_gemm_k(X, ldx, PX, c.K, c.d_wf, c.ldk, c.Cout, bdata(t, ob), ob.ldc, 0, t->params + c.b_off, L.relu ? 1 : 0, c.name.c_str()));
+        c.g_wgrad = add_plan(t, plan_gemm_mn(as<bf16>(bdiff(t, ob)), ob.ldc, c.Cout, X, ldx, c.K, PX, t->grads + c.w_off, c.ldw, c.name.c_str()));
+        if (ib.needs_grad) {
+            // dY[px][Cout] * Wb[Kc][Cout]^T: straight into the bottom diff for 1x1, into the column scratch (then col2im) otherwise
+            FCNOD_CHECK(c.Cin % 8 == 0, "trainer: data gradient of '" + c.name + "' needs Cin % 8 == 0");
+            c.g_dgrad = add_plan(t, plan_gemm_k(as<bf16>(bdiff(t, ob)), ob.ldc, PX, c.Cout, t->wb + c.w_off, c.ldw, c.K,
+                                    direct ? (void*)bdiff(t, ib) : (void*)t->col, direct ? ib.ldc : c.ldk, 0, 0, 0, c.name.c_str()));
+        }
+    }
+}
+
+template <typename TI, typename TO>
+void launch_conv(const void* in, int ldi, int H, int W, int Cin, const float* w, int ldw, const float* bias, void* out, int ldo,
                  int Ho, int Wo, int Cout, int N, int k, int stride, int pad, int relu, int accum, cudaStream_t s) {
     ConvSimtParams p;
     p.in = in; p.w = w; p.bias = bias; p.out = out;
@@ -629,12 +1078,33 @@ void launch_conv(const float* in, int ldi, int H, int W, int Cin, const float* w
     p.kh = p.kw = k; p.stride = stride; p.pad = pad; p.relu = relu; p.accum = accum;
     const long M = (long)N * Ho * Wo;
     dim3 grid((unsigned)((M + 63) / 64), (unsigned)(ldw / 64));
-    conv_simt_kernel<float, float><<<grid, 256, 0, s>>>(p);
+    conv_simt_kernel<TI, TO><<<grid, 256, 0, s>>>(p);
     FCNOD_CUDA(cudaGetLastError());
 }
 
+void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
+    const long PX = (long)t->batch * ob.H * ob.W;
+    const bf16* x = as<bf16>(bdata(t, ib));
+    if (c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0)
+        im2col_kernel<8><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, t->col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
+    else
+        im2col_kernel<1><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, t->col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
+    FCNOD_CUDA(cudaGetLastError());
+}
+
+template <typename T>
 void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
     const int N = t->batch;
+    const bool tcp = sizeof(T) == 2;
+    if (tcp) {
+        // bf16 copies of the (just updated) parameters
+        cast_flat_kernel<<<grid1((long)t->n_params, 256), 256, 0, s>>>(t->params, t->wb, (long)t->n_params);
+        for (size_t ci = 0; ci < t->convs.size(); ++ci) {
+            const TConv& c = t->convs[ci];
+            if (c.tc) pack_wf_kernel<<<grid1((long)c.Cout * c.ldk, 256), 256, 0, s>>>(t->params + c.w_off, c.ldw, c.d_wf, c.ldk, c.K, c.Cout);
+        }
+        FCNOD_CUDA(cudaGetLastError());
+    }
     for (size_t li = 0; li < t->layers.size(); ++li) {
         TLayer& L = t->layers[li];
         if (L.skip) continue;
@@ -643,32 +1113,44 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
         const long in_px = (long)N * ib.H * ib.W, out_px = (long)N * ob.H * ob.W;
         switch (L.def.type) {
         case L_POWER:
-            nchw_to_nhwc_power_kernel<<<grid1(in_px * ib.C, 256), 256, 0, s>>>(data_nchw, bdata(t, ob), N, ib.C, ib.H, ib.W, L.def.scale, L.def.shift);
+            nchw_to_nhwc_power_kernel<T><<<grid1(in_px * ib.C, 256), 256, 0, s>>>(data_nchw, as<T>(bdata(t, ob)), N, ib.C, ib.H, ib.W, L.def.scale, L.def.shift);
             break;
         case L_CONV: {
             const TConv& c = t->convs[L.conv];
-            launch_conv(bdata(t, ib), ib.ldc, ib.H, ib.W, c.Cin, t->params + c.w_off, c.ldw, t->params + c.b_off, bdata(t, ob), ob.ldc,
-                        ob.H, ob.W, c.Cout, N, c.k, c.stride, c.pad, L.relu ? 1 : 0, 0, s);
+            if (tcp && c.tc) {
+                if (!(c.k == 1 && c.stride == 1)) launch_im2col(t, c, ib, ob, s);
+                run_gemm(t, c.g_fwd, 0, s);
+            } else {
+                launch_conv<T, T>(bdata(t, ib), ib.ldc, ib.H, ib.W, c.Cin, t->params + c.w_off, c.ldw, t->params + c.b_off, bdata(t, ob), ob.ldc,
+                                  ob.H, ob.W, c.Cout, N, c.k, c.stride, c.pad, L.relu ? 1 : 0, 0, s);
+            }
             break;
         }
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
-            pool_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), bdata(t, ob), L.idx, g);
+            if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
+                pool_fwd8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g);
+            else
+                pool_fwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), as<T>(bdata(t, ob)), L.idx, g);
             break;
         }
         case L_LRN:
-            lrn_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), ib.ldc, bdata(t, ob), ob.ldc, L.scale, out_px, ob.C,
-                                                                      L.def.local_size, L.def.alpha / (float)L.def.local_size, L.def.beta, L.def.lrn_k);
+            if (tcp && L.def.local_size == 5 && ob.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
+                lrn_fwd8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ib)), ib.ldc, as<bf16>(bdata(t, ob)), ob.ldc, L.scale, out_px,
+                                                                                 ob.C, L.def.alpha / 5.f, L.def.beta, L.def.lrn_k);
+            else
+                lrn_fwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), ib.ldc, as<T>(bdata(t, ob)), ob.ldc, L.scale, out_px, ob.C,
+                                                                             L.def.local_size, L.def.alpha / (float)L.def.local_size, L.def.beta, L.def.lrn_k);
             break;
         case L_DROPOUT: {
             const long n = out_px * ob.C;
             if (t->solver.dropout_ratio_override >= 0.f) L.def.dropout_ratio = t->solver.dropout_ratio_override;
             dropout_mask_kernel<<<grid1(n, 256), 256, 0, s>>>(L.mask, n, t->solver.seed, (uint64_t)t->iter, L.def.dropout_ratio);
-            dropout_apply_kernel<<<grid1(n, 256), 256, 0, s>>>(bdata(t, ib), L.mask, bdata(t, ob), n, 1.f / (1.f - L.def.dropout_ratio), 0);
+            dropout_apply_kernel<T><<<grid1(n, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), L.mask, as<T>(bdata(t, ob)), n, 1.f / (1.f - L.def.dropout_ratio), 0);
             break;
         }
         case L_SIGMOID:
-            sigmoid_fwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), bdata(t, ob), out_px * ob.C);
+            sigmoid_fwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), as<T>(bdata(t, ob)), out_px * ob.C);
             break;
         default:
             FCNOD_CHECK(false, "trainer: layer type '" + L.def.type_name + "' has no training forward");
@@ -677,8 +1159,10 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
     }
 }
 
+template <typename T>
 void backward(fcnod_trainer* t, cudaStream_t s) {
     const int N = t->batch;
+    const bool tcp = sizeof(T) == 2;
     for (size_t b = 0; b < t->blobs.size(); ++b) t->blobs[b].diff_written = false;
     root_of(t, t->cov_blob).diff_written = true;      // written by the head
     root_of(t, t->box_blob).diff_written = true;
@@ -691,42 +1175,72 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
         if (!root_of(t, L.out).diff_written) {
             // nothing consumed this top (not the case in train_val.prototxt): its gradient is zero
             FCNOD_CHECK(ob.ldc == ob.C, "trainer: unconsumed sliced blob");
-            FCNOD_CUDA(cudaMemsetAsync(bdiff(t, ob), 0, (size_t)out_px * ob.C * 4, s));
+            FCNOD_CUDA(cudaMemsetAsync(bdiff(t, ob), 0, (size_t)out_px * ob.C * sizeof(T), s));
             root_of(t, L.out).diff_written = true;
         }
         switch (L.def.type) {
         case L_POWER:
             break;
         case L_SIGMOID:
-            sigmoid_bwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ob), bdiff(t, ob), bdiff(t, ib), out_px * ob.C, claim_diff(t, L.in));
+            sigmoid_bwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ob)), as<T>(bdiff(t, ob)), as<T>(bdiff(t, ib)), out_px * ob.C,
+                                                                             claim_diff(t, L.in));
             break;
         case L_DROPOUT: {
             const long n = out_px * ob.C;
-            dropout_apply_kernel<<<grid1(n, 256), 256, 0, s>>>(bdiff(t, ob), L.mask, bdiff(t, ib), n, 1.f / (1.f - L.def.dropout_ratio), claim_diff(t, L.in));
+            dropout_apply_kernel<T><<<grid1(n, 256), 256, 0, s>>>(as<T>(bdiff(t, ob)), L.mask, as<T>(bdiff(t, ib)), n, 1.f / (1.f - L.def.dropout_ratio),
+                                                                   claim_diff(t, L.in));
             break;
         }
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
-            pool_bwd_kernel<<<grid1(in_px * ib.C, 256), 256, 0, s>>>(bdiff(t, ob), L.idx, bdiff(t, ib), g, claim_diff(t, L.in));
+            if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
+                pool_bwd8_kernel<<<grid1(in_px * (ib.C / 8), 256), 256, 0, s>>>(as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g, claim_diff(t, L.in));
+            else
+                pool_bwd_kernel<T><<<grid1(in_px * ib.C, 256), 256, 0, s>>>(as<T>(bdiff(t, ob)), L.idx, as<T>(bdiff(t, ib)), g, claim_diff(t, L.in));
             break;
         }
         case L_LRN:
-            lrn_bwd_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ib), ib.ldc, bdata(t, ob), bdiff(t, ob), ob.ldc, L.scale, bdiff(t, ib),
-                                                                      out_px, ob.C, L.def.local_size, L.def.alpha / (float)L.def.local_size, L.def.beta,
-                                                                      claim_diff(t, L.in));
+            if (tcp && L.def.local_size == 5 && ob.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
+                lrn_bwd8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ib)), ib.ldc, as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)),
+                                                                                 ob.ldc, L.scale, as<bf16>(bdiff(t, ib)), out_px, ob.C, L.def.alpha / 5.f, L.def.beta,
+                                                                                 claim_diff(t, L.in));
+            else
+                lrn_bwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), ib.ldc, as<T>(bdata(t, ob)), as<T>(bdiff(t, ob)), ob.ldc, L.scale,
+                                                                             as<T>(bdiff(t, ib)), out_px, ob.C, L.def.local_size,
+                                                                             L.def.alpha / (float)L.def.local_size, L.def.beta, claim_diff(t, L.in));
             break;
         case L_CONV: {
             const TConv& c = t->convs[L.conv];
-            float* dy = bdiff(t, ob);
+            T* dy = as<T>(bdiff(t, ob));
             if (L.relu) {
-                relu_mask_kernel<<<grid1(out_px * ob.C, 256), 256, 0, s>>>(bdata(t, ob), dy, out_px, ob.C, ob.ldc);
+                if (tcp && ob.C % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
+                    relu_mask8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), out_px, ob.C, ob.ldc);
+                else
+                    relu_mask_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ob)), dy, out_px, ob.C, ob.ldc);
                 FCNOD_CUDA(cudaGetLastError());
             }
             {   // bias
                 const long chunk = std::max<long>(256, (out_px + 147) / 148);
                 dim3 grid((unsigned)((c.Cout + 31) / 32), (unsigned)((out_px + chunk - 1) / chunk));
-                bias_grad_kernel<<<grid, dim3(32, 8), 0, s>>>(dy, ob.ldc, c.Cout, out_px, chunk, t->grads + c.b_off);
+                bias_grad_kernel<T><<<grid, dim3(32, 8), 0, s>>>(dy, ob.ldc, c.Cout, out_px, chunk, t->grads + c.b_off);
                 FCNOD_CUDA(cudaGetLastError());
+            }
+            if (tcp && c.tc) {
+                const bool direct = c.k == 1 && c.stride == 1;
+                if (!direct) launch_im2col(t, c, ib, ob, s);
+                run_gemm(t, c.g_wgrad, 0, s);
+                if (ib.needs_grad) {
+                    const int accum = claim_diff(t, L.in);
+                    if (direct) {
+                        run_gemm(t, c.g_dgrad, accum, s);
+                    } else {
+                        run_gemm(t, c.g_dgrad, 0, s);         // column gradient into the scratch
+                        col2im_kernel<<<grid1(in_px * (c.Cin / 8), 256), 256, 0, s>>>(t->col, c.ldk, as<bf16>(bdiff(t, ib)), ib.ldc, N, ib.H, ib.W, c.Cin,
+                                                                                       c.k, c.pad, accum);
+                        FCNOD_CUDA(cudaGetLastError());
+                    }
+                }
+                break;
             }
             {   // weights
                 WgradParams p;
@@ -740,14 +1254,14 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
                 p.chunk = ((out_px + nz - 1) / nz + 15) / 16 * 16;
                 nz = (out_px + p.chunk - 1) / p.chunk;
                 dim3 grid((unsigned)((c.K + 63) / 64), (unsigned)(c.ldw / 64), (unsigned)nz);
-                wgrad_simt_kernel<<<grid, 256, 0, s>>>(p);
+                wgrad_simt_kernel<T><<<grid, 256, 0, s>>>(p);
                 FCNOD_CUDA(cudaGetLastError());
             }
             if (ib.needs_grad) {
                 dgrad_pack_kernel<<<grid1((long)c.k * c.k * c.Cout * c.ldt, 256), 256, 0, s>>>(t->params + c.w_off, c.ldw, c.d_wt, c.ldt, c.Cin, c.Cout, c.k);
                 FCNOD_CUDA(cudaGetLastError());
-                launch_conv(dy, ob.ldc, ob.H, ob.W, c.Cout, c.d_wt, c.ldt, 0, bdiff(t, ib), ib.ldc, ib.H, ib.W, c.Cin, N, c.k, 1, c.k - 1 - c.pad, 0,
-                            claim_diff(t, L.in), s);
+                launch_conv<T, T>(dy, ob.ldc, ob.H, ob.W, c.Cout, c.d_wt, c.ldt, 0, bdiff(t, ib), ib.ldc, ib.H, ib.W, c.Cin, N, c.k, 1, c.k - 1 - c.pad, 0,
+                                  claim_diff(t, L.in), s);
             }
             break;
         }
@@ -767,7 +1281,7 @@ int fcnod_solver_defaults(fcnod_solver_params* p) {
     FCNOD_CHECK(p, "null argument");
     // /root/reference/train/bounding_box/solver.prototxt:3-15 (+ caffe.proto defaults for momentum2 / delta)
     p->base_lr = 1e-4f; p->gamma = 0.1f; p->stepsize = 10000; p->momentum = 0.9f; p->momentum2 = 0.999f; p->delta = 1e-8f;
-    p->weight_decay = 1e-7f; p->bbox_loss_weight = 2.0f; p->dropout_ratio_override = -1.f; p->seed = 1;
+    p->weight_decay = 1e-7f; p->bbox_loss_weight = 2.0f; p->dropout_ratio_override = -1.f; p->seed = 1; p->precision = 0; p->reserved = 0;
     FCNOD_API_END
 }
 
@@ -784,6 +1298,8 @@ int fcnod_trainer_create(const char* prototxt_path, const char* caffemodel_path,
     try {
         t->device = device; t->batch = batch; t->in_h = height; t->in_w = width;
         if (solver) t->solver = *solver; else fcnod_solver_defaults(&t->solver);
+        FCNOD_CHECK(t->solver.precision == 0 || t->solver.precision == 1, "trainer: precision must be 0 (float32) or 1 (bf16)");
+        t->prec = t->solver.precision; t->esz = t->prec ? 2 : 4;
         t->def = parse_prototxt_file(prototxt_path, true);
         if (t->def.input_dims[1] > 0) t->in_c = t->def.input_dims[1];
         WeightMap weights = read_caffemodel(caffemodel_path);
@@ -837,20 +1353,30 @@ int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, c
     cudaStream_t s = (cudaStream_t)stream;      // NULL = the legacy default stream, as everywhere in this ABI
     const int N = t->batch, C = t->num_classes;
     FCNOD_CUDA(cudaMemsetAsync(t->grads, 0, t->n_params * 4, s));
-    forward(t, data, s);
+    if (t->prec) forward<bf16>(t, data, s); else forward<float>(t, data, s);
     const TBlob& cb = t->blobs[t->cov_blob];
     const TBlob& bb = t->blobs[t->box_blob];
     const long n1 = (long)N * C * t->gh * t->gw;
-    nhwc_to_nchw_kernel<<<grid1(n1, 256), 256, 0, s>>>(bdata(t, cb), cb.ldc, t->cov_nchw, N, C, t->gh, t->gw);
-    nhwc_to_nchw_kernel<<<grid1(4 * n1, 256), 256, 0, s>>>(bdata(t, bb), bb.ldc, t->box_nchw, N, 4 * C, t->gh, t->gw);
+    if (t->prec) {
+        nhwc_to_nchw_kernel<bf16><<<grid1(n1, 256), 256, 0, s>>>(as<bf16>(bdata(t, cb)), cb.ldc, t->cov_nchw, N, C, t->gh, t->gw);
+        nhwc_to_nchw_kernel<bf16><<<grid1(4 * n1, 256), 256, 0, s>>>(as<bf16>(bdata(t, bb)), bb.ldc, t->box_nchw, N, 4 * C, t->gh, t->gw);
+    } else {
+        nhwc_to_nchw_kernel<float><<<grid1(n1, 256), 256, 0, s>>>(as<float>(bdata(t, cb)), cb.ldc, t->cov_nchw, N, C, t->gh, t->gw);
+        nhwc_to_nchw_kernel<float><<<grid1(4 * n1, 256), 256, 0, s>>>(as<float>(bdata(t, bb)), bb.ldc, t->box_nchw, N, 4 * C, t->gh, t->gw);
+    }
     FCNOD_CUDA(cudaGetLastError());
     int rc = fcnod_train_head_forward_device(t->cov_nchw, t->box_nchw, cvg_label, bbox_label, size_block, obj_block, cvg_block, N, C, t->gh,
                                              t->gw, t->solver.bbox_loss_weight, t->losses_dev, t->dcov_nchw, t->dbox_nchw, t->head_scratch, s);
     FCNOD_CHECK(rc == 0, fcnod_last_error());
-    nchw_to_nhwc_kernel<<<grid1(n1, 256), 256, 0, s>>>(t->dcov_nchw, bdiff(t, cb), cb.ldc, N, C, t->gh, t->gw);
-    nchw_to_nhwc_kernel<<<grid1(4 * n1, 256), 256, 0, s>>>(t->dbox_nchw, bdiff(t, bb), bb.ldc, N, 4 * C, t->gh, t->gw);
+    if (t->prec) {
+        nchw_to_nhwc_kernel<bf16><<<grid1(n1, 256), 256, 0, s>>>(t->dcov_nchw, as<bf16>(bdiff(t, cb)), cb.ldc, N, C, t->gh, t->gw);
+        nchw_to_nhwc_kernel<bf16><<<grid1(4 * n1, 256), 256, 0, s>>>(t->dbox_nchw, as<bf16>(bdiff(t, bb)), bb.ldc, N, 4 * C, t->gh, t->gw);
+    } else {
+        nchw_to_nhwc_kernel<float><<<grid1(n1, 256), 256, 0, s>>>(t->dcov_nchw, as<float>(bdiff(t, cb)), cb.ldc, N, C, t->gh, t->gw);
+        nchw_to_nhwc_kernel<float><<<grid1(4 * n1, 256), 256, 0, s>>>(t->dbox_nchw, as<float>(bdiff(t, bb)), bb.ldc, N, 4 * C, t->gh, t->gw);
+    }
     FCNOD_CUDA(cudaGetLastError());
-    backward(t, s);
+    if (t->prec) backward<bf16>(t, s); else backward<float>(t, s);
     FCNOD_API_END
 }
 
@@ -963,12 +1489,29 @@ int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which, int d
     FCNOD_CUDA(cudaDeviceSynchronize());
     float* tmp = 0;
     FCNOD_CUDA(cudaMalloc((void**)&tmp, n * 4));
-    nhwc_to_nchw_kernel<<<grid1((long)n, 256), 256, 0, t->stream>>>(which == 0 ? bdata(t, b) : bdiff(t, b), b.ldc, tmp, t->batch, b.C, b.H, b.W);
+    char* src = which == 0 ? bdata(t, b) : bdiff(t, b);
+    if (t->prec) nhwc_to_nchw_kernel<bf16><<<grid1((long)n, 256), 256, 0, t->stream>>>(as<bf16>(src), b.ldc, tmp, t->batch, b.C, b.H, b.W);
+    else nhwc_to_nchw_kernel<float><<<grid1((long)n, 256), 256, 0, t->stream>>>(as<float>(src), b.ldc, tmp, t->batch, b.C, b.H, b.W);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, n * 4, cudaMemcpyDeviceToHost, t->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
     cudaFree(tmp);
     FCNOD_CUDA(e);
+    FCNOD_API_END
+}
+
+// The tensor-core GEMM of the bf16 engine on caller-provided device matrices (bf16, row-major with leading dimensions):
+//   mode 0: out[M][N] (bf16, or float32 if out_f32) (+)= A[M][K] * B[N][K]^T (+ bias[N]) (ReLU)        forward / data gradient
+//   mode 1: gout[n * ldo + m] (float32) += sum_k A[k][m] * B[k][n], m < M, n < N                         weight gradient
+int fcnod_gemm_bf16_device(int mode, const void* A, int lda, const void* B, int ldb, int M, int N, int K, void* out, int ldo,
+                           int out_f32, const float* bias, int relu, int accum, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(A && B && out && M > 0 && N > 0 && K > 0 && (mode == 0 || mode == 1), "gemm: bad argument");
+    GemmPlan g = mode == 0 ? plan_gemm_k(static_cast<const bf16*>(A), lda, M, K, static_cast<const bf16*>(B), ldb, N, out, ldo, out_f32, bias,
+                                         relu, "fcnod_gemm_bf16_device")
+                           : plan_gemm_mn(static_cast<const bf16*>(A), lda, M, static_cast<const bf16*>(B), ldb, N, K, static_cast<float*>(out),
+                                          ldo, "fcnod_gemm_bf16_device");
+    run_plan(g, accum, (cudaStream_t)stream);
     FCNOD_API_END
 }
 

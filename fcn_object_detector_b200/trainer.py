@@ -63,7 +63,9 @@ class _DeviceArray(object):
 
 
 class Solver(object):
-    def __init__(self, prototxt, caffemodel, batch, height=448, width=448, device=0, solver_prototxt=None, seed=1, **overrides):
+    def __init__(self, prototxt, caffemodel, batch, height=448, width=448, device=0, solver_prototxt=None, seed=1, precision='fp32',
+                 **overrides):
+        """precision: 'fp32' (parity engine) or 'bf16' (tensor cores: bf16 activations and gradients, fp32 master weights)."""
         L = _lib.lib()
         sp = _lib.SolverParams()
         _lib.check(L.fcnod_solver_defaults(C.byref(sp)))
@@ -76,6 +78,8 @@ class Solver(object):
                 raise TypeError('unknown solver parameter %r' % k)
             setattr(sp, k, v)
         sp.seed = seed
+        sp.precision = {'fp32': 0, 'bf16': 1}[precision]
+        self.precision = precision
         self.params = sp
         self.handle = C.c_void_p()
         _lib.check(L.fcnod_trainer_create(str(prototxt).encode(), str(caffemodel).encode(), device, batch, height, width,

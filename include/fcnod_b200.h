@@ -325,6 +325,9 @@ typedef struct fcnod_solver_params {
     float bbox_loss_weight;          /* loss_weight of bbox_loss (train_val.prototxt:2273) */
     float dropout_ratio_override;    /* < 0: the prototxt's dropout_ratio; 0 switches dropout off */
     uint64_t seed;                   /* dropout masks are a function of (seed, iteration, element) */
+    int32_t precision;               /* 0: float32 storage, SIMT convolutions (parity engine, 1e-4); 1: bf16 storage with fp32
+                                        master weights, convolutions as tcgen05 GEMMs (forward, dgrad, wgrad), fp32 accumulation */
+    int32_t reserved;
 } fcnod_solver_params;
 int fcnod_solver_defaults(fcnod_solver_params* p);   /* the values of train/bounding_box/solver.prototxt */
 int fcnod_trainer_create(const char* prototxt_path, const char* caffemodel_path, int device, int batch, int height, int width,
@@ -345,6 +348,12 @@ int fcnod_trainer_param_read(fcnod_trainer* t, const char* layer, int index, int
 const char* fcnod_trainer_param_layer(const fcnod_trainer* t, int i);   /* i-th convolution's name, NULL past the end */
 int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which /* 0 data, 1 diff */, int dims[3], float* out, size_t count);
 int fcnod_trainer_dropout_mask(fcnod_trainer* t, uint8_t* out /* [N][C][H][W] */, size_t count, int dims[3]);
+/* The tcgen05 GEMM of the bf16 training engine on caller-provided DEVICE matrices (bf16, row-major, leading dimensions in
+ * elements, rows 16-byte aligned).  No counterpart in the reference (it delegates to cuBLAS / cuDNN through Caffe).
+ *   mode 0: out[M][N] (bf16, or float32 if out_f32) (+)= A[M][K] * B[N][K]^T (+ bias[N]) (ReLU)
+ *   mode 1: out[n * ldo + m] (float32) += sum_k A[k][m] * B[k][n]   (reduction over the rows: the weight-gradient form) */
+int fcnod_gemm_bf16_device(int mode, const void* A, int lda, const void* B, int ldb, int M, int N, int K, void* out, int ldo,
+                           int out_f32, const float* bias, int relu, int accum, void* stream);
 /* argmax of a Pooling layer's last forward: dh * k + dw inside the unclipped window, [N][C][Ho][Wo] uint8 */
 int fcnod_trainer_pool_argmax(fcnod_trainer* t, const char* layer, uint8_t* out, size_t count, int dims[3]);
 
