@@ -10,8 +10,8 @@
 //             groups SBO = 1024 bytes apart), and the instruction descriptor sets a_major = b_major = 1.
 //             The pixel range is split over CTAs (split-K); partial tiles are added to the fp32 gradient with red.global.
 // X_col is the activation matrix itself for 1x1 convolutions and an im2col matrix (bf16, written by im2col_kernel) for
-// k x k ones.  One CTA = 6 warps: warp 0 TMA producer, warp 1 MMA issuer (+ TMEM allocation), warps 2..5 epilogue (one TMEM
-// lane quadrant each).  Persistent over output tiles, two accumulators in TMEM so the epilogue of a tile overlaps the MMAs
+// k x k ones.  One CTA = 10 warps: warp 0 TMA producer, warp 1 MMA issuer (+ TMEM allocation), warps 2..9 epilogue (two per
+// TMEM lane quadrant, alternate 16-column chunks).  Persistent over output tiles, two accumulators in TMEM so the epilogue of a tile overlaps the MMAs
 // of the next.
 #pragma once
 #include <cuda.h>
@@ -37,7 +37,13 @@ struct GemmTcParams {
     float* gout; int ldg;                 // gout[n * ldg + m] += D[m][n]
 };
 
-constexpr int kGemmThreads = 192;
+// tcgen05.wait::ld that also names the 16 destination registers of the load it completes: the compiler must treat them as
+// written HERE, not at the (asynchronous) tcgen05.ld, so it cannot read or move them in between
+__device__ __forceinline__ void gemm_ld_wait16(uint32_t* r) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
+}
+
+constexpr int kGemmThreads = 320;       // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kGemmPK = 64;               // pixels per reduction block of the MN-major form
 
 template <bool MNMAJ>
@@ -54,7 +60,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -139,34 +145,42 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
         }
     } else {
-        // ================================================================== epilogue: 4 warps, TMEM lane quadrant = warp % 4
-        const int q = warp & 3;
+        // ================================================================== epilogue: 8 warps, TMEM lane quadrant = warp % 4,
+        // the two warps of a quadrant take alternate 16-column chunks.  The accumulator chunk and (accumulate mode) the old
+        // output values of the NEXT chunk are requested before the current one is processed: the loop is latency-bound.
+        const int q = warp & 3, half = (warp - 2) >> 2;
         uint32_t it = 0;
         for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
             const int tn = w % p.tiles_n, tm = (w / p.tiles_n) % p.tiles_m;
             const int m0 = tm * 128, n0 = tn * p.BN;
             const uint32_t acc = it & 1u, acc_ph = (it >> 1) & 1u;
-            mbar_wait(tfull0 + 8u * acc, acc_ph);
-            fence_after();
             const int row = m0 + q * 32 + lane;
-            const uint32_t taddr = tmem_base + acc * (uint32_t)p.BN + ((uint32_t)(q * 32) << 16);
-            for (int c0 = 0; c0 < p.BN; c0 += 16) {
-                uint32_t r[16];
-                tmem_ld16(taddr + (uint32_t)c0, r);
-                tmem_ld_wait();
-                const int n = n0 + c0;
-                if (n >= p.N) continue;
+            const bool row_ok = row < p.M;
+            const int n_chunks = (min(p.BN, p.N - n0) + 15) / 16;          // chunks that hold at least one column < N
+            const bool rmw = !MNMAJ && p.accum && !p.out_f32 && row_ok;
+            bf16* orow = MNMAJ ? (bf16*)0 : static_cast<bf16*>(p.out) + (long)row * p.ldo + n0;
+            const bool vec_ok = !MNMAJ && !p.out_f32 && ((reinterpret_cast<uintptr_t>(orow) & 15) == 0);
+            uint4 oldA[2], oldB[2];
+            uint32_t rA[16], rB[16];
+            auto prefetch_old = [&](uint4 (&o)[2], int ch) {
+                if (rmw && vec_ok && n0 + 16 * ch + 16 <= p.N) {
+                    o[0] = reinterpret_cast<const uint4*>(orow + 16 * ch)[0];
+                    o[1] = reinterpret_cast<const uint4*>(orow + 16 * ch)[1];
+                }
+            };
+            auto process = [&](const uint32_t (&rr)[16], const uint4 (&oldv)[2], int ch) {
+                const int c0 = 16 * ch, n = n0 + c0;
                 if (MNMAJ) {
-                    if (row < p.M) {
+                    if (row_ok) {
 #pragma unroll
                         for (int j = 0; j < 16; ++j)
-                            if (n + j < p.N) atomicAdd(p.gout + (long)(n + j) * p.ldg + row, __uint_as_float(r[j]));
+                            if (n + j < p.N) atomicAdd(p.gout + (long)(n + j) * p.ldg + row, __uint_as_float(rr[j]));
                     }
-                } else if (row < p.M) {
+                } else if (row_ok) {
                     float v[16];
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
-                        v[j] = __uint_as_float(r[j]);
+                        v[j] = __uint_as_float(rr[j]);
                         if (p.bias && n + j < p.N) v[j] += p.bias[n + j];
                         if (p.relu) v[j] = fmaxf(v[j], 0.f);
                     }
@@ -177,15 +191,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         for (int j = 0; j < 16; ++j)
                             if (full || n + j < p.N) o[j] = p.accum ? o[j] + v[j] : v[j];
                     } else {
-                        bf16* o = static_cast<bf16*>(p.out) + (long)row * p.ldo + n;
-                        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+                        bf16* o = orow + c0;
+                        if (full && vec_ok) {
                             uint4 w4[2];
                             if (p.accum) {
-                                w4[0] = reinterpret_cast<const uint4*>(o)[0];
-                                w4[1] = reinterpret_cast<const uint4*>(o)[1];
-                                const bf16* old = reinterpret_cast<const bf16*>(w4);
+                                const bf16* ov = reinterpret_cast<const bf16*>(oldv);
 #pragma unroll
-                                for (int j = 0; j < 16; ++j) v[j] += __bfloat162float(old[j]);
+                                for (int j = 0; j < 16; ++j) v[j] += __bfloat162float(ov[j]);
                             }
                             __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(w4);
 #pragma unroll
@@ -198,6 +210,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                 if (n + j < p.N) o[j] = __float2bfloat16_rn(p.accum ? __bfloat162float(o[j]) + v[j] : v[j]);
                         }
                     }
+                }
+            };
+            if (half < n_chunks) prefetch_old(oldA, half);
+            mbar_wait(tfull0 + 8u * acc, acc_ph);
+            fence_after();
+            const uint32_t taddr = tmem_base + acc * (uint32_t)p.BN + ((uint32_t)(q * 32) << 16);
+            if (half < n_chunks) tmem_ld16(taddr + 16u * half, rA);
+            for (int ch = half; ch < n_chunks; ch += 4) {
+                gemm_ld_wait16(rA);
+                if (ch + 2 < n_chunks) { tmem_ld16(taddr + 16u * (ch + 2), rB); prefetch_old(oldB, ch + 2); }
+                process(rA, oldA, ch);
+                if (ch + 2 < n_chunks) {
+                    gemm_ld_wait16(rB);
+                    if (ch + 4 < n_chunks) { tmem_ld16(taddr + 16u * (ch + 4), rA); prefetch_old(oldA, ch + 4); }
+                    process(rB, oldB, ch + 2);
                 }
             }
             fence_before();

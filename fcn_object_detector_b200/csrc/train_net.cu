@@ -660,6 +660,7 @@ struct TConv {
     // bf16 engine (tensor cores): transposed bf16 weights [Cout][ldk] (forward B operand), im2col row pitch, GEMM plans
     bool tc = false;
     bf16* d_wf = 0;
+    bf16* d_col = 0;                 // k x k: this layer's im2col matrix, written by the forward and kept for the weight gradient
     int ldk = 0;
     int g_fwd = -1, g_dgrad = -1, g_wgrad = -1;
     float lr_mult[2], decay_mult[2];
@@ -689,7 +690,7 @@ struct fcnod_trainer {
     int prec = 0;                             // 0: float32 storage, SIMT convolutions; 1: bf16 storage, tcgen05 GEMMs
     size_t esz = 4;
     bf16* wb = 0;                             // bf16 copy of the flat parameter buffer
-    bf16* col = 0;                            // im2col / column-gradient scratch
+    bf16* col = 0;                            // column-gradient scratch of the k x k data gradients (shared)
     std::vector<GemmPlan> gemms;
     fcnod_solver_params solver;
     NetDef def;
@@ -1055,7 +1056,8 @@ void build_tc(fcnod_trainer* t) {
         const bool direct = c.k == 1 && c.stride == 1;
         if (direct) FCNOD_CHECK(ib.ldc % 8 == 0 && ib.c_off % 8 == 0, "trainer: input view of '" + c.name + "' is not 16-byte aligned");
         c.d_wf = dalloc<bf16>(t, (size_t)c.Cout * c.ldk);
-        const bf16* X = direct ? as<bf16>(bdata(t, ib)) : t->col;
+        if (!direct) c.d_col = dalloc<bf16>(t, (size_t)PX * c.ldk);
+        const bf16* X = direct ? as<bf16>(bdata(t, ib)) : c.d_col;
         const int ldx = direct ? ib.ldc : c.ldk;
         c.g_fwd = add_plan(t, plan_gemm_k(X, ldx, PX, c.K, c.d_wf, c.ldk, c.Cout, bdata(t, ob), ob.ldc, 0, t->params + c.b_off, L.relu ? 1 : 0, c.name.c_str()));
         c.g_wgrad = add_plan(t, plan_gemm_mn(as<bf16>(bdiff(t, ob)), ob.ldc, c.Cout, X, ldx, c.K, PX, t->grads + c.w_off, c.ldw, c.name.c_str()));
@@ -1086,9 +1088,9 @@ void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlo
     const long PX = (long)t->batch * ob.H * ob.W;
     const bf16* x = as<bf16>(bdata(t, ib));
     if (c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0)
-        im2col_kernel<8><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, t->col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
+        im2col_kernel<8><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, c.d_col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
     else
-        im2col_kernel<1><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, t->col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
+        im2col_kernel<1><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, c.d_col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
     FCNOD_CUDA(cudaGetLastError());
 }
 
@@ -1227,8 +1229,7 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
             }
             if (tcp && c.tc) {
                 const bool direct = c.k == 1 && c.stride == 1;
-                if (!direct) launch_im2col(t, c, ib, ob, s);
-                run_gemm(t, c.g_wgrad, 0, s);
+                run_gemm(t, c.g_wgrad, 0, s);            // (k x k: on the im2col matrix the forward left in c.d_col)
                 if (ib.needs_grad) {
                     const int accum = claim_diff(t, L.in);
                     if (direct) {
