@@ -958,9 +958,10 @@ int pow2_at_least(int v) { int p = 32; while (p < v) p <<= 1; return p; }
 void finish_plan(GemmPlan& g) {
     GemmTcParams& p = g.p;
     const size_t stage = (size_t)p.a_stage_bytes + p.b_stage_bytes;
-    p.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (200 * 1024) / stage));
+    p.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (192 * 1024) / stage));
     p.tmem_cols = (uint32_t)pow2_at_least(2 * p.BN);
-    g.smem = (size_t)p.stages * stage + 16 * p.stages + 64 + 1024;
+    g.smem = (size_t)p.stages * stage + 16 * p.stages + 64 + 1024 + kGemmBiasMax * 4;
+    FCNOD_CHECK(!p.bias || p.N <= 1024, "gemm: a bias needs N <= 1024");
     g.grid = std::min(p.tiles_m * p.tiles_n * p.splits, 148);
 }
 
