@@ -2,8 +2,8 @@
 the two losses (/root/reference/models/train_val.prototxt:36-72,2237-2281), consuming the network's `coverage` /
 `bboxes` and the five label grids `DataArgumentationLayer` produces.  One fused kernel (fcnod_train_head_forward);
 also returns the gradients that reach the two network outputs (the first step of the backward pass).
-The convolution backward (dgrad / wgrad), the ADAM solver and the NCCL gradient all-reduce of BASELINE config 5 are NOT
-built: this is the forward half of SURVEY.md 8(f) row 3.
+The rest of the training iteration (forward at TRAIN phase, backward of the body, ADAM, data-parallel all-reduce) is in
+trainer.py / csrc/train_net.cu, which calls this head on the device.
 """
 import ctypes as C
 
