@@ -381,10 +381,10 @@ __device__ __forceinline__ void st8(bf16* p, const BF8& r) { *reinterpret_cast<u
 
 __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
     const int cv = g.C / 8;
-    const long total = (long)g.N * g.Ho * g.Wo * cv;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)((long)g.N * g.Ho * g.Wo * cv);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int c = (int)(i % cv) * 8;
-        long t = i / cv;
+        unsigned t = i / cv;
         const int pw = (int)(t % g.Wo); t /= g.Wo;
         const int ph = (int)(t % g.Ho);
         const int n = (int)(t / g.Ho);
@@ -417,10 +417,10 @@ __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
 
 __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, PoolGeo g, int accum) {
     const int cv = g.C / 8;
-    const long total = (long)g.N * g.H * g.W * cv;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)((long)g.N * g.H * g.W * cv);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int c = (int)(i % cv) * 8;
-        long t = i / cv;
+        unsigned t = i / cv;
         const int w = (int)(t % g.W); t /= g.W;
         const int h = (int)(t % g.H);
         const int n = (int)(t / g.H);
@@ -454,8 +454,8 @@ __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __r
 
 __global__ void relu_mask8_kernel(const bf16* __restrict__ y, bf16* __restrict__ dy, long npix, int C, int ldc) {
     const int cv = C / 8;
-    const long total = npix * cv;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)(npix * cv);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const long o = (i / cv) * ldc + (i % cv) * 8;
         const BF8 a = ld8(y + o);
         BF8 d = ld8(dy + o);
@@ -471,10 +471,10 @@ __global__ void relu_mask8_kernel(const bf16* __restrict__ y, bf16* __restrict__
 __global__ void lrn_fwd8_kernel(const bf16* __restrict__ x, int ldi, bf16* __restrict__ y, int ldo, float* __restrict__ scale, long npix,
                                 int C, float alpha_over_n, float beta, float k) {
     const int cv = C / 8;
-    const long total = npix * cv;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)(npix * cv);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int c = (int)(i % cv) * 8;
-        const long px = i / cv;
+        const unsigned px = i / cv;
         const bf16* xp = x + px * ldi;
         float v[12];
         const BF8 a = ld8(xp + c);
@@ -503,11 +503,11 @@ __global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16*
                                 const float* __restrict__ scale, bf16* __restrict__ dx, long npix, int C, float alpha_over_n, float beta,
                                 int accum) {
     const int cv = C / 8;
-    const long total = npix * cv;
+    const unsigned total = (unsigned)(npix * cv);
     const float cr = 2.f * alpha_over_n * beta;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int c = (int)(i % cv) * 8;
-        const long px = i / cv;
+        const unsigned px = i / cv;
         float ratio[12], sc[8], dyv[8];
 #pragma unroll
         for (int q = 0; q < 12; ++q) {
@@ -543,12 +543,12 @@ __global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restr
                               int Ho, int Wo, int k, int stride, int pad) {
     const int kc = k * k * Cin;
     const int per_row = ldk / 8;
-    const long total = (long)N * Ho * Wo * per_row;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)((long)N * Ho * Wo * per_row);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int j = (int)(i % per_row) * 8;
-        const long m = i / per_row;
+        const unsigned m = i / per_row;
         const int ow = (int)(m % Wo);
-        const long t = m / Wo;
+        const unsigned t = m / Wo;
         const int oh = (int)(t % Ho);
         const int n = (int)(t / Ho);
         if (VEC == 8) {
@@ -585,12 +585,12 @@ __global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restr
 __global__ void col2im_kernel(const bf16* __restrict__ dcol, int ldk, bf16* __restrict__ dx, int ldi, int N, int H, int W, int Cin,
                               int k, int pad, int accum) {
     const int cv = Cin / 8;
-    const long total = (long)N * H * W * cv;
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const unsigned total = (unsigned)((long)N * H * W * cv);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
         const int c = (int)(i % cv) * 8;
-        const long m = i / cv;
+        const unsigned m = i / cv;
         const int w = (int)(m % W);
-        const long t = m / W;
+        const unsigned t = m / W;
         const int h = (int)(t % H);
         const int n = (int)(t / H);
         float acc[8];
@@ -619,6 +619,106 @@ __global__ void col2im_kernel(const bf16* __restrict__ dcol, int ldk, bf16* __re
 #pragma unroll
         for (int q = 0; q < 8; ++q) oe[q] = __float2bfloat16_rn(acc[q]);
         *reinterpret_cast<uint4*>(o) = ov;
+    }
+}
+
+// ---- the two head convolutions (1x1, 1 and 4 output channels: too narrow for a TMA row): warp-level kernels on the fp32 master
+// weights P[c][ldw] staged in shared memory.  NARROW_MAX output channels, Cin % 8 == 0.
+constexpr int kNarrowMax = 8;
+
+// y[px][co] = bias[co] + sum_c x[px][c] * P[c][co]: one warp per pixel, lanes stride over 8-channel groups
+__global__ void __launch_bounds__(256) narrow_fwd_kernel(const bf16* __restrict__ x, int ldi, const float* __restrict__ P, int ldw,
+                                                          const float* __restrict__ bias, bf16* __restrict__ y, int ldo, unsigned npix,
+                                                          int Cin, int Cout) {
+    extern __shared__ __align__(16) float ws[];            // [Cout][Cin]: a lane reads 8 consecutive floats per output channel
+    for (int i = threadIdx.x; i < Cin * Cout; i += blockDim.x) ws[(i % Cout) * Cin + i / Cout] = P[(long)(i / Cout) * ldw + i % Cout];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    for (unsigned px = blockIdx.x * wpb + warp; px < npix; px += gridDim.x * wpb) {
+        float acc[kNarrowMax];
+#pragma unroll
+        for (int o = 0; o < kNarrowMax; ++o) acc[o] = 0.f;
+        for (int c = lane * 8; c < Cin; c += 256) {
+            const BF8 v = ld8(x + (size_t)px * ldi + c);
+#pragma unroll
+            for (int o = 0; o < kNarrowMax; ++o)
+                if (o < Cout) {
+                    const float4 w0 = *reinterpret_cast<const float4*>(ws + o * Cin + c), w1 = *reinterpret_cast<const float4*>(ws + o * Cin + c + 4);
+                    acc[o] = fmaf(v.get(0), w0.x, fmaf(v.get(1), w0.y, fmaf(v.get(2), w0.z, fmaf(v.get(3), w0.w, acc[o]))));
+                    acc[o] = fmaf(v.get(4), w1.x, fmaf(v.get(5), w1.y, fmaf(v.get(6), w1.z, fmaf(v.get(7), w1.w, acc[o]))));
+                }
+        }
+#pragma unroll
+        for (int o = 0; o < kNarrowMax; ++o)
+            if (o < Cout) {
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], d);
+                if (lane == 0) y[(size_t)px * ldo + o] = __float2bfloat16_rn(acc[o] + bias[o]);
+            }
+    }
+}
+
+// dx[px][c] (+)= sum_co dy[px][co] * P[c][co]: a thread per (pixel, 8 channels)
+__global__ void __launch_bounds__(256) narrow_dgrad_kernel(const bf16* __restrict__ dy, int ldo, const float* __restrict__ P, int ldw,
+                                                            bf16* __restrict__ dx, int ldi, unsigned npix, int Cin, int Cout, int accum) {
+    extern __shared__ __align__(16) float ws[];            // [Cout][Cin]
+    for (int i = threadIdx.x; i < Cin * Cout; i += blockDim.x) ws[(i % Cout) * Cin + i / Cout] = P[(long)(i / Cout) * ldw + i % Cout];
+    __syncthreads();
+    const unsigned cv = Cin / 8, total = npix * cv;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const unsigned px = i / cv;
+        const int c = (int)(i % cv) * 8;
+        float g[kNarrowMax];
+#pragma unroll
+        for (int o = 0; o < kNarrowMax; ++o) g[o] = o < Cout ? __bfloat162float(dy[(size_t)px * ldo + o]) : 0.f;
+        bf16* op = dx + (size_t)px * ldi + c;
+        BF8 r;
+        float v[8];
+        if (accum) r = ld8(op);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = accum ? r.get(q) : 0.f;
+#pragma unroll
+        for (int o = 0; o < kNarrowMax; ++o)
+            if (o < Cout) {
+                const float4 w0 = *reinterpret_cast<const float4*>(ws + o * Cin + c), w1 = *reinterpret_cast<const float4*>(ws + o * Cin + c + 4);
+                v[0] = fmaf(g[o], w0.x, v[0]); v[1] = fmaf(g[o], w0.y, v[1]); v[2] = fmaf(g[o], w0.z, v[2]); v[3] = fmaf(g[o], w0.w, v[3]);
+                v[4] = fmaf(g[o], w1.x, v[4]); v[5] = fmaf(g[o], w1.y, v[5]); v[6] = fmaf(g[o], w1.z, v[6]); v[7] = fmaf(g[o], w1.w, v[7]);
+            }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) r.set(q, v[q]);
+        st8(op, r);
+    }
+}
+
+// dP[c][co] += sum_px x[px][c] * dy[px][co]: a block per pixel chunk, a thread per 8-channel group
+__global__ void __launch_bounds__(128) narrow_wgrad_kernel(const bf16* __restrict__ x, int ldi, const bf16* __restrict__ dy, int ldo,
+                                                            float* __restrict__ G, int ldw, unsigned npix, unsigned chunk, int Cin, int Cout) {
+    const unsigned p0 = blockIdx.x * chunk, p1 = min(p0 + chunk, npix);
+    for (int c = threadIdx.x * 8; c < Cin; c += blockDim.x * 8) {
+        float acc[8][4];
+        for (int o0 = 0; o0 < Cout; o0 += 4) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+                for (int o = 0; o < 4; ++o) acc[q][o] = 0.f;
+            for (unsigned px = p0; px < p1; ++px) {
+                const BF8 v = ld8(x + (size_t)px * ldi + c);
+                float g[4];
+#pragma unroll
+                for (int o = 0; o < 4; ++o) g[o] = o0 + o < Cout ? __bfloat162float(dy[(size_t)px * ldo + o0 + o]) : 0.f;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float xv = v.get(q);
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) acc[q][o] = fmaf(xv, g[o], acc[q][o]);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+                for (int o = 0; o < 4; ++o)
+                    if (o0 + o < Cout) atomicAdd(G + (long)(c + q) * ldw + o0 + o, acc[q][o]);
+        }
     }
 }
 
@@ -659,6 +759,7 @@ struct TConv {
     float* d_wt = 0;                 // SIMT dgrad packing [(r,s,co)][ldt], rebuilt every step
     // bf16 engine (tensor cores): transposed bf16 weights [Cout][ldk] (forward B operand), im2col row pitch, GEMM plans
     bool tc = false;
+    bool narrow = false;             // bf16 engine: 1x1 convolution with fewer than 8 output channels (the heads): narrow_*_kernel
     bf16* d_wf = 0;
     bf16* d_col = 0;                 // k x k: this layer's im2col matrix, written by the forward and kept for the weight gradient
     int ldk = 0;
@@ -1040,10 +1141,15 @@ void build_tc(fcnod_trainer* t) {
         const TBlob& ob = t->blobs[L.out];
         // tensor cores need 16-byte rows on both sides of the output view; the 1- and 4-channel heads stay on the SIMT kernels
         c.tc = ob.ldc % 8 == 0 && ob.c_off % 8 == 0 && c.Cout % 8 == 0;
+        c.narrow = !c.tc && !L.relu && c.k == 1 && c.stride == 1 && c.Cout <= kNarrowMax && c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 &&
+                   (size_t)c.Cin * c.Cout * 4 <= 48 * 1024;
         if (!c.tc) continue;
         c.ldk = (c.K + 7) / 8 * 8;
         if (!(c.k == 1 && c.stride == 1)) col_elems = std::max(col_elems, (size_t)N * ob.H * ob.W * c.ldk);
     }
+    FCNOD_CHECK(col_elems < (1ull << 32), "trainer: batch too large for the 32-bit index arithmetic of the bf16 kernels");
+    for (size_t b = 0; b < t->bufs.size(); ++b)
+        FCNOD_CHECK((size_t)N * t->bufs[b].C * t->bufs[b].H * t->bufs[b].W < (1ull << 31), "trainer: batch too large for the 32-bit index arithmetic of the bf16 kernels");
     t->col = dalloc<bf16>(t, col_elems);
     t->wb = dalloc<bf16>(t, t->n_params);
     for (size_t li = 0; li < t->layers.size(); ++li) {
@@ -1123,6 +1229,10 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
             if (tcp && c.tc) {
                 if (!(c.k == 1 && c.stride == 1)) launch_im2col(t, c, ib, ob, s);
                 run_gemm(t, c.g_fwd, 0, s);
+            } else if (tcp && c.narrow) {
+                narrow_fwd_kernel<<<std::min<long>((out_px + 7) / 8, 148 * 8), 256, (size_t)c.Cin * c.Cout * 4, s>>>(
+                    as<bf16>(bdata(t, ib)), ib.ldc, t->params + c.w_off, c.ldw, t->params + c.b_off, as<bf16>(bdata(t, ob)), ob.ldc, (unsigned)out_px,
+                    c.Cin, c.Cout);
             } else {
                 launch_conv<T, T>(bdata(t, ib), ib.ldc, ib.H, ib.W, c.Cin, t->params + c.w_off, c.ldw, t->params + c.b_off, bdata(t, ob), ob.ldc,
                                   ob.H, ob.W, c.Cout, N, c.k, c.stride, c.pad, L.relu ? 1 : 0, 0, s);
@@ -1241,6 +1351,19 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
                                                                                        c.k, c.pad, accum);
                         FCNOD_CUDA(cudaGetLastError());
                     }
+                }
+                break;
+            }
+            if (tcp && c.narrow) {
+                const unsigned chunk = 128;
+                narrow_wgrad_kernel<<<(unsigned)((out_px + chunk - 1) / chunk), 128, 0, s>>>(as<bf16>(bdata(t, ib)), ib.ldc, as<bf16>(bdiff(t, ob)), ob.ldc,
+                                                                                              t->grads + c.w_off, c.ldw, (unsigned)out_px, chunk, c.Cin, c.Cout);
+                FCNOD_CUDA(cudaGetLastError());
+                if (ib.needs_grad) {
+                    narrow_dgrad_kernel<<<grid1(in_px * (c.Cin / 8), 256), 256, (size_t)c.Cin * c.Cout * 4, s>>>(
+                        as<bf16>(bdiff(t, ob)), ob.ldc, t->params + c.w_off, c.ldw, as<bf16>(bdiff(t, ib)), ib.ldc, (unsigned)in_px, c.Cin, c.Cout,
+                        claim_diff(t, L.in));
+                    FCNOD_CUDA(cudaGetLastError());
                 }
                 break;
             }
