@@ -33,6 +33,8 @@ struct GemmTcParams {
     void* out; int ldo; int out_f32;      // row-major M x N view, leading dimension ldo elements
     const float* bias;                    // [N] or null
     int relu, accum;                      // accum: out += result
+    int tma_out;                          // bf16 output through shared memory + TMA store (accum: TMA reduce-add); needs tmap_o
+    uint32_t out_stage_bytes;             // ceil(BN / 64) * 16 KB when tma_out
     // epilogue, MN-major
     float* gout; int ldg;                 // gout[n * ldg + m] += D[m][n]
 };
@@ -49,12 +51,14 @@ constexpr int kGemmPK = 64;               // pixels per reduction block of the M
 
 template <bool MNMAJ>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmTcParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const __grid_constant__ CUtensorMap tmap_o, const GemmTcParams p) {
     using namespace tc;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
-    const uint32_t bar_base = smem_base + (uint32_t)p.stages * stage_bytes;
+    const uint32_t out_stage = smem_base + (uint32_t)p.stages * stage_bytes;      // 1024-aligned: stage sizes are multiples of 1 KB
+    const uint32_t bar_base = out_stage + p.out_stage_bytes;
     const uint32_t full0 = bar_base, empty0 = full0 + 8u * p.stages;
     const uint32_t tfull0 = empty0 + 8u * p.stages, tempty0 = tfull0 + 16u, tmem_slot = tempty0 + 16u;
     // bias staged in shared memory once per CTA (a global load per column in the epilogue loop costs a full memory latency
@@ -150,6 +154,79 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 umma_commit(tfull0 + 8u * acc);
             }
         }
+    } else if (!MNMAJ && p.tma_out) {
+        // ================================================================== epilogue through shared memory + TMA store.
+        // 8 warps (TMEM lane quadrant = warp % 4, the two warps of a quadrant take alternate 16-column chunks) convert their
+        // rows to bf16 and write them into a [128 rows][64 columns] x ceil(BN / 64) staging area in the SWIZZLE_128B layout of
+        // the output tensor map; one thread then issues a TMA store per 64-column region -- or a TMA reduce-add when the
+        // output accumulates (the Split sum of the data gradients): full-line writes, no read-modify-write latency in the
+        // epilogue warps, and rows / columns beyond M / N are clipped by the TMA unit.
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const bool leader = warp == 2 && lane == 0;
+        uint32_t it = 0;
+        for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
+            const int tn = w % p.tiles_n, tm = (w / p.tiles_n) % p.tiles_m;
+            const int m0 = tm * 128, n0 = tn * p.BN;
+            const uint32_t acc = it & 1u, acc_ph = (it >> 1) & 1u;
+            const int n_chunks = (min(p.BN, p.N - n0) + 15) / 16;
+            const int r = q * 32 + lane;                                   // row of the tile = TMEM lane
+            // the staging area is free once the previous tile's stores have READ it
+            if (leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mbar_wait(tfull0 + 8u * acc, acc_ph);
+            fence_after();
+            const uint32_t taddr = tmem_base + acc * (uint32_t)p.BN + ((uint32_t)(q * 32) << 16);
+            uint32_t rA[16], rB[16];
+            auto emit = [&](const uint32_t (&rr)[16], int ch) {
+                const int n = n0 + 16 * ch;
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    v[j] = __uint_as_float(rr[j]);
+                    if (p.bias) v[j] += bias_s[n + j];
+                    if (p.relu) v[j] = fmaxf(v[j], 0.f);
+                }
+                uint4 w4[2];
+                __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(w4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) h2[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                const uint32_t row_base = out_stage + (uint32_t)(ch >> 2) * 16384u + (uint32_t)r * 128u;
+                const uint32_t u0 = (uint32_t)(ch & 3) * 2u, sw = (uint32_t)r & 7u;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + ((u0 ^ sw) << 4)), "r"(w4[0].x), "r"(w4[0].y), "r"(w4[0].z), "r"(w4[0].w) : "memory");
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + (((u0 + 1u) ^ sw) << 4)), "r"(w4[1].x), "r"(w4[1].y), "r"(w4[1].z), "r"(w4[1].w) : "memory");
+            };
+            if (half < n_chunks) tmem_ld16(taddr + 16u * half, rA);
+            for (int ch = half; ch < n_chunks; ch += 4) {
+                gemm_ld_wait16(rA);
+                if (ch + 2 < n_chunks) tmem_ld16(taddr + 16u * (ch + 2), rB);
+                emit(rA, ch);
+                if (ch + 2 < n_chunks) {
+                    gemm_ld_wait16(rB);
+                    if (ch + 4 < n_chunks) tmem_ld16(taddr + 16u * (ch + 4), rA);
+                    emit(rB, ch + 2);
+                }
+            }
+            // the accumulator is drained: hand it back to the MMA warp, then publish the staged tile
+            fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (leader) {
+                const int regions = (n_chunks + 3) >> 2;
+                for (int g = 0; g < regions; ++g) {
+                    const uint32_t src = out_stage + (uint32_t)g * 16384u;
+                    if (p.accum)
+                        asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&tmap_o), "r"(src), "r"(n0 + 64 * g), "r"(m0) : "memory");
+                    else
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&tmap_o), "r"(src), "r"(n0 + 64 * g), "r"(m0) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+        if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     } else {
         // ================================================================== epilogue: 8 warps, TMEM lane quadrant = warp % 4,
         // the two warps of a quadrant take alternate 16-column chunks.  The accumulator chunk and (accumulate mode) the old

@@ -23,6 +23,7 @@
 // launch.  Padding entries have zero gradient and stay zero.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <vector>
@@ -777,7 +778,7 @@ struct TLayer {
 };
 
 struct GemmPlan {
-    CUtensorMap ta, tb;
+    CUtensorMap ta, tb, to;
     GemmTcParams p;
     int grid = 0;
     size_t smem = 0;
@@ -1059,9 +1060,10 @@ int pow2_at_least(int v) { int p = 32; while (p < v) p <<= 1; return p; }
 void finish_plan(GemmPlan& g) {
     GemmTcParams& p = g.p;
     const size_t stage = (size_t)p.a_stage_bytes + p.b_stage_bytes;
-    p.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (192 * 1024) / stage));
+    p.out_stage_bytes = p.tma_out ? (uint32_t)((p.BN + 63) / 64) * 16384u : 0u;
+    p.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (192 * 1024 - p.out_stage_bytes) / stage));
     p.tmem_cols = (uint32_t)pow2_at_least(2 * p.BN);
-    g.smem = (size_t)p.stages * stage + 16 * p.stages + 64 + 1024 + kGemmBiasMax * 4;
+    g.smem = (size_t)p.stages * stage + p.out_stage_bytes + 16 * p.stages + 64 + 1024 + kGemmBiasMax * 4;
     FCNOD_CHECK(!p.bias || p.N <= 1024, "gemm: a bias needs N <= 1024");
     g.grid = std::min(p.tiles_m * p.tiles_n * p.splits, 148);
 }
@@ -1081,6 +1083,18 @@ GemmPlan plan_gemm_k(const bf16* A, int lda, long M, int K, const bf16* B, int l
     p.out = out; p.ldo = ldo; p.out_f32 = out_f32; p.bias = bias; p.relu = relu; p.accum = 0;
     encode_2d(&g.ta, A, K, M, lda, 128, what);
     encode_2d(&g.tb, B, K, N, ldb, p.BN, what);
+    // bf16 outputs with 16-byte rows leave through shared memory and the TMA unit (store, or reduce-add when accumulating)
+    p.tma_out = (!out_f32 && ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && getenv("FCNOD_GEMM_NO_TMA_STORE") == 0) ? 1 : 0;
+    if (p.tma_out && p.tiles_n > 1) {
+        // the staged tile leaves in 64-column regions: with several N tiles a tile must END on a region boundary, or the tail
+        // of its last region would land on the next tile's columns (a single tile's tail is clipped at N by the TMA unit)
+        p.BN = std::min(256, (((N + nt - 1) / nt) + 63) / 64 * 64);
+        p.tiles_n = (N + p.BN - 1) / p.BN;
+        p.b_stage_bytes = (uint32_t)p.BN * 128;
+        encode_2d(&g.tb, B, K, N, ldb, p.BN, what);
+    }
+    if (p.tma_out) encode_2d(&g.to, out, N, M, ldo, 128, what);
+    else g.to = g.ta;
     g.mn = false;
     finish_plan(g);
     return g;
@@ -1104,6 +1118,7 @@ GemmPlan plan_gemm_mn(const bf16* A, int lda, int Mco, const bf16* B, int ldb, i
     p.gout = gout; p.ldg = ldg;
     encode_2d(&g.ta, A, Mco, PX, lda, kGemmPK, what);
     encode_2d(&g.tb, B, Ncols, PX, ldb, kGemmPK, what);
+    g.to = g.ta;
     g.mn = true;
     finish_plan(g);
     return g;
@@ -1123,8 +1138,8 @@ void run_plan(const GemmPlan& g, int accum, cudaStream_t s) {
     }
     GemmTcParams p = g.p;
     p.accum = accum;
-    if (g.mn) gemm_tc_kernel<true><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, p);
-    else gemm_tc_kernel<false><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, p);
+    if (g.mn) gemm_tc_kernel<true><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, g.to, p);
+    else gemm_tc_kernel<false><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, g.to, p);
     FCNOD_CUDA(cudaGetLastError());
 }
 void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) { run_plan(t->gemms[id], accum, s); }

@@ -38,10 +38,12 @@ def test_gemm_k_major(M, N, K, lda, ldb, ldo):
     torch.cuda.synchronize()
     want = torch.relu(ref + bias)
     assert _rel(outb[:, :N].float(), want) < 1e-2
+    assert bool((outb[:, N:] == 0).all())                      # the TMA store clips at N
     first = outb.clone()
     _lib.check(L.fcnod_gemm_bf16_device(0, A.data_ptr(), lda, B.data_ptr(), ldb, M, N, K, outb.data_ptr(), ldo, 0, None, 0, 1, s))
     torch.cuda.synchronize()
     assert _rel(outb[:, :N].float(), first[:, :N].float() + ref) < 1.5e-2
+    assert bool((outb[:, N:] == 0).all())
 
 
 @pytest.mark.parametrize('PX,M,N,lda,ldb,ldo', [(1000, 96, 147, 480, 152, 128), (64, 128, 64, 128, 64, 128), (25088, 208, 864, 512, 864, 256),
