@@ -133,6 +133,8 @@ SIGNATURES = {
     'fcnod_trainer_blob_read': (_I, [_P, _STR, _I, C.POINTER(_I), _P, _SZ]),
     'fcnod_trainer_dropout_mask': (_I, [_P, _P, _SZ, C.POINTER(_I)]),
     'fcnod_trainer_pool_argmax': (_I, [_P, _STR, _P, _SZ, C.POINTER(_I)]),
+    'fcnod_trainer_set_timing': (_I, [_P, _I]),
+    'fcnod_trainer_gemm_times': (_I, [_P, _P, _P, _P]),
     'fcnod_gemm_bf16_device': (_I, [_I, _P, _I, _P, _I, _I, _I, _I, _P, _I, _I, _P, _I, _I, _P]),
 }
 

@@ -536,91 +536,87 @@ __global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16*
 }
 
 // ------------------------------------------------------------------------------------------------ bf16 engine helpers
+// Exact division of a small dividend by a run-time divisor through a precomputed reciprocal: q = (x * magic) >> 32 with
+// magic = ceil(2^32 / d) is exact for x < 2^16 (the per-row counts below), one multiply instead of an integer division.
+__host__ __device__ __forceinline__ unsigned div_magic(unsigned d) { return (unsigned)((0x100000000ull + d - 1) / d); }
+__device__ __forceinline__ unsigned div_fast(unsigned x, unsigned magic) { return __umulhi(x, magic); }
+
 // im2col for the tensor-core GEMMs: col[px][(r*k + s)*Cin + c] = x[n][oh*stride - pad + r][ow*stride - pad + s][c] (0 outside),
 // rows of ldk elements (Kc rounded up to 8: a TMA row pitch is a multiple of 16 bytes; the padding columns are zeroed).
-// VEC = 8: 16-byte moves (Cin % 8 == 0 and the view 16-byte aligned), VEC = 1: scalar (the first convolution, Cin = 3).
-template <int VEC>      // VEC = 8: Cin % 8 == 0, whole 16-byte groups copied; VEC = 1: any Cin, gathered per element
-__global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restrict__ col, int ldk, int N, int H, int W, int Cin,
-                              int Ho, int Wo, int k, int stride, int pad) {
-    const int kc = k * k * Cin;
-    const int per_row = ldk / 8;
-    const unsigned total = (unsigned)((long)N * Ho * Wo * per_row);
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
-        const int j = (int)(i % per_row) * 8;
-        const unsigned m = i / per_row;
-        const int ow = (int)(m % Wo);
-        const unsigned t = m / Wo;
-        const int oh = (int)(t % Ho);
-        const int n = (int)(t / Ho);
-        if (VEC == 8) {
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (j < kc) {
-                const int c = j % Cin, rs = j / Cin, r = rs / k, s2 = rs % k;
-                const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
-                if (ih >= 0 && ih < H && iw >= 0 && iw < W)
-                    v = *reinterpret_cast<const uint4*>(x + ((long)(n * H + ih) * W + iw) * ldi + c);
-            }
-            *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
-        } else {
-            // few input channels (the first convolution, Cin = 3): every element gathered on its own, still one 16-byte store
-            uint4 v;
-            bf16* e = reinterpret_cast<bf16*>(&v);
+// One thread per 16-byte group of a row; grid = (groups of an output row, Ho, N): no division for the pixel coordinates.
+// VEC = 8: Cin % 8 == 0, whole 16-byte groups copied; VEC = 1: any Cin (the first convolution, Cin = 3), gathered per element.
+template <int VEC, int K>
+__global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restrict__ col, int ldk, int H, int W, int Cin, int Wo,
+                              int stride, int pad, unsigned m_per_row, unsigned m_cin) {
+    const unsigned per_row = (unsigned)ldk / 8u;
+    const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (unsigned)Wo * per_row) return;
+    const int ow = (int)div_fast(idx, m_per_row);
+    const int j = (int)(idx - (unsigned)ow * per_row) * 8;
+    const int oh = blockIdx.y, n = blockIdx.z, Ho = gridDim.y;
+    const int kc = K * K * Cin;
+    const size_t m = ((size_t)n * Ho + oh) * Wo + ow;
+    const bf16* xn = x + (size_t)n * H * W * ldi;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (VEC == 8) {
+        if (j < kc) {
+            const int rs = (int)div_fast((unsigned)j, m_cin), c = j - rs * Cin, r = rs / K, s2 = rs - r * K;     // m_cin = magic(Cin)
+            const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = *reinterpret_cast<const uint4*>(xn + ((size_t)ih * W + iw) * ldi + c);
+        }
+    } else {
+        bf16* e = reinterpret_cast<bf16*>(&v);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int jj = j + q;
-                bf16 a = __float2bfloat16_rn(0.f);
-                if (jj < kc) {
-                    const int c = jj % Cin, rs = jj / Cin, r = rs / k, s2 = rs % k;
-                    const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
-                    if (ih >= 0 && ih < H && iw >= 0 && iw < W) a = x[((long)(n * H + ih) * W + iw) * ldi + c];
-                }
-                e[q] = a;
+        for (int q = 0; q < 8; ++q) {
+            const int jj = j + q;
+            if (jj < kc) {
+                const int rs = (int)div_fast((unsigned)jj, m_cin), c = jj - rs * Cin, r = rs / K, s2 = rs - r * K;
+                const int ih = oh * stride - pad + r, iw = ow * stride - pad + s2;
+                if (ih >= 0 && ih < H && iw >= 0 && iw < W) e[q] = xn[((size_t)ih * W + iw) * ldi + c];
             }
-            *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
         }
     }
+    *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
 }
 
 // data gradient of a stride-1 k x k convolution from the column gradient dcol = dY * W (the adjoint of im2col):
-// dx[n][h][w][c] (+)= sum_{r,s} dcol[(n, h + pad - r, w + pad - s)][(r*k + s)*Cin + c]; 8 channels per thread.
-__global__ void col2im_kernel(const bf16* __restrict__ dcol, int ldk, bf16* __restrict__ dx, int ldi, int N, int H, int W, int Cin,
-                              int k, int pad, int accum) {
-    const int cv = Cin / 8;
-    const unsigned total = (unsigned)((long)N * H * W * cv);
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
-        const int c = (int)(i % cv) * 8;
-        const unsigned m = i / cv;
-        const int w = (int)(m % W);
-        const unsigned t = m / W;
-        const int h = (int)(t % H);
-        const int n = (int)(t / H);
-        float acc[8];
+// dx[n][h][w][c] (+)= sum_{r,s} dcol[(n, h + pad - r, w + pad - s)][(r*k + s)*Cin + c]; 8 channels per thread, grid (., H, N).
+template <int K>
+__global__ void col2im_kernel(const bf16* __restrict__ dcol, int ldk, bf16* __restrict__ dx, int ldi, int W, int Cin, int pad, int accum,
+                              unsigned m_cv) {
+    const unsigned cv = (unsigned)Cin / 8u;
+    const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (unsigned)W * cv) return;
+    const int w = (int)div_fast(idx, m_cv), c = (int)(idx - (unsigned)w * cv) * 8;
+    const int h = blockIdx.y, n = blockIdx.z, H = gridDim.y;
+    float acc[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
-        for (int r = 0; r < k; ++r) {
-            const int oh = h + pad - r;
-            if (oh < 0 || oh >= H) continue;
-            for (int s2 = 0; s2 < k; ++s2) {
-                const int ow = w + pad - s2;
-                if (ow < 0 || ow >= W) continue;
-                const uint4 v = *reinterpret_cast<const uint4*>(dcol + ((long)(n * H + oh) * W + ow) * ldk + (r * k + s2) * Cin + c);
-                const bf16* e = reinterpret_cast<const bf16*>(&v);
+    for (int q = 0; q < 8; ++q) acc[q] = 0.f;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(e[q]);
-            }
+    for (int r = 0; r < K; ++r) {
+        const int oh = h + pad - r;
+        if (oh < 0 || oh >= H) continue;
+#pragma unroll
+        for (int s2 = 0; s2 < K; ++s2) {
+            const int ow = w + pad - s2;
+            if (ow < 0 || ow >= W) continue;
+            const uint4 v = *reinterpret_cast<const uint4*>(dcol + (((size_t)n * H + oh) * W + ow) * ldk + (r * K + s2) * Cin + c);
+            const bf16* e = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(e[q]);
         }
-        bf16* o = dx + m * ldi + c;
-        uint4 ov;
-        bf16* oe = reinterpret_cast<bf16*>(&ov);
-        if (accum) {
-            ov = *reinterpret_cast<const uint4*>(o);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(oe[q]);
-        }
-#pragma unroll
-        for (int q = 0; q < 8; ++q) oe[q] = __float2bfloat16_rn(acc[q]);
-        *reinterpret_cast<uint4*>(o) = ov;
     }
+    bf16* o = dx + (((size_t)n * H + h) * W + w) * ldi + c;
+    uint4 ov;
+    bf16* oe = reinterpret_cast<bf16*>(&ov);
+    if (accum) {
+        ov = *reinterpret_cast<const uint4*>(o);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] += __bfloat162float(oe[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) oe[q] = __float2bfloat16_rn(acc[q]);
+    *reinterpret_cast<uint4*>(o) = ov;
 }
 
 // ---- the two head convolutions (1x1, 1 and 4 output channels: too narrow for a TMA row): warp-level kernels on the fp32 master
@@ -794,6 +790,10 @@ struct fcnod_trainer {
     bf16* wb = 0;                             // bf16 copy of the flat parameter buffer
     bf16* col = 0;                            // column-gradient scratch of the k x k data gradients (shared)
     std::vector<GemmPlan> gemms;
+    // timing mode (bench.py's roofline): CUDA events around every GEMM launch of a step, on the launching stream
+    bool timing = false;
+    std::vector<int> gemm_kind;               // per plan: 0 forward, 1 data gradient, 2 weight gradient
+    std::vector<cudaEvent_t> ev0, ev1;        // per plan
     fcnod_solver_params solver;
     NetDef def;
     std::vector<TBlob> blobs;
@@ -1124,8 +1124,9 @@ GemmPlan plan_gemm_mn(const bf16* A, int lda, int Mco, const bf16* B, int ldb, i
     return g;
 }
 
-int add_plan(fcnod_trainer* t, const GemmPlan& g) {
+int add_plan(fcnod_trainer* t, const GemmPlan& g, int kind = 0) {
     t->gemms.push_back(g);
+    t->gemm_kind.push_back(kind);
     return (int)t->gemms.size() - 1;
 }
 
@@ -1142,7 +1143,20 @@ void run_plan(const GemmPlan& g, int accum, cudaStream_t s) {
     else gemm_tc_kernel<false><<<g.grid, kGemmThreads, g.smem, s>>>(g.ta, g.tb, g.to, p);
     FCNOD_CUDA(cudaGetLastError());
 }
-void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) { run_plan(t->gemms[id], accum, s); }
+void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) {
+    if (t->timing) {
+        if (t->ev0.size() < t->gemms.size()) {
+            const size_t old = t->ev0.size();
+            t->ev0.resize(t->gemms.size()); t->ev1.resize(t->gemms.size());
+            for (size_t i = old; i < t->gemms.size(); ++i) { FCNOD_CUDA(cudaEventCreate(&t->ev0[i])); FCNOD_CUDA(cudaEventCreate(&t->ev1[i])); }
+        }
+        FCNOD_CUDA(cudaEventRecord(t->ev0[id], s));
+        run_plan(t->gemms[id], accum, s);
+        FCNOD_CUDA(cudaEventRecord(t->ev1[id], s));
+    } else {
+        run_plan(t->gemms[id], accum, s);
+    }
+}
 
 // bf16 engine: scratch, bf16 weights and the three GEMM plans of every convolution (pointers are fixed for the trainer's life)
 void build_tc(fcnod_trainer* t) {
@@ -1182,12 +1196,12 @@ void build_tc(fcnod_trainer* t) {
         const bf16* X = direct ? as<bf16>(bdata(t, ib)) : c.d_col;
         const int ldx = direct ? ib.ldc : c.ldk;
         c.g_fwd = add_plan(t, plan_gemm_k(X, ldx, PX, c.K, c.d_wf, c.ldk, c.Cout, bdata(t, ob), ob.ldc, 0, t->params + c.b_off, L.relu ? 1 : 0, c.name.c_str()));
-        c.g_wgrad = add_plan(t, plan_gemm_mn(as<bf16>(bdiff(t, ob)), ob.ldc, c.Cout, X, ldx, c.K, PX, t->grads + c.w_off, c.ldw, c.name.c_str()));
+        c.g_wgrad = add_plan(t, plan_gemm_mn(as<bf16>(bdiff(t, ob)), ob.ldc, c.Cout, X, ldx, c.K, PX, t->grads + c.w_off, c.ldw, c.name.c_str()), 2);
         if (ib.needs_grad) {
             // dY[px][Cout] * Wb[Kc][Cout]^T: straight into the bottom diff for 1x1, into the column scratch (then col2im) otherwise
             FCNOD_CHECK(c.Cin % 8 == 0, "trainer: data gradient of '" + c.name + "' needs Cin % 8 == 0");
             c.g_dgrad = add_plan(t, plan_gemm_k(as<bf16>(bdiff(t, ob)), ob.ldc, PX, c.Cout, t->wb + c.w_off, c.ldw, c.K,
-                                    direct ? (void*)bdiff(t, ib) : (void*)t->col, direct ? ib.ldc : c.ldk, 0, 0, 0, c.name.c_str()));
+                                    direct ? (void*)bdiff(t, ib) : (void*)t->col, direct ? ib.ldc : c.ldk, 0, 0, 0, c.name.c_str()), 1);
         }
     }
 }
@@ -1206,14 +1220,22 @@ void launch_conv(const void* in, int ldi, int H, int W, int Cin, const float* w,
     FCNOD_CUDA(cudaGetLastError());
 }
 
-void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
-    const long PX = (long)t->batch * ob.H * ob.W;
+template <int VEC>
+void launch_im2col_k(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
+    const unsigned per_row = (unsigned)c.ldk / 8u;
+    dim3 grid((ob.W * per_row + 255) / 256, ob.H, t->batch);
     const bf16* x = as<bf16>(bdata(t, ib));
-    if (c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0)
-        im2col_kernel<8><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, c.d_col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
-    else
-        im2col_kernel<1><<<grid1(PX * (c.ldk / 8), 256), 256, 0, s>>>(x, ib.ldc, c.d_col, c.ldk, t->batch, ib.H, ib.W, c.Cin, ob.H, ob.W, c.k, c.stride, c.pad);
+    const unsigned m1 = div_magic(per_row), m2 = div_magic((unsigned)c.Cin);
+#define FCNOD_IM2COL(KK) im2col_kernel<VEC, KK><<<grid, 256, 0, s>>>(x, ib.ldc, c.d_col, c.ldk, ib.H, ib.W, c.Cin, ob.W, c.stride, c.pad, m1, m2)
+    if (c.k == 3) FCNOD_IM2COL(3); else if (c.k == 5) FCNOD_IM2COL(5); else if (c.k == 7) FCNOD_IM2COL(7);
+    else FCNOD_CHECK(false, "trainer: im2col supports 3x3, 5x5 and 7x7 kernels");
+#undef FCNOD_IM2COL
     FCNOD_CUDA(cudaGetLastError());
+}
+void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
+    FCNOD_CHECK(ob.W * (c.ldk / 8) < 65536 && c.ldk < 65536, "trainer: im2col row too long for the fast division");
+    if (c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0) launch_im2col_k<8>(t, c, ib, ob, s);
+    else launch_im2col_k<1>(t, c, ib, ob, s);
 }
 
 template <typename T>
@@ -1362,8 +1384,12 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
                         run_gemm(t, c.g_dgrad, accum, s);
                     } else {
                         run_gemm(t, c.g_dgrad, 0, s);         // column gradient into the scratch
-                        col2im_kernel<<<grid1(in_px * (c.Cin / 8), 256), 256, 0, s>>>(t->col, c.ldk, as<bf16>(bdiff(t, ib)), ib.ldc, N, ib.H, ib.W, c.Cin,
-                                                                                       c.k, c.pad, accum);
+                        FCNOD_CHECK(ib.W * (c.Cin / 8) < 65536, "trainer: col2im row too long for the fast division");
+                        dim3 cgrid((ib.W * (c.Cin / 8) + 255) / 256, ib.H, N);
+                        const unsigned mcv = div_magic((unsigned)c.Cin / 8u);
+                        if (c.k == 3) col2im_kernel<3><<<cgrid, 256, 0, s>>>(t->col, c.ldk, as<bf16>(bdiff(t, ib)), ib.ldc, ib.W, c.Cin, c.pad, accum, mcv);
+                        else if (c.k == 5) col2im_kernel<5><<<cgrid, 256, 0, s>>>(t->col, c.ldk, as<bf16>(bdiff(t, ib)), ib.ldc, ib.W, c.Cin, c.pad, accum, mcv);
+                        else FCNOD_CHECK(false, "trainer: col2im supports 3x3 and 5x5 kernels");
                         FCNOD_CUDA(cudaGetLastError());
                     }
                 }
@@ -1637,6 +1663,33 @@ int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which, int d
     if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
     cudaFree(tmp);
     FCNOD_CUDA(e);
+    FCNOD_API_END
+}
+
+// Timing mode for the roofline of the GEMM kernel: with on != 0 every GEMM launch of the following steps is bracketed by CUDA
+// events on the launching stream; fcnod_trainer_gemm_times then returns, for the last step, the summed launch times (ms) and
+// the algorithmic FLOP (2 M N K per launch) of the forward, data-gradient and weight-gradient GEMMs, and the launch counts.
+int fcnod_trainer_set_timing(fcnod_trainer* t, int on) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t, "null argument");
+    t->timing = on != 0;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_gemm_times(fcnod_trainer* t, float ms[3], double flop[3], int launches[3]) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && ms && flop && launches, "null argument");
+    FCNOD_CHECK(t->prec == 1 && t->ev0.size() == t->gemms.size(), "trainer: no timed bf16 step to report");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    FCNOD_CUDA(cudaDeviceSynchronize());
+    for (int k = 0; k < 3; ++k) { ms[k] = 0.f; flop[k] = 0.0; launches[k] = 0; }
+    for (size_t i = 0; i < t->gemms.size(); ++i) {
+        float e = 0.f;
+        if (cudaEventElapsedTime(&e, t->ev0[i], t->ev1[i]) != cudaSuccess) { cudaGetLastError(); continue; }    // never launched
+        const int k = t->gemm_kind[i];
+        const GemmTcParams& p = t->gemms[i].p;
+        ms[k] += e; flop[k] += 2.0 * p.M * p.N * (double)p.K; ++launches[k];
+    }
     FCNOD_API_END
 }
 

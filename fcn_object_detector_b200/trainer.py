@@ -140,6 +140,21 @@ class Solver(object):
         w = float(self.params.bbox_loss_weight)
         return dict(loss_bbox=float(losses[0]), loss_coverage=float(losses[1]), loss=float(losses[1]) + w * float(losses[0]))
 
+    def gemm_times(self, run_step):
+        """Time the GEMM launches of one step (bf16 engine): run_step() must run one forward + backward.  Returns
+        {'forward' | 'dgrad' | 'wgrad': dict(ms, flop, launches)} summed over the launches of each kind."""
+        L = _lib.lib()
+        _lib.check(L.fcnod_trainer_set_timing(self.handle, 1))
+        try:
+            run_step()
+            ms = (C.c_float * 3)()
+            fl = (C.c_double * 3)()
+            n = (C.c_int * 3)()
+            _lib.check(L.fcnod_trainer_gemm_times(self.handle, ms, fl, n))
+        finally:
+            _lib.check(L.fcnod_trainer_set_timing(self.handle, 0))
+        return {k: dict(ms=float(ms[i]), flop=float(fl[i]), launches=int(n[i])) for i, k in enumerate(('forward', 'dgrad', 'wgrad'))}
+
     def grad_buffer(self):
         """The flat gradient buffer as an object torch can wrap in place (see DataParallelSolver)."""
         return _DeviceArray(self.grad_ptr, self.n_params, self)

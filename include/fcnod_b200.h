@@ -348,6 +348,11 @@ int fcnod_trainer_param_read(fcnod_trainer* t, const char* layer, int index, int
 const char* fcnod_trainer_param_layer(const fcnod_trainer* t, int i);   /* i-th convolution's name, NULL past the end */
 int fcnod_trainer_blob_read(fcnod_trainer* t, const char* blob, int which /* 0 data, 1 diff */, int dims[3], float* out, size_t count);
 int fcnod_trainer_dropout_mask(fcnod_trainer* t, uint8_t* out /* [N][C][H][W] */, size_t count, int dims[3]);
+/* Measurement aid (bench.py's roofline): time every GEMM launch of the following steps with CUDA events on the launching
+ * stream; _gemm_times returns the sums of the last step: ms, algorithmic FLOP (2 M N K) and launch counts of the forward,
+ * data-gradient and weight-gradient GEMMs (bf16 engine).  No counterpart in the reference. */
+int fcnod_trainer_set_timing(fcnod_trainer* t, int on);
+int fcnod_trainer_gemm_times(fcnod_trainer* t, float ms[3], double flop[3], int launches[3]);
 /* The tcgen05 GEMM of the bf16 training engine on caller-provided DEVICE matrices (bf16, row-major, leading dimensions in
  * elements, rows 16-byte aligned).  No counterpart in the reference (it delegates to cuBLAS / cuDNN through Caffe).
  *   mode 0: out[M][N] (bf16, or float32 if out_f32) (+)= A[M][K] * B[N][K]^T (+ bias[N]) (ReLU)
