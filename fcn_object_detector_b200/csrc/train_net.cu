@@ -369,6 +369,11 @@ __global__ void adam_kernel(float* __restrict__ w, float* __restrict__ g, float*
     }
 }
 
+// Exact division of a small dividend by a run-time divisor through a precomputed reciprocal: q = (x * magic) >> 32 with
+// magic = ceil(2^32 / d) is exact for x < 2^16 (the per-row counts below), one multiply instead of an integer division.
+__host__ __device__ __forceinline__ unsigned div_magic(unsigned d) { return (unsigned)((0x100000000ull + d - 1) / d); }
+__device__ __forceinline__ unsigned div_fast(unsigned x, unsigned magic) { return __umulhi(x, magic); }
+
 // ------------------------------------------------------------------------------------------------ bf16 engine: 8 channels per thread
 // Same arithmetic as the generic kernels above on 16-byte groups of channels (all blobs of the network have C % 8 == 0 except
 // the 3-channel input and the two heads, which keep the generic kernels).
@@ -380,91 +385,110 @@ struct BF8 {
 __device__ __forceinline__ BF8 ld8(const bf16* p) { BF8 r; r.v = *reinterpret_cast<const uint4*>(p); return r; }
 __device__ __forceinline__ void st8(bf16* p, const BF8& r) { *reinterpret_cast<uint4*>(p) = r.v; }
 
-__global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g) {
-    const int cv = g.C / 8;
-    const unsigned total = (unsigned)((long)g.N * g.Ho * g.Wo * cv);
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
-        const int c = (int)(i % cv) * 8;
-        unsigned t = i / cv;
-        const int pw = (int)(t % g.Wo); t /= g.Wo;
-        const int ph = (int)(t % g.Ho);
-        const int n = (int)(t / g.Ho);
-        const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
-        const int hs = max(h0, 0), ws = max(w0, 0);
-        const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
-        float best[8];
-        int bi[8];
+__global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g, unsigned m_cv) {
+    // grid (groups of an output row, Ho, N): one thread per (output pixel, 8 channels)
+    const unsigned cv = (unsigned)g.C / 8u;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (unsigned)g.Wo * cv) return;
+    const int pw = (int)__umulhi(i, m_cv), c = (int)(i - (unsigned)pw * cv) * 8;
+    const int ph = blockIdx.y, n = blockIdx.z;
+    const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
+    const int hs = max(h0, 0), ws = max(w0, 0);
+    const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
+    float best[8];
+    int bi[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) { best[q] = -3.402823466e+38f; bi[q] = 0; }
-        for (int h = hs; h < he; ++h)
-            for (int w = ws; w < we; ++w) {
-                const BF8 v = ld8(x + ((long)(n * g.H + h) * g.W + w) * g.ldi + c);
-                const int loc = (h - h0) * g.k + (w - w0);
+    for (int q = 0; q < 8; ++q) { best[q] = -3.402823466e+38f; bi[q] = 0; }
+    const bf16* xn = x + (size_t)n * g.H * g.W * g.ldi + c;
+    for (int h = hs; h < he; ++h)
+        for (int w = ws; w < we; ++w) {
+            const BF8 v = ld8(xn + ((size_t)h * g.W + w) * g.ldi);
+            const int loc = (h - h0) * g.k + (w - w0);
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float f = v.get(q);
-                    if (f > best[q]) { best[q] = f; bi[q] = loc; }
-                }
+            for (int q = 0; q < 8; ++q) {
+                const float f = v.get(q);
+                if (f > best[q]) { best[q] = f; bi[q] = loc; }
             }
-        const long o = (long)(n * g.Ho + ph) * g.Wo + pw;
-        BF8 r;
-        uint2 ib;
+        }
+    const size_t o = ((size_t)n * g.Ho + ph) * g.Wo + pw;
+    BF8 r;
+    uint2 ib;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) { r.set(q, best[q]); reinterpret_cast<uint8_t*>(&ib)[q] = (uint8_t)bi[q]; }
-        st8(y + o * g.ldo + c, r);
-        *reinterpret_cast<uint2*>(idx + o * g.C + c) = ib;
-    }
+    for (int q = 0; q < 8; ++q) { r.set(q, best[q]); reinterpret_cast<uint8_t*>(&ib)[q] = (uint8_t)bi[q]; }
+    st8(y + o * g.ldo + c, r);
+    *reinterpret_cast<uint2*>(idx + o * g.C + c) = ib;
 }
 
-__global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, PoolGeo g, int accum) {
-    const int cv = g.C / 8;
-    const unsigned total = (unsigned)((long)g.N * g.H * g.W * cv);
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
-        const int c = (int)(i % cv) * 8;
-        unsigned t = i / cv;
-        const int w = (int)(t % g.W); t /= g.W;
-        const int h = (int)(t % g.H);
-        const int n = (int)(t / g.H);
-        const int ph0 = (h + g.p < g.k) ? 0 : (h + g.p - g.k) / g.s + 1, ph1 = min((h + g.p) / g.s + 1, g.Ho);
-        const int pw0 = (w + g.p < g.k) ? 0 : (w + g.p - g.k) / g.s + 1, pw1 = min((w + g.p) / g.s + 1, g.Wo);
-        float acc[8];
+__global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, PoolGeo g, int accum,
+                                 unsigned m_cv) {
+    // grid (groups of an input row, H, N): one thread per (input pixel, 8 channels)
+    const unsigned cv = (unsigned)g.C / 8u;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (unsigned)g.W * cv) return;
+    const int w = (int)__umulhi(i, m_cv), c = (int)(i - (unsigned)w * cv) * 8;
+    const int h = blockIdx.y, n = blockIdx.z;
+    const int ph0 = (h + g.p < g.k) ? 0 : (h + g.p - g.k) / g.s + 1, ph1 = min((h + g.p) / g.s + 1, g.Ho);
+    const int pw0 = (w + g.p < g.k) ? 0 : (w + g.p - g.k) / g.s + 1, pw1 = min((w + g.p) / g.s + 1, g.Wo);
+    float acc[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
-        for (int ph = ph0; ph < ph1; ++ph)
-            for (int pw = pw0; pw < pw1; ++pw) {
-                const long o = (long)(n * g.Ho + ph) * g.Wo + pw;
-                const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
-                const uint2 ib = *reinterpret_cast<const uint2*>(idx + o * g.C + c);
-                const BF8 d = ld8(dy + o * g.ldo + c);
+    for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+    for (int ph = ph0; ph < ph1; ++ph)
+        for (int pw = pw0; pw < pw1; ++pw) {
+            const size_t o = ((size_t)n * g.Ho + ph) * g.Wo + pw;
+            const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
+            const uint2 ib = *reinterpret_cast<const uint2*>(idx + o * g.C + c);
+            const BF8 d = ld8(dy + o * g.ldo + c);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                if (reinterpret_cast<const uint8_t*>(&ib)[q] == local) acc[q] += d.get(q);
+        }
+    bf16* o = dx + (((size_t)n * g.H + h) * g.W + w) * g.ldi + c;
+    BF8 r;
+    if (accum) {
+        r = ld8(o);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc[q] += r.get(q);
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) r.set(q, acc[q]);
+    st8(o, r);
+}
+
+// ReLU backward (in place on the convolution's top diff) and the bias gradient in one pass over dy: block = 8 channel groups
+// (64 channels) x 32 pixel lanes; db[c] += sum over the block's pixel chunk.  relu = 0: bias gradient only.
+__global__ void __launch_bounds__(256) relu_bias8_kernel(const bf16* __restrict__ y, bf16* __restrict__ dy, unsigned npix, int C, int ldc,
+                                                          unsigned chunk, int relu, float* __restrict__ db) {
+    __shared__ float red[32][65];
+    const int c = (blockIdx.x * 8 + threadIdx.x) * 8;
+    const unsigned p0 = blockIdx.y * chunk, p1 = min(p0 + chunk, npix);
+    float acc[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+    if (c < C)
+        for (unsigned p = p0 + threadIdx.y; p < p1; p += 32) {
+            const size_t o = (size_t)p * ldc + c;
+            BF8 d = ld8(dy + o);
+            if (relu) {
+                const BF8 a = ld8(y + o);
+                bool any = false;
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
-                    if (reinterpret_cast<const uint8_t*>(&ib)[q] == local) acc[q] += d.get(q);
+                    if (!(a.get(q) > 0.f)) { d.set(q, 0.f); any = true; }
+                if (any) st8(dy + o, d);
             }
-        bf16* o = dx + ((long)(n * g.H + h) * g.W + w) * g.ldi + c;
-        BF8 r;
-        if (accum) {
-            r = ld8(o);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) acc[q] += r.get(q);
+            for (int q = 0; q < 8; ++q) acc[q] += d.get(q);
         }
 #pragma unroll
-        for (int q = 0; q < 8; ++q) r.set(q, acc[q]);
-        st8(o, r);
-    }
-}
-
-__global__ void relu_mask8_kernel(const bf16* __restrict__ y, bf16* __restrict__ dy, long npix, int C, int ldc) {
-    const int cv = C / 8;
-    const unsigned total = (unsigned)(npix * cv);
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {      // 32-bit index arithmetic (checked on the host)
-        const long o = (i / cv) * ldc + (i % cv) * 8;
-        const BF8 a = ld8(y + o);
-        BF8 d = ld8(dy + o);
-        bool any = false;
+    for (int q = 0; q < 8; ++q) red[threadIdx.y][threadIdx.x * 8 + q] = acc[q];
+    __syncthreads();
+    const int tid = threadIdx.y * 8 + threadIdx.x;
+    if (tid < 64) {
+        float a = 0.f;
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-            if (!(a.get(q) > 0.f)) { d.set(q, 0.f); any = true; }
-        if (any) st8(dy + o, d);
+        for (int j = 0; j < 32; ++j) a += red[j][tid];
+        const int cc = blockIdx.x * 64 + tid;
+        if (cc < C) atomicAdd(db + cc, a);
     }
 }
 
@@ -491,7 +515,7 @@ __global__ void lrn_fwd8_kernel(const bf16* __restrict__ x, int ldi, bf16* __res
 #pragma unroll
             for (int d = 0; d < 5; ++d) s = fmaf(v[q + d], v[q + d], s);
             sc[q] = fmaf(alpha_over_n, s, k);
-            r.set(q, v[q + 2] * powf(sc[q], -beta));
+            r.set(q, v[q + 2] * __powf(sc[q], -beta));      // bf16 engine: fast exp2 / log2 (the result is rounded to 8 bits)
         }
         st8(y + px * ldo + c, r);
         float4* so = reinterpret_cast<float4*>(scale + px * C + c);
@@ -516,7 +540,7 @@ __global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16*
             ratio[q] = 0.f;
             if (cc >= 0 && cc < C) {
                 const float d = __bfloat162float(dy[px * ldo + cc]), s = scale[px * C + cc];
-                ratio[q] = d * __bfloat162float(y[px * ldo + cc]) / s;
+                ratio[q] = __fdividef(d * __bfloat162float(y[px * ldo + cc]), s);
                 if (q >= 2 && q < 10) { sc[q - 2] = s; dyv[q - 2] = d; }
             }
         }
@@ -527,7 +551,7 @@ __global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16*
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
             const float s = ratio[q] + ratio[q + 1] + ratio[q + 2] + ratio[q + 3] + ratio[q + 4];
-            float v = dyv[q] * powf(sc[q], -beta) - cr * xv.get(q) * s;
+            float v = dyv[q] * __powf(sc[q], -beta) - cr * xv.get(q) * s;
             if (accum) v += r.get(q);
             r.set(q, v);
         }
@@ -536,11 +560,6 @@ __global__ void lrn_bwd8_kernel(const bf16* __restrict__ x, int ldi, const bf16*
 }
 
 // ------------------------------------------------------------------------------------------------ bf16 engine helpers
-// Exact division of a small dividend by a run-time divisor through a precomputed reciprocal: q = (x * magic) >> 32 with
-// magic = ceil(2^32 / d) is exact for x < 2^16 (the per-row counts below), one multiply instead of an integer division.
-__host__ __device__ __forceinline__ unsigned div_magic(unsigned d) { return (unsigned)((0x100000000ull + d - 1) / d); }
-__device__ __forceinline__ unsigned div_fast(unsigned x, unsigned magic) { return __umulhi(x, magic); }
-
 // im2col for the tensor-core GEMMs: col[px][(r*k + s)*Cin + c] = x[n][oh*stride - pad + r][ow*stride - pad + s][c] (0 outside),
 // rows of ldk elements (Kc rounded up to 8: a TMA row pitch is a multiple of 16 bytes; the padding columns are zeroed).
 // One thread per 16-byte group of a row; grid = (groups of an output row, Ho, N): no division for the pixel coordinates.
@@ -1279,7 +1298,8 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
             if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
-                pool_fwd8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g);
+                pool_fwd8_kernel<<<dim3((ob.W * (ob.C / 8) + 255) / 256, ob.H, N), 256, 0, s>>>(as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g,
+                                                                                                  div_magic((unsigned)ob.C / 8u));
             else
                 pool_fwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), as<T>(bdata(t, ob)), L.idx, g);
             break;
@@ -1344,7 +1364,8 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
             if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
-                pool_bwd8_kernel<<<grid1(in_px * (ib.C / 8), 256), 256, 0, s>>>(as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g, claim_diff(t, L.in));
+                pool_bwd8_kernel<<<dim3((ib.W * (ib.C / 8) + 255) / 256, ib.H, N), 256, 0, s>>>(as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g,
+                                                                                                 claim_diff(t, L.in), div_magic((unsigned)ib.C / 8u));
             else
                 pool_bwd_kernel<T><<<grid1(in_px * ib.C, 256), 256, 0, s>>>(as<T>(bdiff(t, ob)), L.idx, as<T>(bdiff(t, ib)), g, claim_diff(t, L.in));
             break;
@@ -1362,14 +1383,18 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
         case L_CONV: {
             const TConv& c = t->convs[L.conv];
             T* dy = as<T>(bdiff(t, ob));
-            if (L.relu) {
-                if (tcp && ob.C % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
-                    relu_mask8_kernel<<<grid1(out_px * (ob.C / 8), 256), 256, 0, s>>>(as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), out_px, ob.C, ob.ldc);
-                else
-                    relu_mask_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ob)), dy, out_px, ob.C, ob.ldc);
+            if (tcp && ob.C % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0) {
+                // ReLU mask and bias gradient in one pass
+                const unsigned chunk = (unsigned)std::max<long>(512, (out_px + 147 * 2) / (148 * 2));
+                dim3 grid((unsigned)((c.Cout + 63) / 64), (unsigned)((out_px + chunk - 1) / chunk));
+                relu_bias8_kernel<<<grid, dim3(8, 32), 0, s>>>(as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), (unsigned)out_px, c.Cout, ob.ldc, chunk,
+                                                              L.relu ? 1 : 0, t->grads + c.b_off);
                 FCNOD_CUDA(cudaGetLastError());
-            }
-            {   // bias
+            } else {
+                if (L.relu) {
+                    relu_mask_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ob)), dy, out_px, ob.C, ob.ldc);
+                    FCNOD_CUDA(cudaGetLastError());
+                }
                 const long chunk = std::max<long>(256, (out_px + 147) / 148);
                 dim3 grid((unsigned)((c.Cout + 31) / 32), (unsigned)((out_px + chunk - 1) / chunk));
                 bias_grad_kernel<T><<<grid, dim3(32, 8), 0, s>>>(dy, ob.ldc, c.Cout, out_px, chunk, t->grads + c.b_off);
