@@ -275,3 +275,46 @@ def test_bf16_tensor_core_engine_against_the_oracle_and_the_fp32_engine(train_fi
             s.close()
     assert out['bf16'][-1] < 0.8 * out['bf16'][0], out
     assert abs(out['bf16'][0] - out['fp32'][0]) < 2e-2 * out['fp32'][0], out
+
+
+def test_three_class_network_of_train_val2(tmp_path):
+    """models/train_val2.prototxt: the same network with 3 classes (heads of 3 / 12 channels, slice points 3 / 15 / 27 / 39).
+    fp32 engine against the oracle on the losses, the head gradients and the first convolution's gradient; the bf16 engine
+    runs the same step (its 12-channel regressor stays on the SIMT kernels) within 2e-2 of the fp32 losses."""
+    import torch
+    from fcn_object_detector_b200 import netspec
+    from fcn_object_detector_b200.caffemodel import write_synthetic_caffemodel
+    from fcn_object_detector_b200.trainer import Solver
+    C3 = 3
+    proto = netspec.write_train_val_prototxt(str(tmp_path / 'train_val2.prototxt'), num_classes=C3)
+    cm = write_synthetic_caffemodel(str(tmp_path / 'init3.caffemodel'), seed=5, num_cvg=C3, num_bbox=4 * C3)
+    layers = prototxt.layers(prototxt.parse(open(proto).read()))
+    weights = {k: [np.asarray(a, np.float32) for a in v] for k, v in _oracle_weights(cm).items()}
+    rs = np.random.RandomState(9)
+    data = rs.uniform(0, 255, (N, 3, H, W)).astype(np.float32)
+    cvg = (rs.uniform(0, 1, (N, C3, GH, GW)) > 0.8).astype(np.float32)
+    blk = np.repeat(cvg, 4, axis=1)
+    grids = (cvg, (rs.uniform(-30, 30, (N, 4 * C3, GH, GW)) * blk).astype(np.float32), (blk / 64.0).astype(np.float32),
+             (blk / 6.0).astype(np.float32), blk.astype(np.float32))
+    dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+    losses = {}
+    for prec in ('fp32', 'bf16'):
+        s = Solver(proto, cm, batch=N, height=H, width=W, seed=11, precision=prec)
+        try:
+            assert s.num_classes == C3
+            s.forward_backward_device([t.data_ptr() for t in dev])
+            torch.cuda.synchronize()
+            losses[prec] = s.losses()
+            if prec == 'fp32':
+                argmax = {L['name']: s.pool_argmax(L['name']) for L in layers if L['type'] == 'Pooling'}
+                ref = train_net_ref.forward_backward(layers, weights, data, grids, dropout_mask=s.dropout_mask(), pool_argmax=argmax)
+                assert abs(losses[prec]['loss_bbox'] - ref['loss_bbox']) <= 1e-5 * max(1.0, abs(ref['loss_bbox']))
+                assert abs(losses[prec]['loss_coverage'] - ref['loss_coverage']) <= 1e-5 * max(1.0, abs(ref['loss_coverage']))
+                for name in ('bbox/regressor', 'cvg/classifier', 'inception_4c/3x3', 'conv1/7x7_s2'):
+                    gw, gb = ref['grads'][name]
+                    assert rel_err(s.param(name, 0, 'grad').reshape(gw.shape), gw) < 2e-4, name
+                    assert rel_err(s.param(name, 1, 'grad'), gb) < 2e-4, name
+        finally:
+            s.close()
+    for k in ('loss_bbox', 'loss_coverage'):
+        assert abs(losses['bf16'][k] - losses['fp32'][k]) < 2e-2 * max(1.0, abs(losses['fp32'][k])), (k, losses)

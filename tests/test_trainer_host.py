@@ -35,6 +35,20 @@ def test_generated_train_val_matches_the_reference_layer_for_layer():
         assert [p for p in a.get('param', [])] == [p for p in b.get('param', [])], a.get('name')
 
 
+def test_generated_three_class_train_val_matches_train_val2():
+    from fcn_object_detector_b200 import netspec
+    path = os.path.join(REF, 'models', 'train_val2.prototxt')
+    if not os.path.exists(path):
+        pytest.skip('upstream tree not reachable')
+    ours, theirs = _records(netspec.train_val_prototxt(num_classes=3)), _records(open(path).read())
+    assert len(ours) == len(theirs)
+    for a, b in zip(ours, theirs):
+        assert a == b, (a, b)
+    sl = [x for x in prototxt.parse(netspec.train_val_prototxt(num_classes=3))['layer'] if x.get('type') == ['Slice']][0]
+    up = [x for x in prototxt.parse(open(path).read())['layer'] if x.get('type') == ['Slice']][0]
+    assert sl['slice_param'][0]['slice_point'] == up['slice_param'][0]['slice_point'] == [3, 15, 27, 39]
+
+
 def test_solver_prototxt_values(tmp_path):
     from fcn_object_detector_b200 import netspec
     from fcn_object_detector_b200.trainer import read_solver_prototxt
