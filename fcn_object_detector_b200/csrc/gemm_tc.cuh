@@ -254,10 +254,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             auto process = [&](const uint32_t (&rr)[16], const uint4 (&oldv)[2], int ch) {
                 const int c0 = 16 * ch, n = n0 + c0;
                 if (MNMAJ) {
-                    if (row_ok) {
+                    // gout[n][m]: consecutive ROWS of the tile (lanes) are contiguous in memory.  4x4 transposes inside groups of
+                    // four lanes (two shuffle steps) leave lane g of a group with column 4t + g of the group's four rows: one
+                    // 16-byte red.global.add.v4.f32 instead of four scalar ones (the reductions are the cost of this epilogue).
+                    const int g = lane & 3, b = g & 1;
+                    const int mg = m0 + q * 32 + (lane & ~3);
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (n + j < p.N) atomicAdd(p.gout + (long)(n + j) * p.ldg + row, __uint_as_float(rr[j]));
+                    for (int t = 0; t < 4; ++t) {
+                        const float a0 = __uint_as_float(rr[4 * t]), a1 = __uint_as_float(rr[4 * t + 1]);
+                        const float a2 = __uint_as_float(rr[4 * t + 2]), a3 = __uint_as_float(rr[4 * t + 3]);
+                        const bool hi = (g & 2) != 0;
+                        const float x0 = hi ? a2 : a0, x1 = hi ? a3 : a1;                 // the column pair this lane keeps
+                        const float y0 = __shfl_xor_sync(0xffffffffu, hi ? a0 : a2, 2), y1 = __shfl_xor_sync(0xffffffffu, hi ? a1 : a3, 2);
+                        const float xb = b ? x1 : x0, yb = b ? y1 : y0;                   // the column this lane ends up with
+                        const float rx = __shfl_xor_sync(0xffffffffu, b ? x0 : x1, 1), ry = __shfl_xor_sync(0xffffffffu, b ? y0 : y1, 1);
+                        // rows: own = g (xb), g ^ 2 (yb), g ^ 1 (rx), g ^ 3 (ry)
+                        float o[4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) o[r] = r == g ? xb : (r == (g ^ 2) ? yb : (r == (g ^ 1) ? rx : ry));
+                        const int col = n + 4 * t + g;
+                        if (col < p.N && mg < p.ldg)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.gout + (long)col * p.ldg + mg), "f"(o[0]), "f"(o[1]),
+                                         "f"(o[2]), "f"(o[3]) : "memory");
                     }
                 } else if (row_ok) {
                     float v[16];
