@@ -395,27 +395,30 @@ __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
     const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
     const int hs = max(h0, 0), ws = max(w0, 0);
     const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
-    float best[8];
-    int bi[8];
+    // Two channels per instruction: the values ARE bf16, so a bf16 compare is exact; `>` against the lowest finite bf16 keeps the
+    // first maximum in scan order (Caffe's rule), the window position travels in the same 16-bit lanes.
+    uint32_t best[4], bi[4];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) { best[q] = -3.402823466e+38f; bi[q] = 0; }
+    for (int q = 0; q < 4; ++q) { best[q] = 0xff7fff7fu; bi[q] = 0u; }
     const bf16* xn = x + (size_t)n * g.H * g.W * g.ldi + c;
     for (int h = hs; h < he; ++h)
         for (int w = ws; w < we; ++w) {
-            const BF8 v = ld8(xn + ((size_t)h * g.W + w) * g.ldi);
-            const int loc = (h - h0) * g.k + (w - w0);
+            const uint4 v = *reinterpret_cast<const uint4*>(xn + ((size_t)h * g.W + w) * g.ldi);
+            const uint32_t loc2 = (uint32_t)((h - h0) * g.k + (w - w0)) * 0x00010001u;
+            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const float f = v.get(q);
-                if (f > best[q]) { best[q] = f; bi[q] = loc; }
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t m = __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&vv[q]), *reinterpret_cast<const __nv_bfloat162*>(&best[q]));
+                best[q] = (vv[q] & m) | (best[q] & ~m);
+                bi[q] = (loc2 & m) | (bi[q] & ~m);
             }
         }
     const size_t o = ((size_t)n * g.Ho + ph) * g.Wo + pw;
-    BF8 r;
+    *reinterpret_cast<uint4*>(y + o * g.ldo + c) = make_uint4(best[0], best[1], best[2], best[3]);
+    // positions: low bytes of the eight 16-bit lanes -> eight consecutive bytes
     uint2 ib;
-#pragma unroll
-    for (int q = 0; q < 8; ++q) { r.set(q, best[q]); reinterpret_cast<uint8_t*>(&ib)[q] = (uint8_t)bi[q]; }
-    st8(y + o * g.ldo + c, r);
+    ib.x = __byte_perm(bi[0], bi[1], 0x6420);
+    ib.y = __byte_perm(bi[2], bi[3], 0x6420);
     *reinterpret_cast<uint2*>(idx + o * g.C + c) = ib;
 }
 
@@ -437,10 +440,18 @@ __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __r
             const size_t o = ((size_t)n * g.Ho + ph) * g.Wo + pw;
             const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
             const uint2 ib = *reinterpret_cast<const uint2*>(idx + o * g.C + c);
-            const BF8 d = ld8(dy + o * g.ldo + c);
+            const uint4 d = *reinterpret_cast<const uint4*>(dy + o * g.ldo + c);
+            // per-byte equality with the wanted position (0xff where equal), widened to the 16-bit lanes of the gradients;
+            // a bf16 is the high half of its float
+            const uint32_t want = (uint32_t)local * 0x01010101u;
+            const uint32_t e0 = __vcmpeq4(ib.x, want), e1 = __vcmpeq4(ib.y, want);
+            const uint32_t dd[4] = {d.x & __byte_perm(e0, 0, 0x1100), d.y & __byte_perm(e0, 0, 0x3322), d.z & __byte_perm(e1, 0, 0x1100),
+                                    d.w & __byte_perm(e1, 0, 0x3322)};
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-                if (reinterpret_cast<const uint8_t*>(&ib)[q] == local) acc[q] += d.get(q);
+            for (int q = 0; q < 4; ++q) {
+                acc[2 * q] += __uint_as_float(dd[q] << 16);
+                acc[2 * q + 1] += __uint_as_float(dd[q] & 0xffff0000u);
+            }
         }
     bf16* o = dx + (((size_t)n * g.H + h) * g.W + w) * g.ldi + c;
     BF8 r;
