@@ -555,6 +555,9 @@ def main():
                     help="detect = BASELINE config 3 / 4 (the headline metric); train = BASELINE config 5 (bench_train.py)")
     ap.add_argument('--train-precision', default='bf16', choices=['fp32', 'bf16'],
                     help='--workload train: fp32 = SIMT parity engine, bf16 = tcgen05 GEMM engine (fp32 master weights)')
+    ap.add_argument('--train-collective', default='peer', choices=['peer', 'nccl'],
+                    help='--workload train, N > 1: peer = reduce-scatter + ADAM + all-gather in one kernel over NVLink peer memory; '
+                         'nccl = all-reduce of the gradient buffer + update')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-extras', action='store_true', help='skip the layer / latency / bandwidth-kernel sections')
     args = ap.parse_args()

@@ -125,7 +125,8 @@ def run_ours(args, section=False):
     tops = [torch.empty(s, device='cuda') for s in [(B, 3, NET, NET), (B, 1, g, g)] + [(B, 4, g, g)] * 4]
     rects = torch.empty((B, 4), dtype=torch.int32, device='cuda')
     scr = torch.empty(int(L.fcnod_aug_scratch_bytes(B)), dtype=torch.uint8, device='cuda')
-    grads = torch.as_tensor(solver.grad_buffer(), device='cuda:%d' % local)
+    coll = getattr(args, 'train_collective', 'peer') if world > 1 else 'none'
+    dp = DataParallelSolver(solver, collective=coll) if world > 1 else None
     losses_host = np.zeros(2, np.float32)
 
     def aug():
@@ -135,15 +136,15 @@ def run_ours(args, section=False):
     def fwd_bwd():
         solver.forward_backward_device([t.data_ptr() for t in tops], stream=stream)
 
-    def allreduce():
-        if world > 1:
-            dist.all_reduce(grads, op=dist.ReduceOp.SUM)
-
     def update():
-        solver.apply_update(allreduce_scale(world), stream=stream)
+        solver.apply_update(1.0, stream=stream)
 
     def step():
-        aug(); fwd_bwd(); allreduce(); update()
+        aug()
+        if dp is not None:
+            dp.step_device([t.data_ptr() for t in tops])       # forward + backward + collective + update
+        else:
+            fwd_bwd(); update()
 
     def barrier():
         torch.cuda.synchronize()
@@ -234,7 +235,7 @@ def run_ours(args, section=False):
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if prec == 'fp32' else 'bf16', 'data': 'synthetic',
             'config': {'workload': 'train_val.prototxt training step, batch %d/GPU @448x448: DataArgumentationLayer forward on the '
                                    'device (480x640 sources) + TRAIN forward + loss head + backward + %s + ADAM (solver.prototxt '
-                                   'values), %s' % (B, 'NCCL all-reduce of %d fp32 gradients' % solver.n_params if world > 1
+                                   'values), %s' % (B, ('NCCL all-reduce of %d fp32 gradients' % solver.n_params if coll == 'nccl' else 'reduce-scatter + ADAM + all-gather of %d fp32 parameters in one kernel over NVLink peer memory' % solver.n_params) if world > 1
                                                                          else 'no all-reduce (1 GPU)',
                                                                          'fp32 SIMT parity engine' if prec == 'fp32' else
                                                                          'bf16 engine: convolutions as tcgen05 GEMMs (forward, dgrad, wgrad), fp32 master weights'),
@@ -242,7 +243,9 @@ def run_ours(args, section=False):
             'losses_after_timed_steps': l0,
             'e2e': {'value': e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8, 'steps': e_steps,
                     'api': 'pinned host sources / labels / draws -> fcnod_aug_forward_device -> fcnod_trainer_forward_backward_device '
-                           '-> all_reduce -> fcnod_trainer_apply_update -> fcnod_trainer_losses'},
+                           '-> %s -> fcnod_trainer_losses' % {'none': 'fcnod_trainer_apply_update', 'nccl': 'all_reduce -> fcnod_trainer_apply_update',
+                                                               'peer': 'fcnod_trainer_apply_update_peer'}[coll]},
+            'collective': coll,
             'gpu_launches': launches * steps,
             'phases': phases,
             'roofline': ({'bound': 'tensor', 'kernel': 'gemm_tc_kernel (tcgen05; %d launches per step: forward %d, data gradient %d, weight '

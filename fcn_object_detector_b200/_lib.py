@@ -126,6 +126,9 @@ SIGNATURES = {
     'fcnod_trainer_forward_backward_device': (_I, [_P] * 7 + [_P]),
     'fcnod_trainer_apply_update': (_I, [_P, C.c_float, _P]),
     'fcnod_trainer_losses': (_I, [_P, _P, _P]),
+    'fcnod_trainer_ipc_handles': (_I, [_P, _P, _P]),
+    'fcnod_trainer_open_peers': (_I, [_P, _I, _I, _P, _P]),
+    'fcnod_trainer_apply_update_peer': (_I, [_P, _P]),
     'fcnod_trainer_iteration': (_I, [_P]),
     'fcnod_trainer_step': (_I, [_P] * 8),
     'fcnod_trainer_param_read': (_I, [_P, _STR, _I, _I, _P, C.POINTER(_SZ)]),

@@ -763,6 +763,48 @@ __global__ void pack_wf_kernel(const float* __restrict__ P, int ldw, bf16* __res
     }
 }
 
+// ------------------------------------------------------------------------------------------------ data-parallel update over peer memory
+// Reduce-scatter + ADAM + all-gather in ONE kernel over NVLink peer memory (the gradient buffers and the parameter buffers of
+// all ranks of the node are mapped into every process through CUDA IPC): rank r owns the r-th shard of the flat buffers; it
+// sums the shard of every rank's gradient buffer (peer loads, rank order: the same sum on every run), applies Caffe's
+// ApplyUpdate to its shard (ADAM moments are kept only by the owner), and stores the updated parameters into every rank's
+// parameter buffer (peer stores).  No intermediate buffer, no second pass over the gradients, no separate update launch.
+// The caller orders the kernel between two stream-ordered barriers (all ranks finished their backward / all ranks wrote).
+constexpr int kMaxPeers = 8;
+struct PeerPtrs { const float* grads[kMaxPeers]; float* params[kMaxPeers]; };
+
+__global__ void peer_reduce_adam_kernel(PeerPtrs pp, int world, int rank, float* __restrict__ own_grads, float* __restrict__ m,
+                                        float* __restrict__ v, const float2* __restrict__ meta, long begin, long end, AdamArgs a) {
+    const long n4 = (end - begin) / 4;
+    for (long i4 = blockIdx.x * (long)blockDim.x + threadIdx.x; i4 < n4; i4 += (long)gridDim.x * blockDim.x) {
+        const long i = begin + 4 * i4;
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < world; ++j) {
+            const float4 t = *reinterpret_cast<const float4*>(pp.grads[j] + i);
+            g.x = __fadd_rn(g.x, t.x); g.y = __fadd_rn(g.y, t.y); g.z = __fadd_rn(g.z, t.z); g.w = __fadd_rn(g.w, t.w);
+        }
+        const float2 mt = meta[i >> 8];
+        const float4 w4 = *reinterpret_cast<const float4*>(pp.params[rank] + i);
+        float4 m4 = *reinterpret_cast<const float4*>(m + i), v4 = *reinterpret_cast<const float4*>(v + i);
+        float gg[4] = {g.x, g.y, g.z, g.w}, ww[4] = {w4.x, w4.y, w4.z, w4.w}, mm[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float gi = __fmul_rn(gg[q], a.grad_scale);
+            gi = __fadd_rn(gi, __fmul_rn(__fmul_rn(a.weight_decay, mt.y), ww[q]));
+            mm[q] = __fadd_rn(__fmul_rn(a.b1, mm[q]), __fmul_rn(1.f - a.b1, gi));
+            vv[q] = __fadd_rn(__fmul_rn(a.b2, vv[q]), __fmul_rn(1.f - a.b2, __fmul_rn(gi, gi)));
+            const float step = __fmul_rn(__fmul_rn(__fmul_rn(a.rate, mt.x), a.correction), __fdiv_rn(mm[q], __fadd_rn(__fsqrt_rn(vv[q]), a.eps)));
+            ww[q] = __fsub_rn(ww[q], step);
+            gg[q] = gi;
+        }
+        *reinterpret_cast<float4*>(m + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(v + i) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(own_grads + i) = make_float4(gg[0], gg[1], gg[2], gg[3]);
+        const float4 wn = make_float4(ww[0], ww[1], ww[2], ww[3]);
+        for (int j = 0; j < world; ++j) *reinterpret_cast<float4*>(pp.params[j] + i) = wn;
+    }
+}
+
 }  // namespace
 }  // namespace fcnod
 
@@ -840,6 +882,11 @@ struct fcnod_trainer {
     uint8_t* mask_nchw = 0;
     float* stage = 0;                         // host-buffer step: device copies of the inputs
     int iter = 0;
+    // data-parallel update over peer memory (fcnod_trainer_open_peers)
+    int world = 1, rank = 0;
+    float* peer_grads[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    float* peer_params[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool peers_open = false;
     cudaStream_t stream = 0;
     std::vector<void*> allocs;
 };
@@ -1522,6 +1569,8 @@ int fcnod_trainer_destroy(fcnod_trainer* t) {
     if (t) {
         cudaSetDevice(t->device);
         cudaDeviceSynchronize();
+        for (int j = 0; j < t->world && t->peers_open; ++j)
+            if (j != t->rank) { cudaIpcCloseMemHandle(t->peer_params[j]); cudaIpcCloseMemHandle(t->peer_grads[j]); }
         for (size_t i = 0; i < t->allocs.size(); ++i) cudaFree(t->allocs[i]);
         if (t->stream) cudaStreamDestroy(t->stream);
         delete t;
@@ -1582,19 +1631,79 @@ int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, c
     FCNOD_API_END
 }
 
+static AdamArgs adam_args(const fcnod_trainer* t, float grad_scale);
+
 int fcnod_trainer_apply_update(fcnod_trainer* t, float grad_scale, void* stream) {
     FCNOD_API_BEGIN
     FCNOD_CHECK(t, "null argument");
     FCNOD_CUDA(cudaSetDevice(t->device));
     cudaStream_t s = (cudaStream_t)stream;      // NULL = the legacy default stream, as everywhere in this ABI
+    const AdamArgs a = adam_args(t, grad_scale);
+    adam_kernel<<<grid1((long)t->n_params, 256), 256, 0, s>>>(t->params, t->grads, t->m, t->v, t->meta, (long)t->n_params, a);
+    FCNOD_CUDA(cudaGetLastError());
+    ++t->iter;
+    FCNOD_API_END
+}
+
+static AdamArgs adam_args(const fcnod_trainer* t, float grad_scale) {
     const fcnod_solver_params& sp = t->solver;
     AdamArgs a;
     const int tt = t->iter + 1;
     a.rate = (float)((double)sp.base_lr * std::pow((double)sp.gamma, (double)(sp.stepsize > 0 ? t->iter / sp.stepsize : 0)));
     a.correction = (float)(std::sqrt(1.0 - std::pow((double)sp.momentum2, (double)tt)) / (1.0 - std::pow((double)sp.momentum, (double)tt)));
     a.b1 = sp.momentum; a.b2 = sp.momentum2; a.eps = sp.delta; a.weight_decay = sp.weight_decay; a.grad_scale = grad_scale;
-    adam_kernel<<<grid1((long)t->n_params, 256), 256, 0, s>>>(t->params, t->grads, t->m, t->v, t->meta, (long)t->n_params, a);
-    FCNOD_CUDA(cudaGetLastError());
+    return a;
+}
+
+int fcnod_trainer_ipc_handles(fcnod_trainer* t, void* params_handle, void* grads_handle) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && params_handle && grads_handle, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    cudaIpcMemHandle_t h;
+    FCNOD_CUDA(cudaIpcGetMemHandle(&h, t->params));
+    memcpy(params_handle, &h, 64);
+    FCNOD_CUDA(cudaIpcGetMemHandle(&h, t->grads));
+    memcpy(grads_handle, &h, 64);
+    FCNOD_API_END
+}
+
+int fcnod_trainer_open_peers(fcnod_trainer* t, int world, int rank, const void* params_handles, const void* grads_handles) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && params_handles && grads_handles, "null argument");
+    FCNOD_CHECK(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "trainer: the peer update supports 1..8 ranks of one node");
+    FCNOD_CHECK(!t->peers_open, "trainer: peers are already open");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    for (int j = 0; j < world; ++j) {
+        if (j == rank) { t->peer_params[j] = t->params; t->peer_grads[j] = t->grads; continue; }
+        cudaIpcMemHandle_t h;
+        void* p = 0;
+        memcpy(&h, static_cast<const char*>(params_handles) + 64 * j, 64);
+        FCNOD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        t->peer_params[j] = static_cast<float*>(p);
+        memcpy(&h, static_cast<const char*>(grads_handles) + 64 * j, 64);
+        FCNOD_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        t->peer_grads[j] = static_cast<float*>(p);
+    }
+    t->world = world; t->rank = rank; t->peers_open = true;
+    FCNOD_API_END
+}
+
+int fcnod_trainer_apply_update_peer(fcnod_trainer* t, void* stream) {
+    FCNOD_API_BEGIN
+    FCNOD_CHECK(t && t->peers_open, "trainer: fcnod_trainer_open_peers has not been called");
+    FCNOD_CUDA(cudaSetDevice(t->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const long blocks256 = (long)(t->n_params / 256);
+    const long per = (blocks256 + t->world - 1) / t->world;
+    const long begin = std::min(blocks256, per * t->rank) * 256, end = std::min(blocks256, per * (t->rank + 1)) * 256;
+    PeerPtrs pp;
+    for (int j = 0; j < kMaxPeers; ++j) { pp.grads[j] = j < t->world ? t->peer_grads[j] : 0; pp.params[j] = j < t->world ? t->peer_params[j] : 0; }
+    if (end > begin) {
+        peer_reduce_adam_kernel<<<grid1((end - begin) / 4, 256), 256, 0, s>>>(pp, t->world, t->rank, t->grads, t->m, t->v, t->meta, begin, end,
+                                                                             adam_args(t, 1.f / (float)t->world));
+        FCNOD_CUDA(cudaGetLastError());
+    }
     ++t->iter;
     FCNOD_API_END
 }

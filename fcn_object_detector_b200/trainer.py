@@ -234,22 +234,56 @@ def allreduce_scale(world_size):
 
 class DataParallelSolver(object):
     """One process per GPU inside an initialised `torch.distributed` group (NCCL on the GPUs).  Every rank holds a full
-    replica; per iteration: forward + backward on the rank's minibatch, ONE in-place all-reduce (SUM) of the flat gradient
-    buffer, ApplyUpdate with grad_scale = 1 / world_size.  Ranks start from the same snapshot, so replicas stay identical."""
+    replica and runs forward + backward on its own minibatch; then, per iteration,
 
-    def __init__(self, solver, group=None):
+    collective='nccl': ONE in-place all-reduce (SUM) of the flat gradient buffer, ApplyUpdate with grad_scale = 1 / world_size
+                       (Caffe's NCCL solver's rule);
+    collective='peer': ONE kernel per rank over NVLink peer memory (the ranks' gradient and parameter buffers are mapped into
+                       every process through CUDA IPC): the rank sums its shard of all gradient buffers, updates the shard
+                       (ADAM moments live only on the owner) and stores the new parameters into every replica -- reduce-scatter,
+                       update and all-gather without an intermediate buffer.  Two one-element all-reduces bracket it as
+                       stream-ordered barriers.  One node, at most 8 ranks.
+
+    Ranks start from the same snapshot, so replicas stay identical (bit for bit with 'peer': every replica receives the same
+    stored values)."""
+
+    def __init__(self, solver, group=None, collective='nccl'):
         import torch
         import torch.distributed as dist
         self.solver = solver
         self.dist = dist
         self.group = group
         self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.collective = collective if self.world > 1 else 'nccl'
         self.grads = torch.as_tensor(solver.grad_buffer(), device='cuda:%d' % solver.device)
+        if self.collective == 'peer':
+            L = _lib.lib()
+            hp, hg = C.create_string_buffer(64), C.create_string_buffer(64)
+            _lib.check(L.fcnod_trainer_ipc_handles(solver.handle, hp, hg))
+            mine = (bytes(hp.raw), bytes(hg.raw))
+            allh = [None] * self.world
+            dist.all_gather_object(allh, mine, group=group)
+            ps = b''.join(h[0] for h in allh)
+            gs = b''.join(h[1] for h in allh)
+            _lib.check(L.fcnod_trainer_open_peers(solver.handle, self.world, self.rank, ps, gs))
+            self._flag = torch.zeros(1, device='cuda:%d' % solver.device)
+        elif self.collective != 'nccl':
+            raise ValueError("collective must be 'nccl' or 'peer'")
+
+    def _barrier(self):
+        # stream-ordered: the next kernel on this stream starts only after every rank has reached this point on its stream
+        self.dist.all_reduce(self._flag, op=self.dist.ReduceOp.SUM, group=self.group)
 
     def step_device(self, ptrs):
         import torch
         s = torch.cuda.current_stream().cuda_stream
         self.solver.forward_backward_device(ptrs, stream=s)
+        if self.collective == 'peer':
+            self._barrier()                  # every rank's gradients are complete
+            _lib.check(_lib.lib().fcnod_trainer_apply_update_peer(self.solver.handle, C.c_void_p(s)))
+            self._barrier()                  # every rank's shard has been stored into this replica
+            return
         if self.world > 1:
             self.dist.all_reduce(self.grads, op=self.dist.ReduceOp.SUM, group=self.group)
         self.solver.apply_update(allreduce_scale(self.world), stream=s)

@@ -338,6 +338,17 @@ int fcnod_trainer_buffers(fcnod_trainer* t, float** params, float** grads, float
 int fcnod_trainer_forward_backward_device(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label,
                                           const float* size_block, const float* obj_block, const float* cvg_block, void* stream);
 int fcnod_trainer_apply_update(fcnod_trainer* t, float grad_scale, void* stream);
+/* Data-parallel update over NVLink peer memory (one process per GPU on one node; replaces NCCL all-reduce + apply_update):
+ * every rank exports its parameter and gradient buffers (_ipc_handles: two 64-byte CUDA IPC handles), the handles of all
+ * ranks are exchanged by the host (trainer.DataParallelSolver does it over torch.distributed) and opened (_open_peers).
+ * _apply_update_peer is then ONE kernel per rank: it sums its shard of every rank's gradient buffer through peer loads,
+ * applies ApplyUpdate (scaled by 1 / world) to that shard -- ADAM moments exist only on the shard's owner -- and stores the
+ * new parameters into every rank's parameter buffer through peer stores.  The caller must order it between two
+ * stream-ordered barriers: after every rank's backward, and before any rank's next forward. */
+int fcnod_trainer_ipc_handles(fcnod_trainer* t, void* params_handle /* 64 bytes */, void* grads_handle /* 64 bytes */);
+int fcnod_trainer_open_peers(fcnod_trainer* t, int world, int rank, const void* params_handles /* world x 64 bytes */,
+                             const void* grads_handles);
+int fcnod_trainer_apply_update_peer(fcnod_trainer* t, void* stream);
 int fcnod_trainer_losses(fcnod_trainer* t, float losses[2] /* loss_bbox (unweighted), loss_coverage */, void* stream);
 int fcnod_trainer_iteration(const fcnod_trainer* t);
 int fcnod_trainer_step(fcnod_trainer* t, const float* data, const float* cvg_label, const float* bbox_label, const float* size_block,
