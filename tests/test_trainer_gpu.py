@@ -335,3 +335,43 @@ def test_peer_memory_update_matches_the_nccl_path_on_two_gpus():
                        timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert 'replicas identical nccl=True peer=True' in r.stdout
+
+
+def test_full_size_448_step_against_the_oracle(train_files):
+    """BASELINE config 5's geometry (448x448, 28x28 label grids), one frame: fp32 engine losses at 1e-5 and the gradients of the
+    first, a middle and the last convolutions at 2e-4; bf16 engine losses at 1e-2."""
+    import torch
+    from fcn_object_detector_b200.trainer import Solver
+    proto, cm, sp = train_files
+    layers = prototxt.layers(prototxt.parse(open(proto).read()))
+    weights = {k: [np.asarray(a, np.float32) for a in v] for k, v in _oracle_weights(cm).items()}
+    rs = np.random.RandomState(21)
+    data = rs.uniform(0, 255, (1, 3, 448, 448)).astype(np.float32)
+    cvg = np.zeros((1, 1, 28, 28), np.float32)
+    cvg[0, 0, 9:15, 11:19] = 1
+    blk = np.repeat(cvg, 4, axis=1)
+    grids = (cvg, (rs.uniform(-60, 60, (1, 4, 28, 28)) * blk).astype(np.float32), (blk / 128.0).astype(np.float32), (blk / 48.0).astype(np.float32), blk)
+    dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+    ref = None
+    for prec in ('fp32', 'bf16'):
+        s = Solver(proto, cm, batch=1, height=448, width=448, solver_prototxt=sp, seed=13, precision=prec)
+        try:
+            assert (s.grid_h, s.grid_w) == (28, 28)
+            s.forward_backward_device([t.data_ptr() for t in dev])
+            torch.cuda.synchronize()
+            got = s.losses()
+            if prec == 'fp32':
+                argmax = {L['name']: s.pool_argmax(L['name']) for L in layers if L['type'] == 'Pooling'}
+                ref = train_net_ref.forward_backward(layers, weights, data, grids, dropout_mask=s.dropout_mask(), pool_argmax=argmax)
+                for k in ('loss_bbox', 'loss_coverage'):
+                    assert abs(got[k] - ref[k]) <= 1e-5 * max(1.0, abs(ref[k])), (k, got[k], ref[k])
+                for name in ('conv1/7x7_s2', 'inception_4a/5x5', 'bbox/regressor'):
+                    gw, gb = ref['grads'][name]
+                    assert rel_err(s.param(name, 0, 'grad').reshape(gw.shape), gw) < 2e-4, name
+                    assert rel_err(s.param(name, 1, 'grad'), gb) < 2e-4, name
+            else:
+                # (its dropout mask is the same function of (seed, iteration, element), so the oracle run above applies)
+                for k in ('loss_bbox', 'loss_coverage'):
+                    assert abs(got[k] - ref[k]) <= 1e-2 * max(1.0, abs(ref[k])), (k, got[k], ref[k])
+        finally:
+            s.close()
