@@ -72,12 +72,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    if (!MNMAJ && p.bias)
-        for (int i = threadIdx.x; i < kGemmBiasMax; i += kGemmThreads) bias_s[i] = i < p.N ? p.bias[i] : 0.f;
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation) touches no global memory and
+    // may run while the previous kernel of the stream drains; from here on its results are needed.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (!MNMAJ && p.bias)
+        for (int i = threadIdx.x; i < kGemmBiasMax; i += kGemmThreads) bias_s[i] = i < p.N ? p.bias[i] : 0.f;
     fence_before();
     __syncthreads();
     fence_after();
