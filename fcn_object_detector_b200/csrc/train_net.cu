@@ -487,19 +487,30 @@ __global__ void __launch_bounds__(256) relu_bias8_kernel(const bf16* __restrict_
 #pragma unroll
     for (int q = 0; q < 8; ++q) acc[q] = 0.f;
     if (c < C)
-        for (unsigned p = p0 + threadIdx.y; p < p1; p += 32) {
-            const size_t o = (size_t)p * ldc + c;
-            BF8 d = ld8(dy + o);
+        for (unsigned p = p0 + threadIdx.y; p < p1; p += 64) {
+            // two pixels per iteration: four 16-byte loads in flight per thread
+            const unsigned pb = p + 32;
+            const bool hb = pb < p1;
+            const size_t o = (size_t)p * ldc + c, ob = (size_t)pb * ldc + c;
+            BF8 d = ld8(dy + o), db2, a, ab;
+            if (hb) db2 = ld8(dy + ob);
+            if (relu) { a = ld8(y + o); if (hb) ab = ld8(y + ob); }
             if (relu) {
-                const BF8 a = ld8(y + o);
                 bool any = false;
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     if (!(a.get(q) > 0.f)) { d.set(q, 0.f); any = true; }
                 if (any) st8(dy + o, d);
+                if (hb) {
+                    any = false;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        if (!(ab.get(q) > 0.f)) { db2.set(q, 0.f); any = true; }
+                    if (any) st8(dy + ob, db2);
+                }
             }
 #pragma unroll
-            for (int q = 0; q < 8; ++q) acc[q] += d.get(q);
+            for (int q = 0; q < 8; ++q) acc[q] += d.get(q) + (hb ? db2.get(q) : 0.f);
         }
 #pragma unroll
     for (int q = 0; q < 8; ++q) red[threadIdx.y][threadIdx.x * 8 + q] = acc[q];
@@ -774,13 +785,14 @@ __global__ void cast_flat_kernel(const float* __restrict__ in, bf16* __restrict_
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x)
         out[i] = __float2bfloat16_rn(in[i]);
 }
-__global__ void pack_wf_kernel(const float* __restrict__ P, int ldw, bf16* __restrict__ wf, int ldk, int Kc, int Cout) {
-    pdl_wait();
-    pdl_trigger();
-    const long total = (long)Cout * ldk;
+struct PackDesc { const float* P; bf16* wf; int ldw, ldk, Kc, Cout; };
+// all convolutions in one launch: blockIdx.y = convolution
+__global__ void pack_wf_kernel(const PackDesc* __restrict__ descs) {
+    const PackDesc d = descs[blockIdx.y];
+    const long total = (long)d.Cout * d.ldk;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const int j = (int)(i % ldk), co = (int)(i / ldk);
-        wf[i] = __float2bfloat16_rn(j < Kc ? P[(long)j * ldw + co] : 0.f);
+        const int j = (int)(i % d.ldk), co = (int)(i / d.ldk);
+        d.wf[i] = __float2bfloat16_rn(j < d.Kc ? d.P[(long)j * d.ldw + co] : 0.f);
     }
 }
 
@@ -882,6 +894,8 @@ struct fcnod_trainer {
     size_t esz = 4;
     bf16* wb = 0;                             // bf16 copy of the flat parameter buffer
     bf16* col = 0;                            // column-gradient scratch of the k x k data gradients (shared)
+    PackDesc* pack_descs = 0;                 // one entry per tensor-core convolution (pack_wf_kernel)
+    int n_pack = 0;
     std::vector<GemmPlan> gemms;
     // timing mode (bench.py's roofline): CUDA events around every GEMM launch of a step, on the launching stream
     bool timing = false;
@@ -1325,6 +1339,16 @@ void build_tc(fcnod_trainer* t) {
                                     direct ? (void*)bdiff(t, ib) : (void*)t->col, direct ? ib.ldc : c.ldk, 0, 0, 0, c.name.c_str()), 1);
         }
     }
+    std::vector<PackDesc> descs;
+    for (size_t ci = 0; ci < t->convs.size(); ++ci) {
+        const TConv& c = t->convs[ci];
+        if (!c.tc) continue;
+        PackDesc d = {t->params + c.w_off, c.d_wf, c.ldw, c.ldk, c.K, c.Cout};
+        descs.push_back(d);
+    }
+    t->n_pack = (int)descs.size();
+    t->pack_descs = dalloc<PackDesc>(t, descs.size());
+    FCNOD_CUDA(cudaMemcpy(t->pack_descs, descs.data(), descs.size() * sizeof(PackDesc), cudaMemcpyHostToDevice));
 }
 
 template <typename TI, typename TO>
@@ -1366,10 +1390,7 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
     if (tcp) {
         // bf16 copies of the (just updated) parameters
         cast_flat_kernel<<<grid1((long)t->n_params, 256), 256, 0, s>>>(t->params, t->wb, (long)t->n_params);
-        for (size_t ci = 0; ci < t->convs.size(); ++ci) {
-            const TConv& c = t->convs[ci];
-            if (c.tc) launch_k(pack_wf_kernel, grid1((long)c.Cout * c.ldk, 256), 256, 0, s, t->params + c.w_off, c.ldw, c.d_wf, c.ldk, c.K, c.Cout);
-        }
+        if (t->n_pack > 0) pack_wf_kernel<<<dim3(64, t->n_pack), 256, 0, s>>>(t->pack_descs);
         FCNOD_CUDA(cudaGetLastError());
     }
     for (size_t li = 0; li < t->layers.size(); ++li) {
@@ -1487,7 +1508,7 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
             T* dy = as<T>(bdiff(t, ob));
             if (tcp && ob.C % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0) {
                 // ReLU mask and bias gradient in one pass
-                const unsigned chunk = (unsigned)std::max<long>(512, (out_px + 147 * 2) / (148 * 2));
+                const unsigned chunk = (unsigned)std::max<long>(256, (out_px + 148 * 16 - 1) / (148 * 16));      // ~16 blocks per SM: bytes in flight
                 dim3 grid((unsigned)((c.Cout + 63) / 64), (unsigned)((out_px + chunk - 1) / chunk));
                 launch_k(relu_bias8_kernel, grid, dim3(8, 32), 0, s, as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), (unsigned)out_px, c.Cout, ob.ldc, chunk,
                                                               L.relu ? 1 : 0, t->grads + c.b_off);
