@@ -390,6 +390,7 @@ struct BF8 {
 __device__ __forceinline__ BF8 ld8(const bf16* p) { BF8 r; r.v = *reinterpret_cast<const uint4*>(p); return r; }
 __device__ __forceinline__ void st8(bf16* p, const BF8& r) { *reinterpret_cast<uint4*>(p) = r.v; }
 
+template <int K, int S>      // compile-time window and stride (3x3 / 2 and 3x3 / 1 in this network): unrolled loops, no divisions
 __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, PoolGeo g, unsigned m_cv) {
     pdl_wait();
     pdl_trigger();
@@ -399,19 +400,21 @@ __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
     if (i >= (unsigned)g.Wo * cv) return;
     const int pw = (int)__umulhi(i, m_cv), c = (int)(i - (unsigned)pw * cv) * 8;
     const int ph = blockIdx.y, n = blockIdx.z;
-    const int h0 = ph * g.s - g.p, w0 = pw * g.s - g.p;
-    const int hs = max(h0, 0), ws = max(w0, 0);
-    const int he = min(min(h0 + g.k, g.H + g.p), g.H), we = min(min(w0 + g.k, g.W + g.p), g.W);
+    const int h0 = ph * S - g.p, w0 = pw * S - g.p;
     // Two channels per instruction: the values ARE bf16, so a bf16 compare is exact; `>` against the lowest finite bf16 keeps the
     // first maximum in scan order (Caffe's rule), the window position travels in the same 16-bit lanes.
     uint32_t best[4], bi[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) { best[q] = 0xff7fff7fu; bi[q] = 0u; }
     const bf16* xn = x + (size_t)n * g.H * g.W * g.ldi + c;
-    for (int h = hs; h < he; ++h)
-        for (int w = ws; w < we; ++w) {
+#pragma unroll
+    for (int dh = 0; dh < K; ++dh)
+#pragma unroll
+        for (int dw = 0; dw < K; ++dw) {
+            const int h = h0 + dh, w = w0 + dw;
+            if (h < 0 || h >= g.H || w < 0 || w >= g.W) continue;          // (the pad rule min(h0 + k, H + p) never bites for pad < k)
             const uint4 v = *reinterpret_cast<const uint4*>(xn + ((size_t)h * g.W + w) * g.ldi);
-            const uint32_t loc2 = (uint32_t)((h - h0) * g.k + (w - w0)) * 0x00010001u;
+            const uint32_t loc2 = (uint32_t)(dh * K + dw) * 0x00010001u;
             const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -429,6 +432,7 @@ __global__ void pool_fwd8_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
     *reinterpret_cast<uint2*>(idx + o * g.C + c) = ib;
 }
 
+template <int K, int S>
 __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, PoolGeo g, int accum,
                                  unsigned m_cv) {
     pdl_wait();
@@ -439,15 +443,20 @@ __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __r
     if (i >= (unsigned)g.W * cv) return;
     const int w = (int)__umulhi(i, m_cv), c = (int)(i - (unsigned)w * cv) * 8;
     const int h = blockIdx.y, n = blockIdx.z;
-    const int ph0 = (h + g.p < g.k) ? 0 : (h + g.p - g.k) / g.s + 1, ph1 = min((h + g.p) / g.s + 1, g.Ho);
-    const int pw0 = (w + g.p < g.k) ? 0 : (w + g.p - g.k) / g.s + 1, pw1 = min((w + g.p) / g.s + 1, g.Wo);
+    const int ph0 = (h + g.p < K) ? 0 : (h + g.p - K) / S + 1, ph1 = min((h + g.p) / S + 1, g.Ho);
+    const int pw0 = (w + g.p < K) ? 0 : (w + g.p - K) / S + 1, pw1 = min((w + g.p) / S + 1, g.Wo);
     float acc[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) acc[q] = 0.f;
-    for (int ph = ph0; ph < ph1; ++ph)
-        for (int pw = pw0; pw < pw1; ++pw) {
+    constexpr int NW = (K + S - 1) / S;          // windows that can cover a pixel, per axis
+#pragma unroll
+    for (int a = 0; a < NW; ++a)
+#pragma unroll
+        for (int b = 0; b < NW; ++b) {
+            const int ph = ph0 + a, pw = pw0 + b;
+            if (ph >= ph1 || pw >= pw1) continue;
             const size_t o = ((size_t)n * g.Ho + ph) * g.Wo + pw;
-            const int local = (h - (ph * g.s - g.p)) * g.k + (w - (pw * g.s - g.p));
+            const int local = (h - (ph * S - g.p)) * K + (w - (pw * S - g.p));
             const uint2 ib = *reinterpret_cast<const uint2*>(idx + o * g.C + c);
             const uint4 d = *reinterpret_cast<const uint4*>(dy + o * g.ldo + c);
             // per-byte equality with the wanted position (0xff where equal), widened to the 16-bit lanes of the gradients;
@@ -1421,8 +1430,13 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
             if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
-                launch_k(pool_fwd8_kernel, dim3((ob.W * (ob.C / 8) + 255) / 256, ob.H, N), 256, 0, s, as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g,
-                                                                                                  div_magic((unsigned)ob.C / 8u));
+            {
+                const dim3 pg((ob.W * (ob.C / 8) + 255) / 256, ob.H, N);
+                const unsigned mcv = div_magic((unsigned)ob.C / 8u);
+                if (g.k == 3 && g.s == 2) launch_k(pool_fwd8_kernel<3, 2>, pg, 256, 0, s, as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g, mcv);
+                else if (g.k == 3 && g.s == 1) launch_k(pool_fwd8_kernel<3, 1>, pg, 256, 0, s, as<bf16>(bdata(t, ib)), as<bf16>(bdata(t, ob)), L.idx, g, mcv);
+                else FCNOD_CHECK(false, "trainer: bf16 pooling supports 3x3 windows with stride 1 or 2");
+            }
             else
                 pool_fwd_kernel<T><<<grid1(out_px * ob.C, 256), 256, 0, s>>>(as<T>(bdata(t, ib)), as<T>(bdata(t, ob)), L.idx, g);
             break;
@@ -1487,8 +1501,14 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
         case L_POOL: {
             PoolGeo g = {N, ib.C, ib.H, ib.W, ob.H, ob.W, L.def.kernel, L.def.stride, L.def.pad, ib.ldc, ob.ldc};
             if (tcp && ib.C % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0)
-                launch_k(pool_bwd8_kernel, dim3((ib.W * (ib.C / 8) + 255) / 256, ib.H, N), 256, 0, s, as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g,
-                                                                                                 claim_diff(t, L.in), div_magic((unsigned)ib.C / 8u));
+            {
+                const dim3 pg((ib.W * (ib.C / 8) + 255) / 256, ib.H, N);
+                const unsigned mcv = div_magic((unsigned)ib.C / 8u);
+                const int accum = claim_diff(t, L.in);
+                if (g.k == 3 && g.s == 2) launch_k(pool_bwd8_kernel<3, 2>, pg, 256, 0, s, as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g, accum, mcv);
+                else if (g.k == 3 && g.s == 1) launch_k(pool_bwd8_kernel<3, 1>, pg, 256, 0, s, as<bf16>(bdiff(t, ob)), L.idx, as<bf16>(bdiff(t, ib)), g, accum, mcv);
+                else FCNOD_CHECK(false, "trainer: bf16 pooling supports 3x3 windows with stride 1 or 2");
+            }
             else
                 pool_bwd_kernel<T><<<grid1(in_px * ib.C, 256), 256, 0, s>>>(as<T>(bdiff(t, ob)), L.idx, as<T>(bdiff(t, ib)), g, claim_diff(t, L.in));
             break;
