@@ -375,3 +375,35 @@ def test_full_size_448_step_against_the_oracle(train_files):
                     assert abs(got[k] - ref[k]) <= 1e-2 * max(1.0, abs(ref[k])), (k, got[k], ref[k])
         finally:
             s.close()
+
+
+def test_trainer_refuses_a_head_or_a_network_it_does_not_implement(train_files, tmp_path):
+    """The fused head is the one of train_val.prototxt: other slice points, an Eltwise SUM, another bbox loss weight than the
+    solver's, or an in-place-less ReLU are refused with an error that names the layer (never trained differently)."""
+    import ctypes as C
+    from fcn_object_detector_b200 import _lib
+    proto, cm, _ = train_files
+    text = open(proto).read()
+    cases = {
+        'slice': (text.replace('slice_point: 5', 'slice_point: 6'), 'slice-label'),
+        'eltwise': (text.replace('operation: PROD', 'operation: SUM', 1), 'bb-label-norm'),
+        'loss_weight': (text.replace('loss_weight: 2.0', 'loss_weight: 3.0'), 'bbox_loss'),
+        'layer_type': (text.replace('type: "LRN"', 'type: "BatchNorm"', 1), 'BatchNorm'),
+    }
+    L = _lib.lib()
+    for tag, (bad, needle) in cases.items():
+        path = str(tmp_path / ('bad_%s.prototxt' % tag))
+        with open(path, 'w') as f:
+            f.write(bad)
+        h = C.c_void_p()
+        rc = L.fcnod_trainer_create(path.encode(), cm.encode(), 0, 1, 64, 64, None, C.byref(h))
+        msg = L.fcnod_last_error().decode()
+        assert rc != 0 and needle in msg, (tag, rc, msg)
+    # wrong label-grid shapes are refused by the host mirror before anything is launched
+    from fcn_object_detector_b200.trainer import Solver
+    s = Solver(proto, cm, batch=1, height=64, width=64)
+    try:
+        with pytest.raises(ValueError):
+            s.step(np.zeros((1, 3, 64, 64), np.float32), [np.zeros((1, 1, 4, 4), np.float32)] * 5)
+    finally:
+        s.close()
