@@ -345,4 +345,177 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
 }
 
+// ------------------------------------------------------------------------------------------------ grouped weight gradients
+// The weight-gradient GEMMs of a training step are independent of each other once their dY is final (after the ReLU mask) and
+// of everything that follows in the backward pass (they read activations and dY, they write only their own gradient block).
+// Launched one by one, most of them run 13-30 us: (Cout / 128) x (Kc / 256) tiles split over pixel ranges to fill the SMs,
+// each launch paying its prologue, first-TMA latency and drain.  wgrad_group_kernel runs a LIST of them in one launch:
+// one persistent grid walks the concatenated work items (tile x pixel split) of all problems of the group.
+// Same MMA / TMA / epilogue as gemm_tc_kernel<true>; the per-problem tensor maps and sizes live in device memory.
+struct alignas(128) WgradProblem {
+    CUtensorMap ta, tb;        // dY view {Cout, pixels}, X / im2col view {Kc, pixels}: boxes {64, kGemmPK}
+    int M, N, BN;              // Cout, Kc, N tile (multiple of 64, <= 256)
+    int tiles_m, tiles_n, splits, k_blocks, kb_per_split;
+    int work_begin;            // first work item of this problem in the group
+    int ldg;
+    float* gout;               // gout[n * ldg + m] += D[m][n]
+};
+
+struct WgradGroupParams {
+    int n_problems, n_work, stages;
+    uint32_t b_stage_bytes;    // of the widest problem (ring slots are sized for it)
+    uint32_t tmem_cols, bn_max;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1) wgrad_group_kernel(const WgradProblem* __restrict__ probs, const WgradGroupParams gp) {
+    using namespace tc;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    constexpr uint32_t kAStage = 2u * kGemmPK * 128u;
+    const uint32_t stage_bytes = kAStage + gp.b_stage_bytes;
+    const uint32_t bar_base = smem_base + (uint32_t)gp.stages * stage_bytes;
+    const uint32_t full0 = bar_base, empty0 = full0 + 8u * gp.stages;
+    const uint32_t tfull0 = empty0 + 8u * gp.stages, tempty0 = tfull0 + 16u, tmem_slot = tempty0 + 16u;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < gp.stages; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(gp.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
+
+    // work item -> problem (the list is short: linear walk), tile and pixel range
+    struct Item { const WgradProblem* pr; int m0, n0, kb0, kb1, BN; };
+    auto decode = [&](int w) {
+        int q = 0;
+        while (q + 1 < gp.n_problems && probs[q + 1].work_begin <= w) ++q;
+        const WgradProblem* pr = probs + q;
+        const int l = w - pr->work_begin;
+        const int tn = l % pr->tiles_n, tm = (l / pr->tiles_n) % pr->tiles_m, sp = l / (pr->tiles_n * pr->tiles_m);
+        Item it;
+        it.pr = pr; it.m0 = tm * 128; it.n0 = tn * pr->BN; it.BN = pr->BN;
+        it.kb0 = sp * pr->kb_per_split; it.kb1 = min(it.kb0 + pr->kb_per_split, pr->k_blocks);
+        return it;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x) {
+                const Item it = decode(w);
+                const uint32_t tx = kAStage + (uint32_t)(it.BN / 64) * (kGemmPK * 128u);
+                for (int kb = it.kb0; kb < it.kb1; ++kb) {
+                    mbar_wait(empty0 + 8u * s, ph ^ 1u);
+                    const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + kAStage;
+                    mbar_expect_tx(full0 + 8u * s, tx);
+                    const int px = kb * kGemmPK;
+#pragma unroll 1
+                    for (int i = 0; i < 2; ++i) tma_load_2d(a_dst + i * (kGemmPK * 128), &it.pr->ta, full0 + 8u * s, it.m0 + 64 * i, px);
+#pragma unroll 1
+                    for (int i = 0; i < it.BN / 64; ++i) tma_load_2d(b_dst + i * (kGemmPK * 128), &it.pr->tb, full0 + 8u * s, it.n0 + 64 * i, px);
+                    if (++s == (uint32_t)gp.stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t lbo = (uint32_t)(kGemmPK * 128) >> 4;
+            uint32_t s = 0, ph = 0, n = 0;
+            for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x, ++n) {
+                const Item it = decode(w);
+                const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(it.BN >> 3) << 17) | (8u << 24);
+                const uint32_t acc = n & 1u, acc_ph = (n >> 1) & 1u;
+                mbar_wait(tempty0 + 8u * acc, acc_ph ^ 1u);
+                fence_after();
+                const uint32_t tmem_d = tmem_base + acc * gp.bn_max;
+                uint32_t accum = 0;
+                for (int kb = it.kb0; kb < it.kb1; ++kb) {
+                    mbar_wait(full0 + 8u * s, ph);
+                    fence_after();
+                    const uint32_t a_s = smem_base + s * stage_bytes, b_s = a_s + kAStage;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t adv = (uint32_t)k * 2048u;
+                        const uint64_t da = ((uint64_t)desc_hi << 32) | (uint64_t)(((a_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)lbo << 16);
+                        const uint64_t db = ((uint64_t)desc_hi << 32) | (uint64_t)(((b_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)lbo << 16);
+                        umma_bf16(tmem_d, da, db, idesc, accum);
+                        accum = 1;
+                    }
+                    umma_commit(empty0 + 8u * s);
+                    if (++s == (uint32_t)gp.stages) { s = 0; ph ^= 1u; }
+                }
+                umma_commit(tfull0 + 8u * acc);
+            }
+        }
+    } else {
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int g = lane & 3, b = g & 1;
+        uint32_t n = 0;
+        for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x, ++n) {
+            const Item it = decode(w);
+            const int N = it.pr->N, ldg = it.pr->ldg;
+            float* gout = it.pr->gout;
+            const uint32_t acc = n & 1u, acc_ph = (n >> 1) & 1u;
+            const int n_chunks = (min(it.BN, N - it.n0) + 15) / 16;
+            const int mg = it.m0 + q * 32 + (lane & ~3);
+            mbar_wait(tfull0 + 8u * acc, acc_ph);
+            fence_after();
+            const uint32_t taddr = tmem_base + acc * gp.bn_max + ((uint32_t)(q * 32) << 16);
+            uint32_t rA[16], rB[16];
+            auto reduce16 = [&](const uint32_t (&rr)[16], int ch) {
+                const int col0 = it.n0 + 16 * ch;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const float a0 = __uint_as_float(rr[4 * t]), a1 = __uint_as_float(rr[4 * t + 1]);
+                    const float a2 = __uint_as_float(rr[4 * t + 2]), a3 = __uint_as_float(rr[4 * t + 3]);
+                    const bool hi = (g & 2) != 0;
+                    const float x0 = hi ? a2 : a0, x1 = hi ? a3 : a1;
+                    const float y0 = __shfl_xor_sync(0xffffffffu, hi ? a0 : a2, 2), y1 = __shfl_xor_sync(0xffffffffu, hi ? a1 : a3, 2);
+                    const float xb = b ? x1 : x0, yb = b ? y1 : y0;
+                    const float rx = __shfl_xor_sync(0xffffffffu, b ? x0 : x1, 1), ry = __shfl_xor_sync(0xffffffffu, b ? y0 : y1, 1);
+                    float o[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) o[r] = r == g ? xb : (r == (g ^ 2) ? yb : (r == (g ^ 1) ? rx : ry));
+                    const int col = col0 + 4 * t + g;
+                    if (col < N && mg < ldg)
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gout + (long)col * ldg + mg), "f"(o[0]), "f"(o[1]),
+                                     "f"(o[2]), "f"(o[3]) : "memory");
+                }
+            };
+            if (half < n_chunks) tmem_ld16(taddr + 16u * half, rA);
+            for (int ch = half; ch < n_chunks; ch += 4) {
+                gemm_ld_wait16(rA);
+                if (ch + 2 < n_chunks) tmem_ld16(taddr + 16u * (ch + 2), rB);
+                reduce16(rA, ch);
+                if (ch + 2 < n_chunks) {
+                    gemm_ld_wait16(rB);
+                    if (ch + 4 < n_chunks) tmem_ld16(taddr + 16u * (ch + 4), rA);
+                    reduce16(rB, ch + 2);
+                }
+            }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(gp.tmem_cols) : "memory");
+    }
+}
+
 }  // namespace fcnod

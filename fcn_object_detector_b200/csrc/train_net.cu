@@ -905,6 +905,12 @@ struct fcnod_trainer {
     bf16* col = 0;                            // column-gradient scratch of the k x k data gradients (shared)
     PackDesc* pack_descs = 0;                 // one entry per tensor-core convolution (pack_wf_kernel)
     int n_pack = 0;
+    // grouped weight gradients (wgrad_group_kernel): consecutive convolutions of the backward order, launched together when
+    // the last member's dY is final
+    struct WGroup { std::vector<int> convs; WgradProblem* probs = 0; WgradGroupParams gp; size_t smem = 0; int grid = 0; double flop = 0.0;
+                    cudaEvent_t e0 = 0, e1 = 0; };
+    std::vector<WGroup> wgroups;
+    std::vector<int> conv_wgroup;             // per convolution: its group (-1: launched alone)
     std::vector<GemmPlan> gemms;
     // timing mode (bench.py's roofline): CUDA events around every GEMM launch of a step, on the launching stream
     bool timing = false;
@@ -1358,6 +1364,73 @@ void build_tc(fcnod_trainer* t) {
     t->n_pack = (int)descs.size();
     t->pack_descs = dalloc<PackDesc>(t, descs.size());
     FCNOD_CUDA(cudaMemcpy(t->pack_descs, descs.data(), descs.size() * sizeof(PackDesc), cudaMemcpyHostToDevice));
+    // ---- weight-gradient groups: up to G consecutive tensor-core convolutions in backward order
+    t->conv_wgroup.assign(t->convs.size(), -1);
+    int G = 8;
+    if (const char* e = getenv("FCNOD_TRAIN_WGRAD_GROUP")) G = atoi(e);
+    if (G >= 2) {
+        std::vector<int> order;                  // tensor-core convolutions in the order the backward pass reaches them
+        for (size_t li = t->layers.size(); li-- > 0;)
+            if (t->layers[li].def.type == L_CONV && t->convs[t->layers[li].conv].tc) order.push_back(t->layers[li].conv);
+        for (size_t i0 = 0; i0 < order.size(); i0 += G) {
+            fcnod_trainer::WGroup grp;
+            for (size_t i = i0; i < std::min(order.size(), i0 + (size_t)G); ++i) grp.convs.push_back(order[i]);
+            // pixel splits: about 4 work items per SM over the whole group, at least 4 reduction blocks per item
+            double blocks = 0;
+            for (size_t i = 0; i < grp.convs.size(); ++i) {
+                const GemmTcParams& p = t->gemms[t->convs[grp.convs[i]].g_wgrad].p;
+                blocks += (double)p.tiles_m * p.tiles_n * p.k_blocks;
+            }
+            const int target_kb = std::max(4, (int)std::ceil(blocks / (148.0 * 4)));
+            std::vector<WgradProblem> probs(grp.convs.size());
+            int work = 0, bn_max = 64;
+            for (size_t i = 0; i < grp.convs.size(); ++i) {
+                const GemmPlan& g = t->gemms[t->convs[grp.convs[i]].g_wgrad];
+                const GemmTcParams& p = g.p;
+                WgradProblem& q = probs[i];
+                memset(&q, 0, sizeof q);
+                q.ta = g.ta; q.tb = g.tb;
+                q.M = p.M; q.N = p.N; q.BN = p.BN; q.tiles_m = p.tiles_m; q.tiles_n = p.tiles_n; q.k_blocks = p.k_blocks;
+                q.splits = std::max(1, (p.k_blocks + target_kb - 1) / target_kb);
+                q.kb_per_split = (p.k_blocks + q.splits - 1) / q.splits;
+                q.splits = (p.k_blocks + q.kb_per_split - 1) / q.kb_per_split;
+                q.work_begin = work; q.ldg = p.ldg; q.gout = p.gout;
+                work += q.tiles_m * q.tiles_n * q.splits;
+                bn_max = std::max(bn_max, p.BN);
+                grp.flop += 2.0 * p.M * p.N * (double)p.K;
+                t->conv_wgroup[grp.convs[i]] = (int)t->wgroups.size();
+            }
+            grp.gp.n_problems = (int)probs.size(); grp.gp.n_work = work;
+            grp.gp.b_stage_bytes = (uint32_t)(bn_max / 64) * kGemmPK * 128; grp.gp.bn_max = (uint32_t)bn_max;
+            const size_t stage = 2 * kGemmPK * 128 + grp.gp.b_stage_bytes;
+            grp.gp.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (200 * 1024) / stage));
+            grp.gp.tmem_cols = (uint32_t)pow2_at_least(2 * bn_max);
+            grp.smem = (size_t)grp.gp.stages * stage + 16 * grp.gp.stages + 64 + 1024;
+            grp.grid = std::min(work, 148);
+            grp.probs = dalloc<WgradProblem>(t, probs.size());
+            FCNOD_CHECK((reinterpret_cast<uintptr_t>(grp.probs) & 127) == 0, "trainer: problem table not 128-byte aligned");
+            FCNOD_CUDA(cudaMemcpy(grp.probs, probs.data(), probs.size() * sizeof(WgradProblem), cudaMemcpyHostToDevice));
+            t->wgroups.push_back(grp);
+        }
+    }
+}
+
+void launch_wgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
+    static bool attr[64] = {};
+    int dev = 0;
+    FCNOD_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr[dev]) {
+        FCNOD_CUDA(cudaFuncSetAttribute(wgrad_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (dev >= 0 && dev < 64) attr[dev] = true;
+    }
+    fcnod_trainer::WGroup& g = t->wgroups[gi];
+    if (t->timing) {
+        if (!g.e0) { FCNOD_CUDA(cudaEventCreate(&g.e0)); FCNOD_CUDA(cudaEventCreate(&g.e1)); }
+        FCNOD_CUDA(cudaEventRecord(g.e0, s));
+    }
+    wgrad_group_kernel<<<g.grid, kGemmThreads, g.smem, s>>>(g.probs, g.gp);
+    FCNOD_CUDA(cudaGetLastError());
+    if (t->timing) FCNOD_CUDA(cudaEventRecord(g.e1, s));
 }
 
 template <typename TI, typename TO>
@@ -1545,7 +1618,12 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
             }
             if (tcp && c.tc) {
                 const bool direct = c.k == 1 && c.stride == 1;
-                run_gemm(t, c.g_wgrad, 0, s);            // (k x k: on the im2col matrix the forward left in c.d_col)
+                {   // weight gradient (k x k: on the im2col matrix the forward left in c.d_col): alone, or with its group once the
+                    // group's last member has been reached (the members' dY slices are final and nothing later touches them)
+                    const int gi = t->conv_wgroup[L.conv];
+                    if (gi < 0) run_gemm(t, c.g_wgrad, 0, s);
+                    else if (t->wgroups[gi].convs.back() == L.conv) launch_wgroup(t, gi, s);
+                }
                 if (ib.needs_grad) {
                     const int accum = claim_diff(t, L.in);
                     if (direct) {
@@ -1919,6 +1997,11 @@ int fcnod_trainer_gemm_times(fcnod_trainer* t, float ms[3], double flop[3], int 
         const int k = t->gemm_kind[i];
         const GemmTcParams& p = t->gemms[i].p;
         ms[k] += e; flop[k] += 2.0 * p.M * p.N * (double)p.K; ++launches[k];
+    }
+    for (size_t gi = 0; gi < t->wgroups.size(); ++gi) {
+        float e = 0.f;
+        if (!t->wgroups[gi].e0 || cudaEventElapsedTime(&e, t->wgroups[gi].e0, t->wgroups[gi].e1) != cudaSuccess) { cudaGetLastError(); continue; }
+        ms[2] += e; flop[2] += t->wgroups[gi].flop; ++launches[2];
     }
     FCNOD_API_END
 }
