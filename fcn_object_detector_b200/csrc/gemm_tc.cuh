@@ -518,4 +518,189 @@ __global__ void __launch_bounds__(kGemmThreads, 1) wgrad_group_kernel(const Wgra
     }
 }
 
+// ------------------------------------------------------------------------------------------------ grouped K-major GEMMs
+// The same for independent forward / data-gradient GEMMs (the three 1x1 convolutions that read an inception module's input; the
+// three data gradients that accumulate into that input's diff): one persistent grid over the tiles of all problems.
+// bf16 output through shared memory and the TMA unit only (store, or reduce-add where the problem accumulates).
+struct alignas(128) KGemmProblem {
+    CUtensorMap ta, tb, to;    // A {K, M} box {64, 128}; B {K, N} box {64, BN}; out {N, M} box {64, 128}
+    int M, N, BN, tiles_m, tiles_n, k_blocks;
+    int work_begin, bias_off;  // bias_off: offset of this problem's bias in the staged table, -1 = none
+    int relu, accum;
+    const float* bias;
+};
+
+struct KGemmGroupParams {
+    int n_problems, n_work, stages, n_bias;      // n_bias: floats of the staged bias table (all problems, each padded to its tiles)
+    uint32_t b_stage_bytes, out_stage_bytes, tmem_cols, bn_max;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1) kgemm_group_kernel(const KGemmProblem* __restrict__ probs, const KGemmGroupParams gp) {
+    using namespace tc;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    constexpr uint32_t kAStage = 128u * 128u;
+    const uint32_t stage_bytes = kAStage + gp.b_stage_bytes;
+    const uint32_t out_stage = smem_base + (uint32_t)gp.stages * stage_bytes;
+    const uint32_t bar_base = out_stage + gp.out_stage_bytes;
+    const uint32_t full0 = bar_base, empty0 = full0 + 8u * gp.stages;
+    const uint32_t tfull0 = empty0 + 8u * gp.stages, tempty0 = tfull0 + 16u, tmem_slot = tempty0 + 16u;
+    float* bias_s = reinterpret_cast<float*>(smem_raw + (tmem_slot + 16u - smem_u32(smem_raw)));
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < gp.stages; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8u * a, 1); mbar_init(tempty0 + 8u * a, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(gp.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // biases of all problems, each zero-padded to tiles_n * BN entries
+    for (int q = 0; q < gp.n_problems; ++q) {
+        const KGemmProblem& pr = probs[q];
+        if (pr.bias_off < 0) continue;
+        for (int i = threadIdx.x; i < pr.tiles_n * pr.BN; i += kGemmThreads) bias_s[pr.bias_off + i] = i < pr.N ? pr.bias[i] : 0.f;
+    }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
+
+    struct Item { const KGemmProblem* pr; int m0, n0, BN, kb; };
+    auto decode = [&](int w) {
+        int q = 0;
+        while (q + 1 < gp.n_problems && probs[q + 1].work_begin <= w) ++q;
+        const KGemmProblem* pr = probs + q;
+        const int l = w - pr->work_begin;
+        Item it;
+        it.pr = pr; it.n0 = (l % pr->tiles_n) * pr->BN; it.m0 = (l / pr->tiles_n) * 128; it.BN = pr->BN; it.kb = pr->k_blocks;
+        return it;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x) {
+                const Item it = decode(w);
+                const uint32_t tx = kAStage + (uint32_t)it.BN * 128u;
+                for (int kb = 0; kb < it.kb; ++kb) {
+                    mbar_wait(empty0 + 8u * s, ph ^ 1u);
+                    const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + kAStage;
+                    mbar_expect_tx(full0 + 8u * s, tx);
+                    tma_load_2d(a_dst, &it.pr->ta, full0 + 8u * s, kb * 64, it.m0);
+                    tma_load_2d(b_dst, &it.pr->tb, full0 + 8u * s, kb * 64, it.n0);
+                    if (++s == (uint32_t)gp.stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            uint32_t s = 0, ph = 0, n = 0;
+            for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x, ++n) {
+                const Item it = decode(w);
+                const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(it.BN >> 3) << 17) | (8u << 24);
+                const uint32_t acc = n & 1u, acc_ph = (n >> 1) & 1u;
+                mbar_wait(tempty0 + 8u * acc, acc_ph ^ 1u);
+                fence_after();
+                const uint32_t tmem_d = tmem_base + acc * gp.bn_max;
+                uint32_t accum = 0;
+                for (int kb = 0; kb < it.kb; ++kb) {
+                    mbar_wait(full0 + 8u * s, ph);
+                    fence_after();
+                    const uint32_t a_s = smem_base + s * stage_bytes, b_s = a_s + kAStage;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t adv = (uint32_t)k * 32u;
+                        const uint64_t da = ((uint64_t)desc_hi << 32) | (uint64_t)(((a_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)1u << 16);
+                        const uint64_t db = ((uint64_t)desc_hi << 32) | (uint64_t)(((b_s + adv) & 0x3FFFFu) >> 4) | ((uint64_t)1u << 16);
+                        umma_bf16(tmem_d, da, db, idesc, accum);
+                        accum = 1;
+                    }
+                    umma_commit(empty0 + 8u * s);
+                    if (++s == (uint32_t)gp.stages) { s = 0; ph ^= 1u; }
+                }
+                umma_commit(tfull0 + 8u * acc);
+            }
+        }
+    } else {
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const bool leader = warp == 2 && lane == 0;
+        uint32_t n = 0;
+        for (int w = blockIdx.x; w < gp.n_work; w += gridDim.x, ++n) {
+            const Item it = decode(w);
+            const KGemmProblem* pr = it.pr;
+            const int relu = pr->relu, boff = pr->bias_off, N = pr->N;
+            const uint32_t acc = n & 1u, acc_ph = (n >> 1) & 1u;
+            const int n_chunks = (min(it.BN, N - it.n0) + 15) / 16;
+            const int r = q * 32 + lane;
+            if (leader) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mbar_wait(tfull0 + 8u * acc, acc_ph);
+            fence_after();
+            const uint32_t taddr = tmem_base + acc * gp.bn_max + ((uint32_t)(q * 32) << 16);
+            uint32_t rA[16], rB[16];
+            auto emit = [&](const uint32_t (&rr)[16], int ch) {
+                const int nl = (it.n0 - 0) + 16 * ch;                      // column inside the problem
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    v[j] = __uint_as_float(rr[j]);
+                    if (boff >= 0) v[j] += bias_s[boff + nl + j];
+                    if (relu) v[j] = fmaxf(v[j], 0.f);
+                }
+                uint4 w4[2];
+                __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(w4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) h2[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                const uint32_t row_base = out_stage + (uint32_t)(ch >> 2) * 16384u + (uint32_t)r * 128u;
+                const uint32_t u0 = (uint32_t)(ch & 3) * 2u, sw = (uint32_t)r & 7u;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + ((u0 ^ sw) << 4)), "r"(w4[0].x), "r"(w4[0].y), "r"(w4[0].z), "r"(w4[0].w) : "memory");
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_base + (((u0 + 1u) ^ sw) << 4)), "r"(w4[1].x), "r"(w4[1].y), "r"(w4[1].z), "r"(w4[1].w) : "memory");
+            };
+            if (half < n_chunks) tmem_ld16(taddr + 16u * half, rA);
+            for (int ch = half; ch < n_chunks; ch += 4) {
+                gemm_ld_wait16(rA);
+                if (ch + 2 < n_chunks) tmem_ld16(taddr + 16u * (ch + 2), rB);
+                emit(rA, ch);
+                if (ch + 2 < n_chunks) {
+                    gemm_ld_wait16(rB);
+                    if (ch + 4 < n_chunks) tmem_ld16(taddr + 16u * (ch + 4), rA);
+                    emit(rB, ch + 2);
+                }
+            }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8u * acc) : "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (leader) {
+                const int regions = (n_chunks + 3) >> 2;
+                for (int g = 0; g < regions; ++g) {
+                    const uint32_t src = out_stage + (uint32_t)g * 16384u;
+                    if (pr->accum)
+                        asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&pr->to), "r"(src), "r"(it.n0 + 64 * g), "r"(it.m0) : "memory");
+                    else
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&pr->to), "r"(src), "r"(it.n0 + 64 * g), "r"(it.m0) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+        if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(gp.tmem_cols) : "memory");
+    }
+}
+
 }  // namespace fcnod

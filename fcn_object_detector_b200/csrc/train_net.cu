@@ -911,6 +911,12 @@ struct fcnod_trainer {
                     cudaEvent_t e0 = 0, e1 = 0; };
     std::vector<WGroup> wgroups;
     std::vector<int> conv_wgroup;             // per convolution: its group (-1: launched alone)
+    // grouped K-major GEMMs (kgemm_group_kernel): the 1x1 convolutions that read the same blob -- their forward GEMMs launch
+    // together at the first member, their data gradients (all accumulating into that blob's diff) at the last one reached
+    struct KGroup { std::vector<int> convs; KGemmProblem* probs = 0; KGemmGroupParams gp; size_t smem = 0; int grid = 0; double flop = 0.0;
+                    int kind = 0; cudaEvent_t e0 = 0, e1 = 0; };
+    std::vector<KGroup> kgroups;
+    std::vector<int> conv_fgroup, conv_dgroup;
     std::vector<GemmPlan> gemms;
     // timing mode (bench.py's roofline): CUDA events around every GEMM launch of a step, on the launching stream
     bool timing = false;
@@ -1309,6 +1315,8 @@ void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) {
 }
 
 // bf16 engine: scratch, bf16 weights and the three GEMM plans of every convolution (pointers are fixed for the trainer's life)
+void build_kgroups(fcnod_trainer* t);
+
 void build_tc(fcnod_trainer* t) {
     const int N = t->batch;
     size_t col_elems = 8;
@@ -1364,9 +1372,10 @@ void build_tc(fcnod_trainer* t) {
     t->n_pack = (int)descs.size();
     t->pack_descs = dalloc<PackDesc>(t, descs.size());
     FCNOD_CUDA(cudaMemcpy(t->pack_descs, descs.data(), descs.size() * sizeof(PackDesc), cudaMemcpyHostToDevice));
-    // ---- weight-gradient groups: up to G consecutive tensor-core convolutions in backward order
+    // ---- weight-gradient groups: up to G consecutive tensor-core convolutions in backward order (measured: 57 single launches
+    //      1.71 ms, groups of 8 1.05 ms, groups of 16 0.88 ms)
     t->conv_wgroup.assign(t->convs.size(), -1);
-    int G = 8;
+    int G = 16;
     if (const char* e = getenv("FCNOD_TRAIN_WGRAD_GROUP")) G = atoi(e);
     if (G >= 2) {
         std::vector<int> order;                  // tensor-core convolutions in the order the backward pass reaches them
@@ -1413,6 +1422,87 @@ void build_tc(fcnod_trainer* t) {
             t->wgroups.push_back(grp);
         }
     }
+    build_kgroups(t);
+}
+
+int build_kgroup(fcnod_trainer* t, const std::vector<int>& convs, bool dgrad) {
+    fcnod_trainer::KGroup grp;
+    grp.convs = convs; grp.kind = dgrad ? 1 : 0;
+    std::vector<KGemmProblem> probs(convs.size());
+    int work = 0, bn_max = 16, bias = 0;
+    for (size_t i = 0; i < convs.size(); ++i) {
+        const TConv& c = t->convs[convs[i]];
+        const GemmPlan& g = t->gemms[dgrad ? c.g_dgrad : c.g_fwd];
+        const GemmTcParams& p = g.p;
+        if (!p.tma_out) return -1;
+        KGemmProblem& q = probs[i];
+        memset(&q, 0, sizeof q);
+        q.ta = g.ta; q.tb = g.tb; q.to = g.to;
+        q.M = p.M; q.N = p.N; q.BN = p.BN; q.tiles_m = p.tiles_m; q.tiles_n = p.tiles_n; q.k_blocks = p.k_blocks;
+        q.work_begin = work; q.relu = p.relu; q.accum = dgrad ? 1 : 0; q.bias = p.bias;
+        q.bias_off = p.bias ? bias : -1;
+        if (p.bias) bias += p.tiles_n * p.BN;
+        work += p.tiles_m * p.tiles_n;
+        bn_max = std::max(bn_max, p.BN);
+        grp.flop += 2.0 * p.M * p.N * (double)p.K;
+    }
+    if (bias > kGemmBiasMax) return -1;
+    grp.gp.n_problems = (int)probs.size(); grp.gp.n_work = work; grp.gp.n_bias = bias;
+    grp.gp.b_stage_bytes = (uint32_t)bn_max * 128; grp.gp.bn_max = (uint32_t)bn_max;
+    grp.gp.out_stage_bytes = (uint32_t)((bn_max + 63) / 64) * 16384u;
+    const size_t stage = 128 * 128 + grp.gp.b_stage_bytes;
+    grp.gp.stages = (int)std::max<size_t>(2, std::min<size_t>(8, (192 * 1024 - grp.gp.out_stage_bytes) / stage));
+    grp.gp.tmem_cols = (uint32_t)pow2_at_least(2 * bn_max);
+    grp.smem = (size_t)grp.gp.stages * stage + grp.gp.out_stage_bytes + 16 * grp.gp.stages + 64 + 1024 + kGemmBiasMax * 4;
+    grp.grid = std::min(work, 148);
+    grp.probs = dalloc<KGemmProblem>(t, probs.size());
+    FCNOD_CUDA(cudaMemcpy(grp.probs, probs.data(), probs.size() * sizeof(KGemmProblem), cudaMemcpyHostToDevice));
+    t->kgroups.push_back(grp);
+    return (int)t->kgroups.size() - 1;
+}
+
+// sibling sets: tensor-core 1x1 / stride-1 convolutions that read the same blob (the 1x1, 3x3_reduce and 5x5_reduce of an
+// inception module, the two reduce layers being produced early is harmless: nothing else writes their tops)
+void build_kgroups(fcnod_trainer* t) {
+    t->conv_fgroup.assign(t->convs.size(), -1);
+    t->conv_dgroup.assign(t->convs.size(), -1);
+    if (const char* e = getenv("FCNOD_TRAIN_KGROUP")) if (e[0] == '0') return;
+    std::map<int, std::vector<int> > by_input;       // input blob -> convolutions, forward order
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        const TLayer& L = t->layers[li];
+        if (L.def.type != L_CONV) continue;
+        const TConv& c = t->convs[L.conv];
+        if (c.tc && c.k == 1 && c.stride == 1) by_input[L.in].push_back(L.conv);
+    }
+    for (std::map<int, std::vector<int> >::iterator it = by_input.begin(); it != by_input.end(); ++it) {
+        if (it->second.size() < 2) continue;
+        const int fg = build_kgroup(t, it->second, false);
+        if (fg >= 0) for (size_t i = 0; i < it->second.size(); ++i) t->conv_fgroup[it->second[i]] = fg;
+        if (t->blobs[it->first].needs_grad) {
+            const TBlob& ib = t->blobs[it->first];
+            if (ib.ldc != ib.C) continue;            // the diff may have to be zeroed as a whole: dense blobs only
+            const int dg = build_kgroup(t, it->second, true);
+            if (dg >= 0) for (size_t i = 0; i < it->second.size(); ++i) t->conv_dgroup[it->second[i]] = dg;
+        }
+    }
+}
+
+void launch_kgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
+    static bool attr[64] = {};
+    int dev = 0;
+    FCNOD_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr[dev]) {
+        FCNOD_CUDA(cudaFuncSetAttribute(kgemm_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (dev >= 0 && dev < 64) attr[dev] = true;
+    }
+    fcnod_trainer::KGroup& g = t->kgroups[gi];
+    if (t->timing) {
+        if (!g.e0) { FCNOD_CUDA(cudaEventCreate(&g.e0)); FCNOD_CUDA(cudaEventCreate(&g.e1)); }
+        FCNOD_CUDA(cudaEventRecord(g.e0, s));
+    }
+    kgemm_group_kernel<<<g.grid, kGemmThreads, g.smem, s>>>(g.probs, g.gp);
+    FCNOD_CUDA(cudaGetLastError());
+    if (t->timing) FCNOD_CUDA(cudaEventRecord(g.e1, s));
 }
 
 void launch_wgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
@@ -1488,6 +1578,12 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
         case L_CONV: {
             const TConv& c = t->convs[L.conv];
             if (tcp && c.tc) {
+                const int fg = t->conv_fgroup[L.conv];
+                if (fg >= 0) {
+                    // sibling 1x1 convolutions: all of them at the first one, nothing at the others
+                    if (t->kgroups[fg].convs.front() == L.conv) launch_kgroup(t, fg, s);
+                    break;
+                }
                 if (!(c.k == 1 && c.stride == 1)) launch_im2col(t, c, ib, ob, s);
                 run_gemm(t, c.g_fwd, 0, s);
             } else if (tcp && c.narrow) {
@@ -1624,7 +1720,15 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
                     if (gi < 0) run_gemm(t, c.g_wgrad, 0, s);
                     else if (t->wgroups[gi].convs.back() == L.conv) launch_wgroup(t, gi, s);
                 }
-                if (ib.needs_grad) {
+                const int dg = t->conv_dgroup[L.conv];
+                if (ib.needs_grad && dg >= 0) {
+                    // sibling data gradients, all accumulating into the same diff: launched together at the last one reached
+                    // (the first of the forward order); whoever wrote the diff before (the module's pool branch) stays below them
+                    if (t->kgroups[dg].convs.front() == L.conv) {
+                        if (!claim_diff(t, L.in)) FCNOD_CUDA(cudaMemsetAsync(bdiff(t, ib), 0, (size_t)in_px * ib.C * sizeof(T), s));
+                        launch_kgroup(t, dg, s);
+                    }
+                } else if (ib.needs_grad) {
                     const int accum = claim_diff(t, L.in);
                     if (direct) {
                         run_gemm(t, c.g_dgrad, accum, s);
@@ -1997,6 +2101,12 @@ int fcnod_trainer_gemm_times(fcnod_trainer* t, float ms[3], double flop[3], int 
         const int k = t->gemm_kind[i];
         const GemmTcParams& p = t->gemms[i].p;
         ms[k] += e; flop[k] += 2.0 * p.M * p.N * (double)p.K; ++launches[k];
+    }
+    for (size_t gi = 0; gi < t->kgroups.size(); ++gi) {
+        float e = 0.f;
+        if (!t->kgroups[gi].e0 || cudaEventElapsedTime(&e, t->kgroups[gi].e0, t->kgroups[gi].e1) != cudaSuccess) { cudaGetLastError(); continue; }
+        const int k = t->kgroups[gi].kind;
+        ms[k] += e; flop[k] += t->kgroups[gi].flop; ++launches[k];
     }
     for (size_t gi = 0; gi < t->wgroups.size(); ++gi) {
         float e = 0.f;
