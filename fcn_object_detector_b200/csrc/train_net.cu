@@ -917,6 +917,10 @@ struct fcnod_trainer {
                     int kind = 0; cudaEvent_t e0 = 0, e1 = 0; };
     std::vector<KGroup> kgroups;
     std::vector<int> conv_fgroup, conv_dgroup;
+    // forward GEMMs that are not needed at once (the 3x3 / 5x5 / pool_proj branches of a module) wait, after their im2col, for the
+    // first layer that reads one of their outputs (the Concat) and launch together there
+    std::vector<int> conv_fdefer;             // per convolution: the group its forward GEMM waits in (-1: launched at once)
+    std::vector<int> fwd_flush;               // per layer: group to launch BEFORE the layer runs (-1: none)
     std::vector<GemmPlan> gemms;
     // timing mode (bench.py's roofline): CUDA events around every GEMM launch of a step, on the launching stream
     bool timing = false;
@@ -1316,6 +1320,7 @@ void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) {
 
 // bf16 engine: scratch, bf16 weights and the three GEMM plans of every convolution (pointers are fixed for the trainer's life)
 void build_kgroups(fcnod_trainer* t);
+void build_fwd_deferral(fcnod_trainer* t);
 
 void build_tc(fcnod_trainer* t) {
     const int N = t->batch;
@@ -1423,6 +1428,7 @@ void build_tc(fcnod_trainer* t) {
         }
     }
     build_kgroups(t);
+    build_fwd_deferral(t);
 }
 
 int build_kgroup(fcnod_trainer* t, const std::vector<int>& convs, bool dgrad) {
@@ -1485,6 +1491,47 @@ void build_kgroups(fcnod_trainer* t) {
             if (dg >= 0) for (size_t i = 0; i < it->second.size(); ++i) t->conv_dgroup[it->second[i]] = dg;
         }
     }
+}
+
+// static simulation of the forward walk: which GEMMs can wait, and where they must have run
+void build_fwd_deferral(fcnod_trainer* t) {
+    t->conv_fdefer.assign(t->convs.size(), -1);
+    t->fwd_flush.assign(t->layers.size(), -1);
+    if (const char* e = getenv("FCNOD_TRAIN_KGROUP")) if (e[0] == '0') return;
+    std::vector<int> pending;
+    auto root = [&](int b) { return t->blobs[b].root >= 0 ? t->blobs[b].root : b; };
+    auto flush = [&](size_t li) {
+        if (pending.size() >= 2) {
+            const int g = build_kgroup(t, pending, false);
+            if (g >= 0) {
+                for (size_t i = 0; i < pending.size(); ++i) t->conv_fdefer[pending[i]] = g;
+                if (li < t->layers.size()) t->fwd_flush[li] = g;
+            }
+        }
+        pending.clear();
+    };
+    std::map<int, int> out_root;                     // pending convolution -> root blob of its top
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        const TLayer& L = t->layers[li];
+        if (L.def.type == L_RELU) continue;
+        bool reads = false;
+        for (size_t b = 0; b < L.def.bottom.size() && !reads; ++b) {
+            std::map<std::string, int>::iterator bi = t->blob_index.find(L.def.bottom[b]);
+            if (bi == t->blob_index.end()) continue;
+            for (size_t i = 0; i < pending.size(); ++i)
+                if (out_root[pending[i]] == root(bi->second)) reads = true;
+        }
+        if (reads) flush(li);
+        if (L.def.type == L_CONV) {
+            const TConv& c = t->convs[L.conv];
+            if (c.tc && t->conv_fgroup[L.conv] < 0 && t->gemms[c.g_fwd].p.tma_out && pending.size() < 6) {
+                pending.push_back(L.conv);
+                out_root[L.conv] = root(L.out);
+            }
+        }
+    }
+    // whatever is still pending at the end would never be launched by a reader: leave those immediate
+    pending.clear();
 }
 
 void launch_kgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
@@ -1567,6 +1614,7 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
     }
     for (size_t li = 0; li < t->layers.size(); ++li) {
         TLayer& L = t->layers[li];
+        if (tcp && !t->fwd_flush.empty() && t->fwd_flush[li] >= 0) launch_kgroup(t, t->fwd_flush[li], s);     // deferred GEMMs this layer reads
         if (L.skip) continue;
         const TBlob& ib = t->blobs[L.in];
         const TBlob& ob = t->blobs[L.out];
@@ -1585,7 +1633,7 @@ void forward(fcnod_trainer* t, const float* data_nchw, cudaStream_t s) {
                     break;
                 }
                 if (!(c.k == 1 && c.stride == 1)) launch_im2col(t, c, ib, ob, s);
-                run_gemm(t, c.g_fwd, 0, s);
+                if (t->conv_fdefer[L.conv] < 0) run_gemm(t, c.g_fwd, 0, s);       // else: with its group, before the first reader
             } else if (tcp && c.narrow) {
                 narrow_fwd_kernel<<<std::min<long>((out_px + 7) / 8, 148 * 8), 256, (size_t)c.Cin * c.Cout * 4, s>>>(
                     as<bf16>(bdata(t, ib)), ib.ldc, t->params + c.w_off, c.ldw, t->params + c.b_off, as<bf16>(bdata(t, ob)), ob.ldc, (unsigned)out_px,
