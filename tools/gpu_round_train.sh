@@ -18,13 +18,13 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-
   python tools/profile_train.py bf16 > gpurun_out/${tag}_ncu_train.log 2>&1
 echo "ncu launches rc=$?"
 python tools/ncu_by_kernel.py gpurun_out/${tag}_train_step_bf16_launches.csv > gpurun_out/${tag}_train_step_bf16_by_kernel.txt
-timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:gemm_tc -c 6 -o gpurun_out/${tag}_gemm_fwd -f \
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"gemm_tc|kgemm_group|wgrad_group" -c 10 -o gpurun_out/${tag}_gemm_fwd -f \
   python tools/profile_train.py bf16 > gpurun_out/${tag}_ncu_gemm_fwd.log 2>&1
 echo "ncu gemm fwd rc=$?"
 python tools/ncu_summary.py gpurun_out/${tag}_gemm_fwd.ncu-rep gpurun_out/${tag}_gemm_tc_forward_ncu_full.csv
 python tools/ncu_stalls.py gpurun_out/${tag}_gemm_fwd.ncu-rep > gpurun_out/${tag}_gemm_tc_forward_stalls.txt 2>&1
 rm -f gpurun_out/${tag}_gemm_fwd.ncu-rep
-timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:gemm_tc --launch-skip 57 -c 8 -o gpurun_out/${tag}_gemm_bwd -f \
+timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"gemm_tc|kgemm_group|wgrad_group" --launch-skip 21 -c 14 -o gpurun_out/${tag}_gemm_bwd -f \
   python tools/profile_train.py bf16 > gpurun_out/${tag}_ncu_gemm_bwd.log 2>&1
 echo "ncu gemm bwd rc=$?"
 python tools/ncu_summary.py gpurun_out/${tag}_gemm_bwd.ncu-rep gpurun_out/${tag}_gemm_tc_backward_ncu_full.csv
