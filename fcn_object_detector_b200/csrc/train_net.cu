@@ -646,6 +646,44 @@ __global__ void im2col_kernel(const bf16* __restrict__ x, int ldi, bf16* __restr
     *reinterpret_cast<uint4*>(col + m * ldk + j) = v;
 }
 
+// im2col of a dense 3-channel image (conv1): block = one output row.  The K input rows it reads are staged in shared memory with
+// zeroed borders (coalesced 16-byte loads; element (iw, c) of a row at lp + 3 * iw + c), so that a column row is K runs of 3K
+// consecutive shared-memory elements and no thread gathers from global memory.  Writes the same bytes as im2col_kernel<1, K>.
+template <int K>
+__global__ void __launch_bounds__(256) im2col_c3_kernel(const bf16* __restrict__ x, bf16* __restrict__ col, int ldk, int H, int W, int Wo,
+                                                         int stride, int pad, int lp, int pitch, unsigned m_per_row) {
+    pdl_wait();
+    pdl_trigger();
+    extern __shared__ __align__(16) unsigned char im2col_c3_smem[];
+    bf16* sm = reinterpret_cast<bf16*>(im2col_c3_smem);
+    const int oh = blockIdx.x, n = blockIdx.y, Ho = gridDim.x;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < K * (pitch / 8); i += 256) reinterpret_cast<uint4*>(sm)[i] = z;
+    __syncthreads();
+    const int wv = W * 3 / 8;
+    for (int i = threadIdx.x; i < K * wv; i += 256) {
+        const int r = i / wv, v = i - r * wv, ih = oh * stride - pad + r;
+        if (ih >= 0 && ih < H)
+            *reinterpret_cast<uint4*>(sm + r * pitch + lp + v * 8) = *reinterpret_cast<const uint4*>(x + (size_t)(n * H + ih) * W * 3 + v * 8);
+    }
+    __syncthreads();
+    const unsigned per_row = (unsigned)ldk / 8u;
+    const int kc = K * K * 3;
+    bf16* out = col + (size_t)(n * Ho + oh) * Wo * ldk;
+    for (unsigned idx = threadIdx.x; idx < (unsigned)Wo * per_row; idx += 256) {
+        const int ow = (int)div_fast(idx, m_per_row), j = (int)(idx - (unsigned)ow * per_row) * 8;
+        const bf16* src = sm + lp + (ow * stride - pad) * 3;
+        uint4 v = z;
+        bf16* e = reinterpret_cast<bf16*>(&v);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int jj = j + q;
+            if (jj < kc) { const int r = jj / (3 * K); e[q] = src[r * pitch + (jj - r * 3 * K)]; }
+        }
+        *reinterpret_cast<uint4*>(out + (size_t)ow * ldk + j) = v;
+    }
+}
+
 // data gradient of a stride-1 k x k convolution from the column gradient dcol = dY * W (the adjoint of im2col):
 // dx[n][h][w][c] (+)= sum_{r,s} dcol[(n, h + pad - r, w + pad - s)][(r*k + s)*Cin + c]; 8 channels per thread, grid (., H, N).
 template <int K>
@@ -1603,6 +1641,20 @@ void launch_im2col_k(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TB
 }
 void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
     FCNOD_CHECK(ob.W * (c.ldk / 8) < 65536 && c.ldk < 65536, "trainer: im2col row too long for the fast division");
+    static int c3 = -1;        // FCNOD_TRAIN_IM2COL_C3=0: the generic gather for the 3-channel image too
+    if (c3 < 0) { const char* e = getenv("FCNOD_TRAIN_IM2COL_C3"); c3 = (e && e[0] == '0') ? 0 : 1; }
+    if (c3 && c.k == 7 && c.Cin == 3 && ib.ldc == 3 && ib.c_off == 0 && (ib.W * 3) % 8 == 0 && t->batch < 65536) {
+        const int lp = (c.pad * 3 + 7) / 8 * 8;
+        const int reach = std::max(ib.W, (ob.W - 1) * c.stride - c.pad + c.k);
+        const int pitch = (lp + reach * 3 + 7) / 8 * 8;
+        const size_t smem = (size_t)c.k * pitch * sizeof(bf16);
+        if (smem <= 48 * 1024) {
+            launch_k(im2col_c3_kernel<7>, dim3(ob.H, t->batch), 256, smem, s, as<bf16>(bdata(t, ib)), c.d_col, c.ldk, ib.H, ib.W, ob.W, c.stride, c.pad,
+                     lp, pitch, div_magic((unsigned)c.ldk / 8u));
+            FCNOD_CUDA(cudaGetLastError());
+            return;
+        }
+    }
     if (c.Cin % 8 == 0 && ib.ldc % 8 == 0 && ib.c_off % 8 == 0) launch_im2col_k<8>(t, c, ib, ob, s);
     else launch_im2col_k<1>(t, c, ib, ob, s);
 }
@@ -1892,6 +1944,10 @@ int fcnod_trainer_destroy(fcnod_trainer* t) {
         for (int j = 0; j < t->world && t->peers_open; ++j)
             if (j != t->rank) { cudaIpcCloseMemHandle(t->peer_params[j]); cudaIpcCloseMemHandle(t->peer_grads[j]); }
         for (size_t i = 0; i < t->allocs.size(); ++i) cudaFree(t->allocs[i]);
+        // timing-mode events (created lazily by fcnod_trainer_set_timing / the first timed grouped launch)
+        for (size_t i = 0; i < t->ev0.size(); ++i) { if (t->ev0[i]) cudaEventDestroy(t->ev0[i]); if (t->ev1[i]) cudaEventDestroy(t->ev1[i]); }
+        for (size_t i = 0; i < t->wgroups.size(); ++i) { if (t->wgroups[i].e0) cudaEventDestroy(t->wgroups[i].e0); if (t->wgroups[i].e1) cudaEventDestroy(t->wgroups[i].e1); }
+        for (size_t i = 0; i < t->kgroups.size(); ++i) { if (t->kgroups[i].e0) cudaEventDestroy(t->kgroups[i].e0); if (t->kgroups[i].e1) cudaEventDestroy(t->kgroups[i].e1); }
         if (t->stream) cudaStreamDestroy(t->stream);
         delete t;
     }

@@ -320,6 +320,48 @@ def test_three_class_network_of_train_val2(tmp_path):
         assert abs(losses['bf16'][k] - losses['fp32'][k]) < 2e-2 * max(1.0, abs(losses['fp32'][k])), (k, losses)
 
 
+_IM2COL_SCRIPT = r"""
+import sys
+import numpy as np
+import torch
+sys.path.insert(0, %(root)r)
+from fcn_object_detector_b200.trainer import Solver
+from tests.test_trainer_gpu import _inputs, N, H, W
+proto, cm, sp, out = sys.argv[1:5]
+data, grids = _inputs(0)
+dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids]
+s = Solver(proto, cm, batch=N, height=H, width=W, solver_prototxt=sp, seed=7, precision='bf16')
+s.forward_backward_device([t.data_ptr() for t in dev])
+torch.cuda.synchronize()
+np.savez(out, conv1=s.blob('conv1/7x7_s2'), cov=s.blob('coverage'), gw=s.param('conv1/7x7_s2', 0, 'grad'), gb=s.param('conv1/7x7_s2', 1, 'grad'))
+s.close()
+"""
+
+
+def test_staged_im2col_of_the_image_writes_what_the_generic_gather_writes(train_files, tmp_path):
+    """conv1's column matrix: im2col_c3_kernel (input rows staged in shared memory) against im2col_kernel<1, 7>
+    (FCNOD_TRAIN_IM2COL_C3=0), one process each since the knob is read once.  The forward is deterministic, so conv1's output
+    and the network's coverage map must be bit-identical; conv1's weight gradient (the GEMM over the kept column matrix,
+    fp32 reduction order not fixed) to 1e-5."""
+    import subprocess
+    import sys
+    from tests.util import ROOT
+    proto, cm, sp = train_files
+    script = tmp_path / 'im2col_variant.py'
+    script.write_text(_IM2COL_SCRIPT % {'root': ROOT})
+    got = {}
+    for knob in ('0', '1'):
+        out = str(tmp_path / ('im2col_%s.npz' % knob))
+        env = dict(os.environ, FCNOD_TRAIN_IM2COL_C3=knob)
+        r = subprocess.run([sys.executable, str(script), proto, cm, sp, out], cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        got[knob] = np.load(out)
+    assert np.abs(got['1']['conv1']).max() > 0
+    assert np.array_equal(got['0']['conv1'], got['1']['conv1'])
+    assert np.array_equal(got['0']['cov'], got['1']['cov'])
+    assert rel_err(got['1']['gw'], got['0']['gw']) < 1e-5 and rel_err(got['1']['gb'], got['0']['gb']) < 1e-5
+
+
 def test_peer_memory_update_matches_the_nccl_path_on_two_gpus():
     """Data-parallel update: reduce-scatter + ADAM + all-gather in one kernel over NVLink peer memory (CUDA IPC) against
     NCCL all-reduce + update, two ranks under torchrun (tools/dp_check.py): replicas bit-identical, reduced gradients of the
