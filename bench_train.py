@@ -242,7 +242,9 @@ def run_ours(args, section=False):
         n_conv, n_pool, n_lrn = 59, 12, 2
         launches = (1 + n_conv + n_pool + n_lrn + 2 + 1) + 6 + (5 * n_conv - 2 - 2 + n_pool + n_lrn + 1 + 1) + 1 + 1 + 4
         if prec == 'bf16':
-            launches = 228 + 4        # the ncu launch list of one bf16 step (profiles/r02zz_train_step_bf16_launches.csv) + the layer's 4
+            # the ncu launch list of one bf16 step (profiles/r02zz_train_step_bf16_launches.csv: 228) + the layer's 4; since then the
+            # ReLU / bias-gradient pass runs once per Concat blob instead of once per convolution: 9 blobs x (4 - 1) launches fewer
+            launches = 228 + 4 - (0 if os.environ.get('FCNOD_TRAIN_RB_FUSE', '1') == '0' else 27)
         flop = 3 * 2 * CONV_MACS_PER_FRAME * B            # forward + data gradient + weight gradient (conv1 has no dgrad: -4%)
         from bench import peaks
         pk = peaks()

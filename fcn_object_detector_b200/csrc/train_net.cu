@@ -485,8 +485,12 @@ __global__ void pool_bwd8_kernel(const bf16* __restrict__ dy, const uint8_t* __r
 
 // ReLU backward (in place on the convolution's top diff) and the bias gradient in one pass over dy: block = 8 channel groups
 // (64 channels) x 32 pixel lanes; db[c] += sum over the block's pixel chunk.  relu = 0: bias gradient only.
+// segs.n > 0: the blob is a Concat top written by several convolutions; channel cc belongs to the last segment whose c0 <= cc
+// and its bias gradient goes to that convolution's slot (db unused)
+struct RbSeg { int c0; float* db; };
+struct RbSegs { int n; RbSeg s[8]; };
 __global__ void __launch_bounds__(256) relu_bias8_kernel(const bf16* __restrict__ y, bf16* __restrict__ dy, unsigned npix, int C, int ldc,
-                                                          unsigned chunk, int relu, float* __restrict__ db) {
+                                                          unsigned chunk, int relu, float* __restrict__ db, RbSegs segs) {
     pdl_wait();
     pdl_trigger();
     __shared__ float red[32][65];
@@ -530,7 +534,16 @@ __global__ void __launch_bounds__(256) relu_bias8_kernel(const bf16* __restrict_
 #pragma unroll
         for (int j = 0; j < 32; ++j) a += red[j][tid];
         const int cc = blockIdx.x * 64 + tid;
-        if (cc < C) atomicAdd(db + cc, a);
+        if (cc < C) {
+            float* dst = db + cc;
+            if (segs.n > 0) {
+                int k = 0;
+#pragma unroll
+                for (int j = 1; j < 8; ++j) if (j < segs.n && cc >= segs.s[j].c0) k = j;
+                dst = segs.s[k].db + (cc - segs.s[k].c0);
+            }
+            atomicAdd(dst, a);
+        }
     }
 }
 
@@ -954,6 +967,11 @@ struct fcnod_trainer {
                     cudaEvent_t e0 = 0, e1 = 0; };
     std::vector<WGroup> wgroups;
     std::vector<int> conv_wgroup;             // per convolution: its group (-1: launched alone)
+    // ReLU mask + bias gradient of all the convolutions that write one Concat blob in one launch over the blob, at the first
+    // member the backward pass reaches (FCNOD_TRAIN_RB_FUSE)
+    struct RbGroup { int root = -1; RbSegs segs; bool done = false; };
+    std::vector<RbGroup> rb_groups;
+    std::vector<int> conv_rbgroup;            // per convolution: its group (-1: its own launch)
     // grouped K-major GEMMs (kgemm_group_kernel): the 1x1 convolutions that read the same blob -- their forward GEMMs launch
     // together at the first member, their data gradients (all accumulating into that blob's diff) at the last one reached
     struct KGroup { std::vector<int> convs; KGemmProblem* probs = 0; KGemmGroupParams gp; size_t smem = 0; int grid = 0; double flop = 0.0;
@@ -1364,6 +1382,8 @@ void run_gemm(fcnod_trainer* t, int id, int accum, cudaStream_t s) {
 // bf16 engine: scratch, bf16 weights and the three GEMM plans of every convolution (pointers are fixed for the trainer's life)
 void build_kgroups(fcnod_trainer* t);
 void build_fwd_deferral(fcnod_trainer* t);
+void build_rbgroups(fcnod_trainer* t);
+const bool kRbFuseDefault = true;        // measured 7.72 -> 7.56 ms per batch-32 step; FCNOD_TRAIN_RB_FUSE=0 reverts
 
 void build_tc(fcnod_trainer* t) {
     const int N = t->batch;
@@ -1472,6 +1492,46 @@ void build_tc(fcnod_trainer* t) {
     }
     build_kgroups(t);
     build_fwd_deferral(t);
+    build_rbgroups(t);
+}
+
+// Concat blobs all of whose slices are written by tensor-core convolutions with a ReLU: one ReLU / bias-gradient launch per blob
+void build_rbgroups(fcnod_trainer* t) {
+    t->conv_rbgroup.assign(t->convs.size(), -1);
+    const char* e = getenv("FCNOD_TRAIN_RB_FUSE");
+    if (!(e ? e[0] != '0' : kRbFuseDefault)) return;
+    std::map<int, std::vector<int> > by_root;          // concat blob -> layers writing its slices
+    for (size_t li = 0; li < t->layers.size(); ++li) {
+        const TLayer& L = t->layers[li];
+        if (L.skip || L.out < 0) continue;
+        const TBlob& ob = t->blobs[L.out];
+        if (ob.root >= 0 && ob.root != L.out) by_root[ob.root].push_back((int)li);
+    }
+    for (std::map<int, std::vector<int> >::iterator it = by_root.begin(); it != by_root.end(); ++it) {
+        const TBlob& rb = t->blobs[it->first];
+        std::vector<int>& ls = it->second;
+        if (ls.size() < 2 || ls.size() > 8 || rb.C % 8 != 0 || rb.ldc != rb.C || rb.c_off != 0) continue;
+        std::sort(ls.begin(), ls.end(), [&](int a, int b) { return t->blobs[t->layers[a].out].c_off < t->blobs[t->layers[b].out].c_off; });
+        bool ok = true;
+        int next = 0;
+        fcnod_trainer::RbGroup g;
+        g.root = it->first;
+        memset(&g.segs, 0, sizeof g.segs);
+        for (size_t i = 0; i < ls.size() && ok; ++i) {
+            const TLayer& L = t->layers[ls[i]];
+            const TBlob& ob = t->blobs[L.out];
+            ok = L.def.type == L_CONV && L.conv >= 0 && L.relu && t->convs[L.conv].tc && ob.c_off == next && ob.C == t->convs[L.conv].Cout &&
+                 ob.C % 8 == 0 && ob.ldc == rb.C && ob.buf == rb.buf;
+            if (!ok) break;
+            g.segs.s[i].c0 = ob.c_off;
+            g.segs.s[i].db = t->grads + t->convs[L.conv].b_off;
+            next += ob.C;
+        }
+        if (!ok || next != rb.C) continue;
+        g.segs.n = (int)ls.size();
+        for (size_t i = 0; i < ls.size(); ++i) t->conv_rbgroup[t->layers[ls[i]].conv] = (int)t->rb_groups.size();
+        t->rb_groups.push_back(g);
+    }
 }
 
 int build_kgroup(fcnod_trainer* t, const std::vector<int>& convs, bool dgrad) {
@@ -1750,6 +1810,7 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
     const int N = t->batch;
     const bool tcp = sizeof(T) == 2;
     for (size_t b = 0; b < t->blobs.size(); ++b) t->blobs[b].diff_written = false;
+    for (size_t g = 0; g < t->rb_groups.size(); ++g) t->rb_groups[g].done = false;
     root_of(t, t->cov_blob).diff_written = true;      // written by the head
     root_of(t, t->box_blob).diff_written = true;
     for (size_t li = t->layers.size(); li-- > 0;) {
@@ -1811,9 +1872,24 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
                                                  // channel group at 28x28 instead of 98 at 256 -- measured 7.79 -> 7.74 ms per step)
                 if (!min_chunk) { const char* e = getenv("FCNOD_TRAIN_RB_CHUNK"); min_chunk = e ? std::max(64, atoi(e) / 64 * 64) : 64; }
                 const unsigned chunk = (unsigned)std::max<long>(min_chunk, (out_px + 148 * 16 - 1) / (148 * 16));      // ~16 blocks per SM: bytes in flight
-                dim3 grid((unsigned)((c.Cout + 63) / 64), (unsigned)((out_px + chunk - 1) / chunk));
-                launch_k(relu_bias8_kernel, grid, dim3(8, 32), 0, s, as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), (unsigned)out_px, c.Cout, ob.ldc, chunk,
-                                                              L.relu ? 1 : 0, t->grads + c.b_off);
+                const int rg = t->conv_rbgroup.empty() ? -1 : t->conv_rbgroup[L.conv];
+                if (rg >= 0) {
+                    // the whole Concat blob at the first of its convolutions reached: every consumer of the blob has run
+                    fcnod_trainer::RbGroup& g = t->rb_groups[rg];
+                    if (!g.done) {
+                        const TBlob& rb = t->blobs[g.root];
+                        dim3 grid((unsigned)((rb.C + 63) / 64), (unsigned)((out_px + chunk - 1) / chunk));
+                        launch_k(relu_bias8_kernel, grid, dim3(8, 32), 0, s, as<bf16>(bdata(t, rb)), as<bf16>(bdiff(t, rb)), (unsigned)out_px, rb.C, rb.ldc, chunk,
+                                                                      1, t->grads, g.segs);
+                        g.done = true;
+                    }
+                } else {
+                    RbSegs none;
+                    none.n = 0;
+                    dim3 grid((unsigned)((c.Cout + 63) / 64), (unsigned)((out_px + chunk - 1) / chunk));
+                    launch_k(relu_bias8_kernel, grid, dim3(8, 32), 0, s, as<bf16>(bdata(t, ob)), as<bf16>(bdiff(t, ob)), (unsigned)out_px, c.Cout, ob.ldc, chunk,
+                                                                  L.relu ? 1 : 0, t->grads + c.b_off, none);
+                }
                 FCNOD_CUDA(cudaGetLastError());
             } else {
                 if (L.relu) {

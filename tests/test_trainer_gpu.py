@@ -333,7 +333,8 @@ dev = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (data,) + grids
 s = Solver(proto, cm, batch=N, height=H, width=W, solver_prototxt=sp, seed=7, precision='bf16')
 s.forward_backward_device([t.data_ptr() for t in dev])
 torch.cuda.synchronize()
-np.savez(out, conv1=s.blob('conv1/7x7_s2'), cov=s.blob('coverage'), gw=s.param('conv1/7x7_s2', 0, 'grad'), gb=s.param('conv1/7x7_s2', 1, 'grad'))
+np.savez(out, conv1=s.blob('conv1/7x7_s2'), cov=s.blob('coverage'), gw=s.param('conv1/7x7_s2', 0, 'grad'), gb=s.param('conv1/7x7_s2', 1, 'grad'),
+         allb=np.concatenate([s.param(n, 1, 'grad') for n in s.layers]), w3a=s.param('inception_3a/3x3', 0, 'grad'), w5b=s.param('inception_5b/pool_proj', 0, 'grad'))
 s.close()
 """
 
@@ -360,6 +361,29 @@ def test_staged_im2col_of_the_image_writes_what_the_generic_gather_writes(train_
     assert np.array_equal(got['0']['conv1'], got['1']['conv1'])
     assert np.array_equal(got['0']['cov'], got['1']['cov'])
     assert rel_err(got['1']['gw'], got['0']['gw']) < 1e-5 and rel_err(got['1']['gb'], got['0']['gb']) < 1e-5
+
+
+def test_relu_and_bias_gradient_pass_per_concat_blob_equals_the_pass_per_convolution(train_files, tmp_path):
+    """FCNOD_TRAIN_RB_FUSE=1 (one ReLU-mask / bias-gradient launch over a Concat blob, bias sums routed to the writing
+    convolutions by a segment table) against one launch per convolution: every bias gradient of the network and the weight
+    gradients of three layers (which see every masked dY below them) to 1e-5 (fp32 atomics, order not fixed)."""
+    import subprocess
+    import sys
+    from tests.util import ROOT
+    proto, cm, sp = train_files
+    script = tmp_path / 'rb_variant.py'
+    script.write_text(_IM2COL_SCRIPT % {'root': ROOT})
+    got = {}
+    for knob in ('0', '1'):
+        out = str(tmp_path / ('rb_%s.npz' % knob))
+        env = dict(os.environ, FCNOD_TRAIN_RB_FUSE=knob)
+        r = subprocess.run([sys.executable, str(script), proto, cm, sp, out], cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        got[knob] = np.load(out)
+    assert np.abs(got['0']['allb']).max() > 0
+    for k in ('allb', 'gw', 'w3a', 'w5b'):
+        assert rel_err(got['1'][k], got['0'][k]) < 1e-5, (k, rel_err(got['1'][k], got['0'][k]))
+    assert np.array_equal(got['0']['cov'], got['1']['cov'])
 
 
 def test_peer_memory_update_matches_the_nccl_path_on_two_gpus():
