@@ -22,6 +22,7 @@
 // layout, so the gradient all-reduce of a multi-GPU step is one collective over one contiguous buffer and the update is one
 // launch.  Padding entries have zero gradient and stay zero.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -1230,7 +1231,7 @@ void build_trainer(fcnod_trainer* t, const WeightMap& weights) {
 // Opt-in (FCNOD_TRAIN_PDL=1): measured neutral on the training step (10.23 ms with, 10.12 ms without: the gaps between the 373
 // launches of a step add up to 0.3 ms only); without it the same kernels launch fully serialised and the wait is a no-op.
 inline bool pdl_enabled() {
-    static int on = -1;
+    static std::atomic<int> on(-1);
     if (on < 0) { const char* e = getenv("FCNOD_TRAIN_PDL"); on = (e && e[0] == '1') ? 1 : 0; }
     return on != 0;
 }
@@ -1350,7 +1351,7 @@ int add_plan(fcnod_trainer* t, const GemmPlan& g, int kind = 0) {
 }
 
 void run_plan(const GemmPlan& g, int accum, cudaStream_t s) {
-    static bool attr[64] = {};       // per device (function attributes belong to a context); a race writes the same value twice
+    static std::atomic<bool> attr[64];       // per device (function attributes belong to a context); a race writes the same value twice
     int dev = 0;
     FCNOD_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr[dev]) {
@@ -1643,7 +1644,7 @@ void build_fwd_deferral(fcnod_trainer* t) {
 }
 
 void launch_kgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
-    static bool attr[64] = {};
+    static std::atomic<bool> attr[64];
     int dev = 0;
     FCNOD_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr[dev]) {
@@ -1661,7 +1662,7 @@ void launch_kgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
 }
 
 void launch_wgroup(fcnod_trainer* t, int gi, cudaStream_t s) {
-    static bool attr[64] = {};
+    static std::atomic<bool> attr[64];
     int dev = 0;
     FCNOD_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr[dev]) {
@@ -1706,7 +1707,7 @@ void launch_im2col_k(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TB
 }
 void launch_im2col(fcnod_trainer* t, const TConv& c, const TBlob& ib, const TBlob& ob, cudaStream_t s) {
     FCNOD_CHECK(ob.W * (c.ldk / 8) < 65536 && c.ldk < 65536, "trainer: im2col row too long for the fast division");
-    static int c3 = -1;        // FCNOD_TRAIN_IM2COL_C3=0: the generic gather for the 3-channel image too
+    static std::atomic<int> c3(-1);      // FCNOD_TRAIN_IM2COL_C3=0: the generic gather for the 3-channel image too
     if (c3 < 0) { const char* e = getenv("FCNOD_TRAIN_IM2COL_C3"); c3 = (e && e[0] == '0') ? 0 : 1; }
     if (c3 && c.k == 7 && c.Cin == 3 && ib.ldc == 3 && ib.c_off == 0 && (ib.W * 3) % 8 == 0 && t->batch < 65536) {
         const int lp = (c.pad * 3 + 7) / 8 * 8;
@@ -1868,7 +1869,7 @@ void backward(fcnod_trainer* t, cudaStream_t s) {
             T* dy = as<T>(bdiff(t, ob));
             if (tcp && ob.C % 8 == 0 && ob.ldc % 8 == 0 && ob.c_off % 8 == 0) {
                 // ReLU mask and bias gradient in one pass
-                static long min_chunk = 0;       // FCNOD_TRAIN_RB_CHUNK: pixels per block of the small layers (multiple of 64; 64: 392 blocks per
+                static std::atomic<long> min_chunk(0);      // FCNOD_TRAIN_RB_CHUNK: pixels per block of the small layers (multiple of 64; 64: 392 blocks per
                                                  // channel group at 28x28 instead of 98 at 256 -- measured 7.79 -> 7.74 ms per step)
                 if (!min_chunk) { const char* e = getenv("FCNOD_TRAIN_RB_CHUNK"); min_chunk = e ? std::max(64, atoi(e) / 64 * 64) : 64; }
                 const unsigned chunk = (unsigned)std::max<long>(min_chunk, (out_px + 148 * 16 - 1) / (148 * 16));      // ~16 blocks per SM: bytes in flight
