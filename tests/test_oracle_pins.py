@@ -307,3 +307,105 @@ def test_crop_and_flip_fuzz_against_python2_transliteration():
         assert script.bounds[0] == (0, bx) and script.bounds[1] == (0, by)
         checked += 1
     assert checked == 4000
+
+
+# ============================================================================ 4. the training head (train_val.prototxt:36-72,2237-2281)
+def _head_case():
+    """Two frames, one grid cell, one class.  Frame 0 is a foreground cell, frame 1 a background cell (coverage-block 0:
+    its bbox prediction is masked out and its labels are zero)."""
+    f = np.float32
+    coverage = np.array([0.8, 0.3], f).reshape(2, 1, 1, 1)
+    cvg_label = np.array([1.0, 0.0], f).reshape(2, 1, 1, 1)
+    bboxes = np.array([[10, -4, 6, 2], [7, 7, 7, 7]], f).reshape(2, 4, 1, 1)
+    bbox_label = np.array([[8, -8, 6, 4], [0, 0, 0, 0]], f).reshape(2, 4, 1, 1)
+    size_block = np.array([[0.1, 0.05, 0.1, 0.05], [0, 0, 0, 0]], f).reshape(2, 4, 1, 1)
+    obj_block = np.array([[0.5] * 4, [0] * 4], f).reshape(2, 4, 1, 1)
+    cvg_block = np.array([[1] * 4, [0] * 4], f).reshape(2, 4, 1, 1)
+    return coverage, bboxes, cvg_label, bbox_label, size_block, obj_block, cvg_block
+
+
+def test_known_answer_training_head_losses_and_gradients():
+    """Derivation (Caffe's EuclideanLoss: sum (a-b)^2 / (2 num); NVCaffe's L1Loss: sum |a-b| / num; loss_weight 2 on the latter;
+    Eltwise PROD chains of train_val.prototxt:53-72,2237-2266):
+      coverage loss = ((0.8-1)^2 + (0.3-0)^2) / (2*2)                     = (0.04 + 0.09) / 4 = 0.0325
+      frame 0 pred   = bboxes * 1 * size * obj = [10,-4,6,2] * [.1,.05,.1,.05] * .5 = [0.5, -0.1, 0.3, 0.05]
+      frame 0 target = label * size * obj      = [8,-8,6,4]  * [.1,.05,.1,.05] * .5 = [0.4, -0.2, 0.3, 0.10]
+      |pred - target| = [0.1, 0.1, 0, 0.05] -> 0.25; frame 1 is masked -> 0;  bbox loss = 0.25 / 2 = 0.125
+      total = 0.0325 + 2 * 0.125 = 0.2825
+      d coverage = (a - b) / num = [-0.1, 0.15]
+      d bboxes (frame 0) = 2 * sign(pred - target) / num * obj * size * mask = [1, 1, 0, -1] * 0.5 * [.1,.05,.1,.05]
+                         = [0.05, 0.025, 0, -0.025]   (sign(0) = 0, as caffe_cpu_sign gives);  frame 1: 0"""
+    from oracle import train_ref
+    out = train_ref.head_forward(*_head_case())
+    assert abs(out['loss_coverage'] - 0.0325) < 1e-7 and abs(out['loss_bbox'] - 0.125) < 1e-7 and abs(out['loss'] - 0.2825) < 2e-7
+    assert np.allclose(out['d_coverage'].reshape(-1), [-0.1, 0.15], atol=1e-7)
+    assert np.allclose(out['d_bboxes'][0].reshape(-1), [0.05, 0.025, 0.0, -0.025], atol=1e-8)
+    assert np.array_equal(out['d_bboxes'][1], np.zeros((4, 1, 1), np.float32))
+
+
+def test_training_head_gradients_are_the_derivative_of_its_loss():
+    """Central differences of the head's own loss (piecewise linear + quadratic: exact away from the kinks) against the
+    analytic gradients it returns -- independent of the backward formulas of the module header."""
+    from oracle import train_ref
+    rs = np.random.RandomState(4)
+    N, C, G = 3, 1, 4
+    f = np.float32
+    coverage = rs.uniform(0.05, 0.95, (N, C, G, G)).astype(f)
+    bboxes = rs.uniform(-30, 30, (N, 4 * C, G, G)).astype(f)
+    cvg_label = (rs.uniform(0, 1, (N, C, G, G)) > 0.5).astype(f)
+    blk = np.repeat(cvg_label, 4, axis=1)
+    bbox_label = (rs.uniform(-30, 30, (N, 4 * C, G, G)) * blk).astype(f)
+    size_block = (blk * rs.uniform(0.01, 0.1, (N, 4 * C, G, G))).astype(f)
+    obj_block = (blk * 0.25).astype(f)
+    args = [coverage, bboxes, cvg_label, bbox_label, size_block, obj_block, blk]
+    out = train_ref.head_forward(*args)
+
+    def loss_with(i, arr):
+        a = list(args)
+        a[i] = arr
+        return train_ref.head_forward(*a)['loss']
+
+    for i, key, eps in ((0, 'd_coverage', 1e-2), (1, 'd_bboxes', 0.5)):
+        base = args[i]
+        for idx in [tuple(rs.randint(0, s) for s in base.shape) for _ in range(40)]:
+            if i == 1:      # stay off the |.| kink: the step must not cross pred == target
+                d = ((base[idx] - bbox_label[idx]) * size_block[idx] * obj_block[idx])
+                if blk[idx] and abs(d) <= 2 * eps * size_block[idx] * obj_block[idx]:
+                    continue
+            p, m = base.astype(np.float64).copy(), base.astype(np.float64).copy()
+            p[idx] += eps
+            m[idx] -= eps
+            num = (loss_with(i, p.astype(f)) - loss_with(i, m.astype(f))) / (float(p.astype(f)[idx]) - float(m.astype(f)[idx]))
+            assert abs(num - out[key][idx]) < 2e-4 * max(1.0, abs(num)), (key, idx, num, out[key][idx])
+
+
+def test_autograd_oracle_and_numpy_head_agree_through_a_two_layer_network():
+    """oracle/train_net_ref.py (torch autograd over the restated graph) against oracle/train_ref.py (numpy, explicit backward)
+    on a network small enough to follow by hand: data -> 1x1 conv -> Sigmoid = coverage, data -> 1x1 conv = bboxes.  Losses and
+    the gradients reaching coverage / bboxes must agree, and the convolution's weight gradient must be the plain sum
+    dW[o][c] = sum_{n,h,w} dY[n][o][h][w] * X[n][c][h][w] of that gradient (db = sum dY)."""
+    from oracle import train_net_ref, train_ref
+    rs = np.random.RandomState(6)
+    N, G = 2, 3
+    f = np.float32
+    layers = [dict(name='cvg', type='Convolution', bottom=['data'], top=['cvg_raw'], stride=1, pad=0, kernel=1),
+              dict(name='sig', type='Sigmoid', bottom=['cvg_raw'], top=['coverage']),
+              dict(name='box', type='Convolution', bottom=['data'], top=['bboxes'], stride=1, pad=0, kernel=1)]
+    weights = {'cvg': [rs.normal(0, 0.5, (1, 3, 1, 1)).astype(f), np.zeros(1, f)],
+               'box': [rs.normal(0, 2.0, (4, 3, 1, 1)).astype(f), rs.normal(0, 1, 4).astype(f)]}
+    data = rs.uniform(-1, 1, (N, 3, G, G)).astype(f)
+    cvg_label = (rs.uniform(0, 1, (N, 1, G, G)) > 0.4).astype(f)
+    blk = np.repeat(cvg_label, 4, axis=1)
+    grids = (cvg_label, (rs.uniform(-3, 3, (N, 4, G, G)) * blk).astype(f), (blk * 0.125).astype(f), (blk * 0.5).astype(f), blk)
+    ref = train_net_ref.forward_backward(layers, weights, data, grids, want=('coverage', 'bboxes'))
+    head = train_ref.head_forward(ref['blobs']['coverage'], ref['blobs']['bboxes'], *grids)
+    assert abs(ref['loss_bbox'] - head['loss_bbox']) < 1e-6 and abs(ref['loss_coverage'] - head['loss_coverage']) < 1e-6
+    assert np.allclose(ref['blob_grads']['coverage'], head['d_coverage'], atol=1e-7)
+    assert np.allclose(ref['blob_grads']['bboxes'], head['d_bboxes'], atol=1e-7)
+    dW = np.einsum('nohw,nchw->oc', head['d_bboxes'].astype(np.float64), data.astype(np.float64))
+    assert np.allclose(ref['grads']['box'][0].reshape(4, 3), dW, atol=1e-6)
+    assert np.allclose(ref['grads']['box'][1], head['d_bboxes'].astype(np.float64).sum(axis=(0, 2, 3)), atol=1e-6)
+    # through the sigmoid: d raw = d coverage * y * (1 - y)
+    y = ref['blobs']['coverage'].astype(np.float64)
+    d_raw = head['d_coverage'] * y * (1 - y)
+    assert np.allclose(ref['grads']['cvg'][0].reshape(1, 3), np.einsum('nohw,nchw->oc', d_raw, data.astype(np.float64)), atol=1e-6)
