@@ -12,7 +12,12 @@ unpinned" at the upstream boundary.  What can be done is to stop it from being a
   3. a FUZZ of `oracle.layer_ref.crop_window` / `flip_rect` against a line-for-line Python-3 transliteration of
      argumentation_engine.py:157-173,193-236,241-267 whose `/` is Python 2's (floor on two ints, decided at run time by
      the operand types) and whose `random.*` calls replay a script -- the oracle decides statically where `//` applies,
-     the transliteration does not.
+     the transliteration does not;
+  4. the TRAINING HEAD (train_val.prototxt:36-72,2237-2281): a hand-derived known answer for both losses and their
+     gradients, central differences of the loss against the analytic gradients, and the autograd oracle
+     (train_net_ref) against the numpy head (train_ref) through a two-layer network with the weight gradients summed by hand;
+  5. the BACKWARD rules the training oracle leans on: Caffe's first-maximum routing of the pooling gradient (known answer
+     with ties, and the positions against a per-window loop), the LRN backward formula of lrn_layer.cpp in float64 loops.
 """
 import math
 import random
@@ -409,3 +414,86 @@ def test_autograd_oracle_and_numpy_head_agree_through_a_two_layer_network():
     y = ref['blobs']['coverage'].astype(np.float64)
     d_raw = head['d_coverage'] * y * (1 - y)
     assert np.allclose(ref['grads']['cvg'][0].reshape(1, 3), np.einsum('nohw,nchw->oc', d_raw, data.astype(np.float64)), atol=1e-6)
+
+
+# ============================================================================ 5. max-pool routing and LRN backward of the training oracle
+def test_known_answer_first_maximum_routing_of_the_pooling_backward():
+    """Caffe's MAX pooling (pooling_layer.cpp) scans a window row-major and replaces the running maximum only on `>`, so
+    among equal values the FIRST one keeps the gradient.  5x5 input, 3x3 / 2 windows, no pad, ceil mode -> 2x2 outputs with
+    window origins (0,0), (0,2), (2,0), (2,2).
+      constant input: every window selects its own origin -> position 0; with top gradient [[1,2],[3,4]] the bottom gradient
+      is 1 at (0,0), 2 at (0,2), 3 at (2,0), 4 at (2,2), zero elsewhere.
+      a 9 planted at (2,2) (shared by all four windows): positions 8, 6, 2, 0 (= dh*3 + dw from each origin); its gradient is
+      1 + 2 + 3 + 4 = 10."""
+    import torch
+    from oracle import train_net_ref
+    x = np.ones((1, 1, 5, 5), np.float32)
+    y, idx = train_net_ref.caffe_pool_argmax(x, 3, 2, 0)
+    assert y.shape == (1, 1, 2, 2) and np.array_equal(idx.reshape(-1), [0, 0, 0, 0])
+    top = torch.tensor([[1.0, 2.0], [3.0, 4.0]]).view(1, 1, 2, 2)
+    xt = torch.tensor(x, requires_grad=True)
+    (train_net_ref.max_pool_routed(xt, idx, 3, 2, 0) * top).sum().backward()
+    want = np.zeros((5, 5), np.float32)
+    want[0, 0], want[0, 2], want[2, 0], want[2, 2] = 1, 2, 3, 4
+    assert np.array_equal(xt.grad.numpy()[0, 0], want)
+    x[0, 0, 2, 2] = 9
+    y, idx = train_net_ref.caffe_pool_argmax(x, 3, 2, 0)
+    assert np.array_equal(y.reshape(-1), [9, 9, 9, 9]) and np.array_equal(idx.reshape(-1), [8, 6, 2, 0])
+    xt = torch.tensor(x, requires_grad=True)
+    out = train_net_ref.max_pool_routed(xt, idx, 3, 2, 0)
+    assert np.array_equal(out.detach().numpy().reshape(-1), [9, 9, 9, 9])
+    (out * top).sum().backward()
+    want = np.zeros((5, 5), np.float32)
+    want[2, 2] = 10
+    assert np.array_equal(xt.grad.numpy()[0, 0], want)
+
+
+def test_pool_argmax_agrees_with_the_forward_oracle_and_with_a_loop_restatement():
+    """caffe_pool_argmax's values equal net_ref.max_pool_caffe's on the three pooling geometries of the network (3x3/2 pad 0
+    ceil mode, 3x3/1 pad 1), and its positions equal a plain per-window loop with Caffe's clipping and `>` rule, ties included
+    (inputs quantised to a few levels so that most windows hold ties)."""
+    import torch
+    from oracle import train_net_ref
+    rs = np.random.RandomState(8)
+    for (k, s, p, H, W) in ((3, 2, 0, 9, 12), (3, 2, 0, 8, 7), (3, 1, 1, 6, 5)):
+        x = rs.randint(0, 4, (2, 3, H, W)).astype(np.float32)
+        y, idx = train_net_ref.caffe_pool_argmax(x, k, s, p)
+        assert np.array_equal(y, net_ref.max_pool_caffe(torch.tensor(x), k, s, p).numpy())
+        oh, ow = y.shape[2:]
+        for n in range(2):
+            for c in range(3):
+                for ph in range(oh):
+                    for pw in range(ow):
+                        hs, ws = ph * s - p, pw * s - p
+                        he, we = min(hs + k, H + p), min(ws + k, W + p)
+                        best, pos = -np.inf, 0
+                        for h in range(max(hs, 0), min(he, H)):
+                            for w in range(max(ws, 0), min(we, W)):
+                                if x[n, c, h, w] > best:
+                                    best, pos = x[n, c, h, w], (h - hs) * k + (w - ws)
+                        assert (best, pos) == (y[n, c, ph, pw], idx[n, c, ph, pw]), (k, s, p, n, c, ph, pw)
+
+
+def test_known_answer_lrn_backward():
+    """Caffe's across-channel LRN, y_i = x_i * s_i^-beta with s_i = k + alpha/n * sum_{j in window(i)} x_j^2; by the chain rule
+      dx_i = dy_i * s_i^-beta - (2 alpha beta / n) * x_i * sum_{j : i in window(j)} dy_j * y_j / s_j
+    (lrn_layer.cpp's CrossChannelBackward).  Checked on 6 channels, n = 5 (windows clipped at the ends), against the formula
+    evaluated in float64 with explicit loops -- the oracle gets this backward from autograd over
+    torch.nn.functional.local_response_norm."""
+    import torch
+    import torch.nn.functional as F
+    rs = np.random.RandomState(9)
+    C, n, alpha, beta, k = 6, 5, 1e-2, 0.75, 1.0        # alpha large enough for the second term to matter
+    x = rs.uniform(-3, 3, (1, C, 1, 2))
+    dy = rs.uniform(-1, 1, (1, C, 1, 2))
+    xt = torch.tensor(x, dtype=torch.float64, requires_grad=True)
+    (F.local_response_norm(xt, n, alpha, beta, k) * torch.tensor(dy)).sum().backward()
+    want = np.zeros_like(x)
+    for w in range(2):
+        xs, ds = x[0, :, 0, w], dy[0, :, 0, w]
+        sc = np.array([k + alpha / n * sum(xs[j] ** 2 for j in range(max(0, i - 2), min(C, i + 3))) for i in range(C)])
+        ys = xs * sc ** -beta
+        for i in range(C):
+            acc = sum(ds[j] * ys[j] / sc[j] for j in range(max(0, i - 2), min(C, i + 3)))
+            want[0, i, 0, w] = ds[i] * sc[i] ** -beta - 2 * alpha * beta / n * xs[i] * acc
+    assert np.allclose(xt.grad.numpy(), want, rtol=1e-10, atol=1e-12)
